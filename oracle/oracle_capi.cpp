@@ -1,0 +1,122 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY.  C entry points (ctypes) over the CPU restatement.
+// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+// load this library.  PARITY UNPINNED against a reference binary (PCL/Eigen/GTSAM absent); pinned
+// against the reference's own test criteria (tests/test_oracle_*.py).
+#include "ndt_pclomp_align.hpp"
+#include "svn_ndt.hpp"
+
+using namespace oracle;
+
+extern "C" {
+
+// ------------------------------------------------------------------ small-linalg probes (tests)
+void orc_eig3_sym(const double* A, double* evals, double* evecs) { eig3_sym(A, evals, evecs); }
+void orc_mat3_inverse(const double* A, double* inv) { mat3_inverse(A, inv); }
+void orc_svd6_solve(const double* A, const double* b, double* x, double* S) { svd6_solve(A, b, x, S); }
+int orc_ldlt6_solve(const double* A, const double* b, double* x) { return ldlt6_solve(A, b, x) ? 1 : 0; }
+void orc_eig6_sym(const double* A, double* evals, double* evecs) { eig6_sym(A, evals, evecs); }
+void orc_pose_to_matrix_f(const double* p, float* T) { pose_to_matrix_f(p, T); }
+void orc_euler_angles_012_f(const float* T, float* e) { euler_angles_012_f(T, e); }
+
+// ------------------------------------------------------------------ voxel grid (both flavours)
+void* orc_grid_create(int flavour, float leaf, int min_pts, double eig_mult) {
+  VoxelGrid* g = new VoxelGrid();
+  g->flavour = flavour; g->set_leaf_size(leaf); g->min_points_per_voxel = min_pts; g->min_covar_eigvalue_mult = eig_mult;
+  return g;
+}
+void orc_grid_destroy(void* h) { delete static_cast<VoxelGrid*>(h); }
+int orc_grid_build(void* h, const float* xyz, size_t n, size_t stride_floats, int is_dense) {
+  return static_cast<VoxelGrid*>(h)->build(xyz, n, stride_floats, is_dense != 0);
+}
+void orc_grid_meta(void* h, int* min_b, int* max_b, int* div_b) {
+  VoxelGrid* g = static_cast<VoxelGrid*>(h);
+  for (int a = 0; a < 3; ++a) { min_b[a] = g->min_b[a]; max_b[a] = g->max_b[a]; div_b[a] = g->div_b[a]; }
+}
+size_t orc_grid_count(void* h) {
+  VoxelGrid* g = static_cast<VoxelGrid*>(h);
+  return g->flavour == FLAVOUR_PCLOMP ? g->leaves_map.size() : g->leaves_robin.size();
+}
+// Arrays sized by orc_grid_count: idx[V], n[V], mean[3V], cov[9V], icov[9V], evecs[9V], evals[3V]
+void orc_grid_export(void* h, long long* idx, int* n, double* mean, double* cov, double* icov, double* evecs, double* evals) {
+  VoxelGrid* g = static_cast<VoxelGrid*>(h);
+  std::vector<size_t> keys; std::vector<Leaf> leaves;
+  g->export_leaves(keys, leaves);
+  for (size_t v = 0; v < keys.size(); ++v) {
+    idx[v] = static_cast<long long>(keys[v]); n[v] = leaves[v].nr_points;
+    std::memcpy(mean + 3 * v, leaves[v].mean, 24); std::memcpy(cov + 9 * v, leaves[v].cov, 72);
+    std::memcpy(icov + 9 * v, leaves[v].icov, 72); std::memcpy(evecs + 9 * v, leaves[v].evecs, 72);
+    std::memcpy(evals + 3 * v, leaves[v].evals, 24);
+  }
+}
+// Neighbour probe for one point: writes linear-free identifiers (the leaf means) -- returns count.
+int orc_grid_neighbours(void* h, float x, float y, float z, int n_probe, double* means_out) {
+  VoxelGrid* g = static_cast<VoxelGrid*>(h);
+  const Leaf* nb[7];
+  const int nn = g->neighbours(x, y, z, n_probe, nb);
+  for (int k = 0; k < nn; ++k) std::memcpy(means_out + 3 * k, nb[k]->mean, 24);
+  return nn;
+}
+
+// ------------------------------------------------------------------ pclomp NDT
+void* orc_ndt_create() { return new PclompNdt(); }
+void orc_ndt_destroy(void* h) { delete static_cast<PclompNdt*>(h); }
+void* orc_ndt_grid(void* h) { return &static_cast<PclompNdt*>(h)->grid; }
+void orc_ndt_set_params(void* h, float resolution, double step_size, double trans_epsilon, int max_iterations, int search_method,
+                        int num_threads, float reg_scale, int use_line_search, double outlier_ratio, int min_pts, double eig_mult) {
+  PclompNdt* n = static_cast<PclompNdt*>(h);
+  n->params.resolution = resolution; n->params.step_size = step_size; n->params.trans_epsilon = trans_epsilon;
+  n->params.max_iterations = max_iterations; n->params.search_method = search_method; n->params.num_threads = num_threads;
+  n->params.regularization_scale_factor = reg_scale; n->params.use_line_search = use_line_search != 0;
+  n->outlier_ratio = outlier_ratio; n->grid.min_points_per_voxel = min_pts; n->grid.min_covar_eigvalue_mult = eig_mult;
+  n->update_gauss();
+}
+void orc_ndt_gauss(void* h, double* d) { PclompNdt* n = static_cast<PclompNdt*>(h); d[0] = n->gauss_d1; d[1] = n->gauss_d2; d[2] = n->gauss_d3; }
+int orc_ndt_set_target(void* h, const float* xyz, size_t n, size_t stride_floats, int is_dense) {
+  return static_cast<PclompNdt*>(h)->set_target(xyz, n, stride_floats, is_dense != 0);
+}
+void orc_ndt_set_source(void* h, const float* xyz, size_t n, size_t stride_floats) { static_cast<PclompNdt*>(h)->set_source(xyz, n, stride_floats); }
+void orc_ndt_set_regularization_pose(void* h, const float* T) {
+  PclompNdt* n = static_cast<PclompNdt*>(h);
+  n->has_reg_pose = (T != nullptr);
+  if (T) { n->reg_translation[0] = T[3]; n->reg_translation[1] = T[7]; n->reg_translation[2] = T[11]; }
+}
+// One evaluation at pose p: cloud transformed with T(p) as computeStepLengthMT does (:969-978).
+double orc_ndt_compute_derivatives(void* h, const double* p, int compute_hessian, double* g, double* H, double* nvtl) {
+  PclompNdt* n = static_cast<PclompNdt*>(h);
+  n->update_gauss();
+  float T[16]; pose_to_matrix_f(p, T);
+  std::vector<float> trans; n->transform_cloud(T, trans);
+  const double s = n->compute_derivatives(g, H, trans, p, compute_hessian != 0);
+  if (nvtl) *nvtl = n->nvtl;
+  return s;
+}
+// Same but with an explicit float 4x4 for the cloud (the initial-guess evaluation, :101-135).
+double orc_ndt_compute_derivatives_T(void* h, const float* T, const double* p, int compute_hessian, double* g, double* H, double* nvtl) {
+  PclompNdt* n = static_cast<PclompNdt*>(h);
+  n->update_gauss();
+  std::vector<float> trans; n->transform_cloud(T, trans);
+  const double s = n->compute_derivatives(g, H, trans, p, compute_hessian != 0);
+  if (nvtl) *nvtl = n->nvtl;
+  return s;
+}
+// trace: 50 doubles per evaluation (p6, score, g6, H36, nvtl); tarray: 16 floats per entry.
+int orc_ndt_align(void* h, const float* guess, float* final_T, double* hessian, double* trans_probability, double* nvtl, int* iterations,
+                  int* converged, double* trace, int trace_cap, int* n_trace, float* tarray, int tarray_cap, int* n_tarray) {
+  PclompNdt* n = static_cast<PclompNdt*>(h);
+  NdtResult r;
+  n->align(guess, r);
+  std::memcpy(final_T, r.final_transformation, sizeof(r.final_transformation));
+  if (hessian) std::memcpy(hessian, r.hessian, sizeof(r.hessian));
+  if (trans_probability) *trans_probability = r.trans_probability;
+  if (nvtl) *nvtl = r.nvtl;
+  *iterations = r.iterations; *converged = r.converged ? 1 : 0;
+  const int nt = static_cast<int>(r.trace.size() / 50);
+  if (n_trace) *n_trace = nt;
+  if (trace) std::memcpy(trace, r.trace.data(), sizeof(double) * 50 * std::min(nt, trace_cap));
+  const int na = static_cast<int>(r.transformation_array.size() / 16);
+  if (n_tarray) *n_tarray = na;
+  if (tarray) std::memcpy(tarray, r.transformation_array.data(), sizeof(float) * 16 * std::min(na, tarray_cap));
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,254 @@
+"""ctypes binding of the CPU oracle (oracle/libndt_oracle.so).  TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import
+this module; the product package (slam_sam_b200) never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_DIR = os.path.join(os.path.dirname(_HERE), "oracle")
+_LIB = None
+
+c_f = C.POINTER(C.c_float)
+c_d = C.POINTER(C.c_double)
+c_i = C.POINTER(C.c_int)
+c_ll = C.POINTER(C.c_longlong)
+
+
+def build():
+    subprocess.run(["make", "-s", "-C", ORACLE_DIR], check=True)
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(ORACLE_DIR, "libndt_oracle.so")
+        if not os.path.exists(path):
+            build()
+        L = C.CDLL(path)
+        L.orc_grid_create.restype = C.c_void_p
+        L.orc_grid_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_double]
+        L.orc_grid_destroy.argtypes = [C.c_void_p]
+        L.orc_grid_build.argtypes = [C.c_void_p, c_f, C.c_size_t, C.c_size_t, C.c_int]
+        L.orc_grid_meta.argtypes = [C.c_void_p, c_i, c_i, c_i]
+        L.orc_grid_count.restype = C.c_size_t
+        L.orc_grid_count.argtypes = [C.c_void_p]
+        L.orc_grid_export.argtypes = [C.c_void_p, c_ll, c_i, c_d, c_d, c_d, c_d, c_d]
+        L.orc_grid_neighbours.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int, c_d]
+        L.orc_ndt_create.restype = C.c_void_p
+        L.orc_ndt_destroy.argtypes = [C.c_void_p]
+        L.orc_ndt_grid.restype = C.c_void_p
+        L.orc_ndt_grid.argtypes = [C.c_void_p]
+        L.orc_ndt_set_params.argtypes = [C.c_void_p, C.c_float, C.c_double, C.c_double, C.c_int, C.c_int, C.c_int,
+                                         C.c_float, C.c_int, C.c_double, C.c_int, C.c_double]
+        L.orc_ndt_gauss.argtypes = [C.c_void_p, c_d]
+        L.orc_ndt_set_target.argtypes = [C.c_void_p, c_f, C.c_size_t, C.c_size_t, C.c_int]
+        L.orc_ndt_set_source.argtypes = [C.c_void_p, c_f, C.c_size_t, C.c_size_t]
+        L.orc_ndt_set_regularization_pose.argtypes = [C.c_void_p, c_f]
+        L.orc_ndt_compute_derivatives.restype = C.c_double
+        L.orc_ndt_compute_derivatives.argtypes = [C.c_void_p, c_d, C.c_int, c_d, c_d, c_d]
+        L.orc_ndt_compute_derivatives_T.restype = C.c_double
+        L.orc_ndt_compute_derivatives_T.argtypes = [C.c_void_p, c_f, c_d, C.c_int, c_d, c_d, c_d]
+        L.orc_ndt_align.argtypes = [C.c_void_p, c_f, c_f, c_d, c_d, c_d, c_i, c_i, c_d, C.c_int, c_i, c_f, C.c_int, c_i]
+        L.orc_svn_create.restype = C.c_void_p
+        L.orc_svn_destroy.argtypes = [C.c_void_p]
+        L.orc_svn_grid.restype = C.c_void_p
+        L.orc_svn_grid.argtypes = [C.c_void_p]
+        L.orc_svn_set_params.argtypes = [C.c_void_p, C.c_float, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int,
+                                         C.c_double, C.c_double, C.c_double, C.c_int, C.c_int, C.c_double]
+        L.orc_svn_gauss.argtypes = [C.c_void_p, c_d]
+        L.orc_svn_set_target.argtypes = [C.c_void_p, c_f, C.c_size_t, C.c_size_t]
+        L.orc_svn_set_source.argtypes = [C.c_void_p, c_f, C.c_size_t, C.c_size_t]
+        L.orc_svn_sample_particles.argtypes = [c_d, C.c_int, C.c_ulonglong, c_d]
+        L.orc_svn_particle_derivatives.restype = C.c_double
+        L.orc_svn_particle_derivatives.argtypes = [C.c_void_p, c_d, c_d, c_d]
+        L.orc_svn_step.argtypes = [C.c_void_p, C.c_int, c_d, c_d, c_d, c_d, c_d]
+        L.orc_svn_stage2.argtypes = [C.c_void_p, C.c_int, c_d, c_d, c_d, c_d]
+        L.orc_svn_align.restype = C.c_int
+        L.orc_svn_align.argtypes = [C.c_void_p, c_d, C.c_int, c_d, c_d, c_d, c_i]
+        for name in ("orc_eig3_sym", "orc_mat3_inverse", "orc_svd6_solve", "orc_eig6_sym", "orc_pose_expmap",
+                     "orc_pose_logmap", "orc_rot_rpy"):
+            getattr(L, name).restype = None
+        L.orc_ldlt6_solve.restype = C.c_int
+        _LIB = L
+    return _LIB
+
+
+def _f(a):
+    return a.ctypes.data_as(c_f)
+
+
+def _d(a):
+    return a.ctypes.data_as(c_d)
+
+
+def _i(a):
+    return a.ctypes.data_as(c_i)
+
+
+def as_xyz(cloud):
+    a = np.ascontiguousarray(cloud, dtype=np.float32)
+    assert a.ndim == 2 and a.shape[1] >= 3
+    return a
+
+
+SEARCH = {"KDTREE": 0, "DIRECT26": 1, "DIRECT7": 2, "DIRECT1": 3}
+
+
+def export_grid(gptr):
+    L = lib()
+    V = L.orc_grid_count(gptr)
+    idx = np.zeros(V, np.int64); n = np.zeros(V, np.int32)
+    mean = np.zeros((V, 3)); cov = np.zeros((V, 9)); icov = np.zeros((V, 9)); evecs = np.zeros((V, 9)); evals = np.zeros((V, 3))
+    if V:
+        L.orc_grid_export(gptr, idx.ctypes.data_as(c_ll), _i(n), _d(mean), _d(cov), _d(icov), _d(evecs), _d(evals))
+    mn = np.zeros(3, np.int32); mx = np.zeros(3, np.int32); dv = np.zeros(3, np.int32)
+    L.orc_grid_meta(gptr, _i(mn), _i(mx), _i(dv))
+    return dict(idx=idx, n=n, mean=mean, cov=cov, icov=icov, evecs=evecs, evals=evals, min_b=mn, max_b=mx, div_b=dv)
+
+
+class OracleGrid:
+    def __init__(self, flavour=0, leaf=1.0, min_pts=6, eig_mult=0.01):
+        self.h = lib().orc_grid_create(flavour, leaf, min_pts, eig_mult)
+
+    def build(self, cloud, is_dense=True):
+        a = as_xyz(cloud)
+        return lib().orc_grid_build(self.h, _f(a), a.shape[0], a.shape[1], int(is_dense))
+
+    def export(self):
+        return export_grid(self.h)
+
+    def neighbours(self, p, n_probe=7):
+        out = np.zeros((7, 3))
+        n = lib().orc_grid_neighbours(self.h, float(p[0]), float(p[1]), float(p[2]), n_probe, _d(out))
+        return out[:n]
+
+    def __del__(self):
+        try:
+            lib().orc_grid_destroy(self.h)
+        except Exception:
+            pass
+
+
+class OracleNdt:
+    """pclomp::NormalDistributionsTransform restatement."""
+
+    def __init__(self, resolution=1.0, step_size=0.1, trans_epsilon=0.1, max_iterations=35, search="DIRECT7",
+                 num_threads=1, reg_scale=0.0, use_line_search=False, outlier_ratio=0.55, min_pts=6, eig_mult=0.01):
+        self.h = lib().orc_ndt_create()
+        lib().orc_ndt_set_params(self.h, resolution, step_size, trans_epsilon, max_iterations, SEARCH[search], num_threads,
+                                 reg_scale, int(use_line_search), outlier_ratio, min_pts, eig_mult)
+
+    def gauss(self):
+        d = np.zeros(3); lib().orc_ndt_gauss(self.h, _d(d)); return d
+
+    def set_target(self, cloud, is_dense=True):
+        a = as_xyz(cloud)
+        return lib().orc_ndt_set_target(self.h, _f(a), a.shape[0], a.shape[1], int(is_dense))
+
+    def set_source(self, cloud):
+        a = as_xyz(cloud)
+        lib().orc_ndt_set_source(self.h, _f(a), a.shape[0], a.shape[1])
+
+    def set_regularization_pose(self, T):
+        if T is None:
+            lib().orc_ndt_set_regularization_pose(self.h, None)
+        else:
+            t = np.ascontiguousarray(T, np.float32).reshape(16)
+            lib().orc_ndt_set_regularization_pose(self.h, _f(t))
+
+    def grid(self):
+        return export_grid(lib().orc_ndt_grid(self.h))
+
+    def compute_derivatives(self, p, compute_hessian=True, T=None):
+        p = np.ascontiguousarray(p, np.float64)
+        g = np.zeros(6); H = np.zeros((6, 6)); nv = np.zeros(1)
+        if T is None:
+            s = lib().orc_ndt_compute_derivatives(self.h, _d(p), int(compute_hessian), _d(g), _d(H), _d(nv))
+        else:
+            t = np.ascontiguousarray(T, np.float32).reshape(16)
+            s = lib().orc_ndt_compute_derivatives_T(self.h, _f(t), _d(p), int(compute_hessian), _d(g), _d(H), _d(nv))
+        return s, g, H, nv[0]
+
+    def align(self, guess=None, max_trace=128):
+        guess = np.eye(4, dtype=np.float32) if guess is None else np.ascontiguousarray(guess, np.float32)
+        T = np.zeros((4, 4), np.float32); H = np.zeros((6, 6)); tp = np.zeros(1); nv = np.zeros(1)
+        it = np.zeros(1, np.int32); cv = np.zeros(1, np.int32); nt = np.zeros(1, np.int32); na = np.zeros(1, np.int32)
+        trace = np.zeros((max_trace, 50)); tarr = np.zeros((max_trace, 16), np.float32)
+        lib().orc_ndt_align(self.h, _f(guess.reshape(16)), _f(T), _d(H), _d(tp), _d(nv), _i(it), _i(cv), _d(trace), max_trace, _i(nt),
+                            _f(tarr), max_trace, _i(na))
+        return dict(T=T, hessian=H, trans_probability=tp[0], nvtl=nv[0], iterations=int(it[0]), converged=bool(cv[0]),
+                    trace=trace[: nt[0]].copy(), transformation_array=tarr[: na[0]].reshape(-1, 4, 4).copy())
+
+    def __del__(self):
+        try:
+            lib().orc_ndt_destroy(self.h)
+        except Exception:
+            pass
+
+
+class OracleSvn:
+    """svn_ndt::SvnNormalDistributionsTransform restatement."""
+
+    def __init__(self, resolution=1.0, outlier_ratio=0.55, search="DIRECT7", num_threads=1, K=30, max_iter=50, kernel_h=1.0,
+                 step_size=1.0, stop_thresh=1e-4, use_gn=True, min_pts=6, eig_mult=0.01):
+        self.h = lib().orc_svn_create()
+        self.K = K
+        lib().orc_svn_set_params(self.h, resolution, outlier_ratio, SEARCH[search], num_threads, K, max_iter, kernel_h, step_size,
+                                 stop_thresh, int(use_gn), min_pts, eig_mult)
+
+    def gauss(self):
+        d = np.zeros(3); lib().orc_svn_gauss(self.h, _d(d)); return d
+
+    def set_target(self, cloud):
+        a = as_xyz(cloud)
+        return lib().orc_svn_set_target(self.h, _f(a), a.shape[0], a.shape[1])
+
+    def set_source(self, cloud):
+        a = as_xyz(cloud)
+        lib().orc_svn_set_source(self.h, _f(a), a.shape[0], a.shape[1])
+
+    def grid(self):
+        return export_grid(lib().orc_svn_grid(self.h))
+
+    @staticmethod
+    def sample_particles(prior, K, seed):
+        prior = np.ascontiguousarray(prior, np.float64).reshape(16)
+        out = np.zeros((K, 4, 4))
+        lib().orc_svn_sample_particles(_d(prior), K, seed, _d(out))
+        return out
+
+    def particle_derivatives(self, pose):
+        pose = np.ascontiguousarray(pose, np.float64).reshape(16)
+        g = np.zeros(6); H = np.zeros((6, 6))
+        s = lib().orc_svn_particle_derivatives(self.h, _d(pose), _d(g), _d(H))
+        return s, g, H
+
+    def step(self, particles):
+        P = np.ascontiguousarray(particles, np.float64).copy(); K = P.shape[0]
+        s = np.zeros(K); g = np.zeros((K, 6)); H = np.zeros((K, 6, 6)); u = np.zeros((K, 6))
+        lib().orc_svn_step(self.h, K, _d(P), _d(s), _d(g), _d(H), _d(u))
+        return P, s, g, H, u
+
+    def stage2(self, particles, grads, hess):
+        P = np.ascontiguousarray(particles, np.float64); K = P.shape[0]
+        g = np.ascontiguousarray(grads, np.float64); H = np.ascontiguousarray(hess, np.float64); u = np.zeros((K, 6))
+        lib().orc_svn_stage2(self.h, K, _d(P), _d(g), _d(H), _d(u))
+        return u
+
+    def align(self, prior, particles):
+        prior = np.ascontiguousarray(prior, np.float64).reshape(16)
+        P = np.ascontiguousarray(particles, np.float64).copy(); K = P.shape[0]
+        fp = np.zeros((4, 4)); cov = np.zeros((6, 6)); cv = np.zeros(1, np.int32)
+        it = lib().orc_svn_align(self.h, _d(prior), K, _d(P), _d(fp), _d(cov), _i(cv))
+        return dict(final_pose=fp, final_covariance=cov, converged=bool(cv[0]), iterations=it, particles=P)
+
+    def __del__(self):
+        try:
+            lib().orc_svn_destroy(self.h)
+        except Exception:
+            pass
