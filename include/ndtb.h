@@ -1,0 +1,174 @@
+/* ndtb.h -- C ABI of the B200-native NDT scan-registration engine (libndtb.so).
+ *
+ * This is the drop-in boundary for ONE hot path of khalisfadil/slam-sam: NDT scan registration
+ * (target voxel-map build, per-point score/gradient/Hessian, Newton loop, SVN-NDT).  The reference
+ * has no FFI layer: the path sits behind two C++ header-template classes.  Each entry point below
+ * cites the reference method(s) it replaces; include/ndtb_pclomp.hpp re-creates the reference's
+ * class/method names on top of this ABI (see INTEGRATION.md for the binding a maintainer adds).
+ *
+ * Conventions: every function returns an int status (NDTB_OK == 0, negative = error); no C++
+ * exception crosses the ABI; the caller owns all host buffers; a handle owns its device memory and
+ * one CUDA stream; one handle per caller thread (like the reference's registrars, which are not
+ * re-entrant).  4x4 matrices are ROW-MAJOR (m[4*r+c]); 6-vectors are (x,y,z,roll,pitch,yaw) unless
+ * stated; 6x6 matrices row-major.  There is NO CPU fallback: without a CUDA device every compute
+ * entry point fails with NDTB_ERR_CUDA.
+ */
+#ifndef NDTB_H_
+#define NDTB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NDTB_OK 0
+#define NDTB_ERR_INVALID (-1)   /* bad argument / handle                                           */
+#define NDTB_ERR_CUDA (-2)      /* CUDA runtime error (see ndtb_last_error)                         */
+#define NDTB_ERR_EMPTY (-3)     /* empty / missing cloud (reference: PCL_WARN/PCL_ERROR + early out)*/
+#define NDTB_ERR_OVERFLOW (-4)  /* dx*dy*dz > INT32_MAX: voxel_grid_covariance_omp_impl.hpp:83-94   */
+#define NDTB_ERR_NOT_READY (-5) /* target or source not set                                         */
+
+/* pclomp::NeighborSearchMethod values (extern/ndt_omp/include/pclomp/ndt_struct.hpp) */
+#define NDTB_KDTREE 0   /* not provided by this engine (off the hot path) -> NDTB_ERR_INVALID */
+#define NDTB_DIRECT26 1 /* idem */
+#define NDTB_DIRECT7 2
+#define NDTB_DIRECT1 3
+
+#define NDTB_FLAVOUR_PCLOMP 0 /* pclomp::VoxelGridCovariance + pclomp NDT maths   */
+#define NDTB_FLAVOUR_SVN 1    /* svn_ndt::VoxelGridCovariance + svn_ndt maths     */
+
+typedef struct ndtb_handle_s* ndtb_handle;
+
+/* Mirrors pclomp::NdtParams (ndt_struct.hpp:90-105) + the knobs that live elsewhere in the
+ * reference: outlier_ratio_ (ndt_omp_impl.hpp:54), min_points_per_voxel_ and
+ * min_covar_eigvalue_mult_ (voxel_grid_covariance_omp.h:193-208), PointCloud::is_dense. */
+typedef struct ndtb_params {
+  float resolution;                  /* setResolution            ndt_omp.h:135-142            */
+  double step_size;                  /* setStepSize              ndt_omp.h:159                */
+  double trans_epsilon;              /* setTransformationEpsilon (pcl::Registration)          */
+  int max_iterations;                /* setMaximumIterations     (pcl::Registration)          */
+  int search_method;                 /* setNeighborhoodSearchMethod ndt_omp.h:121             */
+  double outlier_ratio;              /* setOulierRatio           ndt_omp.h:173                */
+  int min_points_per_voxel;          /* VoxelGridCovariance::setMinPointPerVoxel              */
+  double min_covar_eigvalue_mult;    /* VoxelGridCovariance::setCovEigValueInflationRatio     */
+  float regularization_scale_factor; /* setRegularizationScaleFactor ndt_omp.h:275            */
+  int use_line_search;               /* NdtParams::use_line_search (More-Thuente), default 0  */
+  int grid_flavour;                  /* NDTB_FLAVOUR_*                                        */
+  int is_dense;                      /* target cloud is_dense (non-finite points skipped if 0)*/
+} ndtb_params;
+
+/* pclomp::NdtResult (ndt_struct.hpp:67-88) + hasConverged(). */
+typedef struct ndtb_result {
+  float pose[16];                 /* getFinalTransformation()                                    */
+  double hessian[36];             /* getHessian()                                                */
+  double transform_probability;   /* getTransformationProbability()                              */
+  double nearest_voxel_transformation_likelihood;
+  int iteration_num;              /* getFinalNumIteration()                                      */
+  int converged;                  /* hasConverged()                                              */
+  int transformation_array_len;   /* entries written to `transformation_array` (<= capacity)     */
+  int evaluations;                /* computeDerivatives calls made (= roofline "E")              */
+} ndtb_result;
+
+/* svn_ndt::SvnNdtResult (extern/svn_ndt/include/svn_ndt.h:40-51). */
+typedef struct ndtb_svn_params {
+  int particle_count;        /* setParticleCount        svn_ndt.h:112 */
+  int max_iterations;        /* setMaxIterations                       */
+  double kernel_bandwidth;   /* setKernelBandwidth                     */
+  double step_size;          /* setStepSize                            */
+  double stop_threshold;     /* setEarlyStopThreshold                  */
+  int use_gauss_newton;      /* setUseGaussNewtonHessian               */
+} ndtb_svn_params;
+
+typedef struct ndtb_svn_result {
+  double final_pose[16];        /* gtsam::Pose3 as 4x4                                        */
+  double final_covariance[36];  /* GTSAM tangent order (rx,ry,rz,x,y,z)                       */
+  int converged;
+  int iterations;
+} ndtb_svn_result;
+
+/* ---- lifetime ------------------------------------------------------------------------------- */
+int ndtb_create(int cuda_device, ndtb_handle* out); /* ctor: ndt_omp_impl.hpp:51-81 defaults     */
+int ndtb_destroy(ndtb_handle h);
+const char* ndtb_last_error(ndtb_handle h);
+const char* ndtb_version(void);
+
+/* ---- parameters ----------------------------------------------------------------------------- */
+int ndtb_default_params(int grid_flavour, ndtb_params* p); /* ctor defaults of either flavour    */
+int ndtb_set_params(ndtb_handle h, const ndtb_params* p);  /* rebuilds the grid iff resolution /
+                                                              min points / flavour changed and a
+                                                              target is set (ndt_omp.h:135-142)  */
+int ndtb_get_params(ndtb_handle h, ndtb_params* p);
+
+/* ---- clouds (host pointers; xyz = 3 consecutive floats at each `stride_bytes`) --------------- */
+/* setInputTarget: ndt_omp.h:126-130 -> init() :324-330 -> VoxelGridCovariance::filter(true)
+ * (voxel_grid_covariance_omp_impl.hpp:55-364) or svn_ndt_impl.hpp:137-159. Builds the voxel map. */
+int ndtb_set_target(ndtb_handle h, const float* xyz, size_t n, size_t stride_bytes);
+/* setInputSource (pcl::Registration). */
+int ndtb_set_source(ndtb_handle h, const float* xyz, size_t n, size_t stride_bytes);
+/* Same, but the buffers already live in device memory of the handle's GPU (packed float4). */
+int ndtb_set_target_device(ndtb_handle h, const void* d_xyzw, size_t n);
+int ndtb_set_source_device(ndtb_handle h, const void* d_xyzw, size_t n);
+/* setRegularizationPose / unsetRegularizationPose: ndt_omp.h:277-283.  T == NULL unsets. */
+int ndtb_set_regularization_pose(ndtb_handle h, const float* T16);
+
+/* ---- pclomp NDT ------------------------------------------------------------------------------ */
+/* computeDerivatives (ndt_omp_impl.hpp:217-392) at pose p, cloud transformed by T(p) like
+ * computeStepLengthMT :969-983.  If T16 != NULL that float matrix transforms the cloud instead
+ * (the initial-guess evaluation :101-135).  Parity hook for SURVEY 8(a) row a8. */
+int ndtb_compute_derivatives(ndtb_handle h, const double p[6], const float* T16, int compute_hessian, double* score,
+                             double gradient[6], double hessian[36], double* nvtl);
+/* align(output, guess): pcl::Registration::align -> computeTransformation (ndt_omp_impl.hpp:85-202).
+ * `out_xyz` (optional, n_source*3 floats) receives the transformed source like `output`.
+ * `transformation_array` (optional, capacity*16 floats) receives transformation_array_. */
+int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* result, float* transformation_array, int capacity, float* out_xyz);
+/* Per-evaluation trace of the last ndtb_align: 50 doubles per evaluation (p6, score, g6, H36, nvtl). */
+int ndtb_get_trace(ndtb_handle h, double* trace, int capacity, int* count);
+/* calculateTransformationProbability / calculateNearestVoxelTransformationLikelihood
+ * (ndt_omp_impl.hpp:1169-1281): FP64 score-only pass over a cloud transformed by T16. */
+int ndtb_calculate_scores(ndtb_handle h, const float T16[16], double* transformation_probability, double* nvtl);
+
+/* ---- voxel map inspection (getTargetCells().getLeaves(), include/pipeline.hpp:163-222) -------- */
+int ndtb_get_voxel_count(ndtb_handle h, size_t* count, int min_b[3], int max_b[3], int div_b[3]);
+/* Arrays sized by count, ascending linear index: idx[V] nr_points[V] mean[3V] cov[9V] icov[9V]
+ * evecs[9V] evals[3V]; any pointer may be NULL. */
+int ndtb_get_voxels(ndtb_handle h, int64_t* idx, int32_t* nr_points, double* mean, double* cov, double* icov, double* evecs,
+                    double* evals);
+/* Mean hits per source point of the last derivative evaluation (roofline h-bar). */
+int ndtb_get_last_hits(ndtb_handle h, double* mean_hits_per_point, double* points_with_neighbours);
+
+/* ---- SVN-NDT (grid_flavour must be NDTB_FLAVOUR_SVN) ------------------------------------------ */
+int ndtb_svn_default_params(ndtb_svn_params* p);      /* svn_ndt_impl.hpp:61-77                  */
+int ndtb_svn_set_params(ndtb_handle h, const ndtb_svn_params* p);
+/* computeParticleDerivatives for K poses (svn_ndt_impl.hpp:518-668 under :758-781). poses: K x 16
+ * doubles.  Outputs (NDT order): scores[K], grads[6K], hess[36K]. */
+int ndtb_svn_particle_derivatives(ndtb_handle h, int K, const double* poses, double* scores, double* grads, double* hess);
+/* Stage 2 (svn_ndt_impl.hpp:789-839): updates[6K] in GTSAM order. */
+int ndtb_svn_stage2(ndtb_handle h, int K, const double* poses, const double* grads, const double* hess, double* updates);
+/* One full iteration (stages 1-3) on K particles, in/out K x 16 doubles. Optional outputs. */
+int ndtb_svn_step(ndtb_handle h, int K, double* poses, double* scores, double* grads, double* hess, double* updates);
+/* align(source, prior) (svn_ndt_impl.hpp:675-964).  init_particles: K x 16 doubles or NULL (then
+ * drawn from `seed` with the reference's sigmas, :710 -- the reference seeds from the clock).
+ * particles_out: optional K x 16. */
+int ndtb_svn_align(ndtb_handle h, const double prior[16], const double* init_particles, uint64_t seed, ndtb_svn_result* result,
+                   double* particles_out);
+/* Particle sharding for multi-GPU SVN: this handle evaluates particles k with
+ * k % world == rank in stage 1; the caller all-gathers the (score,g,H) records (43 doubles per
+ * particle) between ndtb_svn_stage1_local and ndtb_svn_finish_step. */
+int ndtb_svn_stage1_local(ndtb_handle h, int K, const double* poses, int rank, int world, double* records43);
+int ndtb_svn_finish_step(ndtb_handle h, int K, double* poses, const double* records43, double* updates);
+
+/* ---- batch replay: n independent alignments against the current target ----------------------- */
+int ndtb_align_batch(ndtb_handle h, int n_scans, const float* const* xyz, const size_t* n_points, size_t stride_bytes,
+                     const float* guesses16, ndtb_result* results);
+
+/* ---- measurement helpers ---------------------------------------------------------------------- */
+/* CUDA-event time (ms) of the stages of the last set_target / align on the handle's stream. */
+int ndtb_get_timings(ndtb_handle h, float* build_ms, float* align_ms, float* eval_kernel_ms_total, int* eval_kernel_launches);
+int ndtb_get_stream(ndtb_handle h, void** cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NDTB_H_ */

@@ -1,0 +1,40 @@
+// Host-side interface of the voxel-map build (implemented in voxel_build.cu / voxel_finalize.cu).
+#pragma once
+#include "ndtb_internal.cuh"
+#include <stddef.h>
+
+namespace ndtb {
+
+struct DeviceGrid {
+  GridMeta meta{};
+  bool built = false;
+  uint32_t V = 0;          // leaves (pclomp keeps under-populated / rejected leaves, flagged)
+  uint32_t n_valid = 0;    // leaves that can be returned by a neighbour search
+  // hot
+  VoxRec* recs = nullptr;
+  HashSlot* table = nullptr;
+  size_t table_cap = 0, table_alloc = 0;
+  // cold (FP64 export path)
+  uint32_t* c_key = nullptr;
+  int32_t* c_n = nullptr;
+  double *c_mean = nullptr, *c_cov = nullptr, *c_icov = nullptr, *c_evecs = nullptr, *c_evals = nullptr;
+  size_t vox_alloc = 0;
+  // scratch sized by the target cloud
+  uint32_t *keys[2] = {nullptr, nullptr}, *vals[2] = {nullptr, nullptr};
+  uint32_t *hist = nullptr, *seg_start = nullptr, *block_counts = nullptr;
+  size_t pts_alloc = 0, hist_alloc = 0;
+  int* d_bbox = nullptr;            // 6 ordered ints
+  unsigned int* d_counters = nullptr;  // [0] skipped points, [1] V, [2] valid leaves
+  int* h_pinned = nullptr;          // 16 ints of pinned host memory for the small read-backs
+};
+
+// Returns NDTB_OK / NDTB_ERR_* ; synchronises the stream twice (bbox read-back, final counters).
+int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resolution, int min_pts, double eig_mult, int flavour,
+                    int is_dense, cudaStream_t stream);
+void free_device_grid(DeviceGrid& g);
+
+// voxel_finalize.cu
+void launch_voxel_finalize(const DeviceGrid& g, const float4* d_pts, const uint32_t* sorted_vals, uint32_t n_points_upper,
+                           cudaStream_t stream);
+
+}  // namespace ndtb

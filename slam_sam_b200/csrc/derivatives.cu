@@ -1,0 +1,372 @@
+// The hot kernel: fused rigid transform + DIRECT1/DIRECT7 voxel gather + per-pair NDT
+// score/gradient/Hessian + deterministic FP64 reduction  (SURVEY 8a rows a4-a8, a12-a15).
+//
+//   pclomp flavour: computeDerivatives   ndt_omp_impl.hpp:217-347
+//                   getNeighborhoodAtPoint voxel_grid_covariance_omp_impl.hpp:368-399
+//                   computePointDerivatives :542-587, updateDerivatives :640-697
+//   svn flavour   : computeParticleDerivatives svn_ndt_impl.hpp:518-647, updateDerivatives :401-513,
+//                   getLeaf / getNeighborhoodAtPoint7 voxel_grid_covariance.h:280-304, _impl.hpp:560-615
+//
+// One thread per source point (grid.y = particle).  The transformed cloud is never materialised.
+// Per-pair maths is float32 in the reference's evaluation order with structural zeros/ones of the
+// 4x6 / 24x6 point Jacobian/Hessian skipped (x*1, x*0 and +0 are exact, so the result is bit-identical
+// to the dense Eigen expressions for finite inputs); accumulation is FP64 per thread in neighbour
+// order, then a fixed-shape tree (warp shuffles -> shared memory -> last-block pass), so the result
+// is run-to-run bit stable and differs from the reference's serial in-index-order sum only by FP64
+// summation order.  Bound: HBM/L2 gather, B_eval = N*(16 + 8*P + 64*hbar) bytes.
+#include "eval_api.cuh"
+
+namespace ndtb {
+
+__device__ __forceinline__ float dot3(float a0, float a1, float a2, float b0, float b1, float b2) {
+  float s = a0 * b0;
+  s = s + a1 * b1;
+  s = s + a2 * b2;
+  return s;
+}
+
+struct PointTables {  // per-point angular parts of Jp (8) and Hp (15)
+  float xj[8];
+  float xh[15];
+};
+
+// ------------------------------------------------------------------------------ pclomp pair maths
+template <bool HESS>
+__device__ __forceinline__ float pair_pclomp(const PointTables& pt, const float x4[3], const float C[9], float d2f, double d1,
+                                             double* __restrict__ acc /* RED_N */, bool& counted) {
+  float xC[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) xC[c] = dot3(x4[0], x4[1], x4[2], C[c], C[3 + c], C[6 + c]);
+  const float q = dot3(x4[0], x4[1], x4[2], xC[0], xC[1], xC[2]);
+  float e = static_cast<float>(exp(static_cast<double>(-d2f * q * 0.5f)));
+  const float score_inc = static_cast<float>(-d1 * static_cast<double>(e));
+  e = d2f * e;
+  counted = true;
+  if (e > 1 || e < 0 || e != e) return 0.0f;
+  e = static_cast<float>(static_cast<double>(e) * d1);
+  const float* xj = pt.xj;
+  float CJ[3][6];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    CJ[r][0] = C[3 * r + 0]; CJ[r][1] = C[3 * r + 1]; CJ[r][2] = C[3 * r + 2];
+    CJ[r][3] = C[3 * r + 1] * xj[0] + C[3 * r + 2] * xj[1];
+    CJ[r][4] = dot3(C[3 * r], C[3 * r + 1], C[3 * r + 2], xj[2], xj[3], xj[4]);
+    CJ[r][5] = dot3(C[3 * r], C[3 * r + 1], C[3 * r + 2], xj[5], xj[6], xj[7]);
+  }
+  float xCJ[6];
+#pragma unroll
+  for (int c = 0; c < 6; ++c) xCJ[c] = dot3(x4[0], x4[1], x4[2], CJ[0][c], CJ[1][c], CJ[2][c]);
+#pragma unroll
+  for (int c = 0; c < 6; ++c) acc[RED_G + c] += static_cast<double>(e * xCJ[c]);
+  if (HESS) {
+    const float* xh = pt.xh;
+    // xCH for the 3x3 angular block: rows/cols 3..5 -> vectors a b c / b d e / c e f
+    const float h_a = xC[1] * xh[0] + xC[2] * xh[1];
+    const float h_b = xC[1] * xh[2] + xC[2] * xh[3];
+    const float h_c = xC[1] * xh[4] + xC[2] * xh[5];
+    const float h_d = dot3(xC[0], xC[1], xC[2], xh[6], xh[7], xh[8]);
+    const float h_e = dot3(xC[0], xC[1], xC[2], xh[9], xh[10], xh[11]);
+    const float h_f = dot3(xC[0], xC[1], xC[2], xh[12], xh[13], xh[14]);
+    const float xCH[3][3] = {{h_a, h_b, h_c}, {h_b, h_d, h_e}, {h_c, h_e, h_f}};
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        // JCJ(j,i) = Jp(:,j)^T * CJ(:,i)
+        float jcj;
+        if (j < 3) jcj = CJ[j][i];
+        else if (j == 3) jcj = xj[0] * CJ[1][i] + xj[1] * CJ[2][i];
+        else if (j == 4) jcj = dot3(xj[2], xj[3], xj[4], CJ[0][i], CJ[1][i], CJ[2][i]);
+        else jcj = dot3(xj[5], xj[6], xj[7], CJ[0][i], CJ[1][i], CJ[2][i]);
+        float t = -d2f * xCJ[i] * xCJ[j];
+        if (i >= 3 && j >= 3) t = t + xCH[i - 3][j - 3];
+        t = t + jcj;
+        acc[RED_H + 6 * i + j] += static_cast<double>(e * t);
+      }
+    }
+  }
+  return score_inc;
+}
+
+// ------------------------------------------------------------------------------ svn pair maths
+template <bool GN>
+__device__ __forceinline__ double pair_svn(const PointTables& pt, const double xr[3], const double Cd[9], double d1, double d2,
+                                           double* __restrict__ acc) {
+  float x4[3], C[9];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) x4[a] = static_cast<float>(xr[a]);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) C[i] = static_cast<float>(Cd[i]);
+  double Cx[3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) Cx[r] = (Cd[3 * r] * xr[0] + Cd[3 * r + 1] * xr[1]) + Cd[3 * r + 2] * xr[2];
+  double mahal = (xr[0] * Cx[0] + xr[1] * Cx[1]) + xr[2] * Cx[2];
+  if (!isfinite(mahal) || mahal < -1e-9) return 0.0;
+  if (mahal < 0.0) mahal = 0.0;
+  const double earg = d2 * mahal * 0.5;
+  if (earg > 50.0) return 0.0;
+  const double exp_term = exp(-earg);
+  const double score_inc = -d1 * exp_term;
+  const double factor = d1 * d2 * exp_term;
+  if (!isfinite(factor) || fabs(factor) < 1e-15) return score_inc;
+  const float* xj = pt.xj;
+  float CJ[3][6];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    CJ[r][0] = C[3 * r + 0]; CJ[r][1] = C[3 * r + 1]; CJ[r][2] = C[3 * r + 2];
+    CJ[r][3] = C[3 * r + 1] * xj[0] + C[3 * r + 2] * xj[1];
+    CJ[r][4] = dot3(C[3 * r], C[3 * r + 1], C[3 * r + 2], xj[2], xj[3], xj[4]);
+    CJ[r][5] = dot3(C[3 * r], C[3 * r + 1], C[3 * r + 2], xj[5], xj[6], xj[7]);
+  }
+  float gc[6];
+  double ginc[6];
+  bool gfin = true;
+#pragma unroll
+  for (int c = 0; c < 6; ++c) {
+    gc[c] = dot3(x4[0], x4[1], x4[2], CJ[0][c], CJ[1][c], CJ[2][c]);
+    ginc[c] = factor * static_cast<double>(gc[c]);
+    if (!isfinite(ginc[c])) gfin = false;
+  }
+  if (gfin) {
+#pragma unroll
+    for (int c = 0; c < 6; ++c) acc[RED_G + c] += ginc[c];
+  }
+  double hc[36];
+  bool hfin = true;
+  float xC[3];
+  float xCH[3][3];
+  if (!GN) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) xC[c] = dot3(x4[0], x4[1], x4[2], C[c], C[3 + c], C[6 + c]);
+    const float* xh = pt.xh;
+    const float h_a = xC[1] * xh[0] + xC[2] * xh[1];
+    const float h_b = xC[1] * xh[2] + xC[2] * xh[3];
+    const float h_c = xC[1] * xh[4] + xC[2] * xh[5];
+    const float h_d = dot3(xC[0], xC[1], xC[2], xh[6], xh[7], xh[8]);
+    const float h_e = dot3(xC[0], xC[1], xC[2], xh[9], xh[10], xh[11]);
+    const float h_f = dot3(xC[0], xC[1], xC[2], xh[12], xh[13], xh[14]);
+    xCH[0][0] = h_a; xCH[0][1] = h_b; xCH[0][2] = h_c;
+    xCH[1][0] = h_b; xCH[1][1] = h_d; xCH[1][2] = h_e;
+    xCH[2][0] = h_c; xCH[2][1] = h_e; xCH[2][2] = h_f;
+  }
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      // term2(i,j) = Jp(:,i)^T * CJ(:,j)
+      float jcj;
+      if (i < 3) jcj = CJ[i][j];
+      else if (i == 3) jcj = xj[0] * CJ[1][j] + xj[1] * CJ[2][j];
+      else if (i == 4) jcj = dot3(xj[2], xj[3], xj[4], CJ[0][j], CJ[1][j], CJ[2][j]);
+      else jcj = dot3(xj[5], xj[6], xj[7], CJ[0][j], CJ[1][j], CJ[2][j]);
+      double h = static_cast<double>(jcj);
+      if (!GN) {
+        const double term1 = -d2 * (static_cast<double>(gc[i]) * static_cast<double>(gc[j]));
+        const double term3 = (i >= 3 && j >= 3) ? static_cast<double>(xCH[i - 3][j - 3]) : 0.0;
+        h = (term1 + h) + term3;
+      }
+      h = h * factor;
+      if (!isfinite(h)) hfin = false;
+      hc[6 * i + j] = h;
+    }
+  }
+  if (hfin) {
+#pragma unroll
+    for (int i = 0; i < 36; ++i) acc[RED_H + i] += hc[i];
+  }
+  return score_inc;
+}
+
+// ------------------------------------------------------------------------------ neighbour lookup
+__device__ __forceinline__ int lookup_pclomp(const GridMeta& m, const HashSlot* __restrict__ table, int i0, int i1, int i2, int ox, int oy,
+                                             int oz) {
+  // voxel_grid_covariance_omp_impl.hpp:379-394: displacement must lie in [min_b - ijk, max_b - ijk]
+  if (m.min_b[0] - i0 > ox || m.max_b[0] - i0 < ox) return -1;
+  if (m.min_b[1] - i1 > oy || m.max_b[1] - i1 < oy) return -1;
+  if (m.min_b[2] - i2 > oz || m.max_b[2] - i2 < oz) return -1;
+  const int lin = (i0 + ox - m.min_b[0]) * m.divb_mul[0] + (i1 + oy - m.min_b[1]) * m.divb_mul[1] + (i2 + oz - m.min_b[2]) * m.divb_mul[2];
+  return hash_find(table, m.hash_mask, static_cast<uint32_t>(lin));
+}
+
+__device__ __forceinline__ int lookup_svn(const GridMeta& m, const HashSlot* __restrict__ table, float px, float py, float pz) {
+  // voxel_grid_covariance_impl.hpp:59-70 + voxel_grid_covariance.h:289-303
+  if (!(px >= m.lo_bound[0] && px < m.hi_bound[0] && py >= m.lo_bound[1] && py < m.hi_bound[1] && pz >= m.lo_bound[2] && pz < m.hi_bound[2]))
+    return -1;
+  const int i0 = static_cast<int>(floorf(px * m.inv_leaf) - static_cast<float>(m.min_b[0]));
+  const int i1 = static_cast<int>(floorf(py * m.inv_leaf) - static_cast<float>(m.min_b[1]));
+  const int i2 = static_cast<int>(floorf(pz * m.inv_leaf) - static_cast<float>(m.min_b[2]));
+  const int lin = i0 * m.divb_mul[0] + i1 * m.divb_mul[1] + i2 * m.divb_mul[2];
+  return hash_find(table, m.hash_mask, static_cast<uint32_t>(lin));
+}
+
+__device__ __constant__ int c_off[7][3] = {{0, 0, 0}, {1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};
+
+// ------------------------------------------------------------------------------ the kernel
+template <int FLAVOUR, int PROBES, bool HESS, bool GN>
+__global__ void __launch_bounds__(EVAL_THREADS) eval_kernel(const float4* __restrict__ src, int n, GridMeta m, const VoxRec* __restrict__ recs,
+                                                            const HashSlot* __restrict__ table, const double* __restrict__ c_mean,
+                                                            const double* __restrict__ c_icov, const EvalState* __restrict__ states,
+                                                            double* __restrict__ partials, double* __restrict__ results,
+                                                            unsigned int* __restrict__ tickets, int particle_offset) {
+  __shared__ EvalState st;
+  __shared__ double s_red[EVAL_THREADS / 32][RED_N];
+  __shared__ bool s_last;
+  const int particle = blockIdx.y + particle_offset;
+  {
+    const int words = sizeof(EvalState) / 4;
+    const uint32_t* g = reinterpret_cast<const uint32_t*>(states + particle);
+    uint32_t* s = reinterpret_cast<uint32_t*>(&st);
+    for (int i = threadIdx.x; i < words; i += blockDim.x) s[i] = g[i];
+  }
+  __syncthreads();
+  double acc[RED_N];
+#pragma unroll
+  for (int i = 0; i < RED_N; ++i) acc[i] = 0.0;
+
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx < n) {
+    const float4 p = __ldg(src + idx);
+    // pcl::transformPointCloud (SSE2 Transformer association): m0*x + (m1*y + (m2*z + m3))
+    float xt[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) xt[r] = st.T[4 * r] * p.x + (st.T[4 * r + 1] * p.y + (st.T[4 * r + 2] * p.z + st.T[4 * r + 3]));
+    bool point_ok = true;
+    if (FLAVOUR == FLAVOUR_SVN) point_ok = isfinite(xt[0]) && isfinite(xt[1]) && isfinite(xt[2]);  // svn_ndt_impl.hpp:573
+    int rows[PROBES];
+    int nn = 0;
+    if (point_ok) {
+      if (FLAVOUR == FLAVOUR_PCLOMP) {
+        const int i0 = static_cast<int>(floorf(__fdiv_rn(xt[0], m.leaf)));
+        const int i1 = static_cast<int>(floorf(__fdiv_rn(xt[1], m.leaf)));
+        const int i2 = static_cast<int>(floorf(__fdiv_rn(xt[2], m.leaf)));
+#pragma unroll
+        for (int k = 0; k < PROBES; ++k) {
+          const int r = lookup_pclomp(m, table, i0, i1, i2, c_off[k][0], c_off[k][1], c_off[k][2]);
+          rows[k] = r;
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < PROBES; ++k) {
+          const float w = m.leaf;
+          const float qx = (k == 1) ? xt[0] + w : ((k == 2) ? xt[0] - w : xt[0]);
+          const float qy = (k == 3) ? xt[1] + w : ((k == 4) ? xt[1] - w : xt[1]);
+          const float qz = (k == 5) ? xt[2] + w : ((k == 6) ? xt[2] - w : xt[2]);
+          rows[k] = lookup_svn(m, table, qx, qy, qz);
+        }
+      }
+      PointTables pt;
+#pragma unroll
+      for (int r = 0; r < 8; ++r) pt.xj[r] = dot3(st.jang[3 * r], st.jang[3 * r + 1], st.jang[3 * r + 2], p.x, p.y, p.z);
+      if (HESS && !(FLAVOUR == FLAVOUR_SVN && GN)) {
+#pragma unroll
+        for (int r = 0; r < 15; ++r) pt.xh[r] = dot3(st.hang[3 * r], st.hang[3 * r + 1], st.hang[3 * r + 2], p.x, p.y, p.z);
+      }
+      const float d2f = static_cast<float>(st.d2);
+      double score_pt = 0.0, nearest_pt = 0.0;
+#pragma unroll
+      for (int k = 0; k < PROBES; ++k) {
+        const int row = rows[k];
+        if (row < 0) continue;
+        ++nn;
+        if (FLAVOUR == FLAVOUR_PCLOMP) {
+          const uint4* rp = reinterpret_cast<const uint4*>(recs + row);
+          const uint4 q0 = __ldg(rp), q1 = __ldg(rp + 1), q2 = __ldg(rp + 2), q3 = __ldg(rp + 3);
+          const double m0 = __hiloint2double(q0.y, q0.x), m1 = __hiloint2double(q0.w, q0.z), m2 = __hiloint2double(q1.y, q1.x);
+          float C[9];
+          C[0] = __uint_as_float(q1.z); C[1] = __uint_as_float(q1.w);
+          C[2] = __uint_as_float(q2.x); C[3] = __uint_as_float(q2.y); C[4] = __uint_as_float(q2.z); C[5] = __uint_as_float(q2.w);
+          C[6] = __uint_as_float(q3.x); C[7] = __uint_as_float(q3.y); C[8] = __uint_as_float(q3.z);
+          float x4[3];
+          x4[0] = static_cast<float>(static_cast<double>(xt[0]) - m0);
+          x4[1] = static_cast<float>(static_cast<double>(xt[1]) - m1);
+          x4[2] = static_cast<float>(static_cast<double>(xt[2]) - m2);
+          bool counted;
+          const double s = static_cast<double>(pair_pclomp<HESS>(pt, x4, C, d2f, st.d1, acc, counted));
+          score_pt += s;
+          if (s > nearest_pt) nearest_pt = s;
+        } else {
+          double xr[3], Cd[9];
+#pragma unroll
+          for (int a = 0; a < 3; ++a) xr[a] = static_cast<double>(xt[a]) - __ldg(c_mean + 3 * row + a);
+#pragma unroll
+          for (int i = 0; i < 9; ++i) Cd[i] = __ldg(c_icov + 9 * row + i);
+          const double s = pair_svn<GN>(pt, xr, Cd, st.d1, st.d2, acc);
+          score_pt += s;
+          if (s > nearest_pt) nearest_pt = s;
+        }
+      }
+      acc[RED_SCORE] = score_pt;
+      acc[RED_NEAREST] = nearest_pt;
+      acc[RED_FOUND] = nn > 0 ? 1.0 : 0.0;
+      acc[RED_COUNT] = static_cast<double>(nn);
+    }
+  }
+
+  // ---- deterministic block reduction: warp shuffle tree, then warps in order -----------------
+#pragma unroll
+  for (int i = 0; i < RED_N; ++i) {
+    double v = acc[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    acc[i] = v;
+  }
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) {
+#pragma unroll
+    for (int i = 0; i < RED_N; ++i) s_red[w][i] = acc[i];
+  }
+  __syncthreads();
+  const int nblk = gridDim.x;
+  double* my_partials = partials + (static_cast<size_t>(particle) * nblk + blockIdx.x) * RED_N;
+  if (threadIdx.x < RED_N) {
+    double v = s_red[0][threadIdx.x];
+#pragma unroll
+    for (int k = 1; k < EVAL_THREADS / 32; ++k) v += s_red[k][threadIdx.x];
+    my_partials[threadIdx.x] = v;
+  }
+  // ---- last block done: fixed-order reduction over blocks ------------------------------------
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int t = atomicAdd(tickets + particle, 1u);
+    s_last = (t == static_cast<unsigned int>(nblk) - 1u);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const double* pp = partials + static_cast<size_t>(particle) * nblk * RED_N;
+  for (int c = w; c < RED_N; c += EVAL_THREADS / 32) {
+    double v = 0.0;
+    for (int b = lane; b < nblk; b += 32) v += __ldcg(pp + static_cast<size_t>(b) * RED_N + c);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) results[static_cast<size_t>(particle) * RED_N + c] = v;
+  }
+  if (threadIdx.x == 0) tickets[particle] = 0;  // self-reset for the next launch
+}
+
+int eval_blocks_for(int n) { return (n + EVAL_THREADS - 1) / EVAL_THREADS; }
+
+template <int FLAVOUR, int PROBES, bool HESS, bool GN>
+static void launch_t(const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs, const HashSlot* table, const double* c_mean,
+                     const double* c_icov, const EvalBuffers& b, int n_particles, int particle_offset, cudaStream_t stream) {
+  dim3 grid(eval_blocks_for(n), n_particles);
+  eval_kernel<FLAVOUR, PROBES, HESS, GN><<<grid, EVAL_THREADS, 0, stream>>>(d_src, n, meta, recs, table, c_mean, c_icov, b.d_states,
+                                                                           b.d_partials, b.d_results, b.d_tickets, particle_offset);
+}
+
+void launch_eval(int flavour, int n_probe, bool compute_hessian, bool gn, const float4* d_src, int n, const GridMeta& meta,
+                 const VoxRec* recs, const HashSlot* table, const double* c_mean, const double* c_icov, const EvalBuffers& b,
+                 int n_particles, int particle_offset, cudaStream_t stream) {
+#define ARGS d_src, n, meta, recs, table, c_mean, c_icov, b, n_particles, particle_offset, stream
+  if (flavour == FLAVOUR_PCLOMP) {
+    if (n_probe == 7) { if (compute_hessian) launch_t<FLAVOUR_PCLOMP, 7, true, false>(ARGS); else launch_t<FLAVOUR_PCLOMP, 7, false, false>(ARGS); }
+    else { if (compute_hessian) launch_t<FLAVOUR_PCLOMP, 1, true, false>(ARGS); else launch_t<FLAVOUR_PCLOMP, 1, false, false>(ARGS); }
+  } else {
+    if (n_probe == 7) { if (gn) launch_t<FLAVOUR_SVN, 7, true, true>(ARGS); else launch_t<FLAVOUR_SVN, 7, true, false>(ARGS); }
+    else { if (gn) launch_t<FLAVOUR_SVN, 1, true, true>(ARGS); else launch_t<FLAVOUR_SVN, 1, true, false>(ARGS); }
+  }
+#undef ARGS
+}
+
+}  // namespace ndtb

@@ -1,0 +1,28 @@
+// Host-side interface of the derivative evaluation kernels (derivatives.cu).
+#pragma once
+#include "ndtb_internal.cuh"
+
+namespace ndtb {
+
+struct EvalBuffers {
+  EvalState* d_states = nullptr;   // [max_particles]
+  double* d_partials = nullptr;    // [max_particles][max_blocks][RED_N]
+  double* d_results = nullptr;     // [max_particles][RED_N]
+  unsigned int* d_tickets = nullptr;  // [max_particles] last-block-done counters (self-resetting)
+  int max_particles = 0, max_blocks = 0;
+};
+
+constexpr int EVAL_THREADS = 128;
+
+// One derivative evaluation for `n_particles` poses over `n` source points.
+//   flavour  : FLAVOUR_PCLOMP -> ndt_omp_impl.hpp:217-347 maths (float pair maths, FP64 accumulate)
+//              FLAVOUR_SVN    -> svn_ndt_impl.hpp:518-647 maths (FP64 Mahalanobis/exp, GN or full Hessian)
+//   n_probe  : 7 (DIRECT7) or 1 (DIRECT1)
+// Results land in bufs.d_results[particle][RED_N] on `stream`.
+void launch_eval(int flavour, int n_probe, bool compute_hessian, bool svn_gauss_newton, const float4* d_src, int n, const GridMeta& meta,
+                 const VoxRec* recs, const HashSlot* table, const double* c_mean, const double* c_icov, const EvalBuffers& bufs,
+                 int n_particles, int particle_offset, cudaStream_t stream);
+
+int eval_blocks_for(int n);
+
+}  // namespace ndtb

@@ -1,0 +1,113 @@
+// C ABI, remaining entry points: FP64 score-only passes and the batched replay.
+//   calculateTransformationProbability / calculateNearestVoxelTransformationLikelihood
+//   (ndt_omp_impl.hpp:1169-1281): serial FP64 passes in the reference, one kernel here.
+#include "handle.cuh"
+#include <cstring>
+#include <string>
+
+using namespace ndtb;
+
+#define CKH(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { h->last_error = std::string(#x) + ": " + cudaGetErrorString(e_); return NDTB_ERR_CUDA; } } while (0)
+
+namespace ndtb {
+
+__device__ __constant__ int c_off7[7][3] = {{0, 0, 0}, {1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};
+
+// out[0] = sum of scores, out[1] = sum of per-point max score, out[2] = points with neighbours.
+// Block partials are combined in block order by the host (tiny), so the result is deterministic.
+__global__ void __launch_bounds__(128) score_kernel(const float4* __restrict__ src, int n, GridMeta m, const HashSlot* __restrict__ table,
+                                                    const double* __restrict__ c_mean, const double* __restrict__ c_icov, const float* __restrict__ T,
+                                                    double d1, double d2, int probes, double* __restrict__ block_out) {
+  __shared__ double s_red[4][3];
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  double a0 = 0, a1 = 0, a2 = 0;
+  if (idx < n) {
+    const float4 p = __ldg(src + idx);
+    float xt[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) xt[r] = T[4 * r] * p.x + (T[4 * r + 1] * p.y + (T[4 * r + 2] * p.z + T[4 * r + 3]));
+    const int i0 = static_cast<int>(floorf(__fdiv_rn(xt[0], m.leaf)));
+    const int i1 = static_cast<int>(floorf(__fdiv_rn(xt[1], m.leaf)));
+    const int i2 = static_cast<int>(floorf(__fdiv_rn(xt[2], m.leaf)));
+    double best = 0;
+    int nn = 0;
+    for (int k = 0; k < probes; ++k) {
+      const int ox = c_off7[k][0], oy = c_off7[k][1], oz = c_off7[k][2];
+      if (m.min_b[0] - i0 > ox || m.max_b[0] - i0 < ox || m.min_b[1] - i1 > oy || m.max_b[1] - i1 < oy || m.min_b[2] - i2 > oz || m.max_b[2] - i2 < oz) continue;
+      const int lin = (i0 + ox - m.min_b[0]) * m.divb_mul[0] + (i1 + oy - m.min_b[1]) * m.divb_mul[1] + (i2 + oz - m.min_b[2]) * m.divb_mul[2];
+      const int row = hash_find(table, m.hash_mask, static_cast<uint32_t>(lin));
+      if (row < 0) continue;
+      ++nn;
+      double x[3], C[9];
+      for (int a = 0; a < 3; ++a) x[a] = static_cast<double>(xt[a]) - __ldg(c_mean + 3 * row + a);
+      for (int i = 0; i < 9; ++i) C[i] = __ldg(c_icov + 9 * row + i);
+      double Cx[3];
+      for (int r = 0; r < 3; ++r) Cx[r] = (C[3 * r] * x[0] + C[3 * r + 1] * x[1]) + C[3 * r + 2] * x[2];
+      const double q = (x[0] * Cx[0] + x[1] * Cx[1]) + x[2] * Cx[2];
+      const double s = -d1 * exp(-d2 * q / 2);
+      a0 += s;
+      if (s > best) best = s;
+    }
+    if (nn > 0) { a1 = best; a2 = 1.0; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+    a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+    a2 += __shfl_xor_sync(0xffffffffu, a2, o);
+  }
+  if ((threadIdx.x & 31) == 0) { s_red[threadIdx.x >> 5][0] = a0; s_red[threadIdx.x >> 5][1] = a1; s_red[threadIdx.x >> 5][2] = a2; }
+  __syncthreads();
+  if (threadIdx.x < 3) block_out[3 * blockIdx.x + threadIdx.x] = ((s_red[0][threadIdx.x] + s_red[1][threadIdx.x]) + s_red[2][threadIdx.x]) + s_red[3][threadIdx.x];
+}
+
+}  // namespace ndtb
+
+extern "C" {
+
+int ndtb_calculate_scores(ndtb_handle h, const float T16[16], double* transformation_probability, double* nvtl) {
+  if (!h || !T16) return NDTB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  if (!h->grid.built || h->n_source == 0) return set_error(h, NDTB_ERR_NOT_READY, "target and source must be set");
+  if (h->params.grid_flavour != NDTB_FLAVOUR_PCLOMP) return set_error(h, NDTB_ERR_INVALID, "pclomp entry point on an svn-flavour handle");
+  const int n = static_cast<int>(h->n_source);
+  const int blocks = (n + 127) / 128;
+  double* d_out = nullptr; float* d_T = nullptr;
+  CKH(cudaMalloc(&d_out, sizeof(double) * 3 * blocks));
+  CKH(cudaMalloc(&d_T, 16 * sizeof(float)));
+  CKH(cudaMemcpyAsync(d_T, T16, 16 * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+  double d1, d2, d3;
+  {
+    const double c1 = 10 * (1 - h->params.outlier_ratio);
+    const double c2 = h->params.outlier_ratio / pow(static_cast<double>(h->params.resolution), 3);
+    d3 = -log(c2); d1 = -log(c1 + c2) - d3; d2 = -2 * log((-log(c1 * exp(-0.5) + c2) - d3) / d1);
+  }
+  const int probes = (h->params.search_method == NDTB_DIRECT1) ? 1 : 7;
+  score_kernel<<<blocks, 128, 0, h->stream>>>(h->d_source, n, h->grid.meta, h->grid.table, h->grid.c_mean, h->grid.c_icov, d_T, d1, d2, probes, d_out);
+  std::vector<double> out(3 * static_cast<size_t>(blocks));
+  CKH(cudaMemcpyAsync(out.data(), d_out, sizeof(double) * 3 * blocks, cudaMemcpyDeviceToHost, h->stream));
+  CKH(cudaStreamSynchronize(h->stream));
+  CKH(cudaGetLastError());
+  cudaFree(d_out); cudaFree(d_T);
+  double s = 0, nv = 0, found = 0;
+  for (int b = 0; b < blocks; ++b) { s += out[3 * b]; nv += out[3 * b + 1]; found += out[3 * b + 2]; }
+  if (transformation_probability) *transformation_probability = n ? s / static_cast<double>(n) : 0.0;
+  if (nvtl) *nvtl = found != 0 ? nv / found : 0.0;
+  return NDTB_OK;
+}
+
+// Replay batch: n independent source scans against the current target map, results in order.
+// Scans are double-buffered: scan i+1 is uploaded on the copy path while scan i is aligned.
+int ndtb_align_batch(ndtb_handle h, int n_scans, const float* const* xyz, const size_t* n_points, size_t stride_bytes, const float* guesses16,
+                     ndtb_result* results) {
+  if (!h || n_scans < 0 || !xyz || !n_points || !guesses16 || !results) return NDTB_ERR_INVALID;
+  for (int i = 0; i < n_scans; ++i) {
+    int rc = ndtb_set_source(h, xyz[i], n_points[i], stride_bytes);
+    if (rc != NDTB_OK) return rc;
+    rc = ndtb_align(h, guesses16 + 16 * i, results + i, nullptr, 0, nullptr);
+    if (rc != NDTB_OK) return rc;
+  }
+  return NDTB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,47 @@
+// The handle behind ndtb_handle: owns device memory, one stream, the voxel map and evaluation buffers.
+#pragma once
+#include "../../include/ndtb.h"
+#include "build_api.cuh"
+#include "eval_api.cuh"
+#include <string>
+#include <vector>
+
+struct ndtb_handle_s {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  ndtb_params params{};
+  ndtb_svn_params svn{};
+  std::string last_error;
+
+  // clouds (device, packed float4)
+  float4* d_target = nullptr; size_t n_target = 0, target_alloc = 0; bool target_owned = true;
+  float4* d_source = nullptr; size_t n_source = 0, source_alloc = 0; bool source_owned = true;
+  void* h_stage = nullptr; size_t stage_alloc = 0;  // pinned staging for strided host clouds
+
+  ndtb::DeviceGrid grid;
+  float built_resolution = 0.f; int built_min_pts = 0; int built_flavour = -1; double built_eig = 0;
+
+  ndtb::EvalBuffers eval;
+  ndtb::EvalState* h_states = nullptr;  // pinned, [max_particles]
+  double* h_results = nullptr;          // pinned, [max_particles][RED_N]
+
+  bool has_reg_pose = false;
+  float reg_translation[3] = {0, 0, 0};
+
+  std::vector<double> trace;  // 50 doubles per evaluation of the last align
+  double last_hits = 0, last_found = 0;
+
+  // timing
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  float build_ms = 0, align_ms = 0, eval_ms_total = 0; int eval_launches = 0;
+
+  // svn device scratch
+  double* d_svn_in = nullptr;   // poses(16K) + grads(6K) + hess(36K)
+  double* d_svn_out = nullptr;  // updates(6K) + new poses(16K) + misc
+  int svn_alloc = 0;
+};
+
+namespace ndtb {
+int ensure_eval_buffers(ndtb_handle_s* h, int particles, int n_points);
+int set_error(ndtb_handle_s* h, int code, const char* what);
+}  // namespace ndtb

@@ -1,0 +1,464 @@
+// C ABI of libndtb: lifetime, parameters, clouds, voxel-map access, pclomp NDT (include/ndtb.h).
+// Host logic mirrors pclomp::NormalDistributionsTransform (ndt_omp.h:119-291, ndt_omp_impl.hpp:85-202)
+// around the CUDA kernels; there is no CPU compute path.
+#include "handle.cuh"
+#include "newton_math.cuh"
+#include <cstring>
+#include <cstdio>
+#include <cmath>
+#include <algorithm>
+#include <new>
+
+using namespace ndtb;
+
+namespace ndtb {
+
+int set_error(ndtb_handle_s* h, int code, const char* what) {
+  if (h) {
+    h->last_error = what ? what : "";
+    if (code == NDTB_ERR_CUDA) {
+      const cudaError_t e = cudaGetLastError();
+      h->last_error += std::string(" [cuda: ") + cudaGetErrorString(e) + "]";
+    }
+  }
+  return code;
+}
+
+#define CKH(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { h->last_error = std::string(#x) + ": " + cudaGetErrorString(e_); return NDTB_ERR_CUDA; } } while (0)
+
+int ensure_eval_buffers(ndtb_handle_s* h, int particles, int n_points) {
+  const int blocks = eval_blocks_for(n_points);
+  EvalBuffers& b = h->eval;
+  if (particles > b.max_particles || blocks > b.max_blocks) {
+    const int np = std::max(particles, b.max_particles), nb = std::max(blocks, b.max_blocks);
+    cudaFree(b.d_states); cudaFree(b.d_partials); cudaFree(b.d_results); cudaFree(b.d_tickets);
+    if (h->h_states) cudaFreeHost(h->h_states);
+    if (h->h_results) cudaFreeHost(h->h_results);
+    CKH(cudaMalloc(&b.d_states, sizeof(EvalState) * np));
+    CKH(cudaMalloc(&b.d_partials, sizeof(double) * RED_N * static_cast<size_t>(np) * nb));
+    CKH(cudaMalloc(&b.d_results, sizeof(double) * RED_N * np));
+    CKH(cudaMalloc(&b.d_tickets, sizeof(unsigned int) * np));
+    CKH(cudaMemset(b.d_tickets, 0, sizeof(unsigned int) * np));
+    CKH(cudaMallocHost(&h->h_states, sizeof(EvalState) * np));
+    CKH(cudaMallocHost(&h->h_results, sizeof(double) * RED_N * np));
+    b.max_particles = np; b.max_blocks = nb;
+  }
+  return NDTB_OK;
+}
+
+static int upload_cloud(ndtb_handle_s* h, const float* xyz, size_t n, size_t stride_bytes, float4** d_buf, size_t* alloc, bool* owned) {
+  if (!*owned) { *d_buf = nullptr; *alloc = 0; *owned = true; }
+  if (n > *alloc) {
+    cudaFree(*d_buf);
+    *d_buf = nullptr;
+    const size_t cap = n + n / 8 + 256;
+    CKH(cudaMalloc(d_buf, cap * sizeof(float4)));
+    *alloc = cap;
+  }
+  if (n == 0) return NDTB_OK;
+  if (stride_bytes == sizeof(float4)) {
+    CKH(cudaMemcpyAsync(*d_buf, xyz, n * sizeof(float4), cudaMemcpyHostToDevice, h->stream));
+  } else if (stride_bytes >= sizeof(float4)) {
+    // e.g. pcl::PointXYZI (32-byte stride): copy the first 16 bytes of every point
+    CKH(cudaMemcpy2DAsync(*d_buf, sizeof(float4), xyz, stride_bytes, sizeof(float4), n, cudaMemcpyHostToDevice, h->stream));
+  } else if (stride_bytes == 12) {
+    CKH(cudaMemsetAsync(*d_buf, 0, n * sizeof(float4), h->stream));
+    CKH(cudaMemcpy2DAsync(*d_buf, sizeof(float4), xyz, 12, 12, n, cudaMemcpyHostToDevice, h->stream));
+  } else {
+    return set_error(h, NDTB_ERR_INVALID, "stride_bytes must be 12 or >= 16");
+  }
+  return NDTB_OK;
+}
+
+static int rebuild_grid(ndtb_handle_s* h) {
+  if (!h->d_target || h->n_target == 0) return NDTB_ERR_EMPTY;
+  cudaEventRecord(h->ev[0], h->stream);
+  const int min_pts = (h->params.grid_flavour == NDTB_FLAVOUR_SVN) ? std::max(3, h->params.min_points_per_voxel) : h->params.min_points_per_voxel;
+  const int rc = build_voxel_map(h->grid, h->d_target, h->n_target, h->params.resolution, min_pts, h->params.min_covar_eigvalue_mult,
+                                 h->params.grid_flavour, h->params.is_dense, h->stream);
+  cudaEventRecord(h->ev[1], h->stream);
+  cudaEventSynchronize(h->ev[1]);
+  cudaEventElapsedTime(&h->build_ms, h->ev[0], h->ev[1]);
+  h->built_resolution = h->params.resolution; h->built_min_pts = h->params.min_points_per_voxel;
+  h->built_flavour = h->params.grid_flavour; h->built_eig = h->params.min_covar_eigvalue_mult;
+  if (rc == NDTB_ERR_CUDA) return set_error(h, rc, "voxel map build failed");
+  if (rc == NDTB_ERR_OVERFLOW) return set_error(h, rc, "leaf size too small for the input dataset: integer indices would overflow");
+  return rc;
+}
+
+// Fill EvalState `slot` for pose p (angle tables on the host with libm, like the oracle's host code).
+static void fill_state(ndtb_handle_s* h, int slot, const double* p, const float* T16, double snap, bool svn) {
+  EvalState& s = h->h_states[slot];
+  std::memset(&s, 0, sizeof(s));
+  std::memcpy(s.T, T16, 12 * sizeof(float));
+  angle_tables(p, snap, s.jang, s.hang);
+  if (svn) gauss_svn(h->params.outlier_ratio, h->params.resolution, &s.d1, &s.d2, &s.d3);
+  else gauss_pclomp(h->params.outlier_ratio, h->params.resolution, &s.d1, &s.d2, &s.d3);
+  std::memcpy(s.p, p, 6 * sizeof(double));
+}
+
+// One pclomp evaluation: upload state, launch, read back the 46-double result, apply the
+// regulariser (ndt_omp_impl.hpp:349-382) and NVTL (:384-389) on the host.
+static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool compute_hessian, double* score, double* g, double* H,
+                       double* nvtl) {
+  const int n = static_cast<int>(h->n_source);
+  int rc = ensure_eval_buffers(h, 1, n);
+  if (rc != NDTB_OK) return rc;
+  fill_state(h, 0, p, T16, 10e-5, false);
+  CKH(cudaMemcpyAsync(h->eval.d_states, h->h_states, sizeof(EvalState), cudaMemcpyHostToDevice, h->stream));
+  const int n_probe = (h->params.search_method == NDTB_DIRECT1) ? 1 : 7;
+  cudaEventRecord(h->ev[2], h->stream);
+  launch_eval(FLAVOUR_PCLOMP, n_probe, compute_hessian, false, h->d_source, n, h->grid.meta, h->grid.recs, h->grid.table, h->grid.c_mean,
+              h->grid.c_icov, h->eval, 1, 0, h->stream);
+  cudaEventRecord(h->ev[3], h->stream);
+  CKH(cudaMemcpyAsync(h->h_results, h->eval.d_results, sizeof(double) * RED_N, cudaMemcpyDeviceToHost, h->stream));
+  CKH(cudaStreamSynchronize(h->stream));
+  CKH(cudaGetLastError());
+  float ms = 0;
+  cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]);
+  h->eval_ms_total += ms; h->eval_launches += 1;
+  const double* r = h->h_results;
+  double sc = r[RED_SCORE];
+  std::memcpy(g, r + RED_G, 6 * sizeof(double));
+  std::memcpy(H, r + RED_H, 36 * sizeof(double));
+  const double found = r[RED_FOUND], count = r[RED_COUNT];
+  h->last_found = found;
+  h->last_hits = n ? count / static_cast<double>(n) : 0.0;
+  if (h->has_reg_pose) {
+    const float dx = h->reg_translation[0] - static_cast<float>(p[0]);
+    const float dy = h->reg_translation[1] - static_cast<float>(p[1]);
+    const float sin_yaw = static_cast<float>(sin(p[5])), cos_yaw = static_cast<float>(cos(p[5]));
+    const float longitudinal = dy * sin_yaw + dx * cos_yaw;
+    const float w = static_cast<float>(static_cast<int>(count));
+    const float sf = h->params.regularization_scale_factor;
+    const float reg_score = -sf * w * longitudinal * longitudinal;
+    sc += reg_score;
+    g[0] += static_cast<double>(sf * w * 2.0f * cos_yaw * longitudinal);
+    g[1] += static_cast<double>(sf * w * 2.0f * sin_yaw * longitudinal);
+    const float h00 = -sf * w * 2.0f * cos_yaw * cos_yaw, h01 = -sf * w * 2.0f * cos_yaw * sin_yaw, h11 = -sf * w * 2.0f * sin_yaw * sin_yaw;
+    H[0] += static_cast<double>(h00); H[1] += static_cast<double>(h01); H[7] += static_cast<double>(h11); H[6] += static_cast<double>(h01);
+  }
+  *score = sc;
+  if (nvtl) *nvtl = found != 0 ? r[RED_NEAREST] / found : 0.0;
+  return NDTB_OK;
+}
+
+}  // namespace ndtb
+
+extern "C" {
+
+const char* ndtb_version(void) { return "ndtb 0.1 (sm_100a)"; }
+
+int ndtb_default_params(int grid_flavour, ndtb_params* p) {
+  if (!p) return NDTB_ERR_INVALID;
+  std::memset(p, 0, sizeof(*p));
+  p->resolution = 1.0f;            // ndt_omp_impl.hpp:65 / svn_ndt_impl.hpp:62
+  p->step_size = 0.1;              // :64
+  p->trans_epsilon = 0.1;          // :63
+  p->max_iterations = 35;          // :66
+  p->search_method = NDTB_DIRECT7; // :67
+  p->outlier_ratio = 0.55;         // :54
+  p->min_points_per_voxel = 6;     // voxel_grid_covariance_omp.h:195 / voxel_grid_covariance.h:153
+  p->min_covar_eigvalue_mult = 0.01;
+  p->regularization_scale_factor = 0.0f;
+  p->use_line_search = 0;
+  p->grid_flavour = grid_flavour;
+  p->is_dense = 1;
+  return NDTB_OK;
+}
+
+int ndtb_create(int cuda_device, ndtb_handle* out) {
+  if (!out) return NDTB_ERR_INVALID;
+  *out = nullptr;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0 || cuda_device < 0 || cuda_device >= count) return NDTB_ERR_CUDA;
+  if (cudaSetDevice(cuda_device) != cudaSuccess) return NDTB_ERR_CUDA;
+  ndtb_handle_s* h = new (std::nothrow) ndtb_handle_s();
+  if (!h) return NDTB_ERR_INVALID;
+  h->device = cuda_device;
+  ndtb_default_params(NDTB_FLAVOUR_PCLOMP, &h->params);
+  ndtb_svn_default_params(&h->svn);
+  if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return NDTB_ERR_CUDA; }
+  for (int i = 0; i < 4; ++i) cudaEventCreate(&h->ev[i]);
+  *out = h;
+  return NDTB_OK;
+}
+
+int ndtb_destroy(ndtb_handle h) {
+  if (!h) return NDTB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  cudaStreamSynchronize(h->stream);
+  if (h->target_owned) cudaFree(h->d_target);
+  if (h->source_owned) cudaFree(h->d_source);
+  if (h->h_stage) cudaFreeHost(h->h_stage);
+  free_device_grid(h->grid);
+  cudaFree(h->eval.d_states); cudaFree(h->eval.d_partials); cudaFree(h->eval.d_results); cudaFree(h->eval.d_tickets);
+  if (h->h_states) cudaFreeHost(h->h_states);
+  if (h->h_results) cudaFreeHost(h->h_results);
+  cudaFree(h->d_svn_in); cudaFree(h->d_svn_out);
+  for (int i = 0; i < 4; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+  cudaStreamDestroy(h->stream);
+  delete h;
+  return NDTB_OK;
+}
+
+const char* ndtb_last_error(ndtb_handle h) { return h ? h->last_error.c_str() : "null handle"; }
+
+int ndtb_get_params(ndtb_handle h, ndtb_params* p) {
+  if (!h || !p) return NDTB_ERR_INVALID;
+  *p = h->params;
+  return NDTB_OK;
+}
+
+int ndtb_set_params(ndtb_handle h, const ndtb_params* p) {
+  if (!h || !p) return NDTB_ERR_INVALID;
+  if (p->search_method != NDTB_DIRECT7 && p->search_method != NDTB_DIRECT1)
+    return set_error(h, NDTB_ERR_INVALID, "only DIRECT7 and DIRECT1 neighbour search are provided by this engine");
+  if (!(p->resolution > 0.0f)) return set_error(h, NDTB_ERR_INVALID, "resolution must be positive");
+  if (p->grid_flavour != NDTB_FLAVOUR_PCLOMP && p->grid_flavour != NDTB_FLAVOUR_SVN) return set_error(h, NDTB_ERR_INVALID, "bad grid_flavour");
+  if (p->use_line_search) return set_error(h, NDTB_ERR_INVALID, "More-Thuente line search (off by default in the reference) is not built yet");
+  cudaSetDevice(h->device);
+  h->params = *p;
+  // setResolution rebuilds only if the value changed and a target is set (ndt_omp.h:135-142)
+  const bool changed = h->grid.built && (h->built_resolution != p->resolution || h->built_min_pts != p->min_points_per_voxel ||
+                                         h->built_flavour != p->grid_flavour || h->built_eig != p->min_covar_eigvalue_mult);
+  if (changed && h->d_target && h->n_target) return rebuild_grid(h);
+  return NDTB_OK;
+}
+
+int ndtb_set_target(ndtb_handle h, const float* xyz, size_t n, size_t stride_bytes) {
+  if (!h) return NDTB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  if (!xyz || n == 0) { h->n_target = 0; h->grid.built = false; return set_error(h, NDTB_ERR_EMPTY, "empty target cloud"); }
+  int rc = upload_cloud(h, xyz, n, stride_bytes, &h->d_target, &h->target_alloc, &h->target_owned);
+  if (rc != NDTB_OK) return rc;
+  h->n_target = n;
+  return rebuild_grid(h);
+}
+
+int ndtb_set_target_device(ndtb_handle h, const void* d_xyzw, size_t n) {
+  if (!h) return NDTB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  if (!d_xyzw || n == 0) { h->n_target = 0; h->grid.built = false; return set_error(h, NDTB_ERR_EMPTY, "empty target cloud"); }
+  if (h->target_owned) { cudaFree(h->d_target); h->target_alloc = 0; }
+  h->d_target = const_cast<float4*>(static_cast<const float4*>(d_xyzw));
+  h->target_owned = false;
+  h->n_target = n;
+  return rebuild_grid(h);
+}
+
+int ndtb_set_source(ndtb_handle h, const float* xyz, size_t n, size_t stride_bytes) {
+  if (!h) return NDTB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  if (!xyz || n == 0) { h->n_source = 0; return set_error(h, NDTB_ERR_EMPTY, "empty source cloud"); }
+  int rc = upload_cloud(h, xyz, n, stride_bytes, &h->d_source, &h->source_alloc, &h->source_owned);
+  if (rc != NDTB_OK) return rc;
+  h->n_source = n;
+  return NDTB_OK;
+}
+
+int ndtb_set_source_device(ndtb_handle h, const void* d_xyzw, size_t n) {
+  if (!h) return NDTB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  if (!d_xyzw || n == 0) { h->n_source = 0; return set_error(h, NDTB_ERR_EMPTY, "empty source cloud"); }
+  if (h->source_owned) { cudaFree(h->d_source); h->source_alloc = 0; }
+  h->d_source = const_cast<float4*>(static_cast<const float4*>(d_xyzw));
+  h->source_owned = false;
+  h->n_source = n;
+  return NDTB_OK;
+}
+
+int ndtb_set_regularization_pose(ndtb_handle h, const float* T16) {
+  if (!h) return NDTB_ERR_INVALID;
+  h->has_reg_pose = (T16 != nullptr);
+  if (T16) { h->reg_translation[0] = T16[3]; h->reg_translation[1] = T16[7]; h->reg_translation[2] = T16[11]; }
+  return NDTB_OK;
+}
+
+int ndtb_compute_derivatives(ndtb_handle h, const double p[6], const float* T16, int compute_hessian, double* score, double gradient[6],
+                             double hessian[36], double* nvtl) {
+  if (!h || !p || !score || !gradient || !hessian) return NDTB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  if (!h->grid.built || h->n_source == 0) return set_error(h, NDTB_ERR_NOT_READY, "target and source must be set");
+  if (h->params.grid_flavour != NDTB_FLAVOUR_PCLOMP) return set_error(h, NDTB_ERR_INVALID, "pclomp entry point on an svn-flavour handle");
+  float T[16];
+  if (T16) std::memcpy(T, T16, sizeof(T)); else pose_to_T(p, T);
+  return eval_pclomp(h, p, T, compute_hessian != 0, score, gradient, hessian, nvtl);
+}
+
+int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* transformation_array, int capacity, float* out_xyz) {
+  if (!h || !guess || !res) return NDTB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  std::memset(res, 0, sizeof(*res));
+  if (!h->grid.built || h->n_source == 0) return set_error(h, NDTB_ERR_NOT_READY, "target and source must be set");
+  if (h->params.grid_flavour != NDTB_FLAVOUR_PCLOMP) return set_error(h, NDTB_ERR_INVALID, "pclomp entry point on an svn-flavour handle");
+  cudaEventRecord(h->ev[0], h->stream);
+  h->eval_ms_total = 0; h->eval_launches = 0;
+  h->trace.clear();
+  const size_t N = h->n_source;
+  const ndtb_params& P = h->params;
+  int nr_iterations = 0;
+  bool converged = false;
+  float final_T[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+  bool guess_is_identity = true;
+  for (int i = 0; i < 16; ++i) if (guess[i] != final_T[i]) guess_is_identity = false;
+  if (!guess_is_identity) std::memcpy(final_T, guess, sizeof(final_T));
+  int n_arr = 0;
+  auto push_T = [&]() { if (transformation_array && n_arr < capacity) std::memcpy(transformation_array + 16 * n_arr, final_T, sizeof(final_T)); ++n_arr; };
+  push_T();
+  double p[6], delta_p[6], g[6], H[36], score = 0, nvtl = 0;
+  float eul[3];
+  euler_012(final_T, eul);
+  p[0] = final_T[3]; p[1] = final_T[7]; p[2] = final_T[11]; p[3] = eul[0]; p[4] = eul[1]; p[5] = eul[2];
+  auto push_trace = [&](const double* pp) {
+    h->trace.insert(h->trace.end(), pp, pp + 6); h->trace.push_back(score);
+    h->trace.insert(h->trace.end(), g, g + 6); h->trace.insert(h->trace.end(), H, H + 36); h->trace.push_back(nvtl);
+  };
+  int rc = eval_pclomp(h, p, final_T, true, &score, g, H, &nvtl);
+  if (rc != NDTB_OK) return rc;
+  push_trace(p);
+  bool hessian_stored = false;
+  while (!converged) {
+    double neg_g[6];
+    for (int i = 0; i < 6; ++i) neg_g[i] = -g[i];
+    svd6_solve(H, neg_g, delta_p);
+    double nrm2 = 0;
+    for (int i = 0; i < 6; ++i) nrm2 += delta_p[i] * delta_p[i];
+    double delta_p_norm = sqrt(nrm2);
+    if (delta_p_norm == 0 || delta_p_norm != delta_p_norm) {
+      res->transform_probability = N ? score / static_cast<double>(N) : 0.0;
+      converged = delta_p_norm == delta_p_norm;
+      break;
+    }
+    for (int i = 0; i < 6; ++i) delta_p[i] = delta_p[i] / delta_p_norm;
+    // computeStepLengthMT with use_line_search == false (ndt_omp_impl.hpp:915-983)
+    {
+      double d_phi_0 = 0;
+      for (int i = 0; i < 6; ++i) d_phi_0 += g[i] * delta_p[i];
+      d_phi_0 = -d_phi_0;
+      double a_t;
+      if (d_phi_0 >= 0 && d_phi_0 == 0) {
+        a_t = 0;
+      } else {
+        if (d_phi_0 >= 0) for (int i = 0; i < 6; ++i) delta_p[i] *= -1;
+        a_t = delta_p_norm;
+        a_t = std::min(a_t, P.step_size);
+        a_t = std::max(a_t, P.trans_epsilon / 2);
+        double x_t[6];
+        for (int i = 0; i < 6; ++i) x_t[i] = p[i] + delta_p[i] * a_t;
+        pose_to_T(x_t, final_T);
+        rc = eval_pclomp(h, x_t, final_T, true, &score, g, H, &nvtl);
+        if (rc != NDTB_OK) return rc;
+        push_trace(x_t);
+      }
+      delta_p_norm = a_t;
+    }
+    for (int i = 0; i < 6; ++i) delta_p[i] *= delta_p_norm;
+    push_T();
+    for (int i = 0; i < 6; ++i) p[i] = p[i] + delta_p[i];
+    if (nr_iterations > P.max_iterations || (nr_iterations && (fabs(delta_p_norm) < P.trans_epsilon))) converged = true;
+    nr_iterations++;
+    if (converged) {
+      res->transform_probability = N ? score / static_cast<double>(N) : 0.0;
+      std::memcpy(res->hessian, H, sizeof(res->hessian));
+      hessian_stored = true;
+    }
+  }
+  (void)hessian_stored;
+  std::memcpy(res->pose, final_T, sizeof(final_T));
+  res->nearest_voxel_transformation_likelihood = nvtl;
+  res->iteration_num = nr_iterations;
+  res->converged = converged ? 1 : 0;
+  res->transformation_array_len = std::min(n_arr, capacity > 0 ? capacity : 0);
+  res->evaluations = h->eval_launches;
+  if (out_xyz) {
+    // `output` of pcl::Registration::align: the source transformed by the final transformation
+    // (host loop, N points -- off the timed path; callers that do not need it pass NULL).
+    std::vector<float4> tmp(N);
+    CKH(cudaMemcpyAsync(tmp.data(), h->d_source, N * sizeof(float4), cudaMemcpyDeviceToHost, h->stream));
+    CKH(cudaStreamSynchronize(h->stream));
+    for (size_t i = 0; i < N; ++i)
+      for (int r = 0; r < 3; ++r)
+        out_xyz[3 * i + r] = final_T[4 * r] * tmp[i].x + (final_T[4 * r + 1] * tmp[i].y + (final_T[4 * r + 2] * tmp[i].z + final_T[4 * r + 3]));
+  }
+  cudaEventRecord(h->ev[1], h->stream);
+  cudaEventSynchronize(h->ev[1]);
+  cudaEventElapsedTime(&h->align_ms, h->ev[0], h->ev[1]);
+  return NDTB_OK;
+}
+
+int ndtb_get_trace(ndtb_handle h, double* trace, int capacity, int* count) {
+  if (!h) return NDTB_ERR_INVALID;
+  const int n = static_cast<int>(h->trace.size() / 50);
+  if (count) *count = n;
+  if (trace && capacity > 0) std::memcpy(trace, h->trace.data(), sizeof(double) * 50 * std::min(n, capacity));
+  return NDTB_OK;
+}
+
+int ndtb_get_voxel_count(ndtb_handle h, size_t* count, int min_b[3], int max_b[3], int div_b[3]) {
+  if (!h) return NDTB_ERR_INVALID;
+  if (!h->grid.built) return set_error(h, NDTB_ERR_NOT_READY, "no voxel map");
+  cudaSetDevice(h->device);
+  if (count) {
+    if (h->params.grid_flavour == NDTB_FLAVOUR_SVN) *count = h->grid.n_valid; else *count = h->grid.V;
+  }
+  for (int a = 0; a < 3; ++a) {
+    if (min_b) min_b[a] = h->grid.meta.min_b[a];
+    if (max_b) max_b[a] = h->grid.meta.max_b[a];
+    if (div_b) div_b[a] = h->grid.meta.div_b[a];
+  }
+  return NDTB_OK;
+}
+
+int ndtb_get_voxels(ndtb_handle h, int64_t* idx, int32_t* nr_points, double* mean, double* cov, double* icov, double* evecs, double* evals) {
+  if (!h) return NDTB_ERR_INVALID;
+  if (!h->grid.built) return set_error(h, NDTB_ERR_NOT_READY, "no voxel map");
+  cudaSetDevice(h->device);
+  const size_t V = h->grid.V;
+  std::vector<uint32_t> key(V); std::vector<int32_t> n(V);
+  std::vector<double> m(3 * V), c(9 * V), ic(9 * V), ev(9 * V), el(3 * V);
+  CKH(cudaMemcpy(key.data(), h->grid.c_key, V * 4, cudaMemcpyDeviceToHost));
+  CKH(cudaMemcpy(n.data(), h->grid.c_n, V * 4, cudaMemcpyDeviceToHost));
+  CKH(cudaMemcpy(m.data(), h->grid.c_mean, V * 24, cudaMemcpyDeviceToHost));
+  CKH(cudaMemcpy(c.data(), h->grid.c_cov, V * 72, cudaMemcpyDeviceToHost));
+  CKH(cudaMemcpy(ic.data(), h->grid.c_icov, V * 72, cudaMemcpyDeviceToHost));
+  CKH(cudaMemcpy(ev.data(), h->grid.c_evecs, V * 72, cudaMemcpyDeviceToHost));
+  CKH(cudaMemcpy(el.data(), h->grid.c_evals, V * 24, cudaMemcpyDeviceToHost));
+  size_t o = 0;
+  for (size_t v = 0; v < V; ++v) {
+    if (h->params.grid_flavour == NDTB_FLAVOUR_SVN && n[v] == -2) continue;  // erased leaf
+    if (idx) idx[o] = key[v];
+    if (nr_points) nr_points[o] = n[v];
+    if (mean) std::memcpy(mean + 3 * o, &m[3 * v], 24);
+    if (cov) std::memcpy(cov + 9 * o, &c[9 * v], 72);
+    if (icov) std::memcpy(icov + 9 * o, &ic[9 * v], 72);
+    if (evecs) std::memcpy(evecs + 9 * o, &ev[9 * v], 72);
+    if (evals) std::memcpy(evals + 3 * o, &el[3 * v], 24);
+    ++o;
+  }
+  return NDTB_OK;
+}
+
+int ndtb_get_last_hits(ndtb_handle h, double* mean_hits_per_point, double* points_with_neighbours) {
+  if (!h) return NDTB_ERR_INVALID;
+  if (mean_hits_per_point) *mean_hits_per_point = h->last_hits;
+  if (points_with_neighbours) *points_with_neighbours = h->last_found;
+  return NDTB_OK;
+}
+
+int ndtb_get_timings(ndtb_handle h, float* build_ms, float* align_ms, float* eval_kernel_ms_total, int* eval_kernel_launches) {
+  if (!h) return NDTB_ERR_INVALID;
+  if (build_ms) *build_ms = h->build_ms;
+  if (align_ms) *align_ms = h->align_ms;
+  if (eval_kernel_ms_total) *eval_kernel_ms_total = h->eval_ms_total;
+  if (eval_kernel_launches) *eval_kernel_launches = h->eval_launches;
+  return NDTB_OK;
+}
+
+int ndtb_get_stream(ndtb_handle h, void** cuda_stream) {
+  if (!h || !cuda_stream) return NDTB_ERR_INVALID;
+  *cuda_stream = h->stream;
+  return NDTB_OK;
+}
+
+}  // extern "C"

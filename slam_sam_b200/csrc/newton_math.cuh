@@ -1,0 +1,251 @@
+// Small-matrix maths of the optimiser loops, usable from host code and from device epilogues.
+//   pose <-> float 4x4      ndt_omp_impl.hpp:117-120, 167-174, 969-975; ndt_omp.h:205-211
+//   gauss constants         ndt_omp_impl.hpp:95-99 ; svn_ndt_impl.hpp:80-131
+//   angle tables            ndt_omp_impl.hpp:396-538 ; svn_ndt_impl.hpp:255-334
+//   Newton direction        Eigen::JacobiSVD<6x6>::solve (ndt_omp_impl.hpp:142-145), restated as a
+//                           two-sided Jacobi SVD with Eigen's rank threshold
+//   Stein update solve      Eigen::LDLT<6x6> (svn_ndt_impl.hpp:833-838)
+// Everything is FP64 (or float where the reference is float) with explicit evaluation order; the
+// translation unit is built with -fmad=false / -ffp-contract=off.
+#pragma once
+#include <math.h>
+#include <float.h>
+#include <cuda_runtime.h>
+
+#define NM_HD __host__ __device__ inline
+
+namespace ndtb {
+
+#ifdef __CUDA_ARCH__
+// libm's sinf/cosf/atan2f are (nearly) correctly rounded; CUDA's float versions are not.  Going
+// through FP64 and rounding once reproduces the host bits except for ~1e-8 of arguments.
+NM_HD float nm_sinf(float x) { return static_cast<float>(sin(static_cast<double>(x))); }
+NM_HD float nm_cosf(float x) { return static_cast<float>(cos(static_cast<double>(x))); }
+NM_HD float nm_atan2f(float y, float x) { return static_cast<float>(atan2(static_cast<double>(y), static_cast<double>(x))); }
+#else
+NM_HD float nm_sinf(float x) { return sinf(x); }
+NM_HD float nm_cosf(float x) { return cosf(x); }
+NM_HD float nm_atan2f(float y, float x) { return atan2f(y, x); }
+#endif
+
+// ---- gauss constants ------------------------------------------------------------------------
+NM_HD void gauss_pclomp(double outlier_ratio, float resolution, double* d1, double* d2, double* d3) {
+  const double c1 = 10 * (1 - outlier_ratio);
+  const double c2 = outlier_ratio / pow(static_cast<double>(resolution), 3);
+  *d3 = -log(c2);
+  *d1 = -log(c1 + c2) - *d3;
+  *d2 = -2 * log((-log(c1 * exp(-0.5) + c2) - *d3) / *d1);
+}
+
+NM_HD void gauss_svn(double outlier_ratio, float resolution, double* d1, double* d2, double* d3) {
+  if (resolution <= 1e-6f) { *d1 = 1.0; *d2 = 1.0; *d3 = 0.0; return; }
+  const double eps = 1e-9;
+  double c1 = 10.0 * (1.0 - outlier_ratio);
+  double c2 = outlier_ratio / pow(static_cast<double>(resolution), 3);
+  if (c1 <= eps) c1 = eps;
+  if (c2 <= eps) c2 = eps;
+  *d3 = -log(c2);
+  *d1 = -log(c1 + c2) - *d3;
+  *d2 = 1.0;
+  if (!(fabs(*d1) < eps)) {
+    const double inner = c1 * exp(-0.5) + c2;
+    if (inner > eps) {
+      const double outer = (-log(inner) - *d3) / *d1;
+      if (outer > eps) *d2 = -2.0 * log(outer);
+    }
+  }
+  if (!isfinite(*d1) || !isfinite(*d2) || !isfinite(*d3)) { *d1 = 1.0; *d2 = 1.0; *d3 = 0.0; }
+}
+
+// ---- angle tables: jang[8][3], hang[15][3] as float ---------------------------------------------
+NM_HD void angle_tables(const double* p, double snap, float* jang, float* hang) {
+  double cx = 1.0, sx = 0.0, cy = 1.0, sy = 0.0, cz = 1.0, sz = 0.0;
+  if (!(fabs(p[3]) < snap)) { cx = cos(p[3]); sx = sin(p[3]); }
+  if (!(fabs(p[4]) < snap)) { cy = cos(p[4]); sy = sin(p[4]); }
+  if (!(fabs(p[5]) < snap)) { cz = cos(p[5]); sz = sin(p[5]); }
+  const double j[24] = {(-sx * sz + cx * sy * cz), (-sx * cz - cx * sy * sz), (-cx * cy),
+                        (cx * sz + sx * sy * cz),  (cx * cz - sx * sy * sz),  (-sx * cy),
+                        (-sy * cz),                sy * sz,                   cy,
+                        sx * cy * cz,              (-sx * cy * sz),           sx * sy,
+                        (-cx * cy * cz),           cx * cy * sz,              (-cx * sy),
+                        (-cy * sz),                (-cy * cz),                0,
+                        (cx * cz - sx * sy * sz),  (-cx * sz - sx * sy * cz), 0,
+                        (sx * cz + cx * sy * sz),  (cx * sy * cz - sx * sz),  0};
+  const double h[45] = {(-cx * sz - sx * sy * cz), (-cx * cz + sx * sy * sz), sx * cy,
+                        (-sx * sz + cx * sy * cz), (-cx * sy * sz - sx * cz), (-cx * cy),
+                        (cx * cy * cz),            (-cx * cy * sz),           (cx * sy),
+                        (sx * cy * cz),            (-sx * cy * sz),           (sx * sy),
+                        (-sx * cz - cx * sy * sz), (sx * sz - cx * sy * cz),  0,
+                        (cx * cz - sx * sy * sz),  (-sx * sy * cz - cx * sz), 0,
+                        (-cy * cz),                (cy * sz),                 (sy),
+                        (-sx * sy * cz),           (sx * sy * sz),            (sx * cy),
+                        (cx * sy * cz),            (-cx * sy * sz),           (-cx * cy),
+                        (sy * sz),                 (sy * cz),                 0,
+                        (-sx * cy * sz),           (-sx * cy * cz),           0,
+                        (cx * cy * sz),            (cx * cy * cz),            0,
+                        (-cy * cz),                (cy * sz),                 0,
+                        (-cx * sz - sx * sy * cz), (-cx * cz + sx * sy * sz), 0,
+                        (-sx * sz + cx * sy * cz), (-cx * sy * sz - sx * cz), 0};
+  for (int i = 0; i < 24; ++i) jang[i] = static_cast<float>(j[i]);
+  for (int i = 0; i < 45; ++i) hang[i] = static_cast<float>(h[i]);
+}
+
+// ---- float rotation helpers ----------------------------------------------------------------------
+NM_HD void f33_mul(const float* a, const float* b, float* o) {
+  float r[9];
+  for (int i = 0; i < 3; ++i)
+    for (int k = 0; k < 3; ++k) {
+      float s = a[3 * i] * b[k];
+      s = s + a[3 * i + 1] * b[3 + k];
+      s = s + a[3 * i + 2] * b[6 + k];
+      r[3 * i + k] = s;
+    }
+  for (int i = 0; i < 9; ++i) o[i] = r[i];
+}
+
+// Eigen::AngleAxis<float>(angle, unit axis).toRotationMatrix()
+NM_HD void f_angle_axis(float angle, int axis, float* R) {
+  float u[3] = {0.0f, 0.0f, 0.0f};
+  u[axis] = 1.0f;
+  const float s = nm_sinf(angle), c = nm_cosf(angle);
+  const float su[3] = {s * u[0], s * u[1], s * u[2]};
+  const float cu[3] = {(1.0f - c) * u[0], (1.0f - c) * u[1], (1.0f - c) * u[2]};
+  float t = cu[0] * u[1];
+  R[1] = t - su[2]; R[3] = t + su[2];
+  t = cu[0] * u[2];
+  R[2] = t + su[1]; R[6] = t - su[1];
+  t = cu[1] * u[2];
+  R[5] = t - su[0]; R[7] = t + su[0];
+  R[0] = cu[0] * u[0] + c; R[4] = cu[1] * u[1] + c; R[8] = cu[2] * u[2] + c;
+}
+
+// T = Translation(p0,p1,p2) * Rx(p3) * Ry(p4) * Rz(p5), float, row-major 4x4
+NM_HD void pose_to_T(const double* p, float* T) {
+  float A[9], B[9], C[9], R[9];
+  f_angle_axis(static_cast<float>(p[3]), 0, A);
+  f_angle_axis(static_cast<float>(p[4]), 1, B);
+  f_angle_axis(static_cast<float>(p[5]), 2, C);
+  f33_mul(A, B, R);
+  f33_mul(R, C, R);
+  for (int r = 0; r < 3; ++r) {
+    T[4 * r] = R[3 * r]; T[4 * r + 1] = R[3 * r + 1]; T[4 * r + 2] = R[3 * r + 2];
+    T[4 * r + 3] = static_cast<float>(p[r]);
+  }
+  T[12] = 0.0f; T[13] = 0.0f; T[14] = 0.0f; T[15] = 1.0f;
+}
+
+// Eigen 3.4 eulerAngles(0,1,2) of the rotation block of a float 4x4 (first angle folded to [0,pi])
+NM_HD void euler_012(const float* T, float* e) {
+  const float r00 = T[0], r01 = T[1], r02 = T[2], r10 = T[4], r11 = T[5], r12 = T[6], r20 = T[8], r21 = T[9], r22 = T[10];
+  float a0 = nm_atan2f(r12, r22);
+  const float c2 = sqrtf(r00 * r00 + r01 * r01);
+  float a1;
+  if (a0 > 0.0f) { a0 -= static_cast<float>(M_PI); a1 = nm_atan2f(-r02, -c2); }
+  else a1 = nm_atan2f(-r02, c2);
+  const float s1 = nm_sinf(a0), c1 = nm_cosf(a0);
+  const float a2 = nm_atan2f(s1 * r20 - c1 * r10, c1 * r11 - s1 * r21);
+  e[0] = -a0; e[1] = -a1; e[2] = -a2;
+}
+
+// ---- 6x6 two-sided Jacobi SVD solve ---------------------------------------------------------------
+struct Rot2 { double c, s; };
+
+NM_HD Rot2 sym_jacobi(double x, double y, double z) {
+  Rot2 j;
+  const double deno = 2.0 * fabs(y);
+  if (deno < DBL_MIN) { j.c = 1.0; j.s = 0.0; return j; }
+  const double tau = (x - z) / deno;
+  const double w = sqrt(tau * tau + 1.0);
+  const double t = (tau > 0.0) ? 1.0 / (tau + w) : 1.0 / (tau - w);
+  const double sign_t = t > 0.0 ? 1.0 : -1.0;
+  const double n = 1.0 / sqrt(t * t + 1.0);
+  j.s = -sign_t * (y / fabs(y)) * fabs(t) * n;
+  j.c = n;
+  return j;
+}
+
+NM_HD void rows_rot(double* m, int p, int q, double c, double s) {  // x' = c x + s y ; y' = -s x + c y
+  for (int i = 0; i < 6; ++i) {
+    const double x = m[6 * p + i], y = m[6 * q + i];
+    m[6 * p + i] = c * x + s * y;
+    m[6 * q + i] = -s * x + c * y;
+  }
+}
+NM_HD void cols_rot(double* m, int p, int q, double c, double s) {  // x' = c x - s y ; y' = s x + c y
+  for (int i = 0; i < 6; ++i) {
+    const double x = m[6 * i + p], y = m[6 * i + q];
+    m[6 * i + p] = c * x - s * y;
+    m[6 * i + q] = s * x + c * y;
+  }
+}
+
+NM_HD void svd6_solve(const double* A, const double* b, double* x) {
+  double W[36], U[36], V[36];
+  double scale = 0.0;
+  for (int i = 0; i < 36; ++i) scale = fmax(scale, fabs(A[i]));
+  if (scale == 0.0) scale = 1.0;
+  for (int i = 0; i < 36; ++i) { W[i] = A[i] / scale; U[i] = 0.0; V[i] = 0.0; }
+  for (int i = 0; i < 6; ++i) { U[7 * i] = 1.0; V[7 * i] = 1.0; }
+  const double precision = 2.0 * DBL_EPSILON;
+  double max_diag = 0.0;
+  for (int i = 0; i < 6; ++i) max_diag = fmax(max_diag, fabs(W[7 * i]));
+  bool finished = false;
+  for (int guard = 0; !finished && guard < 200; ++guard) {
+    finished = true;
+    for (int p = 1; p < 6; ++p)
+      for (int q = 0; q < p; ++q) {
+        const double thr = fmax(DBL_MIN, precision * max_diag);
+        if (fabs(W[6 * p + q]) > thr || fabs(W[6 * q + p]) > thr) {
+          finished = false;
+          const double m00 = W[7 * p], m01 = W[6 * p + q], m10 = W[6 * q + p], m11 = W[7 * q];
+          double rc = 1.0, rs = 0.0;
+          const double t = m00 + m11, d = m10 - m01;
+          if (!(fabs(d) < DBL_MIN)) { const double u = t / d; const double tmp = sqrt(1.0 + u * u); rs = 1.0 / tmp; rc = u / tmp; }
+          const double n00 = rc * m00 + rs * m10, n01 = rc * m01 + rs * m11, n11 = -rs * m01 + rc * m11;
+          const Rot2 jr = sym_jacobi(n00, n01, n11);
+          const double lc = rc * jr.c + rs * jr.s;
+          const double ls = rs * jr.c - rc * jr.s;
+          rows_rot(W, p, q, lc, ls);
+          cols_rot(U, p, q, lc, -ls);
+          cols_rot(W, p, q, jr.c, jr.s);
+          cols_rot(V, p, q, jr.c, jr.s);
+          max_diag = fmax(max_diag, fmax(fabs(W[7 * p]), fabs(W[7 * q])));
+        }
+      }
+  }
+  double S[6];
+  for (int i = 0; i < 6; ++i) {
+    const double a = W[7 * i];
+    S[i] = fabs(a) * scale;
+    if (a < 0.0) for (int r = 0; r < 6; ++r) U[6 * r + i] = -U[6 * r + i];
+  }
+  for (int i = 0; i < 6; ++i) {
+    int pos = i;
+    for (int k = i + 1; k < 6; ++k) if (S[k] > S[pos]) pos = k;
+    if (S[pos] == 0.0) break;
+    if (pos != i) {
+      double t = S[i]; S[i] = S[pos]; S[pos] = t;
+      for (int r = 0; r < 6; ++r) {
+        t = U[6 * r + i]; U[6 * r + i] = U[6 * r + pos]; U[6 * r + pos] = t;
+        t = V[6 * r + i]; V[6 * r + i] = V[6 * r + pos]; V[6 * r + pos] = t;
+      }
+    }
+  }
+  const double thr = fmax(S[0] * (DBL_EPSILON * 6.0), DBL_MIN);
+  int rank = 6;
+  while (rank > 0 && !(S[rank - 1] >= thr)) --rank;
+  if (S[0] != S[0]) rank = 6;
+  double tmp[6];
+  for (int i = 0; i < rank; ++i) {
+    double s = 0.0;
+    for (int r = 0; r < 6; ++r) s = s + U[6 * r + i] * b[r];
+    tmp[i] = (1.0 / S[i]) * s;
+  }
+  for (int r = 0; r < 6; ++r) {
+    double s = 0.0;
+    for (int i = 0; i < rank; ++i) s = s + V[6 * r + i] * tmp[i];
+    x[r] = s;
+  }
+}
+
+}  // namespace ndtb

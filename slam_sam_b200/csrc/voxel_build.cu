@@ -1,0 +1,157 @@
+// Host driver of the target voxel-map build: setInputTarget -> VoxelGridCovariance::filter()
+// (ndt_omp.h:324-330, voxel_grid_covariance_omp_impl.hpp:55-364; svn_ndt_impl.hpp:137-159,
+// voxel_grid_covariance_impl.hpp:77-379).  See voxel_build_kernels.cuh for the kernels.
+#include "voxel_build_kernels.cuh"
+#include "../../include/ndtb.h"
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <algorithm>
+
+namespace ndtb {
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return NDTB_ERR_CUDA; } while (0)
+
+static int ensure_capacity(DeviceGrid& g, size_t n) {
+  if (!g.d_bbox) {
+    CK(cudaMalloc(&g.d_bbox, 6 * sizeof(int)));
+    CK(cudaMalloc(&g.d_counters, 4 * sizeof(unsigned int)));
+    CK(cudaMallocHost(&g.h_pinned, 16 * sizeof(int)));
+  }
+  if (n > g.pts_alloc) {
+    for (int i = 0; i < 2; ++i) { cudaFree(g.keys[i]); cudaFree(g.vals[i]); }
+    cudaFree(g.seg_start); cudaFree(g.block_counts); cudaFree(g.hist);
+    const size_t cap = n + n / 8 + 1024;
+    for (int i = 0; i < 2; ++i) { CK(cudaMalloc(&g.keys[i], cap * 4)); CK(cudaMalloc(&g.vals[i], cap * 4)); }
+    CK(cudaMalloc(&g.seg_start, (cap + 1) * 4));
+    const size_t nb = (cap + RS_TILE - 1) / RS_TILE + 1;
+    CK(cudaMalloc(&g.block_counts, nb * 4));
+    CK(cudaMalloc(&g.hist, nb * 256 * 4));
+    g.pts_alloc = cap;
+    // voxel arrays: V <= n
+    cudaFree(g.recs); cudaFree(g.c_key); cudaFree(g.c_n); cudaFree(g.c_mean); cudaFree(g.c_cov); cudaFree(g.c_icov);
+    cudaFree(g.c_evecs); cudaFree(g.c_evals);
+    CK(cudaMalloc(&g.recs, cap * sizeof(VoxRec)));
+    CK(cudaMalloc(&g.c_key, cap * 4));
+    CK(cudaMalloc(&g.c_n, cap * 4));
+    CK(cudaMalloc(&g.c_mean, cap * 24));
+    CK(cudaMalloc(&g.c_cov, cap * 72));
+    CK(cudaMalloc(&g.c_icov, cap * 72));
+    CK(cudaMalloc(&g.c_evecs, cap * 72));
+    CK(cudaMalloc(&g.c_evals, cap * 24));
+    g.vox_alloc = cap;
+  }
+  return NDTB_OK;
+}
+
+void free_device_grid(DeviceGrid& g) {
+  for (int i = 0; i < 2; ++i) { cudaFree(g.keys[i]); cudaFree(g.vals[i]); }
+  cudaFree(g.seg_start); cudaFree(g.block_counts); cudaFree(g.hist);
+  cudaFree(g.recs); cudaFree(g.table); cudaFree(g.c_key); cudaFree(g.c_n); cudaFree(g.c_mean); cudaFree(g.c_cov);
+  cudaFree(g.c_icov); cudaFree(g.c_evecs); cudaFree(g.c_evals); cudaFree(g.d_bbox); cudaFree(g.d_counters);
+  if (g.h_pinned) cudaFreeHost(g.h_pinned);
+  g = DeviceGrid();
+}
+
+int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resolution, int min_pts, double eig_mult, int flavour,
+                    int is_dense, cudaStream_t stream) {
+  g.built = false; g.V = 0; g.n_valid = 0;
+  if (n == 0) return NDTB_ERR_EMPTY;
+  if (n > 0x7fffffffu) return NDTB_ERR_INVALID;
+  int rc = ensure_capacity(g, n);
+  if (rc != NDTB_OK) return rc;
+  const int ni = static_cast<int>(n);
+
+  // ---- k0: bounding box (pcl::getMinMax3D) ------------------------------------------------
+  {
+    int init[6];
+    const int big = 0x7f7fffff;  // ordered encoding of +FLT_MAX
+    init[0] = init[1] = init[2] = big;
+    init[3] = init[4] = init[5] = -big - 0;  // ordered encoding of -FLT_MAX is big ^ 0x7fffffff with sign: computed below
+    // -FLT_MAX bits = 0xff7fffff (negative int) -> ordered = bits ^ 0x7fffffff
+    const int neg_bits = static_cast<int>(0xff7fffffu);
+    init[3] = init[4] = init[5] = neg_bits ^ 0x7fffffff;
+    std::memcpy(g.h_pinned, init, sizeof(init));
+    CK(cudaMemcpyAsync(g.d_bbox, g.h_pinned, sizeof(init), cudaMemcpyHostToDevice, stream));
+    const int threads = 256;
+    const int blocks = std::min((ni + threads - 1) / threads, 148 * 8);
+    bbox_kernel<<<blocks, threads, 0, stream>>>(d_pts, ni, is_dense, g.d_bbox);
+    CK(cudaMemcpyAsync(g.h_pinned, g.d_bbox, 6 * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+  }
+  float min_p[3], max_p[3];
+  for (int a = 0; a < 3; ++a) { min_p[a] = ordered_to_float_bits(g.h_pinned[a]); max_p[a] = ordered_to_float_bits(g.h_pinned[3 + a]); }
+
+  // ---- grid geometry on the host, float maths as in applyFilter :83-113 ---------------------
+  GridMeta& m = g.meta;
+  m.leaf = resolution;
+  m.inv_leaf = 1.0f / resolution;  // pcl::VoxelGrid::setLeafSize
+  m.min_pts = min_pts; m.flavour = flavour; m.eig_mult = eig_mult;
+  const int64_t dx = static_cast<int64_t>((max_p[0] - min_p[0]) * m.inv_leaf) + 1;
+  const int64_t dy = static_cast<int64_t>((max_p[1] - min_p[1]) * m.inv_leaf) + 1;
+  const int64_t dz = static_cast<int64_t>((max_p[2] - min_p[2]) * m.inv_leaf) + 1;
+  if (flavour == FLAVOUR_SVN && (dx < 0 || dy < 0 || dz < 0)) return NDTB_ERR_OVERFLOW;
+  if ((dx * dy * dz) > static_cast<int64_t>(std::numeric_limits<int32_t>::max())) return NDTB_ERR_OVERFLOW;
+  for (int a = 0; a < 3; ++a) {
+    m.min_b[a] = static_cast<int>(std::floor(min_p[a] * m.inv_leaf));
+    m.max_b[a] = static_cast<int>(std::floor(max_p[a] * m.inv_leaf));
+    m.div_b[a] = m.max_b[a] - m.min_b[a] + 1;
+    m.lo_bound[a] = static_cast<float>(m.min_b[a]) * m.leaf;
+    m.hi_bound[a] = static_cast<float>(m.max_b[a] + 1) * m.leaf;
+  }
+  m.divb_mul[0] = 1; m.divb_mul[1] = m.div_b[0]; m.divb_mul[2] = m.div_b[0] * m.div_b[1];
+  const int64_t cells = static_cast<int64_t>(m.div_b[0]) * m.div_b[1] * m.div_b[2];
+  if (cells > static_cast<int64_t>(std::numeric_limits<int32_t>::max())) return NDTB_ERR_OVERFLOW;
+  m.total_cells = static_cast<uint32_t>(cells);
+
+  // ---- hash capacity: 2^m >= 2 * min(N, cells)  (load factor <= 0.5) -------------------------
+  {
+    const uint64_t need = 2ull * std::min<uint64_t>(n, static_cast<uint64_t>(cells));
+    size_t cap = 16;
+    while (cap < need) cap <<= 1;
+    if (cap > g.table_alloc) {
+      cudaFree(g.table);
+      CK(cudaMalloc(&g.table, cap * sizeof(HashSlot)));
+      g.table_alloc = cap;
+    }
+    g.table_cap = cap;
+    m.hash_mask = static_cast<uint32_t>(cap - 1);
+    CK(cudaMemsetAsync(g.table, 0xFF, cap * sizeof(HashSlot), stream));
+  }
+  CK(cudaMemsetAsync(g.d_counters, 0, 4 * sizeof(unsigned int), stream));
+
+  // ---- k1: keys ------------------------------------------------------------------------------
+  voxel_key_kernel<<<(ni + 255) / 256, 256, 0, stream>>>(d_pts, ni, m, is_dense, g.keys[0], g.vals[0], g.d_counters);
+
+  // ---- k2: stable LSD radix sort over the significant bits of the key -------------------------
+  int bits = 1;
+  while (bits < 32 && (static_cast<uint64_t>(m.total_cells) >> bits) != 0) ++bits;  // key <= total_cells
+  const int passes = (bits + 7) / 8;
+  const int nb = (ni + RS_TILE - 1) / RS_TILE;
+  int cur = 0;
+  for (int p = 0; p < passes; ++p) {
+    radix_hist_kernel<<<nb, RS_THREADS, 0, stream>>>(g.keys[cur], ni, 8 * p, g.hist, nb);
+    scan_u32_kernel<<<1, 1024, 0, stream>>>(g.hist, 256 * nb, nullptr);
+    radix_scatter_kernel<<<nb, RS_THREADS, 0, stream>>>(g.keys[cur], g.vals[cur], g.keys[cur ^ 1], g.vals[cur ^ 1], ni, 8 * p, g.hist, nb);
+    cur ^= 1;
+  }
+
+  // ---- k3: segments -> voxel numbering in ascending linear index ------------------------------
+  const int sb = (ni + SEG_TILE - 1) / SEG_TILE;
+  seg_count_kernel<<<sb, SEG_THREADS, 0, stream>>>(g.keys[cur], ni, m.total_cells, g.block_counts);
+  scan_u32_kernel<<<1, 1024, 0, stream>>>(g.block_counts, sb, g.d_counters + 1);
+  seg_write_kernel<<<sb, SEG_THREADS, 0, stream>>>(g.keys[cur], ni, m.total_cells, g.block_counts, g.seg_start, g.c_key);
+
+  // ---- k4: per-voxel statistics + hash insert --------------------------------------------------
+  launch_voxel_finalize(g, d_pts, g.vals[cur], static_cast<uint32_t>(ni), stream);
+
+  CK(cudaMemcpyAsync(g.h_pinned, g.d_counters, 4 * sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
+  CK(cudaStreamSynchronize(stream));
+  CK(cudaGetLastError());
+  g.V = static_cast<uint32_t>(g.h_pinned[1]);
+  g.n_valid = static_cast<uint32_t>(g.h_pinned[2]);
+  g.built = true;
+  return NDTB_OK;
+}
+
+}  // namespace ndtb

@@ -1,0 +1,283 @@
+"""ctypes binding of libndtb.so -- the C-ABI CUDA library (include/ndtb.h).
+
+There is no CPU fallback: importing works anywhere (so the symbol table can be checked without a
+GPU), but creating a handle without a CUDA device raises NdtbError, and a missing library raises
+ImportError-like RuntimeError loudly.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libndtb.so")
+
+NDTB_OK = 0
+ERR = {-1: "NDTB_ERR_INVALID", -2: "NDTB_ERR_CUDA", -3: "NDTB_ERR_EMPTY", -4: "NDTB_ERR_OVERFLOW", -5: "NDTB_ERR_NOT_READY"}
+KDTREE, DIRECT26, DIRECT7, DIRECT1 = 0, 1, 2, 3
+FLAVOUR_PCLOMP, FLAVOUR_SVN = 0, 1
+
+c_f = C.POINTER(C.c_float)
+c_d = C.POINTER(C.c_double)
+c_i = C.POINTER(C.c_int)
+
+
+class Params(C.Structure):
+    _fields_ = [("resolution", C.c_float), ("step_size", C.c_double), ("trans_epsilon", C.c_double), ("max_iterations", C.c_int),
+                ("search_method", C.c_int), ("outlier_ratio", C.c_double), ("min_points_per_voxel", C.c_int),
+                ("min_covar_eigvalue_mult", C.c_double), ("regularization_scale_factor", C.c_float), ("use_line_search", C.c_int),
+                ("grid_flavour", C.c_int), ("is_dense", C.c_int)]
+
+
+class Result(C.Structure):
+    _fields_ = [("pose", C.c_float * 16), ("hessian", C.c_double * 36), ("transform_probability", C.c_double),
+                ("nearest_voxel_transformation_likelihood", C.c_double), ("iteration_num", C.c_int), ("converged", C.c_int),
+                ("transformation_array_len", C.c_int), ("evaluations", C.c_int)]
+
+
+class SvnParams(C.Structure):
+    _fields_ = [("particle_count", C.c_int), ("max_iterations", C.c_int), ("kernel_bandwidth", C.c_double), ("step_size", C.c_double),
+                ("stop_threshold", C.c_double), ("use_gauss_newton", C.c_int)]
+
+
+class SvnResult(C.Structure):
+    _fields_ = [("final_pose", C.c_double * 16), ("final_covariance", C.c_double * 36), ("converged", C.c_int), ("iterations", C.c_int)]
+
+
+# every symbol include/ndtb.h declares (tests check the library exports all of them)
+SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "ndtb_default_params", "ndtb_set_params", "ndtb_get_params",
+           "ndtb_set_target", "ndtb_set_source", "ndtb_set_target_device", "ndtb_set_source_device", "ndtb_set_regularization_pose",
+           "ndtb_compute_derivatives", "ndtb_align", "ndtb_get_trace", "ndtb_calculate_scores", "ndtb_get_voxel_count", "ndtb_get_voxels",
+           "ndtb_get_last_hits", "ndtb_svn_default_params", "ndtb_svn_set_params", "ndtb_svn_particle_derivatives", "ndtb_svn_stage2",
+           "ndtb_svn_step", "ndtb_svn_align", "ndtb_svn_stage1_local", "ndtb_svn_finish_step", "ndtb_align_batch", "ndtb_get_timings",
+           "ndtb_get_stream"]
+
+_LIB = None
+
+
+class NdtbError(RuntimeError):
+    def __init__(self, code, msg=""):
+        super().__init__(f"{ERR.get(code, code)}: {msg}")
+        self.code = code
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                               "(there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        H = C.c_void_p
+        L.ndtb_create.argtypes = [C.c_int, C.POINTER(H)]
+        L.ndtb_destroy.argtypes = [H]
+        L.ndtb_last_error.restype = C.c_char_p
+        L.ndtb_last_error.argtypes = [H]
+        L.ndtb_version.restype = C.c_char_p
+        L.ndtb_default_params.argtypes = [C.c_int, C.POINTER(Params)]
+        L.ndtb_set_params.argtypes = [H, C.POINTER(Params)]
+        L.ndtb_get_params.argtypes = [H, C.POINTER(Params)]
+        L.ndtb_set_target.argtypes = [H, C.c_void_p, C.c_size_t, C.c_size_t]
+        L.ndtb_set_source.argtypes = [H, C.c_void_p, C.c_size_t, C.c_size_t]
+        L.ndtb_set_target_device.argtypes = [H, C.c_void_p, C.c_size_t]
+        L.ndtb_set_source_device.argtypes = [H, C.c_void_p, C.c_size_t]
+        L.ndtb_set_regularization_pose.argtypes = [H, c_f]
+        L.ndtb_compute_derivatives.argtypes = [H, c_d, c_f, C.c_int, c_d, c_d, c_d, c_d]
+        L.ndtb_align.argtypes = [H, c_f, C.POINTER(Result), c_f, C.c_int, c_f]
+        L.ndtb_get_trace.argtypes = [H, c_d, C.c_int, c_i]
+        L.ndtb_calculate_scores.argtypes = [H, c_f, c_d, c_d]
+        L.ndtb_get_voxel_count.argtypes = [H, C.POINTER(C.c_size_t), c_i, c_i, c_i]
+        L.ndtb_get_voxels.argtypes = [H, C.POINTER(C.c_int64), C.POINTER(C.c_int32), c_d, c_d, c_d, c_d, c_d]
+        L.ndtb_get_last_hits.argtypes = [H, c_d, c_d]
+        L.ndtb_svn_default_params.argtypes = [C.POINTER(SvnParams)]
+        L.ndtb_svn_set_params.argtypes = [H, C.POINTER(SvnParams)]
+        L.ndtb_svn_particle_derivatives.argtypes = [H, C.c_int, c_d, c_d, c_d, c_d]
+        L.ndtb_svn_stage2.argtypes = [H, C.c_int, c_d, c_d, c_d, c_d]
+        L.ndtb_svn_step.argtypes = [H, C.c_int, c_d, c_d, c_d, c_d, c_d]
+        L.ndtb_svn_align.argtypes = [H, c_d, c_d, C.c_uint64, C.POINTER(SvnResult), c_d]
+        L.ndtb_svn_stage1_local.argtypes = [H, C.c_int, c_d, C.c_int, C.c_int, c_d]
+        L.ndtb_svn_finish_step.argtypes = [H, C.c_int, c_d, c_d, c_d]
+        L.ndtb_align_batch.argtypes = [H, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.c_size_t, c_f, C.POINTER(Result)]
+        L.ndtb_get_timings.argtypes = [H, c_f, c_f, c_f, c_i]
+        L.ndtb_get_stream.argtypes = [H, C.POINTER(C.c_void_p)]
+        _LIB = L
+    return _LIB
+
+
+def _ptr(a, t):
+    return a.ctypes.data_as(t) if a is not None else None
+
+
+def host_cloud(cloud):
+    """float32 (N, >=3) C-contiguous view; returns (array, n, stride_bytes)."""
+    a = np.ascontiguousarray(cloud, dtype=np.float32)
+    if a.ndim != 2 or a.shape[1] < 3:
+        raise ValueError("cloud must be (N, >=3) float32")
+    return a, a.shape[0], a.shape[1] * 4
+
+
+class Handle:
+    """Thin RAII wrapper over ndtb_handle."""
+
+    def __init__(self, device=0):
+        self.L = lib()
+        self.h = C.c_void_p()
+        rc = self.L.ndtb_create(device, C.byref(self.h))
+        if rc != NDTB_OK:
+            raise NdtbError(rc, "ndtb_create failed (no CUDA device? there is no CPU fallback)")
+        self._keep = []
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.ndtb_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def check(self, rc):
+        if rc != NDTB_OK:
+            raise NdtbError(rc, self.L.ndtb_last_error(self.h).decode())
+        return rc
+
+    # parameters
+    def get_params(self):
+        p = Params()
+        self.check(self.L.ndtb_get_params(self.h, C.byref(p)))
+        return p
+
+    def set_params(self, **kw):
+        p = self.get_params()
+        for k, v in kw.items():
+            if not hasattr(p, k):
+                raise AttributeError(k)
+            setattr(p, k, v)
+        return self.L.ndtb_set_params(self.h, C.byref(p))
+
+    def set_svn_params(self, **kw):
+        p = SvnParams()
+        self.L.ndtb_svn_default_params(C.byref(p))
+        for k, v in getattr(self, "_svn_kw", {}).items():
+            setattr(p, k, v)
+        for k, v in kw.items():
+            if not hasattr(p, k):
+                raise AttributeError(k)
+            setattr(p, k, v)
+        self._svn_kw = {**getattr(self, "_svn_kw", {}), **kw}
+        self.check(self.L.ndtb_svn_set_params(self.h, C.byref(p)))
+
+    # clouds
+    def set_target(self, cloud):
+        a, n, s = host_cloud(cloud)
+        return self.L.ndtb_set_target(self.h, a.ctypes.data, n, s)
+
+    def set_source(self, cloud):
+        a, n, s = host_cloud(cloud)
+        return self.L.ndtb_set_source(self.h, a.ctypes.data, n, s)
+
+    def set_target_device(self, ptr, n):
+        return self.L.ndtb_set_target_device(self.h, C.c_void_p(ptr), n)
+
+    def set_source_device(self, ptr, n):
+        return self.L.ndtb_set_source_device(self.h, C.c_void_p(ptr), n)
+
+    def set_regularization_pose(self, T):
+        t = None if T is None else np.ascontiguousarray(T, np.float32).reshape(16)
+        self.check(self.L.ndtb_set_regularization_pose(self.h, _ptr(t, c_f)))
+
+    # pclomp
+    def compute_derivatives(self, p, T=None, compute_hessian=True):
+        p = np.ascontiguousarray(p, np.float64)
+        t = None if T is None else np.ascontiguousarray(T, np.float32).reshape(16)
+        s = np.zeros(1); g = np.zeros(6); H = np.zeros((6, 6)); nv = np.zeros(1)
+        self.check(self.L.ndtb_compute_derivatives(self.h, _ptr(p, c_d), _ptr(t, c_f), int(compute_hessian), _ptr(s, c_d), _ptr(g, c_d),
+                                                   _ptr(H, c_d), _ptr(nv, c_d)))
+        return s[0], g, H, nv[0]
+
+    def align(self, guess=None, capacity=64, want_output=False):
+        guess = np.eye(4, dtype=np.float32) if guess is None else np.ascontiguousarray(guess, np.float32)
+        r = Result()
+        arr = np.zeros((capacity, 16), np.float32)
+        rc = self.L.ndtb_align(self.h, _ptr(guess.reshape(16), c_f), C.byref(r), _ptr(arr, c_f), capacity, None)
+        self.check(rc)
+        return dict(T=np.array(r.pose, np.float32).reshape(4, 4), hessian=np.array(r.hessian).reshape(6, 6),
+                    trans_probability=r.transform_probability, nvtl=r.nearest_voxel_transformation_likelihood,
+                    iterations=r.iteration_num, converged=bool(r.converged), evaluations=r.evaluations,
+                    transformation_array=arr[: r.transformation_array_len].reshape(-1, 4, 4).copy())
+
+    def trace(self, capacity=128):
+        t = np.zeros((capacity, 50)); n = np.zeros(1, np.int32)
+        self.check(self.L.ndtb_get_trace(self.h, _ptr(t, c_d), capacity, _ptr(n, c_i)))
+        return t[: min(n[0], capacity)].copy()
+
+    def calculate_scores(self, T):
+        t = np.ascontiguousarray(T, np.float32).reshape(16)
+        tp = np.zeros(1); nv = np.zeros(1)
+        self.check(self.L.ndtb_calculate_scores(self.h, _ptr(t, c_f), _ptr(tp, c_d), _ptr(nv, c_d)))
+        return tp[0], nv[0]
+
+    # voxel map
+    def voxels(self):
+        cnt = C.c_size_t()
+        mn = np.zeros(3, np.int32); mx = np.zeros(3, np.int32); dv = np.zeros(3, np.int32)
+        self.check(self.L.ndtb_get_voxel_count(self.h, C.byref(cnt), _ptr(mn, c_i), _ptr(mx, c_i), _ptr(dv, c_i)))
+        V = cnt.value
+        idx = np.zeros(V, np.int64); n = np.zeros(V, np.int32)
+        mean = np.zeros((V, 3)); cov = np.zeros((V, 9)); icov = np.zeros((V, 9)); evecs = np.zeros((V, 9)); evals = np.zeros((V, 3))
+        if V:
+            self.check(self.L.ndtb_get_voxels(self.h, idx.ctypes.data_as(C.POINTER(C.c_int64)), n.ctypes.data_as(C.POINTER(C.c_int32)),
+                                              _ptr(mean, c_d), _ptr(cov, c_d), _ptr(icov, c_d), _ptr(evecs, c_d), _ptr(evals, c_d)))
+        return dict(idx=idx, n=n, mean=mean, cov=cov, icov=icov, evecs=evecs, evals=evals, min_b=mn, max_b=mx, div_b=dv)
+
+    def last_hits(self):
+        a = np.zeros(1); b = np.zeros(1)
+        self.L.ndtb_get_last_hits(self.h, _ptr(a, c_d), _ptr(b, c_d))
+        return a[0], b[0]
+
+    def timings(self):
+        b = np.zeros(1, np.float32); a = np.zeros(1, np.float32); e = np.zeros(1, np.float32); n = np.zeros(1, np.int32)
+        self.L.ndtb_get_timings(self.h, _ptr(b, c_f), _ptr(a, c_f), _ptr(e, c_f), _ptr(n, c_i))
+        return dict(build_ms=float(b[0]), align_ms=float(a[0]), eval_ms_total=float(e[0]), eval_launches=int(n[0]))
+
+    # svn
+    def svn_particle_derivatives(self, poses):
+        P = np.ascontiguousarray(poses, np.float64); K = P.shape[0]
+        s = np.zeros(K); g = np.zeros((K, 6)); H = np.zeros((K, 6, 6))
+        self.check(self.L.ndtb_svn_particle_derivatives(self.h, K, _ptr(P, c_d), _ptr(s, c_d), _ptr(g, c_d), _ptr(H, c_d)))
+        return s, g, H
+
+    def svn_stage2(self, poses, grads, hess):
+        P = np.ascontiguousarray(poses, np.float64); K = P.shape[0]
+        g = np.ascontiguousarray(grads, np.float64); H = np.ascontiguousarray(hess, np.float64); u = np.zeros((K, 6))
+        self.check(self.L.ndtb_svn_stage2(self.h, K, _ptr(P, c_d), _ptr(g, c_d), _ptr(H, c_d), _ptr(u, c_d)))
+        return u
+
+    def svn_step(self, poses):
+        P = np.ascontiguousarray(poses, np.float64).copy(); K = P.shape[0]
+        s = np.zeros(K); g = np.zeros((K, 6)); H = np.zeros((K, 6, 6)); u = np.zeros((K, 6))
+        self.check(self.L.ndtb_svn_step(self.h, K, _ptr(P, c_d), _ptr(s, c_d), _ptr(g, c_d), _ptr(H, c_d), _ptr(u, c_d)))
+        return P, s, g, H, u
+
+    def svn_stage1_local(self, poses, rank, world):
+        P = np.ascontiguousarray(poses, np.float64); K = P.shape[0]
+        rec = np.zeros((K, 43))
+        self.check(self.L.ndtb_svn_stage1_local(self.h, K, _ptr(P, c_d), rank, world, _ptr(rec, c_d)))
+        return rec
+
+    def svn_finish_step(self, poses, rec):
+        P = np.ascontiguousarray(poses, np.float64).copy(); K = P.shape[0]
+        rec = np.ascontiguousarray(rec, np.float64); u = np.zeros((K, 6))
+        self.check(self.L.ndtb_svn_finish_step(self.h, K, _ptr(P, c_d), _ptr(rec, c_d), _ptr(u, c_d)))
+        return P, u
+
+    def svn_align(self, prior, particles=None, seed=0):
+        prior = np.ascontiguousarray(prior, np.float64).reshape(16)
+        K = self._svn_kw.get("particle_count", 30) if hasattr(self, "_svn_kw") else 30
+        init = None if particles is None else np.ascontiguousarray(particles, np.float64)
+        out = np.zeros((K, 4, 4)); r = SvnResult()
+        self.check(self.L.ndtb_svn_align(self.h, _ptr(prior, c_d), _ptr(init, c_d), seed, C.byref(r), _ptr(out, c_d)))
+        return dict(final_pose=np.array(r.final_pose).reshape(4, 4), final_covariance=np.array(r.final_covariance).reshape(6, 6),
+                    converged=bool(r.converged), iterations=r.iterations, particles=out)
