@@ -201,15 +201,57 @@ __device__ __forceinline__ int lookup_svn(const GridMeta& m, const HashSlot* __r
 
 __device__ __constant__ int c_off[7][3] = {{0, 0, 0}, {1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};
 
+// ------------------------------------------------------------------------------ reductions
+constexpr int RED_PAD = 48;  // RED_N padded so the vector can be halved 4 times (48,24,12,6,3)
+
+// Transpose-reduce across a warp: at each butterfly step a lane keeps one half of its values and
+// sends the other half, so 48 values cost 24+12+6+3+3 = 48 64-bit shuffles instead of 48*5.
+// Afterwards even lanes hold 3 finished sums each; component index = b4*24 + b3*12 + b2*6 + b1*3 + j.
+// The summation tree is fixed by lane ids -> run-to-run bit stable.
+template <int N, int OFF>
+__device__ __forceinline__ void halve_step(double* v, int lane) {
+  const bool up = (lane & OFF) != 0;
+#pragma unroll
+  for (int i = 0; i < N / 2; ++i) {
+    const double keep = up ? v[N / 2 + i] : v[i];
+    const double send = up ? v[i] : v[N / 2 + i];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, OFF);
+  }
+}
+
+// Reduce acc[RED_PAD] over the block and store RED_N sums to `out` (fixed order: warp tree, then
+// warps 0..W-1 in order).
+__device__ __forceinline__ void block_reduce_store(double* acc, double (*s_red)[RED_PAD], double* __restrict__ out) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  halve_step<48, 16>(acc, lane);
+  halve_step<24, 8>(acc, lane);
+  halve_step<12, 4>(acc, lane);
+  halve_step<6, 2>(acc, lane);
+#pragma unroll
+  for (int j = 0; j < 3; ++j) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 1);
+  if ((lane & 1) == 0) {
+    const int base = ((lane >> 4) & 1) * 24 + ((lane >> 3) & 1) * 12 + ((lane >> 2) & 1) * 6 + ((lane >> 1) & 1) * 3;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) s_red[w][base + j] = acc[j];
+  }
+  __syncthreads();
+  if (threadIdx.x < RED_N) {
+    double v = s_red[0][threadIdx.x];
+#pragma unroll
+    for (int k = 1; k < EVAL_THREADS / 32; ++k) v += s_red[k][threadIdx.x];
+    out[threadIdx.x] = v;
+  }
+}
+
 // ------------------------------------------------------------------------------ the kernel
 template <int FLAVOUR, int PROBES, bool HESS, bool GN>
-__global__ void __launch_bounds__(EVAL_THREADS) eval_kernel(const float4* __restrict__ src, int n, GridMeta m, const VoxRec* __restrict__ recs,
+__global__ void __launch_bounds__(EVAL_THREADS, 3) eval_kernel(const float4* __restrict__ src, int n, GridMeta m, const VoxRec* __restrict__ recs,
                                                             const HashSlot* __restrict__ table, const double* __restrict__ c_mean,
                                                             const double* __restrict__ c_icov, const EvalState* __restrict__ states,
                                                             double* __restrict__ partials, double* __restrict__ results,
                                                             unsigned int* __restrict__ tickets, int particle_offset) {
   __shared__ EvalState st;
-  __shared__ double s_red[EVAL_THREADS / 32][RED_N];
+  __shared__ double s_red[EVAL_THREADS / 32][RED_PAD];
   __shared__ bool s_last;
   const int particle = blockIdx.y + particle_offset;
   {
@@ -219,12 +261,12 @@ __global__ void __launch_bounds__(EVAL_THREADS) eval_kernel(const float4* __rest
     for (int i = threadIdx.x; i < words; i += blockDim.x) s[i] = g[i];
   }
   __syncthreads();
-  double acc[RED_N];
+  double acc[RED_PAD];
 #pragma unroll
-  for (int i = 0; i < RED_N; ++i) acc[i] = 0.0;
+  for (int i = 0; i < RED_PAD; ++i) acc[i] = 0.0;
 
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx < n) {
+  // grid-stride over points: a thread's points are visited in a fixed order -> deterministic sums
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
     const float4 p = __ldg(src + idx);
     // pcl::transformPointCloud (SSE2 Transformer association): m0*x + (m1*y + (m2*z + m3))
     float xt[3];
@@ -263,9 +305,13 @@ __global__ void __launch_bounds__(EVAL_THREADS) eval_kernel(const float4* __rest
       }
       const float d2f = static_cast<float>(st.d2);
       double score_pt = 0.0, nearest_pt = 0.0;
-#pragma unroll
+      // ONE copy of the pair maths in the instruction stream (a fully unrolled 7-neighbour body
+      // overflows the instruction cache: ncu showed "no_instruction" as the top stall).
+#pragma unroll 1
       for (int k = 0; k < PROBES; ++k) {
-        const int row = rows[k];
+        int row = rows[0];
+#pragma unroll
+        for (int q = 1; q < PROBES; ++q) row = (k == q) ? rows[q] : row;
         if (row < 0) continue;
         ++nn;
         if (FLAVOUR == FLAVOUR_PCLOMP) {
@@ -295,36 +341,17 @@ __global__ void __launch_bounds__(EVAL_THREADS) eval_kernel(const float4* __rest
           if (s > nearest_pt) nearest_pt = s;
         }
       }
-      acc[RED_SCORE] = score_pt;
-      acc[RED_NEAREST] = nearest_pt;
-      acc[RED_FOUND] = nn > 0 ? 1.0 : 0.0;
-      acc[RED_COUNT] = static_cast<double>(nn);
+      acc[RED_SCORE] += score_pt;
+      acc[RED_NEAREST] += nearest_pt;
+      acc[RED_FOUND] += nn > 0 ? 1.0 : 0.0;
+      acc[RED_COUNT] += static_cast<double>(nn);
     }
   }
 
-  // ---- deterministic block reduction: warp shuffle tree, then warps in order -----------------
-#pragma unroll
-  for (int i = 0; i < RED_N; ++i) {
-    double v = acc[i];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    acc[i] = v;
-  }
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  if (lane == 0) {
-#pragma unroll
-    for (int i = 0; i < RED_N; ++i) s_red[w][i] = acc[i];
-  }
-  __syncthreads();
+  // ---- deterministic block reduction ----------------------------------------------------------
+  block_reduce_store(acc, s_red, partials + (static_cast<size_t>(particle) * gridDim.x + blockIdx.x) * RED_N);
+  // ---- last block done: fixed-order reduction over all block partials --------------------------
   const int nblk = gridDim.x;
-  double* my_partials = partials + (static_cast<size_t>(particle) * nblk + blockIdx.x) * RED_N;
-  if (threadIdx.x < RED_N) {
-    double v = s_red[0][threadIdx.x];
-#pragma unroll
-    for (int k = 1; k < EVAL_THREADS / 32; ++k) v += s_red[k][threadIdx.x];
-    my_partials[threadIdx.x] = v;
-  }
-  // ---- last block done: fixed-order reduction over blocks ------------------------------------
   __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -335,17 +362,20 @@ __global__ void __launch_bounds__(EVAL_THREADS) eval_kernel(const float4* __rest
   if (!s_last) return;
   __threadfence();
   const double* pp = partials + static_cast<size_t>(particle) * nblk * RED_N;
-  for (int c = w; c < RED_N; c += EVAL_THREADS / 32) {
-    double v = 0.0;
-    for (int b = lane; b < nblk; b += 32) v += __ldcg(pp + static_cast<size_t>(b) * RED_N + c);
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0) results[static_cast<size_t>(particle) * RED_N + c] = v;
+  for (int i = 0; i < RED_PAD; ++i) acc[i] = 0.0;
+  for (int b = threadIdx.x; b < nblk; b += EVAL_THREADS) {
+    const double* row = pp + static_cast<size_t>(b) * RED_N;
+#pragma unroll
+    for (int i = 0; i < RED_N; ++i) acc[i] += __ldcg(row + i);
   }
+  __syncthreads();
+  block_reduce_store(acc, s_red, results + static_cast<size_t>(particle) * RED_N);
   if (threadIdx.x == 0) tickets[particle] = 0;  // self-reset for the next launch
 }
 
-int eval_blocks_for(int n) { return (n + EVAL_THREADS - 1) / EVAL_THREADS; }
+// One resident wave: 148 SMs x 3 CTAs (register-limited); larger clouds are covered by the grid-stride loop.
+int eval_blocks_for(int n) { const int b = (n + EVAL_THREADS - 1) / EVAL_THREADS; return b < 148 * 3 ? b : 148 * 3; }
 
 template <int FLAVOUR, int PROBES, bool HESS, bool GN>
 static void launch_t(const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs, const HashSlot* table, const double* c_mean,
