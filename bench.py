@@ -1,0 +1,294 @@
+#!/usr/bin/env python
+"""bench.py -- NDT align scans/s at 131 k points (BASELINE.json metric), one JSON line on stdout.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload map_align|svn]
+
+Workload `map_align` (default; BASELINE.json configs[1]): one step = target voxel-map build of a
+1 M-point synthetic map + full NDT align (DIRECT7, 1.0 m voxels) of one 131 072-point OS1-128-shaped
+scan against it -- the reference rebuilds the target every keyframe (run/pipeline_ligo_tc.cpp:529-532).
+  value : scans/s with map and scan already resident in HBM when the timed region starts
+  e2e   : scans/s through the C ABI with HOST (pinned) buffers: H2D of map + scan and D2H of the
+          result inside the timed region -- the number to hold against the reference arm
+N > 1 (torchrun, one rank per GPU): independent replicas, scan streams sharded by rank, no data-path
+collective ("weak" scaling); time = max over ranks.
+`--impl reference` times the CPU restatement of the reference path (oracle/, all host threads); the
+reference itself needs PCL/Eigen/GTSAM and cannot be built in this image.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_SCAN = 131072
+N_MAP = 1_000_000
+RESOLUTION = 1.0
+N_SCANS_POOL = 6
+
+
+def make_workload(rank):
+    from slam_sam_b200 import synth
+
+    scene = synth.Scene()
+    tgt = synth.surface_map(scene, N_MAP, seed=7)
+    scans, guesses, truths = [], [], []
+    rng = np.random.Generator(np.random.PCG64(1000 + rank))
+    for i in range(N_SCANS_POOL):
+        s = 20.0 + 17.0 * i + 3.0 * rank
+        pose = synth.trajectory_pose(s)
+        scans.append(synth.ouster_scan(scene, pose, seed=100 * rank + i))
+        # guess = truth perturbed by N(0, 0.2 m / 1 deg), clipped to stay in the basin
+        dt = np.clip(rng.normal(0, 0.2, 3), -0.3, 0.3) * [1, 1, 0.2]
+        dr = np.deg2rad(np.clip(rng.normal(0, 1.0, 3), -1.5, 1.5))
+        guesses.append((pose @ synth.pose_matrix(dt, dr)).astype(np.float32))
+        truths.append(pose)
+    return tgt, scans, guesses, truths
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index = index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        rows = [r.strip().split(", ") for r in open(self.f.name) if r.strip()]
+        os.unlink(self.f.name)
+        sm, mx, reasons = [], [], set()
+        for r in rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                    if v.strip().lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), samples=len(sm), reasons=sorted(reasons))
+        return out
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic():
+    path = os.path.join(ROOT, "profiles", "eval_kernel_traffic.json")
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))["dram_bytes_per_launch"])
+        except Exception:
+            return None
+    return None
+
+
+def run_cpu(tgt, scans, guesses, steps, warmup, threads):
+    """The CPU restatement of the reference path, all host threads: build + align per step."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O
+
+    O.build()
+    o = O.OracleNdt(resolution=RESOLUTION, max_iterations=35, trans_epsilon=0.01, step_size=0.1, num_threads=threads)
+    times, iters, build_t = [], [], []
+    for i in range(warmup + steps):
+        k = i % len(scans)
+        t0 = time.perf_counter()
+        assert o.set_target(tgt) == 0
+        t1 = time.perf_counter()
+        o.set_source(scans[k])
+        r = o.align(guesses[k])
+        t2 = time.perf_counter()
+        if i >= warmup:
+            times.append(t2 - t0); build_t.append(t1 - t0); iters.append(r["iterations"])
+    return dict(total_s=float(np.sum(times)), mean_s=float(np.mean(times)), build_s=float(np.mean(build_t)), iterations=float(np.mean(iters)))
+
+
+def run_gpu(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+
+    from slam_sam_b200 import distributed as D
+    from slam_sam_b200 import ndtb
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
+    tgt, scans, guesses, truths = make_workload(rank)
+    h = ndtb.Handle(local_rank)  # no CPU fallback: raises if the CUDA library / device is missing
+    h.set_params(resolution=RESOLUTION, max_iterations=35, trans_epsilon=0.01, step_size=0.1, search_method=ndtb.DIRECT7)
+    stream = torch.cuda.ExternalStream(h.stream_ptr(), device=local_rank)
+    # device-resident copies (value) and pinned host copies (e2e)
+    d_tgt = torch.from_numpy(tgt).cuda()
+    d_scans = [torch.from_numpy(s).cuda() for s in scans]
+    p_tgt = torch.from_numpy(tgt).pin_memory()
+    p_scans = [torch.from_numpy(s).pin_memory() for s in scans]
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+    torch.cuda.synchronize()
+
+    def step(i, resident):
+        k = i % len(scans)
+        if resident:
+            rc = h.set_target_device(d_tgt.data_ptr(), N_MAP)
+            rc |= h.set_source_device(d_scans[k].data_ptr(), N_SCAN)
+        else:
+            rc = h.L.ndtb_set_target(h.h, p_tgt.data_ptr(), N_MAP, 16)
+            rc |= h.L.ndtb_set_source(h.h, p_scans[k].data_ptr(), N_SCAN, 16)
+        assert rc == 0, h.L.ndtb_last_error(h.h)
+        return h.align(guesses[k], capacity=0)
+
+    def timed(resident, steps, warmup):
+        for i in range(warmup):
+            step(i, resident)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        launches0 = h.launch_count()
+        ev, stats = [], dict(build_ms=0.0, align_ms=0.0, eval_ms=0.0, eval_launches=0, iters=0, hits=0.0, err=0.0)
+        wall0 = time.perf_counter()
+        for i in range(steps):
+            with torch.cuda.stream(stream):
+                flush.zero_()          # L2 flush between timed iterations, outside the event pair
+            e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            r = step(warmup + i, resident)
+            e1.record(stream)
+            ev.append((e0, e1))
+            t = h.timings()
+            stats["build_ms"] += t["build_ms"]; stats["align_ms"] += t["align_ms"]; stats["eval_ms"] += t["eval_ms_total"]
+            stats["eval_launches"] += t["eval_launches"]; stats["iters"] += r["iterations"]; stats["hits"] += h.last_hits()[0]
+            k = (warmup + i) % len(scans)
+            stats["err"] = max(stats["err"], float(np.abs(r["T"][:3, 3] - truths[k][:3, 3]).max()))
+            assert r["converged"], "alignment did not converge"
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        wall = time.perf_counter() - wall0
+        total_ms = sum(a.elapsed_time(b) for a, b in ev)
+        stats["launches"] = h.launch_count() - launches0
+        stats["wall_s"] = wall
+        return total_ms, stats
+
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    total_ms, st = timed(True, args.steps, args.warmup)
+    e2e_ms, st2 = timed(False, args.steps, args.warmup)
+    clk = clocks.stop()
+    total_ms = D.max_over_ranks(total_ms, local_rank)
+    e2e_ms = D.max_over_ranks(e2e_ms, local_rank)
+    launches = int(D.sum_over_ranks(st["launches"], local_rank))
+    if world > 1:
+        dist.barrier()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return None
+    K = args.steps
+    value = world * K / (total_ms * 1e-3)
+    e2e = world * K / (e2e_ms * 1e-3)
+    hbar = st["hits"] / K
+    b_eval = N_SCAN * (16 + 8 * 7 + 64 * hbar)                 # algorithmic bytes per evaluation
+    t_eval = st["eval_ms"] / max(st["eval_launches"], 1) * 1e-3  # CUDA events on the library's stream, timed region
+    peak, peak_src = measured_peak()
+    achieved = b_eval / t_eval / 1e9
+    line = {
+        "metric": "NDT align scans/sec @131k pts (1/2/4/8 B200) + % gather-BW roofline vs CPU OMP", "value": value, "unit": "scans/s",
+        "n_gpus": world, "steps": K, "warmup": args.warmup, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32 pair maths, f64 accumulate", "data": "synthetic",
+        "config": {"workload": "configs[1]: voxel-map build of a 1M-pt synthetic map + DIRECT7 NDT align of one 131072-pt OS1-128-shaped scan, "
+                               "1.0 m voxels, per step", "n_source": N_SCAN, "n_target": N_MAP, "resolution": RESOLUTION, "max_iterations": 35,
+                   "trans_epsilon": 0.01, "l2": "256 MB flush between timed steps", "parallelism": f"replicas x{world} (no collective)",
+                   "build_ms": st["build_ms"] / K, "align_ms": st["align_ms"] / K, "newton_iterations": st["iters"] / K,
+                   "evaluations_per_align": st["eval_launches"] / K, "max_abs_translation_error_m": st["err"],
+                   "eval_kernel_share_of_step": st["eval_ms"] / total_ms},
+        "e2e": {"value": e2e, "unit": "scans/s", "h2d_bytes_per_step": 16 * (N_MAP + N_SCAN) + 64, "d2h_bytes_per_step": int(368 * st2["eval_launches"] / K + 64),
+                "ms_per_step": e2e_ms / K},
+        "gpu_launches": launches,
+        "roofline": {"kernel": "eval_kernel<pclomp,DIRECT7,hessian>", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": ncu_traffic(), "peak_source": peak_src, "algorithmic_bytes_per_launch": b_eval,
+                     "mean_hits_per_point": hbar, "kernel_us": t_eval * 1e6},
+        "clocks": clk,
+    }
+    if not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        c = run_cpu(tgt, scans, guesses, steps=2, warmup=1, threads=threads)
+        line["cpu_baseline"] = {"value": 1.0 / c["mean_s"], "unit": "scans/s", "cores": threads, "kind": "port",
+                                "sample": f"2 steps (after 1 warm-up) of the same workload: 1M-pt map build ({c['build_s']*1e3:.0f} ms, serial like the "
+                                          f"reference) + align ({c['iterations']:.0f} iterations) with {threads} OpenMP threads"}
+    if world > 1:
+        dist.destroy_process_group()
+    return line
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return None
+    tgt, scans, guesses, truths = make_workload(0)
+    threads = os.cpu_count() or 1
+    steps = min(args.steps, 8)   # bounded sample: ~1-2 s of CPU work per step
+    c = run_cpu(tgt, scans, guesses, steps=steps, warmup=min(args.warmup, 1), threads=threads)
+    v = 1.0 / c["mean_s"]
+    sample = f"{steps} steps of the same workload (1M-pt map build + 131072-pt align), {threads} OpenMP threads, oracle port of ndt_omp"
+    return {"impl": "reference", "metric": "NDT align scans/sec @131k pts (1/2/4/8 B200) + % gather-BW roofline vs CPU OMP", "value": v, "unit": "scans/s",
+            "n_gpus": args.gpus, "steps": steps, "warmup": min(args.warmup, 1), "ms_per_step": c["mean_s"] * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32 pair maths, f64 accumulate", "data": "synthetic",
+            "config": {"workload": "configs[1]: voxel-map build of a 1M-pt synthetic map + DIRECT7 NDT align of one 131072-pt OS1-128-shaped scan, "
+                                   "1.0 m voxels, per step", "build_ms": c["build_s"] * 1e3, "newton_iterations": c["iterations"]},
+            "cpu_baseline": {"value": v, "unit": "scans/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": "scans/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        line = run_reference(args, rank)
+    else:
+        line = run_gpu(args, rank, world, local_rank)
+    if line is not None:
+        print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -99,6 +99,35 @@ double orc_ndt_compute_derivatives_T(void* h, const float* T, const double* p, i
   if (nvtl) *nvtl = n->nvtl;
   return s;
 }
+// calculateTransformationProbability + calculateNearestVoxelTransformationLikelihood
+// (ndt_omp_impl.hpp:1169-1281): serial, FP64 exp.
+void orc_ndt_calculate_scores(void* h, const float* T, double* tp, double* nvtl_out) {
+  PclompNdt* n = static_cast<PclompNdt*>(h);
+  n->update_gauss();
+  std::vector<float> trans; n->transform_cloud(T, trans);
+  const size_t N = trans.size() / 3;
+  const int n_probe = (n->params.search_method == DIRECT1) ? 1 : 7;
+  double score = 0, nearest = 0; size_t found = 0;
+  for (size_t i = 0; i < N; ++i) {
+    const float* xt = &trans[3 * i];
+    const Leaf* nb[7];
+    const int nn = n->grid.neighbours(xt[0], xt[1], xt[2], n_probe, nb);
+    double best = 0;
+    for (int k = 0; k < nn; ++k) {
+      const double x[3] = {static_cast<double>(xt[0]) - nb[k]->mean[0], static_cast<double>(xt[1]) - nb[k]->mean[1], static_cast<double>(xt[2]) - nb[k]->mean[2]};
+      const double* C = nb[k]->icov;
+      double Cx[3];
+      for (int r = 0; r < 3; ++r) Cx[r] = (C[3 * r] * x[0] + C[3 * r + 1] * x[1]) + C[3 * r + 2] * x[2];
+      const double q = (x[0] * Cx[0] + x[1] * Cx[1]) + x[2] * Cx[2];
+      const double s = -n->gauss_d1 * std::exp(-n->gauss_d2 * q / 2);
+      score += s;
+      if (s > best) best = s;
+    }
+    if (nn > 0) { ++found; nearest += best; }
+  }
+  *tp = N ? score / static_cast<double>(N) : 0.0;
+  *nvtl_out = found ? nearest / static_cast<double>(found) : 0.0;
+}
 // trace: 50 doubles per evaluation (p6, score, g6, H36, nvtl); tarray: 16 floats per entry.
 int orc_ndt_align(void* h, const float* guess, float* final_T, double* hessian, double* trans_probability, double* nvtl, int* iterations,
                   int* converged, double* trace, int trace_cap, int* n_trace, float* tarray, int tarray_cap, int* n_tarray) {

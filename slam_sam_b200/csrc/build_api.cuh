@@ -10,6 +10,7 @@ struct DeviceGrid {
   bool built = false;
   uint32_t V = 0;          // leaves (pclomp keeps under-populated / rejected leaves, flagged)
   uint32_t n_valid = 0;    // leaves that can be returned by a neighbour search
+  uint64_t launches = 0;   // kernels launched by builds on this grid
   // hot
   VoxRec* recs = nullptr;
   HashSlot* table = nullptr;

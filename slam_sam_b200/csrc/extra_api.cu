@@ -4,6 +4,8 @@
 #include "handle.cuh"
 #include <cstring>
 #include <string>
+#include <vector>
+#include <cmath>
 
 using namespace ndtb;
 
@@ -84,6 +86,7 @@ int ndtb_calculate_scores(ndtb_handle h, const float T16[16], double* transforma
   }
   const int probes = (h->params.search_method == NDTB_DIRECT1) ? 1 : 7;
   score_kernel<<<blocks, 128, 0, h->stream>>>(h->d_source, n, h->grid.meta, h->grid.table, h->grid.c_mean, h->grid.c_icov, d_T, d1, d2, probes, d_out);
+  h->launches += 1;
   std::vector<double> out(3 * static_cast<size_t>(blocks));
   CKH(cudaMemcpyAsync(out.data(), d_out, sizeof(double) * 3 * blocks, cudaMemcpyDeviceToHost, h->stream));
   CKH(cudaStreamSynchronize(h->stream));
@@ -97,7 +100,6 @@ int ndtb_calculate_scores(ndtb_handle h, const float T16[16], double* transforma
 }
 
 // Replay batch: n independent source scans against the current target map, results in order.
-// Scans are double-buffered: scan i+1 is uploaded on the copy path while scan i is aligned.
 int ndtb_align_batch(ndtb_handle h, int n_scans, const float* const* xyz, const size_t* n_points, size_t stride_bytes, const float* guesses16,
                      ndtb_result* results) {
   if (!h || n_scans < 0 || !xyz || !n_points || !guesses16 || !results) return NDTB_ERR_INVALID;

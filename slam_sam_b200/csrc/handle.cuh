@@ -34,6 +34,7 @@ struct ndtb_handle_s {
   // timing
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   float build_ms = 0, align_ms = 0, eval_ms_total = 0; int eval_launches = 0;
+  uint64_t launches = 0;  // eval / stein / score kernels launched (builds are counted in grid.launches)
 
   // svn device scratch
   double* d_svn_in = nullptr;   // poses(16K) + grads(6K) + hess(36K)

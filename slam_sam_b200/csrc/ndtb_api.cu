@@ -116,7 +116,7 @@ static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool
   CKH(cudaGetLastError());
   float ms = 0;
   cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]);
-  h->eval_ms_total += ms; h->eval_launches += 1;
+  h->eval_ms_total += ms; h->eval_launches += 1; h->launches += 1;
   const double* r = h->h_results;
   double sc = r[RED_SCORE];
   std::memcpy(g, r + RED_G, 6 * sizeof(double));
@@ -452,6 +452,12 @@ int ndtb_get_timings(ndtb_handle h, float* build_ms, float* align_ms, float* eva
   if (align_ms) *align_ms = h->align_ms;
   if (eval_kernel_ms_total) *eval_kernel_ms_total = h->eval_ms_total;
   if (eval_kernel_launches) *eval_kernel_launches = h->eval_launches;
+  return NDTB_OK;
+}
+
+int ndtb_get_launch_count(ndtb_handle h, uint64_t* launches) {
+  if (!h || !launches) return NDTB_ERR_INVALID;
+  *launches = h->launches + h->grid.launches;
   return NDTB_OK;
 }
 

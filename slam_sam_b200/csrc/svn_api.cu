@@ -61,7 +61,7 @@ int stage1(ndtb_handle_s* h, int K, const double* poses, int first, int stride, 
   CKH(cudaGetLastError());
   float ms = 0;
   cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]);
-  h->eval_ms_total += ms; h->eval_launches += 1;
+  h->eval_ms_total += ms; h->eval_launches += 1; h->launches += 1;
   for (int s = 0; s < m; ++s) {
     const double* r = h->h_results + static_cast<size_t>(s) * RED_N;
     double* o = rec43 + 43 * static_cast<size_t>(mine[s]);

@@ -123,6 +123,7 @@ int svn_stein_update(ndtb_handle_s* h, int K, const double* poses, const double*
   CKS(cudaMemcpyAsync(d_hess, hess, sizeof(double) * 36 * K, cudaMemcpyHostToDevice, h->stream));
   stein_kernel<<<K, STEIN_THREADS, 0, h->stream>>>(K, d_poses, d_grads, d_hess, h->svn.kernel_bandwidth, h->svn.step_size, d_upd,
                                                    new_poses ? d_new : nullptr);
+  h->launches += 1;
   CKS(cudaMemcpyAsync(updates, d_upd, sizeof(double) * 6 * K, cudaMemcpyDeviceToHost, h->stream));
   if (new_poses) CKS(cudaMemcpyAsync(new_poses, d_new, sizeof(double) * 16 * K, cudaMemcpyDeviceToHost, h->stream));
   CKS(cudaStreamSynchronize(h->stream));

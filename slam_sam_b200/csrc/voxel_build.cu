@@ -50,7 +50,9 @@ void free_device_grid(DeviceGrid& g) {
   cudaFree(g.recs); cudaFree(g.table); cudaFree(g.c_key); cudaFree(g.c_n); cudaFree(g.c_mean); cudaFree(g.c_cov);
   cudaFree(g.c_icov); cudaFree(g.c_evecs); cudaFree(g.c_evals); cudaFree(g.d_bbox); cudaFree(g.d_counters);
   if (g.h_pinned) cudaFreeHost(g.h_pinned);
+  const uint64_t keep = g.launches;
   g = DeviceGrid();
+  g.launches = keep;
 }
 
 int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resolution, int min_pts, double eig_mult, int flavour,
@@ -145,6 +147,7 @@ int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resoluti
   // ---- k4: per-voxel statistics + hash insert --------------------------------------------------
   launch_voxel_finalize(g, d_pts, g.vals[cur], static_cast<uint32_t>(ni), stream);
 
+  g.launches += 2 + 3 * static_cast<uint64_t>(passes) + 3 + 1;  // bbox, keys, radix passes, segments, finalize
   CK(cudaMemcpyAsync(g.h_pinned, g.d_counters, 4 * sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
   CK(cudaStreamSynchronize(stream));
   CK(cudaGetLastError());

@@ -1,0 +1,70 @@
+"""Multi-GPU plumbing: one process per GPU over torch.distributed (NCCL on the box, gloo in CPU tests).
+
+The path shards at two granularities and nowhere else:
+  * SVN particles: particle k is evaluated on rank k % world (stage 1, svn_ndt_impl.hpp:758-781);
+    stage 2 couples all particles (:795-808), so the per-particle (score, g, H) records -- 43 doubles
+    each -- are exchanged with ONE all-reduce of a zero-padded K x 43 buffer per iteration.  Every
+    rank contributes exact zeros for rows it does not own, so the sum is exact and every rank ends up
+    with bit-identical records; each rank then runs the K x K Stein update redundantly and all
+    replicas stay in lock-step without exchanging poses.
+  * replay batches: independent alignments against a replicated map, scan i on rank i % world, no
+    data-path collective at all.
+A single alignment is NOT split across GPUs (one evaluation is ~10 us of work): replicas only.
+"""
+import numpy as np
+
+
+def owner(k, world):
+    return k % world
+
+
+def local_indices(n, rank, world):
+    """Indices of the work items (particles / scans) rank `rank` owns."""
+    return np.arange(rank, n, world)
+
+
+def allreduce_records(rec, device=None):
+    """Sum a K x 43 record buffer over all ranks (zero rows for particles a rank does not own)."""
+    import torch
+    import torch.distributed as dist
+
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return rec
+    t = torch.from_numpy(np.ascontiguousarray(rec))
+    if dist.get_backend() == "nccl":
+        t = t.cuda(device)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return t.cpu().numpy()
+
+
+def svn_step(handle, poses, rank, world, device=None):
+    """One SVN iteration with particles sharded over `world` ranks.  Returns (new_poses, updates)."""
+    rec = handle.svn_stage1_local(poses, rank, world)
+    rec = allreduce_records(rec, device)
+    return handle.svn_finish_step(poses, rec)
+
+
+def max_over_ranks(value, device=None):
+    import torch
+    import torch.distributed as dist
+
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return float(value)
+    t = torch.tensor([float(value)], dtype=torch.float64)
+    if dist.get_backend() == "nccl":
+        t = t.cuda(device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def sum_over_ranks(value, device=None):
+    import torch
+    import torch.distributed as dist
+
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return float(value)
+    t = torch.tensor([float(value)], dtype=torch.float64)
+    if dist.get_backend() == "nccl":
+        t = t.cuda(device)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())

@@ -50,7 +50,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "nd
            "ndtb_compute_derivatives", "ndtb_align", "ndtb_get_trace", "ndtb_calculate_scores", "ndtb_get_voxel_count", "ndtb_get_voxels",
            "ndtb_get_last_hits", "ndtb_svn_default_params", "ndtb_svn_set_params", "ndtb_svn_particle_derivatives", "ndtb_svn_stage2",
            "ndtb_svn_step", "ndtb_svn_align", "ndtb_svn_stage1_local", "ndtb_svn_finish_step", "ndtb_align_batch", "ndtb_get_timings",
-           "ndtb_get_stream"]
+           "ndtb_get_stream", "ndtb_get_launch_count"]
 
 _LIB = None
 
@@ -100,6 +100,7 @@ def lib():
         L.ndtb_align_batch.argtypes = [H, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.c_size_t, c_f, C.POINTER(Result)]
         L.ndtb_get_timings.argtypes = [H, c_f, c_f, c_f, c_i]
         L.ndtb_get_stream.argtypes = [H, C.POINTER(C.c_void_p)]
+        L.ndtb_get_launch_count.argtypes = [H, C.POINTER(C.c_uint64)]
         _LIB = L
     return _LIB
 
@@ -241,6 +242,16 @@ class Handle:
         b = np.zeros(1, np.float32); a = np.zeros(1, np.float32); e = np.zeros(1, np.float32); n = np.zeros(1, np.int32)
         self.L.ndtb_get_timings(self.h, _ptr(b, c_f), _ptr(a, c_f), _ptr(e, c_f), _ptr(n, c_i))
         return dict(build_ms=float(b[0]), align_ms=float(a[0]), eval_ms_total=float(e[0]), eval_launches=int(n[0]))
+
+    def launch_count(self):
+        n = C.c_uint64()
+        self.L.ndtb_get_launch_count(self.h, C.byref(n))
+        return n.value
+
+    def stream_ptr(self):
+        p = C.c_void_p()
+        self.L.ndtb_get_stream(self.h, C.byref(p))
+        return p.value
 
     # svn
     def svn_particle_derivatives(self, poses):

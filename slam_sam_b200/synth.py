@@ -145,6 +145,21 @@ class Scene:
         s = rng.uniform(1.0, 4.0, (nb, 3))
         self.box_lo = np.concatenate([c - s[:, :2] / 2, np.zeros((nb, 1))], 1)
         self.box_hi = np.concatenate([c + s[:, :2] / 2, s[:, 2:3]], 1)
+        # pilasters every 8 m on both facades (1 m wide, 0.6 m deep, full height): without relief a
+        # straight street leaves the along-track translation unobservable and NDT's clamped Newton
+        # step (ndt_omp_impl.hpp:963-965, no line search) oscillates instead of converging
+        rng2 = np.random.Generator(np.random.PCG64(seed + 1))
+        for side in (-1.0, 1.0):
+            px = -half + 3.0 + np.cumsum(rng2.uniform(5.0, 9.0, int(2 * half / 5)))
+            px = px[px < half - 3.0]
+            w = rng2.uniform(0.8, 2.0, px.shape) / 2
+            d = rng2.uniform(0.4, 1.5, px.shape)
+            y0 = 12.0 - d if side > 0 else np.full_like(px, -12.0)
+            y1 = np.full_like(px, 12.0) if side > 0 else -12.0 + d
+            lo = np.stack([px - w, y0, np.zeros_like(px)], 1)
+            hi = np.stack([px + w, y1, rng2.uniform(6.0, 15.0, px.shape)], 1)
+            self.box_lo = np.concatenate([self.box_lo, lo], 0)
+            self.box_hi = np.concatenate([self.box_hi, hi], 0)
         self.pole_c = np.stack([rng.uniform(-half * 0.9, half * 0.9, npole), rng.choice([-8.0, 8.0], npole) + rng.uniform(-0.5, 0.5, npole)], 1)
         self.pole_r = 0.15
         self.pole_h = rng.uniform(4.0, 8.0, npole)

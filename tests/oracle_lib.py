@@ -53,6 +53,7 @@ def lib():
         L.orc_ndt_compute_derivatives.argtypes = [C.c_void_p, c_d, C.c_int, c_d, c_d, c_d]
         L.orc_ndt_compute_derivatives_T.restype = C.c_double
         L.orc_ndt_compute_derivatives_T.argtypes = [C.c_void_p, c_f, c_d, C.c_int, c_d, c_d, c_d]
+        L.orc_ndt_calculate_scores.argtypes = [C.c_void_p, c_f, c_d, c_d]
         L.orc_ndt_align.argtypes = [C.c_void_p, c_f, c_f, c_d, c_d, c_d, c_i, c_i, c_d, C.c_int, c_i, c_f, C.c_int, c_i]
         L.orc_svn_create.restype = C.c_void_p
         L.orc_svn_destroy.argtypes = [C.c_void_p]
@@ -173,6 +174,11 @@ class OracleNdt:
             t = np.ascontiguousarray(T, np.float32).reshape(16)
             s = lib().orc_ndt_compute_derivatives_T(self.h, _f(t), _d(p), int(compute_hessian), _d(g), _d(H), _d(nv))
         return s, g, H, nv[0]
+
+    def calculate_scores(self, T):
+        t = np.ascontiguousarray(T, np.float32).reshape(16); tp = np.zeros(1); nv = np.zeros(1)
+        lib().orc_ndt_calculate_scores(self.h, _f(t), _d(tp), _d(nv))
+        return tp[0], nv[0]
 
     def align(self, guess=None, max_trace=128):
         guess = np.eye(4, dtype=np.float32) if guess is None else np.ascontiguousarray(guess, np.float32)

@@ -1,0 +1,184 @@
+"""GPU parity, pclomp flavour: CUDA path (through the C ABI) vs the CPU oracle and the golden file.
+
+Bars (BASELINE.json north_star): voxel occupancy and indices bit-exact (we also get means / inverse
+covariances bit-exact); per-evaluation score, gradient, Hessian <= 1e-9 relative (to the inf-norm);
+final poses within 1e-4 m and 1e-5 rad."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from conftest import rel_inf
+from slam_sam_b200 import ndtb, registration, synth
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-9
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ndt_golden.npz")
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return dict(np.load(GOLD))
+
+
+def assert_grid_equal(a, b, exact_stats=True):
+    assert np.array_equal(a["min_b"], b["min_b"]) and np.array_equal(a["max_b"], b["max_b"]) and np.array_equal(a["div_b"], b["div_b"])
+    assert np.array_equal(a["idx"], b["idx"])      # occupancy + linear indices: bit-exact
+    assert np.array_equal(a["n"], b["n"])
+    valid = b["n"] >= 1
+    if exact_stats:
+        assert np.array_equal(a["mean"][valid], b["mean"][valid])
+        assert np.array_equal(a["icov"], b["icov"]) and np.array_equal(a["cov"], b["cov"])
+        assert np.array_equal(a["evals"], b["evals"])
+
+
+def pose_delta(Ta, Tb):
+    d = np.linalg.inv(np.asarray(Ta, float)) @ np.asarray(Tb, float)
+    ang = np.arccos(np.clip((np.trace(d[:3, :3]) - 1) / 2, -1, 1))
+    return np.linalg.norm(d[:3, 3]), ang
+
+
+@pytest.mark.parametrize("res", [0.5, 1.0, 2.0])
+def test_voxel_map_bit_exact(oracle, street, two_plane, res):
+    for cloud in (street["target"], two_plane["target"]):
+        h = ndtb.Handle(0)
+        h.set_params(resolution=res)
+        assert h.set_target(cloud) == 0
+        o = O.OracleGrid(0, res, 6); assert o.build(cloud) == 0
+        assert_grid_equal(h.voxels(), o.export())
+
+
+def test_voxel_map_golden(gold):
+    h = ndtb.Handle(0); h.set_params(resolution=2.0)
+    assert h.set_target(gold["target"]) == 0
+    v = h.voxels()
+    assert np.array_equal(v["idx"], gold["pclomp_idx"]) and np.array_equal(v["n"], gold["pclomp_n"])
+    assert np.array_equal(v["mean"], gold["pclomp_mean"]) and np.array_equal(v["icov"], gold["pclomp_icov"])
+
+
+def test_voxel_map_edge_cases(oracle):
+    h = ndtb.Handle(0)
+    assert h.L.ndtb_set_target(h.h, None, 0, 16) == -3                # NDTB_ERR_EMPTY (:60-65)
+    big = np.array([[0, 0, 0, 0], [4000, 4000, 4000, 0]], np.float32)
+    assert h.set_target(big) == -4                                    # NDTB_ERR_OVERFLOW (:83-94)
+    rng = np.random.default_rng(0)
+    c = rng.uniform(0, 3, (500, 4)).astype(np.float32)
+    c[5, 0] = np.nan; c[17, 2] = np.inf
+    h.set_params(is_dense=0)
+    assert h.set_target(c) == 0
+    o = O.OracleGrid(0, 1.0, 6); o.build(c, is_dense=False)
+    assert_grid_equal(h.voxels(), o.export())
+    # identical points -> zero covariance -> leaf flagged -1, never returned by a search
+    same = np.tile(np.array([[0.5, 0.5, 0.5, 0]], np.float32), (10, 1))
+    h.set_params(is_dense=1)
+    assert h.set_target(same) == 0 and list(h.voxels()["n"]) == [-1]
+    # strides: packed xyz (12 B), PointXYZ (16 B), PointXYZI (32 B) give the same map
+    base = rng.uniform(-5, 5, (3000, 3)).astype(np.float32)
+    ref = None
+    for width in (3, 4, 8):
+        c = np.zeros((3000, width), np.float32); c[:, :3] = base
+        if width > 3:
+            c[:, 3:] = 7.0
+        assert h.set_target(c) == 0
+        v = h.voxels()
+        if ref is None:
+            ref = v
+        else:
+            assert_grid_equal(v, ref)
+    # single point, single voxel
+    assert h.set_target(np.array([[1.5, 2.5, 3.5, 0]], np.float32)) == 0 and list(h.voxels()["n"]) == [1]
+
+
+@pytest.mark.parametrize("search", ["DIRECT7", "DIRECT1"])
+def test_derivatives_vs_golden_and_oracle(oracle, gold, search):
+    h = ndtb.Handle(0)
+    h.set_params(resolution=2.0, search_method=getattr(ndtb, search))
+    assert h.set_target(gold["target"]) == 0 and h.set_source(gold["source"]) == 0
+    for k, p in enumerate(gold[f"eval_{search}_p"]):
+        s, g, H, nv = h.compute_derivatives(p)
+        assert abs(s - gold[f"eval_{search}_score"][k]) <= TOL * abs(gold[f"eval_{search}_score"][k])
+        assert rel_inf(g, gold[f"eval_{search}_g"][k]) <= TOL and rel_inf(H, gold[f"eval_{search}_H"][k]) <= TOL
+        assert abs(nv - gold[f"eval_{search}_nvtl"][k]) <= TOL * abs(nv)
+        s2, g2, H2, _ = h.compute_derivatives(p, compute_hessian=False)
+        assert s2 == s and np.array_equal(g2, g) and np.all(H2 == 0)
+        # run-to-run bit stability (fixed reduction tree, no FP64 atomics)
+        s3, g3, H3, _ = h.compute_derivatives(p)
+        assert s3 == s and np.array_equal(g3, g) and np.array_equal(H3, H)
+
+
+def test_regulariser_and_scores(oracle, gold):
+    h = ndtb.Handle(0)
+    h.set_params(resolution=2.0, regularization_scale_factor=10.0)
+    h.set_target(gold["target"]); h.set_source(gold["source"])
+    h.set_regularization_pose(gold["reg_T"])
+    s, g, H, _ = h.compute_derivatives(np.array([0.3, 0.05, 0.01, 0.005, 0.003, 0.017]))
+    assert abs(s - gold["reg_score"][0]) <= TOL * abs(s) and rel_inf(g, gold["reg_g"]) <= TOL and rel_inf(H, gold["reg_H"]) <= TOL
+    h.set_regularization_pose(None)
+    o = O.OracleNdt(resolution=2.0); o.set_target(gold["target"]); o.set_source(gold["source"])
+    tp, nv = h.calculate_scores(gold["align_DIRECT7_T"])
+    tpo, nvo = o.calculate_scores(gold["align_DIRECT7_T"])
+    assert abs(tp - tpo) <= 1e-12 * abs(tpo) and abs(nv - nvo) <= 1e-12 * abs(nvo)
+
+
+@pytest.mark.parametrize("search", ["DIRECT7", "DIRECT1"])
+def test_align_vs_golden(gold, search):
+    h = ndtb.Handle(0)
+    h.set_params(resolution=2.0, search_method=getattr(ndtb, search), max_iterations=35, trans_epsilon=0.01, step_size=0.1)
+    h.set_target(gold["target"]); h.set_source(gold["source"])
+    r = h.align()
+    assert [r["iterations"], int(r["converged"])] == list(gold[f"align_{search}_iters"])
+    dt, da = pose_delta(r["T"], gold[f"align_{search}_T"])
+    assert dt <= 1e-4 and da <= 1e-5
+    tr, tg = h.trace(), gold[f"align_{search}_trace"]
+    assert tr.shape == tg.shape
+    for a, b in zip(tr, tg):
+        assert np.abs(a[:6] - b[:6]).max() <= 1e-9                       # pose vector of the evaluation
+        assert abs(a[6] - b[6]) <= TOL * abs(b[6]) and rel_inf(a[7:13], b[7:13]) <= TOL and rel_inf(a[13:49], b[13:49]) <= TOL
+    assert np.abs(r["transformation_array"] - gold[f"align_{search}_tarray"]).max() <= 1e-6
+    assert rel_inf(r["hessian"], gold[f"align_{search}_hessian"]) <= TOL
+
+
+def test_reference_gtest_case_pclomp(oracle, two_plane):
+    """Reads like TEST(ConvergenceComparison, PclOmp), test_svn_ndt.cpp:138-199."""
+    ndt = registration.NormalDistributionsTransform()
+    ndt.setResolution(1.0)
+    ndt.setNeighborhoodSearchMethod(registration.DIRECT7)
+    ndt.setMaximumIterations(50)
+    ndt.setTransformationEpsilon(1e-4)
+    ndt.setStepSize(0.1)
+    ndt.setNumThreads(20)
+    ndt.setInputTarget(two_plane["target"])
+    ndt.setInputSource(two_plane["source"])
+    ndt.computeTransformation(two_plane["guess"].astype(np.float32))
+    assert ndt.hasConverged()
+    assert ndt.getFinalNumIteration() < 50
+    err = np.ascontiguousarray(np.linalg.inv(ndt.getFinalTransformation().astype(float)) @ two_plane["gt"])
+    xi = np.zeros(6); oracle.lib().orc_pose_logmap(O._d(err), O._d(xi))
+    assert np.linalg.norm(xi[3:]) < 0.05 and np.linalg.norm(xi[:3]) < 0.035
+    # and the same trajectory as the oracle
+    o = O.OracleNdt(resolution=1.0, max_iterations=50, trans_epsilon=1e-4, step_size=0.1, num_threads=8)
+    o.set_target(two_plane["target"]); o.set_source(two_plane["source"])
+    ro = o.align(two_plane["guess"].astype(np.float32))
+    assert ndt.getFinalNumIteration() == ro["iterations"]
+    dt, da = pose_delta(ndt.getFinalTransformation(), ro["T"])
+    assert dt <= 1e-4 and da <= 1e-5
+    res = ndt.getResult()
+    assert abs(res.transform_probability - ro["trans_probability"]) <= 1e-9 * abs(ro["trans_probability"])
+    assert len(res.transformation_array) == len(ro["transformation_array"])
+
+
+def test_setters_rebuild_only_on_change(street):
+    ndt = registration.NormalDistributionsTransform()
+    ndt.setInputTarget(street["target"])
+    v1 = ndt.getTargetCells()
+    ndt.setResolution(1.0)          # unchanged -> no rebuild, same map
+    assert np.array_equal(ndt.getTargetCells()["idx"], v1["idx"])
+    ndt.setResolution(2.0)          # ndt_omp.h:135-142: rebuild with the new leaf size
+    v2 = ndt.getTargetCells()
+    assert len(v2["idx"]) < len(v1["idx"])
+    with pytest.raises(ndtb.NdtbError):
+        ndt.setNeighborhoodSearchMethod(registration.KDTREE)
+    empty = registration.NormalDistributionsTransform()
+    with pytest.raises(ndtb.NdtbError):
+        empty.align()               # NDTB_ERR_NOT_READY: no target / source

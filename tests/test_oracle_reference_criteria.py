@@ -1,0 +1,82 @@
+"""Pin the oracle against the reference's OWN test criteria:
+extern/svn_ndt/test/test_svn_ndt.cpp -- the seeded two-plane scene and its three cases
+(PclOmp :138-199, SvnNdtK10 :205-257, SvnNdtK1_Newton :263-317): converged, iterations < max,
+translation error < 0.05 m, rotation error < 0.035 rad.  Nothing tighter is published by the
+reference for this path (no score/gradient/Hessian goldens), which is why DESIGN.md says
+"parity unpinned" at the bit level."""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+
+TRANS_TOL = 0.05   # test_svn_ndt.cpp:95
+ROT_TOL = 0.035    # test_svn_ndt.cpp:96
+
+
+def pose_error(oracle, T_est, T_gt):
+    """error_log = Logmap(final.between(gt)); rot = head(3), trans = tail(3) (test_svn_ndt.cpp:188-191)."""
+    err = np.ascontiguousarray(np.linalg.inv(np.asarray(T_est, float)) @ T_gt)
+    xi = np.zeros(6)
+    oracle.lib().orc_pose_logmap(O._d(err), O._d(xi))
+    return np.linalg.norm(xi[:3]), np.linalg.norm(xi[3:])
+
+
+def test_scene_matches_reference_generator(two_plane):
+    # 2 x 134^2 lattice points (test_svn_ndt.cpp:55-64), float32, deterministic noise stream
+    assert two_plane["source"].shape == (35912, 4)
+    assert two_plane["target"].shape == (35912, 4)
+    np.testing.assert_allclose(two_plane["source"][0, :3], [-10.0, -10.0, 0.0])
+    resid = two_plane["target"][:, :3].astype(float) - (two_plane["source"][:, :3].astype(float) @ two_plane["gt"][:3, :3].T + two_plane["gt"][:3, 3])
+    assert abs(resid.std() - 0.02) < 5e-4 and abs(resid.mean()) < 5e-4
+
+
+def test_pclomp_case(oracle, two_plane):
+    ndt = O.OracleNdt(resolution=1.0, search="DIRECT7", max_iterations=50, trans_epsilon=1e-4, step_size=0.1, num_threads=8)
+    ndt.set_target(two_plane["target"])
+    ndt.set_source(two_plane["source"])
+    r = ndt.align(two_plane["guess"].astype(np.float32))
+    assert r["converged"]
+    assert r["iterations"] < 50
+    rot, trans = pose_error(oracle, r["T"], two_plane["gt"])
+    assert trans < TRANS_TOL and rot < ROT_TOL
+    # the optimiser maximises the score (d1 < 0): it must not decrease from first to last evaluation
+    assert r["trace"][-1, 6] > r["trace"][0, 6]
+
+
+@pytest.mark.parametrize("K,use_gn", [(10, True)])
+def test_svn_cases(oracle, two_plane, K, use_gn):
+    svn = O.OracleSvn(resolution=1.0, min_pts=3, search="DIRECT7", num_threads=8, K=K, max_iter=100, kernel_h=1.0,
+                      stop_thresh=1e-4, step_size=1.0, use_gn=use_gn)
+    svn.set_target(two_plane["target"])
+    svn.set_source(two_plane["source"])
+    P0 = O.OracleSvn.sample_particles(two_plane["guess"], K, seed=1337)
+    r = svn.align(two_plane["guess"], P0)
+    assert r["converged"]
+    assert r["iterations"] < 100
+    rot, trans = pose_error(oracle, r["final_pose"], two_plane["gt"])
+    assert trans < TRANS_TOL and rot < ROT_TOL
+    cov = r["final_covariance"]
+    assert np.allclose(cov, cov.T, atol=1e-12) and np.linalg.eigvalsh(cov).min() >= 1e-9 * (1 - 1e-6)
+
+
+def test_svn_k1_full_newton_is_indefinite_at_the_guess(oracle, two_plane):
+    """SvnNdtK1_Newton (test_svn_ndt.cpp:263-317) cannot be used as a pin: at the test's initial
+    guess the FULL analytic NDT Hessian (svn_ndt_impl.hpp:472-494, same maths as
+    ndt_omp_impl.hpp:687-691) is indefinite, so an un-safeguarded Newton step of length 1 leaves
+    the basin.  pclomp survives this through its step clamp + direction flip
+    (ndt_omp_impl.hpp:927-934, 963-965).  Both flavours of the oracle agree on that Hessian, which
+    is what this test records ("Oracle pins")."""
+    svn = O.OracleSvn(resolution=1.0, min_pts=3, K=1, use_gn=False)
+    svn.set_target(two_plane["target"]); svn.set_source(two_plane["source"])
+    _, _, H_svn = svn.particle_derivatives(two_plane["guess"])
+    ev_svn = np.linalg.eigvalsh((H_svn + H_svn.T) / 2)
+    assert ev_svn[-1] > 1e6 and ev_svn[0] < -1e6
+    ndt = O.OracleNdt(resolution=1.0, min_pts=3, max_iterations=1, trans_epsilon=1e-4)
+    ndt.set_target(two_plane["target"]); ndt.set_source(two_plane["source"])
+    r = ndt.align(two_plane["guess"].astype(np.float32))
+    H_p = r["trace"][0, 13:49].reshape(6, 6)
+    ev_p = np.linalg.eigvalsh((H_p + H_p.T) / 2)
+    assert np.allclose(ev_p[[0, -1]], ev_svn[[0, -1]], rtol=0.2)
+    # at the ground truth both are negative definite (a maximum of the score)
+    _, _, H_gt = svn.particle_derivatives(two_plane["gt"])
+    assert np.linalg.eigvalsh((H_gt + H_gt.T) / 2).max() < 0
