@@ -13,7 +13,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libndtb.so")
 
 NDTB_OK = 0
-ERR = {-1: "NDTB_ERR_INVALID", -2: "NDTB_ERR_CUDA", -3: "NDTB_ERR_EMPTY", -4: "NDTB_ERR_OVERFLOW", -5: "NDTB_ERR_NOT_READY"}
+NDTB_ERR_INVALID, NDTB_ERR_CUDA, NDTB_ERR_EMPTY, NDTB_ERR_OVERFLOW, NDTB_ERR_NOT_READY = -1, -2, -3, -4, -5
+ERR ={-1: "NDTB_ERR_INVALID", -2: "NDTB_ERR_CUDA", -3: "NDTB_ERR_EMPTY", -4: "NDTB_ERR_OVERFLOW", -5: "NDTB_ERR_NOT_READY"}
 KDTREE, DIRECT26, DIRECT7, DIRECT1 = 0, 1, 2, 3
 FLAVOUR_PCLOMP, FLAVOUR_SVN = 0, 1
 
