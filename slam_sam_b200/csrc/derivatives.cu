@@ -178,25 +178,42 @@ __device__ __forceinline__ double pair_svn(const PointTables& pt, const double x
 }
 
 // ------------------------------------------------------------------------------ neighbour lookup
-__device__ __forceinline__ int lookup_pclomp(const GridMeta& m, const HashSlot* __restrict__ table, int i0, int i1, int i2, int ox, int oy,
-                                             int oz) {
-  // voxel_grid_covariance_omp_impl.hpp:379-394: displacement must lie in [min_b - ijk, max_b - ijk]
-  if (m.min_b[0] - i0 > ox || m.max_b[0] - i0 < ox) return -1;
-  if (m.min_b[1] - i1 > oy || m.max_b[1] - i1 < oy) return -1;
-  if (m.min_b[2] - i2 > oz || m.max_b[2] - i2 < oz) return -1;
-  const int lin = (i0 + ox - m.min_b[0]) * m.divb_mul[0] + (i1 + oy - m.min_b[1]) * m.divb_mul[1] + (i2 + oz - m.min_b[2]) * m.divb_mul[2];
-  return hash_find(table, m.hash_mask, static_cast<uint32_t>(lin));
+// Linear index of the neighbour cell, or HASH_EMPTY when the displacement leaves the bounding box
+// (voxel_grid_covariance_omp_impl.hpp:379-394: displacement must lie in [min_b - ijk, max_b - ijk]).
+__device__ __forceinline__ uint32_t cell_key_pclomp(const GridMeta& m, int i0, int i1, int i2, int ox, int oy, int oz) {
+  if (m.min_b[0] - i0 > ox || m.max_b[0] - i0 < ox) return HASH_EMPTY;
+  if (m.min_b[1] - i1 > oy || m.max_b[1] - i1 < oy) return HASH_EMPTY;
+  if (m.min_b[2] - i2 > oz || m.max_b[2] - i2 < oz) return HASH_EMPTY;
+  return static_cast<uint32_t>((i0 + ox - m.min_b[0]) * m.divb_mul[0] + (i1 + oy - m.min_b[1]) * m.divb_mul[1] + (i2 + oz - m.min_b[2]) * m.divb_mul[2]);
 }
 
-__device__ __forceinline__ int lookup_svn(const GridMeta& m, const HashSlot* __restrict__ table, float px, float py, float pz) {
-  // voxel_grid_covariance_impl.hpp:59-70 + voxel_grid_covariance.h:289-303
+// Cell key of svn's getLeaf (voxel_grid_covariance_impl.hpp:59-70 + voxel_grid_covariance.h:289-303)
+__device__ __forceinline__ uint32_t cell_key_svn(const GridMeta& m, float px, float py, float pz) {
   if (!(px >= m.lo_bound[0] && px < m.hi_bound[0] && py >= m.lo_bound[1] && py < m.hi_bound[1] && pz >= m.lo_bound[2] && pz < m.hi_bound[2]))
-    return -1;
+    return HASH_EMPTY;
   const int i0 = static_cast<int>(floorf(px * m.inv_leaf) - static_cast<float>(m.min_b[0]));
   const int i1 = static_cast<int>(floorf(py * m.inv_leaf) - static_cast<float>(m.min_b[1]));
   const int i2 = static_cast<int>(floorf(pz * m.inv_leaf) - static_cast<float>(m.min_b[2]));
-  const int lin = i0 * m.divb_mul[0] + i1 * m.divb_mul[1] + i2 * m.divb_mul[2];
-  return hash_find(table, m.hash_mask, static_cast<uint32_t>(lin));
+  return static_cast<uint32_t>(i0 * m.divb_mul[0] + i1 * m.divb_mul[1] + i2 * m.divb_mul[2]);
+}
+
+// All P home slots are fetched before any is examined (one L2 round trip instead of P); the rare
+// displaced key (load factor <= 0.5) continues with the usual linear probe.
+template <int PROBES>
+__device__ __forceinline__ void hash_find_batch(const HashSlot* __restrict__ table, uint32_t mask, const uint32_t* key, int* rows) {
+  uint2 s[PROBES];
+#pragma unroll
+  for (int q = 0; q < PROBES; ++q) s[q] = (key[q] != HASH_EMPTY) ? __ldg(reinterpret_cast<const uint2*>(table) + (key[q] & mask)) : make_uint2(HASH_EMPTY, 0u);
+#pragma unroll
+  for (int q = 0; q < PROBES; ++q) {
+    uint2 v = s[q];
+    uint32_t b = key[q] & mask;
+    while (v.x != key[q] && v.x != HASH_EMPTY) {
+      b = (b + 1) & mask;
+      v = __ldg(reinterpret_cast<const uint2*>(table) + b);
+    }
+    rows[q] = (v.x == HASH_EMPTY) ? -1 : static_cast<int>(v.y);
+  }
 }
 
 __device__ __constant__ int c_off[7][3] = {{0, 0, 0}, {1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};
@@ -221,7 +238,7 @@ __device__ __forceinline__ void halve_step(double* v, int lane) {
 
 // Reduce acc[RED_PAD] over the block and store RED_N sums to `out` (fixed order: warp tree, then
 // warps 0..W-1 in order).
-__device__ __forceinline__ void block_reduce_store(double* acc, double (*s_red)[RED_PAD], double* __restrict__ out) {
+__device__ __forceinline__ void block_reduce_store(double* acc, double (*s_red)[RED_PAD], double* __restrict__ out, size_t stride) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   halve_step<48, 16>(acc, lane);
   halve_step<24, 8>(acc, lane);
@@ -239,117 +256,237 @@ __device__ __forceinline__ void block_reduce_store(double* acc, double (*s_red)[
     double v = s_red[0][threadIdx.x];
 #pragma unroll
     for (int k = 1; k < EVAL_THREADS / 32; ++k) v += s_red[k][threadIdx.x];
-    out[threadIdx.x] = v;
+    out[threadIdx.x * stride] = v;
   }
 }
 
 // ------------------------------------------------------------------------------ the kernel
+// Every WARP is autonomous (no block barrier in the main loop) and alternates two phases that are
+// decoupled through a small shared-memory pair queue of its own:
+//   phase A (one lane per POINT, 32 points): transform, the P hash probes (independent loads -> one
+//            or two L2 round trips), an L1 prefetch of every hit voxel record, the per-point
+//            Jacobian/Hessian tables (computePointDerivatives) into a shared-memory slot, and the
+//            point's (slot,row) pairs appended to the queue by a warp scan;
+//   phase B (one lane per PAIR): 32 real (point,voxel) pairs evaluate updateDerivatives, so no lane
+//            idles on a missed probe (h-bar/P of the lanes would otherwise be masked off).
+// Pairs that do not fill a round stay queued for the next chunk.  Points are dealt to warps in
+// groups of PT_GROUP consecutive points, round-robin, so every warp sees the same hit density.
+// The point -> warp -> queue position -> lane mapping is static: every accumulator sees its terms
+// in a fixed order (run-to-run bit stable).
+constexpr int PT_GROUP = 4;                   // consecutive points per deal (64 B of the cloud)
+constexpr int GROUPS_PER_CHUNK = 32 / PT_GROUP;
+constexpr int Q_CAP = 256;                    // >= 31 + 7 * 32, power of two
+constexpr int SLOT_RING = 64;                 // point slots of the current and the previous chunk
+constexpr int EVAL_WARPS = EVAL_THREADS / 32;
+
+struct __align__(16) PtSlot {  // 28 words
+  float xt[3];        // transformed point
+  int nearest_bits;   // max pair score of the point as float bits (>= 0): NVTL, ndt_omp_impl.hpp:384-389
+  float xj[8];
+  float xh[16];
+};
+
+struct WarpScratch {
+  PtSlot pts[SLOT_RING];
+  int qrow[Q_CAP];
+  unsigned char qslot[Q_CAP];
+};
+
+template <int FLAVOUR, bool HESS, bool GN>
+__device__ __forceinline__ void eval_pair(PtSlot* __restrict__ s_pts, int slot, int row, const EvalState& st, const VoxRec* __restrict__ recs,
+                                          const double* __restrict__ c_mean, const double* __restrict__ c_icov, float d2f,
+                                          double* __restrict__ acc) {
+  PointTables pt;
+  float xt[3];
+  {
+    const float4* sp = reinterpret_cast<const float4*>(s_pts + slot);
+    const float4 a = sp[0], b = sp[1], c = sp[2];
+    xt[0] = a.x; xt[1] = a.y; xt[2] = a.z;
+    pt.xj[0] = b.x; pt.xj[1] = b.y; pt.xj[2] = b.z; pt.xj[3] = b.w; pt.xj[4] = c.x; pt.xj[5] = c.y; pt.xj[6] = c.z; pt.xj[7] = c.w;
+    if (HESS && !(FLAVOUR == FLAVOUR_SVN && GN)) {
+      const float4 d = sp[3], e = sp[4], f = sp[5], g = sp[6];
+      pt.xh[0] = d.x; pt.xh[1] = d.y; pt.xh[2] = d.z; pt.xh[3] = d.w; pt.xh[4] = e.x; pt.xh[5] = e.y; pt.xh[6] = e.z; pt.xh[7] = e.w;
+      pt.xh[8] = f.x; pt.xh[9] = f.y; pt.xh[10] = f.z; pt.xh[11] = f.w; pt.xh[12] = g.x; pt.xh[13] = g.y; pt.xh[14] = g.z;
+    }
+  }
+  if (FLAVOUR == FLAVOUR_PCLOMP) {
+    const uint4* rp = reinterpret_cast<const uint4*>(recs + row);
+    const uint4 q0 = __ldg(rp), q1 = __ldg(rp + 1), q2 = __ldg(rp + 2), q3 = __ldg(rp + 3);
+    const double m0 = __hiloint2double(q0.y, q0.x), m1 = __hiloint2double(q0.w, q0.z), m2 = __hiloint2double(q1.y, q1.x);
+    float C[9];
+    C[0] = __uint_as_float(q1.z); C[1] = __uint_as_float(q1.w);
+    C[2] = __uint_as_float(q2.x); C[3] = __uint_as_float(q2.y); C[4] = __uint_as_float(q2.z); C[5] = __uint_as_float(q2.w);
+    C[6] = __uint_as_float(q3.x); C[7] = __uint_as_float(q3.y); C[8] = __uint_as_float(q3.z);
+    float x4[3];
+    x4[0] = static_cast<float>(static_cast<double>(xt[0]) - m0);
+    x4[1] = static_cast<float>(static_cast<double>(xt[1]) - m1);
+    x4[2] = static_cast<float>(static_cast<double>(xt[2]) - m2);
+    bool counted;
+    const float sf = pair_pclomp<HESS>(pt, x4, C, d2f, st.d1, acc, counted);
+    acc[RED_SCORE] += static_cast<double>(sf);
+    if (sf > 0.0f) atomicMax(&s_pts[slot].nearest_bits, __float_as_int(sf));
+  } else {
+    double xr[3], Cd[9];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) xr[a] = static_cast<double>(xt[a]) - __ldg(c_mean + 3 * row + a);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) Cd[i] = __ldg(c_icov + 9 * row + i);
+    acc[RED_SCORE] += pair_svn<GN>(pt, xr, Cd, st.d1, st.d2, acc);
+  }
+}
+
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
 template <int FLAVOUR, int PROBES, bool HESS, bool GN>
-__global__ void __launch_bounds__(EVAL_THREADS, 3) eval_kernel(const float4* __restrict__ src, int n, GridMeta m, const VoxRec* __restrict__ recs,
-                                                            const HashSlot* __restrict__ table, const double* __restrict__ c_mean,
-                                                            const double* __restrict__ c_icov, const EvalState* __restrict__ states,
-                                                            double* __restrict__ partials, double* __restrict__ results,
-                                                            unsigned int* __restrict__ tickets, int particle_offset) {
+__global__ void __launch_bounds__(EVAL_THREADS, EVAL_MIN_BLOCKS) eval_kernel(const float4* __restrict__ src, int n, GridMeta m,
+                                                                          const VoxRec* __restrict__ recs, const HashSlot* __restrict__ table,
+                                                                          const double* __restrict__ c_mean, const double* __restrict__ c_icov,
+                                                                          const EvalState* __restrict__ states, double* __restrict__ partials,
+                                                                          double* __restrict__ results, unsigned int* __restrict__ tickets,
+                                                                          int particle_offset) {
   __shared__ EvalState st;
-  __shared__ double s_red[EVAL_THREADS / 32][RED_PAD];
+  __shared__ WarpScratch s_warp[EVAL_WARPS];
+  __shared__ double s_red[EVAL_WARPS][RED_PAD];
   __shared__ bool s_last;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const int particle = blockIdx.y + particle_offset;
   {
     const int words = sizeof(EvalState) / 4;
     const uint32_t* g = reinterpret_cast<const uint32_t*>(states + particle);
     uint32_t* s = reinterpret_cast<uint32_t*>(&st);
-    for (int i = threadIdx.x; i < words; i += blockDim.x) s[i] = g[i];
+    for (int i = tid; i < words; i += blockDim.x) s[i] = g[i];
   }
+  PtSlot* const s_pts = s_warp[w].pts;
+  int* const s_qrow = s_warp[w].qrow;
+  unsigned char* const s_qslot = s_warp[w].qslot;
+  s_pts[lane].nearest_bits = 0;
+  s_pts[32 + lane].nearest_bits = 0;
   __syncthreads();
   double acc[RED_PAD];
 #pragma unroll
   for (int i = 0; i < RED_PAD; ++i) acc[i] = 0.0;
+  const float d2f = static_cast<float>(st.d2);
 
-  // grid-stride over points: a thread's points are visited in a fixed order -> deterministic sums
-  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
-    const float4 p = __ldg(src + idx);
-    // pcl::transformPointCloud (SSE2 Transformer association): m0*x + (m1*y + (m2*z + m3))
-    float xt[3];
-#pragma unroll
-    for (int r = 0; r < 3; ++r) xt[r] = st.T[4 * r] * p.x + (st.T[4 * r + 1] * p.y + (st.T[4 * r + 2] * p.z + st.T[4 * r + 3]));
-    bool point_ok = true;
-    if (FLAVOUR == FLAVOUR_SVN) point_ok = isfinite(xt[0]) && isfinite(xt[1]) && isfinite(xt[2]);  // svn_ndt_impl.hpp:573
+  const int n_groups = (n + PT_GROUP - 1) / PT_GROUP;
+  const int n_warps = gridDim.x * EVAL_WARPS;
+  const int warp_global = blockIdx.x * EVAL_WARPS + w;
+  // this warp's groups: warp_global + k * n_warps, k = 0 .. my_groups-1
+  const int my_groups = (n_groups > warp_global) ? (n_groups - warp_global + n_warps - 1) / n_warps : 0;
+  int head = 0, tail = 0;  // queue positions (monotonic; entry = pos & (Q_CAP - 1))
+  int chunk = 0;
+  for (int k0 = 0; k0 < my_groups; k0 += GROUPS_PER_CHUNK, ++chunk) {
+    // ---------------------------------------------------------------- phase A: one lane per point
+    const int k = k0 + lane / PT_GROUP;
+    const int idx = (warp_global + k * n_warps) * PT_GROUP + (lane % PT_GROUP);
+    const bool have = (k < my_groups) && (idx < n);
+    const int slot = (chunk & 1) * 32 + lane;
+    // the slot's previous occupant (two chunks ago) has had all its pairs evaluated: retire its NVTL term
+    if (FLAVOUR == FLAVOUR_PCLOMP) acc[RED_NEAREST] += static_cast<double>(__int_as_float(s_pts[slot].nearest_bits));
     int rows[PROBES];
     int nn = 0;
-    if (point_ok) {
-      if (FLAVOUR == FLAVOUR_PCLOMP) {
-        const int i0 = static_cast<int>(floorf(__fdiv_rn(xt[0], m.leaf)));
-        const int i1 = static_cast<int>(floorf(__fdiv_rn(xt[1], m.leaf)));
-        const int i2 = static_cast<int>(floorf(__fdiv_rn(xt[2], m.leaf)));
+    bool filled = false;
+    if (have) {
+      const float4 p = __ldg(src + idx);
+      // pcl::transformPointCloud (SSE2 Transformer association): m0*x + (m1*y + (m2*z + m3))
+      float xt[3];
 #pragma unroll
-        for (int k = 0; k < PROBES; ++k) {
-          const int r = lookup_pclomp(m, table, i0, i1, i2, c_off[k][0], c_off[k][1], c_off[k][2]);
-          rows[k] = r;
-        }
-      } else {
-#pragma unroll
-        for (int k = 0; k < PROBES; ++k) {
-          const float w = m.leaf;
-          const float qx = (k == 1) ? xt[0] + w : ((k == 2) ? xt[0] - w : xt[0]);
-          const float qy = (k == 3) ? xt[1] + w : ((k == 4) ? xt[1] - w : xt[1]);
-          const float qz = (k == 5) ? xt[2] + w : ((k == 6) ? xt[2] - w : xt[2]);
-          rows[k] = lookup_svn(m, table, qx, qy, qz);
-        }
-      }
-      PointTables pt;
-#pragma unroll
-      for (int r = 0; r < 8; ++r) pt.xj[r] = dot3(st.jang[3 * r], st.jang[3 * r + 1], st.jang[3 * r + 2], p.x, p.y, p.z);
-      if (HESS && !(FLAVOUR == FLAVOUR_SVN && GN)) {
-#pragma unroll
-        for (int r = 0; r < 15; ++r) pt.xh[r] = dot3(st.hang[3 * r], st.hang[3 * r + 1], st.hang[3 * r + 2], p.x, p.y, p.z);
-      }
-      const float d2f = static_cast<float>(st.d2);
-      double score_pt = 0.0, nearest_pt = 0.0;
-      // ONE copy of the pair maths in the instruction stream (a fully unrolled 7-neighbour body
-      // overflows the instruction cache: ncu showed "no_instruction" as the top stall).
-#pragma unroll 1
-      for (int k = 0; k < PROBES; ++k) {
-        int row = rows[0];
-#pragma unroll
-        for (int q = 1; q < PROBES; ++q) row = (k == q) ? rows[q] : row;
-        if (row < 0) continue;
-        ++nn;
+      for (int r = 0; r < 3; ++r) xt[r] = st.T[4 * r] * p.x + (st.T[4 * r + 1] * p.y + (st.T[4 * r + 2] * p.z + st.T[4 * r + 3]));
+      bool point_ok = true;
+      if (FLAVOUR == FLAVOUR_SVN) point_ok = isfinite(xt[0]) && isfinite(xt[1]) && isfinite(xt[2]);  // svn_ndt_impl.hpp:573
+      if (point_ok) {
+        uint32_t key[PROBES];
         if (FLAVOUR == FLAVOUR_PCLOMP) {
-          const uint4* rp = reinterpret_cast<const uint4*>(recs + row);
-          const uint4 q0 = __ldg(rp), q1 = __ldg(rp + 1), q2 = __ldg(rp + 2), q3 = __ldg(rp + 3);
-          const double m0 = __hiloint2double(q0.y, q0.x), m1 = __hiloint2double(q0.w, q0.z), m2 = __hiloint2double(q1.y, q1.x);
-          float C[9];
-          C[0] = __uint_as_float(q1.z); C[1] = __uint_as_float(q1.w);
-          C[2] = __uint_as_float(q2.x); C[3] = __uint_as_float(q2.y); C[4] = __uint_as_float(q2.z); C[5] = __uint_as_float(q2.w);
-          C[6] = __uint_as_float(q3.x); C[7] = __uint_as_float(q3.y); C[8] = __uint_as_float(q3.z);
-          float x4[3];
-          x4[0] = static_cast<float>(static_cast<double>(xt[0]) - m0);
-          x4[1] = static_cast<float>(static_cast<double>(xt[1]) - m1);
-          x4[2] = static_cast<float>(static_cast<double>(xt[2]) - m2);
-          bool counted;
-          const double s = static_cast<double>(pair_pclomp<HESS>(pt, x4, C, d2f, st.d1, acc, counted));
-          score_pt += s;
-          if (s > nearest_pt) nearest_pt = s;
+          const int i0 = static_cast<int>(floorf(__fdiv_rn(xt[0], m.leaf)));
+          const int i1 = static_cast<int>(floorf(__fdiv_rn(xt[1], m.leaf)));
+          const int i2 = static_cast<int>(floorf(__fdiv_rn(xt[2], m.leaf)));
+#pragma unroll
+          for (int q = 0; q < PROBES; ++q) key[q] = cell_key_pclomp(m, i0, i1, i2, c_off[q][0], c_off[q][1], c_off[q][2]);
         } else {
-          double xr[3], Cd[9];
 #pragma unroll
-          for (int a = 0; a < 3; ++a) xr[a] = static_cast<double>(xt[a]) - __ldg(c_mean + 3 * row + a);
+          for (int q = 0; q < PROBES; ++q) {
+            const float lw = m.leaf;
+            const float qx = (q == 1) ? xt[0] + lw : ((q == 2) ? xt[0] - lw : xt[0]);
+            const float qy = (q == 3) ? xt[1] + lw : ((q == 4) ? xt[1] - lw : xt[1]);
+            const float qz = (q == 5) ? xt[2] + lw : ((q == 6) ? xt[2] - lw : xt[2]);
+            key[q] = cell_key_svn(m, qx, qy, qz);
+          }
+        }
+        hash_find_batch<PROBES>(table, m.hash_mask, key, rows);
 #pragma unroll
-          for (int i = 0; i < 9; ++i) Cd[i] = __ldg(c_icov + 9 * row + i);
-          const double s = pair_svn<GN>(pt, xr, Cd, st.d1, st.d2, acc);
-          score_pt += s;
-          if (s > nearest_pt) nearest_pt = s;
+        for (int q = 0; q < PROBES; ++q) {
+          if (rows[q] >= 0) {
+            ++nn;
+            if (FLAVOUR == FLAVOUR_PCLOMP) prefetch_l1(recs + rows[q]);
+          }
+        }
+        // computePointDerivatives (ndt_omp_impl.hpp:542-587) once per point
+        float4* sp = reinterpret_cast<float4*>(s_pts + slot);
+        float xj[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) xj[r] = dot3(st.jang[3 * r], st.jang[3 * r + 1], st.jang[3 * r + 2], p.x, p.y, p.z);
+        sp[0] = make_float4(xt[0], xt[1], xt[2], 0.0f);  // .w = nearest_bits = 0
+        sp[1] = make_float4(xj[0], xj[1], xj[2], xj[3]);
+        sp[2] = make_float4(xj[4], xj[5], xj[6], xj[7]);
+        if (HESS && !(FLAVOUR == FLAVOUR_SVN && GN)) {
+          float xh[16];
+#pragma unroll
+          for (int r = 0; r < 15; ++r) xh[r] = dot3(st.hang[3 * r], st.hang[3 * r + 1], st.hang[3 * r + 2], p.x, p.y, p.z);
+          xh[15] = 0.0f;
+          sp[3] = make_float4(xh[0], xh[1], xh[2], xh[3]);
+          sp[4] = make_float4(xh[4], xh[5], xh[6], xh[7]);
+          sp[5] = make_float4(xh[8], xh[9], xh[10], xh[11]);
+          sp[6] = make_float4(xh[12], xh[13], xh[14], xh[15]);
+        }
+        filled = true;
+        acc[RED_FOUND] += nn > 0 ? 1.0 : 0.0;
+        acc[RED_COUNT] += static_cast<double>(nn);
+      }
+    }
+    if (!filled) s_pts[slot].nearest_bits = 0;
+    // warp exclusive scan of nn -> queue positions
+    int incl = nn;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    if (nn > 0) {
+      int pos = tail + incl - nn;
+#pragma unroll
+      for (int q = 0; q < PROBES; ++q) {
+        if (rows[q] >= 0) {
+          s_qrow[pos & (Q_CAP - 1)] = rows[q];
+          s_qslot[pos & (Q_CAP - 1)] = static_cast<unsigned char>(slot);
+          ++pos;
         }
       }
-      acc[RED_SCORE] += score_pt;
-      acc[RED_NEAREST] += nearest_pt;
-      acc[RED_FOUND] += nn > 0 ? 1.0 : 0.0;
-      acc[RED_COUNT] += static_cast<double>(nn);
     }
+    const int must = tail;  // everything queued before this chunk must be consumed before its slots are reused
+    tail += total;
+    __syncwarp();
+    // ---------------------------------------------------------------- phase B: one lane per pair
+    while (tail - head >= 32 || head < must) {
+      const int e = head + lane;
+      if (e < tail) eval_pair<FLAVOUR, HESS, GN>(s_pts, s_qslot[e & (Q_CAP - 1)], s_qrow[e & (Q_CAP - 1)], st, recs, c_mean, c_icov, d2f, acc);
+      head = min(head + 32, tail);
+    }
+    __syncwarp();
+  }
+  while (head < tail) {  // flush
+    const int e = head + lane;
+    if (e < tail) eval_pair<FLAVOUR, HESS, GN>(s_pts, s_qslot[e & (Q_CAP - 1)], s_qrow[e & (Q_CAP - 1)], st, recs, c_mean, c_icov, d2f, acc);
+    head = min(head + 32, tail);
+  }
+  __syncwarp();
+  if (FLAVOUR == FLAVOUR_PCLOMP) {
+    acc[RED_NEAREST] += static_cast<double>(__int_as_float(s_pts[(chunk & 1) * 32 + lane].nearest_bits));
+    acc[RED_NEAREST] += static_cast<double>(__int_as_float(s_pts[((chunk + 1) & 1) * 32 + lane].nearest_bits));
   }
 
   // ---- deterministic block reduction ----------------------------------------------------------
-  block_reduce_store(acc, s_red, partials + (static_cast<size_t>(particle) * gridDim.x + blockIdx.x) * RED_N);
+  // partials are component-major [particle][RED_N][gridDim.x] so that the final pass reads them coalesced
+  block_reduce_store(acc, s_red, partials + static_cast<size_t>(particle) * gridDim.x * RED_N + blockIdx.x, gridDim.x);
   // ---- last block done: fixed-order reduction over all block partials --------------------------
   const int nblk = gridDim.x;
   __threadfence();
@@ -365,17 +502,19 @@ __global__ void __launch_bounds__(EVAL_THREADS, 3) eval_kernel(const float4* __r
 #pragma unroll
   for (int i = 0; i < RED_PAD; ++i) acc[i] = 0.0;
   for (int b = threadIdx.x; b < nblk; b += EVAL_THREADS) {
-    const double* row = pp + static_cast<size_t>(b) * RED_N;
 #pragma unroll
-    for (int i = 0; i < RED_N; ++i) acc[i] += __ldcg(row + i);
+    for (int i = 0; i < RED_N; ++i) acc[i] += __ldcg(pp + static_cast<size_t>(i) * nblk + b);
   }
   __syncthreads();
-  block_reduce_store(acc, s_red, results + static_cast<size_t>(particle) * RED_N);
+  block_reduce_store(acc, s_red, results + static_cast<size_t>(particle) * RED_N, 1);
   if (threadIdx.x == 0) tickets[particle] = 0;  // self-reset for the next launch
 }
 
-// One resident wave: 148 SMs x 3 CTAs (register-limited); larger clouds are covered by the grid-stride loop.
-int eval_blocks_for(int n) { const int b = (n + EVAL_THREADS - 1) / EVAL_THREADS; return b < 148 * 3 ? b : 148 * 3; }
+// One resident wave: 148 SMs x EVAL_MIN_BLOCKS CTAs (register-limited); the cloud is dealt to the warps round-robin.
+int eval_blocks_for(int n) {
+  const int b = (n + EVAL_THREADS - 1) / EVAL_THREADS;
+  return b < 148 * EVAL_MIN_BLOCKS ? b : 148 * EVAL_MIN_BLOCKS;
+}
 
 template <int FLAVOUR, int PROBES, bool HESS, bool GN>
 static void launch_t(const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs, const HashSlot* table, const double* c_mean,

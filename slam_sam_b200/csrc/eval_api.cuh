@@ -13,6 +13,9 @@ struct EvalBuffers {
 };
 
 constexpr int EVAL_THREADS = 128;
+#ifndef EVAL_MIN_BLOCKS
+#define EVAL_MIN_BLOCKS 3
+#endif
 
 // One derivative evaluation for `n_particles` poses over `n` source points.
 //   flavour  : FLAVOUR_PCLOMP -> ndt_omp_impl.hpp:217-347 maths (float pair maths, FP64 accumulate)

@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libndtb.so")
+LIB_PATH = os.environ.get("NDTB_LIB", os.path.join(_HERE, "libndtb.so"))  # NDTB_LIB: development builds of the same CUDA library
 
 NDTB_OK = 0
 NDTB_ERR_INVALID, NDTB_ERR_CUDA, NDTB_ERR_EMPTY, NDTB_ERR_OVERFLOW, NDTB_ERR_NOT_READY = -1, -2, -3, -4, -5
