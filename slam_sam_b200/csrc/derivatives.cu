@@ -88,6 +88,66 @@ __device__ __forceinline__ float pair_pclomp(const PointTables& pt, const float 
   return score_inc;
 }
 
+// Same arithmetic as pair_pclomp, but the 43 float terms (score, 6 gradient, 36 Hessian entries) are
+// RETURNED instead of accumulated: t[0] = score_inc, t[1..6] = e*xCJ, t[7..42] = e*(...), exactly the
+// floats the reference widens to double and adds (ndt_omp_impl.hpp:657,671,691).  A rejected pair
+// (:662) contributes nothing: all terms are +0.
+template <bool HESS>
+__device__ __forceinline__ void pclomp_terms(const PointTables& pt, const float x4[3], const float C[9], float d2f, double d1, float* __restrict__ t) {
+  float xC[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) xC[c] = dot3(x4[0], x4[1], x4[2], C[c], C[3 + c], C[6 + c]);
+  const float q = dot3(x4[0], x4[1], x4[2], xC[0], xC[1], xC[2]);
+  float e = static_cast<float>(exp(static_cast<double>(-d2f * q * 0.5f)));
+  const float score_inc = static_cast<float>(-d1 * static_cast<double>(e));
+  e = d2f * e;
+  const bool reject = (e > 1 || e < 0 || e != e);
+  e = static_cast<float>(static_cast<double>(e) * d1);
+  // a rejected pair adds nothing (:662).  Its terms are e * (finite) with e forced to 0, i.e. +-0: adding a
+  // signed zero to an FP64 sum leaves it unchanged, so no per-term select is needed.
+  if (reject) e = 0.0f;
+  const float* xj = pt.xj;
+  float CJ[3][6];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    CJ[r][0] = C[3 * r + 0]; CJ[r][1] = C[3 * r + 1]; CJ[r][2] = C[3 * r + 2];
+    CJ[r][3] = C[3 * r + 1] * xj[0] + C[3 * r + 2] * xj[1];
+    CJ[r][4] = dot3(C[3 * r], C[3 * r + 1], C[3 * r + 2], xj[2], xj[3], xj[4]);
+    CJ[r][5] = dot3(C[3 * r], C[3 * r + 1], C[3 * r + 2], xj[5], xj[6], xj[7]);
+  }
+  float xCJ[6];
+#pragma unroll
+  for (int c = 0; c < 6; ++c) xCJ[c] = dot3(x4[0], x4[1], x4[2], CJ[0][c], CJ[1][c], CJ[2][c]);
+  t[0] = reject ? 0.0f : score_inc;
+#pragma unroll
+  for (int c = 0; c < 6; ++c) t[1 + c] = e * xCJ[c];
+  if (HESS) {
+    const float* xh = pt.xh;
+    const float h_a = xC[1] * xh[0] + xC[2] * xh[1];
+    const float h_b = xC[1] * xh[2] + xC[2] * xh[3];
+    const float h_c = xC[1] * xh[4] + xC[2] * xh[5];
+    const float h_d = dot3(xC[0], xC[1], xC[2], xh[6], xh[7], xh[8]);
+    const float h_e = dot3(xC[0], xC[1], xC[2], xh[9], xh[10], xh[11]);
+    const float h_f = dot3(xC[0], xC[1], xC[2], xh[12], xh[13], xh[14]);
+    const float xCH[3][3] = {{h_a, h_b, h_c}, {h_b, h_d, h_e}, {h_c, h_e, h_f}};
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        float jcj;  // JCJ(j,i) = Jp(:,j)^T * CJ(:,i)
+        if (j < 3) jcj = CJ[j][i];
+        else if (j == 3) jcj = xj[0] * CJ[1][i] + xj[1] * CJ[2][i];
+        else if (j == 4) jcj = dot3(xj[2], xj[3], xj[4], CJ[0][i], CJ[1][i], CJ[2][i]);
+        else jcj = dot3(xj[5], xj[6], xj[7], CJ[0][i], CJ[1][i], CJ[2][i]);
+        float v = -d2f * xCJ[i] * xCJ[j];
+        if (i >= 3 && j >= 3) v = v + xCH[i - 3][j - 3];
+        v = v + jcj;
+        t[7 + 6 * i + j] = e * v;
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------ svn pair maths
 template <bool GN>
 __device__ __forceinline__ double pair_svn(const PointTables& pt, const double xr[3], const double Cd[9], double d1, double d2,
@@ -337,51 +397,13 @@ __device__ __forceinline__ void eval_pair(PtSlot* __restrict__ s_pts, int slot, 
 
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
+// Phase A for one chunk: lane `lane` handles point `idx` (if `have`), fills its slot, appends its pairs
+// to the warp's queue at `tail`; returns the number of pairs the warp appended.
 template <int FLAVOUR, int PROBES, bool HESS, bool GN>
-__global__ void __launch_bounds__(EVAL_THREADS, EVAL_MIN_BLOCKS) eval_kernel(const float4* __restrict__ src, int n, GridMeta m,
-                                                                          const VoxRec* __restrict__ recs, const HashSlot* __restrict__ table,
-                                                                          const double* __restrict__ c_mean, const double* __restrict__ c_icov,
-                                                                          const EvalState* __restrict__ states, double* __restrict__ partials,
-                                                                          double* __restrict__ results, unsigned int* __restrict__ tickets,
-                                                                          int particle_offset) {
-  __shared__ EvalState st;
-  __shared__ WarpScratch s_warp[EVAL_WARPS];
-  __shared__ double s_red[EVAL_WARPS][RED_PAD];
-  __shared__ bool s_last;
-  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  const int particle = blockIdx.y + particle_offset;
-  {
-    const int words = sizeof(EvalState) / 4;
-    const uint32_t* g = reinterpret_cast<const uint32_t*>(states + particle);
-    uint32_t* s = reinterpret_cast<uint32_t*>(&st);
-    for (int i = tid; i < words; i += blockDim.x) s[i] = g[i];
-  }
-  PtSlot* const s_pts = s_warp[w].pts;
-  int* const s_qrow = s_warp[w].qrow;
-  unsigned char* const s_qslot = s_warp[w].qslot;
-  s_pts[lane].nearest_bits = 0;
-  s_pts[32 + lane].nearest_bits = 0;
-  __syncthreads();
-  double acc[RED_PAD];
-#pragma unroll
-  for (int i = 0; i < RED_PAD; ++i) acc[i] = 0.0;
-  const float d2f = static_cast<float>(st.d2);
-
-  const int n_groups = (n + PT_GROUP - 1) / PT_GROUP;
-  const int n_warps = gridDim.x * EVAL_WARPS;
-  const int warp_global = blockIdx.x * EVAL_WARPS + w;
-  // this warp's groups: warp_global + k * n_warps, k = 0 .. my_groups-1
-  const int my_groups = (n_groups > warp_global) ? (n_groups - warp_global + n_warps - 1) / n_warps : 0;
-  int head = 0, tail = 0;  // queue positions (monotonic; entry = pos & (Q_CAP - 1))
-  int chunk = 0;
-  for (int k0 = 0; k0 < my_groups; k0 += GROUPS_PER_CHUNK, ++chunk) {
-    // ---------------------------------------------------------------- phase A: one lane per point
-    const int k = k0 + lane / PT_GROUP;
-    const int idx = (warp_global + k * n_warps) * PT_GROUP + (lane % PT_GROUP);
-    const bool have = (k < my_groups) && (idx < n);
-    const int slot = (chunk & 1) * 32 + lane;
-    // the slot's previous occupant (two chunks ago) has had all its pairs evaluated: retire its NVTL term
-    if (FLAVOUR == FLAVOUR_PCLOMP) acc[RED_NEAREST] += static_cast<double>(__int_as_float(s_pts[slot].nearest_bits));
+__device__ __forceinline__ int phase_a(const float4* __restrict__ src, int idx, bool have, int slot, int lane, int tail, const GridMeta& m,
+                                       const VoxRec* __restrict__ recs, const HashSlot* __restrict__ table, const EvalState& st,
+                                       PtSlot* __restrict__ s_pts, int* __restrict__ s_qrow, unsigned char* __restrict__ s_qslot,
+                                       double& found, double& count) {
     int rows[PROBES];
     int nn = 0;
     bool filled = false;
@@ -438,8 +460,8 @@ __global__ void __launch_bounds__(EVAL_THREADS, EVAL_MIN_BLOCKS) eval_kernel(con
           sp[6] = make_float4(xh[12], xh[13], xh[14], xh[15]);
         }
         filled = true;
-        acc[RED_FOUND] += nn > 0 ? 1.0 : 0.0;
-        acc[RED_COUNT] += static_cast<double>(nn);
+        found += nn > 0 ? 1.0 : 0.0;
+        count += static_cast<double>(nn);
       }
     }
     if (!filled) s_pts[slot].nearest_bits = 0;
@@ -462,6 +484,56 @@ __global__ void __launch_bounds__(EVAL_THREADS, EVAL_MIN_BLOCKS) eval_kernel(con
         }
       }
     }
+    return total;
+}
+
+template <int FLAVOUR, int PROBES, bool HESS, bool GN>
+__global__ void __launch_bounds__(EVAL_THREADS, EVAL_MIN_BLOCKS) eval_kernel(const float4* __restrict__ src, int n, GridMeta m,
+                                                                          const VoxRec* __restrict__ recs, const HashSlot* __restrict__ table,
+                                                                          const double* __restrict__ c_mean, const double* __restrict__ c_icov,
+                                                                          const EvalState* __restrict__ states, double* __restrict__ partials,
+                                                                          double* __restrict__ results, unsigned int* __restrict__ tickets,
+                                                                          int particle_offset) {
+  __shared__ EvalState st;
+  __shared__ WarpScratch s_warp[EVAL_WARPS];
+  __shared__ double s_red[EVAL_WARPS][RED_PAD];
+  __shared__ bool s_last;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int particle = blockIdx.y + particle_offset;
+  {
+    const int words = sizeof(EvalState) / 4;
+    const uint32_t* g = reinterpret_cast<const uint32_t*>(states + particle);
+    uint32_t* s = reinterpret_cast<uint32_t*>(&st);
+    for (int i = tid; i < words; i += blockDim.x) s[i] = g[i];
+  }
+  PtSlot* const s_pts = s_warp[w].pts;
+  int* const s_qrow = s_warp[w].qrow;
+  unsigned char* const s_qslot = s_warp[w].qslot;
+  s_pts[lane].nearest_bits = 0;
+  s_pts[32 + lane].nearest_bits = 0;
+  __syncthreads();
+  double acc[RED_PAD];
+#pragma unroll
+  for (int i = 0; i < RED_PAD; ++i) acc[i] = 0.0;
+  const float d2f = static_cast<float>(st.d2);
+
+  const int n_groups = (n + PT_GROUP - 1) / PT_GROUP;
+  const int n_warps = gridDim.x * EVAL_WARPS;
+  const int warp_global = blockIdx.x * EVAL_WARPS + w;
+  // this warp's groups: warp_global + k * n_warps, k = 0 .. my_groups-1
+  const int my_groups = (n_groups > warp_global) ? (n_groups - warp_global + n_warps - 1) / n_warps : 0;
+  int head = 0, tail = 0;  // queue positions (monotonic; entry = pos & (Q_CAP - 1))
+  int chunk = 0;
+  for (int k0 = 0; k0 < my_groups; k0 += GROUPS_PER_CHUNK, ++chunk) {
+    // ---------------------------------------------------------------- phase A: one lane per point
+    const int k = k0 + lane / PT_GROUP;
+    const int idx = (warp_global + k * n_warps) * PT_GROUP + (lane % PT_GROUP);
+    const bool have = (k < my_groups) && (idx < n);
+    const int slot = (chunk & 1) * 32 + lane;
+    // the slot's previous occupant (two chunks ago) has had all its pairs evaluated: retire its NVTL term
+    if (FLAVOUR == FLAVOUR_PCLOMP) acc[RED_NEAREST] += static_cast<double>(__int_as_float(s_pts[slot].nearest_bits));
+    const int total = phase_a<FLAVOUR, PROBES, HESS, GN>(src, idx, have, slot, lane, tail, m, recs, table, st, s_pts, s_qrow, s_qslot,
+                                                         acc[RED_FOUND], acc[RED_COUNT]);
     const int must = tail;  // everything queued before this chunk must be consumed before its slots are reused
     tail += total;
     __syncwarp();
@@ -510,10 +582,268 @@ __global__ void __launch_bounds__(EVAL_THREADS, EVAL_MIN_BLOCKS) eval_kernel(con
   if (threadIdx.x == 0) tickets[particle] = 0;  // self-reset for the next launch
 }
 
-// One resident wave: 148 SMs x EVAL_MIN_BLOCKS CTAs (register-limited); the cloud is dealt to the warps round-robin.
+// ------------------------------------------------------------------------------ the pclomp kernel
+// Same two phases, plus a register diet: a lane does not keep 43 FP64 accumulators.  Each round the
+// 32 lanes write their 43 float terms to a shared-memory tile and read it back TRANSPOSED: lane
+// (q = lane >> 3, g = lane & 7) owns 6 of every 24 terms and adds the terms of the four lanes
+// g, g+8, g+16, g+24 (widened to FP64, fixed order).  12 + 3 accumulators per lane instead of 46
+// -> <= 128 registers -> 16 resident warps per SM, one 512-thread CTA per SM, 148 partial rows.
+constexpr int PCL_THREADS = 512;
+constexpr int PCL_WARPS = PCL_THREADS / 32;
+constexpr int TR_STRIDE = 28;  // 24 terms + 4 pad words: conflict-free 16-byte stores and 8-byte transposed loads
+
+struct WarpScratchP {
+  PtSlot pts[SLOT_RING];
+  int qrow[Q_CAP];
+  unsigned char qslot[Q_CAP];
+  float tr[32 * TR_STRIDE];
+};
+
+struct PclShared {
+  WarpScratchP warp[PCL_WARPS];
+  double red[PCL_WARPS][RED_PAD];
+  bool last;
+};
+
+// Owner q of a pass holds terms {4q..4q+3} and {16+2q, 16+2q+1}: one 16-byte and one 8-byte load per source lane.
+__device__ __forceinline__ void transposed_add(const float* __restrict__ s_tr, int q, int g, double* __restrict__ a) {
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+    const float* r = s_tr + (g + 8 * s) * TR_STRIDE;
+    const float4 v0 = *reinterpret_cast<const float4*>(r + 4 * q);
+    const float2 v1 = *reinterpret_cast<const float2*>(r + 16 + 2 * q);
+    a[0] += static_cast<double>(v0.x); a[1] += static_cast<double>(v0.y);
+    a[2] += static_cast<double>(v0.z); a[3] += static_cast<double>(v0.w);
+    a[4] += static_cast<double>(v1.x); a[5] += static_cast<double>(v1.y);
+  }
+}
+
+// term index (0..47) of accumulator i (0..5) of pass p for owner q
+__device__ __forceinline__ int owner_term(int p, int q, int i) { return 24 * p + (i < 4 ? 4 * q + i : 16 + 2 * q + (i - 4)); }
+
+// One round of phase B: every lane takes part (inactive lanes contribute +0 terms).
+template <bool HESS>
+__device__ __forceinline__ void pclomp_round(bool active, int slot, int row, PtSlot* __restrict__ s_pts, float* __restrict__ s_tr, int lane,
+                                             const EvalState& st, const VoxRec* __restrict__ recs, float d2f, double* __restrict__ a) {
+  float t[44];
+  if (!active) {
+#pragma unroll
+    for (int i = 0; i < 44; ++i) t[i] = 0.0f;
+  } else {
+    PointTables pt;
+    const float4* sp = reinterpret_cast<const float4*>(s_pts + slot);
+    const float4 pa = sp[0], pb = sp[1], pc = sp[2];
+    pt.xj[0] = pb.x; pt.xj[1] = pb.y; pt.xj[2] = pb.z; pt.xj[3] = pb.w; pt.xj[4] = pc.x; pt.xj[5] = pc.y; pt.xj[6] = pc.z; pt.xj[7] = pc.w;
+    if (HESS) {
+      const float4 d = sp[3], e = sp[4], f = sp[5], g = sp[6];
+      pt.xh[0] = d.x; pt.xh[1] = d.y; pt.xh[2] = d.z; pt.xh[3] = d.w; pt.xh[4] = e.x; pt.xh[5] = e.y; pt.xh[6] = e.z; pt.xh[7] = e.w;
+      pt.xh[8] = f.x; pt.xh[9] = f.y; pt.xh[10] = f.z; pt.xh[11] = f.w; pt.xh[12] = g.x; pt.xh[13] = g.y; pt.xh[14] = g.z;
+    }
+    const uint4* rp = reinterpret_cast<const uint4*>(recs + row);
+    const uint4 q0 = __ldg(rp), q1 = __ldg(rp + 1), q2 = __ldg(rp + 2), q3 = __ldg(rp + 3);
+    const double m0 = __hiloint2double(q0.y, q0.x), m1 = __hiloint2double(q0.w, q0.z), m2 = __hiloint2double(q1.y, q1.x);
+    float C[9];
+    C[0] = __uint_as_float(q1.z); C[1] = __uint_as_float(q1.w);
+    C[2] = __uint_as_float(q2.x); C[3] = __uint_as_float(q2.y); C[4] = __uint_as_float(q2.z); C[5] = __uint_as_float(q2.w);
+    C[6] = __uint_as_float(q3.x); C[7] = __uint_as_float(q3.y); C[8] = __uint_as_float(q3.z);
+    float x4[3];
+    x4[0] = static_cast<float>(static_cast<double>(pa.x) - m0);
+    x4[1] = static_cast<float>(static_cast<double>(pa.y) - m1);
+    x4[2] = static_cast<float>(static_cast<double>(pa.z) - m2);
+    pclomp_terms<HESS>(pt, x4, C, d2f, st.d1, t);
+    t[43] = 0.0f;
+    if (!HESS) {
+#pragma unroll
+      for (int i = 7; i < 43; ++i) t[i] = 0.0f;
+    }
+    if (t[0] > 0.0f) atomicMax(&s_pts[slot].nearest_bits, __float_as_int(t[0]));
+  }
+  const int q = lane >> 3, g = lane & 7;
+  float4* my = reinterpret_cast<float4*>(s_tr + lane * TR_STRIDE);
+#pragma unroll
+  for (int i = 0; i < 6; ++i) my[i] = make_float4(t[4 * i], t[4 * i + 1], t[4 * i + 2], t[4 * i + 3]);
+  __syncwarp();
+  transposed_add(s_tr, q, g, a);
+  __syncwarp();
+  if (HESS) {
+#pragma unroll
+    for (int i = 0; i < 5; ++i) my[i] = make_float4(t[24 + 4 * i], t[25 + 4 * i], t[26 + 4 * i], t[27 + 4 * i]);
+    my[5] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    __syncwarp();
+    transposed_add(s_tr, q, g, a + 6);
+    __syncwarp();
+  }
+}
+
+template <int PROBES, bool HESS>
+__global__ void __launch_bounds__(PCL_THREADS, 1) eval_kernel_pclomp(const float4* __restrict__ src, int n, GridMeta m,
+                                                                     const VoxRec* __restrict__ recs, const HashSlot* __restrict__ table,
+                                                                     const __grid_constant__ EvalState st, double* __restrict__ partials,
+                                                                     double* __restrict__ results, unsigned int* __restrict__ tickets,
+                                                                     unsigned long long result_key,
+                                                                     unsigned long long* __restrict__ dbg /* optional: 8 stamps per block */) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  PclShared& sh = *reinterpret_cast<PclShared*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  auto stamp = [&](int k) {
+    if (dbg && tid == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); dbg[8 * blockIdx.x + k] = t; }
+  };
+  stamp(0);
+  PtSlot* const s_pts = sh.warp[w].pts;
+  int* const s_qrow = sh.warp[w].qrow;
+  unsigned char* const s_qslot = sh.warp[w].qslot;
+  float* const s_tr = sh.warp[w].tr;
+  s_pts[lane].nearest_bits = 0;
+  s_pts[32 + lane].nearest_bits = 0;
+  __syncwarp();
+  double a[12];
+#pragma unroll
+  for (int i = 0; i < 12; ++i) a[i] = 0.0;
+  double nearest = 0.0, found = 0.0, count = 0.0;
+  const float d2f = static_cast<float>(st.d2);
+
+  const int n_groups = (n + PT_GROUP - 1) / PT_GROUP;
+  const int n_warps = gridDim.x * PCL_WARPS;
+  const int warp_global = blockIdx.x * PCL_WARPS + w;
+  const int my_groups = (n_groups > warp_global) ? (n_groups - warp_global + n_warps - 1) / n_warps : 0;
+  int head = 0, tail = 0, chunk = 0;
+  for (int k0 = 0; k0 < my_groups; k0 += GROUPS_PER_CHUNK, ++chunk) {
+    const int k = k0 + lane / PT_GROUP;
+    const int idx = (warp_global + k * n_warps) * PT_GROUP + (lane % PT_GROUP);
+    const bool have = (k < my_groups) && (idx < n);
+    const int slot = (chunk & 1) * 32 + lane;
+    nearest += static_cast<double>(__int_as_float(s_pts[slot].nearest_bits));  // retire the slot's previous occupant
+    const int total = phase_a<FLAVOUR_PCLOMP, PROBES, HESS, false>(src, idx, have, slot, lane, tail, m, recs, table, st, s_pts, s_qrow, s_qslot,
+                                                                   found, count);
+    const int must = tail;
+    tail += total;
+    __syncwarp();
+    while (tail - head >= 32 || head < must) {
+      const int e = head + lane;
+      const bool active = e < tail;
+      pclomp_round<HESS>(active, active ? s_qslot[e & (Q_CAP - 1)] : 0, active ? s_qrow[e & (Q_CAP - 1)] : 0, s_pts, s_tr, lane, st, recs, d2f, a);
+      head = min(head + 32, tail);
+    }
+    __syncwarp();
+  }
+  while (head < tail) {  // flush
+    const int e = head + lane;
+    const bool active = e < tail;
+    pclomp_round<HESS>(active, active ? s_qslot[e & (Q_CAP - 1)] : 0, active ? s_qrow[e & (Q_CAP - 1)] : 0, s_pts, s_tr, lane, st, recs, d2f, a);
+    head = min(head + 32, tail);
+  }
+  __syncwarp();
+  nearest += static_cast<double>(__int_as_float(s_pts[(chunk & 1) * 32 + lane].nearest_bits));
+  nearest += static_cast<double>(__int_as_float(s_pts[((chunk + 1) & 1) * 32 + lane].nearest_bits));
+
+  stamp(1);
+  // ---- warp reduction (fixed tree): the 8 lanes that share q hold partial sums of the same 12 terms
+#pragma unroll
+  for (int o = 1; o < 8; o <<= 1) {
+#pragma unroll
+    for (int i = 0; i < 12; ++i) a[i] += __shfl_xor_sync(0xffffffffu, a[i], o);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    nearest += __shfl_xor_sync(0xffffffffu, nearest, o);
+    found += __shfl_xor_sync(0xffffffffu, found, o);
+    count += __shfl_xor_sync(0xffffffffu, count, o);
+  }
+  if ((lane & 7) == 0) {
+    const int q = lane >> 3;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      sh.red[w][owner_term(0, q, i)] = a[i];
+      if (owner_term(1, q, i) < 43) sh.red[w][owner_term(1, q, i)] = a[6 + i];
+    }
+  }
+  if (lane == 0) { sh.red[w][RED_NEAREST] = nearest; sh.red[w][RED_FOUND] = found; sh.red[w][RED_COUNT] = count; }
+  __syncthreads();
+  stamp(2);
+  const int nblk = gridDim.x;
+  if (tid < RED_N) {
+    double v = sh.red[0][tid];
+#pragma unroll
+    for (int kk = 1; kk < PCL_WARPS; ++kk) v += sh.red[kk][tid];
+    partials[static_cast<size_t>(tid) * nblk + blockIdx.x] = v;  // component-major
+  }
+  // ---- last block done: fixed-order reduction over the block partials --------------------------
+  // Release/acquire on the ticket (ordered with the CTA barriers) instead of a membar in every thread.
+  __syncthreads();
+  if (tid == 0) {
+    unsigned int tk;
+    asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(tk) : "l"(tickets) : "memory");
+    sh.last = (tk == static_cast<unsigned int>(nblk) - 1u);
+  }
+  __syncthreads();
+  stamp(3);
+  if (!sh.last) return;
+  if (tid < ((RED_N * 8 + 31) & ~31)) {  // whole warps: 8 lanes per component
+    const int c = tid >> 3, l = tid & 7;
+    const bool valid = c < RED_N;
+    constexpr int MAXI = (148 + 7) / 8;
+    double v[MAXI];
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) {
+      const int b = l + 8 * i;
+      v[i] = (valid && b < nblk) ? __ldcg(partials + static_cast<size_t>(c) * nblk + b) : 0.0;
+    }
+    double sum = v[0];
+#pragma unroll
+    for (int i = 1; i < MAXI; ++i) sum += v[i];
+    if (valid) for (int b = l + 8 * MAXI; b < nblk; b += 8) sum += __ldcg(partials + static_cast<size_t>(c) * nblk + b);
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (l == 0 && valid) {
+      // Self-validating result slot {value, value ^ key}: two 8-byte stores, no system fence and no separate flag.
+      // The host accepts slot c once w0 ^ w1 == key (a stale half cannot satisfy it), see wait_results().
+      const unsigned long long bits = static_cast<unsigned long long>(__double_as_longlong(sum));
+      volatile unsigned long long* slot = reinterpret_cast<volatile unsigned long long*>(results) + 2 * c;
+      slot[0] = bits;
+      slot[1] = bits ^ result_key;
+    }
+  }
+  stamp(4);
+  if (tid == 0) tickets[0] = 0;  // self-reset for the next launch (kernels on the stream are serialised)
+  stamp(5);
+}
+
+// Generic (svn) kernel: one resident wave of 148 SMs x EVAL_MIN_BLOCKS CTAs (register-limited); the cloud is dealt to the warps round-robin.
 int eval_blocks_for(int n) {
   const int b = (n + EVAL_THREADS - 1) / EVAL_THREADS;
   return b < 148 * EVAL_MIN_BLOCKS ? b : 148 * EVAL_MIN_BLOCKS;
+}
+
+int eval_blocks_pclomp(int n) {
+  const int per_block = PCL_WARPS * 32;  // at least one full chunk per warp
+  const int b = (n + per_block - 1) / per_block;
+  return b < 1 ? 1 : (b < 148 ? b : 148);
+}
+
+template <int PROBES, bool HESS>
+static cudaError_t launch_pclomp_t(const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs, const HashSlot* table, const EvalState& st,
+                                   const EvalBuffers& b, double* results, unsigned long long result_key,
+                                   cudaStream_t stream, unsigned long long* dbg) {
+  static bool configured = false;  // one handle per caller thread, but the attribute is per function: benign if set twice
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(eval_kernel_pclomp<PROBES, HESS>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(PclShared)));
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  eval_kernel_pclomp<PROBES, HESS><<<eval_blocks_pclomp(n), PCL_THREADS, sizeof(PclShared), stream>>>(d_src, n, meta, recs, table, st, b.d_partials,
+                                                                                                  results, b.d_tickets, result_key, dbg);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_eval_pclomp(int n_probe, bool compute_hessian, const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs,
+                               const HashSlot* table, const EvalState& st, const EvalBuffers& b, double* results, unsigned long long result_key,
+                               cudaStream_t stream, unsigned long long* dbg) {
+  if (n_probe == 7) {
+    return compute_hessian ? launch_pclomp_t<7, true>(d_src, n, meta, recs, table, st, b, results, result_key, stream, dbg)
+                           : launch_pclomp_t<7, false>(d_src, n, meta, recs, table, st, b, results, result_key, stream, dbg);
+  }
+  return compute_hessian ? launch_pclomp_t<1, true>(d_src, n, meta, recs, table, st, b, results, result_key, stream, dbg)
+                         : launch_pclomp_t<1, false>(d_src, n, meta, recs, table, st, b, results, result_key, stream, dbg);
 }
 
 template <int FLAVOUR, int PROBES, bool HESS, bool GN>
@@ -529,8 +859,7 @@ void launch_eval(int flavour, int n_probe, bool compute_hessian, bool gn, const 
                  int n_particles, int particle_offset, cudaStream_t stream) {
 #define ARGS d_src, n, meta, recs, table, c_mean, c_icov, b, n_particles, particle_offset, stream
   if (flavour == FLAVOUR_PCLOMP) {
-    if (n_probe == 7) { if (compute_hessian) launch_t<FLAVOUR_PCLOMP, 7, true, false>(ARGS); else launch_t<FLAVOUR_PCLOMP, 7, false, false>(ARGS); }
-    else { if (compute_hessian) launch_t<FLAVOUR_PCLOMP, 1, true, false>(ARGS); else launch_t<FLAVOUR_PCLOMP, 1, false, false>(ARGS); }
+    return;  // pclomp evaluations go through launch_eval_pclomp
   } else {
     if (n_probe == 7) { if (gn) launch_t<FLAVOUR_SVN, 7, true, true>(ARGS); else launch_t<FLAVOUR_SVN, 7, true, false>(ARGS); }
     else { if (gn) launch_t<FLAVOUR_SVN, 1, true, true>(ARGS); else launch_t<FLAVOUR_SVN, 1, true, false>(ARGS); }

@@ -28,4 +28,13 @@ void launch_eval(int flavour, int n_probe, bool compute_hessian, bool svn_gauss_
 
 int eval_blocks_for(int n);
 
+// pclomp flavour, ONE pose passed by value (kernel parameter, no state upload).  The 46 results are
+// written to `results` (device or mapped pinned host memory) as self-validating 16-byte slots
+// {bits(value), bits(value) ^ result_key}: a host thread can poll the slots instead of synchronising
+// the stream, and needs neither a flag nor a system-scope fence in the kernel.
+cudaError_t launch_eval_pclomp(int n_probe, bool compute_hessian, const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs,
+                               const HashSlot* table, const EvalState& st, const EvalBuffers& bufs, double* results,
+                               unsigned long long result_key, cudaStream_t stream, unsigned long long* dbg_stamps = nullptr);
+int eval_blocks_pclomp(int n);
+
 }  // namespace ndtb

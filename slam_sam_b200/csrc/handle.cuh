@@ -23,7 +23,11 @@ struct ndtb_handle_s {
 
   ndtb::EvalBuffers eval;
   ndtb::EvalState* h_states = nullptr;  // pinned, [max_particles]
-  double* h_results = nullptr;          // pinned, [max_particles][RED_N]
+  double* h_results = nullptr;          // pinned, [max_particles][RED_N]; the pclomp kernel writes it directly (zero-copy)
+  volatile unsigned int* h_flag = nullptr;  // pinned completion flag the pclomp kernel publishes (host polls it)
+  unsigned int flag_seq = 0;
+  std::vector<cudaEvent_t> ev_pool;     // per-evaluation event pairs, resolved after the loop (no per-iteration sync)
+  size_t ev_used = 0;
 
   bool has_reg_pose = false;
   float reg_translation[3] = {0, 0, 0};

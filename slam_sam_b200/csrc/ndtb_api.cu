@@ -40,7 +40,9 @@ int ensure_eval_buffers(ndtb_handle_s* h, int particles, int n_points) {
     CKH(cudaMalloc(&b.d_tickets, sizeof(unsigned int) * np));
     CKH(cudaMemset(b.d_tickets, 0, sizeof(unsigned int) * np));
     CKH(cudaMallocHost(&h->h_states, sizeof(EvalState) * np));
-    CKH(cudaMallocHost(&h->h_results, sizeof(double) * RED_N * np));
+    CKH(cudaMallocHost(&h->h_results, sizeof(double) * std::max(RED_N * np, 2 * RED_N + 36)));
+    std::memset(h->h_results, 0, sizeof(double) * std::max(RED_N * np, 2 * RED_N + 36));
+    if (!h->h_flag) { CKH(cudaMallocHost(const_cast<unsigned int**>(&h->h_flag), 64)); *h->h_flag = 0; }
     b.max_particles = np; b.max_blocks = nb;
   }
   return NDTB_OK;
@@ -97,6 +99,19 @@ static void fill_state(ndtb_handle_s* h, int slot, const double* p, const float*
   std::memcpy(s.p, p, 6 * sizeof(double));
 }
 
+// Sum the CUDA-event durations of the evaluations issued since the last call (needs the stream idle).
+static int resolve_eval_events(ndtb_handle_s* h) {
+  if (h->ev_used == 0) return NDTB_OK;
+  CKH(cudaEventSynchronize(h->ev_pool[h->ev_used - 1]));
+  for (size_t i = 0; i + 1 < h->ev_used; i += 2) {
+    float ms = 0;
+    cudaEventElapsedTime(&ms, h->ev_pool[i], h->ev_pool[i + 1]);
+    h->eval_ms_total += ms;
+  }
+  h->ev_used = 0;
+  return NDTB_OK;
+}
+
 // One pclomp evaluation: upload state, launch, read back the 46-double result, apply the
 // regulariser (ndt_omp_impl.hpp:349-382) and NVTL (:384-389) on the host.
 static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool compute_hessian, double* score, double* g, double* H,
@@ -105,19 +120,58 @@ static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool
   int rc = ensure_eval_buffers(h, 1, n);
   if (rc != NDTB_OK) return rc;
   fill_state(h, 0, p, T16, 10e-5, false);
-  CKH(cudaMemcpyAsync(h->eval.d_states, h->h_states, sizeof(EvalState), cudaMemcpyHostToDevice, h->stream));
   const int n_probe = (h->params.search_method == NDTB_DIRECT1) ? 1 : 7;
-  cudaEventRecord(h->ev[2], h->stream);
-  launch_eval(FLAVOUR_PCLOMP, n_probe, compute_hessian, false, h->d_source, n, h->grid.meta, h->grid.recs, h->grid.table, h->grid.c_mean,
-              h->grid.c_icov, h->eval, 1, 0, h->stream);
-  cudaEventRecord(h->ev[3], h->stream);
-  CKH(cudaMemcpyAsync(h->h_results, h->eval.d_results, sizeof(double) * RED_N, cudaMemcpyDeviceToHost, h->stream));
-  CKH(cudaStreamSynchronize(h->stream));
-  CKH(cudaGetLastError());
-  float ms = 0;
-  cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]);
-  h->eval_ms_total += ms; h->eval_launches += 1; h->launches += 1;
-  const double* r = h->h_results;
+  // event pair from the pool: elapsed times are resolved by resolve_eval_events() after the loop
+  if (h->ev_used + 2 > h->ev_pool.size()) {
+    for (int i = 0; i < 2; ++i) { cudaEvent_t e; CKH(cudaEventCreate(&e)); h->ev_pool.push_back(e); }
+  }
+  cudaEvent_t e0 = h->ev_pool[h->ev_used], e1 = h->ev_pool[h->ev_used + 1];
+  h->ev_used += 2;
+  const unsigned long long key = 0x9E3779B97F4A7C15ull * static_cast<unsigned long long>(++h->flag_seq) | 1ull;
+  cudaEventRecord(e0, h->stream);
+  static unsigned long long* d_dbg = nullptr;  // development aid: NDTB_DEBUG_TIMING=1 prints in-kernel globaltimer stamps
+  static const bool dbg_on = getenv("NDTB_DEBUG_TIMING") != nullptr;
+  if (dbg_on && !d_dbg) { cudaMalloc(&d_dbg, 8 * 148 * sizeof(unsigned long long)); }
+  if (dbg_on) cudaMemsetAsync(d_dbg, 0, 8 * 148 * sizeof(unsigned long long), h->stream);
+  // state by value (kernel parameter); the kernel writes 46 self-validating slots {bits, bits ^ key} straight into
+  // pinned host memory, and this thread polls them instead of synchronising the stream
+  CKH(launch_eval_pclomp(n_probe, compute_hessian, h->d_source, n, h->grid.meta, h->grid.recs, h->grid.table, h->h_states[0], h->eval,
+                         h->h_results, key, h->stream, dbg_on ? d_dbg : nullptr));
+  cudaEventRecord(e1, h->stream);
+  double rbuf[RED_N];
+  {
+    volatile unsigned long long* slots = reinterpret_cast<volatile unsigned long long*>(h->h_results);
+    unsigned int spins = 0;
+    for (int c = RED_N - 1; c >= 0; --c) {
+      for (;;) {
+        const unsigned long long w0 = slots[2 * c], w1 = slots[2 * c + 1];
+        if ((w0 ^ w1) == key) { std::memcpy(&rbuf[c], &w0, 8); break; }
+        if ((++spins & 4095u) == 0) {  // a stream query every 4096 spins catches a failed launch
+          const cudaError_t q = cudaStreamQuery(h->stream);
+          if (q != cudaSuccess && q != cudaErrorNotReady) { h->last_error = std::string("eval kernel: ") + cudaGetErrorString(q); return NDTB_ERR_CUDA; }
+          if (q == cudaSuccess) {
+            const unsigned long long x0 = slots[2 * c], x1 = slots[2 * c + 1];
+            if ((x0 ^ x1) != key) { h->last_error = "eval kernel finished without publishing its result"; return NDTB_ERR_CUDA; }
+          }
+        }
+      }
+    }
+  }
+  __sync_synchronize();
+  if (dbg_on) {
+    std::vector<unsigned long long> st(8 * 148);
+    cudaStreamSynchronize(h->stream);
+    cudaMemcpy(st.data(), d_dbg, st.size() * 8, cudaMemcpyDeviceToHost);
+    const int nb = eval_blocks_pclomp(n);
+    unsigned long long t0 = ~0ull;
+    for (int b = 0; b < nb; ++b) t0 = std::min(t0, st[8 * b]);
+    unsigned long long mx[6] = {0, 0, 0, 0, 0, 0}, mn[6] = {~0ull, ~0ull, ~0ull, ~0ull, ~0ull, ~0ull};
+    for (int b = 0; b < nb; ++b) for (int k = 0; k < 6; ++k) if (st[8 * b + k]) { mx[k] = std::max(mx[k], st[8 * b + k] - t0); mn[k] = std::min(mn[k], st[8 * b + k] - t0); }
+    fprintf(stderr, "[dbg n=%d blocks=%d] ns since first block start: start %llu..%llu | main done %llu..%llu | block reduced %llu..%llu | ticket %llu..%llu | final %llu | flag %llu\n",
+            n, nb, mn[0], mx[0], mn[1], mx[1], mn[2], mx[2], mn[3], mx[3], mx[4], mx[5]);
+  }
+  h->eval_launches += 1; h->launches += 1;
+  const double* r = rbuf;
   double sc = r[RED_SCORE];
   std::memcpy(g, r + RED_G, 6 * sizeof(double));
   std::memcpy(H, r + RED_H, 36 * sizeof(double));
@@ -195,6 +249,8 @@ int ndtb_destroy(ndtb_handle h) {
   cudaFree(h->eval.d_states); cudaFree(h->eval.d_partials); cudaFree(h->eval.d_results); cudaFree(h->eval.d_tickets);
   if (h->h_states) cudaFreeHost(h->h_states);
   if (h->h_results) cudaFreeHost(h->h_results);
+  if (h->h_flag) cudaFreeHost(const_cast<unsigned int*>(h->h_flag));
+  for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   cudaFree(h->d_svn_in); cudaFree(h->d_svn_out);
   for (int i = 0; i < 4; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   cudaStreamDestroy(h->stream);
@@ -283,7 +339,9 @@ int ndtb_compute_derivatives(ndtb_handle h, const double p[6], const float* T16,
   if (h->params.grid_flavour != NDTB_FLAVOUR_PCLOMP) return set_error(h, NDTB_ERR_INVALID, "pclomp entry point on an svn-flavour handle");
   float T[16];
   if (T16) std::memcpy(T, T16, sizeof(T)); else pose_to_T(p, T);
-  return eval_pclomp(h, p, T, compute_hessian != 0, score, gradient, hessian, nvtl);
+  const int rc = eval_pclomp(h, p, T, compute_hessian != 0, score, gradient, hessian, nvtl);
+  if (rc != NDTB_OK) return rc;
+  return resolve_eval_events(h);
 }
 
 int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* transformation_array, int capacity, float* out_xyz) {
@@ -384,7 +442,7 @@ int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* tr
   cudaEventRecord(h->ev[1], h->stream);
   cudaEventSynchronize(h->ev[1]);
   cudaEventElapsedTime(&h->align_ms, h->ev[0], h->ev[1]);
-  return NDTB_OK;
+  return resolve_eval_events(h);
 }
 
 int ndtb_get_trace(ndtb_handle h, double* trace, int capacity, int* count) {
