@@ -27,6 +27,12 @@ struct DeviceGrid {
   int* d_bbox = nullptr;            // 6 ordered ints
   unsigned int* d_counters = nullptr;  // [0] skipped points, [1] V, [2] valid leaves
   int* h_pinned = nullptr;          // 16 ints of pinned host memory for the small read-backs
+  double* sorted_xyz = nullptr;     // target points in voxel order (input order inside a voxel), widened to FP64, 3 per point
+  double* vox_sums = nullptr;       // [V][9] Sum x, Sum x x^T per voxel (k4a -> k4b)
+  uint32_t* digit_totals = nullptr; // 256 per-digit totals of the current radix pass
+  unsigned int* d_ticket = nullptr; // last-block-done tickets of the bbox / finalize kernels
+  volatile unsigned long long* h_slots = nullptr;  // pinned self-validating slots the kernels publish to (bbox 0..5, counters 8..10)
+  unsigned long long slot_seq = 0;
 };
 
 // Returns NDTB_OK / NDTB_ERR_* ; synchronises the stream twice (bbox read-back, final counters).
@@ -35,7 +41,6 @@ int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resoluti
 void free_device_grid(DeviceGrid& g);
 
 // voxel_finalize.cu
-void launch_voxel_finalize(const DeviceGrid& g, const float4* d_pts, const uint32_t* sorted_vals, uint32_t n_points_upper,
-                           cudaStream_t stream);
+void launch_voxel_finalize(const DeviceGrid& g, uint32_t n_points_upper, unsigned long long publish_key, cudaStream_t stream);
 
 }  // namespace ndtb

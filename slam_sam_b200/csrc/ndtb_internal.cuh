@@ -74,6 +74,13 @@ __host__ __device__ __forceinline__ float ordered_to_float_bits(int i) {
 #endif
 }
 
+// Self-validating host slot (same scheme as the eval kernel's results): {bits, bits ^ key}, two 8-byte
+// stores into pinned host memory; the host polls w0 ^ w1 == key instead of synchronising the stream.
+__device__ __forceinline__ void publish_slot(volatile unsigned long long* slots, int i, unsigned long long bits, unsigned long long key) {
+  slots[2 * i] = bits;
+  slots[2 * i + 1] = bits ^ key;
+}
+
 // Hash lookup: linear probing from key & mask; returns row or -1.
 __device__ __forceinline__ int hash_find(const HashSlot* __restrict__ table, uint32_t mask, uint32_t key) {
   uint32_t b = key & mask;

@@ -17,11 +17,17 @@ static int ensure_capacity(DeviceGrid& g, size_t n) {
     CK(cudaMalloc(&g.d_bbox, 6 * sizeof(int)));
     CK(cudaMalloc(&g.d_counters, 4 * sizeof(unsigned int)));
     CK(cudaMallocHost(&g.h_pinned, 16 * sizeof(int)));
+    CK(cudaMalloc(&g.digit_totals, 256 * sizeof(uint32_t)));
+    CK(cudaMalloc(&g.d_ticket, 2 * sizeof(unsigned int)));
+    CK(cudaMemset(g.d_ticket, 0, 2 * sizeof(unsigned int)));
+    CK(cudaMallocHost(&g.h_slots, 32 * sizeof(unsigned long long)));
+    std::memset(const_cast<unsigned long long*>(g.h_slots), 0, 32 * sizeof(unsigned long long));
   }
   if (n > g.pts_alloc) {
     for (int i = 0; i < 2; ++i) { cudaFree(g.keys[i]); cudaFree(g.vals[i]); }
-    cudaFree(g.seg_start); cudaFree(g.block_counts); cudaFree(g.hist);
+    cudaFree(g.seg_start); cudaFree(g.block_counts); cudaFree(g.hist); cudaFree(g.sorted_xyz);
     const size_t cap = n + n / 8 + 1024;
+    CK(cudaMalloc(&g.sorted_xyz, cap * 3 * sizeof(double)));
     for (int i = 0; i < 2; ++i) { CK(cudaMalloc(&g.keys[i], cap * 4)); CK(cudaMalloc(&g.vals[i], cap * 4)); }
     CK(cudaMalloc(&g.seg_start, (cap + 1) * 4));
     const size_t nb = (cap + RS_TILE - 1) / RS_TILE + 1;
@@ -30,7 +36,8 @@ static int ensure_capacity(DeviceGrid& g, size_t n) {
     g.pts_alloc = cap;
     // voxel arrays: V <= n
     cudaFree(g.recs); cudaFree(g.c_key); cudaFree(g.c_n); cudaFree(g.c_mean); cudaFree(g.c_cov); cudaFree(g.c_icov);
-    cudaFree(g.c_evecs); cudaFree(g.c_evals);
+    cudaFree(g.c_evecs); cudaFree(g.c_evals); cudaFree(g.vox_sums);
+    CK(cudaMalloc(&g.vox_sums, cap * 72));
     CK(cudaMalloc(&g.recs, cap * sizeof(VoxRec)));
     CK(cudaMalloc(&g.c_key, cap * 4));
     CK(cudaMalloc(&g.c_n, cap * 4));
@@ -46,13 +53,36 @@ static int ensure_capacity(DeviceGrid& g, size_t n) {
 
 void free_device_grid(DeviceGrid& g) {
   for (int i = 0; i < 2; ++i) { cudaFree(g.keys[i]); cudaFree(g.vals[i]); }
-  cudaFree(g.seg_start); cudaFree(g.block_counts); cudaFree(g.hist);
+  cudaFree(g.seg_start); cudaFree(g.block_counts); cudaFree(g.hist); cudaFree(g.sorted_xyz); cudaFree(g.vox_sums); cudaFree(g.digit_totals); cudaFree(g.d_ticket);
+  if (g.h_slots) cudaFreeHost(const_cast<unsigned long long*>(g.h_slots));
   cudaFree(g.recs); cudaFree(g.table); cudaFree(g.c_key); cudaFree(g.c_n); cudaFree(g.c_mean); cudaFree(g.c_cov);
   cudaFree(g.c_icov); cudaFree(g.c_evecs); cudaFree(g.c_evals); cudaFree(g.d_bbox); cudaFree(g.d_counters);
   if (g.h_pinned) cudaFreeHost(g.h_pinned);
   const uint64_t keep = g.launches;
   g = DeviceGrid();
   g.launches = keep;
+}
+
+// Poll `count` self-validating host slots starting at `first` (see publish_slot); a stream query
+// every 4096 spins catches a failed kernel.
+static int wait_slots(DeviceGrid& g, int first, int count, unsigned long long key, cudaStream_t stream) {
+  unsigned int spins = 0;
+  for (int i = first + count - 1; i >= first; --i) {
+    for (;;) {
+      const unsigned long long w0 = g.h_slots[2 * i], w1 = g.h_slots[2 * i + 1];
+      if ((w0 ^ w1) == key) break;
+      if ((++spins & 4095u) == 0) {
+        const cudaError_t q = cudaStreamQuery(stream);
+        if (q != cudaSuccess && q != cudaErrorNotReady) return NDTB_ERR_CUDA;
+        if (q == cudaSuccess) {
+          const unsigned long long x0 = g.h_slots[2 * i], x1 = g.h_slots[2 * i + 1];
+          if ((x0 ^ x1) != key) return NDTB_ERR_CUDA;
+        }
+      }
+    }
+  }
+  __sync_synchronize();
+  return NDTB_OK;
 }
 
 int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resolution, int min_pts, double eig_mult, int flavour,
@@ -64,22 +94,20 @@ int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resoluti
   if (rc != NDTB_OK) return rc;
   const int ni = static_cast<int>(n);
 
-  // ---- k0: bounding box (pcl::getMinMax3D) ------------------------------------------------
+  // ---- k0: bounding box (pcl::getMinMax3D); the last block publishes it to pinned host slots -----------
   {
     int init[6];
-    const int big = 0x7f7fffff;  // ordered encoding of +FLT_MAX
-    init[0] = init[1] = init[2] = big;
-    init[3] = init[4] = init[5] = -big - 0;  // ordered encoding of -FLT_MAX is big ^ 0x7fffffff with sign: computed below
-    // -FLT_MAX bits = 0xff7fffff (negative int) -> ordered = bits ^ 0x7fffffff
-    const int neg_bits = static_cast<int>(0xff7fffffu);
-    init[3] = init[4] = init[5] = neg_bits ^ 0x7fffffff;
+    init[0] = init[1] = init[2] = 0x7f7fffff;                                     // ordered encoding of +FLT_MAX
+    init[3] = init[4] = init[5] = static_cast<int>(0xff7fffffu) ^ 0x7fffffff;     // ordered encoding of -FLT_MAX
     std::memcpy(g.h_pinned, init, sizeof(init));
     CK(cudaMemcpyAsync(g.d_bbox, g.h_pinned, sizeof(init), cudaMemcpyHostToDevice, stream));
-    const int threads = 256;
-    const int blocks = std::min((ni + threads - 1) / threads, 148 * 8);
-    bbox_kernel<<<blocks, threads, 0, stream>>>(d_pts, ni, is_dense, g.d_bbox);
-    CK(cudaMemcpyAsync(g.h_pinned, g.d_bbox, 6 * sizeof(int), cudaMemcpyDeviceToHost, stream));
-    CK(cudaStreamSynchronize(stream));
+    const int blocks = std::min((ni + BBOX_THREADS - 1) / BBOX_THREADS, 148 * 4);
+    const unsigned long long key = 0x9E3779B97F4A7C15ull * (++g.slot_seq) | 1ull;
+    bbox_kernel<<<blocks, BBOX_THREADS, 0, stream>>>(d_pts, ni, is_dense, g.d_bbox, g.d_ticket, g.h_slots, key);
+    CK(cudaGetLastError());
+    int rc2 = wait_slots(g, 0, 6, key, stream);
+    if (rc2 != NDTB_OK) return rc2;
+    for (int a = 0; a < 6; ++a) g.h_pinned[a] = static_cast<int>(static_cast<unsigned int>(g.h_slots[2 * a]));
   }
   float min_p[3], max_p[3];
   for (int a = 0; a < 3; ++a) { min_p[a] = ordered_to_float_bits(g.h_pinned[a]); max_p[a] = ordered_to_float_bits(g.h_pinned[3 + a]); }
@@ -122,35 +150,36 @@ int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resoluti
   }
   CK(cudaMemsetAsync(g.d_counters, 0, 4 * sizeof(unsigned int), stream));
 
-  // ---- k1: keys ------------------------------------------------------------------------------
-  voxel_key_kernel<<<(ni + 255) / 256, 256, 0, stream>>>(d_pts, ni, m, is_dense, g.keys[0], g.vals[0], g.d_counters);
-
-  // ---- k2: stable LSD radix sort over the significant bits of the key -------------------------
+  // ---- k1 + k2: keys (fused into the first histogram) and the stable LSD radix sort over the significant key bits
   int bits = 1;
   while (bits < 32 && (static_cast<uint64_t>(m.total_cells) >> bits) != 0) ++bits;  // key <= total_cells
   const int passes = (bits + 7) / 8;
   const int nb = (ni + RS_TILE - 1) / RS_TILE;
   int cur = 0;
   for (int p = 0; p < passes; ++p) {
-    radix_hist_kernel<<<nb, RS_THREADS, 0, stream>>>(g.keys[cur], ni, 8 * p, g.hist, nb);
-    scan_u32_kernel<<<1, 1024, 0, stream>>>(g.hist, 256 * nb, nullptr);
-    radix_scatter_kernel<<<nb, RS_THREADS, 0, stream>>>(g.keys[cur], g.vals[cur], g.keys[cur ^ 1], g.vals[cur ^ 1], ni, 8 * p, g.hist, nb);
+    if (p == 0) radix_hist_kernel<true><<<nb, RS_THREADS, 0, stream>>>(d_pts, m, is_dense, g.keys[0], ni, 0, g.hist, nb, g.d_counters);
+    else radix_hist_kernel<false><<<nb, RS_THREADS, 0, stream>>>(nullptr, m, is_dense, g.keys[cur], ni, 8 * p, g.hist, nb, g.d_counters);
+    radix_scan_kernel<<<256, 256, 0, stream>>>(g.hist, nb, g.digit_totals);
+    if (p == 0) radix_scatter_kernel<true><<<nb, RS_THREADS, 0, stream>>>(g.keys[0], nullptr, g.keys[1], g.vals[1], ni, 0, g.hist, nb, g.digit_totals);
+    else radix_scatter_kernel<false><<<nb, RS_THREADS, 0, stream>>>(g.keys[cur], g.vals[cur], g.keys[cur ^ 1], g.vals[cur ^ 1], ni, 8 * p, g.hist, nb, g.digit_totals);
     cur ^= 1;
   }
 
-  // ---- k3: segments -> voxel numbering in ascending linear index ------------------------------
+  // ---- k3: segments -> voxel numbering in ascending linear index; points gathered into sorted order -----
   const int sb = (ni + SEG_TILE - 1) / SEG_TILE;
   seg_count_kernel<<<sb, SEG_THREADS, 0, stream>>>(g.keys[cur], ni, m.total_cells, g.block_counts);
-  scan_u32_kernel<<<1, 1024, 0, stream>>>(g.block_counts, sb, g.d_counters + 1);
+  scan_small_kernel<<<1, 1024, 0, stream>>>(g.block_counts, sb, g.d_counters + 1);
   seg_write_kernel<<<sb, SEG_THREADS, 0, stream>>>(g.keys[cur], ni, m.total_cells, g.block_counts, g.seg_start, g.c_key);
+  gather_points_kernel<<<(ni + 255) / 256, 256, 0, stream>>>(d_pts, g.vals[cur], ni, g.sorted_xyz);
 
-  // ---- k4: per-voxel statistics + hash insert --------------------------------------------------
-  launch_voxel_finalize(g, d_pts, g.vals[cur], static_cast<uint32_t>(ni), stream);
-
-  g.launches += 2 + 3 * static_cast<uint64_t>(passes) + 3 + 1;  // bbox, keys, radix passes, segments, finalize
-  CK(cudaMemcpyAsync(g.h_pinned, g.d_counters, 4 * sizeof(unsigned int), cudaMemcpyDeviceToHost, stream));
-  CK(cudaStreamSynchronize(stream));
+  // ---- k4: per-voxel statistics + hash insert; its last block publishes the counters to the host ---------
+  const unsigned long long key = 0x9E3779B97F4A7C15ull * (++g.slot_seq) | 1ull;
+  launch_voxel_finalize(g, static_cast<uint32_t>(ni), key, stream);
+  g.launches += 1 + 3 * static_cast<uint64_t>(passes) + 4 + 2;  // bbox, radix passes, segments + gather, sums + finalize
   CK(cudaGetLastError());
+  rc = wait_slots(g, 8, 3, key, stream);
+  if (rc != NDTB_OK) return rc;
+  for (int a = 0; a < 3; ++a) g.h_pinned[a] = static_cast<int>(static_cast<unsigned int>(g.h_slots[2 * (8 + a)]));
   g.V = static_cast<uint32_t>(g.h_pinned[1]);
   g.n_valid = static_cast<uint32_t>(g.h_pinned[2]);
   g.built = true;

@@ -7,6 +7,7 @@
 //       svn flavour     voxel_grid_covariance_impl.hpp:270-343
 // and the voxel is inserted into the open-addressing hash (atomicCAS linear probing).
 #include "build_api.cuh"
+#include <algorithm>
 
 namespace ndtb {
 
@@ -132,27 +133,149 @@ __device__ __forceinline__ void hash_insert(HashSlot* table, uint32_t mask, uint
   }
 }
 
-__global__ void __launch_bounds__(128) voxel_finalize_kernel(const float4* __restrict__ pts, const uint32_t* __restrict__ sorted_vals,
-                                                             const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ vox_key,
-                                                             const unsigned int* __restrict__ counters, uint32_t n_points, GridMeta m,
-                                                             VoxRec* __restrict__ recs, HashSlot* __restrict__ table, int32_t* __restrict__ c_n,
-                                                             double* __restrict__ c_mean, double* __restrict__ c_cov, double* __restrict__ c_icov,
-                                                             double* __restrict__ c_evecs, double* __restrict__ c_evals,
-                                                             unsigned int* __restrict__ n_valid_out) {
-  const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+constexpr int FIN_BATCH = 4;   // points per software-pipeline stage (light voxels)
+constexpr int FIN_HEAVY = 48;  // voxels with more points are summed by the whole warp
+
+// Everything per voxel after the sums.  `n`, sums in; writes the cold arrays, the hot record and the hash slot.
+__device__ void finalize_voxel(uint32_t v, int n, double sx, double sy, double sz, double sxx, double sxy, double sxz, double syy, double syz, double szz,
+                               const uint32_t* __restrict__ vox_key, const GridMeta& m, VoxRec* __restrict__ recs, HashSlot* __restrict__ table,
+                               int32_t* __restrict__ c_n, double* __restrict__ c_mean, double* __restrict__ c_cov, double* __restrict__ c_icov,
+                               double* __restrict__ c_evecs, double* __restrict__ c_evals, unsigned int* __restrict__ n_valid_out);
+
+// k4a: per-voxel sums (Sum x, Sum x x^T in input order) -> vox_sums[v][0..8], one resident wave.
+__global__ void __launch_bounds__(128) voxel_sum_kernel(const double* __restrict__ sorted_xyz, const uint32_t* __restrict__ seg_start,
+                                                        const unsigned int* __restrict__ counters, uint32_t n_points,
+                                                        double* __restrict__ vox_sums) {
+  __shared__ double s_prod[4][32][9];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const uint32_t V = counters[1];
-  if (v >= V) return;
   const uint32_t n_valid_pts = n_points - counters[0];
-  const uint32_t lo = seg_start[v];
-  const uint32_t hi = (v + 1 < V) ? seg_start[v + 1] : n_valid_pts;
-  double sx = 0, sy = 0, sz = 0, sxx = 0, sxy = 0, sxz = 0, syy = 0, syz = 0, szz = 0;
-  for (uint32_t i = lo; i < hi; ++i) {
-    const float4 p = __ldg(pts + __ldg(sorted_vals + i));
-    const double x = p.x, y = p.y, z = p.z;
-    sx += x; sy += y; sz += z;
-    sxx += x * x; sxy += x * y; sxz += x * z; syy += y * y; syz += y * z; szz += z * z;
+  // Voxels are dealt to threads through a multiplicative permutation of [0, Vr), Vr = V rounded up to a warp:
+  // neighbouring voxels (a wall is a run of equally heavy voxels) land in different warps, so no warp collects
+  // all the long segments.  2654435761 is prime, hence coprime with Vr: t -> t * P mod Vr is a bijection.
+  const uint32_t Vr = (V + 31u) & ~31u;
+  for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < Vr; t += gridDim.x * blockDim.x) {  // warp-uniform trip count
+    const uint32_t v = static_cast<uint32_t>((static_cast<unsigned long long>(t) * 2654435761ull) % Vr);
+    const bool has = v < V;
+    const uint32_t lo = has ? seg_start[v] : 0u;
+    const uint32_t hi = has ? ((v + 1 < V) ? seg_start[v + 1] : n_valid_pts) : 0u;
+    const int n = static_cast<int>(hi - lo);
+    const bool heavy = n > FIN_HEAVY;
+    double sum[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};  // sx sy sz sxx sxy sxz syy syz szz
+    if (has && !heavy) {
+      // Light voxel: this lane adds its points IN INPUT ORDER (stable sort; already widened to FP64 by the
+      // gather kernel), loads software-pipelined one batch ahead of the sequential FP64 chains.
+      const double* q = sorted_xyz + 3 * static_cast<size_t>(lo);
+      double cur[3 * FIN_BATCH], nxt[3 * FIN_BATCH];
+      const int full = n / FIN_BATCH;
+      if (full > 0) {
+#pragma unroll
+        for (int u = 0; u < 3 * FIN_BATCH; ++u) cur[u] = __ldg(q + u);
+      }
+      for (int bt = 0; bt < full; ++bt) {
+        if (bt + 1 < full) {
+#pragma unroll
+          for (int u = 0; u < 3 * FIN_BATCH; ++u) nxt[u] = __ldg(q + 3 * FIN_BATCH * (bt + 1) + u);
+        }
+#pragma unroll
+        for (int u = 0; u < FIN_BATCH; ++u) {
+          const double x = cur[3 * u], y = cur[3 * u + 1], z = cur[3 * u + 2];
+          sum[0] += x; sum[1] += y; sum[2] += z;
+          sum[3] += x * x; sum[4] += x * y; sum[5] += x * z; sum[6] += y * y; sum[7] += y * z; sum[8] += z * z;
+        }
+#pragma unroll
+        for (int u = 0; u < 3 * FIN_BATCH; ++u) cur[u] = nxt[u];
+      }
+      for (int i = full * FIN_BATCH; i < n; ++i) {
+        const double x = __ldg(q + 3 * i), y = __ldg(q + 3 * i + 1), z = __ldg(q + 3 * i + 2);
+        sum[0] += x; sum[1] += y; sum[2] += z;
+        sum[3] += x * x; sum[4] += x * y; sum[5] += x * z; sum[6] += y * y; sum[7] += y * z; sum[8] += z * z;
+      }
+    }
+    // Heavy voxels: the whole warp takes them one at a time.  32 lanes load 32 points (coalesced) and form the
+    // nine products; lane c < 9 then runs chain c over those 32 points in order, so the nine serial FP64 chains
+    // advance in the same instruction and a point costs one dependent DADD instead of nine.
+    unsigned int hm = __ballot_sync(0xffffffffu, heavy);
+    while (hm) {
+      const int o = __ffs(hm) - 1;
+      hm &= hm - 1;
+      const uint32_t wlo = __shfl_sync(0xffffffffu, lo, o);
+      const int wn = __shfl_sync(0xffffffffu, n, o);
+      const double* q = sorted_xyz + 3 * static_cast<size_t>(wlo);
+      double acc = 0.0;
+      double x = 0, y = 0, z = 0;
+      if (lane < wn) { x = __ldg(q + 3 * lane); y = __ldg(q + 3 * lane + 1); z = __ldg(q + 3 * lane + 2); }
+      for (int base = 0; base < wn; base += 32) {
+        double* pr = s_prod[w][lane];
+        pr[0] = x; pr[1] = y; pr[2] = z; pr[3] = x * x; pr[4] = x * y; pr[5] = x * z; pr[6] = y * y; pr[7] = y * z; pr[8] = z * z;
+        const int nxt_i = base + 32 + lane;
+        if (nxt_i < wn) { x = __ldg(q + 3 * nxt_i); y = __ldg(q + 3 * nxt_i + 1); z = __ldg(q + 3 * nxt_i + 2); }  // next tile in flight
+        __syncwarp();
+        const int cnt = min(32, wn - base);
+        if (lane < 9) {
+          int k = 0;
+          for (; k + 8 <= cnt; k += 8) {
+            double t8[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) t8[u] = s_prod[w][k + u][lane];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) acc += t8[u];
+          }
+          for (; k < cnt; ++k) acc += s_prod[w][k][lane];
+        }
+        __syncwarp();
+      }
+#pragma unroll
+      for (int c = 0; c < 9; ++c) {
+        const double tv = __shfl_sync(0xffffffffu, acc, c);
+        if (lane == o) sum[c] = tv;
+      }
+    }
+    if (has) {
+      double* o = vox_sums + 9 * static_cast<size_t>(v);
+#pragma unroll
+      for (int c = 0; c < 9; ++c) o[c] = sum[c];
+    }
   }
-  int n = static_cast<int>(hi - lo);
+}
+
+// k4b: one thread per voxel: mean / covariance / eigen-inflation / inverse, the hot record and the hash insert.
+__global__ void __launch_bounds__(128, 5) voxel_finalize_kernel(const double* __restrict__ vox_sums, const uint32_t* __restrict__ seg_start,
+                                                                const uint32_t* __restrict__ vox_key, unsigned int* __restrict__ counters,
+                                                                uint32_t n_points, GridMeta m, VoxRec* __restrict__ recs, HashSlot* __restrict__ table,
+                                                                int32_t* __restrict__ c_n, double* __restrict__ c_mean, double* __restrict__ c_cov,
+                                                                double* __restrict__ c_icov, double* __restrict__ c_evecs, double* __restrict__ c_evals,
+                                                                unsigned int* __restrict__ ticket, volatile unsigned long long* host_slots,
+                                                                unsigned long long publish_key) {
+  __shared__ bool s_last;
+  const uint32_t V = counters[1];
+  const uint32_t n_valid_pts = n_points - counters[0];
+  for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < V; v += gridDim.x * blockDim.x) {
+    const uint32_t lo = seg_start[v];
+    const uint32_t hi = (v + 1 < V) ? seg_start[v + 1] : n_valid_pts;
+    const double* q = vox_sums + 9 * static_cast<size_t>(v);
+    finalize_voxel(v, static_cast<int>(hi - lo), q[0], q[1], q[2], q[3], q[4], q[5], q[6], q[7], q[8], vox_key, m, recs, table, c_n, c_mean, c_cov,
+                   c_icov, c_evecs, c_evals, counters + 2);
+  }
+  // ---- last block done: publish {skipped, V, n_valid} to the host slots 8..10 ----------------------------
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int tk;
+    asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(tk) : "l"(ticket) : "memory");
+    s_last = (tk == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (s_last && threadIdx.x < 3) {
+    const unsigned int c = atomicAdd(counters + threadIdx.x, 0u);
+    publish_slot(host_slots, 8 + threadIdx.x, static_cast<unsigned long long>(c), publish_key);
+    if (threadIdx.x == 0) *ticket = 0;
+  }
+}
+
+__device__ void finalize_voxel(uint32_t v, int n, double sx, double sy, double sz, double sxx, double sxy, double sxz, double syy, double syz, double szz,
+                               const uint32_t* __restrict__ vox_key, const GridMeta& m, VoxRec* __restrict__ recs, HashSlot* __restrict__ table,
+                               int32_t* __restrict__ c_n, double* __restrict__ c_mean, double* __restrict__ c_cov, double* __restrict__ c_icov,
+                               double* __restrict__ c_evecs, double* __restrict__ c_evals, unsigned int* __restrict__ n_valid_out) {
   const double dn = static_cast<double>(n);
   double mean[3] = {sx, sy, sz};
   double cov[9] = {sxx, sxy, sxz, sxy, syy, syz, sxz, syz, szz};
@@ -259,13 +382,13 @@ __global__ void __launch_bounds__(128) voxel_finalize_kernel(const float4* __res
   }
 }
 
-void launch_voxel_finalize(const DeviceGrid& g, const float4* d_pts, const uint32_t* sorted_vals, uint32_t n_points_upper,
-                           cudaStream_t stream) {
+void launch_voxel_finalize(const DeviceGrid& g, uint32_t n_points_upper, unsigned long long publish_key, cudaStream_t stream) {
   const int threads = 128;
-  const int blocks = static_cast<int>((n_points_upper + threads - 1) / threads);
-  voxel_finalize_kernel<<<blocks, threads, 0, stream>>>(d_pts, sorted_vals, g.seg_start, g.c_key, g.d_counters, n_points_upper, g.meta,
-                                                        g.recs, g.table, g.c_n, g.c_mean, g.c_cov, g.c_icov, g.c_evecs, g.c_evals,
-                                                        g.d_counters + 2);
+  const int need = static_cast<int>((n_points_upper + threads - 1) / threads);
+  voxel_sum_kernel<<<std::min(need, 148 * 4), threads, 0, stream>>>(g.sorted_xyz, g.seg_start, g.d_counters, n_points_upper, g.vox_sums);
+  voxel_finalize_kernel<<<std::min(need, 148 * 5), threads, 0, stream>>>(g.vox_sums, g.seg_start, g.c_key, g.d_counters, n_points_upper, g.meta, g.recs,
+                                                                      g.table, g.c_n, g.c_mean, g.c_cov, g.c_icov, g.c_evecs, g.c_evals,
+                                                                      g.d_ticket + 1, g.h_slots, publish_key);
 }
 
 }  // namespace ndtb
