@@ -167,6 +167,10 @@ int ndtb_align_batch(ndtb_handle h, int n_scans, const float* const* xyz, const 
 /* CUDA-event time (ms) of the stages of the last set_target / align on the handle's stream. */
 int ndtb_get_timings(ndtb_handle h, float* build_ms, float* align_ms, float* eval_kernel_ms_total, int* eval_kernel_launches);
 int ndtb_get_stream(ndtb_handle h, void** cuda_stream);
+/* Per-kernel CUDA events around every derivative evaluation (eval_kernel_ms_total of ndtb_get_timings).
+ * On by default; switching them off removes two event records (several microseconds of stream time)
+ * from every Newton iteration -- eval_kernel_ms_total then stays 0. */
+int ndtb_set_profiling(ndtb_handle h, int per_kernel_events);
 /* Number of CUDA kernels this handle has launched since creation (bench.py's gpu_launches). */
 int ndtb_get_launch_count(ndtb_handle h, uint64_t* launches);
 

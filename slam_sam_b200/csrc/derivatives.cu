@@ -148,6 +148,93 @@ __device__ __forceinline__ void pclomp_terms(const PointTables& pt, const float 
   }
 }
 
+// Packed-FP32 version of pclomp_terms for sm_100a: the same IEEE round-to-nearest multiplies and adds in the
+// same association, with the multiplies issued two at a time as FMUL2 (__fmul2_rn), which removes a quarter of
+// the issue slots of the per-pair maths.  Element results are bit-identical to the scalar code.  The point tables come from a
+// PtSlot written in the PAIRED layout (see phase_a<..., PAIRED = true>):
+//   words 4,5: xj0 xj1 | 6..11: (xj2,xj5) (xj3,xj6) (xj4,xj7) | 12..15: (xh0,xh2) (xh1,xh3)
+//   16..21: (xh6,xh9) (xh7,xh10) (xh8,xh11) | 22,23: xh4 xh5 | 24..26: xh12 xh13 xh14
+__device__ __forceinline__ float2 bc2(float x) { return make_float2(x, x); }
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
+// The additions stay SCALAR on purpose: ptxas 12.9 contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even with
+// explicit .rn and --fmad=false (checked with cuobjdump), which would change the reference's two-rounding
+// arithmetic; scalar add.rn.f32 is never contracted.
+__device__ __forceinline__ float2 add2(float2 a, float2 b) { return make_float2(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y)); }
+// (a0*b0 + a1*b1) + a2*b2 on pairs: dot3's association
+__device__ __forceinline__ float2 dot3_2(float a0, float a1, float a2, float2 b0, float2 b1, float2 b2) {
+  return add2(add2(mul2(bc2(a0), b0), mul2(bc2(a1), b1)), mul2(bc2(a2), b2));
+}
+
+template <bool HESS>
+// Output: 22 PAIRS in the order the packed multiplies produce them (no register shuffling before the stores):
+//   tp[0] = (score, 0) | tp[1..3] = (g0,g1) (g2,g3) (g4,g5) | tp[4 + 3j + p] = (H(2p, j), H(2p+1, j)), j = 0..5, p = 0..2
+// pair_word_component() maps a word of this layout back to the RED_* index.
+__device__ __forceinline__ void pclomp_terms2(const float4* __restrict__ sp, const float x4[3], const float C[9], float d2f, double d1,
+                                              float2* __restrict__ tp) {
+  const float4 s1 = sp[1], s2 = sp[2];
+  const float xj0 = s1.x, xj1 = s1.y;
+  const float2 J25 = make_float2(s1.z, s1.w), J36 = make_float2(s2.x, s2.y), J47 = make_float2(s2.z, s2.w);
+  float xC[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) xC[c] = dot3(x4[0], x4[1], x4[2], C[c], C[3 + c], C[6 + c]);
+  const float q = dot3(x4[0], x4[1], x4[2], xC[0], xC[1], xC[2]);
+  float e = static_cast<float>(exp(static_cast<double>(-d2f * q * 0.5f)));
+  const float score_inc = static_cast<float>(-d1 * static_cast<double>(e));
+  e = d2f * e;
+  const bool reject = (e > 1 || e < 0 || e != e);
+  e = static_cast<float>(static_cast<double>(e) * d1);
+  if (reject) e = 0.0f;  // see pclomp_terms
+  // CJ = C4 * Jp, rows r, columns as pairs (0,1) (2,3) (4,5)
+  float2 cj[3][3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const float c0 = C[3 * r], c1 = C[3 * r + 1], c2 = C[3 * r + 2];
+    cj[r][0] = make_float2(c0, c1);
+    cj[r][1] = make_float2(c2, c1 * xj0 + c2 * xj1);
+    cj[r][2] = dot3_2(c0, c1, c2, J25, J36, J47);
+  }
+  float2 xcj[3];
+#pragma unroll
+  for (int p = 0; p < 3; ++p) xcj[p] = dot3_2(x4[0], x4[1], x4[2], cj[0][p], cj[1][p], cj[2][p]);
+  tp[0] = make_float2(reject ? 0.0f : score_inc, 0.0f);
+  const float2 e2 = bc2(e);
+#pragma unroll
+  for (int p = 0; p < 3; ++p) tp[1 + p] = mul2(e2, xcj[p]);
+  if (HESS) {
+    const float4 s3 = sp[3], s4 = sp[4], s5 = sp[5], s6 = sp[6];
+    const float2 hab = add2(mul2(bc2(xC[1]), make_float2(s3.x, s3.y)), mul2(bc2(xC[2]), make_float2(s3.z, s3.w)));  // (h_a, h_b)
+    const float2 hde = dot3_2(xC[0], xC[1], xC[2], make_float2(s4.x, s4.y), make_float2(s4.z, s4.w), make_float2(s5.x, s5.y));  // (h_d, h_e)
+    const float h_c = xC[1] * s5.z + xC[2] * s5.w;
+    const float h_f = dot3(xC[0], xC[1], xC[2], s6.x, s6.y, s6.z);
+    // xCH rows for i = 3,4,5 and columns j = 3,4,5: [a b c; b d e; c e f]
+    const float xch3[3] = {hab.x, hab.y, h_c};                                                          // row i = 3, j = 3..5
+    const float2 xch45[3] = {make_float2(hab.y, h_c), make_float2(hde.x, hde.y), make_float2(hde.y, h_f)};  // (row 4, row 5) for j = 3..5
+    const float2 nd2 = bc2(-d2f);
+    float2 ap[3];
+#pragma unroll
+    for (int p = 0; p < 3; ++p) ap[p] = mul2(nd2, xcj[p]);  // (-d2 * xCJ_i) for i = 2p, 2p+1
+    const float xjs[8] = {xj0, xj1, J25.x, J36.x, J47.x, J25.y, J36.y, J47.y};
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      const float xcjj = (j & 1) ? xcj[j >> 1].y : xcj[j >> 1].x;
+      const float2 xcjj2 = bc2(xcjj);
+#pragma unroll
+      for (int p = 0; p < 3; ++p) {
+        float2 jc;  // JCJ(j, i) for i = 2p, 2p+1
+        if (j < 3) jc = cj[j][p];
+        else if (j == 3) jc = add2(mul2(bc2(xjs[0]), cj[1][p]), mul2(bc2(xjs[1]), cj[2][p]));
+        else if (j == 4) jc = dot3_2(xjs[2], xjs[3], xjs[4], cj[0][p], cj[1][p], cj[2][p]);
+        else jc = dot3_2(xjs[5], xjs[6], xjs[7], cj[0][p], cj[1][p], cj[2][p]);
+        float2 v = mul2(ap[p], xcjj2);
+        if (j >= 3 && p == 1) v.y = v.y + xch3[j - 3];
+        if (j >= 3 && p == 2) v = add2(v, xch45[j - 3]);
+        v = add2(v, jc);
+        tp[4 + 3 * j + p] = mul2(e2, v);
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------ svn pair maths
 template <bool GN>
 __device__ __forceinline__ double pair_svn(const PointTables& pt, const double xr[3], const double Cd[9], double d1, double d2,
@@ -399,7 +486,7 @@ __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefe
 
 // Phase A for one chunk: lane `lane` handles point `idx` (if `have`), fills its slot, appends its pairs
 // to the warp's queue at `tail`; returns the number of pairs the warp appended.
-template <int FLAVOUR, int PROBES, bool HESS, bool GN>
+template <int FLAVOUR, int PROBES, bool HESS, bool GN, bool PAIRED = false>
 __device__ __forceinline__ int phase_a(const float4* __restrict__ src, int idx, bool have, int slot, int lane, int tail, const GridMeta& m,
                                        const VoxRec* __restrict__ recs, const HashSlot* __restrict__ table, const EvalState& st,
                                        PtSlot* __restrict__ s_pts, int* __restrict__ s_qrow, unsigned char* __restrict__ s_qslot,
@@ -447,17 +534,29 @@ __device__ __forceinline__ int phase_a(const float4* __restrict__ src, int idx, 
 #pragma unroll
         for (int r = 0; r < 8; ++r) xj[r] = dot3(st.jang[3 * r], st.jang[3 * r + 1], st.jang[3 * r + 2], p.x, p.y, p.z);
         sp[0] = make_float4(xt[0], xt[1], xt[2], 0.0f);  // .w = nearest_bits = 0
-        sp[1] = make_float4(xj[0], xj[1], xj[2], xj[3]);
-        sp[2] = make_float4(xj[4], xj[5], xj[6], xj[7]);
+        if (PAIRED) {  // layout of pclomp_terms2
+          sp[1] = make_float4(xj[0], xj[1], xj[2], xj[5]);
+          sp[2] = make_float4(xj[3], xj[6], xj[4], xj[7]);
+        } else {
+          sp[1] = make_float4(xj[0], xj[1], xj[2], xj[3]);
+          sp[2] = make_float4(xj[4], xj[5], xj[6], xj[7]);
+        }
         if (HESS && !(FLAVOUR == FLAVOUR_SVN && GN)) {
           float xh[16];
 #pragma unroll
           for (int r = 0; r < 15; ++r) xh[r] = dot3(st.hang[3 * r], st.hang[3 * r + 1], st.hang[3 * r + 2], p.x, p.y, p.z);
           xh[15] = 0.0f;
-          sp[3] = make_float4(xh[0], xh[1], xh[2], xh[3]);
-          sp[4] = make_float4(xh[4], xh[5], xh[6], xh[7]);
-          sp[5] = make_float4(xh[8], xh[9], xh[10], xh[11]);
-          sp[6] = make_float4(xh[12], xh[13], xh[14], xh[15]);
+          if (PAIRED) {
+            sp[3] = make_float4(xh[0], xh[2], xh[1], xh[3]);
+            sp[4] = make_float4(xh[6], xh[9], xh[7], xh[10]);
+            sp[5] = make_float4(xh[8], xh[11], xh[4], xh[5]);
+            sp[6] = make_float4(xh[12], xh[13], xh[14], xh[15]);
+          } else {
+            sp[3] = make_float4(xh[0], xh[1], xh[2], xh[3]);
+            sp[4] = make_float4(xh[4], xh[5], xh[6], xh[7]);
+            sp[5] = make_float4(xh[8], xh[9], xh[10], xh[11]);
+            sp[6] = make_float4(xh[12], xh[13], xh[14], xh[15]);
+          }
         }
         filled = true;
         found += nn > 0 ? 1.0 : 0.0;
@@ -625,20 +724,13 @@ __device__ __forceinline__ int owner_term(int p, int q, int i) { return 24 * p +
 template <bool HESS>
 __device__ __forceinline__ void pclomp_round(bool active, int slot, int row, PtSlot* __restrict__ s_pts, float* __restrict__ s_tr, int lane,
                                              const EvalState& st, const VoxRec* __restrict__ recs, float d2f, double* __restrict__ a) {
-  float t[44];
+  float2 tp[22];
   if (!active) {
 #pragma unroll
-    for (int i = 0; i < 44; ++i) t[i] = 0.0f;
+    for (int i = 0; i < 22; ++i) tp[i] = make_float2(0.0f, 0.0f);
   } else {
-    PointTables pt;
     const float4* sp = reinterpret_cast<const float4*>(s_pts + slot);
-    const float4 pa = sp[0], pb = sp[1], pc = sp[2];
-    pt.xj[0] = pb.x; pt.xj[1] = pb.y; pt.xj[2] = pb.z; pt.xj[3] = pb.w; pt.xj[4] = pc.x; pt.xj[5] = pc.y; pt.xj[6] = pc.z; pt.xj[7] = pc.w;
-    if (HESS) {
-      const float4 d = sp[3], e = sp[4], f = sp[5], g = sp[6];
-      pt.xh[0] = d.x; pt.xh[1] = d.y; pt.xh[2] = d.z; pt.xh[3] = d.w; pt.xh[4] = e.x; pt.xh[5] = e.y; pt.xh[6] = e.z; pt.xh[7] = e.w;
-      pt.xh[8] = f.x; pt.xh[9] = f.y; pt.xh[10] = f.z; pt.xh[11] = f.w; pt.xh[12] = g.x; pt.xh[13] = g.y; pt.xh[14] = g.z;
-    }
+    const float4 pa = sp[0];
     const uint4* rp = reinterpret_cast<const uint4*>(recs + row);
     const uint4 q0 = __ldg(rp), q1 = __ldg(rp + 1), q2 = __ldg(rp + 2), q3 = __ldg(rp + 3);
     const double m0 = __hiloint2double(q0.y, q0.x), m1 = __hiloint2double(q0.w, q0.z), m2 = __hiloint2double(q1.y, q1.x);
@@ -650,29 +742,39 @@ __device__ __forceinline__ void pclomp_round(bool active, int slot, int row, PtS
     x4[0] = static_cast<float>(static_cast<double>(pa.x) - m0);
     x4[1] = static_cast<float>(static_cast<double>(pa.y) - m1);
     x4[2] = static_cast<float>(static_cast<double>(pa.z) - m2);
-    pclomp_terms<HESS>(pt, x4, C, d2f, st.d1, t);
-    t[43] = 0.0f;
+    pclomp_terms2<HESS>(sp, x4, C, d2f, st.d1, tp);
     if (!HESS) {
 #pragma unroll
-      for (int i = 7; i < 43; ++i) t[i] = 0.0f;
+      for (int i = 4; i < 22; ++i) tp[i] = make_float2(0.0f, 0.0f);
     }
-    if (t[0] > 0.0f) atomicMax(&s_pts[slot].nearest_bits, __float_as_int(t[0]));
+    if (tp[0].x > 0.0f) atomicMax(&s_pts[slot].nearest_bits, __float_as_int(tp[0].x));
   }
   const int q = lane >> 3, g = lane & 7;
-  float4* my = reinterpret_cast<float4*>(s_tr + lane * TR_STRIDE);
+  float2* my = reinterpret_cast<float2*>(s_tr + lane * TR_STRIDE);
 #pragma unroll
-  for (int i = 0; i < 6; ++i) my[i] = make_float4(t[4 * i], t[4 * i + 1], t[4 * i + 2], t[4 * i + 3]);
+  for (int i = 0; i < 12; ++i) my[i] = tp[i];
   __syncwarp();
   transposed_add(s_tr, q, g, a);
   __syncwarp();
   if (HESS) {
 #pragma unroll
-    for (int i = 0; i < 5; ++i) my[i] = make_float4(t[24 + 4 * i], t[25 + 4 * i], t[26 + 4 * i], t[27 + 4 * i]);
-    my[5] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    for (int i = 0; i < 10; ++i) my[i] = tp[12 + i];
+    my[10] = make_float2(0.0f, 0.0f);
+    my[11] = make_float2(0.0f, 0.0f);
     __syncwarp();
     transposed_add(s_tr, q, g, a + 6);
     __syncwarp();
   }
+}
+
+// RED_* index of word `w` (0..47) of the pair layout of pclomp_terms2, or -1 for padding.
+__device__ __forceinline__ int pair_word_component(int w) {
+  const int P = w >> 1, half = w & 1;
+  if (P == 0) return half ? -1 : RED_SCORE;
+  if (P < 4) return RED_G + 2 * (P - 1) + half;
+  if (P >= 22) return -1;
+  const int hp = P - 4, j = hp / 3, pp = hp % 3;
+  return RED_H + 6 * (2 * pp + half) + j;
 }
 
 template <int PROBES, bool HESS>
@@ -713,7 +815,7 @@ __global__ void __launch_bounds__(PCL_THREADS, 1) eval_kernel_pclomp(const float
     const bool have = (k < my_groups) && (idx < n);
     const int slot = (chunk & 1) * 32 + lane;
     nearest += static_cast<double>(__int_as_float(s_pts[slot].nearest_bits));  // retire the slot's previous occupant
-    const int total = phase_a<FLAVOUR_PCLOMP, PROBES, HESS, false>(src, idx, have, slot, lane, tail, m, recs, table, st, s_pts, s_qrow, s_qslot,
+    const int total = phase_a<FLAVOUR_PCLOMP, PROBES, HESS, false, true>(src, idx, have, slot, lane, tail, m, recs, table, st, s_pts, s_qrow, s_qslot,
                                                                    found, count);
     const int must = tail;
     tail += total;
@@ -753,8 +855,9 @@ __global__ void __launch_bounds__(PCL_THREADS, 1) eval_kernel_pclomp(const float
     const int q = lane >> 3;
 #pragma unroll
     for (int i = 0; i < 6; ++i) {
-      sh.red[w][owner_term(0, q, i)] = a[i];
-      if (owner_term(1, q, i) < 43) sh.red[w][owner_term(1, q, i)] = a[6 + i];
+      const int c0 = pair_word_component(owner_term(0, q, i)), c1 = pair_word_component(owner_term(1, q, i));
+      if (c0 >= 0) sh.red[w][c0] = a[i];
+      if (c1 >= 0) sh.red[w][c1] = a[6 + i];
     }
   }
   if (lane == 0) { sh.red[w][RED_NEAREST] = nearest; sh.red[w][RED_FOUND] = found; sh.red[w][RED_COUNT] = count; }

@@ -28,6 +28,7 @@ struct ndtb_handle_s {
   unsigned int flag_seq = 0;
   std::vector<cudaEvent_t> ev_pool;     // per-evaluation event pairs, resolved after the loop (no per-iteration sync)
   size_t ev_used = 0;
+  bool kernel_events = true;            // ndtb_set_profiling
 
   bool has_reg_pose = false;
   float reg_translation[3] = {0, 0, 0};

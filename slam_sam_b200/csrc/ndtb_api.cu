@@ -122,13 +122,16 @@ static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool
   fill_state(h, 0, p, T16, 10e-5, false);
   const int n_probe = (h->params.search_method == NDTB_DIRECT1) ? 1 : 7;
   // event pair from the pool: elapsed times are resolved by resolve_eval_events() after the loop
-  if (h->ev_used + 2 > h->ev_pool.size()) {
-    for (int i = 0; i < 2; ++i) { cudaEvent_t e; CKH(cudaEventCreate(&e)); h->ev_pool.push_back(e); }
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (h->kernel_events) {
+    if (h->ev_used + 2 > h->ev_pool.size()) {
+      for (int i = 0; i < 2; ++i) { cudaEvent_t e; CKH(cudaEventCreate(&e)); h->ev_pool.push_back(e); }
+    }
+    e0 = h->ev_pool[h->ev_used]; e1 = h->ev_pool[h->ev_used + 1];
+    h->ev_used += 2;
   }
-  cudaEvent_t e0 = h->ev_pool[h->ev_used], e1 = h->ev_pool[h->ev_used + 1];
-  h->ev_used += 2;
   const unsigned long long key = 0x9E3779B97F4A7C15ull * static_cast<unsigned long long>(++h->flag_seq) | 1ull;
-  cudaEventRecord(e0, h->stream);
+  if (e0) cudaEventRecord(e0, h->stream);
   static unsigned long long* d_dbg = nullptr;  // development aid: NDTB_DEBUG_TIMING=1 prints in-kernel globaltimer stamps
   static const bool dbg_on = getenv("NDTB_DEBUG_TIMING") != nullptr;
   if (dbg_on && !d_dbg) { cudaMalloc(&d_dbg, 8 * 148 * sizeof(unsigned long long)); }
@@ -137,7 +140,7 @@ static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool
   // pinned host memory, and this thread polls them instead of synchronising the stream
   CKH(launch_eval_pclomp(n_probe, compute_hessian, h->d_source, n, h->grid.meta, h->grid.recs, h->grid.table, h->h_states[0], h->eval,
                          h->h_results, key, h->stream, dbg_on ? d_dbg : nullptr));
-  cudaEventRecord(e1, h->stream);
+  if (e1) cudaEventRecord(e1, h->stream);
   double rbuf[RED_N];
   {
     volatile unsigned long long* slots = reinterpret_cast<volatile unsigned long long*>(h->h_results);
@@ -516,6 +519,12 @@ int ndtb_get_timings(ndtb_handle h, float* build_ms, float* align_ms, float* eva
 int ndtb_get_launch_count(ndtb_handle h, uint64_t* launches) {
   if (!h || !launches) return NDTB_ERR_INVALID;
   *launches = h->launches + h->grid.launches;
+  return NDTB_OK;
+}
+
+int ndtb_set_profiling(ndtb_handle h, int per_kernel_events) {
+  if (!h) return NDTB_ERR_INVALID;
+  h->kernel_events = per_kernel_events != 0;
   return NDTB_OK;
 }
 

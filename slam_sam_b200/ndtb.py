@@ -51,7 +51,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "nd
            "ndtb_compute_derivatives", "ndtb_align", "ndtb_get_trace", "ndtb_calculate_scores", "ndtb_get_voxel_count", "ndtb_get_voxels",
            "ndtb_get_last_hits", "ndtb_svn_default_params", "ndtb_svn_set_params", "ndtb_svn_particle_derivatives", "ndtb_svn_stage2",
            "ndtb_svn_step", "ndtb_svn_align", "ndtb_svn_stage1_local", "ndtb_svn_finish_step", "ndtb_align_batch", "ndtb_get_timings",
-           "ndtb_get_stream", "ndtb_get_launch_count"]
+           "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_set_profiling"]
 
 _LIB = None
 
@@ -102,6 +102,7 @@ def lib():
         L.ndtb_get_timings.argtypes = [H, c_f, c_f, c_f, c_i]
         L.ndtb_get_stream.argtypes = [H, C.POINTER(C.c_void_p)]
         L.ndtb_get_launch_count.argtypes = [H, C.POINTER(C.c_uint64)]
+        L.ndtb_set_profiling.argtypes = [H, C.c_int]
         _LIB = L
     return _LIB
 
@@ -248,6 +249,9 @@ class Handle:
         n = C.c_uint64()
         self.L.ndtb_get_launch_count(self.h, C.byref(n))
         return n.value
+
+    def set_profiling(self, on):
+        self.check(self.L.ndtb_set_profiling(self.h, int(bool(on))))
 
     def stream_ptr(self):
         p = C.c_void_p()

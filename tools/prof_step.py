@@ -13,6 +13,8 @@ scan = synth.ouster_scan(scene, pose, seed=100)
 guess = (pose @ synth.pose_matrix((0.15, -0.1, 0.02), np.deg2rad((0.4, -0.3, 0.8)))).astype(np.float32)
 h = ndtb.Handle(0)
 h.set_params(resolution=1.0, max_iterations=35, trans_epsilon=0.01, step_size=0.1, search_method=ndtb.DIRECT7)
+import os as _os
+h.set_profiling(_os.environ.get("NDTB_EVENTS", "1") == "1")
 for rep in range(reps):
     assert h.set_target(tgt) == 0 and h.set_source(scan) == 0
     r = h.align(guess, capacity=0)
