@@ -1,5 +1,6 @@
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests -m gpu -x -q > gpurun_out/r1r_pytest.log 2>&1; tail -3 gpurun_out/r1r_pytest.log
-python tools/eval_scaling.py 2>&1 | grep "^n="
-python tools/prof_eval_big.py 8 > gpurun_out/r1r_plain.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:eval_kernel_pclomp -s 3 -c 1 -o gpurun_out/r1r_eval python tools/prof_eval_big.py 8 > gpurun_out/r1r_ncu.log 2>&1
+python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/r1s_bench_small.json 2> gpurun_out/r1s_bench_small.err &&
+ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/r1s_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/r1s_ncu1.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:eval_kernel_pclomp -s 60 -c 3 -o gpurun_out/r1s_eval python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/r1s_ncu2.log 2>&1
+cat gpurun_out/r1s_bench_small.json; tail -2 gpurun_out/r1s_bench_small.err
+python bench.py --steps 20 --warmup 3 > gpurun_out/r1s_bench.json 2> gpurun_out/r1s_bench.err; cat gpurun_out/r1s_bench.json; tail -3 gpurun_out/r1s_bench.err
