@@ -259,6 +259,98 @@ def run_gpu(args, rank, world, local_rank):
     return line
 
 
+def run_gpu_svn(args, rank, world, local_rank):
+    """configs[2]: SVN-NDT, K = 100 particles, 131072-pt scan pair; particles sharded over the ranks (strong scaling),
+    one all-reduce of K x 43 doubles per iteration.  One step = one full align(source, prior)."""
+    import torch
+    import torch.distributed as dist
+
+    from slam_sam_b200 import distributed as D
+    from slam_sam_b200 import ndtb, synth
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
+    K = 100
+    scene = synth.Scene()
+    A = synth.trajectory_pose(40.0)
+    tgt = synth.ouster_scan(scene, A, seed=1)
+    pool = []
+    for i in range(4):
+        B = A @ synth.pose_matrix((0.5 - 0.1 * i, 0.1, 0.02), np.deg2rad((0.5, 0.3, 2.0 - 0.3 * i)))
+        pool.append((synth.ouster_scan(scene, B, seed=2 + i), np.linalg.inv(A) @ B))
+    h = ndtb.Handle(local_rank)
+    h.set_params(grid_flavour=ndtb.FLAVOUR_SVN, resolution=RESOLUTION, min_points_per_voxel=3, search_method=ndtb.DIRECT7)
+    h.set_svn_params(particle_count=K, max_iterations=50, kernel_bandwidth=1.0, step_size=1.0, stop_threshold=1e-4, use_gauss_newton=1)
+    assert h.set_target(tgt) == 0
+    p_scans = [torch.from_numpy(s).pin_memory() for s, _ in pool]
+    d_scans = [torch.from_numpy(s).cuda() for s, _ in pool]
+    rng = np.random.Generator(np.random.PCG64(7))
+    prior = np.eye(4)
+    P0 = np.stack([prior @ synth.pose_matrix(rng.normal(0, 0.05, 3), rng.normal(0, 0.01, 3)) for _ in range(K)])  # sigmas of svn_ndt_impl.hpp:710
+    stream = torch.cuda.ExternalStream(h.stream_ptr(), device=local_rank)
+
+    def step(i, resident):
+        k = i % len(pool)
+        if resident:
+            assert h.set_source_device(d_scans[k].data_ptr(), N_SCAN) == 0
+        else:
+            assert h.L.ndtb_set_source(h.h, p_scans[k].data_ptr(), N_SCAN, 16) == 0
+        mean, P, it, conv = D.svn_align(h, prior, P0, rank, world, 50, 1e-4, local_rank)
+        return mean, it, conv, float(np.abs(mean[:3, 3] - pool[k][1][:3, 3]).max())
+
+    def timed(resident, steps, warmup):
+        for i in range(warmup):
+            step(i, resident)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        l0 = h.launch_count(); t0 = h.timings()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        iters = 0; err = 0.0
+        e0.record(stream)
+        for i in range(steps):
+            _, it, conv, er = step(warmup + i, resident)
+            iters += it; err = max(err, er)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t1 = h.timings()
+        return e0.elapsed_time(e1), dict(iters=iters, err=err, launches=h.launch_count() - l0, eval_ms=t1["eval_ms_total"] - t0["eval_ms_total"],
+                                         hits=h.last_hits()[0])
+
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    steps = max(1, min(args.steps, 10))
+    total_ms, st = timed(True, steps, min(args.warmup, 3))
+    e2e_ms, st2 = timed(False, steps, 1)
+    clk = clocks.stop()
+    total_ms = D.max_over_ranks(total_ms, local_rank); e2e_ms = D.max_over_ranks(e2e_ms, local_rank)
+    launches = int(D.sum_over_ranks(st["launches"], local_rank))
+    if world > 1:
+        dist.barrier(); dist.destroy_process_group()
+    if rank != 0:
+        return None
+    k_local = len(range(0, K, world))
+    b_eval = k_local * N_SCAN * (16 + 8 * 7 + 96 * st["hits"])   # FP64 records (mean 3 + icov 9 doubles) in the svn kernel
+    t_eval = st["eval_ms"] / max(st["iters"], 1) * 1e-3
+    peak, peak_src = measured_peak()
+    return {"metric": "NDT align scans/sec @131k pts (1/2/4/8 B200) + % gather-BW roofline vs CPU OMP", "value": steps / (total_ms * 1e-3), "unit": "scans/s",
+            "n_gpus": world, "steps": steps, "warmup": min(args.warmup, 3), "ms_per_step": total_ms / steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64 Mahalanobis/exp, f32 products, f64 accumulate", "data": "synthetic",
+            "config": {"workload": "configs[2]: SVN-NDT align, K=100 particles, 131072-pt OS1-128-shaped scan pair, 1.0 m voxels, Gauss-Newton Hessian, per step",
+                       "particles": K, "parallelism": f"particles sharded x{world}, one all-reduce of K x 43 f64 per iteration", "svn_iterations_per_align": st["iters"] / steps,
+                       "max_abs_translation_error_m": st["err"], "l2": "inputs of one align (K x 131072 point evaluations per iteration) exceed nothing: L2-resident by design"},
+            "e2e": {"value": steps / (e2e_ms * 1e-3), "unit": "scans/s", "h2d_bytes_per_step": 16 * N_SCAN, "d2h_bytes_per_step": int(43 * 8 * k_local * st2["iters"] / steps),
+                    "ms_per_step": e2e_ms / steps},
+            "gpu_launches": launches,
+            "roofline": {"kernel": "eval_kernel<svn,DIRECT7,GN>", "bound": "hbm", "achieved": b_eval / t_eval / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": b_eval / t_eval / 1e9 / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": b_eval,
+                         "mean_hits_per_point": st["hits"], "kernel_us": t_eval * 1e6},
+            "clocks": clk}
+
+
 def run_reference(args, rank):
     if rank != 0:
         return None
@@ -284,6 +376,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="map_align", choices=["map_align", "svn"])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -291,6 +384,8 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         line = run_reference(args, rank)
+    elif args.workload == "svn":
+        line = run_gpu_svn(args, rank, world, local_rank)
     else:
         line = run_gpu(args, rank, world, local_rank)
     if line is not None:

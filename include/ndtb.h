@@ -159,6 +159,12 @@ int ndtb_svn_align(ndtb_handle h, const double prior[16], const double* init_par
 int ndtb_svn_stage1_local(ndtb_handle h, int K, const double* poses, int rank, int world, double* records43);
 int ndtb_svn_finish_step(ndtb_handle h, int K, double* poses, const double* records43, double* updates);
 
+/* Host helpers of the sharded SVN loop (every rank runs them redundantly on identical particles):
+ * mean pose = prior.retract(mean_k Logmap(prior^-1 P_k)) (svn_ndt_impl.hpp:867-878) and the stop
+ * test || Logmap(a^-1 b) || (:879-884). */
+int ndtb_svn_mean_pose(int K, const double* poses, const double prior[16], double mean16[16]);
+int ndtb_svn_pose_distance(const double a[16], const double b[16], double* norm);
+
 /* ---- batch replay: n independent alignments against the current target ----------------------- */
 int ndtb_align_batch(ndtb_handle h, int n_scans, const float* const* xyz, const size_t* n_points, size_t stride_bytes,
                      const float* guesses16, ndtb_result* results);

@@ -159,6 +159,29 @@ int ndtb_svn_step(ndtb_handle h, int K, double* poses, double* scores, double* g
   return ndtb_svn_finish_step(h, K, poses, rec.data(), updates);
 }
 
+int ndtb_svn_mean_pose(int K, const double* poses, const double prior[16], double mean16[16]) {
+  if (K <= 0 || !poses || !prior || !mean16) return NDTB_ERR_INVALID;
+  Pose prior_p; pose_from16(prior, prior_p);
+  double mean_xi[6] = {0, 0, 0, 0, 0, 0};
+  for (int k = 0; k < K; ++k) {
+    Pose pk; pose_from16(poses + 16 * k, pk);
+    double xi[6]; pose_logmap(pose_between(prior_p, pk), xi);
+    for (int i = 0; i < 6; ++i) mean_xi[i] += xi[i];
+  }
+  for (int i = 0; i < 6; ++i) mean_xi[i] /= static_cast<double>(K);
+  pose_to16(pose_retract(prior_p, mean_xi), mean16);
+  return NDTB_OK;
+}
+
+int ndtb_svn_pose_distance(const double a[16], const double b[16], double* norm) {
+  if (!a || !b || !norm) return NDTB_ERR_INVALID;
+  Pose pa, pb; pose_from16(a, pa); pose_from16(b, pb);
+  double d[6]; pose_logmap(pose_between(pa, pb), d);
+  double n2 = 0; for (int i = 0; i < 6; ++i) n2 += d[i] * d[i];
+  *norm = sqrt(n2);
+  return NDTB_OK;
+}
+
 int ndtb_svn_align(ndtb_handle h, const double prior[16], const double* init_particles, uint64_t seed, ndtb_svn_result* result,
                    double* particles_out) {
   if (!h || !prior || !result) return NDTB_ERR_INVALID;

@@ -44,6 +44,25 @@ def svn_step(handle, poses, rank, world, device=None):
     return handle.svn_finish_step(poses, rec)
 
 
+def svn_align(handle, prior, particles, rank, world, max_iterations=50, stop_threshold=1e-4, device=None):
+    """align(source, prior) of svn_ndt (svn_ndt_impl.hpp:675-964) with the particles sharded over `world` ranks:
+    the loop of ndtb_svn_align, stage 1 local + one all-reduce per iteration.  Returns (mean pose, particles,
+    iterations, converged); every rank returns bit-identical values."""
+    from . import ndtb
+
+    P = np.ascontiguousarray(particles, np.float64).copy()
+    mean_cur = np.ascontiguousarray(prior, np.float64).reshape(4, 4)
+    it, converged = 0, False
+    for it in range(1, max_iterations + 1):
+        mean_last = mean_cur
+        P, _ = svn_step(handle, P, rank, world, device)
+        mean_cur = ndtb.svn_mean_pose(P, prior)
+        if ndtb.svn_pose_distance(mean_last, mean_cur) < stop_threshold:
+            converged = True
+            break
+    return mean_cur, P, it, converged
+
+
 def max_over_ranks(value, device=None):
     import torch
     import torch.distributed as dist

@@ -51,7 +51,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "nd
            "ndtb_compute_derivatives", "ndtb_align", "ndtb_get_trace", "ndtb_calculate_scores", "ndtb_get_voxel_count", "ndtb_get_voxels",
            "ndtb_get_last_hits", "ndtb_svn_default_params", "ndtb_svn_set_params", "ndtb_svn_particle_derivatives", "ndtb_svn_stage2",
            "ndtb_svn_step", "ndtb_svn_align", "ndtb_svn_stage1_local", "ndtb_svn_finish_step", "ndtb_align_batch", "ndtb_get_timings",
-           "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_set_profiling"]
+           "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_set_profiling", "ndtb_svn_mean_pose", "ndtb_svn_pose_distance"]
 
 _LIB = None
 
@@ -103,6 +103,8 @@ def lib():
         L.ndtb_get_stream.argtypes = [H, C.POINTER(C.c_void_p)]
         L.ndtb_get_launch_count.argtypes = [H, C.POINTER(C.c_uint64)]
         L.ndtb_set_profiling.argtypes = [H, C.c_int]
+        L.ndtb_svn_mean_pose.argtypes = [C.c_int, c_d, c_d, c_d]
+        L.ndtb_svn_pose_distance.argtypes = [c_d, c_d, c_d]
         _LIB = L
     return _LIB
 
@@ -117,6 +119,22 @@ def host_cloud(cloud):
     if a.ndim != 2 or a.shape[1] < 3:
         raise ValueError("cloud must be (N, >=3) float32")
     return a, a.shape[0], a.shape[1] * 4
+
+
+def svn_mean_pose(poses, prior):
+    P = np.ascontiguousarray(poses, np.float64); pr = np.ascontiguousarray(prior, np.float64).reshape(16); out = np.zeros(16)
+    rc = lib().ndtb_svn_mean_pose(P.shape[0], _ptr(P, c_d), _ptr(pr, c_d), _ptr(out, c_d))
+    if rc != NDTB_OK:
+        raise NdtbError(rc, "ndtb_svn_mean_pose")
+    return out.reshape(4, 4)
+
+
+def svn_pose_distance(a, b):
+    a = np.ascontiguousarray(a, np.float64).reshape(16); b = np.ascontiguousarray(b, np.float64).reshape(16); n = np.zeros(1)
+    rc = lib().ndtb_svn_pose_distance(_ptr(a, c_d), _ptr(b, c_d), _ptr(n, c_d))
+    if rc != NDTB_OK:
+        raise NdtbError(rc, "ndtb_svn_pose_distance")
+    return float(n[0])
 
 
 class Handle:
