@@ -173,10 +173,24 @@ int ndtb_align_batch(ndtb_handle h, int n_scans, const float* const* xyz, const 
 /* CUDA-event time (ms) of the stages of the last set_target / align on the handle's stream. */
 int ndtb_get_timings(ndtb_handle h, float* build_ms, float* align_ms, float* eval_kernel_ms_total, int* eval_kernel_launches);
 int ndtb_get_stream(ndtb_handle h, void** cuda_stream);
-/* Per-kernel CUDA events around every derivative evaluation (eval_kernel_ms_total of ndtb_get_timings).
- * On by default; switching them off removes two event records (several microseconds of stream time)
- * from every Newton iteration -- eval_kernel_ms_total then stays 0. */
+/* Per-kernel CUDA events around every derivative evaluation: eval_kernel_ms_total of ndtb_get_timings is
+ * then the sum of event-pair times, and every evaluation is its own kernel launch.  Off by default: ndtb_align
+ * serves all evaluations of a Newton loop from ONE resident kernel (an "alignment session", commands through a
+ * pinned mailbox) and eval_kernel_ms_total is the device-side (globaltimer) duration of those evaluations. */
 int ndtb_set_profiling(ndtb_handle h, int per_kernel_events);
+/* Named switches (no counterpart in the reference):
+ *   "direct_solver" (default 1)  Newton direction H^-1(-g) (ndt_omp_impl.hpp:142-145) by elimination with complete
+ *                                pivoting + one refinement step when the pivots certify cond(H) <~ 1e6, else -- and
+ *                                always with 0 -- by the two-sided Jacobi SVD that restates Eigen::JacobiSVD::solve.
+ *                                For a full-rank H the two agree to ~1e-12 relative.
+ *   "sessions" (default 1)       0: one kernel launch per evaluation instead of a resident kernel per ndtb_align.
+ *   "session_idle_timeout_ms" (default 50)  the resident kernel leaves by itself after this long without a command;
+ *                                the host then falls back to one launch per evaluation. */
+int ndtb_set_option(ndtb_handle h, const char* name, double value);
+/* The Newton-direction solve of ndtb_align on its own (host code, no GPU): x = H^-1 b by the path "direct_solver"
+ * selects (method 1; falls back to the SVD when H is not certified well conditioned) or by the Jacobi SVD with
+ * Eigen's rank threshold (method 0).  *used_direct reports which one produced x.  Parity hook for the tests. */
+int ndtb_newton_direction(const double H[36], const double b[6], int method, double x[6], int* used_direct);
 /* Number of CUDA kernels this handle has launched since creation (bench.py's gpu_launches). */
 int ndtb_get_launch_count(ndtb_handle h, uint64_t* launches);
 

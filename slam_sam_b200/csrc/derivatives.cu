@@ -711,9 +711,13 @@ __device__ __forceinline__ void transposed_add(const float* __restrict__ s_tr, i
     const float* r = s_tr + (g + 8 * s) * TR_STRIDE;
     const float4 v0 = *reinterpret_cast<const float4*>(r + 4 * q);
     const float2 v1 = *reinterpret_cast<const float2*>(r + 16 + 2 * q);
+#ifdef EXP_HALF_CVT  // timing experiment only (wrong results): half of the conversions
+    a[0] += static_cast<double>(v0.x + v0.y); a[2] += static_cast<double>(v0.z + v0.w); a[4] += static_cast<double>(v1.x + v1.y);
+#else
     a[0] += static_cast<double>(v0.x); a[1] += static_cast<double>(v0.y);
     a[2] += static_cast<double>(v0.z); a[3] += static_cast<double>(v0.w);
     a[4] += static_cast<double>(v1.x); a[5] += static_cast<double>(v1.y);
+#endif
   }
 }
 
@@ -777,15 +781,15 @@ __device__ __forceinline__ int pair_word_component(int w) {
   return RED_H + 6 * (2 * pp + half) + j;
 }
 
+// The evaluation proper, shared by the one-shot kernel (state in the constant bank) and the alignment-session
+// kernel (state in shared memory).  Every thread of the CTA calls it; it ends with a CTA-wide barrier-free tail
+// (only the last CTA to take a ticket runs the final reduction), so callers that loop must __syncthreads() after it.
 template <int PROBES, bool HESS>
-__global__ void __launch_bounds__(PCL_THREADS, 1) eval_kernel_pclomp(const float4* __restrict__ src, int n, GridMeta m,
-                                                                     const VoxRec* __restrict__ recs, const HashSlot* __restrict__ table,
-                                                                     const __grid_constant__ EvalState st, double* __restrict__ partials,
-                                                                     double* __restrict__ results, unsigned int* __restrict__ tickets,
-                                                                     unsigned long long result_key,
-                                                                     unsigned long long* __restrict__ dbg /* optional: 8 stamps per block */) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  PclShared& sh = *reinterpret_cast<PclShared*>(smem_raw);
+__device__ __forceinline__ void pclomp_eval_body(PclShared& sh, const float4* __restrict__ src, int n, const GridMeta& m,
+                                                 const VoxRec* __restrict__ recs, const HashSlot* __restrict__ table, const EvalState& st,
+                                                 double* __restrict__ partials, double* __restrict__ results, unsigned int* __restrict__ tickets,
+                                                 unsigned long long result_key, unsigned long long* __restrict__ dbg /* optional: 8 stamps per block */,
+                                                 unsigned long long t_seen /* session: globaltimer when the command was seen, else 0 */) {
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   auto stamp = [&](int k) {
     if (dbg && tid == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); dbg[8 * blockIdx.x + k] = t; }
@@ -880,35 +884,154 @@ __global__ void __launch_bounds__(PCL_THREADS, 1) eval_kernel_pclomp(const float
   }
   __syncthreads();
   stamp(3);
-  if (!sh.last) return;
-  if (tid < ((RED_N * 8 + 31) & ~31)) {  // whole warps: 8 lanes per component
-    const int c = tid >> 3, l = tid & 7;
-    const bool valid = c < RED_N;
-    constexpr int MAXI = (148 + 7) / 8;
-    double v[MAXI];
+  if (sh.last) {
+    // reset the ticket BEFORE the results are published: the next evaluation (next launch, or the next command of a
+    // session, which the host only sends after it has seen these results) finds it at zero
+    if (tid == 0) { tickets[0] = 0; __threadfence(); }
+    __syncthreads();
+    if (tid < ((RED_N * 8 + 31) & ~31)) {  // whole warps: 8 lanes per component
+      const int c = tid >> 3, l = tid & 7;
+      const bool valid = c < RED_N;
+      constexpr int MAXI = (148 + 7) / 8;
+      double v[MAXI];
 #pragma unroll
-    for (int i = 0; i < MAXI; ++i) {
-      const int b = l + 8 * i;
-      v[i] = (valid && b < nblk) ? __ldcg(partials + static_cast<size_t>(c) * nblk + b) : 0.0;
+      for (int i = 0; i < MAXI; ++i) {
+        const int b = l + 8 * i;
+        v[i] = (valid && b < nblk) ? __ldcg(partials + static_cast<size_t>(c) * nblk + b) : 0.0;
+      }
+      double sum = v[0];
+#pragma unroll
+      for (int i = 1; i < MAXI; ++i) sum += v[i];
+      if (valid) for (int b = l + 8 * MAXI; b < nblk; b += 8) sum += __ldcg(partials + static_cast<size_t>(c) * nblk + b);
+#pragma unroll
+      for (int o = 1; o < 8; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+      if (l == 0 && valid) {
+        // Self-validating result slot {value, value ^ key}: two 8-byte stores, no system fence and no separate flag.
+        // The host accepts slot c once w0 ^ w1 == key (a stale half cannot satisfy it), see eval_pclomp().
+        const unsigned long long bits = static_cast<unsigned long long>(__double_as_longlong(sum));
+        volatile unsigned long long* slot = reinterpret_cast<volatile unsigned long long*>(results) + 2 * c;
+        slot[0] = bits;
+        slot[1] = bits ^ result_key;
+      }
     }
-    double sum = v[0];
-#pragma unroll
-    for (int i = 1; i < MAXI; ++i) sum += v[i];
-    if (valid) for (int b = l + 8 * MAXI; b < nblk; b += 8) sum += __ldcg(partials + static_cast<size_t>(c) * nblk + b);
-#pragma unroll
-    for (int o = 1; o < 8; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    if (l == 0 && valid) {
-      // Self-validating result slot {value, value ^ key}: two 8-byte stores, no system fence and no separate flag.
-      // The host accepts slot c once w0 ^ w1 == key (a stale half cannot satisfy it), see wait_results().
-      const unsigned long long bits = static_cast<unsigned long long>(__double_as_longlong(sum));
-      volatile unsigned long long* slot = reinterpret_cast<volatile unsigned long long*>(results) + 2 * c;
-      slot[0] = bits;
-      slot[1] = bits ^ result_key;
+    stamp(4);
+    if (t_seen && tid == 0) {  // session: device-side duration of this evaluation (command seen -> results stored), slot RED_N
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      publish_slot(reinterpret_cast<volatile unsigned long long*>(results), RED_N, t - t_seen, result_key);
     }
   }
-  stamp(4);
-  if (tid == 0) tickets[0] = 0;  // self-reset for the next launch (kernels on the stream are serialised)
   stamp(5);
+}
+
+template <int PROBES, bool HESS>
+__global__ void __launch_bounds__(PCL_THREADS, 1) eval_kernel_pclomp(const float4* __restrict__ src, int n, GridMeta m,
+                                                                     const VoxRec* __restrict__ recs, const HashSlot* __restrict__ table,
+                                                                     const __grid_constant__ EvalState st, double* __restrict__ partials,
+                                                                     double* __restrict__ results, unsigned int* __restrict__ tickets,
+                                                                     unsigned long long result_key,
+                                                                     unsigned long long* __restrict__ dbg /* optional: 8 stamps per block */) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  PclShared& sh = *reinterpret_cast<PclShared*>(smem_raw);
+  pclomp_eval_body<PROBES, HESS>(sh, src, n, m, recs, table, st, partials, results, tickets, result_key, dbg, 0ull);
+}
+
+// ---- alignment session: ONE resident launch serves every evaluation of a Newton loop -----------------------
+// ndtb_align launches this kernel once (one CTA per SM, cooperative launch so that all CTAs are co-resident) and
+// then sends one command per evaluation through a 1 KB mailbox in pinned host memory: 64 self-validating 16-byte
+// units {word, word ^ session_key(seq)}.  Warp 0 of CTA 0 polls the mailbox over PCIe, copies the validated command
+// to device memory and releases `seq` to the other CTAs, which spin on it in L2.  Results leave through the same
+// host slots as the one-shot kernel.  This removes the per-iteration launch path (API call, front-end, CTA
+// start-up) from the host <-> device ping-pong.  The kernel leaves by itself on a quit command or after
+// `idle_timeout_ns` without a command (the host then falls back to one-shot launches), so it cannot hang the GPU.
+struct PclSessionShared {
+  PclShared sh;
+  SessionCmd cmd;
+  unsigned long long t_seen;
+};
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+template <int PROBES>
+__global__ void __launch_bounds__(PCL_THREADS, 1) align_session_kernel(const float4* __restrict__ src, int n, GridMeta m,
+                                                                       const VoxRec* __restrict__ recs, const HashSlot* __restrict__ table,
+                                                                       const ulonglong2* mailbox, unsigned long long* d_cmd,
+                                                                       double* __restrict__ partials, double* __restrict__ results,
+                                                                       unsigned int* __restrict__ tickets, unsigned long long seq0,
+                                                                       unsigned long long idle_timeout_ns) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  PclSessionShared& ss = *reinterpret_cast<PclSessionShared*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31;
+  unsigned long long seq = seq0;
+  for (;;) {
+    ++seq;
+    if (blockIdx.x == 0 && tid < 32) {
+      const unsigned long long key = session_key(seq);
+      const volatile ulonglong2* mb = mailbox;
+      const unsigned long long t_wait = globaltimer_ns();
+      unsigned long long w0 = 0, w1 = 0;
+      bool quit = false;
+      for (;;) {
+        const unsigned long long a0 = mb[lane].x, a1 = mb[lane].y, b0 = mb[32 + lane].x, b1 = mb[32 + lane].y;
+        w0 = a0; w1 = b0;
+        if (__all_sync(0xffffffffu, ((a0 ^ a1) == key) && ((b0 ^ b1) == key))) break;
+        const bool late = globaltimer_ns() - t_wait > idle_timeout_ns;
+        if (__shfl_sync(0xffffffffu, late ? 1 : 0, 0)) { quit = true; break; }
+      }
+      d_cmd[lane] = w0;
+      d_cmd[32 + lane] = w1;
+      __syncwarp();
+      if (lane == 0) {
+        if (quit) d_cmd[SESSION_FLAGS_WORD] = SESSION_QUIT;
+        d_cmd[SESSION_TSEEN_WORD] = globaltimer_ns();
+        __threadfence();
+        asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(d_cmd + SESSION_SEQ_WORD), "l"(seq) : "memory");
+      }
+    }
+    if (tid == 0) {
+      unsigned long long seen;
+      do {
+        asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(seen) : "l"(d_cmd + SESSION_SEQ_WORD) : "memory");
+      } while (seen != seq);
+    }
+    __syncthreads();
+    if (tid < SESSION_CMD_WORDS) reinterpret_cast<unsigned long long*>(&ss.cmd)[tid] = __ldcg(d_cmd + tid);
+    if (tid == 64) ss.t_seen = __ldcg(d_cmd + SESSION_TSEEN_WORD);
+    __syncthreads();
+    if (ss.cmd.flags & SESSION_QUIT) return;
+    pclomp_eval_body<PROBES, true>(ss.sh, src, n, m, recs, table, ss.cmd.st, partials, results, tickets, ss.cmd.result_key, nullptr, ss.t_seen);
+    __syncthreads();
+  }
+}
+
+template <int PROBES>
+static cudaError_t launch_session_t(const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs, const HashSlot* table,
+                                    const ulonglong2* mailbox, unsigned long long* d_cmd, const EvalBuffers& b, double* results,
+                                    unsigned long long seq0, unsigned long long idle_timeout_ns, cudaStream_t stream) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(align_session_kernel<PROBES>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(PclSessionShared)));
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  GridMeta m = meta;
+  double* partials = b.d_partials;
+  unsigned int* tickets = b.d_tickets;
+  void* args[] = {&d_src, &n, &m, &recs, &table, &mailbox, &d_cmd, &partials, &results, &tickets, &seq0, &idle_timeout_ns};
+  // cooperative launch: fails (instead of deadlocking on the inter-CTA spin) if the CTAs cannot all be resident at once
+  return cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(align_session_kernel<PROBES>), dim3(eval_blocks_pclomp(n)), dim3(PCL_THREADS), args,
+                                     sizeof(PclSessionShared), stream);
+}
+
+cudaError_t launch_align_session(int n_probe, const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs, const HashSlot* table,
+                                 const ulonglong2* mailbox, unsigned long long* d_cmd, const EvalBuffers& b, double* results,
+                                 unsigned long long seq0, unsigned long long idle_timeout_ns, cudaStream_t stream) {
+  return n_probe == 7 ? launch_session_t<7>(d_src, n, meta, recs, table, mailbox, d_cmd, b, results, seq0, idle_timeout_ns, stream)
+                      : launch_session_t<1>(d_src, n, meta, recs, table, mailbox, d_cmd, b, results, seq0, idle_timeout_ns, stream);
 }
 
 // Generic (svn) kernel: one resident wave of 148 SMs x EVAL_MIN_BLOCKS CTAs (register-limited); the cloud is dealt to the warps round-robin.

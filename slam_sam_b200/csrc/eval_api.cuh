@@ -37,4 +37,25 @@ cudaError_t launch_eval_pclomp(int n_probe, bool compute_hessian, const float4* 
                                unsigned long long result_key, cudaStream_t stream, unsigned long long* dbg_stamps = nullptr);
 int eval_blocks_pclomp(int n);
 
+// Alignment session (see align_session_kernel): one command per evaluation, written by the host into a pinned
+// mailbox of 64 units {word, word ^ session_key(seq)}; seq increases monotonically over the life of a handle.
+struct SessionCmd {
+  EvalState st;
+  unsigned long long result_key;  // key of the result slots of this evaluation
+  unsigned long long flags;       // SESSION_QUIT
+};
+constexpr int SESSION_CMD_WORDS = static_cast<int>(sizeof(SessionCmd) / 8);
+constexpr int SESSION_FLAGS_WORD = SESSION_CMD_WORDS - 1;
+constexpr int SESSION_UNITS = 64;           // mailbox units (16 bytes each)
+constexpr int SESSION_SEQ_WORD = 64;        // d_cmd[64]: sequence number released by CTA 0
+constexpr int SESSION_TSEEN_WORD = 65;      // d_cmd[65]: globaltimer when CTA 0 saw the command
+constexpr int SESSION_DCMD_WORDS = 80;
+constexpr unsigned long long SESSION_QUIT = 1ull;
+static_assert(sizeof(SessionCmd) % 8 == 0 && SESSION_CMD_WORDS <= SESSION_UNITS, "command must fit the mailbox");
+__host__ __device__ inline unsigned long long session_key(unsigned long long seq) { return (0xD1B54A32D192ED03ull * seq) | 1ull; }
+
+cudaError_t launch_align_session(int n_probe, const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs, const HashSlot* table,
+                                 const ulonglong2* mailbox, unsigned long long* d_cmd, const EvalBuffers& bufs, double* results,
+                                 unsigned long long seq0, unsigned long long idle_timeout_ns, cudaStream_t stream);
+
 }  // namespace ndtb

@@ -28,7 +28,17 @@ struct ndtb_handle_s {
   unsigned int flag_seq = 0;
   std::vector<cudaEvent_t> ev_pool;     // per-evaluation event pairs, resolved after the loop (no per-iteration sync)
   size_t ev_used = 0;
-  bool kernel_events = true;            // ndtb_set_profiling
+  bool kernel_events = false;           // ndtb_set_profiling: CUDA-event pair around every evaluation (one launch each)
+  // alignment session (align_session_kernel): mailbox the resident kernel polls, device-side command copy
+  ulonglong2* h_mailbox = nullptr;      // pinned, SESSION_UNITS x 16 bytes
+  unsigned long long* d_cmd = nullptr;  // device, SESSION_DCMD_WORDS
+  unsigned long long mail_seq = 0;      // commands sent so far (never repeats: keys a stale mailbox cannot satisfy)
+  bool session_open = false;
+  bool use_sessions = true;             // off with per-kernel events (ndtb_set_profiling) or NDTB_NO_SESSION=1
+  double session_idle_ms = 50.0;        // the resident kernel leaves after this long without a command
+  bool direct_solver = true;            // Newton direction by pivoted elimination when well conditioned (ndtb_set_option)
+  unsigned long long pending_time_key = 0;  // result key of the last session evaluation whose duration slot is unread
+  double session_eval_ns = 0;           // device-side duration of the session evaluations of the last align
 
   bool has_reg_pose = false;
   float reg_translation[3] = {0, 0, 0};

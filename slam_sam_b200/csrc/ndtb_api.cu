@@ -112,6 +112,62 @@ static int resolve_eval_events(ndtb_handle_s* h) {
   return NDTB_OK;
 }
 
+// ---- alignment session (host side) ---------------------------------------------------------------------------
+static void session_send(ndtb_handle_s* h, const EvalState* st, unsigned long long result_key, unsigned long long flags) {
+  SessionCmd cmd;
+  std::memset(&cmd, 0, sizeof(cmd));
+  if (st) cmd.st = *st;
+  cmd.result_key = result_key;
+  cmd.flags = flags;
+  unsigned long long words[SESSION_UNITS] = {0};
+  std::memcpy(words, &cmd, sizeof(cmd));
+  const unsigned long long key = session_key(++h->mail_seq);
+  volatile unsigned long long* mb = reinterpret_cast<volatile unsigned long long*>(h->h_mailbox);
+  for (int i = 0; i < SESSION_UNITS; ++i) { mb[2 * i] = words[i]; mb[2 * i + 1] = words[i] ^ key; }
+  __sync_synchronize();
+}
+
+// The duration slot of the previous session evaluation is published a little after its results: collect it late.
+static void session_collect_time(ndtb_handle_s* h) {
+  if (!h->pending_time_key) return;
+  volatile unsigned long long* slots = reinterpret_cast<volatile unsigned long long*>(h->h_results);
+  for (int spin = 0; spin < 200000; ++spin) {
+    const unsigned long long w0 = slots[2 * RED_N], w1 = slots[2 * RED_N + 1];
+    if ((w0 ^ w1) == h->pending_time_key) { h->session_eval_ns += static_cast<double>(w0); break; }
+  }
+  h->pending_time_key = 0;
+}
+
+static void session_begin(ndtb_handle_s* h) {
+  static const bool env_off = getenv("NDTB_NO_SESSION") != nullptr;
+  h->session_eval_ns = 0;
+  if (!h->use_sessions || h->kernel_events || env_off || h->session_open) return;
+  const int n = static_cast<int>(h->n_source);
+  if (ensure_eval_buffers(h, 1, n) != NDTB_OK) return;
+  if (!h->h_mailbox) {
+    if (cudaMallocHost(&h->h_mailbox, SESSION_UNITS * sizeof(ulonglong2)) != cudaSuccess ||
+        cudaMalloc(&h->d_cmd, SESSION_DCMD_WORDS * sizeof(unsigned long long)) != cudaSuccess) { cudaGetLastError(); h->use_sessions = false; return; }
+    std::memset(h->h_mailbox, 0, SESSION_UNITS * sizeof(ulonglong2));
+  }
+  // the device copy of the sequence number starts at the value the kernel starts from
+  if (cudaMemcpyAsync(h->d_cmd + SESSION_SEQ_WORD, &h->mail_seq, sizeof(unsigned long long), cudaMemcpyHostToDevice, h->stream) != cudaSuccess) {
+    cudaGetLastError(); h->use_sessions = false; return;
+  }
+  const int n_probe = (h->params.search_method == NDTB_DIRECT1) ? 1 : 7;
+  const cudaError_t e = launch_align_session(n_probe, h->d_source, n, h->grid.meta, h->grid.recs, h->grid.table, h->h_mailbox, h->d_cmd, h->eval,
+                                             h->h_results, h->mail_seq, static_cast<unsigned long long>(h->session_idle_ms * 1e6), h->stream);
+  if (e != cudaSuccess) { cudaGetLastError(); h->use_sessions = false; return; }  // e.g. the CTAs cannot be co-resident: one-shot launches
+  h->session_open = true;
+  h->launches += 1;
+}
+
+static void session_end(ndtb_handle_s* h) {
+  if (!h->session_open) return;
+  session_collect_time(h);
+  session_send(h, nullptr, 0, SESSION_QUIT);
+  h->session_open = false;
+}
+
 // One pclomp evaluation: upload state, launch, read back the 46-double result, apply the
 // regulariser (ndt_omp_impl.hpp:349-382) and NVTL (:384-389) on the host.
 static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool compute_hessian, double* score, double* g, double* H,
@@ -130,35 +186,52 @@ static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool
     e0 = h->ev_pool[h->ev_used]; e1 = h->ev_pool[h->ev_used + 1];
     h->ev_used += 2;
   }
-  const unsigned long long key = 0x9E3779B97F4A7C15ull * static_cast<unsigned long long>(++h->flag_seq) | 1ull;
-  if (e0) cudaEventRecord(e0, h->stream);
   static unsigned long long* d_dbg = nullptr;  // development aid: NDTB_DEBUG_TIMING=1 prints in-kernel globaltimer stamps
   static const bool dbg_on = getenv("NDTB_DEBUG_TIMING") != nullptr;
-  if (dbg_on && !d_dbg) { cudaMalloc(&d_dbg, 8 * 148 * sizeof(unsigned long long)); }
-  if (dbg_on) cudaMemsetAsync(d_dbg, 0, 8 * 148 * sizeof(unsigned long long), h->stream);
-  // state by value (kernel parameter); the kernel writes 46 self-validating slots {bits, bits ^ key} straight into
-  // pinned host memory, and this thread polls them instead of synchronising the stream
-  CKH(launch_eval_pclomp(n_probe, compute_hessian, h->d_source, n, h->grid.meta, h->grid.recs, h->grid.table, h->h_states[0], h->eval,
-                         h->h_results, key, h->stream, dbg_on ? d_dbg : nullptr));
-  if (e1) cudaEventRecord(e1, h->stream);
   double rbuf[RED_N];
-  {
+  for (int attempt = 0;; ++attempt) {
+    const unsigned long long key = 0x9E3779B97F4A7C15ull * static_cast<unsigned long long>(++h->flag_seq) | 1ull;
+    const bool via_session = h->session_open && compute_hessian && !dbg_on;
+    if (via_session) {
+      // one command into the resident kernel's mailbox; it answers through the same result slots
+      session_collect_time(h);
+      session_send(h, &h->h_states[0], key, 0);
+      h->pending_time_key = key;
+    } else {
+      if (h->session_open) session_end(h);  // an evaluation the session kernel does not serve: it leaves, the launch queues behind it
+      if (e0) cudaEventRecord(e0, h->stream);
+      if (dbg_on && !d_dbg) { cudaMalloc(&d_dbg, 8 * 148 * sizeof(unsigned long long)); }
+      if (dbg_on) cudaMemsetAsync(d_dbg, 0, 8 * 148 * sizeof(unsigned long long), h->stream);
+      // state by value (kernel parameter); the kernel writes 46 self-validating slots {bits, bits ^ key} straight into
+      // pinned host memory, and this thread polls them instead of synchronising the stream
+      CKH(launch_eval_pclomp(n_probe, compute_hessian, h->d_source, n, h->grid.meta, h->grid.recs, h->grid.table, h->h_states[0], h->eval,
+                             h->h_results, key, h->stream, dbg_on ? d_dbg : nullptr));
+      if (e1) cudaEventRecord(e1, h->stream);
+      h->launches += 1;
+    }
+    bool lost = false;
     volatile unsigned long long* slots = reinterpret_cast<volatile unsigned long long*>(h->h_results);
     unsigned int spins = 0;
-    for (int c = RED_N - 1; c >= 0; --c) {
+    for (int c = RED_N - 1; c >= 0 && !lost; --c) {
       for (;;) {
         const unsigned long long w0 = slots[2 * c], w1 = slots[2 * c + 1];
         if ((w0 ^ w1) == key) { std::memcpy(&rbuf[c], &w0, 8); break; }
         if ((++spins & 4095u) == 0) {  // a stream query every 4096 spins catches a failed launch
           const cudaError_t q = cudaStreamQuery(h->stream);
-          if (q != cudaSuccess && q != cudaErrorNotReady) { h->last_error = std::string("eval kernel: ") + cudaGetErrorString(q); return NDTB_ERR_CUDA; }
+          if (q != cudaSuccess && q != cudaErrorNotReady) { h->session_open = false; h->last_error = std::string("eval kernel: ") + cudaGetErrorString(q); return NDTB_ERR_CUDA; }
           if (q == cudaSuccess) {
             const unsigned long long x0 = slots[2 * c], x1 = slots[2 * c + 1];
-            if ((x0 ^ x1) != key) { h->last_error = "eval kernel finished without publishing its result"; return NDTB_ERR_CUDA; }
+            if ((x0 ^ x1) == key) continue;
+            if (via_session && attempt == 0) { lost = true; break; }  // the session kernel left on its idle timeout: one-shot launch
+            h->last_error = "eval kernel finished without publishing its result";
+            return NDTB_ERR_CUDA;
           }
         }
       }
     }
+    if (!lost) break;
+    h->session_open = false;
+    h->pending_time_key = 0;
   }
   __sync_synchronize();
   if (dbg_on) {
@@ -173,7 +246,7 @@ static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool
     fprintf(stderr, "[dbg n=%d blocks=%d] ns since first block start: start %llu..%llu | main done %llu..%llu | block reduced %llu..%llu | ticket %llu..%llu | final %llu | flag %llu\n",
             n, nb, mn[0], mx[0], mn[1], mx[1], mn[2], mx[2], mn[3], mx[3], mx[4], mx[5]);
   }
-  h->eval_launches += 1; h->launches += 1;
+  h->eval_launches += 1;
   const double* r = rbuf;
   double sc = r[RED_SCORE];
   std::memcpy(g, r + RED_G, 6 * sizeof(double));
@@ -253,6 +326,8 @@ int ndtb_destroy(ndtb_handle h) {
   if (h->h_states) cudaFreeHost(h->h_states);
   if (h->h_results) cudaFreeHost(h->h_results);
   if (h->h_flag) cudaFreeHost(const_cast<unsigned int*>(h->h_flag));
+  if (h->h_mailbox) cudaFreeHost(h->h_mailbox);
+  cudaFree(h->d_cmd);
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   cudaFree(h->d_svn_in); cudaFree(h->d_svn_out);
   for (int i = 0; i < 4; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
@@ -375,6 +450,12 @@ int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* tr
     h->trace.insert(h->trace.end(), pp, pp + 6); h->trace.push_back(score);
     h->trace.insert(h->trace.end(), g, g + 6); h->trace.insert(h->trace.end(), H, H + 36); h->trace.push_back(nvtl);
   };
+  // every evaluation of the loop below is served by ONE resident kernel (closed on every way out of this function)
+  struct SessionGuard {
+    ndtb_handle_s* h;
+    ~SessionGuard() { session_end(h); }
+  } session_guard{h};
+  session_begin(h);
   int rc = eval_pclomp(h, p, final_T, true, &score, g, H, &nvtl);
   if (rc != NDTB_OK) return rc;
   push_trace(p);
@@ -382,7 +463,8 @@ int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* tr
   while (!converged) {
     double neg_g[6];
     for (int i = 0; i < 6; ++i) neg_g[i] = -g[i];
-    svd6_solve(H, neg_g, delta_p);
+    // H^-1 (-g): elimination with complete pivoting when the pivots certify a well-conditioned H, else the Jacobi SVD
+    if (!(h->direct_solver && gecp6_solve(H, neg_g, delta_p, 1e-6))) svd6_solve(H, neg_g, delta_p);
     double nrm2 = 0;
     for (int i = 0; i < 6; ++i) nrm2 += delta_p[i] * delta_p[i];
     double delta_p_norm = sqrt(nrm2);
@@ -442,9 +524,11 @@ int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* tr
       for (int r = 0; r < 3; ++r)
         out_xyz[3 * i + r] = final_T[4 * r] * tmp[i].x + (final_T[4 * r + 1] * tmp[i].y + (final_T[4 * r + 2] * tmp[i].z + final_T[4 * r + 3]));
   }
+  session_end(h);
   cudaEventRecord(h->ev[1], h->stream);
   cudaEventSynchronize(h->ev[1]);
   cudaEventElapsedTime(&h->align_ms, h->ev[0], h->ev[1]);
+  if (h->session_eval_ns > 0) h->eval_ms_total = static_cast<float>(h->session_eval_ns * 1e-6);  // device-side (globaltimer) durations
   return resolve_eval_events(h);
 }
 
@@ -525,6 +609,24 @@ int ndtb_get_launch_count(ndtb_handle h, uint64_t* launches) {
 int ndtb_set_profiling(ndtb_handle h, int per_kernel_events) {
   if (!h) return NDTB_ERR_INVALID;
   h->kernel_events = per_kernel_events != 0;
+  return NDTB_OK;
+}
+
+int ndtb_newton_direction(const double H[36], const double b[6], int method, double x[6], int* used_direct) {
+  if (!H || !b || !x) return NDTB_ERR_INVALID;
+  const bool direct = method != 0 && gecp6_solve(H, b, x, 1e-6);
+  if (!direct) svd6_solve(H, b, x);
+  if (used_direct) *used_direct = direct ? 1 : 0;
+  return NDTB_OK;
+}
+
+int ndtb_set_option(ndtb_handle h, const char* name, double value) {
+  if (!h || !name) return NDTB_ERR_INVALID;
+  const std::string k(name);
+  if (k == "direct_solver") h->direct_solver = value != 0;           // 0: always the Jacobi SVD (Eigen::JacobiSVD restatement)
+  else if (k == "sessions") h->use_sessions = value != 0;            // 0: one kernel launch per evaluation
+  else if (k == "session_idle_timeout_ms") h->session_idle_ms = value > 0 ? value : 50.0;
+  else return set_error(h, NDTB_ERR_INVALID, "unknown option");
   return NDTB_OK;
 }
 

@@ -248,4 +248,70 @@ NM_HD void svd6_solve(const double* A, const double* b, double* x) {
   }
 }
 
+// Newton direction for a well-conditioned H: Gaussian elimination with complete pivoting plus one step of
+// iterative refinement.  Returns false (x untouched) unless the pivots certify cond(H) <~ 1/min_ratio; the caller
+// then takes svd6_solve, whose rank truncation is what the reference's JacobiSVD::solve does for a (nearly)
+// singular H (ndt_omp_impl.hpp:142-145).  For a full-rank H both give H^-1 b: they agree to ~cond(H) * 1e-16
+// relative, i.e. <= ~1e-10 at min_ratio = 1e-6, far inside the 1e-9 per-iteration parity bar -- at 1/30 of the
+// host time of the Jacobi sweeps, which sit on the critical path of every Newton iteration.
+NM_HD bool gecp6_solve(const double* A, const double* b, double* x, double min_ratio) {
+  double M[36];  // P A Q = L U in place (unit L below the diagonal)
+  int rowperm[6], colperm[6];
+  for (int i = 0; i < 36; ++i) M[i] = A[i];
+  for (int i = 0; i < 6; ++i) { rowperm[i] = i; colperm[i] = i; }
+  double first_pivot = 0.0;
+  for (int k = 0; k < 6; ++k) {
+    int pr = k, pc = k;
+    double best = -1.0;
+    for (int i = k; i < 6; ++i)
+      for (int j = k; j < 6; ++j) {
+        const double a = fabs(M[6 * i + j]);
+        if (a > best) { best = a; pr = i; pc = j; }
+      }
+    if (k == 0) first_pivot = best;
+    if (!(best >= first_pivot * min_ratio) || !(best > 0.0) || best > DBL_MAX) return false;  // also catches NaN
+    if (pr != k) {
+      for (int j = 0; j < 6; ++j) { const double t = M[6 * k + j]; M[6 * k + j] = M[6 * pr + j]; M[6 * pr + j] = t; }
+      const int t = rowperm[k]; rowperm[k] = rowperm[pr]; rowperm[pr] = t;
+    }
+    if (pc != k) {
+      for (int i = 0; i < 6; ++i) { const double t = M[6 * i + k]; M[6 * i + k] = M[6 * i + pc]; M[6 * i + pc] = t; }
+      const int t = colperm[k]; colperm[k] = colperm[pc]; colperm[pc] = t;
+    }
+    const double inv = 1.0 / M[7 * k];
+    for (int i = k + 1; i < 6; ++i) {
+      const double f = M[6 * i + k] * inv;
+      M[6 * i + k] = f;
+      for (int j = k + 1; j < 6; ++j) M[6 * i + j] = M[6 * i + j] - f * M[6 * k + j];
+    }
+  }
+  double sol[6] = {0, 0, 0, 0, 0, 0};
+  double rhs[6];
+  for (int i = 0; i < 6; ++i) rhs[i] = b[i];
+  for (int pass = 0; pass < 2; ++pass) {  // pass 0: A x0 = b ; pass 1: one refinement step A d = b - A x0
+    double y[6];
+    for (int i = 0; i < 6; ++i) {
+      double sum = rhs[rowperm[i]];
+      for (int j = 0; j < i; ++j) sum = sum - M[6 * i + j] * y[j];
+      y[i] = sum;
+    }
+    for (int i = 5; i >= 0; --i) {
+      double sum = y[i];
+      for (int j = i + 1; j < 6; ++j) sum = sum - M[6 * i + j] * y[j];
+      y[i] = sum / M[7 * i];
+    }
+    for (int i = 0; i < 6; ++i) sol[colperm[i]] = sol[colperm[i]] + y[i];
+    if (pass == 0) {
+      for (int i = 0; i < 6; ++i) {
+        double r = b[i];
+        for (int j = 0; j < 6; ++j) r = r - A[6 * i + j] * sol[j];
+        rhs[i] = r;
+      }
+    }
+  }
+  for (int i = 0; i < 6; ++i) if (!(fabs(sol[i]) <= DBL_MAX)) return false;
+  for (int i = 0; i < 6; ++i) x[i] = sol[i];
+  return true;
+}
+
 }  // namespace ndtb

@@ -51,7 +51,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "nd
            "ndtb_compute_derivatives", "ndtb_align", "ndtb_get_trace", "ndtb_calculate_scores", "ndtb_get_voxel_count", "ndtb_get_voxels",
            "ndtb_get_last_hits", "ndtb_svn_default_params", "ndtb_svn_set_params", "ndtb_svn_particle_derivatives", "ndtb_svn_stage2",
            "ndtb_svn_step", "ndtb_svn_align", "ndtb_svn_stage1_local", "ndtb_svn_finish_step", "ndtb_align_batch", "ndtb_get_timings",
-           "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_set_profiling", "ndtb_svn_mean_pose", "ndtb_svn_pose_distance"]
+           "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_set_profiling", "ndtb_set_option", "ndtb_newton_direction", "ndtb_svn_mean_pose", "ndtb_svn_pose_distance"]
 
 _LIB = None
 
@@ -103,6 +103,8 @@ def lib():
         L.ndtb_get_stream.argtypes = [H, C.POINTER(C.c_void_p)]
         L.ndtb_get_launch_count.argtypes = [H, C.POINTER(C.c_uint64)]
         L.ndtb_set_profiling.argtypes = [H, C.c_int]
+        L.ndtb_set_option.argtypes = [H, C.c_char_p, C.c_double]
+        L.ndtb_newton_direction.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.ndtb_svn_mean_pose.argtypes = [C.c_int, c_d, c_d, c_d]
         L.ndtb_svn_pose_distance.argtypes = [c_d, c_d, c_d]
         _LIB = L
@@ -135,6 +137,16 @@ def svn_pose_distance(a, b):
     if rc != NDTB_OK:
         raise NdtbError(rc, "ndtb_svn_pose_distance")
     return float(n[0])
+
+
+def newton_direction(H, b, method=1):
+    """x = H^-1 b as ndtb_align computes it (host code).  Returns (x, used_direct)."""
+    H = np.ascontiguousarray(H, np.float64).reshape(36); b = np.ascontiguousarray(b, np.float64).reshape(6)
+    x = np.zeros(6); used = C.c_int(0)
+    rc = lib().ndtb_newton_direction(_ptr(H, c_d), _ptr(b, c_d), int(method), _ptr(x, c_d), C.byref(used))
+    if rc != NDTB_OK:
+        raise NdtbError(rc, "ndtb_newton_direction")
+    return x, bool(used.value)
 
 
 class Handle:
@@ -270,6 +282,10 @@ class Handle:
 
     def set_profiling(self, on):
         self.check(self.L.ndtb_set_profiling(self.h, int(bool(on))))
+
+    def set_option(self, name, value):
+        """ndtb_set_option: "direct_solver", "sessions", "session_idle_timeout_ms"."""
+        self.check(self.L.ndtb_set_option(self.h, name.encode(), float(value)))
 
     def stream_ptr(self):
         p = C.c_void_p()

@@ -1,0 +1,85 @@
+"""The Newton loop's plumbing on the GPU: ndtb_align serves every evaluation from one resident kernel (an
+"alignment session") by default.  It must give bit-identical traces to one launch per evaluation, survive its own
+idle time-out, and the pivoted-elimination Newton direction must stay inside the parity bar of the Jacobi SVD."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import rel_inf
+from slam_sam_b200 import ndtb
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ndt_golden.npz")
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return dict(np.load(GOLD))
+
+
+def make_handle(gold, search=ndtb.DIRECT7):
+    h = ndtb.Handle(0)
+    h.set_params(resolution=2.0, search_method=search, max_iterations=35, trans_epsilon=0.01, step_size=0.1)
+    h.set_target(gold["target"]); h.set_source(gold["source"])
+    return h
+
+
+@pytest.mark.parametrize("search", ["DIRECT7", "DIRECT1"])
+def test_session_is_bit_identical_to_one_launch_per_evaluation(gold, search):
+    h = make_handle(gold, getattr(ndtb, search))
+    n0 = h.launch_count()
+    r_s = h.align(); tr_s = h.trace()
+    session_launches = h.launch_count() - n0
+    assert session_launches == 1                      # one resident kernel for the whole Newton loop
+    assert h.timings()["eval_ms_total"] > 0           # device-side (globaltimer) evaluation time is reported
+    h.set_option("sessions", 0)
+    n0 = h.launch_count()
+    r_l = h.align(); tr_l = h.trace()
+    assert h.launch_count() - n0 == r_l["evaluations"]
+    h.set_option("sessions", 1); h.set_profiling(True)  # per-kernel events imply one launch per evaluation
+    n0 = h.launch_count()
+    r_p = h.align(); tr_p = h.trace()
+    assert h.launch_count() - n0 == r_p["evaluations"]
+    assert np.array_equal(tr_s, tr_l) and np.array_equal(tr_s, tr_p)
+    assert np.array_equal(r_s["T"], r_l["T"]) and r_s["iterations"] == r_l["iterations"] == r_p["iterations"]
+
+
+def test_session_idle_timeout_falls_back_to_launches(gold):
+    h = make_handle(gold)
+    ref = h.align(); tr_ref = h.trace()
+    h.set_option("session_idle_timeout_ms", 1e-4)     # 100 ns: the resident kernel leaves before a command can arrive
+    for _ in range(3):
+        r = h.align()
+        assert np.array_equal(h.trace(), tr_ref) and np.array_equal(r["T"], ref["T"])
+    h.set_option("session_idle_timeout_ms", 50)
+    r = h.align()
+    assert np.array_equal(h.trace(), tr_ref)
+
+
+def test_sessions_back_to_back_with_new_sources(gold):
+    h = make_handle(gold)
+    rng = np.random.default_rng(3)
+    src = gold["source"]
+    traces = []
+    for k in range(4):
+        sub = np.ascontiguousarray(src[rng.permutation(len(src))[: len(src) - 37 * k]])
+        h.set_source(sub)
+        h.set_option("sessions", 1); h.align(); a = h.trace()
+        h.set_option("sessions", 0); h.align(); b = h.trace()
+        assert np.array_equal(a, b)
+        traces.append(a)
+    assert len(traces) == 4
+
+
+def test_direct_solver_stays_inside_the_parity_bar(gold):
+    h = make_handle(gold)
+    h.set_option("direct_solver", 0)
+    r0 = h.align(); t0 = h.trace()
+    h.set_option("direct_solver", 1)
+    r1 = h.align(); t1 = h.trace()
+    assert t0.shape == t1.shape and r0["iterations"] == r1["iterations"]
+    for a, b in zip(t1, t0):
+        assert np.abs(a[:6] - b[:6]).max() <= 1e-11
+        assert abs(a[6] - b[6]) <= 1e-9 * abs(b[6]) and rel_inf(a[7:13], b[7:13]) <= 1e-9 and rel_inf(a[13:49], b[13:49]) <= 1e-9
+    assert np.abs(r0["T"] - r1["T"]).max() <= 1e-6
