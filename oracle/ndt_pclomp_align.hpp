@@ -155,7 +155,10 @@ inline double PclompNdt::step_length_mt(const double* x, double* step_dir, doubl
       step_iterations++;
     }
   }
-  if (step_iterations) compute_hessian_f64(H, trans);
+  if (step_iterations) {
+    compute_hessian_f64(H, trans);
+    push_trace(res, x_t, score, g, H, nvtl);  // extra trace row: the FP64 Hessian-only pass (parity hook, not in the reference)
+  }
   return a_t;
 }
 

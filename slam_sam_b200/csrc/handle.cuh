@@ -60,4 +60,5 @@ struct ndtb_handle_s {
 namespace ndtb {
 int ensure_eval_buffers(ndtb_handle_s* h, int particles, int n_points);
 int set_error(ndtb_handle_s* h, int code, const char* what);
+int compute_hessian_f64(ndtb_handle_s* h, const double* p, const float* T16, double* H);  // line_search.cu
 }  // namespace ndtb

@@ -141,7 +141,7 @@ static void session_collect_time(ndtb_handle_s* h) {
 static void session_begin(ndtb_handle_s* h) {
   static const bool env_off = getenv("NDTB_NO_SESSION") != nullptr;
   h->session_eval_ns = 0;
-  if (!h->use_sessions || h->kernel_events || env_off || h->session_open) return;
+  if (!h->use_sessions || h->kernel_events || env_off || h->session_open || h->params.use_line_search) return;
   const int n = static_cast<int>(h->n_source);
   if (ensure_eval_buffers(h, 1, n) != NDTB_OK) return;
   if (!h->h_mailbox) {
@@ -350,7 +350,6 @@ int ndtb_set_params(ndtb_handle h, const ndtb_params* p) {
     return set_error(h, NDTB_ERR_INVALID, "only DIRECT7 and DIRECT1 neighbour search are provided by this engine");
   if (!(p->resolution > 0.0f)) return set_error(h, NDTB_ERR_INVALID, "resolution must be positive");
   if (p->grid_flavour != NDTB_FLAVOUR_PCLOMP && p->grid_flavour != NDTB_FLAVOUR_SVN) return set_error(h, NDTB_ERR_INVALID, "bad grid_flavour");
-  if (p->use_line_search) return set_error(h, NDTB_ERR_INVALID, "More-Thuente line search (off by default in the reference) is not built yet");
   cudaSetDevice(h->device);
   h->params = *p;
   // setResolution rebuilds only if the value changed and a target is set (ndt_omp.h:135-142)
@@ -474,8 +473,9 @@ int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* tr
       break;
     }
     for (int i = 0; i < 6; ++i) delta_p[i] = delta_p[i] / delta_p_norm;
-    // computeStepLengthMT with use_line_search == false (ndt_omp_impl.hpp:915-983)
+    // computeStepLengthMT (ndt_omp_impl.hpp:915-1079)
     {
+      const double phi_0 = -score;
       double d_phi_0 = 0;
       for (int i = 0; i < 6; ++i) d_phi_0 += g[i] * delta_p[i];
       d_phi_0 = -d_phi_0;
@@ -483,16 +483,58 @@ int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* tr
       if (d_phi_0 >= 0 && d_phi_0 == 0) {
         a_t = 0;
       } else {
-        if (d_phi_0 >= 0) for (int i = 0; i < 6; ++i) delta_p[i] *= -1;
+        if (d_phi_0 >= 0) { d_phi_0 *= -1; for (int i = 0; i < 6; ++i) delta_p[i] *= -1; }
+        const int max_step_iterations = 10;
+        int step_iterations = 0;
+        const double mu = 1.e-4, nu = 0.9;
+        const double step_max = P.step_size, step_min = P.trans_epsilon / 2;
+        double a_l = 0, a_u = 0;
+        double f_l = mt_psi(a_l, phi_0, phi_0, d_phi_0, mu), g_l = mt_dpsi(d_phi_0, d_phi_0, mu);
+        double f_u = mt_psi(a_u, phi_0, phi_0, d_phi_0, mu), g_u = mt_dpsi(d_phi_0, d_phi_0, mu);
+        bool interval_converged = (step_max - step_min) < 0, open_interval = true;
         a_t = delta_p_norm;
-        a_t = std::min(a_t, P.step_size);
-        a_t = std::max(a_t, P.trans_epsilon / 2);
+        a_t = std::min(a_t, step_max);
+        a_t = std::max(a_t, step_min);
         double x_t[6];
         for (int i = 0; i < 6; ++i) x_t[i] = p[i] + delta_p[i] * a_t;
         pose_to_T(x_t, final_T);
         rc = eval_pclomp(h, x_t, final_T, true, &score, g, H, &nvtl);
         if (rc != NDTB_OK) return rc;
         push_trace(x_t);
+        if (P.use_line_search) {
+          double phi_t = -score, d_phi_t = 0;
+          for (int i = 0; i < 6; ++i) d_phi_t += g[i] * delta_p[i];
+          d_phi_t = -d_phi_t;
+          double psi_t = mt_psi(a_t, phi_t, phi_0, d_phi_0, mu), d_psi_t = mt_dpsi(d_phi_t, d_phi_0, mu);
+          while (!interval_converged && step_iterations < max_step_iterations && !(psi_t <= 0 && d_phi_t <= -nu * d_phi_0)) {
+            if (open_interval) a_t = mt_trial_value(a_l, f_l, g_l, a_u, f_u, g_u, a_t, psi_t, d_psi_t);
+            else a_t = mt_trial_value(a_l, f_l, g_l, a_u, f_u, g_u, a_t, phi_t, d_phi_t);
+            a_t = std::min(a_t, step_max);
+            a_t = std::max(a_t, step_min);
+            for (int i = 0; i < 6; ++i) x_t[i] = p[i] + delta_p[i] * a_t;
+            pose_to_T(x_t, final_T);
+            rc = eval_pclomp(h, x_t, final_T, false, &score, g, H, &nvtl);  // score and gradient only (:1031)
+            if (rc != NDTB_OK) return rc;
+            phi_t = -score; d_phi_t = 0;
+            for (int i = 0; i < 6; ++i) d_phi_t += g[i] * delta_p[i];
+            d_phi_t = -d_phi_t;
+            psi_t = mt_psi(a_t, phi_t, phi_0, d_phi_0, mu);
+            d_psi_t = mt_dpsi(d_phi_t, d_phi_0, mu);
+            if (open_interval && (psi_t <= 0 && d_psi_t >= 0)) {
+              open_interval = false;
+              f_l = f_l + phi_0 - mu * d_phi_0 * a_l; g_l = g_l + mu * d_phi_0;
+              f_u = f_u + phi_0 - mu * d_phi_0 * a_u; g_u = g_u + mu * d_phi_0;
+            }
+            if (open_interval) interval_converged = mt_update_interval(a_l, f_l, g_l, a_u, f_u, g_u, a_t, psi_t, d_psi_t);
+            else interval_converged = mt_update_interval(a_l, f_l, g_l, a_u, f_u, g_u, a_t, phi_t, d_phi_t);
+            step_iterations++;
+          }
+        }
+        if (step_iterations) {  // the loop evaluated without Hessians: computeHessian, all FP64 (:1073)
+          rc = compute_hessian_f64(h, x_t, final_T, H);
+          if (rc != NDTB_OK) return rc;
+          push_trace(x_t);
+        }
       }
       delta_p_norm = a_t;
     }

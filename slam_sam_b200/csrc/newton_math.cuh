@@ -248,6 +248,51 @@ NM_HD void svd6_solve(const double* A, const double* b, double* x) {
   }
 }
 
+// ---- More-Thuente line search pieces (ndt_omp.h:473-489, ndt_omp_impl.hpp:805-911) -------------------------
+NM_HD double mt_psi(double a, double f_a, double f_0, double g_0, double mu) { return f_a - f_0 - mu * g_0 * a; }
+NM_HD double mt_dpsi(double g_a, double g_0, double mu) { return g_a - mu * g_0; }
+
+// Update Algorithm / Modified Update Algorithm: returns true when the interval has converged.
+NM_HD bool mt_update_interval(double& a_l, double& f_l, double& g_l, double& a_u, double& f_u, double& g_u, double a_t, double f_t, double g_t) {
+  if (f_t > f_l) { a_u = a_t; f_u = f_t; g_u = g_t; return false; }                                   // case U1 / a
+  if (g_t * (a_l - a_t) > 0) { a_l = a_t; f_l = f_t; g_l = g_t; return false; }                       // case U2 / b
+  if (g_t * (a_l - a_t) < 0) { a_u = a_l; f_u = f_l; g_u = g_l; a_l = a_t; f_l = f_t; g_l = g_t; return false; }  // case U3 / c
+  return true;
+}
+
+// Trial value selection: cubic / quadratic / secant minimisers of the four cases.
+NM_HD double mt_trial_value(double a_l, double f_l, double g_l, double a_u, double f_u, double g_u, double a_t, double f_t, double g_t) {
+  if (f_t > f_l) {
+    const double z = 3 * (f_t - f_l) / (a_t - a_l) - g_t - g_l;
+    const double w = sqrt(z * z - g_t * g_l);
+    const double a_c = a_l + (a_t - a_l) * (w - g_l - z) / (g_t - g_l + 2 * w);
+    const double a_q = a_l - 0.5 * (a_l - a_t) * g_l / (g_l - (f_l - f_t) / (a_l - a_t));
+    if (fabs(a_c - a_l) < fabs(a_q - a_l)) return a_c;
+    return 0.5 * (a_q + a_c);
+  }
+  if (g_t * g_l < 0) {
+    const double z = 3 * (f_t - f_l) / (a_t - a_l) - g_t - g_l;
+    const double w = sqrt(z * z - g_t * g_l);
+    const double a_c = a_l + (a_t - a_l) * (w - g_l - z) / (g_t - g_l + 2 * w);
+    const double a_s = a_l - (a_l - a_t) / (g_l - g_t) * g_l;
+    if (fabs(a_c - a_t) >= fabs(a_s - a_t)) return a_c;
+    return a_s;
+  }
+  if (fabs(g_t) <= fabs(g_l)) {
+    const double z = 3 * (f_t - f_l) / (a_t - a_l) - g_t - g_l;
+    const double w = sqrt(z * z - g_t * g_l);
+    const double a_c = a_l + (a_t - a_l) * (w - g_l - z) / (g_t - g_l + 2 * w);
+    const double a_s = a_l - (a_l - a_t) / (g_l - g_t) * g_l;
+    const double a_t_next = (fabs(a_c - a_t) < fabs(a_s - a_t)) ? a_c : a_s;
+    const double lim = a_t + 0.66 * (a_u - a_t);
+    if (a_t > a_l) return (a_t_next < lim) ? a_t_next : lim;  // std::min(lim, a_t_next)
+    return (lim < a_t_next) ? a_t_next : lim;                  // std::max(lim, a_t_next)
+  }
+  const double z = 3 * (f_t - f_u) / (a_t - a_u) - g_t - g_u;
+  const double w = sqrt(z * z - g_t * g_u);
+  return a_u + (a_t - a_u) * (w - g_u - z) / (g_t - g_u + 2 * w);
+}
+
 // Newton direction for a well-conditioned H: Gaussian elimination with complete pivoting plus one step of
 // iterative refinement.  Returns false (x untouched) unless the pivots certify cond(H) <~ 1/min_ratio; the caller
 // then takes svd6_solve, whose rank truncation is what the reference's JacobiSVD::solve does for a (nearly)

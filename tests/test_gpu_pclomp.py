@@ -139,6 +139,29 @@ def test_align_vs_golden(gold, search):
     assert rel_inf(r["hessian"], gold[f"align_{search}_hessian"]) <= TOL
 
 
+@pytest.mark.parametrize("step", [0.1, 0.5, 1.0])
+def test_align_with_line_search(oracle, gold, step):
+    """NdtParams::use_line_search: More-Thuente step length (ndt_omp_impl.hpp:995-1071) with gradient-only
+    evaluations inside the search and the all-FP64 computeHessian pass (:701-800) after a search that iterated."""
+    guess = np.eye(4, dtype=np.float32); guess[0, 3] = 0.8; guess[1, 3] = -0.5
+    h = ndtb.Handle(0)
+    h.set_params(resolution=2.0, max_iterations=35, trans_epsilon=0.01, step_size=step, use_line_search=1)
+    h.set_target(gold["target"]); h.set_source(gold["source"])
+    r = h.align(guess)
+    o = O.OracleNdt(resolution=2.0, max_iterations=35, trans_epsilon=0.01, step_size=step, use_line_search=True, num_threads=8)
+    o.set_target(gold["target"]); o.set_source(gold["source"])
+    ro = o.align(guess)
+    assert (r["iterations"], r["converged"]) == (ro["iterations"], ro["converged"])
+    tr, tg = h.trace(), ro["trace"]
+    assert tr.shape == tg.shape and len(tr) > r["iterations"] + 1        # the search iterated: extra FP64-Hessian rows
+    for a, b in zip(tr, tg):
+        assert np.abs(a[:6] - b[:6]).max() <= 1e-9
+        assert abs(a[6] - b[6]) <= TOL * abs(b[6]) and rel_inf(a[7:13], b[7:13]) <= TOL and rel_inf(a[13:49], b[13:49]) <= TOL
+    dt, da = pose_delta(r["T"], ro["T"])
+    assert dt <= 1e-4 and da <= 1e-5
+    assert rel_inf(r["hessian"], ro["hessian"]) <= TOL
+
+
 def test_reference_gtest_case_pclomp(oracle, two_plane):
     """Reads like TEST(ConvergenceComparison, PclOmp), test_svn_ndt.cpp:138-199."""
     ndt = registration.NormalDistributionsTransform()
