@@ -141,7 +141,7 @@ def run_gpu(args, rank, world, local_rank):
     import torch.distributed as dist
 
     from slam_sam_b200 import distributed as D
-    from slam_sam_b200 import ndtb
+    from slam_sam_b200 import ndtb, synth
 
     torch.cuda.set_device(local_rank)
     if world > 1:
@@ -158,9 +158,29 @@ def run_gpu(args, rank, world, local_rank):
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")  # > 126 MB L2
     torch.cuda.synchronize()
 
+    # sliding-window variant of the end-to-end step: the map window lives in HBM as 5 archived keyframe clouds (uploaded
+    # once, outside the timed region, like pointsArchive of run/pipeline_ligo_tc.cpp:519-526); per step the window is
+    # re-assembled on the device with the keyframes' poses, and only the new scan crosses PCIe
+    n_kf = 5
+    # identity poses: the assembled window is then bit-identical to the 1M-pt map of the other regions (same voxels, same
+    # Newton trajectories -- a non-trivial pose moves points by a float ulp, which this un-line-searched Newton loop
+    # amplifies into different iteration counts); the kernel does the same arithmetic for any pose
+    kf_poses = np.stack([np.eye(4) for j in range(n_kf)])
+    kf_ids = np.arange(n_kf, dtype=np.int64)
+    bounds = np.linspace(0, N_MAP, n_kf + 1).astype(int)
+    for j in range(n_kf):
+        Tinv = np.linalg.inv(kf_poses[j])
+        part = tgt[bounds[j]:bounds[j + 1], :3].astype(np.float64)
+        body = np.zeros((len(part), 4), np.float32)
+        body[:, :3] = (part @ Tinv[:3, :3].T + Tinv[:3, 3]).astype(np.float32)
+        assert h.keyframe_put(int(kf_ids[j]), body) == 0
+
     def step(i, resident):
         k = i % len(scans)
-        if resident:
+        if resident == "window":
+            rc = h.set_target_window(kf_ids, kf_poses)
+            rc |= h.L.ndtb_set_source(h.h, p_scans[k].data_ptr(), N_SCAN, 16)
+        elif resident:
             rc = h.set_target_device(d_tgt.data_ptr(), N_MAP)
             rc |= h.set_source_device(d_scans[k].data_ptr(), N_SCAN)
         else:
@@ -209,11 +229,13 @@ def run_gpu(args, rank, world, local_rank):
     h.set_profiling(False)
     total_ms, st = timed(True, args.steps, args.warmup)
     e2e_ms, st2 = timed(False, args.steps, args.warmup)
+    win_ms, st4 = timed("window", args.steps, args.warmup)
     h.set_profiling(True)
     roof_ms, st3 = timed(True, args.steps, 1)
     clk = clocks.stop()
     total_ms = D.max_over_ranks(total_ms, local_rank)
     e2e_ms = D.max_over_ranks(e2e_ms, local_rank)
+    win_ms = D.max_over_ranks(win_ms, local_rank)
     launches = int(D.sum_over_ranks(st["launches"], local_rank))
     if world > 1:
         dist.barrier()
@@ -245,6 +267,12 @@ def run_gpu(args, rank, world, local_rank):
                              "and a CUDA event pair around each (an empty launch between two events reads ~7 us on this box)"},
         "e2e": {"value": e2e, "unit": "scans/s", "h2d_bytes_per_step": 16 * (N_MAP + N_SCAN) + 64, "d2h_bytes_per_step": int(368 * st2["eval_launches"] / K + 64),
                 "ms_per_step": e2e_ms / K},
+        "e2e_window": {"value": world * K / (win_ms * 1e-3), "unit": "scans/s", "h2d_bytes_per_step": 16 * N_SCAN + 64 + 128 * n_kf,
+                       "d2h_bytes_per_step": int(368 * st4["eval_launches"] / K + 64), "ms_per_step": win_ms / K,
+                       "what": "same step through ndtb_set_target_window: the 1M-pt target is assembled on the device from 5 archived keyframe "
+                               "clouds (resident, uploaded once) with their poses (identity here, so the map is bit-identical to the other regions), "
+                               "then built; only the new scan is copied from pinned host memory",
+                       "max_abs_translation_error_m": st4["err"]},
         "gpu_launches": launches,
         "roofline": {"kernel": "eval_kernel_pclomp<7,hessian>", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": ncu_traffic(), "peak_source": peak_src, "algorithmic_bytes_per_launch": b_eval,

@@ -165,6 +165,21 @@ int ndtb_svn_finish_step(ndtb_handle h, int K, double* poses, const double* reco
 int ndtb_svn_mean_pose(int K, const double* poses, const double prior[16], double mean16[16]);
 int ndtb_svn_pose_distance(const double a[16], const double b[16], double* norm);
 
+/* ---- sliding-window target, assembled on the device ------------------------------------------------------
+ * The reference's pipelines keep every keyframe cloud in `pointsArchive` and, per frame, build the NDT target from
+ * the last few of them: `pcl::transformPointCloud(*archive.points, *cur, Tb2m.matrix()); *target += *cur;`
+ * (run/pipeline_ligo_tc.cpp:519-526, run/pipeline_lo_svn.cpp) followed by setInputTarget.  Here a keyframe cloud is
+ * uploaded once (ndtb_keyframe_put), and ndtb_set_target_window transforms the listed keyframes with their CURRENT
+ * pose estimates (row-major double 4x4, the arithmetic of pcl::transformPointCloud<PointT,double>), concatenates
+ * them in the given order and rebuilds the voxel map -- equivalent to the loop above + setInputTarget, with no
+ * per-frame host->device copy of the map window. */
+int ndtb_keyframe_put(ndtb_handle h, int64_t id, const float* xyz, size_t n, size_t stride_bytes);
+int ndtb_keyframe_drop(ndtb_handle h, int64_t id);
+int ndtb_keyframe_count(ndtb_handle h, size_t* count, size_t* total_points);
+int ndtb_set_target_window(ndtb_handle h, int n_keyframes, const int64_t* ids, const double* poses16);
+/* The current target cloud as packed x,y,z,w floats (device -> host copy; parity tests of the window assembly). */
+int ndtb_get_target_points(ndtb_handle h, float* xyzw, size_t capacity_points, size_t* n_points);
+
 /* ---- batch replay: n independent alignments against the current target ----------------------- */
 int ndtb_align_batch(ndtb_handle h, int n_scans, const float* const* xyz, const size_t* n_points, size_t stride_bytes,
                      const float* guesses16, ndtb_result* results);

@@ -22,6 +22,7 @@
 #include "ndtb.h"
 
 #include <cstddef>
+#include <cstdint>
 #include <cstring>
 #include <memory>
 #include <stdexcept>
@@ -153,6 +154,7 @@ public:
 
   void setInputTarget(const PointCloudTargetConstPtr& cloud) {  // ndt_omp.h:126-130 -> init() :324-330
     target_ = cloud;
+    window_target_ = false;
     push_params();
     target_rc_ = cloud ? ndtb_facade::upload(h_.h, *cloud, true) : NDTB_ERR_EMPTY;
   }
@@ -161,8 +163,26 @@ public:
     source_rc_ = cloud ? ndtb_facade::upload(h_.h, *cloud, false) : NDTB_ERR_EMPTY;
   }
 
+  // --- extension: sliding-window target kept on the device (replaces the transformPointCloud + `+=` loop of
+  // run/pipeline_ligo_tc.cpp:519-526 and the setInputTarget that follows it) ---------------------------------
+  int putKeyframe(std::int64_t id, const CloudTarget& cloud) {  // pointsArchive[id].points, uploaded once
+    using PointT = typename std::remove_reference<decltype(cloud.points[0])>::type;
+    return ndtb_keyframe_put(h_.h, id, cloud.points.empty() ? nullptr : reinterpret_cast<const float*>(cloud.points.data()), cloud.points.size(), sizeof(PointT));
+  }
+  int dropKeyframe(std::int64_t id) { return ndtb_keyframe_drop(h_.h, id); }
+  template <class Matrix4dLike>
+  void setInputTargetWindow(const std::vector<std::int64_t>& ids, const std::vector<Matrix4dLike>& poses_b2m) {
+    if (ids.size() != poses_b2m.size()) throw std::invalid_argument("ndtb: one pose per keyframe id");
+    std::vector<double> P(16 * ids.size());
+    for (std::size_t k = 0; k < ids.size(); ++k) ndtb_facade::to_rows(poses_b2m[k], 4, P.data() + 16 * k);
+    push_params();
+    target_.reset();
+    window_target_ = true;
+    target_rc_ = ndtb_set_target_window(h_.h, static_cast<int>(ids.size()), ids.data(), P.data());
+  }
+
   void setResolution(float resolution) {  // ndt_omp.h:135-142: rebuilds only if the value changed and a target is set
-    if (p_.resolution != resolution) { p_.resolution = resolution; if (target_) target_rc_ = push_params(); }
+    if (p_.resolution != resolution) { p_.resolution = resolution; if (target_ || window_target_) target_rc_ = push_params(); }
   }
   float getResolution() const { return p_.resolution; }
   double getStepSize() const { return p_.step_size; }
@@ -281,6 +301,7 @@ private:
   ndtb_params p_{};
   int num_threads_ = 1;
   PointCloudTargetConstPtr target_;
+  bool window_target_ = false;  // the target was assembled on the device from keyframes
   PointCloudSourceConstPtr source_;
   int target_rc_ = NDTB_ERR_NOT_READY, source_rc_ = NDTB_ERR_NOT_READY;
   Matrix4f final_transformation_;

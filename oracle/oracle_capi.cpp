@@ -148,4 +148,26 @@ int orc_ndt_align(void* h, const float* guess, float* final_T, double* hessian, 
   return 0;
 }
 
+// Sliding-window target assembly (run/pipeline_ligo_tc.cpp:519-526): for every keyframe, in order,
+//   pcl::transformPointCloud(*archive.points, *cur, Tb2m.matrix());   *target += *cur;
+// pcl::transformPointCloud<PointT, double> is PCL code (>= 1.14, common/impl/transforms.hpp, not vendored in the
+// reference): generic Transformer<double>::se3 -- out[r] = float(T(r,0)*x + T(r,1)*y + T(r,2)*z + T(r,3)) evaluated
+// left to right in double, out[3] = 1 (the reference is built without -mavx, so no AVX specialisation).
+// clouds: n_keyframes pointers to float arrays with `stride` floats per point; poses: n x 16 row-major doubles;
+// out: packed x,y,z,w floats for sum(n_points) points.
+void orc_assemble_window(int n_keyframes, const float* const* clouds, const size_t* n_points, size_t stride, const double* poses16, float* out) {
+  size_t o = 0;
+  for (int k = 0; k < n_keyframes; ++k) {
+    const double* T = poses16 + 16 * static_cast<size_t>(k);
+    for (size_t i = 0; i < n_points[k]; ++i, ++o) {
+      const float* s = clouds[k] + stride * i;
+      const double p[3] = {s[0], s[1], s[2]};
+      out[4 * o + 0] = static_cast<float>(T[0] * p[0] + T[1] * p[1] + T[2] * p[2] + T[3]);
+      out[4 * o + 1] = static_cast<float>(T[4] * p[0] + T[5] * p[1] + T[6] * p[2] + T[7]);
+      out[4 * o + 2] = static_cast<float>(T[8] * p[0] + T[9] * p[1] + T[10] * p[2] + T[11]);
+      out[4 * o + 3] = 1.0f;
+    }
+  }
+}
+
 }  // extern "C"

@@ -3,6 +3,7 @@
 #include "../../include/ndtb.h"
 #include "build_api.cuh"
 #include "eval_api.cuh"
+#include <map>
 #include <string>
 #include <vector>
 
@@ -17,6 +18,10 @@ struct ndtb_handle_s {
   float4* d_target = nullptr; size_t n_target = 0, target_alloc = 0; bool target_owned = true;
   float4* d_source = nullptr; size_t n_source = 0, source_alloc = 0; bool source_owned = true;
   void* h_stage = nullptr; size_t stage_alloc = 0;  // pinned staging for strided host clouds
+
+  // keyframe archive (pointsArchive of the reference's pipelines): clouds uploaded once, windows assembled on device
+  struct Keyframe { float4* d_points = nullptr; size_t n = 0; };
+  std::map<int64_t, Keyframe> keyframes;
 
   ndtb::DeviceGrid grid;
   float built_resolution = 0.f; int built_min_pts = 0; int built_flavour = -1; double built_eig = 0;
@@ -60,5 +65,7 @@ struct ndtb_handle_s {
 namespace ndtb {
 int ensure_eval_buffers(ndtb_handle_s* h, int particles, int n_points);
 int set_error(ndtb_handle_s* h, int code, const char* what);
+int upload_cloud(ndtb_handle_s* h, const float* xyz, size_t n, size_t stride_bytes, float4** d_buf, size_t* alloc, bool* owned);
+int rebuild_grid(ndtb_handle_s* h);
 int compute_hessian_f64(ndtb_handle_s* h, const double* p, const float* T16, double* H);  // line_search.cu
 }  // namespace ndtb

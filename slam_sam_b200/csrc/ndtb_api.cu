@@ -48,7 +48,7 @@ int ensure_eval_buffers(ndtb_handle_s* h, int particles, int n_points) {
   return NDTB_OK;
 }
 
-static int upload_cloud(ndtb_handle_s* h, const float* xyz, size_t n, size_t stride_bytes, float4** d_buf, size_t* alloc, bool* owned) {
+int upload_cloud(ndtb_handle_s* h, const float* xyz, size_t n, size_t stride_bytes, float4** d_buf, size_t* alloc, bool* owned) {
   if (!*owned) { *d_buf = nullptr; *alloc = 0; *owned = true; }
   if (n > *alloc) {
     cudaFree(*d_buf);
@@ -72,7 +72,7 @@ static int upload_cloud(ndtb_handle_s* h, const float* xyz, size_t n, size_t str
   return NDTB_OK;
 }
 
-static int rebuild_grid(ndtb_handle_s* h) {
+int rebuild_grid(ndtb_handle_s* h) {
   if (!h->d_target || h->n_target == 0) return NDTB_ERR_EMPTY;
   cudaEventRecord(h->ev[0], h->stream);
   const int min_pts = (h->params.grid_flavour == NDTB_FLAVOUR_SVN) ? std::max(3, h->params.min_points_per_voxel) : h->params.min_points_per_voxel;
@@ -328,6 +328,7 @@ int ndtb_destroy(ndtb_handle h) {
   if (h->h_flag) cudaFreeHost(const_cast<unsigned int*>(h->h_flag));
   if (h->h_mailbox) cudaFreeHost(h->h_mailbox);
   cudaFree(h->d_cmd);
+  for (auto& kv : h->keyframes) cudaFree(kv.second.d_points);
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   cudaFree(h->d_svn_in); cudaFree(h->d_svn_out);
   for (int i = 0; i < 4; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);

@@ -51,7 +51,8 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "nd
            "ndtb_compute_derivatives", "ndtb_align", "ndtb_get_trace", "ndtb_calculate_scores", "ndtb_get_voxel_count", "ndtb_get_voxels",
            "ndtb_get_last_hits", "ndtb_svn_default_params", "ndtb_svn_set_params", "ndtb_svn_particle_derivatives", "ndtb_svn_stage2",
            "ndtb_svn_step", "ndtb_svn_align", "ndtb_svn_stage1_local", "ndtb_svn_finish_step", "ndtb_align_batch", "ndtb_get_timings",
-           "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_set_profiling", "ndtb_set_option", "ndtb_newton_direction", "ndtb_svn_mean_pose", "ndtb_svn_pose_distance"]
+           "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_set_profiling", "ndtb_set_option", "ndtb_newton_direction", "ndtb_keyframe_put", "ndtb_keyframe_drop", "ndtb_keyframe_count",
+           "ndtb_set_target_window", "ndtb_get_target_points", "ndtb_svn_mean_pose", "ndtb_svn_pose_distance"]
 
 _LIB = None
 
@@ -104,6 +105,11 @@ def lib():
         L.ndtb_get_launch_count.argtypes = [H, C.POINTER(C.c_uint64)]
         L.ndtb_set_profiling.argtypes = [H, C.c_int]
         L.ndtb_set_option.argtypes = [H, C.c_char_p, C.c_double]
+        L.ndtb_keyframe_put.argtypes = [H, C.c_int64, C.c_void_p, C.c_size_t, C.c_size_t]
+        L.ndtb_keyframe_drop.argtypes = [H, C.c_int64]
+        L.ndtb_keyframe_count.argtypes = [H, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]
+        L.ndtb_set_target_window.argtypes = [H, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_double)]
+        L.ndtb_get_target_points.argtypes = [H, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.ndtb_newton_direction.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.ndtb_svn_mean_pose.argtypes = [C.c_int, c_d, c_d, c_d]
         L.ndtb_svn_pose_distance.argtypes = [c_d, c_d, c_d]
@@ -282,6 +288,33 @@ class Handle:
 
     def set_profiling(self, on):
         self.check(self.L.ndtb_set_profiling(self.h, int(bool(on))))
+
+    def keyframe_put(self, kid, cloud):
+        """Upload a keyframe cloud once (pointsArchive entry); float32 (n, 3|4|8) array."""
+        a, n, st = host_cloud(cloud)
+        return self.L.ndtb_keyframe_put(self.h, int(kid), a.ctypes.data, n, st)
+
+    def keyframe_drop(self, kid):
+        return self.L.ndtb_keyframe_drop(self.h, int(kid))
+
+    def keyframe_count(self):
+        c = C.c_size_t(); t = C.c_size_t()
+        self.L.ndtb_keyframe_count(self.h, C.byref(c), C.byref(t))
+        return c.value, t.value
+
+    def set_target_window(self, ids, poses):
+        """Transform the listed keyframes by their poses (n x 4 x 4 float64), concatenate, rebuild the voxel map."""
+        ids = np.ascontiguousarray(ids, np.int64)
+        P = np.ascontiguousarray(poses, np.float64).reshape(len(ids), 16)
+        return self.L.ndtb_set_target_window(self.h, len(ids), ids.ctypes.data_as(C.POINTER(C.c_int64)), _ptr(P, c_d))
+
+    def target_points(self):
+        n = C.c_size_t()
+        self.check(self.L.ndtb_get_target_points(self.h, None, 0, C.byref(n)))
+        out = np.zeros((n.value, 4), np.float32)
+        if n.value:
+            self.check(self.L.ndtb_get_target_points(self.h, out.ctypes.data, n.value, C.byref(n)))
+        return out
 
     def set_option(self, name, value):
         """ndtb_set_option: "direct_solver", "sessions", "session_idle_timeout_ms"."""

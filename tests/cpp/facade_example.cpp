@@ -52,6 +52,18 @@ int main(int argc, char** argv) {
     for (int i = 0; i < 16; ++i) prior(i / 4, i % 4) = guess(i / 4, i % 4);
     const svn_ndt::SvnNdtResult s = svn.align(*load(argv[2]), prior, nullptr, 7);
     std::printf("svn %d %d %.9g\n", s.converged ? 1 : 0, s.iterations, s.final_pose(0, 3));
+    // the same pclomp alignment with the target assembled on the device from an archived keyframe (identity pose)
+    pclomp::NormalDistributionsTransform<PointXYZ, PointXYZ> win;
+    win.setResolution(1.0f); win.setMaximumIterations(50); win.setTransformationEpsilon(1e-4); win.setStepSize(0.1);
+    win.putKeyframe(7, *load(argv[1]));
+    win.setInputTargetWindow(std::vector<std::int64_t>{7}, std::vector<ndtb_facade::Matrix4d>{ndtb_facade::identity<ndtb_facade::Matrix4d>()});
+    win.setInputSource(load(argv[2]));
+    Cloud aligned2;
+    win.align(aligned2, guess);
+    const auto Tw = win.getFinalTransformation();
+    std::printf("win %d %d", win.hasConverged() ? 1 : 0, win.getFinalNumIteration());
+    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) std::printf(" %.9g", static_cast<double>(Tw(i, j)));
+    std::printf("\n");
   }
   return 0;
 }

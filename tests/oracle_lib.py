@@ -55,6 +55,8 @@ def lib():
         L.orc_ndt_compute_derivatives_T.argtypes = [C.c_void_p, c_f, c_d, C.c_int, c_d, c_d, c_d]
         L.orc_ndt_calculate_scores.argtypes = [C.c_void_p, c_f, c_d, c_d]
         L.orc_ndt_align.argtypes = [C.c_void_p, c_f, c_f, c_d, c_d, c_d, c_i, c_i, c_d, C.c_int, c_i, c_f, C.c_int, c_i]
+        L.orc_assemble_window.argtypes = [C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.c_size_t, c_d, c_f]
+        L.orc_assemble_window.restype = None
         L.orc_svn_create.restype = C.c_void_p
         L.orc_svn_destroy.argtypes = [C.c_void_p]
         L.orc_svn_grid.restype = C.c_void_p
@@ -133,6 +135,20 @@ class OracleGrid:
             lib().orc_grid_destroy(self.h)
         except Exception:
             pass
+
+
+def assemble_window(clouds, poses):
+    """Sliding-window target: every keyframe cloud moved by its double 4x4 pose (pcl::transformPointCloud<.,double>),
+    concatenated in order.  Returns packed (sum n, 4) float32 with w = 1."""
+    arrs = [as_xyz(c) for c in clouds]
+    stride = arrs[0].shape[1]
+    assert all(a.shape[1] == stride for a in arrs)
+    ptrs = (C.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs])
+    ns = (C.c_size_t * len(arrs))(*[a.shape[0] for a in arrs])
+    P = np.ascontiguousarray(poses, np.float64).reshape(len(arrs), 16)
+    out = np.zeros((sum(a.shape[0] for a in arrs), 4), np.float32)
+    lib().orc_assemble_window(len(arrs), ptrs, ns, stride, _d(P), _f(out))
+    return out
 
 
 class OracleNdt:

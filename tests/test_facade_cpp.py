@@ -54,3 +54,5 @@ def test_facade_matches_python_binding(two_plane, tmp_path):
     assert np.abs(T - ndt.getFinalTransformation()).max() <= 1e-6
     assert int(f[18]) == len(two_plane["source"]) and int(f[19]) == len(ndt.getTargetCells()["idx"])
     assert lines[1].startswith("svn ") and int(lines[1].split()[2]) == 5
+    w = lines[2].split()   # device-assembled window of one identity-pose keyframe == the uploaded target
+    assert w[0] == "win" and w[1:3] == f[0:2] and w[3:19] == f[2:18]

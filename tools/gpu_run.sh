@@ -1,1 +1,2 @@
-timeout 600 python -m pytest tests/test_gpu_pclomp.py tests/test_gpu_session.py -x -q 2>&1 | tail -15
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
+timeout 200 python __graft_entry__.py smoke 2>&1 | tail -1
