@@ -205,6 +205,11 @@ int ndtb_set_option(ndtb_handle h, const char* name, double value);
 /* The Newton-direction solve of ndtb_align on its own (host code, no GPU): x = H^-1 b by the path "direct_solver"
  * selects (method 1; falls back to the SVD when H is not certified well conditioned) or by the Jacobi SVD with
  * Eigen's rank threshold (method 0).  *used_direct reports which one produced x.  Parity hook for the tests. */
+/* The step after align in the reference's pipelines (run/pipeline_ligo_tc.cpp:536-542, src/registercallback.cpp:170-186):
+ * lidar factor covariance = -(hessian + 1e-6 I)^-1, reordered from NDT's (translation, rotation) to GTSAM's
+ * (rotation, translation) block order.  Host code, row-major 6x6 in and out; a singular matrix yields NaNs (as
+ * Eigen's inverse() would yield non-finite values). */
+int ndtb_hessian_to_covariance(const double hessian[36], double covariance_gtsam[36]);
 int ndtb_newton_direction(const double H[36], const double b[6], int method, double x[6], int* used_direct);
 /* Number of CUDA kernels this handle has launched since creation (bench.py's gpu_launches). */
 int ndtb_get_launch_count(ndtb_handle h, uint64_t* launches);

@@ -655,6 +655,28 @@ int ndtb_set_profiling(ndtb_handle h, int per_kernel_events) {
   return NDTB_OK;
 }
 
+int ndtb_hessian_to_covariance(const double hessian[36], double covariance_gtsam[36]) {
+  if (!hessian || !covariance_gtsam) return NDTB_ERR_INVALID;
+  double A[36], inv[36];
+  for (int i = 0; i < 36; ++i) A[i] = hessian[i];
+  for (int i = 0; i < 6; ++i) A[7 * i] = A[7 * i] + 1e-6;
+  for (int j = 0; j < 6; ++j) {
+    double e[6] = {0, 0, 0, 0, 0, 0}, x[6];
+    e[j] = 1.0;
+    const bool ok = gecp6_solve(A, e, x, 0.0);
+    for (int i = 0; i < 6; ++i) inv[6 * i + j] = ok ? -x[i] : NAN;
+  }
+  // reorderCovarianceForGTSAM: C_rr -> top-left, C_tt -> bottom-right, the two cross blocks stay where they are
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) {
+      covariance_gtsam[6 * (3 + r) + (3 + c)] = inv[6 * r + c];
+      covariance_gtsam[6 * r + c] = inv[6 * (3 + r) + (3 + c)];
+      covariance_gtsam[6 * r + (3 + c)] = inv[6 * r + (3 + c)];
+      covariance_gtsam[6 * (3 + r) + c] = inv[6 * (3 + r) + c];
+    }
+  return NDTB_OK;
+}
+
 int ndtb_newton_direction(const double H[36], const double b[6], int method, double x[6], int* used_direct) {
   if (!H || !b || !x) return NDTB_ERR_INVALID;
   const bool direct = method != 0 && gecp6_solve(H, b, x, 1e-6);

@@ -51,7 +51,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "nd
            "ndtb_compute_derivatives", "ndtb_align", "ndtb_get_trace", "ndtb_calculate_scores", "ndtb_get_voxel_count", "ndtb_get_voxels",
            "ndtb_get_last_hits", "ndtb_svn_default_params", "ndtb_svn_set_params", "ndtb_svn_particle_derivatives", "ndtb_svn_stage2",
            "ndtb_svn_step", "ndtb_svn_align", "ndtb_svn_stage1_local", "ndtb_svn_finish_step", "ndtb_align_batch", "ndtb_get_timings",
-           "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_set_profiling", "ndtb_set_option", "ndtb_newton_direction", "ndtb_keyframe_put", "ndtb_keyframe_drop", "ndtb_keyframe_count",
+           "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_set_profiling", "ndtb_set_option", "ndtb_newton_direction", "ndtb_hessian_to_covariance", "ndtb_keyframe_put", "ndtb_keyframe_drop", "ndtb_keyframe_count",
            "ndtb_set_target_window", "ndtb_get_target_points", "ndtb_svn_mean_pose", "ndtb_svn_pose_distance"]
 
 _LIB = None
@@ -105,6 +105,7 @@ def lib():
         L.ndtb_get_launch_count.argtypes = [H, C.POINTER(C.c_uint64)]
         L.ndtb_set_profiling.argtypes = [H, C.c_int]
         L.ndtb_set_option.argtypes = [H, C.c_char_p, C.c_double]
+        L.ndtb_hessian_to_covariance.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.ndtb_keyframe_put.argtypes = [H, C.c_int64, C.c_void_p, C.c_size_t, C.c_size_t]
         L.ndtb_keyframe_drop.argtypes = [H, C.c_int64]
         L.ndtb_keyframe_count.argtypes = [H, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]
@@ -143,6 +144,15 @@ def svn_pose_distance(a, b):
     if rc != NDTB_OK:
         raise NdtbError(rc, "ndtb_svn_pose_distance")
     return float(n[0])
+
+
+def hessian_to_covariance(H):
+    """-(H + 1e-6 I)^-1 in GTSAM block order (run/pipeline_ligo_tc.cpp:536-542)."""
+    H = np.ascontiguousarray(H, np.float64).reshape(36); out = np.zeros(36)
+    rc = lib().ndtb_hessian_to_covariance(_ptr(H, c_d), _ptr(out, c_d))
+    if rc != NDTB_OK:
+        raise NdtbError(rc, "ndtb_hessian_to_covariance")
+    return out.reshape(6, 6)
 
 
 def newton_direction(H, b, method=1):

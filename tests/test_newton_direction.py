@@ -60,3 +60,16 @@ def test_ill_conditioned_uses_svd():
     x, used = ndtb.newton_direction(H, np.ones(6), method=1)
     assert not used
     np.testing.assert_allclose(x, -1.0 / np.diag(-H) * 1.0, rtol=1e-12)
+
+
+def test_hessian_to_covariance_matches_reference_formula():
+    """run/pipeline_ligo_tc.cpp:536-542 + RegisterCallback::reorderCovarianceForGTSAM (src/registercallback.cpp:170-186)."""
+    rng = np.random.default_rng(9)
+    for _ in range(50):
+        H, _ = ndt_like_hessian(rng)
+        inv = -np.linalg.inv(H + 1e-6 * np.eye(6))
+        want = np.zeros((6, 6))
+        want[3:, 3:] = inv[:3, :3]; want[:3, :3] = inv[3:, 3:]; want[:3, 3:] = inv[:3, 3:]; want[3:, :3] = inv[3:, :3]
+        got = ndtb.hessian_to_covariance(H)
+        assert np.abs(got - want).max() <= 1e-9 * np.abs(want).max()
+    assert np.isnan(ndtb.hessian_to_covariance(-1e-6 * np.eye(6))).all()   # H + 1e-6 I singular
