@@ -156,13 +156,15 @@ __device__ __forceinline__ void pclomp_terms(const PointTables& pt, const float 
 //   16..21: (xh6,xh9) (xh7,xh10) (xh8,xh11) | 22,23: xh4 xh5 | 24..26: xh12 xh13 xh14
 __device__ __forceinline__ float2 bc2(float x) { return make_float2(x, x); }
 __device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
-// The additions stay SCALAR on purpose: ptxas 12.9 contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even with
-// explicit .rn and --fmad=false (checked with cuobjdump), which would change the reference's two-rounding
-// arithmetic; scalar add.rn.f32 is never contracted.
-__device__ __forceinline__ float2 add2(float2 a, float2 b) { return make_float2(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y)); }
+// Packed additions: ptxas 12.9 contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even with explicit .rn and
+// --fmad=false (checked with cuobjdump), which would change the reference's two-rounding arithmetic.  An addition
+// written as fma(a, 1, b) cannot be contracted with the multiply that produced `a` (a*1+b rounds once and is
+// exactly a+b, signed zeros and NaNs included), provided ptxas cannot see that the multiplier is 1: it comes from
+// the evaluation state (EvalState::one), i.e. from the constant bank or shared memory.
+__device__ __forceinline__ float2 add2(float2 a, float2 b, float2 one2) { return __ffma2_rn(a, one2, b); }
 // (a0*b0 + a1*b1) + a2*b2 on pairs: dot3's association
-__device__ __forceinline__ float2 dot3_2(float a0, float a1, float a2, float2 b0, float2 b1, float2 b2) {
-  return add2(add2(mul2(bc2(a0), b0), mul2(bc2(a1), b1)), mul2(bc2(a2), b2));
+__device__ __forceinline__ float2 dot3_2(float a0, float a1, float a2, float2 b0, float2 b1, float2 b2, float2 one2) {
+  return add2(add2(mul2(bc2(a0), b0), mul2(bc2(a1), b1), one2), mul2(bc2(a2), b2), one2);
 }
 
 template <bool HESS>
@@ -170,7 +172,8 @@ template <bool HESS>
 //   tp[0] = (score, 0) | tp[1..3] = (g0,g1) (g2,g3) (g4,g5) | tp[4 + 3j + p] = (H(2p, j), H(2p+1, j)), j = 0..5, p = 0..2
 // pair_word_component() maps a word of this layout back to the RED_* index.
 __device__ __forceinline__ void pclomp_terms2(const float4* __restrict__ sp, const float x4[3], const float C[9], float d2f, double d1,
-                                              float2* __restrict__ tp) {
+                                              float one, float2* __restrict__ tp) {
+  const float2 one2 = bc2(one);
   const float4 s1 = sp[1], s2 = sp[2];
   const float xj0 = s1.x, xj1 = s1.y;
   const float2 J25 = make_float2(s1.z, s1.w), J36 = make_float2(s2.x, s2.y), J47 = make_float2(s2.z, s2.w);
@@ -191,19 +194,19 @@ __device__ __forceinline__ void pclomp_terms2(const float4* __restrict__ sp, con
     const float c0 = C[3 * r], c1 = C[3 * r + 1], c2 = C[3 * r + 2];
     cj[r][0] = make_float2(c0, c1);
     cj[r][1] = make_float2(c2, c1 * xj0 + c2 * xj1);
-    cj[r][2] = dot3_2(c0, c1, c2, J25, J36, J47);
+    cj[r][2] = dot3_2(c0, c1, c2, J25, J36, J47, one2);
   }
   float2 xcj[3];
 #pragma unroll
-  for (int p = 0; p < 3; ++p) xcj[p] = dot3_2(x4[0], x4[1], x4[2], cj[0][p], cj[1][p], cj[2][p]);
+  for (int p = 0; p < 3; ++p) xcj[p] = dot3_2(x4[0], x4[1], x4[2], cj[0][p], cj[1][p], cj[2][p], one2);
   tp[0] = make_float2(reject ? 0.0f : score_inc, 0.0f);
   const float2 e2 = bc2(e);
 #pragma unroll
   for (int p = 0; p < 3; ++p) tp[1 + p] = mul2(e2, xcj[p]);
   if (HESS) {
     const float4 s3 = sp[3], s4 = sp[4], s5 = sp[5], s6 = sp[6];
-    const float2 hab = add2(mul2(bc2(xC[1]), make_float2(s3.x, s3.y)), mul2(bc2(xC[2]), make_float2(s3.z, s3.w)));  // (h_a, h_b)
-    const float2 hde = dot3_2(xC[0], xC[1], xC[2], make_float2(s4.x, s4.y), make_float2(s4.z, s4.w), make_float2(s5.x, s5.y));  // (h_d, h_e)
+    const float2 hab = add2(mul2(bc2(xC[1]), make_float2(s3.x, s3.y)), mul2(bc2(xC[2]), make_float2(s3.z, s3.w)), one2);  // (h_a, h_b)
+    const float2 hde = dot3_2(xC[0], xC[1], xC[2], make_float2(s4.x, s4.y), make_float2(s4.z, s4.w), make_float2(s5.x, s5.y), one2);  // (h_d, h_e)
     const float h_c = xC[1] * s5.z + xC[2] * s5.w;
     const float h_f = dot3(xC[0], xC[1], xC[2], s6.x, s6.y, s6.z);
     // xCH rows for i = 3,4,5 and columns j = 3,4,5: [a b c; b d e; c e f]
@@ -222,13 +225,13 @@ __device__ __forceinline__ void pclomp_terms2(const float4* __restrict__ sp, con
       for (int p = 0; p < 3; ++p) {
         float2 jc;  // JCJ(j, i) for i = 2p, 2p+1
         if (j < 3) jc = cj[j][p];
-        else if (j == 3) jc = add2(mul2(bc2(xjs[0]), cj[1][p]), mul2(bc2(xjs[1]), cj[2][p]));
-        else if (j == 4) jc = dot3_2(xjs[2], xjs[3], xjs[4], cj[0][p], cj[1][p], cj[2][p]);
-        else jc = dot3_2(xjs[5], xjs[6], xjs[7], cj[0][p], cj[1][p], cj[2][p]);
+        else if (j == 3) jc = add2(mul2(bc2(xjs[0]), cj[1][p]), mul2(bc2(xjs[1]), cj[2][p]), one2);
+        else if (j == 4) jc = dot3_2(xjs[2], xjs[3], xjs[4], cj[0][p], cj[1][p], cj[2][p], one2);
+        else jc = dot3_2(xjs[5], xjs[6], xjs[7], cj[0][p], cj[1][p], cj[2][p], one2);
         float2 v = mul2(ap[p], xcjj2);
         if (j >= 3 && p == 1) v.y = v.y + xch3[j - 3];
-        if (j >= 3 && p == 2) v = add2(v, xch45[j - 3]);
-        v = add2(v, jc);
+        if (j >= 3 && p == 2) v = add2(v, xch45[j - 3], one2);
+        v = add2(v, jc, one2);
         tp[4 + 3 * j + p] = mul2(e2, v);
       }
     }
@@ -746,7 +749,7 @@ __device__ __forceinline__ void pclomp_round(bool active, int slot, int row, PtS
     x4[0] = static_cast<float>(static_cast<double>(pa.x) - m0);
     x4[1] = static_cast<float>(static_cast<double>(pa.y) - m1);
     x4[2] = static_cast<float>(static_cast<double>(pa.z) - m2);
-    pclomp_terms2<HESS>(sp, x4, C, d2f, st.d1, tp);
+    pclomp_terms2<HESS>(sp, x4, C, d2f, st.d1, st.one, tp);
     if (!HESS) {
 #pragma unroll
       for (int i = 4; i < 22; ++i) tp[i] = make_float2(0.0f, 0.0f);

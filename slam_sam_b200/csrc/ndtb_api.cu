@@ -93,6 +93,7 @@ static void fill_state(ndtb_handle_s* h, int slot, const double* p, const float*
   EvalState& s = h->h_states[slot];
   std::memset(&s, 0, sizeof(s));
   std::memcpy(s.T, T16, 12 * sizeof(float));
+  s.one = 1.0f;
   angle_tables(p, snap, s.jang, s.hang);
   if (svn) gauss_svn(h->params.outlier_ratio, h->params.resolution, &s.d1, &s.d2, &s.d3);
   else gauss_pclomp(h->params.outlier_ratio, h->params.resolution, &s.d1, &s.d2, &s.d3);

@@ -51,7 +51,7 @@ struct EvalState {
   float T[12];       // rows 0..2 of the float 4x4 that transforms the source cloud
   float jang[24];    // j_ang  8 x 3 (ndt_omp_impl.hpp:442-464)
   float hang[45];    // h_ang 15 x 3 (ndt_omp_impl.hpp:490-536)
-  float pad0;
+  float one;         // 1.0f, opaque to the compiler: multiplier of the packed fma(a, 1, b) additions (derivatives.cu add2)
   double d1, d2, d3; // gauss constants (ndt_omp_impl.hpp:95-99)
   double p[6];       // pose vector of this evaluation
 };
