@@ -257,6 +257,19 @@ class Handle:
                     iterations=r.iteration_num, converged=bool(r.converged), evaluations=r.evaluations,
                     transformation_array=arr[: r.transformation_array_len].reshape(-1, 4, 4).copy())
 
+    def align_batch(self, scans, guesses):
+        """ndtb_align_batch: n independent scans (each float32 (n_i, 4)) against the current target; one result per scan."""
+        arrs = [np.ascontiguousarray(sc, np.float32) for sc in scans]
+        assert all(a.ndim == 2 and a.shape[1] == 4 for a in arrs)
+        ptrs = (C.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs])
+        ns = (C.c_size_t * len(arrs))(*[a.shape[0] for a in arrs])
+        g = np.ascontiguousarray(guesses, np.float32).reshape(len(arrs), 16)
+        res = (Result * len(arrs))()
+        self.check(self.L.ndtb_align_batch(self.h, len(arrs), ptrs, ns, 16, _ptr(g, c_f), res))
+        return [dict(T=np.array(r.pose, np.float32).reshape(4, 4), hessian=np.array(r.hessian).reshape(6, 6),
+                     trans_probability=r.transform_probability, nvtl=r.nearest_voxel_transformation_likelihood,
+                     iterations=r.iteration_num, converged=bool(r.converged), evaluations=r.evaluations) for r in res]
+
     def trace(self, capacity=128):
         t = np.zeros((capacity, 50)); n = np.zeros(1, np.int32)
         self.check(self.L.ndtb_get_trace(self.h, _ptr(t, c_d), capacity, _ptr(n, c_i)))
