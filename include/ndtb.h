@@ -211,6 +211,10 @@ int ndtb_set_option(ndtb_handle h, const char* name, double value);
  * Eigen's inverse() would yield non-finite values). */
 int ndtb_hessian_to_covariance(const double hessian[36], double covariance_gtsam[36]);
 int ndtb_newton_direction(const double H[36], const double b[6], int method, double x[6], int* used_direct);
+/* Duration of ONE derivative evaluation kernel (DIRECT1/7 as configured, with Hessian) at pose p / transform T16,
+ * measured as `reps` back-to-back launches between a single pair of CUDA events on the handle's stream: the event
+ * overhead (~7 us per pair on a B200 box) is amortised over the launches instead of being added to each. */
+int ndtb_time_eval_kernel(ndtb_handle h, const double p[6], const float* T16, int reps, float* mean_us);
 /* Number of CUDA kernels this handle has launched since creation (bench.py's gpu_launches). */
 int ndtb_get_launch_count(ndtb_handle h, uint64_t* launches);
 

@@ -650,6 +650,32 @@ int ndtb_get_launch_count(ndtb_handle h, uint64_t* launches) {
   return NDTB_OK;
 }
 
+int ndtb_time_eval_kernel(ndtb_handle h, const double p[6], const float* T16, int reps, float* mean_us) {
+  if (!h || !p || !mean_us || reps < 1) return NDTB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  if (!h->grid.built || h->n_source == 0) return set_error(h, NDTB_ERR_NOT_READY, "target and source must be set");
+  if (h->params.grid_flavour != NDTB_FLAVOUR_PCLOMP) return set_error(h, NDTB_ERR_INVALID, "pclomp entry point on an svn-flavour handle");
+  float Tloc[16];
+  if (T16) std::memcpy(Tloc, T16, sizeof(Tloc)); else pose_to_T(p, Tloc);
+  const int n = static_cast<int>(h->n_source);
+  int rc = ensure_eval_buffers(h, 1, n);
+  if (rc != NDTB_OK) return rc;
+  fill_state(h, 0, p, Tloc, 10e-5, false);
+  const int n_probe = (h->params.search_method == NDTB_DIRECT1) ? 1 : 7;
+  for (int warm = 0; warm < 2; ++warm)
+    CKH(launch_eval_pclomp(n_probe, true, h->d_source, n, h->grid.meta, h->grid.recs, h->grid.table, h->h_states[0], h->eval, h->h_results, 1ull, h->stream));
+  CKH(cudaEventRecord(h->ev[2], h->stream));
+  for (int r = 0; r < reps; ++r)
+    CKH(launch_eval_pclomp(n_probe, true, h->d_source, n, h->grid.meta, h->grid.recs, h->grid.table, h->h_states[0], h->eval, h->h_results, 1ull, h->stream));
+  CKH(cudaEventRecord(h->ev[3], h->stream));
+  CKH(cudaEventSynchronize(h->ev[3]));
+  float ms = 0;
+  CKH(cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]));
+  h->launches += static_cast<uint64_t>(reps) + 2;
+  *mean_us = ms * 1000.0f / static_cast<float>(reps);
+  return NDTB_OK;
+}
+
 int ndtb_set_profiling(ndtb_handle h, int per_kernel_events) {
   if (!h) return NDTB_ERR_INVALID;
   h->kernel_events = per_kernel_events != 0;

@@ -51,7 +51,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "nd
            "ndtb_compute_derivatives", "ndtb_align", "ndtb_get_trace", "ndtb_calculate_scores", "ndtb_get_voxel_count", "ndtb_get_voxels",
            "ndtb_get_last_hits", "ndtb_svn_default_params", "ndtb_svn_set_params", "ndtb_svn_particle_derivatives", "ndtb_svn_stage2",
            "ndtb_svn_step", "ndtb_svn_align", "ndtb_svn_stage1_local", "ndtb_svn_finish_step", "ndtb_align_batch", "ndtb_get_timings",
-           "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_set_profiling", "ndtb_set_option", "ndtb_newton_direction", "ndtb_hessian_to_covariance", "ndtb_keyframe_put", "ndtb_keyframe_drop", "ndtb_keyframe_count",
+           "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_set_profiling", "ndtb_set_option", "ndtb_time_eval_kernel", "ndtb_newton_direction", "ndtb_hessian_to_covariance", "ndtb_keyframe_put", "ndtb_keyframe_drop", "ndtb_keyframe_count",
            "ndtb_set_target_window", "ndtb_get_target_points", "ndtb_svn_mean_pose", "ndtb_svn_pose_distance"]
 
 _LIB = None
@@ -105,6 +105,7 @@ def lib():
         L.ndtb_get_launch_count.argtypes = [H, C.POINTER(C.c_uint64)]
         L.ndtb_set_profiling.argtypes = [H, C.c_int]
         L.ndtb_set_option.argtypes = [H, C.c_char_p, C.c_double]
+        L.ndtb_time_eval_kernel.argtypes = [H, C.POINTER(C.c_double), C.POINTER(C.c_float), C.c_int, C.POINTER(C.c_float)]
         L.ndtb_hessian_to_covariance.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.ndtb_keyframe_put.argtypes = [H, C.c_int64, C.c_void_p, C.c_size_t, C.c_size_t]
         L.ndtb_keyframe_drop.argtypes = [H, C.c_int64]
@@ -338,6 +339,14 @@ class Handle:
         if n.value:
             self.check(self.L.ndtb_get_target_points(self.h, out.ctypes.data, n.value, C.byref(n)))
         return out
+
+    def time_eval_kernel(self, p, T=None, reps=50):
+        """Mean duration (us) of one evaluation kernel over `reps` back-to-back launches between one CUDA event pair."""
+        p = np.ascontiguousarray(p, np.float64)
+        t = None if T is None else np.ascontiguousarray(T, np.float32).reshape(16)
+        us = np.zeros(1, np.float32)
+        self.check(self.L.ndtb_time_eval_kernel(self.h, _ptr(p, c_d), _ptr(t, c_f), int(reps), _ptr(us, c_f)))
+        return float(us[0])
 
     def set_option(self, name, value):
         """ndtb_set_option: "direct_solver", "sessions", "session_idle_timeout_ms"."""
