@@ -714,13 +714,9 @@ __device__ __forceinline__ void transposed_add(const float* __restrict__ s_tr, i
     const float* r = s_tr + (g + 8 * s) * TR_STRIDE;
     const float4 v0 = *reinterpret_cast<const float4*>(r + 4 * q);
     const float2 v1 = *reinterpret_cast<const float2*>(r + 16 + 2 * q);
-#ifdef EXP_HALF_CVT  // timing experiment only (wrong results): half of the conversions
-    a[0] += static_cast<double>(v0.x + v0.y); a[2] += static_cast<double>(v0.z + v0.w); a[4] += static_cast<double>(v1.x + v1.y);
-#else
     a[0] += static_cast<double>(v0.x); a[1] += static_cast<double>(v0.y);
     a[2] += static_cast<double>(v0.z); a[3] += static_cast<double>(v0.w);
     a[4] += static_cast<double>(v1.x); a[5] += static_cast<double>(v1.y);
-#endif
   }
 }
 
