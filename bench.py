@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- NDT align scans/s at 131 k points (BASELINE.json metric), one JSON line on stdout.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload map_align|svn]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload map_align|svn|replay]
 
 Workload `map_align` (default; BASELINE.json configs[1]): one step = target voxel-map build of a
 1 M-point synthetic map + full NDT align (DIRECT7, 1.0 m voxels) of one 131 072-point OS1-128-shaped
@@ -390,6 +390,90 @@ def run_gpu_svn(args, rank, world, local_rank):
             "clocks": clk}
 
 
+def run_gpu_replay(args, rank, world, local_rank):
+    """configs[3]: replay batch.  Every rank holds the (replicated, built once) 1M-pt map and aligns its own shard of the scans
+    through ndtb_align_batch from pinned host buffers; no data-path collective (weak scaling).  One step = one batch of 32 scans."""
+    import torch
+    import torch.distributed as dist
+
+    from slam_sam_b200 import distributed as D
+    from slam_sam_b200 import ndtb
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
+    tgt, scans, guesses, truths = make_workload(rank)
+    B = 32
+    h = ndtb.Handle(local_rank)
+    h.set_params(resolution=RESOLUTION, max_iterations=35, trans_epsilon=0.01, step_size=0.1, search_method=ndtb.DIRECT7)
+    assert h.set_target(tgt) == 0
+    pinned = [torch.from_numpy(s).pin_memory() for s in scans]
+    batch = [pinned[i % len(pinned)].numpy() for i in range(B)]
+    gb = np.stack([guesses[i % len(guesses)] for i in range(B)])
+    stream = torch.cuda.ExternalStream(h.stream_ptr(), device=local_rank)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
+
+    def timed(steps, warmup, interleave):
+        h.set_option("batch_interleave", interleave)
+        for _ in range(warmup):
+            h.align_batch(batch, gb)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        l0 = h.launch_count()
+        ev, evals, err = [], 0, 0.0
+        for _ in range(steps):
+            with torch.cuda.stream(stream):
+                flush.zero_()
+            e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            res = h.align_batch(batch, gb)
+            e1.record(stream)
+            ev.append((e0, e1))
+            evals += sum(r["evaluations"] for r in res)
+            err = max(err, max(float(np.abs(r["T"][:3, 3] - truths[i % len(truths)][:3, 3]).max()) for i, r in enumerate(res)))
+            assert all(r["converged"] for r in res)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        return sum(a.elapsed_time(b) for a, b in ev), dict(evals=evals, err=err, launches=h.launch_count() - l0)
+
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    steps = max(1, min(args.steps, 10))
+    ms, st = timed(steps, 3, 1)
+    ms_serial, st_s = timed(steps, 1, 0)
+    clk = clocks.stop()
+    ms = D.max_over_ranks(ms, local_rank); ms_serial = D.max_over_ranks(ms_serial, local_rank)
+    launches = int(D.sum_over_ranks(st["launches"], local_rank))
+    if world > 1:
+        dist.barrier(); dist.destroy_process_group()
+    if rank != 0:
+        return None
+    hbar = h.last_hits()[0]
+    b_eval = N_SCAN * (16 + 8 * 7 + 64 * hbar)
+    t_eval = ms * 1e-3 / st["evals"]        # wall time per evaluation with two alignments in flight: the GPU is never idle
+    peak, peak_src = measured_peak()
+    v = world * steps * B / (ms * 1e-3)
+    return {"metric": "NDT align scans/sec @131k pts (1/2/4/8 B200) + % gather-BW roofline vs CPU OMP", "value": v, "unit": "scans/s",
+            "n_gpus": world, "steps": steps, "warmup": 3, "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32 pair maths, f64 accumulate", "data": "synthetic",
+            "config": {"workload": "configs[3]: replay batch, 32 synthetic 131072-pt OS1-128-shaped scans per step and rank against a replicated 1M-pt map "
+                                   "(built once), DIRECT7, 1.0 m voxels, through ndtb_align_batch from pinned host buffers",
+                       "scans_per_step_per_rank": B, "parallelism": f"scan shards x{world} (no collective)", "l2": "256 MB flush between timed steps",
+                       "evaluations_per_scan": st["evals"] / (steps * B), "max_abs_translation_error_m": st["err"],
+                       "serial_scans_per_s": world * steps * B / (ms_serial * 1e-3),
+                       "note": "value == e2e: the batch entry point takes host buffers; two alignments are kept in flight on one stream "
+                               "(serial_scans_per_s is the same batch with batch_interleave = 0)"},
+            "e2e": {"value": v, "unit": "scans/s", "h2d_bytes_per_step": 16 * N_SCAN * B, "d2h_bytes_per_step": int(736 * st["evals"] / steps), "ms_per_step": ms / steps},
+            "gpu_launches": launches,
+            "roofline": {"kernel": "eval_kernel_pclomp<7,hessian>", "bound": "hbm", "achieved": b_eval / t_eval / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": b_eval / t_eval / 1e9 / peak, "traffic": ncu_traffic(), "peak_source": peak_src, "algorithmic_bytes_per_launch": b_eval,
+                         "mean_hits_per_point": hbar, "kernel_us": t_eval * 1e6,
+                         "note": "kernel_us here is WALL time per evaluation of the whole batch (launch gaps, uploads and host work included)"},
+            "clocks": clk}
+
+
 def run_reference(args, rank):
     if rank != 0:
         return None
@@ -415,7 +499,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="map_align", choices=["map_align", "svn"])
+    ap.add_argument("--workload", default="map_align", choices=["map_align", "svn", "replay"])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -425,6 +509,8 @@ def main():
         line = run_reference(args, rank)
     elif args.workload == "svn":
         line = run_gpu_svn(args, rank, world, local_rank)
+    elif args.workload == "replay":
+        line = run_gpu_replay(args, rank, world, local_rank)
     else:
         line = run_gpu(args, rank, world, local_rank)
     if line is not None:

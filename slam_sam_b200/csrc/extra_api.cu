@@ -99,17 +99,4 @@ int ndtb_calculate_scores(ndtb_handle h, const float T16[16], double* transforma
   return NDTB_OK;
 }
 
-// Replay batch: n independent source scans against the current target map, results in order.
-int ndtb_align_batch(ndtb_handle h, int n_scans, const float* const* xyz, const size_t* n_points, size_t stride_bytes, const float* guesses16,
-                     ndtb_result* results) {
-  if (!h || n_scans < 0 || !xyz || !n_points || !guesses16 || !results) return NDTB_ERR_INVALID;
-  for (int i = 0; i < n_scans; ++i) {
-    int rc = ndtb_set_source(h, xyz[i], n_points[i], stride_bytes);
-    if (rc != NDTB_OK) return rc;
-    rc = ndtb_align(h, guesses16 + 16 * i, results + i, nullptr, 0, nullptr);
-    if (rc != NDTB_OK) return rc;
-  }
-  return NDTB_OK;
-}
-
 }  // extern "C"

@@ -23,6 +23,12 @@ struct ndtb_handle_s {
   struct Keyframe { float4* d_points = nullptr; size_t n = 0; };
   std::map<int64_t, Keyframe> keyframes;
 
+  // ndtb_align_batch scratch, kept between calls (allocation costs milliseconds): three scan slots + a copy stream
+  struct BatchSlot { float4* d_src = nullptr; size_t alloc = 0; cudaEvent_t uploaded = nullptr; };
+  BatchSlot batch_slot[3];
+  cudaStream_t batch_copy_stream = nullptr;
+  double* batch_h_results = nullptr;    // pinned, 3 x 2 x (RED_N + 2) words
+
   ndtb::DeviceGrid grid;
   float built_resolution = 0.f; int built_min_pts = 0; int built_flavour = -1; double built_eig = 0;
 
@@ -41,6 +47,7 @@ struct ndtb_handle_s {
   bool session_open = false;
   bool use_sessions = true;             // off with per-kernel events (ndtb_set_profiling) or NDTB_NO_SESSION=1
   double session_idle_ms = 50.0;        // the resident kernel leaves after this long without a command
+  bool batch_interleave = true;         // ndtb_align_batch keeps two alignments in flight (ndtb_set_option "batch_interleave")
   bool direct_solver = true;            // Newton direction by pivoted elimination when well conditioned (ndtb_set_option)
   unsigned long long pending_time_key = 0;  // result key of the last session evaluation whose duration slot is unread
   double session_eval_ns = 0;           // device-side duration of the session evaluations of the last align
@@ -67,5 +74,7 @@ int ensure_eval_buffers(ndtb_handle_s* h, int particles, int n_points);
 int set_error(ndtb_handle_s* h, int code, const char* what);
 int upload_cloud(ndtb_handle_s* h, const float* xyz, size_t n, size_t stride_bytes, float4** d_buf, size_t* alloc, bool* owned);
 int rebuild_grid(ndtb_handle_s* h);
+void fill_eval_state(ndtb_handle_s* h, EvalState& s, const double* p, const float* T16, double snap, bool svn);
+void finish_eval(ndtb_handle_s* h, int n, const double* r, const double* p, double* score, double* g, double* H, double* nvtl);
 int compute_hessian_f64(ndtb_handle_s* h, const double* p, const float* T16, double* H);  // line_search.cu
 }  // namespace ndtb

@@ -89,8 +89,11 @@ int rebuild_grid(ndtb_handle_s* h) {
 }
 
 // Fill EvalState `slot` for pose p (angle tables on the host with libm, like the oracle's host code).
+void fill_eval_state(ndtb_handle_s* h, EvalState& s, const double* p, const float* T16, double snap, bool svn);
 static void fill_state(ndtb_handle_s* h, int slot, const double* p, const float* T16, double snap, bool svn) {
-  EvalState& s = h->h_states[slot];
+  fill_eval_state(h, h->h_states[slot], p, T16, snap, svn);
+}
+void fill_eval_state(ndtb_handle_s* h, EvalState& s, const double* p, const float* T16, double snap, bool svn) {
   std::memset(&s, 0, sizeof(s));
   std::memcpy(s.T, T16, 12 * sizeof(float));
   s.one = 1.0f;
@@ -168,6 +171,8 @@ static void session_end(ndtb_handle_s* h) {
   session_send(h, nullptr, 0, SESSION_QUIT);
   h->session_open = false;
 }
+
+void finish_eval(ndtb_handle_s* h, int n, const double* r, const double* p, double* score, double* g, double* H, double* nvtl);
 
 // One pclomp evaluation: upload state, launch, read back the 46-double result, apply the
 // regulariser (ndt_omp_impl.hpp:349-382) and NVTL (:384-389) on the host.
@@ -248,7 +253,12 @@ static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool
             n, nb, mn[0], mx[0], mn[1], mx[1], mn[2], mx[2], mn[3], mx[3], mx[4], mx[5]);
   }
   h->eval_launches += 1;
-  const double* r = rbuf;
+  finish_eval(h, n, rbuf, p, score, g, H, nvtl);
+  return NDTB_OK;
+}
+
+// Host epilogue of one evaluation: unpack the 46 reduced values, add the regulariser (ndt_omp_impl.hpp:349-382), NVTL (:384-389).
+void finish_eval(ndtb_handle_s* h, int n, const double* r, const double* p, double* score, double* g, double* H, double* nvtl) {
   double sc = r[RED_SCORE];
   std::memcpy(g, r + RED_G, 6 * sizeof(double));
   std::memcpy(H, r + RED_H, 36 * sizeof(double));
@@ -271,7 +281,6 @@ static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool
   }
   *score = sc;
   if (nvtl) *nvtl = found != 0 ? r[RED_NEAREST] / found : 0.0;
-  return NDTB_OK;
 }
 
 }  // namespace ndtb
@@ -330,6 +339,9 @@ int ndtb_destroy(ndtb_handle h) {
   if (h->h_mailbox) cudaFreeHost(h->h_mailbox);
   cudaFree(h->d_cmd);
   for (auto& kv : h->keyframes) cudaFree(kv.second.d_points);
+  for (auto& bs : h->batch_slot) { cudaFree(bs.d_src); if (bs.uploaded) cudaEventDestroy(bs.uploaded); }
+  if (h->batch_copy_stream) cudaStreamDestroy(h->batch_copy_stream);
+  if (h->batch_h_results) cudaFreeHost(h->batch_h_results);
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   cudaFree(h->d_svn_in); cudaFree(h->d_svn_out);
   for (int i = 0; i < 4; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
@@ -718,6 +730,7 @@ int ndtb_set_option(ndtb_handle h, const char* name, double value) {
   if (k == "direct_solver") h->direct_solver = value != 0;           // 0: always the Jacobi SVD (Eigen::JacobiSVD restatement)
   else if (k == "sessions") h->use_sessions = value != 0;            // 0: one kernel launch per evaluation
   else if (k == "session_idle_timeout_ms") h->session_idle_ms = value > 0 ? value : 50.0;
+  else if (k == "batch_interleave") h->batch_interleave = value != 0;  // 0: ndtb_align_batch aligns one scan after the other
   else return set_error(h, NDTB_ERR_INVALID, "unknown option");
   return NDTB_OK;
 }

@@ -90,3 +90,23 @@ def test_replay_batch_sharding_matches_serial(big):
             merged[i] = r
     for a, b in zip(serial, merged):
         assert np.array_equal(a["T"], b["T"]) and a["iterations"] == b["iterations"] and a["converged"] == b["converged"]
+    # the batch keeps two alignments in flight; every one of them must equal the stand-alone ndtb_align bit for bit
+    h.set_option("batch_interleave", 0)
+    one_by_one = h.align_batch(scans, np.stack(guesses))
+    for i, (a, b) in enumerate(zip(serial, one_by_one)):
+        h.set_source(scans[i])
+        c = h.align(guesses[i], capacity=0)
+        for r in (b, c):
+            assert np.array_equal(a["T"], r["T"]) and np.array_equal(a["hessian"], r["hessian"])
+            assert (a["iterations"], a["converged"], a["evaluations"]) == (r["iterations"], r["converged"], r["evaluations"])
+            assert a["trans_probability"] == r["trans_probability"] and a["nvtl"] == r["nvtl"]
+    # ragged batch: different scan sizes, identity guess, a batch of one
+    h.set_option("batch_interleave", 1)
+    ragged = [np.ascontiguousarray(sc[: len(sc) - 101 * k]) for k, sc in enumerate(scans[:5])]
+    gg = np.stack(guesses[:5]); gg[2] = np.eye(4, dtype=np.float32)
+    rb = h.align_batch(ragged, gg)
+    for i, a in enumerate(rb):
+        h.set_source(ragged[i])
+        c = h.align(gg[i], capacity=0)
+        assert np.array_equal(a["T"], c["T"]) and a["iterations"] == c["iterations"]
+    assert np.array_equal(h.align_batch(ragged[:1], gg[:1])[0]["T"], rb[0]["T"])
