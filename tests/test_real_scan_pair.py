@@ -1,0 +1,76 @@
+"""The scan pair the reference ships (extern/ndt_omp/data/*.pcd), prepared as extern/ndt_omp/apps/align.cpp does
+(tests/golden/make_pcd_fixture.py: both clouds through a restated pcl::VoxelGrid at 0.1 m): REAL LiDAR data instead
+of synthetic scenes.
+
+* CPU: the oracle's alignment lands where the reference's README says this pair lands.  extern/ndt_omp/README.md:19-49
+  prints `fitness` (pcl::Registration::getFitnessScore, mean squared nearest-neighbour distance after align) for this
+  pair: 0.214205 (DIRECT7), 0.208511 (DIRECT1), 0.213937 (KDTREE / pcl::NDT).  Those lines were produced by the
+  original ndt_omp (2018) and an older PCL -- different defaults and an active line search -- so they are a plausibility
+  band, not a golden vector: the identity pose scores 0.2709, every method of the README 0.2085-0.2142.
+* GPU: the CUDA path against the oracle on the same real data -- voxel map bit-exact, per-evaluation trace <= 1e-9."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from conftest import rel_inf
+from slam_sam_b200 import ndtb
+
+FIX = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ndt_omp_pair.npz")
+
+
+@pytest.fixture(scope="module")
+def pair():
+    d = dict(np.load(FIX))
+    d["target4"] = np.ascontiguousarray(np.c_[d["target"], np.zeros(len(d["target"]), np.float32)])
+    d["source4"] = np.ascontiguousarray(np.c_[d["source"], np.zeros(len(d["source"]), np.float32)])
+    return d
+
+
+def fitness(pair, T):
+    from scipy.spatial import cKDTree
+
+    tree = cKDTree(pair["target"].astype(np.float64))
+    T = np.asarray(T, np.float32)
+    q = (pair["source"] @ T[:3, :3].T + T[:3, 3]).astype(np.float64)
+    dist, _ = tree.query(q)
+    return float((dist ** 2).mean())
+
+
+@pytest.mark.parametrize("search,eps", [("DIRECT7", 0.1), ("DIRECT1", 0.1), ("DIRECT7", 0.01), ("DIRECT1", 0.01)])
+def test_oracle_fitness_in_the_readme_band(oracle, pair, search, eps):
+    assert len(pair["target"]) == 15772 and len(pair["source"]) == 15950
+    assert abs(fitness(pair, np.eye(4)) - 0.2709) < 1e-3
+    o = O.OracleNdt(resolution=1.0, step_size=0.1, trans_epsilon=eps, max_iterations=35, search=search, num_threads=4)
+    o.set_target(pair["target"]); o.set_source(pair["source"])
+    r = o.align(None)                                   # align(*aligned): identity guess, apps/align.cpp:27
+    assert r["converged"] and r["iterations"] < 35
+    f = fitness(pair, r["T"])
+    assert 0.200 < f < 0.230                            # README: 0.2085 ... 0.2142; identity 0.2709
+    if eps == 0.01:                                     # run to a tighter epsilon both methods meet the README's KDTREE / pcl::NDT value
+        assert abs(f - 0.213937) < 0.005
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("search", ["DIRECT7", "DIRECT1"])
+def test_gpu_matches_oracle_on_real_data(oracle, pair, search):
+    h = ndtb.Handle(0)
+    h.set_params(resolution=1.0, step_size=0.1, trans_epsilon=0.01, max_iterations=35, search_method=getattr(ndtb, search))
+    assert h.set_target(pair["target4"]) == 0 and h.set_source(pair["source4"]) == 0
+    o = O.OracleNdt(resolution=1.0, step_size=0.1, trans_epsilon=0.01, max_iterations=35, search=search, num_threads=8)
+    o.set_target(pair["target"]); o.set_source(pair["source"])
+    v, w = h.voxels(), o.grid()
+    assert np.array_equal(v["idx"], w["idx"]) and np.array_equal(v["n"], w["n"])
+    valid = w["n"] >= 1
+    assert np.array_equal(v["mean"][valid], w["mean"][valid]) and np.array_equal(v["icov"], w["icov"])
+    r, ro = h.align(None), o.align(None)
+    assert (r["iterations"], r["converged"]) == (ro["iterations"], ro["converged"])
+    tr, tg = h.trace(), ro["trace"]
+    assert tr.shape == tg.shape
+    for a, b in zip(tr, tg):
+        assert np.abs(a[:6] - b[:6]).max() <= 1e-9
+        assert abs(a[6] - b[6]) <= 1e-9 * abs(b[6]) and rel_inf(a[7:13], b[7:13]) <= 1e-9 and rel_inf(a[13:49], b[13:49]) <= 1e-9
+    d = np.linalg.inv(r["T"].astype(float)) @ ro["T"].astype(float)
+    assert np.linalg.norm(d[:3, 3]) <= 1e-4 and np.arccos(np.clip((np.trace(d[:3, :3]) - 1) / 2, -1, 1)) <= 1e-5
+    assert abs(fitness(pair, r["T"]) - fitness(pair, ro["T"])) < 1e-9
