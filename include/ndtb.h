@@ -177,6 +177,13 @@ int ndtb_keyframe_put(ndtb_handle h, int64_t id, const float* xyz, size_t n, siz
 int ndtb_keyframe_drop(ndtb_handle h, int64_t id);
 int ndtb_keyframe_count(ndtb_handle h, size_t* count, size_t* total_points);
 int ndtb_set_target_window(ndtb_handle h, int n_keyframes, const int64_t* ids, const double* poses16);
+/* pcl::VoxelGrid<PointT>::filter with a cubic leaf (apps/align.cpp:65-74, run/pipeline_ins_map_distribution.cpp:324-341,
+ * PCL >= 1.14 filters/impl/voxel_grid.hpp): one centroid (float32 sum / count, CentroidPoint) per occupied leaf, in ascending
+ * leaf index.  dest 0: centroids are copied to `out` (packed x,y,z,1; at most `capacity` points); dest 1: they become the
+ * source cloud; dest 2: they become the target cloud and the voxel map is rebuilt.  *n_out = points produced.  xyz only:
+ * intensity and other fields are not carried (the registration never reads them). */
+int ndtb_voxelgrid_filter(ndtb_handle h, const float* xyz, size_t n, size_t stride_bytes, float leaf, int dest, float* out, size_t capacity,
+                          size_t* n_out);
 /* The current target cloud as packed x,y,z,w floats (device -> host copy; parity tests of the window assembly). */
 int ndtb_get_target_points(ndtb_handle h, float* xyzw, size_t capacity_points, size_t* n_points);
 

@@ -7,6 +7,13 @@
 
 using namespace oracle;
 
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <limits>
+#include <utility>
+#include <vector>
+
 extern "C" {
 
 // ------------------------------------------------------------------ small-linalg probes (tests)
@@ -168,6 +175,59 @@ void orc_assemble_window(int n_keyframes, const float* const* clouds, const size
       out[4 * o + 3] = 1.0f;
     }
   }
+}
+
+// pcl::VoxelGrid<PointT>::applyFilter with downsample_all_data_ = true, min_points_per_voxel_ = 0 (PCL >= 1.14,
+// filters/impl/voxel_grid.hpp -- not vendored in the reference; call sites extern/ndt_omp/apps/align.cpp:65-74,
+// run/pipeline_ins_map_distribution.cpp:324-341): getMinMax3D over the finite points, min_b = floor(min_p * inv_leaf),
+// idx = sum_k int(floor(p_k * inv_leaf) - float(min_b_k)) * divb_mul_k, points ordered by idx (PCL sorts with an
+// unstable integer sort; here: stable, i.e. input order inside a leaf), one output per occupied leaf in ascending idx
+// = float32 sum / float(count) (CentroidPoint / AccumulatorXYZ).  Returns the number of output points, -2 on index overflow.
+long orc_voxelgrid_filter(const float* xyz, size_t n, size_t stride, float leaf, float* out_xyzw) {
+  const float inv = 1.0f / leaf;
+  float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+  std::vector<size_t> finite;
+  finite.reserve(n);
+  for (size_t i = 0; i < n; ++i) {
+    const float* p = xyz + stride * i;
+    if (!std::isfinite(p[0]) || !std::isfinite(p[1]) || !std::isfinite(p[2])) continue;
+    finite.push_back(i);
+    for (int k = 0; k < 3; ++k) { mn[k] = std::min(mn[k], p[k]); mx[k] = std::max(mx[k], p[k]); }
+  }
+  if (finite.empty()) return 0;
+  const int64_t dx = static_cast<int64_t>((mx[0] - mn[0]) * inv) + 1, dy = static_cast<int64_t>((mx[1] - mn[1]) * inv) + 1,
+                dz = static_cast<int64_t>((mx[2] - mn[2]) * inv) + 1;
+  if (dx * dy * dz > static_cast<int64_t>(std::numeric_limits<int32_t>::max())) return -2;
+  int min_b[3], div_b[3];
+  for (int k = 0; k < 3; ++k) {
+    min_b[k] = static_cast<int>(std::floor(mn[k] * inv));
+    div_b[k] = static_cast<int>(std::floor(mx[k] * inv)) - min_b[k] + 1;
+  }
+  const int mul[3] = {1, div_b[0], div_b[0] * div_b[1]};
+  std::vector<std::pair<unsigned int, size_t>> iv;
+  iv.reserve(finite.size());
+  for (size_t i : finite) {
+    const float* p = xyz + stride * i;
+    int idx = 0;
+    for (int k = 0; k < 3; ++k) idx += static_cast<int>(std::floor(p[k] * inv) - static_cast<float>(min_b[k])) * mul[k];
+    iv.emplace_back(static_cast<unsigned int>(idx), i);
+  }
+  std::stable_sort(iv.begin(), iv.end(), [](const std::pair<unsigned int, size_t>& a, const std::pair<unsigned int, size_t>& b) { return a.first < b.first; });
+  long m = 0;
+  for (size_t a = 0; a < iv.size();) {
+    size_t b = a;
+    float s[3] = {0.0f, 0.0f, 0.0f};
+    while (b < iv.size() && iv[b].first == iv[a].first) {
+      const float* p = xyz + stride * iv[b].second;
+      s[0] = s[0] + p[0]; s[1] = s[1] + p[1]; s[2] = s[2] + p[2];
+      ++b;
+    }
+    const float cnt = static_cast<float>(b - a);
+    out_xyzw[4 * m + 0] = s[0] / cnt; out_xyzw[4 * m + 1] = s[1] / cnt; out_xyzw[4 * m + 2] = s[2] / cnt; out_xyzw[4 * m + 3] = 1.0f;
+    ++m;
+    a = b;
+  }
+  return m;
 }
 
 }  // extern "C"

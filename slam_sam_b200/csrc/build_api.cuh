@@ -39,6 +39,8 @@ struct DeviceGrid {
 int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resolution, int min_pts, double eig_mult, int flavour,
                     int is_dense, cudaStream_t stream);
 void free_device_grid(DeviceGrid& g);
+int voxelgrid_downsample(DeviceGrid& scratch, const float4* d_pts, size_t n, float leaf, int is_dense, float4* d_out, size_t* n_out,
+                         cudaStream_t stream);
 
 // voxel_finalize.cu
 void launch_voxel_finalize(const DeviceGrid& g, uint32_t n_points_upper, unsigned long long publish_key, cudaStream_t stream);

@@ -29,6 +29,11 @@ struct ndtb_handle_s {
   cudaStream_t batch_copy_stream = nullptr;
   double* batch_h_results = nullptr;    // pinned, 3 x 2 x (RED_N + 2) words
 
+  // pcl::VoxelGrid down-sampling scratch (ndtb_voxelgrid_filter): its own sort buffers, so the current map is untouched
+  ndtb::DeviceGrid ds_grid;
+  float4* d_ds_in = nullptr; size_t ds_in_alloc = 0; bool ds_in_owned = true;
+  float4* d_ds_out = nullptr; size_t ds_out_alloc = 0;
+
   ndtb::DeviceGrid grid;
   float built_resolution = 0.f; int built_min_pts = 0; int built_flavour = -1; double built_eig = 0;
 

@@ -339,6 +339,8 @@ int ndtb_destroy(ndtb_handle h) {
   if (h->h_mailbox) cudaFreeHost(h->h_mailbox);
   cudaFree(h->d_cmd);
   for (auto& kv : h->keyframes) cudaFree(kv.second.d_points);
+  free_device_grid(h->ds_grid);
+  cudaFree(h->d_ds_in); cudaFree(h->d_ds_out);
   for (auto& bs : h->batch_slot) { cudaFree(bs.d_src); if (bs.uploaded) cudaEventDestroy(bs.uploaded); }
   if (h->batch_copy_stream) cudaStreamDestroy(h->batch_copy_stream);
   if (h->batch_h_results) cudaFreeHost(h->batch_h_results);

@@ -12,7 +12,7 @@ namespace ndtb {
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return NDTB_ERR_CUDA; } while (0)
 
-static int ensure_capacity(DeviceGrid& g, size_t n) {
+static int ensure_capacity(DeviceGrid& g, size_t n, bool voxel_arrays) {
   if (!g.d_bbox) {
     CK(cudaMalloc(&g.d_bbox, 6 * sizeof(int)));
     CK(cudaMalloc(&g.d_counters, 4 * sizeof(unsigned int)));
@@ -25,21 +25,23 @@ static int ensure_capacity(DeviceGrid& g, size_t n) {
   }
   if (n > g.pts_alloc) {
     for (int i = 0; i < 2; ++i) { cudaFree(g.keys[i]); cudaFree(g.vals[i]); }
-    cudaFree(g.seg_start); cudaFree(g.block_counts); cudaFree(g.hist); cudaFree(g.sorted_xyz);
+    cudaFree(g.seg_start); cudaFree(g.block_counts); cudaFree(g.hist); cudaFree(g.sorted_xyz); cudaFree(g.c_key);
     const size_t cap = n + n / 8 + 1024;
     CK(cudaMalloc(&g.sorted_xyz, cap * 3 * sizeof(double)));
+    CK(cudaMalloc(&g.c_key, cap * 4));  // leaf keys, written with the segments
     for (int i = 0; i < 2; ++i) { CK(cudaMalloc(&g.keys[i], cap * 4)); CK(cudaMalloc(&g.vals[i], cap * 4)); }
     CK(cudaMalloc(&g.seg_start, (cap + 1) * 4));
     const size_t nb = (cap + RS_TILE - 1) / RS_TILE + 1;
     CK(cudaMalloc(&g.block_counts, nb * 4));
     CK(cudaMalloc(&g.hist, nb * 256 * 4));
     g.pts_alloc = cap;
-    // voxel arrays: V <= n
-    cudaFree(g.recs); cudaFree(g.c_key); cudaFree(g.c_n); cudaFree(g.c_mean); cudaFree(g.c_cov); cudaFree(g.c_icov);
+  }
+  if (voxel_arrays && n > g.vox_alloc) {  // voxel arrays: V <= n (not needed by the down-sampling scratch)
+    const size_t cap = n + n / 8 + 1024;
+    cudaFree(g.recs); cudaFree(g.c_n); cudaFree(g.c_mean); cudaFree(g.c_cov); cudaFree(g.c_icov);
     cudaFree(g.c_evecs); cudaFree(g.c_evals); cudaFree(g.vox_sums);
     CK(cudaMalloc(&g.vox_sums, cap * 72));
     CK(cudaMalloc(&g.recs, cap * sizeof(VoxRec)));
-    CK(cudaMalloc(&g.c_key, cap * 4));
     CK(cudaMalloc(&g.c_n, cap * 4));
     CK(cudaMalloc(&g.c_mean, cap * 24));
     CK(cudaMalloc(&g.c_cov, cap * 72));
@@ -85,14 +87,11 @@ static int wait_slots(DeviceGrid& g, int first, int count, unsigned long long ke
   return NDTB_OK;
 }
 
-int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resolution, int min_pts, double eig_mult, int flavour,
-                    int is_dense, cudaStream_t stream) {
-  g.built = false; g.V = 0; g.n_valid = 0;
-  if (n == 0) return NDTB_ERR_EMPTY;
-  if (n > 0x7fffffffu) return NDTB_ERR_INVALID;
-  int rc = ensure_capacity(g, n);
-  if (rc != NDTB_OK) return rc;
-  const int ni = static_cast<int>(n);
+// bbox -> grid geometry -> voxel keys -> stable radix sort -> segments (one per occupied leaf, ascending linear index).
+// Leaves g.meta, g.keys/vals[*cur], g.seg_start, g.c_key and d_counters[0] (skipped points) / [1] (leaf count) ready on the stream.
+static int sort_into_segments(DeviceGrid& g, const float4* d_pts, int ni, float resolution, int min_pts, double eig_mult, int flavour,
+                              int is_dense, cudaStream_t stream, int* cur_out, int* passes_out) {
+  const size_t n = static_cast<size_t>(ni);
 
   // ---- k0: bounding box (pcl::getMinMax3D); the last block publishes it to pinned host slots -----------
   {
@@ -134,20 +133,7 @@ int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resoluti
   if (cells > static_cast<int64_t>(std::numeric_limits<int32_t>::max())) return NDTB_ERR_OVERFLOW;
   m.total_cells = static_cast<uint32_t>(cells);
 
-  // ---- hash capacity: 2^m >= 2 * min(N, cells)  (load factor <= 0.5) -------------------------
-  {
-    const uint64_t need = 2ull * std::min<uint64_t>(n, static_cast<uint64_t>(cells));
-    size_t cap = 16;
-    while (cap < need) cap <<= 1;
-    if (cap > g.table_alloc) {
-      cudaFree(g.table);
-      CK(cudaMalloc(&g.table, cap * sizeof(HashSlot)));
-      g.table_alloc = cap;
-    }
-    g.table_cap = cap;
-    m.hash_mask = static_cast<uint32_t>(cap - 1);
-    CK(cudaMemsetAsync(g.table, 0xFF, cap * sizeof(HashSlot), stream));
-  }
+  (void)n;
   CK(cudaMemsetAsync(g.d_counters, 0, 4 * sizeof(unsigned int), stream));
 
   // ---- k1 + k2: keys (fused into the first histogram) and the stable LSD radix sort over the significant key bits
@@ -170,6 +156,38 @@ int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resoluti
   seg_count_kernel<<<sb, SEG_THREADS, 0, stream>>>(g.keys[cur], ni, m.total_cells, g.block_counts);
   scan_small_kernel<<<1, 1024, 0, stream>>>(g.block_counts, sb, g.d_counters + 1);
   seg_write_kernel<<<sb, SEG_THREADS, 0, stream>>>(g.keys[cur], ni, m.total_cells, g.block_counts, g.seg_start, g.c_key);
+  CK(cudaGetLastError());
+  *cur_out = cur;
+  *passes_out = passes;
+  return NDTB_OK;
+}
+
+int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resolution, int min_pts, double eig_mult, int flavour,
+                    int is_dense, cudaStream_t stream) {
+  g.built = false; g.V = 0; g.n_valid = 0;
+  if (n == 0) return NDTB_ERR_EMPTY;
+  if (n > 0x7fffffffu) return NDTB_ERR_INVALID;
+  int rc = ensure_capacity(g, n, true);
+  if (rc != NDTB_OK) return rc;
+  const int ni = static_cast<int>(n);
+  int cur = 0, passes = 0;
+  rc = sort_into_segments(g, d_pts, ni, resolution, min_pts, eig_mult, flavour, is_dense, stream, &cur, &passes);
+  if (rc != NDTB_OK) return rc;
+  GridMeta& m = g.meta;
+  // ---- hash capacity: 2^m >= 2 * min(N, cells)  (load factor <= 0.5); the table is first touched by the finalize kernel
+  {
+    const uint64_t need = 2ull * std::min<uint64_t>(n, static_cast<uint64_t>(m.total_cells));
+    size_t cap = 16;
+    while (cap < need) cap <<= 1;
+    if (cap > g.table_alloc) {
+      cudaFree(g.table);
+      CK(cudaMalloc(&g.table, cap * sizeof(HashSlot)));
+      g.table_alloc = cap;
+    }
+    g.table_cap = cap;
+    m.hash_mask = static_cast<uint32_t>(cap - 1);
+    CK(cudaMemsetAsync(g.table, 0xFF, cap * sizeof(HashSlot), stream));
+  }
   gather_points_kernel<<<(ni + 255) / 256, 256, 0, stream>>>(d_pts, g.vals[cur], ni, g.sorted_xyz);
 
   // ---- k4: per-voxel statistics + hash insert; its last block publishes the counters to the host ---------
@@ -183,6 +201,28 @@ int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resoluti
   g.V = static_cast<uint32_t>(g.h_pinned[1]);
   g.n_valid = static_cast<uint32_t>(g.h_pinned[2]);
   g.built = true;
+  return NDTB_OK;
+}
+
+// pcl::VoxelGrid::filter on the device: same bbox / index / sort / segment machinery as the map build, then centroids.
+// `g` is scratch (its NDT voxel arrays are not allocated); d_out must hold n points; *n_out = occupied leaves.
+int voxelgrid_downsample(DeviceGrid& g, const float4* d_pts, size_t n, float leaf, int is_dense, float4* d_out, size_t* n_out, cudaStream_t stream) {
+  if (n == 0) return NDTB_ERR_EMPTY;
+  if (n > 0x7fffffffu || !(leaf > 0.0f)) return NDTB_ERR_INVALID;
+  int rc = ensure_capacity(g, n, false);
+  if (rc != NDTB_OK) return rc;
+  const int ni = static_cast<int>(n);
+  int cur = 0, passes = 0;
+  rc = sort_into_segments(g, d_pts, ni, leaf, 0, 0.0, FLAVOUR_PCLOMP, is_dense, stream, &cur, &passes);
+  if (rc != NDTB_OK) return rc;
+  const unsigned long long key = 0x9E3779B97F4A7C15ull * (++g.slot_seq) | 1ull;
+  const int blocks = std::min((ni + 255) / 256, 148 * 8);
+  centroid_kernel<<<blocks, 256, 0, stream>>>(d_pts, g.vals[cur], g.seg_start, g.d_counters, static_cast<uint32_t>(ni), d_out, g.d_ticket + 1, g.h_slots, key);
+  CK(cudaGetLastError());
+  g.launches += 1 + 3 * static_cast<uint64_t>(passes) + 3 + 1;
+  rc = wait_slots(g, 12, 1, key, stream);
+  if (rc != NDTB_OK) return rc;
+  *n_out = static_cast<size_t>(static_cast<unsigned int>(g.h_slots[2 * 12]));
   return NDTB_OK;
 }
 

@@ -300,4 +300,36 @@ __global__ void __launch_bounds__(SEG_THREADS) seg_write_kernel(const uint32_t* 
   for (int i = 0; i < SEG_ITEMS; ++i) if (head[i]) { seg_start[v] = base + i; vox_key[v] = __ldg(keys + base + i); ++v; }
 }
 
+// pcl::VoxelGrid centroid pass (PCL >= 1.14 filters/impl/voxel_grid.hpp, CentroidPoint<PointT>/AccumulatorXYZ): one output
+// point per occupied leaf, in ascending leaf index = float32 sum of the leaf's points / float(count).  One thread per
+// leaf walks its segment in sorted order (stable sort: input order inside a leaf).  The last block publishes the count.
+__global__ void __launch_bounds__(256) centroid_kernel(const float4* __restrict__ pts, const uint32_t* __restrict__ vals,
+                                                       const uint32_t* __restrict__ seg_start, const unsigned int* __restrict__ counters,
+                                                       uint32_t n_points, float4* __restrict__ out, unsigned int* __restrict__ ticket,
+                                                       volatile unsigned long long* host_slots, unsigned long long key) {
+  const uint32_t V = counters[1];
+  const uint32_t n_valid_pts = n_points - counters[0];
+  for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < V; v += gridDim.x * blockDim.x) {
+    const uint32_t lo = seg_start[v], hi = (v + 1 < V) ? seg_start[v + 1] : n_valid_pts;
+    float sx = 0.0f, sy = 0.0f, sz = 0.0f;
+    for (uint32_t i = lo; i < hi; ++i) {
+      const float4 p = __ldg(pts + __ldg(vals + i));
+      sx = sx + p.x; sy = sy + p.y; sz = sz + p.z;
+    }
+    const float cnt = static_cast<float>(hi - lo);
+    out[v] = make_float4(__fdiv_rn(sx, cnt), __fdiv_rn(sy, cnt), __fdiv_rn(sz, cnt), 1.0f);
+  }
+  __shared__ bool last;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (last && threadIdx.x == 0) {
+    *ticket = 0;
+    publish_slot(host_slots, 12, V, key);
+  }
+}
+
 }  // namespace ndtb

@@ -10,6 +10,7 @@
 // Transformer<Scalar>::se3 -- the reference builds without -mavx, so the AVX specialisation is not used):
 //   out[r] = float( T(r,0)*double(x) + T(r,1)*double(y) + T(r,2)*double(z) + T(r,3) ),  left to right;  out[3] = 1.
 #include "handle.cuh"
+#include <algorithm>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -128,6 +129,46 @@ int ndtb_set_target_window(ndtb_handle h, int n_keyframes, const int64_t* ids, c
   }
   CKH(cudaGetLastError());
   h->n_target = total;
+  return rebuild_grid(h);
+}
+
+// pcl::VoxelGrid<PointT>::filter (leaf x leaf x leaf) of a host cloud on the device.  dest: 0 = copy the centroids back to
+// `out` (packed x,y,z,1 floats, at most `capacity` points), 1 = they become the SOURCE cloud, 2 = they become the TARGET
+// cloud (and the voxel map is rebuilt); in every case *n_out = number of occupied leaves = points produced.
+int ndtb_voxelgrid_filter(ndtb_handle h, const float* xyz, size_t n, size_t stride_bytes, float leaf, int dest, float* out, size_t capacity,
+                          size_t* n_out) {
+  if (!h || dest < 0 || dest > 2) return NDTB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  if (!xyz || n == 0) return set_error(h, NDTB_ERR_EMPTY, "empty cloud");
+  int rc = upload_cloud(h, xyz, n, stride_bytes, &h->d_ds_in, &h->ds_in_alloc, &h->ds_in_owned);
+  if (rc != NDTB_OK) return rc;
+  float4** d_out = &h->d_ds_out;
+  size_t* alloc = &h->ds_out_alloc;
+  if (dest == 1) { if (!h->source_owned) { h->d_source = nullptr; h->source_alloc = 0; h->source_owned = true; } d_out = &h->d_source; alloc = &h->source_alloc; }
+  if (dest == 2) { if (!h->target_owned) { h->d_target = nullptr; h->target_alloc = 0; h->target_owned = true; } d_out = &h->d_target; alloc = &h->target_alloc; }
+  if (n > *alloc) {
+    CKH(cudaStreamSynchronize(h->stream));
+    cudaFree(*d_out);
+    *d_out = nullptr;
+    const size_t cap = n + n / 8 + 256;
+    CKH(cudaMalloc(d_out, cap * sizeof(float4)));
+    *alloc = cap;
+  }
+  size_t produced = 0;
+  rc = voxelgrid_downsample(h->ds_grid, h->d_ds_in, n, leaf, h->params.is_dense, *d_out, &produced, h->stream);
+  if (rc == NDTB_ERR_OVERFLOW) return set_error(h, rc, "leaf size too small for the input dataset: integer indices would overflow");
+  if (rc != NDTB_OK) return set_error(h, rc, "voxel-grid filter failed");
+  if (n_out) *n_out = produced;
+  if (dest == 0) {
+    const size_t m = std::min(produced, capacity);
+    if (out && m) {
+      CKH(cudaMemcpyAsync(out, *d_out, m * sizeof(float4), cudaMemcpyDeviceToHost, h->stream));
+      CKH(cudaStreamSynchronize(h->stream));
+    }
+    return NDTB_OK;
+  }
+  if (dest == 1) { h->n_source = produced; return produced ? NDTB_OK : set_error(h, NDTB_ERR_EMPTY, "empty source cloud"); }
+  h->n_target = produced;
   return rebuild_grid(h);
 }
 

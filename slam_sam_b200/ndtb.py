@@ -52,7 +52,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "nd
            "ndtb_get_last_hits", "ndtb_svn_default_params", "ndtb_svn_set_params", "ndtb_svn_particle_derivatives", "ndtb_svn_stage2",
            "ndtb_svn_step", "ndtb_svn_align", "ndtb_svn_stage1_local", "ndtb_svn_finish_step", "ndtb_align_batch", "ndtb_get_timings",
            "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_set_profiling", "ndtb_set_option", "ndtb_time_eval_kernel", "ndtb_newton_direction", "ndtb_hessian_to_covariance", "ndtb_keyframe_put", "ndtb_keyframe_drop", "ndtb_keyframe_count",
-           "ndtb_set_target_window", "ndtb_get_target_points", "ndtb_svn_mean_pose", "ndtb_svn_pose_distance"]
+           "ndtb_set_target_window", "ndtb_get_target_points", "ndtb_voxelgrid_filter", "ndtb_svn_mean_pose", "ndtb_svn_pose_distance"]
 
 _LIB = None
 
@@ -112,6 +112,7 @@ def lib():
         L.ndtb_keyframe_count.argtypes = [H, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]
         L.ndtb_set_target_window.argtypes = [H, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_double)]
         L.ndtb_get_target_points.argtypes = [H, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.ndtb_voxelgrid_filter.argtypes = [H, C.c_void_p, C.c_size_t, C.c_size_t, C.c_float, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.ndtb_newton_direction.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.ndtb_svn_mean_pose.argtypes = [C.c_int, c_d, c_d, c_d]
         L.ndtb_svn_pose_distance.argtypes = [c_d, c_d, c_d]
@@ -331,6 +332,18 @@ class Handle:
         ids = np.ascontiguousarray(ids, np.int64)
         P = np.ascontiguousarray(poses, np.float64).reshape(len(ids), 16)
         return self.L.ndtb_set_target_window(self.h, len(ids), ids.ctypes.data_as(C.POINTER(C.c_int64)), _ptr(P, c_d))
+
+    def voxelgrid_filter(self, cloud, leaf, dest="host"):
+        """pcl::VoxelGrid down-sampling on the device.  dest: "host" -> returns the (m, 4) centroids, "source" / "target" ->
+        they become that cloud (returns m)."""
+        a, n, st = host_cloud(cloud)
+        m = C.c_size_t()
+        if dest == "host":
+            out = np.zeros((n, 4), np.float32)
+            self.check(self.L.ndtb_voxelgrid_filter(self.h, a.ctypes.data, n, st, float(leaf), 0, out.ctypes.data, n, C.byref(m)))
+            return out[: m.value].copy()
+        self.check(self.L.ndtb_voxelgrid_filter(self.h, a.ctypes.data, n, st, float(leaf), 1 if dest == "source" else 2, None, 0, C.byref(m)))
+        return m.value
 
     def target_points(self):
         n = C.c_size_t()

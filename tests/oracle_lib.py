@@ -57,6 +57,8 @@ def lib():
         L.orc_ndt_align.argtypes = [C.c_void_p, c_f, c_f, c_d, c_d, c_d, c_i, c_i, c_d, C.c_int, c_i, c_f, C.c_int, c_i]
         L.orc_assemble_window.argtypes = [C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.c_size_t, c_d, c_f]
         L.orc_assemble_window.restype = None
+        L.orc_voxelgrid_filter.argtypes = [c_f, C.c_size_t, C.c_size_t, C.c_float, c_f]
+        L.orc_voxelgrid_filter.restype = C.c_long
         L.orc_svn_create.restype = C.c_void_p
         L.orc_svn_destroy.argtypes = [C.c_void_p]
         L.orc_svn_grid.restype = C.c_void_p
@@ -149,6 +151,16 @@ def assemble_window(clouds, poses):
     out = np.zeros((sum(a.shape[0] for a in arrs), 4), np.float32)
     lib().orc_assemble_window(len(arrs), ptrs, ns, stride, _d(P), _f(out))
     return out
+
+
+def voxelgrid_filter(cloud, leaf):
+    """pcl::VoxelGrid down-sampling restatement: (m, 4) float32 centroids in ascending leaf index."""
+    a = as_xyz(cloud)
+    out = np.zeros((a.shape[0], 4), np.float32)
+    m = lib().orc_voxelgrid_filter(_f(a), a.shape[0], a.shape[1], float(leaf), _f(out))
+    if m < 0:
+        raise OverflowError("leaf size too small")
+    return out[:m].copy()
 
 
 class OracleNdt:
