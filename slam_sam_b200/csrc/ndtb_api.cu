@@ -474,7 +474,6 @@ int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* tr
   int rc = eval_pclomp(h, p, final_T, true, &score, g, H, &nvtl);
   if (rc != NDTB_OK) return rc;
   push_trace(p);
-  bool hessian_stored = false;
   while (!converged) {
     double neg_g[6];
     for (int i = 0; i < 6; ++i) neg_g[i] = -g[i];
@@ -562,10 +561,8 @@ int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* tr
     if (converged) {
       res->transform_probability = N ? score / static_cast<double>(N) : 0.0;
       std::memcpy(res->hessian, H, sizeof(res->hessian));
-      hessian_stored = true;
     }
   }
-  (void)hessian_stored;
   std::memcpy(res->pose, final_T, sizeof(final_T));
   res->nearest_voxel_transformation_likelihood = nvtl;
   res->iteration_num = nr_iterations;

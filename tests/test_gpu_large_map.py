@@ -35,8 +35,10 @@ def test_20m_point_map_bit_exact(oracle, big):
     assert np.array_equal(v["idx"], w["idx"]) and np.array_equal(v["n"], w["n"])
     valid = w["n"] >= 1
     assert np.array_equal(v["mean"][valid], w["mean"][valid]) and np.array_equal(v["icov"], w["icov"])
-    # build time at this size (reported, loosely bounded: 20x the 1 M-point build is ~4 ms)
-    assert h.timings()["build_ms"] < 50.0
+    # build time at this size, second build (the first one allocates gigabytes of scratch): 20x the 1 M-point build is ~4 ms
+    assert h.set_target(big["target"]) == 0
+    assert h.timings()["build_ms"] < 20.0
+    assert np.array_equal(h.voxels()["idx"], w["idx"])
 
 
 def test_multi_resolution_align_on_20m_map(oracle, big):
