@@ -7,7 +7,8 @@
 //   :701-801 (computeHessian/updateHessian), :805-1079 (More-Thuente), :1169-1281 (score helpers)
 //   and extern/ndt_omp/include/pclomp/ndt_omp.h:205-222 (pose -> matrix).
 //
-// Pinned evaluation order (PARITY UNPINNED against a reference binary: Eigen/PCL are absent):
+// Parity: pinned to the reference's published output (README fitness of the bundled scan pair, six digits,
+// tests/test_real_scan_pair.py); not bit-pinned (Eigen/PCL are absent, no reference binary).  Evaluation order:
 //   * every float dot/matrix product: k ascending, left-to-right adds, no FMA, padded 4th lane
 //     (always 0) skipped -- bit-identical to Eigen's scalar path for finite inputs;
 //   * exp at ndt_omp_impl.hpp:655 = float(exp(double(arg)));
@@ -273,8 +274,27 @@ struct PclompNdt {
 
   int set_target(const float* xyz, size_t n, size_t stride_floats, bool is_dense) {
     grid.set_leaf_size(params.resolution);
-    return grid.build(xyz, n, stride_floats, is_dense);
+    const int rc = grid.build(xyz, n, stride_floats, is_dense);
+    grid.prepare_radius_search();
+    return rc;
   }
+  // The neighbour search switch of ndt_omp_impl.hpp:279-294 (same at :734-749 for computeHessian).
+  int find_neighbours(const float* xt, const Leaf** nb) const {
+    switch (params.search_method) {
+      case KDTREE: {
+        std::vector<std::pair<float, const Leaf*>> hits;
+        grid.radius_search(xt, static_cast<double>(params.resolution), false, hits);
+        std::stable_sort(hits.begin(), hits.end(), [](const std::pair<float, const Leaf*>& a, const std::pair<float, const Leaf*>& b) { return a.first < b.first; });
+        int n = 0;
+        for (auto& h : hits) if (n < MAX_NB) nb[n++] = h.second;
+        return n;
+      }
+      case DIRECT26: return grid.neighbours26(xt[0], xt[1], xt[2], nb);
+      case DIRECT1: return grid.neighbours(xt[0], xt[1], xt[2], 1, nb);
+      default: return grid.neighbours(xt[0], xt[1], xt[2], 7, nb);
+    }
+  }
+  static constexpr int MAX_NB = 128;
   void set_source(const float* xyz, size_t n, size_t stride_floats) {
     source.resize(3 * n);
     for (size_t i = 0; i < n; ++i) for (int a = 0; a < 3; ++a) source[3 * i + a] = xyz[i * stride_floats + a];
@@ -289,14 +309,13 @@ struct PclompNdt {
     std::vector<size_t> found(N, 0);
     std::vector<int> counts(N, 0);
     compute_angle_derivatives(p, 10e-5, tables);
-    const int n_probe = (params.search_method == DIRECT1) ? 1 : 7;
     const int nt = std::max(1, params.num_threads);
 #pragma omp parallel for num_threads(nt) schedule(guided, 8)
     for (long idx = 0; idx < static_cast<long>(N); ++idx) {
       PointDeriv pd; init_point_deriv(pd);
       const float* xt = &trans[3 * idx];
-      const Leaf* nb[7];
-      const int nn = grid.neighbours(xt[0], xt[1], xt[2], n_probe, nb);
+      const Leaf* nb[MAX_NB];
+      const int nn = find_neighbours(xt, nb);
       double sum_score = 0, nearest_pt = 0;
       double* gp = &grads[6 * idx];
       double* hp = &hess[36 * idx];

@@ -76,11 +76,10 @@ inline void PclompNdt::compute_hessian_f64(double* H, const std::vector<float>& 
   // ndt_omp_impl.hpp:701-770 -- serial, FP64, uses the angle vectors of the LAST computeDerivatives.
   std::memset(H, 0, 36 * sizeof(double));
   const size_t N = source.size() / 3;
-  const int n_probe = (params.search_method == DIRECT1) ? 1 : 7;
   for (size_t idx = 0; idx < N; ++idx) {
     const float* xt = &trans[3 * idx];
-    const Leaf* nb[7];
-    const int nn = grid.neighbours(xt[0], xt[1], xt[2], n_probe, nb);
+    const Leaf* nb[MAX_NB];
+    const int nn = find_neighbours(xt, nb);
     for (int k = 0; k < nn; ++k) {
       const double x[3] = {source[3 * idx], source[3 * idx + 1], source[3 * idx + 2]};
       const double x_trans[3] = {static_cast<double>(xt[0]) - nb[k]->mean[0], static_cast<double>(xt[1]) - nb[k]->mean[1], static_cast<double>(xt[2]) - nb[k]->mean[2]};

@@ -1,6 +1,6 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY.  C entry points (ctypes) over the CPU restatement.
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
-// load this library.  PARITY UNPINNED against a reference binary (PCL/Eigen/GTSAM absent); pinned
+// load this library.  Not bit-pinned against a reference binary (PCL/Eigen/GTSAM absent); pinned to the README fitness values and
 // against the reference's own test criteria (tests/test_oracle_*.py).
 #include "ndt_pclomp_align.hpp"
 #include "svn_ndt.hpp"
@@ -113,12 +113,11 @@ void orc_ndt_calculate_scores(void* h, const float* T, double* tp, double* nvtl_
   n->update_gauss();
   std::vector<float> trans; n->transform_cloud(T, trans);
   const size_t N = trans.size() / 3;
-  const int n_probe = (n->params.search_method == DIRECT1) ? 1 : 7;
   double score = 0, nearest = 0; size_t found = 0;
   for (size_t i = 0; i < N; ++i) {
     const float* xt = &trans[3 * i];
-    const Leaf* nb[7];
-    const int nn = n->grid.neighbours(xt[0], xt[1], xt[2], n_probe, nb);
+    const Leaf* nb[PclompNdt::MAX_NB];
+    const int nn = n->find_neighbours(xt, nb);
     double best = 0;
     for (int k = 0; k < nn; ++k) {
       const double x[3] = {static_cast<double>(xt[0]) - nb[k]->mean[0], static_cast<double>(xt[1]) - nb[k]->mean[1], static_cast<double>(xt[2]) - nb[k]->mean[2]};

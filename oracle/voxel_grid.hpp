@@ -11,7 +11,10 @@
 #pragma once
 #include <cstdint>
 #include <cstddef>
+#include <algorithm>
 #include <map>
+#include <unordered_map>
+#include <utility>
 #include <vector>
 #include <cmath>
 #include <limits>
@@ -24,10 +27,17 @@ enum Flavour { FLAVOUR_PCLOMP = 0, FLAVOUR_SVN = 1 };
 struct Leaf {
   int nr_points = 0;
   double mean[3] = {0, 0, 0};
-  double cov[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  // Both reference Leaf constructors start cov_ at IDENTITY (voxel_grid_covariance_omp.h:113,
+  // svn voxel_grid_covariance.h:109) and applyFilter accumulates x x^T on top of it
+  // (voxel_grid_covariance_omp_impl.hpp:182,239; voxel_grid_covariance_impl.hpp:206,240): the
+  // single-pass second moment is I + Sum x x^T, i.e. every covariance carries an extra I/n term.
+  double cov[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
   double icov[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
   double evecs[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
   double evals[3] = {0, 0, 0};
+  // Float running sum -> centroid (Leaf::centroid_, voxel_grid_covariance_omp_impl.hpp:244-245,285;
+  // multi_voxel_grid_covariance_omp_impl.hpp:404-405,358): what the multigrid kd-tree is built over.
+  float centroid[3] = {0, 0, 0};
 };
 
 // Open-addressing Robin-Hood map restating the keying the svn grid inherits from tsl::robin_map
@@ -181,6 +191,75 @@ struct VoxelGrid {
     return found;
   }
 
+  // DIRECT26 (pclomp): voxel_grid_covariance_omp_impl.hpp:366-411 with pcl::getAllNeighborCellIndices(), which is
+  // the 13 "half" displacements followed by their negatives -- 26 cells, the CENTRE CELL IS NOT AMONG THEM
+  // (PCL voxel_grid.h getHalfNeighborCellIndices / getAllNeighborCellIndices, restated from the published source).
+  int neighbours26(float px, float py, float pz, const Leaf** out) const {
+    if (!built) return 0;
+    int half[13][3]; int n = 0;
+    for (int i = -1; i < 2; ++i) for (int j = -1; j < 2; ++j) { half[n][0] = i; half[n][1] = j; half[n][2] = -1; ++n; }
+    for (int i = -1; i < 2; ++i) { half[n][0] = i; half[n][1] = -1; half[n][2] = 0; ++n; }
+    half[n][0] = -1; half[n][1] = 0; half[n][2] = 0; ++n;
+    const int ijk[3] = {static_cast<int>(std::floor(px / leaf_size)), static_cast<int>(std::floor(py / leaf_size)),
+                        static_cast<int>(std::floor(pz / leaf_size))};
+    int found = 0;
+    for (int ni = 0; ni < 26; ++ni) {
+      int off[3];
+      for (int a = 0; a < 3; ++a) off[a] = ni < 13 ? half[ni][a] : -half[ni - 13][a];
+      bool in = true;
+      for (int a = 0; a < 3; ++a) if (!(min_b[a] - ijk[a] <= off[a]) || !(max_b[a] - ijk[a] >= off[a])) in = false;
+      if (!in) continue;
+      const int lin = (ijk[0] + off[0] - min_b[0]) * divb_mul[0] + (ijk[1] + off[1] - min_b[1]) * divb_mul[1] +
+                      (ijk[2] + off[2] - min_b[2]) * divb_mul[2];
+      const Leaf* l = find_index(static_cast<size_t>(lin));
+      if (l) out[found++] = l;
+    }
+    return found;
+  }
+
+  // Radius search over the voxel-centroid cloud (pclomp only), restating
+  //   voxel_grid_covariance_omp.h:458-485 (radiusSearch -> pcl::KdTreeFLANN::radiusSearch, sorted results) and
+  //   multi_voxel_grid_covariance_omp_impl.hpp:236-258.
+  // PCL/FLANN pieces restated from their published behaviour: KdTreeFLANN passes float(radius*radius) to an exact
+  // (eps = 0) FLANN KDTreeSingleIndex search with L2_Simple<float> (dist = dx*dx + dy*dy + dz*dz accumulated in float
+  // in that order) and RadiusResultSet keeps a point iff dist < radius^2 (strict); results sorted by distance.
+  // The kd-tree is restated as an exhaustive test over every cell whose centroid can lie inside the ball.
+  // Searchable leaves: nr_points >= min_points at filter time, i.e. also the ones flagged -1 afterwards
+  // (voxel_grid_covariance_omp_impl.hpp:294-322, multi_voxel_grid_covariance_omp_impl.hpp:346-359).
+  //   mg_centroid = false: the cloud point is float(leaf.mean_) (pclomp, _omp_impl.hpp:301-303)
+  //   mg_centroid = true : the cloud point is leaf.centroid_ (multigrid, multi_..._impl.hpp:221-225)
+  void prepare_radius_search() {
+    fast_.clear();
+    for (auto& kv : leaves_map)
+      if (kv.second.nr_points >= min_points_per_voxel || kv.second.nr_points == -1) fast_[kv.first] = &kv.second;
+  }
+  void radius_search(const float* q, double radius, bool mg_centroid, std::vector<std::pair<float, const Leaf*>>& out) const {
+    if (!built) return;
+    const float r2 = static_cast<float>(radius * radius);
+    const int reach = static_cast<int>(std::ceil(radius / static_cast<double>(leaf_size))) + 1;
+    int c[3];
+    for (int a = 0; a < 3; ++a) c[a] = static_cast<int>(std::floor(static_cast<double>(q[a]) / static_cast<double>(leaf_size)));
+    for (int dz = -reach; dz <= reach; ++dz) {
+      const int k = c[2] + dz; if (k < min_b[2] || k > max_b[2]) continue;
+      for (int dy = -reach; dy <= reach; ++dy) {
+        const int j = c[1] + dy; if (j < min_b[1] || j > max_b[1]) continue;
+        for (int dx = -reach; dx <= reach; ++dx) {
+          const int i = c[0] + dx; if (i < min_b[0] || i > max_b[0]) continue;
+          const size_t lin = static_cast<size_t>((i - min_b[0]) * divb_mul[0] + (j - min_b[1]) * divb_mul[1] + (k - min_b[2]) * divb_mul[2]);
+          auto it = fast_.find(lin);
+          if (it == fast_.end()) continue;
+          const Leaf* l = it->second;
+          float pc[3];
+          for (int a = 0; a < 3; ++a) pc[a] = mg_centroid ? l->centroid[a] : static_cast<float>(l->mean[a]);
+          float d = 0.0f;
+          for (int a = 0; a < 3; ++a) { const float diff = q[a] - pc[a]; d += diff * diff; }
+          if (d < r2) out.emplace_back(d, l);
+        }
+      }
+    }
+  }
+  std::unordered_map<size_t, const Leaf*> fast_;
+
   // Export every leaf that survives (pclomp: all leaves incl. flagged ones; svn: valid ones),
   // sorted by ascending linear index.
   void export_leaves(std::vector<size_t>& idx, std::vector<Leaf>& out) const {
@@ -198,6 +277,7 @@ struct VoxelGrid {
 inline void finalize_leaf_pclomp(Leaf& leaf, int min_pts, double eig_mult) {
   // voxel_grid_covariance_omp_impl.hpp:286-360
   const double n = static_cast<double>(leaf.nr_points);
+  for (int a = 0; a < 3; ++a) leaf.centroid[a] /= static_cast<float>(leaf.nr_points);
   double pt_sum[3] = {leaf.mean[0], leaf.mean[1], leaf.mean[2]};
   for (int a = 0; a < 3; ++a) leaf.mean[a] = leaf.mean[a] / n;
   if (leaf.nr_points < min_pts) return;
@@ -294,6 +374,7 @@ inline int VoxelGrid::build(const float* xyz, size_t n, size_t sf, bool is_dense
     Leaf& leaf = (flavour == FLAVOUR_PCLOMP) ? leaves_map[static_cast<size_t>(idx)] : leaves_robin[static_cast<size_t>(idx)];
     const double d[3] = {p[0], p[1], p[2]};
     for (int a = 0; a < 3; ++a) leaf.mean[a] += d[a];
+    for (int a = 0; a < 3; ++a) leaf.centroid[a] += p[a];
     for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) leaf.cov[3 * r + c] += d[r] * d[c];
     ++leaf.nr_points;
   }

@@ -161,7 +161,10 @@ __global__ void __launch_bounds__(128) voxel_sum_kernel(const double* __restrict
     const uint32_t hi = has ? ((v + 1 < V) ? seg_start[v + 1] : n_valid_pts) : 0u;
     const int n = static_cast<int>(hi - lo);
     const bool heavy = n > FIN_HEAVY;
-    double sum[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};  // sx sy sz sxx sxy sxz syy syz szz
+    // sx sy sz sxx sxy sxz syy syz szz.  The reference's Leaf starts cov_ at identity and adds x x^T onto it
+    // (voxel_grid_covariance_omp.h:113 + _impl.hpp:239; svn voxel_grid_covariance.h:109 + _impl.hpp:240), so the
+    // diagonal chains start at 1.0, not 0.
+    double sum[9] = {0, 0, 0, 1.0, 0, 0, 1.0, 0, 1.0};
     if (has && !heavy) {
       // Light voxel: this lane adds its points IN INPUT ORDER (stable sort; already widened to FP64 by the
       // gather kernel), loads software-pipelined one batch ahead of the sequential FP64 chains.
@@ -202,7 +205,7 @@ __global__ void __launch_bounds__(128) voxel_sum_kernel(const double* __restrict
       const uint32_t wlo = __shfl_sync(0xffffffffu, lo, o);
       const int wn = __shfl_sync(0xffffffffu, n, o);
       const double* q = sorted_xyz + 3 * static_cast<size_t>(wlo);
-      double acc = 0.0;
+      double acc = (lane == 3 || lane == 6 || lane == 8) ? 1.0 : 0.0;  // identity-initialised second moment (see above)
       double x = 0, y = 0, z = 0;
       if (lane < wn) { x = __ldg(q + 3 * lane); y = __ldg(q + 3 * lane + 1); z = __ldg(q + 3 * lane + 2); }
       for (int base = 0; base < wn; base += 32) {

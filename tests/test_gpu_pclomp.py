@@ -69,10 +69,15 @@ def test_voxel_map_edge_cases(oracle):
     assert h.set_target(c) == 0
     o = O.OracleGrid(0, 1.0, 6); o.build(c, is_dense=False)
     assert_grid_equal(h.voxels(), o.export())
-    # identical points -> zero covariance -> leaf flagged -1, never returned by a search
+    # identical points: zero scatter, but the reference's second moment starts at identity (Leaf::cov_ = I,
+    # voxel_grid_covariance_omp.h:113), so the leaf is kept with cov = I (n-1)/n^2
     same = np.tile(np.array([[0.5, 0.5, 0.5, 0]], np.float32), (10, 1))
     h.set_params(is_dense=1)
-    assert h.set_target(same) == 0 and list(h.voxels()["n"]) == [-1]
+    assert h.set_target(same) == 0
+    o = O.OracleGrid(0, 1.0, 6); o.build(same)
+    v = h.voxels(); assert list(v["n"]) == [10]
+    assert_grid_equal(v, o.export())
+    np.testing.assert_allclose(v["icov"][0].reshape(3, 3), np.eye(3) * 100 / 9, rtol=1e-12)
     # strides: packed xyz (12 B), PointXYZ (16 B), PointXYZI (32 B) give the same map
     base = rng.uniform(-5, 5, (3000, 3)).astype(np.float32)
     ref = None
@@ -143,7 +148,7 @@ def test_align_vs_golden(gold, search):
 def test_align_with_line_search(oracle, gold, step):
     """NdtParams::use_line_search: More-Thuente step length (ndt_omp_impl.hpp:995-1071) with gradient-only
     evaluations inside the search and the all-FP64 computeHessian pass (:701-800) after a search that iterated."""
-    guess = np.eye(4, dtype=np.float32); guess[0, 3] = 0.8; guess[1, 3] = -0.5
+    guess = np.eye(4, dtype=np.float32); guess[0, 3] = 2.5; guess[1, 3] = 1.5     # far enough that every step size makes the search iterate
     h = ndtb.Handle(0)
     h.set_params(resolution=2.0, max_iterations=35, trans_epsilon=0.01, step_size=step, use_line_search=1)
     h.set_target(gold["target"]); h.set_source(gold["source"])

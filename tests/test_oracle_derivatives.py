@@ -2,46 +2,64 @@
 This ties the restated float pair maths (ndt_omp_impl.hpp:640-697) to the objective it
 differentiates (Magnusson 2009, eq 6.9-6.13) independently of any golden vector."""
 import numpy as np
+import pytest
 
 import oracle_lib as O
 
 
-def fd_setup(street, search, res=2.0):
+def fd_setup(street, search, res=2.0, keep=None):
     ndt = O.OracleNdt(resolution=res, search=search, num_threads=8)
     assert ndt.set_target(street["target"]) == 0
-    ndt.set_source(street["source"])
+    ndt.set_source(street["source"] if keep is None else np.ascontiguousarray(street["source"][keep]))
     return ndt
 
 
 P0 = np.array([0.45, 0.0, 0.3, 0.01, 0.08, 0.25])   # near the two-plane ground truth
+FD_H = 1e-3
 
 
-def test_gradient_matches_finite_differences(oracle, two_plane):
-    ndt = fd_setup(two_plane, "DIRECT7", 1.0)
+def interior_points(scene, res=1.0, margin=0.04):
+    """Source points that stay inside their voxel for every pose P0 +- FD_H e_i.  The NDT score is only piecewise
+    smooth: a point that changes voxel swaps its neighbour set, a jump the analytic derivatives (eq 6.12/6.13) do not
+    contain.  With the reference's identity-inflated covariances (Leaf::cov_ = I) the Gaussians are wide enough at a
+    voxel face that this boundary flux reaches 15 % (DIRECT7) - 40 % (DIRECT1) of the rotational gradient on the
+    full cloud, so the check is made on the points whose association is frozen (lever arm <= 15 m x 1e-3 rad)."""
+    from slam_sam_b200 import synth
+
+    T = synth.pose_matrix(P0[:3], P0[3:])
+    q = scene["source"][:, :3].astype(float) @ T[:3, :3].T + T[:3, 3]
+    frac = q / res - np.floor(q / res)
+    keep = np.all((frac > margin / res) & (frac < 1 - margin / res), axis=1)
+    assert keep.sum() > 0.5 * len(q)
+    return keep
+
+
+@pytest.mark.parametrize("search", ["DIRECT7", "DIRECT1"])
+def test_gradient_matches_finite_differences(oracle, two_plane, search):
+    ndt = fd_setup(two_plane, search, 1.0, interior_points(two_plane))
     p0 = P0
     s0, g, H, _ = ndt.compute_derivatives(p0)
-    # the score is piecewise smooth (points change voxels) and evaluated in float: use a step large
-    # enough to beat float noise and compare to a few percent
-    for i, h in enumerate([1e-3] * 6):
-        dp = np.zeros(6); dp[i] = h
+    for i in range(6):
+        dp = np.zeros(6); dp[i] = FD_H
         sp = ndt.compute_derivatives(p0 + dp)[0]
         sm = ndt.compute_derivatives(p0 - dp)[0]
-        fd = (sp - sm) / (2 * h)
-        assert abs(fd - g[i]) <= 0.04 * abs(g).max(), (i, fd, g[i])
+        fd = (sp - sm) / (2 * FD_H)
+        assert abs(fd - g[i]) <= 2e-3 * abs(g).max(), (i, fd, g[i])      # measured 3e-4 (float pair maths + O(h^2))
 
 
-def test_hessian_matches_gradient_differences(oracle, two_plane):
-    ndt = fd_setup(two_plane, "DIRECT7", 1.0)
+@pytest.mark.parametrize("search", ["DIRECT7", "DIRECT1"])
+def test_hessian_matches_gradient_differences(oracle, two_plane, search):
+    ndt = fd_setup(two_plane, search, 1.0, interior_points(two_plane))
     p0 = P0
     _, g0, H, _ = ndt.compute_derivatives(p0)
     Hs = (H + H.T) / 2
     assert np.abs(H - H.T).max() <= 1e-5 * np.abs(H).max()     # symmetric up to float rounding only
-    for i, h in enumerate([1e-3] * 6):
-        dp = np.zeros(6); dp[i] = h
+    for i in range(6):
+        dp = np.zeros(6); dp[i] = FD_H
         gp = ndt.compute_derivatives(p0 + dp)[1]
         gm = ndt.compute_derivatives(p0 - dp)[1]
-        fd = (gp - gm) / (2 * h)
-        assert np.abs(fd - Hs[i]).max() <= 0.1 * np.abs(Hs).max(), (i, fd, Hs[i])
+        fd = (gp - gm) / (2 * FD_H)
+        assert np.abs(fd - Hs[i]).max() <= 5e-3 * np.abs(Hs).max(), (i, fd, Hs[i])   # measured 1.6e-3
 
 
 def test_direct1_is_subset_of_direct7(oracle, street):

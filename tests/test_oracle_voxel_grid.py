@@ -20,7 +20,7 @@ def numpy_grid(cloud, leaf, flavour, min_pts, eig_mult=0.01):
     for key in np.unique(idx):
         pts = xyz[idx == key].astype(np.float64)
         n = len(pts)
-        S = pts.sum(0); SS = pts.T @ pts
+        S = pts.sum(0); SS = np.eye(3) + pts.T @ pts      # Leaf::cov_ starts at identity (voxel_grid_covariance_omp.h:113, svn .h:109)
         mean = S / n
         if n < min_pts:
             if flavour == 0:
@@ -118,10 +118,14 @@ def test_edge_cases(oracle):
     assert g.export()["n"].sum() <= 198
     # a cloud flagged dense that still holds inf: pcl::getMinMax3D takes every point -> overflow guard trips
     assert O.OracleGrid(1, 1.0, 3).build(c, is_dense=True) == -2
-    # a voxel with identical points: zero covariance -> rejected (lambda2 <= 0), flagged -1 / erased
+    # a voxel with identical points: the scatter is zero, but the reference's second moment starts at identity
+    # (Leaf::cov_ = I, voxel_grid_covariance_omp.h:113 / svn voxel_grid_covariance.h:109), so the covariance is
+    # I/n scaled by Bessel's factor -- the leaf is KEPT, the lambda2 <= 0 rejection never fires on real clouds
     same = np.tile(np.array([[0.5, 0.5, 0.5, 0]], np.float32), (10, 1))
-    g = O.OracleGrid(0, 1.0, 6); g.build(same); assert list(g.export()["n"]) == [-1]
-    g = O.OracleGrid(1, 1.0, 6); g.build(same); assert len(g.export()["n"]) == 0
+    g = O.OracleGrid(0, 1.0, 6); g.build(same); e = g.export(); assert list(e["n"]) == [10]
+    np.testing.assert_allclose(e["cov"][0].reshape(3, 3), np.eye(3) * (1 / 10) * (9 / 10), atol=1e-12)
+    g = O.OracleGrid(1, 1.0, 6); g.build(same); e = g.export(); assert list(e["n"]) == [10]
+    np.testing.assert_allclose(e["icov"][0].reshape(3, 3), np.eye(3) * 9.0, atol=1e-9)
     # exactly min_points_per_voxel points is enough, one fewer is not
     pts = rng.uniform(0, 1, (6, 4)).astype(np.float32)
     g = O.OracleGrid(0, 1.0, 6); g.build(pts); assert len(g.neighbours((0.5, 0.5, 0.5), 1)) == 1

