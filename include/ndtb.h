@@ -187,6 +187,35 @@ int ndtb_voxelgrid_filter(ndtb_handle h, const float* xyz, size_t n, size_t stri
 /* The current target cloud as packed x,y,z,w floats (device -> host copy; parity tests of the window assembly). */
 int ndtb_get_target_points(ndtb_handle h, float* xyzw, size_t capacity_points, size_t* n_points);
 
+/* ---- multigrid NDT: pclomp::MultiGridNormalDistributionsTransform --------------------------------------------
+ * TIER IV's dynamic-map variant of ndt_omp (extern/ndt_omp/include/multigrid_pclomp/): the target is a SET of voxel
+ * grids keyed by a string id that come and go as map tiles stream in, the neighbour search is a radius search
+ * (radius = resolution) over the leaf centroids of all grids, and score / gradient / Hessian are FP64 end to end.
+ * The handle's ndtb_params apply (resolution, step_size, trans_epsilon, max_iterations, outlier_ratio,
+ * min_points_per_voxel, min_covar_eigvalue_mult, regularization_scale_factor, use_line_search, is_dense;
+ * search_method is ignored: KDTREE only, multigrid_ndt_omp_impl.hpp:197).  The source cloud and the regularisation
+ * pose are the handle's (ndtb_set_source, ndtb_set_regularization_pose); the pclomp target of ndtb_set_target is a
+ * separate object and is not touched.
+ *   ndtb_mg_add_target      addTarget(cloud, id)        multigrid_ndt_omp.h:150-155 (an existing id is replaced)
+ *   ndtb_mg_remove_target   removeTarget(id)            multigrid_ndt_omp.h:157 (unknown ids are ignored)
+ *   ndtb_mg_create_kdtree   createVoxelKdtree()         multigrid_ndt_omp.h:159-163
+ *   ndtb_mg_set_input_target setInputTarget(cloud)      multigrid_ndt_omp.h:143-148 (= addTarget("default") + createVoxelKdtree)
+ *   ndtb_mg_get_grid_ids    getCurrentMapIDs()          multigrid_ndt_omp.h:325 (ids joined by '\n')
+ *   ndtb_mg_compute_derivatives  computeDerivatives     multigrid_ndt_omp_impl.hpp:338-494
+ *   ndtb_mg_align           align() / computeTransformation  multigrid_ndt_omp_impl.hpp:210-323; ndtb_get_trace works as for ndtb_align
+ * Evaluating or aligning after add/remove without ndtb_mg_create_kdtree returns NDTB_ERR_NOT_READY (the reference
+ * would search a stale kd-tree whose leaf pointers may dangle). */
+int ndtb_mg_add_target(ndtb_handle h, const char* grid_id, const float* xyz, size_t n, size_t stride_bytes);
+int ndtb_mg_remove_target(ndtb_handle h, const char* grid_id);
+int ndtb_mg_create_kdtree(ndtb_handle h);
+int ndtb_mg_set_input_target(ndtb_handle h, const float* xyz, size_t n, size_t stride_bytes);
+int ndtb_mg_get_info(ndtb_handle h, int* n_grids_total, int* n_grids_in_tree, size_t* leaves_in_tree, int* tree_is_current);
+int ndtb_mg_get_grid_ids(ndtb_handle h, char* buf, size_t capacity, size_t* needed);
+int ndtb_mg_get_leaves(ndtb_handle h, size_t capacity, int32_t* nr_points, double* mean, double* icov, float* centroid_xyz, size_t* count);
+int ndtb_mg_compute_derivatives(ndtb_handle h, const double p[6], const float* T16, int compute_hessian, double* score, double gradient[6],
+                                double hessian[36], double* nvtl);
+int ndtb_mg_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* transformation_array, int capacity, float* out_xyz);
+
 /* ---- batch replay: n independent alignments against the current target ----------------------- */
 int ndtb_align_batch(ndtb_handle h, int n_scans, const float* const* xyz, const size_t* n_points, size_t stride_bytes,
                      const float* guesses16, ndtb_result* results);

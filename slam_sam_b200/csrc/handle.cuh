@@ -7,6 +7,8 @@
 #include <string>
 #include <vector>
 
+namespace ndtb { struct MgState; }  // multigrid.cu
+
 struct ndtb_handle_s {
   int device = 0;
   cudaStream_t stream = nullptr;
@@ -33,6 +35,9 @@ struct ndtb_handle_s {
   ndtb::DeviceGrid ds_grid;
   float4* d_ds_in = nullptr; size_t ds_in_alloc = 0; bool ds_in_owned = true;
   float4* d_ds_out = nullptr; size_t ds_out_alloc = 0;
+
+  // multigrid NDT (pclomp::MultiGridNormalDistributionsTransform): one voxel map per target id, see multigrid.cu
+  ndtb::MgState* mg = nullptr;
 
   ndtb::DeviceGrid grid;
   float built_resolution = 0.f; int built_min_pts = 0; int built_flavour = -1; double built_eig = 0;
@@ -82,4 +87,7 @@ int rebuild_grid(ndtb_handle_s* h);
 void fill_eval_state(ndtb_handle_s* h, EvalState& s, const double* p, const float* T16, double snap, bool svn);
 void finish_eval(ndtb_handle_s* h, int n, const double* r, const double* p, double* score, double* g, double* H, double* nvtl);
 int compute_hessian_f64(ndtb_handle_s* h, const double* p, const float* T16, double* H);  // line_search.cu
+int mg_eval(ndtb_handle_s* h, const double* p, const float* T16, bool compute_hessian, double* score, double* g, double* H, double* nvtl);  // multigrid.cu
+bool mg_ready(ndtb_handle_s* h);
+void mg_free(ndtb_handle_s* h);
 }  // namespace ndtb

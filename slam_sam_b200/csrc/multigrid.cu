@@ -1,0 +1,459 @@
+// pclomp::MultiGridNormalDistributionsTransform on the device (TIER IV's dynamic-map NDT, the variant autoware-style
+// localisers drive with addTarget / removeTarget as map tiles stream in):
+//   extern/ndt_omp/include/multigrid_pclomp/multigrid_ndt_omp.h:143-165 (setInputTarget / addTarget / removeTarget /
+//     createVoxelKdtree) and multigrid_ndt_omp_impl.hpp:338-494 (computeDerivatives, FP64), :590-697 (point and pair
+//     maths, FP64), :701-801 (computeHessian);
+//   extern/ndt_omp/include/multigrid_pclomp/multi_voxel_grid_covariance_omp_impl.hpp:157-258, :291-439 (the set of
+//     voxel grids, one per target id, and the radius search over their leaf centroids).
+// Device layout: every target id owns a full voxel map (the same build as ndtb_set_target: sort, per-voxel FP64 sums,
+// eigen-inflation, hash table) plus one float4 centroid per leaf (float running sum in input order / float n, the
+// point the reference's kd-tree is built over).  ndtb_mg_create_kdtree freezes the current set into a device table of
+// grid descriptors -- the "kd-tree": a radius search with radius = resolution = leaf size can only reach the 3x3x3
+// cells around the query in each grid, so it is 27 hash probes per overlapping grid plus the float distance test
+// FLANN applies (L2_Simple<float>, dist < float(r*r)).
+// Kernel: one thread per source point (grid-stride), FP64 pair maths with a fixed operation order, 46 FP64 accumulators per thread, shuffle + shared-memory block reduction, block partials summed in
+// block order by a second one-block kernel -> deterministic, ~1e-13 from the CPU restatement.
+#include "handle.cuh"
+#include "newton_math.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace ndtb;
+
+#define CKH(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { h->last_error = std::string(#x) + ": " + cudaGetErrorString(e_); return NDTB_ERR_CUDA; } } while (0)
+
+namespace ndtb {
+
+struct MgGridDev {
+  GridMeta meta;
+  const HashSlot* table;
+  const double* c_mean;
+  const double* c_icov;
+  const float4* centroid;
+};
+
+struct MgGrid {
+  DeviceGrid grid;
+  float4* d_centroid = nullptr;
+  size_t centroid_alloc = 0;
+};
+
+struct MgState {
+  std::map<std::string, MgGrid*> grids;  // sid_to_iid_ + grid_list_: createKdtree walks the ids in map order
+  MgGridDev* d_table = nullptr;          // descriptors of the grids the current "kd-tree" covers
+  int table_alloc = 0, n_tree = 0;
+  size_t tree_leaves = 0;
+  std::vector<std::string> tree_ids;
+  bool dirty = false;
+  float tree_resolution = 0.f;
+  float4* d_in = nullptr; size_t in_alloc = 0; bool in_owned = true;  // upload scratch of add_target
+  double* d_partials = nullptr; size_t partials_alloc = 0;
+  double* h_out = nullptr;               // pinned, RED_N doubles
+};
+
+struct MgEvalState {
+  float T[12];
+  double jd[24];  // 8 x 3 FP64 angle rows (multigrid_ndt_omp_impl.hpp:535-544)
+  double hd[45];  // 15 x 3 (:548-571)
+  double d1, d2;
+  float r2;       // float(radius * radius), pcl::KdTreeFLANN::radiusSearch
+};
+
+// leaf.centroid_ (multi_voxel_grid_covariance_omp_impl.hpp:404-405, :358): float running sum in input order / float(n)
+__global__ void mg_centroid_kernel(const double* __restrict__ sorted_xyz, const uint32_t* __restrict__ seg_start, uint32_t V, uint32_t n_valid_pts,
+                                   float4* __restrict__ out) {
+  for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < V; v += gridDim.x * blockDim.x) {
+    const uint32_t lo = seg_start[v], hi = (v + 1 < V) ? seg_start[v + 1] : n_valid_pts;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+    for (uint32_t i = lo; i < hi; ++i) {
+      const double* q = sorted_xyz + 3 * static_cast<size_t>(i);
+      s0 += static_cast<float>(q[0]); s1 += static_cast<float>(q[1]); s2 += static_cast<float>(q[2]);  // exact: widened floats
+    }
+    const float fn = static_cast<float>(hi - lo);
+    out[v] = make_float4(s0 / fn, s1 / fn, s2 / fn, 0.f);
+  }
+}
+
+constexpr int MG_THREADS = 128;
+constexpr int MG_WARPS = MG_THREADS / 32;
+
+__device__ __forceinline__ double dot3s(double a0, double a1, double a2, double b0, double b1, double b2) {
+  double s = a0 * b0; s = s + a1 * b1; s = s + a2 * b2; return s;
+}
+
+// updateDerivatives, FP64 (multigrid_ndt_omp_impl.hpp:640-697) with every dot product k ascending, left to right (the order the
+// CPU restatement used by the tests pins).
+// Jp: dense 3x6 point gradient; hv: vectors a..f of eq 6.21 (3 doubles each).  acc layout = RED_*.
+template <bool HESS>
+__device__ __forceinline__ double mg_pair(const double (&Jp)[3][6], const double (&hv)[6][3], const double* x, const double* C, double d1, double d2,
+                                          double* __restrict__ acc) {
+  double xC[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) xC[c] = dot3s(x[0], x[1], x[2], C[c], C[3 + c], C[6 + c]);
+  const double q = dot3s(x[0], x[1], x[2], xC[0], xC[1], xC[2]);
+  double e = exp(-d2 * q * 0.5);
+  const double score_inc = -d1 * e;
+  e = d2 * e;
+  if (e > 1 || e < 0 || e != e) return 0.0;
+  e *= d1;
+  double CJ[3][6], xCJ[6];
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int c = 0; c < 6; ++c) CJ[r][c] = dot3s(C[3 * r], C[3 * r + 1], C[3 * r + 2], Jp[0][c], Jp[1][c], Jp[2][c]);
+#pragma unroll
+  for (int c = 0; c < 6; ++c) xCJ[c] = dot3s(x[0], x[1], x[2], CJ[0][c], CJ[1][c], CJ[2][c]);
+#pragma unroll
+  for (int c = 0; c < 6; ++c) acc[RED_G + c] += e * xCJ[c];
+  if (HESS) {
+    const int hsel[3][3] = {{0, 1, 2}, {1, 3, 4}, {2, 4, 5}};
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        const double jcj = dot3s(Jp[0][j], Jp[1][j], Jp[2][j], CJ[0][i], CJ[1][i], CJ[2][i]);  // (Jp^T C Jp)(j, i)
+        double xch = 0.0;  // x C (zero block of point_hessian) = 0
+        if (i >= 3 && j >= 3) {
+          const int s = hsel[i - 3][j - 3];
+          xch = dot3s(xC[0], xC[1], xC[2], hv[s][0], hv[s][1], hv[s][2]);
+        }
+        acc[RED_H + 6 * i + j] += e * (-d2 * xCJ[i] * xCJ[j] + xch + jcj);
+      }
+    }
+  }
+  return score_inc;
+}
+
+template <bool HESS>
+__global__ void __launch_bounds__(MG_THREADS) mg_eval_kernel(const float4* __restrict__ src, int n, const MgGridDev* __restrict__ grids, int n_grids,
+                                                             const __grid_constant__ MgEvalState st, double* __restrict__ block_out) {
+  __shared__ double s_red[MG_WARPS][RED_N];
+  double acc[RED_N];
+#pragma unroll
+  for (int i = 0; i < RED_N; ++i) acc[i] = 0.0;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
+    const float4 p = __ldg(src + idx);
+    float xt[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) xt[r] = st.T[4 * r] * p.x + (st.T[4 * r + 1] * p.y + (st.T[4 * r + 2] * p.z + st.T[4 * r + 3]));
+    bool have_tables = false;
+    double Jp[3][6], hv[6][3];
+    double sum_score = 0.0, nearest = 0.0;
+    int nn = 0;
+    for (int gi = 0; gi < n_grids; ++gi) {
+      const MgGridDev& G = grids[gi];
+      const float leaf = G.meta.leaf;
+      const int i0 = static_cast<int>(floorf(__fdiv_rn(xt[0], leaf)));
+      const int i1 = static_cast<int>(floorf(__fdiv_rn(xt[1], leaf)));
+      const int i2 = static_cast<int>(floorf(__fdiv_rn(xt[2], leaf)));
+      if (i0 + 1 < G.meta.min_b[0] || i0 - 1 > G.meta.max_b[0] || i1 + 1 < G.meta.min_b[1] || i1 - 1 > G.meta.max_b[1] ||
+          i2 + 1 < G.meta.min_b[2] || i2 - 1 > G.meta.max_b[2]) continue;
+      for (int oz = -1; oz <= 1; ++oz) {
+        const int c2 = i2 + oz;
+        if (c2 < G.meta.min_b[2] || c2 > G.meta.max_b[2]) continue;
+        for (int oy = -1; oy <= 1; ++oy) {
+          const int c1 = i1 + oy;
+          if (c1 < G.meta.min_b[1] || c1 > G.meta.max_b[1]) continue;
+          for (int ox = -1; ox <= 1; ++ox) {
+            const int c0 = i0 + ox;
+            if (c0 < G.meta.min_b[0] || c0 > G.meta.max_b[0]) continue;
+            const uint32_t key = static_cast<uint32_t>((c0 - G.meta.min_b[0]) * G.meta.divb_mul[0] + (c1 - G.meta.min_b[1]) * G.meta.divb_mul[1] +
+                                                       (c2 - G.meta.min_b[2]) * G.meta.divb_mul[2]);
+            const int row = hash_find(G.table, G.meta.hash_mask, key);
+            if (row < 0) continue;
+            // FLANN L2_Simple<float> against the leaf centroid, strict '<' (RadiusResultSet::addPoint)
+            const float4 cen = __ldg(G.centroid + row);
+            const float dx = xt[0] - cen.x, dy = xt[1] - cen.y, dz = xt[2] - cen.z;
+            float d = dx * dx; d = d + dy * dy; d = d + dz * dz;
+            if (!(d < st.r2)) continue;
+            if (!have_tables) {
+              // computePointDerivatives, FP64 (multigrid_ndt_omp_impl.hpp:590-636): once per point with neighbours
+              have_tables = true;
+              const double x0 = static_cast<double>(p.x), x1 = static_cast<double>(p.y), x2 = static_cast<double>(p.z);
+              auto dj = [&](int r) { return dot3s(st.jd[3 * r], st.jd[3 * r + 1], st.jd[3 * r + 2], x0, x1, x2); };
+              auto dh = [&](int r) { return dot3s(st.hd[3 * r], st.hd[3 * r + 1], st.hd[3 * r + 2], x0, x1, x2); };
+#pragma unroll
+              for (int r = 0; r < 3; ++r)
+#pragma unroll
+                for (int c = 0; c < 6; ++c) Jp[r][c] = (r == c) ? 1.0 : 0.0;
+              Jp[1][3] = dj(0); Jp[2][3] = dj(1); Jp[0][4] = dj(2); Jp[1][4] = dj(3); Jp[2][4] = dj(4); Jp[0][5] = dj(5); Jp[1][5] = dj(6); Jp[2][5] = dj(7);
+              if (HESS) {
+                hv[0][0] = 0.0; hv[0][1] = dh(0); hv[0][2] = dh(1);
+                hv[1][0] = 0.0; hv[1][1] = dh(2); hv[1][2] = dh(3);
+                hv[2][0] = 0.0; hv[2][1] = dh(4); hv[2][2] = dh(5);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) { hv[3][k] = dh(6 + k); hv[4][k] = dh(9 + k); hv[5][k] = dh(12 + k); }
+              }
+            }
+            double xr[3], C[9];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) xr[a] = static_cast<double>(xt[a]) - __ldg(G.c_mean + 3 * static_cast<size_t>(row) + a);
+#pragma unroll
+            for (int i = 0; i < 9; ++i) C[i] = __ldg(G.c_icov + 9 * static_cast<size_t>(row) + i);
+            const double s = mg_pair<HESS>(Jp, hv, xr, C, st.d1, st.d2, acc);
+            sum_score += s;
+            if (s > nearest) nearest = s;
+            ++nn;
+          }
+        }
+      }
+    }
+    if (nn > 0) {
+      acc[RED_SCORE] += sum_score;
+      acc[RED_NEAREST] += nearest;
+      acc[RED_FOUND] += 1.0;
+      acc[RED_COUNT] += static_cast<double>(nn);
+    }
+  }
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = 0; i < RED_N; ++i) {
+    double v = acc[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) s_red[w][i] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < RED_N) {
+    double v = s_red[0][threadIdx.x];
+#pragma unroll
+    for (int k = 1; k < MG_WARPS; ++k) v += s_red[k][threadIdx.x];
+    block_out[RED_N * static_cast<size_t>(blockIdx.x) + threadIdx.x] = v;
+  }
+}
+
+// Block partials -> RED_N sums, block order (fixed): one thread per component, written to pinned host memory.
+__global__ void mg_reduce_kernel(const double* __restrict__ block_out, int blocks, double* __restrict__ out) {
+  const int c = threadIdx.x;
+  if (c >= RED_N) return;
+  double v = 0.0;
+  for (int b = 0; b < blocks; ++b) v += block_out[RED_N * static_cast<size_t>(b) + c];
+  out[c] = v;
+}
+
+static void mg_angle_vectors(const double* p, double* jd, double* hd) {  // computeAngleDerivatives :498-586 (FP64 rows, snap 10e-5)
+  const double snap = 10e-5;
+  double cx = 1.0, sx = 0.0, cy = 1.0, sy = 0.0, cz = 1.0, sz = 0.0;
+  if (!(fabs(p[3]) < snap)) { cx = cos(p[3]); sx = sin(p[3]); }
+  if (!(fabs(p[4]) < snap)) { cy = cos(p[4]); sy = sin(p[4]); }
+  if (!(fabs(p[5]) < snap)) { cz = cos(p[5]); sz = sin(p[5]); }
+  const double j[24] = {(-sx * sz + cx * sy * cz), (-sx * cz - cx * sy * sz), (-cx * cy), (cx * sz + sx * sy * cz), (cx * cz - sx * sy * sz), (-sx * cy),
+                        (-sy * cz), sy * sz, cy, sx * cy * cz, (-sx * cy * sz), sx * sy, (-cx * cy * cz), cx * cy * sz, (-cx * sy),
+                        (-cy * sz), (-cy * cz), 0, (cx * cz - sx * sy * sz), (-cx * sz - sx * sy * cz), 0, (sx * cz + cx * sy * sz), (cx * sy * cz - sx * sz), 0};
+  const double hh[45] = {(-cx * sz - sx * sy * cz), (-cx * cz + sx * sy * sz), sx * cy, (-sx * sz + cx * sy * cz), (-cx * sy * sz - sx * cz), (-cx * cy),
+                         (cx * cy * cz), (-cx * cy * sz), (cx * sy), (sx * cy * cz), (-sx * cy * sz), (sx * sy),
+                         (-sx * cz - cx * sy * sz), (sx * sz - cx * sy * cz), 0, (cx * cz - sx * sy * sz), (-sx * sy * cz - cx * sz), 0,
+                         (-cy * cz), (cy * sz), (sy), (-sx * sy * cz), (sx * sy * sz), (sx * cy), (cx * sy * cz), (-cx * sy * sz), (-cx * cy),
+                         (sy * sz), (sy * cz), 0, (-sx * cy * sz), (-sx * cy * cz), 0, (cx * cy * sz), (cx * cy * cz), 0,
+                         (-cy * cz), (cy * sz), 0, (-cx * sz - sx * sy * cz), (-cx * cz + sx * sy * sz), 0, (-sx * sz + cx * sy * cz), (-cx * sy * sz - sx * cz), 0};
+  std::memcpy(jd, j, sizeof(j));
+  std::memcpy(hd, hh, sizeof(hh));
+}
+
+static MgState* mg_state(ndtb_handle_s* h) {
+  if (!h->mg) h->mg = new MgState();
+  return h->mg;
+}
+
+void mg_free(ndtb_handle_s* h) {
+  MgState* s = h->mg;
+  if (!s) return;
+  for (auto& kv : s->grids) { free_device_grid(kv.second->grid); cudaFree(kv.second->d_centroid); delete kv.second; }
+  cudaFree(s->d_table);
+  if (s->in_owned) cudaFree(s->d_in);
+  cudaFree(s->d_partials);
+  cudaFreeHost(s->h_out);
+  delete s;
+  h->mg = nullptr;
+}
+
+bool mg_ready(ndtb_handle_s* h) { return h->mg && h->mg->n_tree > 0 && !h->mg->dirty; }
+
+// One multigrid evaluation (computeDerivatives :338-494); compute_hessian = false leaves H zero.
+int mg_eval(ndtb_handle_s* h, const double* p, const float* T16, bool compute_hessian, double* score, double* g, double* H, double* nvtl) {
+  MgState* s = h->mg;
+  if (!s || s->n_tree == 0) return set_error(h, NDTB_ERR_NOT_READY, "multigrid: no target in the kd-tree (ndtb_mg_add_target + ndtb_mg_create_kdtree)");
+  if (s->dirty) return set_error(h, NDTB_ERR_NOT_READY, "multigrid: targets changed since ndtb_mg_create_kdtree");
+  const int n = static_cast<int>(h->n_source);
+  if (n == 0) return set_error(h, NDTB_ERR_NOT_READY, "source must be set");
+  const int blocks = std::min((n + MG_THREADS - 1) / MG_THREADS, 148 * 4);
+  if (static_cast<size_t>(blocks) * RED_N > s->partials_alloc) {
+    cudaFree(s->d_partials);
+    CKH(cudaMalloc(&s->d_partials, sizeof(double) * RED_N * 148 * 4));
+    s->partials_alloc = static_cast<size_t>(RED_N) * 148 * 4;
+  }
+  if (!s->h_out) CKH(cudaHostAlloc(&s->h_out, sizeof(double) * RED_N, cudaHostAllocDefault));
+  MgEvalState st;
+  std::memcpy(st.T, T16, 12 * sizeof(float));
+  mg_angle_vectors(p, st.jd, st.hd);
+  double d3;
+  gauss_pclomp(h->params.outlier_ratio, s->tree_resolution, &st.d1, &st.d2, &d3);
+  const double radius = static_cast<double>(s->tree_resolution);
+  st.r2 = static_cast<float>(radius * radius);
+  if (compute_hessian) mg_eval_kernel<true><<<blocks, MG_THREADS, 0, h->stream>>>(h->d_source, n, s->d_table, s->n_tree, st, s->d_partials);
+  else mg_eval_kernel<false><<<blocks, MG_THREADS, 0, h->stream>>>(h->d_source, n, s->d_table, s->n_tree, st, s->d_partials);
+  mg_reduce_kernel<<<1, 64, 0, h->stream>>>(s->d_partials, blocks, s->h_out);
+  h->launches += 2;
+  h->eval_launches += 1;
+  CKH(cudaGetLastError());
+  CKH(cudaStreamSynchronize(h->stream));
+  double r[RED_N];
+  std::memcpy(r, s->h_out, sizeof(r));
+  finish_eval(h, n, r, p, score, g, H, nvtl);  // regulariser (:446-480) and NVTL (:482-488): same host epilogue as pclomp
+  return NDTB_OK;
+}
+
+}  // namespace ndtb
+
+extern "C" {
+
+int ndtb_mg_add_target(ndtb_handle h, const char* grid_id, const float* xyz, size_t n, size_t stride_bytes) {
+  if (!h || !grid_id) return NDTB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  if (!xyz || n == 0) return set_error(h, NDTB_ERR_EMPTY, "empty target cloud");
+  MgState* s = mg_state(h);
+  int rc = upload_cloud(h, xyz, n, stride_bytes, &s->d_in, &s->in_alloc, &s->in_owned);
+  if (rc != NDTB_OK) return rc;
+  // an existing id is replaced: the reference orphans the old node (sid_to_iid_[id] = new index) and createKdtree drops it
+  MgGrid* g = nullptr;
+  auto it = s->grids.find(grid_id);
+  if (it != s->grids.end()) g = it->second; else { g = new MgGrid(); s->grids[grid_id] = g; }
+  s->dirty = true;
+  const ndtb_params& P = h->params;
+  rc = build_voxel_map(g->grid, s->d_in, n, P.resolution, P.min_points_per_voxel, P.min_covar_eigvalue_mult, FLAVOUR_PCLOMP, P.is_dense, h->stream);
+  if (rc != NDTB_OK) {  // applyFilter :307-313 warns and leaves the node empty; here the id is not registered at all
+    free_device_grid(g->grid); cudaFree(g->d_centroid); delete g; s->grids.erase(grid_id);
+    return set_error(h, rc, "multigrid: voxel map build failed");
+  }
+  const uint32_t V = g->grid.V;
+  if (V > g->centroid_alloc) {
+    cudaFree(g->d_centroid);
+    CKH(cudaMalloc(&g->d_centroid, sizeof(float4) * V));
+    g->centroid_alloc = V;
+  }
+  const uint32_t n_valid_pts = static_cast<uint32_t>(n) - static_cast<uint32_t>(g->grid.h_pinned[0]);
+  mg_centroid_kernel<<<std::min<int>((V + 127) / 128, 148 * 8), 128, 0, h->stream>>>(g->grid.sorted_xyz, g->grid.seg_start, V, n_valid_pts, g->d_centroid);
+  g->grid.launches += 1;
+  CKH(cudaGetLastError());
+  CKH(cudaStreamSynchronize(h->stream));
+  return NDTB_OK;
+}
+
+int ndtb_mg_remove_target(ndtb_handle h, const char* grid_id) {
+  if (!h || !grid_id) return NDTB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  MgState* s = mg_state(h);
+  auto it = s->grids.find(grid_id);
+  if (it == s->grids.end()) return NDTB_OK;  // removeCloud :183-185: unknown ids are ignored
+  CKH(cudaStreamSynchronize(h->stream));
+  free_device_grid(it->second->grid); cudaFree(it->second->d_centroid); delete it->second;
+  s->grids.erase(it);
+  s->dirty = true;
+  return NDTB_OK;
+}
+
+int ndtb_mg_create_kdtree(ndtb_handle h) {
+  if (!h) return NDTB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  MgState* s = mg_state(h);
+  std::vector<MgGridDev> tab;
+  s->tree_ids.clear();
+  s->tree_leaves = 0;
+  float res = 0.f;
+  for (auto& kv : s->grids) {
+    MgGrid* g = kv.second;
+    if (!g->grid.built) continue;
+    if (res != 0.f && g->grid.meta.leaf != res) return set_error(h, NDTB_ERR_INVALID, "multigrid: targets were added with different resolutions");
+    res = g->grid.meta.leaf;
+    MgGridDev d;
+    d.meta = g->grid.meta; d.table = g->grid.table; d.c_mean = g->grid.c_mean; d.c_icov = g->grid.c_icov; d.centroid = g->d_centroid;
+    tab.push_back(d);
+    s->tree_ids.push_back(kv.first);
+    s->tree_leaves += g->grid.n_valid;
+  }
+  if (static_cast<int>(tab.size()) > s->table_alloc) {
+    cudaFree(s->d_table);
+    const int cap = std::max<int>(16, 2 * static_cast<int>(tab.size()));
+    CKH(cudaMalloc(&s->d_table, sizeof(MgGridDev) * cap));
+    s->table_alloc = cap;
+  }
+  if (!tab.empty()) CKH(cudaMemcpyAsync(s->d_table, tab.data(), sizeof(MgGridDev) * tab.size(), cudaMemcpyHostToDevice, h->stream));
+  CKH(cudaStreamSynchronize(h->stream));
+  s->n_tree = static_cast<int>(tab.size());
+  s->tree_resolution = res;
+  s->dirty = false;
+  return NDTB_OK;
+}
+
+int ndtb_mg_set_input_target(ndtb_handle h, const float* xyz, size_t n, size_t stride_bytes) {  // multigrid_ndt_omp.h:143-148
+  const int rc = ndtb_mg_add_target(h, "default", xyz, n, stride_bytes);
+  if (rc != NDTB_OK) return rc;
+  return ndtb_mg_create_kdtree(h);
+}
+
+int ndtb_mg_get_info(ndtb_handle h, int* n_grids_total, int* n_grids_in_tree, size_t* leaves_in_tree, int* tree_is_current) {
+  if (!h) return NDTB_ERR_INVALID;
+  MgState* s = mg_state(h);
+  if (n_grids_total) *n_grids_total = static_cast<int>(s->grids.size());
+  if (n_grids_in_tree) *n_grids_in_tree = s->n_tree;
+  if (leaves_in_tree) *leaves_in_tree = s->tree_leaves;
+  if (tree_is_current) *tree_is_current = s->dirty ? 0 : 1;
+  return NDTB_OK;
+}
+
+// getCurrentMapIDs (multi_voxel_grid_covariance_omp_impl.hpp:277-288): ids joined by '\n' into buf (NUL-terminated);
+// *needed = bytes required including the terminator.
+int ndtb_mg_get_grid_ids(ndtb_handle h, char* buf, size_t capacity, size_t* needed) {
+  if (!h) return NDTB_ERR_INVALID;
+  MgState* s = mg_state(h);
+  std::string all;
+  for (auto& kv : s->grids) { if (!all.empty()) all += '\n'; all += kv.first; }
+  if (needed) *needed = all.size() + 1;
+  if (buf && capacity > 0) { const size_t c = std::min(capacity - 1, all.size()); std::memcpy(buf, all.data(), c); buf[c] = 0; }
+  return NDTB_OK;
+}
+
+// Leaves of the current kd-tree, in tree order (grid id order, ascending linear index inside a grid; searchable
+// leaves only): getVoxelPCD-style export for parity tests.  Any output pointer may be NULL.
+int ndtb_mg_get_leaves(ndtb_handle h, size_t capacity, int32_t* nr_points, double* mean, double* icov, float* centroid_xyz, size_t* count) {
+  if (!h) return NDTB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  MgState* s = mg_state(h);
+  if (s->dirty) return set_error(h, NDTB_ERR_NOT_READY, "multigrid: targets changed since ndtb_mg_create_kdtree");
+  size_t k = 0;
+  for (const std::string& id : s->tree_ids) {
+    MgGrid* g = s->grids[id];
+    const size_t V = g->grid.V;
+    std::vector<int32_t> n(V); std::vector<double> m(3 * V), ic(9 * V); std::vector<float4> cen(V);
+    CKH(cudaMemcpy(n.data(), g->grid.c_n, sizeof(int32_t) * V, cudaMemcpyDeviceToHost));
+    CKH(cudaMemcpy(m.data(), g->grid.c_mean, sizeof(double) * 3 * V, cudaMemcpyDeviceToHost));
+    CKH(cudaMemcpy(ic.data(), g->grid.c_icov, sizeof(double) * 9 * V, cudaMemcpyDeviceToHost));
+    CKH(cudaMemcpy(cen.data(), g->d_centroid, sizeof(float4) * V, cudaMemcpyDeviceToHost));
+    for (size_t v = 0; v < V; ++v) {
+      if (n[v] < h->params.min_points_per_voxel) continue;  // dropped by applyFilter :345-347 (and the flagged -1 leaves: unreachable, cov >= I(n-1)/n^2)
+      if (k < capacity) {
+        if (nr_points) nr_points[k] = n[v];
+        if (mean) std::memcpy(mean + 3 * k, &m[3 * v], 24);
+        if (icov) std::memcpy(icov + 9 * k, &ic[9 * v], 72);
+        if (centroid_xyz) { centroid_xyz[3 * k] = cen[v].x; centroid_xyz[3 * k + 1] = cen[v].y; centroid_xyz[3 * k + 2] = cen[v].z; }
+      }
+      ++k;
+    }
+  }
+  if (count) *count = k;
+  return NDTB_OK;
+}
+
+int ndtb_mg_compute_derivatives(ndtb_handle h, const double p[6], const float* T16, int compute_hessian, double* score, double gradient[6],
+                                double hessian[36], double* nvtl) {
+  if (!h || !p || !score || !gradient || !hessian) return NDTB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  float T[16];
+  if (T16) std::memcpy(T, T16, sizeof(T)); else pose_to_T(p, T);
+  return mg_eval(h, p, T, compute_hessian != 0, score, gradient, hessian, nvtl);
+}
+
+}  // extern "C"

@@ -340,6 +340,7 @@ int ndtb_destroy(ndtb_handle h) {
   cudaFree(h->d_cmd);
   for (auto& kv : h->keyframes) cudaFree(kv.second.d_points);
   free_device_grid(h->ds_grid);
+  mg_free(h);
   cudaFree(h->d_ds_in); cudaFree(h->d_ds_out);
   for (auto& bs : h->batch_slot) { cudaFree(bs.d_src); if (bs.uploaded) cudaEventDestroy(bs.uploaded); }
   if (h->batch_copy_stream) cudaStreamDestroy(h->batch_copy_stream);
@@ -437,12 +438,23 @@ int ndtb_compute_derivatives(ndtb_handle h, const double p[6], const float* T16,
   return resolve_eval_events(h);
 }
 
-int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* transformation_array, int capacity, float* out_xyz) {
+// computeTransformation of pclomp::NormalDistributionsTransform (ndt_omp_impl.hpp:85-202, multigrid = false) and of
+// pclomp::MultiGridNormalDistributionsTransform (multigrid_ndt_omp_impl.hpp:210-323, multigrid = true).  The two
+// loops differ in the evaluation they call, in the iteration cap (`nr_iterations > max` tested before the increment
+// vs `>= max` after it) and in when hessian_ is stored.
+static int align_impl(ndtb_handle h, bool multigrid, const float guess[16], ndtb_result* res, float* transformation_array, int capacity, float* out_xyz) {
   if (!h || !guess || !res) return NDTB_ERR_INVALID;
   cudaSetDevice(h->device);
   std::memset(res, 0, sizeof(*res));
-  if (!h->grid.built || h->n_source == 0) return set_error(h, NDTB_ERR_NOT_READY, "target and source must be set");
+  if (multigrid) {
+    if (!mg_ready(h) || h->n_source == 0) return set_error(h, NDTB_ERR_NOT_READY, "multigrid: targets + ndtb_mg_create_kdtree and a source must be set");
+  } else {
+    if (!h->grid.built || h->n_source == 0) return set_error(h, NDTB_ERR_NOT_READY, "target and source must be set");
+  }
   if (h->params.grid_flavour != NDTB_FLAVOUR_PCLOMP) return set_error(h, NDTB_ERR_INVALID, "pclomp entry point on an svn-flavour handle");
+  auto evaluate = [&](const double* pp, const float* T16, bool hess, double* sc, double* gg, double* HH, double* nv) {
+    return multigrid ? mg_eval(h, pp, T16, hess, sc, gg, HH, nv) : eval_pclomp(h, pp, T16, hess, sc, gg, HH, nv);
+  };
   cudaEventRecord(h->ev[0], h->stream);
   h->eval_ms_total = 0; h->eval_launches = 0;
   h->trace.clear();
@@ -470,8 +482,8 @@ int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* tr
     ndtb_handle_s* h;
     ~SessionGuard() { session_end(h); }
   } session_guard{h};
-  session_begin(h);
-  int rc = eval_pclomp(h, p, final_T, true, &score, g, H, &nvtl);
+  if (!multigrid) session_begin(h);
+  int rc = evaluate(p, final_T, true, &score, g, H, &nvtl);
   if (rc != NDTB_OK) return rc;
   push_trace(p);
   while (!converged) {
@@ -513,7 +525,7 @@ int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* tr
         double x_t[6];
         for (int i = 0; i < 6; ++i) x_t[i] = p[i] + delta_p[i] * a_t;
         pose_to_T(x_t, final_T);
-        rc = eval_pclomp(h, x_t, final_T, true, &score, g, H, &nvtl);
+        rc = evaluate(x_t, final_T, true, &score, g, H, &nvtl);
         if (rc != NDTB_OK) return rc;
         push_trace(x_t);
         if (P.use_line_search) {
@@ -528,7 +540,7 @@ int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* tr
             a_t = std::max(a_t, step_min);
             for (int i = 0; i < 6; ++i) x_t[i] = p[i] + delta_p[i] * a_t;
             pose_to_T(x_t, final_T);
-            rc = eval_pclomp(h, x_t, final_T, false, &score, g, H, &nvtl);  // score and gradient only (:1031)
+            rc = evaluate(x_t, final_T, false, &score, g, H, &nvtl);  // score and gradient only (:1031)
             if (rc != NDTB_OK) return rc;
             phi_t = -score; d_phi_t = 0;
             for (int i = 0; i < 6; ++i) d_phi_t += g[i] * delta_p[i];
@@ -546,7 +558,15 @@ int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* tr
           }
         }
         if (step_iterations) {  // the loop evaluated without Hessians: computeHessian, all FP64 (:1073)
-          rc = compute_hessian_f64(h, x_t, final_T, H);
+          if (multigrid) {  // computeHessian (multigrid_ndt_omp_impl.hpp:701-801): the FP64 pair maths again, Hessian kept
+            double sc2, g2[6], nv2;
+            const bool reg = h->has_reg_pose;
+            h->has_reg_pose = false;  // computeHessian carries no regulariser
+            rc = mg_eval(h, x_t, final_T, true, &sc2, g2, H, &nv2);
+            h->has_reg_pose = reg;
+          } else {
+            rc = compute_hessian_f64(h, x_t, final_T, H);
+          }
           if (rc != NDTB_OK) return rc;
           push_trace(x_t);
         }
@@ -556,8 +576,13 @@ int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* tr
     for (int i = 0; i < 6; ++i) delta_p[i] *= delta_p_norm;
     push_T();
     for (int i = 0; i < 6; ++i) p[i] = p[i] + delta_p[i];
-    if (nr_iterations > P.max_iterations || (nr_iterations && (fabs(delta_p_norm) < P.trans_epsilon))) converged = true;
-    nr_iterations++;
+    if (multigrid) {
+      nr_iterations++;
+      if (nr_iterations >= P.max_iterations || (nr_iterations && (fabs(delta_p_norm) < P.trans_epsilon))) converged = true;  // :300-304
+    } else {
+      if (nr_iterations > P.max_iterations || (nr_iterations && (fabs(delta_p_norm) < P.trans_epsilon))) converged = true;
+      nr_iterations++;
+    }
     if (converged) {
       res->transform_probability = N ? score / static_cast<double>(N) : 0.0;
       std::memcpy(res->hessian, H, sizeof(res->hessian));
@@ -585,6 +610,14 @@ int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* tr
   cudaEventElapsedTime(&h->align_ms, h->ev[0], h->ev[1]);
   if (h->session_eval_ns > 0) h->eval_ms_total = static_cast<float>(h->session_eval_ns * 1e-6);  // device-side (globaltimer) durations
   return resolve_eval_events(h);
+}
+
+int ndtb_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* transformation_array, int capacity, float* out_xyz) {
+  return align_impl(h, false, guess, res, transformation_array, capacity, out_xyz);
+}
+
+int ndtb_mg_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* transformation_array, int capacity, float* out_xyz) {
+  return align_impl(h, true, guess, res, transformation_array, capacity, out_xyz);
 }
 
 int ndtb_get_trace(ndtb_handle h, double* trace, int capacity, int* count) {

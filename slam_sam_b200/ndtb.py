@@ -52,7 +52,9 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "nd
            "ndtb_get_last_hits", "ndtb_svn_default_params", "ndtb_svn_set_params", "ndtb_svn_particle_derivatives", "ndtb_svn_stage2",
            "ndtb_svn_step", "ndtb_svn_align", "ndtb_svn_stage1_local", "ndtb_svn_finish_step", "ndtb_align_batch", "ndtb_get_timings",
            "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_set_profiling", "ndtb_set_option", "ndtb_time_eval_kernel", "ndtb_newton_direction", "ndtb_hessian_to_covariance", "ndtb_keyframe_put", "ndtb_keyframe_drop", "ndtb_keyframe_count",
-           "ndtb_set_target_window", "ndtb_get_target_points", "ndtb_voxelgrid_filter", "ndtb_svn_mean_pose", "ndtb_svn_pose_distance"]
+           "ndtb_set_target_window", "ndtb_get_target_points", "ndtb_voxelgrid_filter", "ndtb_svn_mean_pose", "ndtb_svn_pose_distance",
+           "ndtb_mg_add_target", "ndtb_mg_remove_target", "ndtb_mg_create_kdtree", "ndtb_mg_set_input_target", "ndtb_mg_get_info",
+           "ndtb_mg_get_grid_ids", "ndtb_mg_get_leaves", "ndtb_mg_compute_derivatives", "ndtb_mg_align"]
 
 _LIB = None
 
@@ -116,6 +118,15 @@ def lib():
         L.ndtb_newton_direction.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.ndtb_svn_mean_pose.argtypes = [C.c_int, c_d, c_d, c_d]
         L.ndtb_svn_pose_distance.argtypes = [c_d, c_d, c_d]
+        L.ndtb_mg_add_target.argtypes = [H, C.c_char_p, C.c_void_p, C.c_size_t, C.c_size_t]
+        L.ndtb_mg_remove_target.argtypes = [H, C.c_char_p]
+        L.ndtb_mg_create_kdtree.argtypes = [H]
+        L.ndtb_mg_set_input_target.argtypes = [H, C.c_void_p, C.c_size_t, C.c_size_t]
+        L.ndtb_mg_get_info.argtypes = [H, c_i, c_i, C.POINTER(C.c_size_t), c_i]
+        L.ndtb_mg_get_grid_ids.argtypes = [H, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.ndtb_mg_get_leaves.argtypes = [H, C.c_size_t, C.POINTER(C.c_int32), c_d, c_d, c_f, C.POINTER(C.c_size_t)]
+        L.ndtb_mg_compute_derivatives.argtypes = [H, c_d, c_f, C.c_int, c_d, c_d, c_d, c_d]
+        L.ndtb_mg_align.argtypes = [H, c_f, C.POINTER(Result), c_f, C.c_int, c_f]
         _LIB = L
     return _LIB
 
@@ -254,6 +265,60 @@ class Handle:
         arr = np.zeros((capacity, 16), np.float32)
         rc = self.L.ndtb_align(self.h, _ptr(guess.reshape(16), c_f), C.byref(r), _ptr(arr, c_f), capacity, None)
         self.check(rc)
+        return dict(T=np.array(r.pose, np.float32).reshape(4, 4), hessian=np.array(r.hessian).reshape(6, 6),
+                    trans_probability=r.transform_probability, nvtl=r.nearest_voxel_transformation_likelihood,
+                    iterations=r.iteration_num, converged=bool(r.converged), evaluations=r.evaluations,
+                    transformation_array=arr[: r.transformation_array_len].reshape(-1, 4, 4).copy())
+
+    # ---- multigrid NDT (pclomp::MultiGridNormalDistributionsTransform) ----
+    def mg_add_target(self, cloud, grid_id):
+        a, n, st = host_cloud(cloud)
+        return self.L.ndtb_mg_add_target(self.h, str(grid_id).encode(), a.ctypes.data, n, st)
+
+    def mg_remove_target(self, grid_id):
+        return self.L.ndtb_mg_remove_target(self.h, str(grid_id).encode())
+
+    def mg_create_kdtree(self):
+        return self.L.ndtb_mg_create_kdtree(self.h)
+
+    def mg_set_input_target(self, cloud):
+        a, n, st = host_cloud(cloud)
+        return self.L.ndtb_mg_set_input_target(self.h, a.ctypes.data, n, st)
+
+    def mg_info(self):
+        a = np.zeros(1, np.int32); b = np.zeros(1, np.int32); c = C.c_size_t(0); d = np.zeros(1, np.int32)
+        self.check(self.L.ndtb_mg_get_info(self.h, _ptr(a, c_i), _ptr(b, c_i), C.byref(c), _ptr(d, c_i)))
+        return dict(grids=int(a[0]), grids_in_tree=int(b[0]), leaves=int(c.value), current=bool(d[0]))
+
+    def mg_grid_ids(self):
+        need = C.c_size_t(0)
+        self.check(self.L.ndtb_mg_get_grid_ids(self.h, None, 0, C.byref(need)))
+        buf = C.create_string_buffer(need.value)
+        self.check(self.L.ndtb_mg_get_grid_ids(self.h, buf, need.value, None))
+        txt = buf.value.decode()
+        return txt.split("\n") if txt else []
+
+    def mg_leaves(self):
+        cnt = C.c_size_t(0)
+        self.check(self.L.ndtb_mg_get_leaves(self.h, 0, None, None, None, None, C.byref(cnt)))
+        k = cnt.value
+        n = np.zeros(k, np.int32); mean = np.zeros((k, 3)); icov = np.zeros((k, 9)); cen = np.zeros((k, 3), np.float32)
+        self.check(self.L.ndtb_mg_get_leaves(self.h, k, _ptr(n, C.POINTER(C.c_int32)), _ptr(mean, c_d), _ptr(icov, c_d), _ptr(cen, c_f), None))
+        return dict(n=n, mean=mean, icov=icov, centroid=cen)
+
+    def mg_compute_derivatives(self, p, T=None, compute_hessian=True):
+        p = np.ascontiguousarray(p, np.float64)
+        t = None if T is None else np.ascontiguousarray(T, np.float32).reshape(16)
+        s = np.zeros(1); g = np.zeros(6); H = np.zeros((6, 6)); nv = np.zeros(1)
+        self.check(self.L.ndtb_mg_compute_derivatives(self.h, _ptr(p, c_d), _ptr(t, c_f), int(compute_hessian), _ptr(s, c_d), _ptr(g, c_d),
+                                                      _ptr(H, c_d), _ptr(nv, c_d)))
+        return s[0], g, H, nv[0]
+
+    def mg_align(self, guess=None, capacity=64):
+        guess = np.eye(4, dtype=np.float32) if guess is None else np.ascontiguousarray(guess, np.float32)
+        r = Result()
+        arr = np.zeros((capacity, 16), np.float32)
+        self.check(self.L.ndtb_mg_align(self.h, _ptr(guess.reshape(16), c_f), C.byref(r), _ptr(arr, c_f), capacity, None))
         return dict(T=np.array(r.pose, np.float32).reshape(4, 4), hessian=np.array(r.hessian).reshape(6, 6),
                     trans_probability=r.transform_probability, nvtl=r.nearest_voxel_transformation_likelihood,
                     iterations=r.iteration_num, converged=bool(r.converged), evaluations=r.evaluations,

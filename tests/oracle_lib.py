@@ -58,6 +58,23 @@ def lib():
         L.orc_assemble_window.argtypes = [C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.c_size_t, c_d, c_f]
         L.orc_assemble_window.restype = None
         L.orc_voxelgrid_filter.argtypes = [c_f, C.c_size_t, C.c_size_t, C.c_float, c_f]
+        L.orc_mg_create.restype = C.c_void_p
+        L.orc_mg_destroy.argtypes = [C.c_void_p]
+        L.orc_mg_set_params.argtypes = [C.c_void_p, C.c_float, C.c_double, C.c_double, C.c_int, C.c_int, C.c_float, C.c_int, C.c_double,
+                                        C.c_int, C.c_double]
+        L.orc_mg_add_target.argtypes = [C.c_void_p, c_f, C.c_size_t, C.c_size_t, C.c_int, C.c_char_p]
+        L.orc_mg_remove_target.argtypes = [C.c_void_p, C.c_char_p]
+        L.orc_mg_create_kdtree.argtypes = [C.c_void_p]
+        L.orc_mg_leaf_count.restype = C.c_long
+        L.orc_mg_leaf_count.argtypes = [C.c_void_p]
+        L.orc_mg_export.restype = C.c_long
+        L.orc_mg_export.argtypes = [C.c_void_p, C.c_long, c_i, c_d, c_d, c_f]
+        L.orc_mg_radius_search.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int, c_d, c_f]
+        L.orc_mg_set_source.argtypes = [C.c_void_p, c_f, C.c_size_t, C.c_size_t]
+        L.orc_mg_set_regularization_pose.argtypes = [C.c_void_p, c_f]
+        L.orc_mg_compute_derivatives.restype = C.c_double
+        L.orc_mg_compute_derivatives.argtypes = [C.c_void_p, c_d, C.c_int, c_d, c_d, c_d]
+        L.orc_mg_align.argtypes = [C.c_void_p, c_f, c_f, c_d, c_d, c_d, c_i, c_i, c_d, C.c_int, c_i, c_f, C.c_int, c_i]
         L.orc_voxelgrid_filter.restype = C.c_long
         L.orc_svn_create.restype = C.c_void_p
         L.orc_svn_destroy.argtypes = [C.c_void_p]
@@ -221,6 +238,75 @@ class OracleNdt:
     def __del__(self):
         try:
             lib().orc_ndt_destroy(self.h)
+        except Exception:
+            pass
+
+
+class OracleMultigrid:
+    """pclomp::MultiGridNormalDistributionsTransform restatement (oracle/multigrid_ndt.hpp)."""
+
+    def __init__(self, resolution=1.0, step_size=0.1, trans_epsilon=0.1, max_iterations=35, num_threads=1, reg_scale=0.0,
+                 use_line_search=False, outlier_ratio=0.55, min_pts=6, eig_mult=0.01):
+        self.h = lib().orc_mg_create()
+        lib().orc_mg_set_params(self.h, resolution, step_size, trans_epsilon, max_iterations, num_threads, reg_scale, int(use_line_search),
+                                outlier_ratio, min_pts, eig_mult)
+
+    def add_target(self, cloud, grid_id, is_dense=True):
+        a = as_xyz(cloud)
+        return lib().orc_mg_add_target(self.h, _f(a), a.shape[0], a.shape[1], int(is_dense), str(grid_id).encode())
+
+    def remove_target(self, grid_id):
+        lib().orc_mg_remove_target(self.h, str(grid_id).encode())
+
+    def create_kdtree(self):
+        lib().orc_mg_create_kdtree(self.h)
+
+    def set_input_target(self, cloud):          # multigrid_ndt_omp.h:143-148
+        rc = self.add_target(cloud, "default"); self.create_kdtree(); return rc
+
+    def leaves(self):
+        n = lib().orc_mg_leaf_count(self.h)
+        npts = np.zeros(n, np.int32); mean = np.zeros((n, 3)); icov = np.zeros((n, 9)); cen = np.zeros((n, 3), np.float32)
+        lib().orc_mg_export(self.h, n, _i(npts), _d(mean), _d(icov), _f(cen))
+        return dict(n=npts, mean=mean, icov=icov, centroid=cen)
+
+    def radius_search(self, p, cap=128):
+        means = np.zeros((cap, 3)); dist = np.zeros(cap, np.float32)
+        k = lib().orc_mg_radius_search(self.h, float(p[0]), float(p[1]), float(p[2]), cap, _d(means), _f(dist))
+        return means[:k].copy(), dist[:k].copy()
+
+    def set_source(self, cloud):
+        a = as_xyz(cloud)
+        lib().orc_mg_set_source(self.h, _f(a), a.shape[0], a.shape[1])
+
+    def set_regularization_pose(self, T):
+        if T is None:
+            lib().orc_mg_set_regularization_pose(self.h, None)
+        else:
+            t = np.ascontiguousarray(T, np.float32).reshape(16)
+            lib().orc_mg_set_regularization_pose(self.h, _f(t))
+
+    def compute_derivatives(self, p, compute_hessian=True):
+        p = np.ascontiguousarray(p, np.float64)
+        g = np.zeros(6); H = np.zeros((6, 6)); nv = np.zeros(1)
+        s = lib().orc_mg_compute_derivatives(self.h, _d(p), int(compute_hessian), _d(g), _d(H), _d(nv))
+        return s, g, H, nv[0]
+
+    def align(self, guess=None, max_trace=128):
+        guess = np.eye(4, dtype=np.float32) if guess is None else np.ascontiguousarray(guess, np.float32)
+        T = np.zeros((4, 4), np.float32); H = np.zeros((6, 6)); tp = np.zeros(1); nv = np.zeros(1)
+        it = np.zeros(1, np.int32); cv = np.zeros(1, np.int32); nt = np.zeros(1, np.int32); na = np.zeros(1, np.int32)
+        trace = np.zeros((max_trace, 50)); tarr = np.zeros((max_trace, 16), np.float32)
+        rc = lib().orc_mg_align(self.h, _f(guess.reshape(16)), _f(T), _d(H), _d(tp), _d(nv), _i(it), _i(cv), _d(trace), max_trace, _i(nt),
+                                _f(tarr), max_trace, _i(na))
+        if rc != 0:
+            raise RuntimeError("kd-tree is stale: call create_kdtree() after add_target / remove_target")
+        return dict(T=T, hessian=H, trans_probability=tp[0], nvtl=nv[0], iterations=int(it[0]), converged=bool(cv[0]),
+                    trace=trace[: nt[0]].copy(), transformation_array=tarr[: na[0]].reshape(-1, 4, 4).copy())
+
+    def __del__(self):
+        try:
+            lib().orc_mg_destroy(self.h)
         except Exception:
             pass
 
