@@ -214,6 +214,8 @@ int ndtb_mg_get_grid_ids(ndtb_handle h, char* buf, size_t capacity, size_t* need
 int ndtb_mg_get_leaves(ndtb_handle h, size_t capacity, int32_t* nr_points, double* mean, double* icov, float* centroid_xyz, size_t* count);
 int ndtb_mg_compute_derivatives(ndtb_handle h, const double p[6], const float* T16, int compute_hessian, double* score, double gradient[6],
                                 double hessian[36], double* nvtl);
+/* calculateTransformationProbability / calculateNearestVoxelTransformationLikelihood, multigrid_ndt_omp_impl.hpp:1054-1145 */
+int ndtb_mg_calculate_scores(ndtb_handle h, const float T16[16], double* transform_probability, double* nvtl);
 int ndtb_mg_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* transformation_array, int capacity, float* out_xyz);
 
 /* ---- batch replay: n independent alignments against the current target ----------------------- */

@@ -312,6 +312,163 @@ private:
   bool converged_ = false;
 };
 
+// pclomp::MultiGridNormalDistributionsTransform (extern/ndt_omp/include/multigrid_pclomp/multigrid_ndt_omp.h:96-567):
+// the dynamic-map variant -- targets come and go by id, the neighbour search is the radius search over leaf
+// centroids, derivatives are FP64.  Same method names and argument meaning as the reference class.
+template <typename PointSource, typename PointTarget, typename CloudSource = ndtb_facade::PointCloud<PointSource>,
+          typename CloudTarget = ndtb_facade::PointCloud<PointTarget>>
+class MultiGridNormalDistributionsTransform {
+public:
+  using PointCloudSource = CloudSource;
+  using PointCloudSourceConstPtr = std::shared_ptr<const CloudSource>;
+  using PointCloudTarget = CloudTarget;
+  using PointCloudTargetConstPtr = std::shared_ptr<const CloudTarget>;
+  using Ptr = std::shared_ptr<MultiGridNormalDistributionsTransform>;
+  using Matrix4f = ndtb_facade::Matrix4f;
+
+  explicit MultiGridNormalDistributionsTransform(int cuda_device = 0) : h_(cuda_device) {  // multigrid_ndt_omp_impl.hpp:180-207
+    ndtb_default_params(NDTB_FLAVOUR_PCLOMP, &p_);
+    final_transformation_ = ndtb_facade::identity<Matrix4f>();
+  }
+  void setNumThreads(int n) { num_threads_ = n; }  // multigrid_ndt_omp.h:119-123
+  int getNumThreads() const { return num_threads_; }
+  void setInputSource(const PointCloudSourceConstPtr& cloud) {  // :127-135 (a null source is fatal in the reference)
+    if (!cloud) throw std::invalid_argument("Error: Null input source cloud is not allowed");
+    source_ = cloud;
+    source_rc_ = ndtb_facade::upload(h_.h, *cloud, false);
+  }
+  void setInputTarget(const PointCloudTargetConstPtr& cloud) {  // :143-148
+    addTarget(cloud, "default");
+    createVoxelKdtree();
+  }
+  void addTarget(const PointCloudTargetConstPtr& cloud, const std::string& target_id) {  // :150-155
+    using PointT = typename std::remove_reference<decltype(cloud->points[0])>::type;
+    ndtb_set_params(h_.h, &p_);
+    target_rc_ = cloud ? ndtb_mg_add_target(h_.h, target_id.c_str(), cloud->points.empty() ? nullptr : reinterpret_cast<const float*>(cloud->points.data()),
+                                            cloud->points.size(), sizeof(PointT))
+                       : NDTB_ERR_EMPTY;
+  }
+  void removeTarget(const std::string target_id) { ndtb_mg_remove_target(h_.h, target_id.c_str()); }  // :157
+  void createVoxelKdtree() { tree_rc_ = ndtb_mg_create_kdtree(h_.h); }                                 // :159-163
+  void setResolution(float resolution) { p_.resolution = resolution; }  // :165-171 (the reference re-inits only the default target)
+  float getResolution() const { return p_.resolution; }
+  double getStepSize() const { return p_.step_size; }
+  void setStepSize(double s) { p_.step_size = s; }
+  double getOutlierRatio() const { return p_.outlier_ratio; }
+  void setOutlierRatio(double r) { p_.outlier_ratio = r; }
+  void setTransformationEpsilon(double e) { p_.trans_epsilon = e; }
+  double getTransformationEpsilon() { return p_.trans_epsilon; }
+  void setMaximumIterations(int n) { p_.max_iterations = n; }
+  int getMaxIterations() const { return p_.max_iterations; }
+  void setRegularizationScaleFactor(float f) { p_.regularization_scale_factor = f; }
+  void setRegularizationPose(const Matrix4f& pose) {
+    float T[16];
+    ndtb_facade::to_rows(pose, 4, T);
+    ndtb_set_regularization_pose(h_.h, T);
+  }
+  void unsetRegularizationPose() { ndtb_set_regularization_pose(h_.h, nullptr); }
+  void setParams(const NdtParams& q) {  // :302-307
+    p_.trans_epsilon = q.trans_epsilon; p_.step_size = q.step_size; p_.max_iterations = q.max_iterations;
+    p_.regularization_scale_factor = q.regularization_scale_factor; p_.use_line_search = q.use_line_search ? 1 : 0;
+    p_.resolution = static_cast<float>(q.resolution);
+    num_threads_ = q.num_threads;
+  }
+  NdtParams getParams() const {
+    NdtParams q;
+    q.trans_epsilon = p_.trans_epsilon; q.step_size = p_.step_size; q.resolution = p_.resolution; q.max_iterations = p_.max_iterations;
+    q.search_method = KDTREE; q.num_threads = num_threads_;
+    q.regularization_scale_factor = p_.regularization_scale_factor; q.use_line_search = p_.use_line_search != 0;
+    return q;
+  }
+  std::vector<std::string> getCurrentMapIDs() const {  // :325
+    std::size_t need = 0;
+    ndtb_mg_get_grid_ids(h_.h, nullptr, 0, &need);
+    std::string buf(need, '\0');
+    ndtb_mg_get_grid_ids(h_.h, &buf[0], need, nullptr);
+    std::vector<std::string> out;
+    std::size_t a = 0;
+    const std::string s(buf.c_str());
+    while (a < s.size()) { std::size_t b = s.find('\n', a); if (b == std::string::npos) b = s.size(); out.push_back(s.substr(a, b - a)); a = b + 1; }
+    return out;
+  }
+  CloudTarget getVoxelPCD() const {  // :323: the leaf centroids the kd-tree is built over
+    CloudTarget out;
+    std::size_t k = 0;
+    if (ndtb_mg_get_leaves(h_.h, 0, nullptr, nullptr, nullptr, nullptr, &k) != NDTB_OK || k == 0) return out;
+    std::vector<float> c(3 * k);
+    ndtb_mg_get_leaves(h_.h, k, nullptr, nullptr, nullptr, c.data(), nullptr);
+    out.points.resize(k);
+    for (std::size_t i = 0; i < k; ++i) std::memcpy(reinterpret_cast<float*>(&out.points[i]), c.data() + 3 * i, 12);
+    return out;
+  }
+
+  void align(CloudSource& output, const Matrix4f& guess) {  // pcl::Registration::align -> computeTransformation :210-323
+    converged_ = false;
+    nr_iterations_ = 0;
+    if (ndtb_set_params(h_.h, &p_) != NDTB_OK || target_rc_ != NDTB_OK || tree_rc_ != NDTB_OK || source_rc_ != NDTB_OK || !source_) return;
+    float g[16];
+    ndtb_facade::to_rows(guess, 4, g);
+    ndtb_result r;
+    std::vector<float> arr(16 * kMaxArray);
+    const std::size_t n = source_->points.size();
+    std::vector<float> out(3 * n);
+    if (ndtb_mg_align(h_.h, g, &r, arr.data(), kMaxArray, out.data()) != NDTB_OK) return;
+    ndtb_facade::from_rows(r.pose, 4, final_transformation_);
+    ndtb_facade::from_rows(r.hessian, 6, hessian_);
+    trans_probability_ = r.transform_probability;
+    nvtl_ = r.nearest_voxel_transformation_likelihood;
+    nr_iterations_ = r.iteration_num;
+    converged_ = r.converged != 0;
+    transformation_array_.resize(r.transformation_array_len);
+    for (int i = 0; i < r.transformation_array_len; ++i) ndtb_facade::from_rows(arr.data() + 16 * i, 4, transformation_array_[i]);
+    output = *source_;
+    for (std::size_t i = 0; i < n; ++i) std::memcpy(reinterpret_cast<float*>(&output.points[i]), out.data() + 3 * i, 12);
+  }
+  void align(CloudSource& output) { align(output, ndtb_facade::identity<Matrix4f>()); }
+
+  Matrix4f getFinalTransformation() const { return final_transformation_; }
+  bool hasConverged() const { return converged_; }
+  double getTransformationProbability() const { return trans_probability_; }
+  double getNearestVoxelTransformationLikelihood() const { return nvtl_; }
+  int getFinalNumIteration() const { return nr_iterations_; }
+  ndtb_facade::Matrix6d getHessian() const { return hessian_; }
+  const std::vector<Matrix4f>& getFinalTransformationArray() const { return transformation_array_; }
+  NdtResult getResult() {  // :283-296
+    NdtResult r;
+    r.pose = final_transformation_;
+    r.transform_probability = static_cast<float>(trans_probability_);
+    r.nearest_voxel_transformation_likelihood = static_cast<float>(nvtl_);
+    r.iteration_num = nr_iterations_;
+    r.transformation_array = transformation_array_;
+    r.hessian = hessian_;
+    return r;
+  }
+  // the reference takes an already transformed cloud; here the transform is passed and applied on the device
+  double calculateTransformationProbability(const Matrix4f& trans) { double tp = 0, nv = 0; scores(trans, &tp, &nv); return tp; }
+  double calculateNearestVoxelTransformationLikelihood(const Matrix4f& trans) { double tp = 0, nv = 0; scores(trans, &tp, &nv); return nv; }
+  std::string lastError() const { return ndtb_last_error(h_.h); }
+  ndtb_handle native() { return h_.h; }
+
+private:
+  static constexpr int kMaxArray = 64;
+  void scores(const Matrix4f& trans, double* tp, double* nv) {
+    float T[16];
+    ndtb_facade::to_rows(trans, 4, T);
+    ndtb_mg_calculate_scores(h_.h, T, tp, nv);
+  }
+  ndtb_facade::Handle h_;
+  ndtb_params p_{};
+  int num_threads_ = 1;
+  PointCloudSourceConstPtr source_;
+  int target_rc_ = NDTB_ERR_NOT_READY, tree_rc_ = NDTB_ERR_NOT_READY, source_rc_ = NDTB_ERR_NOT_READY;
+  Matrix4f final_transformation_;
+  ndtb_facade::Matrix6d hessian_;
+  std::vector<Matrix4f> transformation_array_;
+  double trans_probability_ = 0, nvtl_ = 0;
+  int nr_iterations_ = 0;
+  bool converged_ = false;
+};
+
 }  // namespace pclomp
 
 namespace svn_ndt {

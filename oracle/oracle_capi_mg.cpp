@@ -65,6 +65,34 @@ double orc_mg_compute_derivatives(void* h, const double* p, int compute_hessian,
   if (nvtl) *nvtl = n->nvtl;
   return s;
 }
+// calculateTransformationProbability + calculateNearestVoxelTransformationLikelihood (multigrid_ndt_omp_impl.hpp:1054-1145)
+void orc_mg_calculate_scores(void* h, const float* T, double* tp, double* nvtl_out) {
+  MultigridNdt* n = static_cast<MultigridNdt*>(h);
+  n->update_gauss();
+  std::vector<float> trans; n->transform_cloud(T, trans);
+  const size_t N = trans.size() / 3;
+  double score = 0, nearest = 0; size_t found = 0;
+  std::vector<std::pair<float, const Leaf*>> hits;
+  for (size_t i = 0; i < N; ++i) {
+    const float* xt = &trans[3 * i];
+    n->radius_search(xt, hits);
+    if (hits.empty()) continue;
+    double tmp = 0, best = 0;
+    for (auto& hh : hits) {
+      const double x[3] = {static_cast<double>(xt[0]) - hh.second->mean[0], static_cast<double>(xt[1]) - hh.second->mean[1], static_cast<double>(xt[2]) - hh.second->mean[2]};
+      const double* C = hh.second->icov;
+      double Cx[3];
+      for (int r = 0; r < 3; ++r) Cx[r] = (C[3 * r] * x[0] + C[3 * r + 1] * x[1]) + C[3 * r + 2] * x[2];
+      const double q = (x[0] * Cx[0] + x[1] * Cx[1]) + x[2] * Cx[2];
+      const double s = -n->gauss_d1 * std::exp(-n->gauss_d2 * q / 2.0);
+      tmp += s;
+      if (s > best) best = s;
+    }
+    score += tmp; nearest += best; ++found;
+  }
+  *tp = N ? score / static_cast<double>(N) : 0.0;
+  *nvtl_out = found ? nearest / static_cast<double>(found) : 0.0;
+}
 int orc_mg_align(void* h, const float* guess, float* final_T, double* hessian, double* trans_probability, double* nvtl, int* iterations,
                  int* converged, double* trace, int trace_cap, int* n_trace, float* tarray, int tarray_cap, int* n_tarray) {
   MultigridNdt* n = static_cast<MultigridNdt*>(h);

@@ -85,10 +85,12 @@ __device__ __forceinline__ double dot3s(double a0, double a1, double a2, double 
 }
 
 // updateDerivatives, FP64 (multigrid_ndt_omp_impl.hpp:640-697) with every dot product k ascending, left to right (the order the
-// CPU restatement used by the tests pins).
-// Jp: dense 3x6 point gradient; hv: vectors a..f of eq 6.21 (3 doubles each).  acc layout = RED_*.
+// CPU restatement used by the tests pins).  The point gradient is [I | J] with J = columns 3..5 (jc[c][r]); the products
+// with the identity block are not executed: C*1 + C*0 + C*0 == C and x.(C e_c) is the expression of xC[c] itself, so
+// the skipped work is bit-neutral for finite inverse covariances (and no other kind passes the voxel build).
+// hv: vectors a..f of eq 6.21 (3 doubles each).  acc layout = RED_*.
 template <bool HESS>
-__device__ __forceinline__ double mg_pair(const double (&Jp)[3][6], const double (&hv)[6][3], const double* x, const double* C, double d1, double d2,
+__device__ __forceinline__ double mg_pair(const double (&jc)[3][3], const double (&hv)[6][3], const double* x, const double* C, double d1, double d2,
                                           double* __restrict__ acc) {
   double xC[3];
 #pragma unroll
@@ -101,11 +103,16 @@ __device__ __forceinline__ double mg_pair(const double (&Jp)[3][6], const double
   e *= d1;
   double CJ[3][6], xCJ[6];
 #pragma unroll
-  for (int r = 0; r < 3; ++r)
+  for (int r = 0; r < 3; ++r) {
 #pragma unroll
-    for (int c = 0; c < 6; ++c) CJ[r][c] = dot3s(C[3 * r], C[3 * r + 1], C[3 * r + 2], Jp[0][c], Jp[1][c], Jp[2][c]);
+    for (int c = 0; c < 3; ++c) CJ[r][c] = C[3 * r + c];
 #pragma unroll
-  for (int c = 0; c < 6; ++c) xCJ[c] = dot3s(x[0], x[1], x[2], CJ[0][c], CJ[1][c], CJ[2][c]);
+    for (int c = 0; c < 3; ++c) CJ[r][3 + c] = dot3s(C[3 * r], C[3 * r + 1], C[3 * r + 2], jc[c][0], jc[c][1], jc[c][2]);
+  }
+#pragma unroll
+  for (int c = 0; c < 3; ++c) xCJ[c] = xC[c];
+#pragma unroll
+  for (int c = 3; c < 6; ++c) xCJ[c] = dot3s(x[0], x[1], x[2], CJ[0][c], CJ[1][c], CJ[2][c]);
 #pragma unroll
   for (int c = 0; c < 6; ++c) acc[RED_G + c] += e * xCJ[c];
   if (HESS) {
@@ -114,7 +121,8 @@ __device__ __forceinline__ double mg_pair(const double (&Jp)[3][6], const double
     for (int i = 0; i < 6; ++i) {
 #pragma unroll
       for (int j = 0; j < 6; ++j) {
-        const double jcj = dot3s(Jp[0][j], Jp[1][j], Jp[2][j], CJ[0][i], CJ[1][i], CJ[2][i]);  // (Jp^T C Jp)(j, i)
+        // (Jp^T C Jp)(j, i): column j of Jp dotted with column i of C Jp
+        const double jcj = (j < 3) ? CJ[j][i] : dot3s(jc[j - 3][0], jc[j - 3][1], jc[j - 3][2], CJ[0][i], CJ[1][i], CJ[2][i]);
         double xch = 0.0;  // x C (zero block of point_hessian) = 0
         if (i >= 3 && j >= 3) {
           const int s = hsel[i - 3][j - 3];
@@ -127,6 +135,11 @@ __device__ __forceinline__ double mg_pair(const double (&Jp)[3][6], const double
   return score_inc;
 }
 
+constexpr int MG_HITS = 48;  // per-point hit list; a longer neighbourhood is evaluated in several flushes
+
+// Phase A collects a point's neighbourhood (per overlapping grid 3 layers x 9 hash probes issued together, then the
+// centroid distance test), phase B runs the FP64 pair maths over the collected hits: the lanes of a warp stay in the
+// maths loop together instead of entering it once per probed cell with a handful of lanes active.
 template <bool HESS>
 __global__ void __launch_bounds__(MG_THREADS) mg_eval_kernel(const float4* __restrict__ src, int n, const MgGridDev* __restrict__ grids, int n_grids,
                                                              const __grid_constant__ MgEvalState st, double* __restrict__ block_out) {
@@ -139,10 +152,43 @@ __global__ void __launch_bounds__(MG_THREADS) mg_eval_kernel(const float4* __res
     float xt[3];
 #pragma unroll
     for (int r = 0; r < 3; ++r) xt[r] = st.T[4 * r] * p.x + (st.T[4 * r + 1] * p.y + (st.T[4 * r + 2] * p.z + st.T[4 * r + 3]));
-    bool have_tables = false;
-    double Jp[3][6], hv[6][3];
+    // computePointDerivatives, FP64 (multigrid_ndt_omp_impl.hpp:590-636)
+    double jc[3][3], hv[6][3];
+    {
+      const double x0 = static_cast<double>(p.x), x1 = static_cast<double>(p.y), x2 = static_cast<double>(p.z);
+      auto dj = [&](int r) { return dot3s(st.jd[3 * r], st.jd[3 * r + 1], st.jd[3 * r + 2], x0, x1, x2); };
+      auto dh = [&](int r) { return dot3s(st.hd[3 * r], st.hd[3 * r + 1], st.hd[3 * r + 2], x0, x1, x2); };
+      jc[0][0] = 0.0; jc[0][1] = dj(0); jc[0][2] = dj(1);
+      jc[1][0] = dj(2); jc[1][1] = dj(3); jc[1][2] = dj(4);
+      jc[2][0] = dj(5); jc[2][1] = dj(6); jc[2][2] = dj(7);
+      if (HESS) {
+        hv[0][0] = 0.0; hv[0][1] = dh(0); hv[0][2] = dh(1);
+        hv[1][0] = 0.0; hv[1][1] = dh(2); hv[1][2] = dh(3);
+        hv[2][0] = 0.0; hv[2][1] = dh(4); hv[2][2] = dh(5);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { hv[3][k] = dh(6 + k); hv[4][k] = dh(9 + k); hv[5][k] = dh(12 + k); }
+      }
+    }
     double sum_score = 0.0, nearest = 0.0;
-    int nn = 0;
+    int nn = 0, n_list = 0;
+    int hit_row[MG_HITS];
+    unsigned char hit_grid[MG_HITS];
+    auto flush = [&]() {
+      for (int k = 0; k < n_list; ++k) {
+        const MgGridDev& G = grids[hit_grid[k]];
+        const size_t row = static_cast<size_t>(hit_row[k]);
+        double xr[3], C[9];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) xr[a] = static_cast<double>(xt[a]) - __ldg(G.c_mean + 3 * row + a);
+#pragma unroll
+        for (int i = 0; i < 9; ++i) C[i] = __ldg(G.c_icov + 9 * row + i);
+        const double s = mg_pair<HESS>(jc, hv, xr, C, st.d1, st.d2, acc);
+        sum_score += s;
+        if (s > nearest) nearest = s;
+      }
+      nn += n_list;
+      n_list = 0;
+    };
     for (int gi = 0; gi < n_grids; ++gi) {
       const MgGridDev& G = grids[gi];
       const float leaf = G.meta.leaf;
@@ -151,56 +197,52 @@ __global__ void __launch_bounds__(MG_THREADS) mg_eval_kernel(const float4* __res
       const int i2 = static_cast<int>(floorf(__fdiv_rn(xt[2], leaf)));
       if (i0 + 1 < G.meta.min_b[0] || i0 - 1 > G.meta.max_b[0] || i1 + 1 < G.meta.min_b[1] || i1 - 1 > G.meta.max_b[1] ||
           i2 + 1 < G.meta.min_b[2] || i2 - 1 > G.meta.max_b[2]) continue;
+      const uint32_t mask = G.meta.hash_mask;
       for (int oz = -1; oz <= 1; ++oz) {
         const int c2 = i2 + oz;
         if (c2 < G.meta.min_b[2] || c2 > G.meta.max_b[2]) continue;
-        for (int oy = -1; oy <= 1; ++oy) {
-          const int c1 = i1 + oy;
-          if (c1 < G.meta.min_b[1] || c1 > G.meta.max_b[1]) continue;
-          for (int ox = -1; ox <= 1; ++ox) {
-            const int c0 = i0 + ox;
-            if (c0 < G.meta.min_b[0] || c0 > G.meta.max_b[0]) continue;
-            const uint32_t key = static_cast<uint32_t>((c0 - G.meta.min_b[0]) * G.meta.divb_mul[0] + (c1 - G.meta.min_b[1]) * G.meta.divb_mul[1] +
-                                                       (c2 - G.meta.min_b[2]) * G.meta.divb_mul[2]);
-            const int row = hash_find(G.table, G.meta.hash_mask, key);
-            if (row < 0) continue;
-            // FLANN L2_Simple<float> against the leaf centroid, strict '<' (RadiusResultSet::addPoint)
-            const float4 cen = __ldg(G.centroid + row);
-            const float dx = xt[0] - cen.x, dy = xt[1] - cen.y, dz = xt[2] - cen.z;
-            float d = dx * dx; d = d + dy * dy; d = d + dz * dz;
-            if (!(d < st.r2)) continue;
-            if (!have_tables) {
-              // computePointDerivatives, FP64 (multigrid_ndt_omp_impl.hpp:590-636): once per point with neighbours
-              have_tables = true;
-              const double x0 = static_cast<double>(p.x), x1 = static_cast<double>(p.y), x2 = static_cast<double>(p.z);
-              auto dj = [&](int r) { return dot3s(st.jd[3 * r], st.jd[3 * r + 1], st.jd[3 * r + 2], x0, x1, x2); };
-              auto dh = [&](int r) { return dot3s(st.hd[3 * r], st.hd[3 * r + 1], st.hd[3 * r + 2], x0, x1, x2); };
+        uint32_t key[9];
+        uint2 slot[9];
 #pragma unroll
-              for (int r = 0; r < 3; ++r)
+        for (int q = 0; q < 9; ++q) {
+          const int c0 = i0 + (q % 3) - 1, c1 = i1 + (q / 3) - 1;
+          const bool in = c0 >= G.meta.min_b[0] && c0 <= G.meta.max_b[0] && c1 >= G.meta.min_b[1] && c1 <= G.meta.max_b[1];
+          key[q] = in ? static_cast<uint32_t>((c0 - G.meta.min_b[0]) * G.meta.divb_mul[0] + (c1 - G.meta.min_b[1]) * G.meta.divb_mul[1] +
+                                              (c2 - G.meta.min_b[2]) * G.meta.divb_mul[2])
+                      : HASH_EMPTY;
+        }
 #pragma unroll
-                for (int c = 0; c < 6; ++c) Jp[r][c] = (r == c) ? 1.0 : 0.0;
-              Jp[1][3] = dj(0); Jp[2][3] = dj(1); Jp[0][4] = dj(2); Jp[1][4] = dj(3); Jp[2][4] = dj(4); Jp[0][5] = dj(5); Jp[1][5] = dj(6); Jp[2][5] = dj(7);
-              if (HESS) {
-                hv[0][0] = 0.0; hv[0][1] = dh(0); hv[0][2] = dh(1);
-                hv[1][0] = 0.0; hv[1][1] = dh(2); hv[1][2] = dh(3);
-                hv[2][0] = 0.0; hv[2][1] = dh(4); hv[2][2] = dh(5);
+        for (int q = 0; q < 9; ++q)
+          slot[q] = (key[q] != HASH_EMPTY) ? __ldg(reinterpret_cast<const uint2*>(G.table) + (key[q] & mask)) : make_uint2(HASH_EMPTY, 0u);
+        int rows[9];
 #pragma unroll
-                for (int k = 0; k < 3; ++k) { hv[3][k] = dh(6 + k); hv[4][k] = dh(9 + k); hv[5][k] = dh(12 + k); }
-              }
-            }
-            double xr[3], C[9];
-#pragma unroll
-            for (int a = 0; a < 3; ++a) xr[a] = static_cast<double>(xt[a]) - __ldg(G.c_mean + 3 * static_cast<size_t>(row) + a);
-#pragma unroll
-            for (int i = 0; i < 9; ++i) C[i] = __ldg(G.c_icov + 9 * static_cast<size_t>(row) + i);
-            const double s = mg_pair<HESS>(Jp, hv, xr, C, st.d1, st.d2, acc);
-            sum_score += s;
-            if (s > nearest) nearest = s;
-            ++nn;
+        for (int q = 0; q < 9; ++q) {
+          uint2 v = slot[q];
+          uint32_t b = key[q] & mask;
+          while (v.x != key[q] && v.x != HASH_EMPTY) {  // displaced key (load <= 0.5): the usual linear probe
+            b = (b + 1) & mask;
+            v = __ldg(reinterpret_cast<const uint2*>(G.table) + b);
           }
+          rows[q] = (v.x == HASH_EMPTY) ? -1 : static_cast<int>(v.y);
+        }
+        float4 cen[9];
+#pragma unroll
+        for (int q = 0; q < 9; ++q) cen[q] = (rows[q] >= 0) ? __ldg(G.centroid + rows[q]) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int q = 0; q < 9; ++q) {
+          if (rows[q] < 0) continue;
+          // FLANN L2_Simple<float> against the leaf centroid, strict '<' (RadiusResultSet::addPoint)
+          const float dx = xt[0] - cen[q].x, dy = xt[1] - cen[q].y, dz = xt[2] - cen[q].z;
+          float d = dx * dx; d = d + dy * dy; d = d + dz * dz;
+          if (!(d < st.r2)) continue;
+          if (n_list == MG_HITS) flush();
+          hit_row[n_list] = rows[q];
+          hit_grid[n_list] = static_cast<unsigned char>(gi);
+          ++n_list;
         }
       }
     }
+    flush();
     if (nn > 0) {
       acc[RED_SCORE] += sum_score;
       acc[RED_NEAREST] += nearest;
@@ -323,6 +365,7 @@ int ndtb_mg_add_target(ndtb_handle h, const char* grid_id, const float* xyz, siz
   if (it != s->grids.end()) g = it->second; else { g = new MgGrid(); s->grids[grid_id] = g; }
   s->dirty = true;
   const ndtb_params& P = h->params;
+  const uint64_t launches_before = g->grid.launches;
   rc = build_voxel_map(g->grid, s->d_in, n, P.resolution, P.min_points_per_voxel, P.min_covar_eigvalue_mult, FLAVOUR_PCLOMP, P.is_dense, h->stream);
   if (rc != NDTB_OK) {  // applyFilter :307-313 warns and leaves the node empty; here the id is not registered at all
     free_device_grid(g->grid); cudaFree(g->d_centroid); delete g; s->grids.erase(grid_id);
@@ -337,6 +380,7 @@ int ndtb_mg_add_target(ndtb_handle h, const char* grid_id, const float* xyz, siz
   const uint32_t n_valid_pts = static_cast<uint32_t>(n) - static_cast<uint32_t>(g->grid.h_pinned[0]);
   mg_centroid_kernel<<<std::min<int>((V + 127) / 128, 148 * 8), 128, 0, h->stream>>>(g->grid.sorted_xyz, g->grid.seg_start, V, n_valid_pts, g->d_centroid);
   g->grid.launches += 1;
+  h->launches += g->grid.launches - launches_before;  // ndtb_get_launch_count: the per-tile builds are this handle's kernels too
   CKH(cudaGetLastError());
   CKH(cudaStreamSynchronize(h->stream));
   return NDTB_OK;
@@ -444,6 +488,24 @@ int ndtb_mg_get_leaves(ndtb_handle h, size_t capacity, int32_t* nr_points, doubl
     }
   }
   if (count) *count = k;
+  return NDTB_OK;
+}
+
+// calculateTransformationProbability / calculateNearestVoxelTransformationLikelihood (multigrid_ndt_omp_impl.hpp:1054-1145)
+// for the source cloud transformed by T16: sum of the pair scores / N and mean of the per-point best pair score over the
+// points with neighbours.  Same pair score as computeDerivatives (no regulariser, no gradient work kept).
+int ndtb_mg_calculate_scores(ndtb_handle h, const float T16[16], double* transform_probability, double* nvtl) {
+  if (!h || !T16) return NDTB_ERR_INVALID;
+  cudaSetDevice(h->device);
+  const bool reg = h->has_reg_pose;
+  h->has_reg_pose = false;
+  const double p0[6] = {0, 0, 0, 0, 0, 0};
+  double score = 0, g[6], H[36], nv = 0;
+  const int rc = mg_eval(h, p0, T16, false, &score, g, H, &nv);
+  h->has_reg_pose = reg;
+  if (rc != NDTB_OK) return rc;
+  if (transform_probability) *transform_probability = h->n_source ? score / static_cast<double>(h->n_source) : 0.0;
+  if (nvtl) *nvtl = nv;
   return NDTB_OK;
 }
 

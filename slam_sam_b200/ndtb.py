@@ -54,7 +54,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "nd
            "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_set_profiling", "ndtb_set_option", "ndtb_time_eval_kernel", "ndtb_newton_direction", "ndtb_hessian_to_covariance", "ndtb_keyframe_put", "ndtb_keyframe_drop", "ndtb_keyframe_count",
            "ndtb_set_target_window", "ndtb_get_target_points", "ndtb_voxelgrid_filter", "ndtb_svn_mean_pose", "ndtb_svn_pose_distance",
            "ndtb_mg_add_target", "ndtb_mg_remove_target", "ndtb_mg_create_kdtree", "ndtb_mg_set_input_target", "ndtb_mg_get_info",
-           "ndtb_mg_get_grid_ids", "ndtb_mg_get_leaves", "ndtb_mg_compute_derivatives", "ndtb_mg_align"]
+           "ndtb_mg_get_grid_ids", "ndtb_mg_get_leaves", "ndtb_mg_compute_derivatives", "ndtb_mg_align", "ndtb_mg_calculate_scores"]
 
 _LIB = None
 
@@ -127,6 +127,7 @@ def lib():
         L.ndtb_mg_get_leaves.argtypes = [H, C.c_size_t, C.POINTER(C.c_int32), c_d, c_d, c_f, C.POINTER(C.c_size_t)]
         L.ndtb_mg_compute_derivatives.argtypes = [H, c_d, c_f, C.c_int, c_d, c_d, c_d, c_d]
         L.ndtb_mg_align.argtypes = [H, c_f, C.POINTER(Result), c_f, C.c_int, c_f]
+        L.ndtb_mg_calculate_scores.argtypes = [H, c_f, c_d, c_d]
         _LIB = L
     return _LIB
 
@@ -313,6 +314,11 @@ class Handle:
         self.check(self.L.ndtb_mg_compute_derivatives(self.h, _ptr(p, c_d), _ptr(t, c_f), int(compute_hessian), _ptr(s, c_d), _ptr(g, c_d),
                                                       _ptr(H, c_d), _ptr(nv, c_d)))
         return s[0], g, H, nv[0]
+
+    def mg_calculate_scores(self, T):
+        t = np.ascontiguousarray(T, np.float32).reshape(16); tp = np.zeros(1); nv = np.zeros(1)
+        self.check(self.L.ndtb_mg_calculate_scores(self.h, _ptr(t, c_f), _ptr(tp, c_d), _ptr(nv, c_d)))
+        return tp[0], nv[0]
 
     def mg_align(self, guess=None, capacity=64):
         guess = np.eye(4, dtype=np.float32) if guess is None else np.ascontiguousarray(guess, np.float32)

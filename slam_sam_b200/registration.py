@@ -150,6 +150,54 @@ class NormalDistributionsTransform:
         return self._h
 
 
+class MultiGridNormalDistributionsTransform(NormalDistributionsTransform):
+    """pclomp::MultiGridNormalDistributionsTransform (extern/ndt_omp/include/multigrid_pclomp/multigrid_ndt_omp.h):
+    the target is a set of voxel grids keyed by an id (addTarget / removeTarget / createVoxelKdtree), the only
+    neighbour search is the radius search over leaf centroids, derivatives are FP64.  Setters are the base class's."""
+
+    def setNeighborhoodSearchMethod(self, m):  # noqa: N802  multigrid_ndt_omp_impl.hpp:197: KDTREE only
+        if int(m) != KDTREE:
+            raise ndtb.NdtbError(ndtb.NDTB_ERR_INVALID, "only KDTREE is supported in multigrid_ndt_omp")
+
+    def setInputTarget(self, cloud):  # noqa: N802  multigrid_ndt_omp.h:143-148
+        self.addTarget(cloud, "default")
+        self.createVoxelKdtree()
+
+    def addTarget(self, cloud, target_id):  # noqa: N802  multigrid_ndt_omp.h:150-155
+        rc = self._h.mg_add_target(cloud, target_id)
+        if rc not in (ndtb.NDTB_OK, ndtb.NDTB_ERR_EMPTY, ndtb.NDTB_ERR_OVERFLOW):   # the reference only warns on those
+            self._h.check(rc)
+        self.last_status = rc
+
+    def removeTarget(self, target_id):  # noqa: N802  multigrid_ndt_omp.h:157
+        self._h.check(self._h.mg_remove_target(target_id))
+
+    def createVoxelKdtree(self):  # noqa: N802  multigrid_ndt_omp.h:159-163
+        self._h.check(self._h.mg_create_kdtree())
+
+    def getCurrentMapIDs(self):  # noqa: N802  multigrid_ndt_omp.h:325
+        return self._h.mg_grid_ids()
+
+    def getVoxelPCD(self):  # noqa: N802  multigrid_ndt_omp.h:323: the leaf centroids the kd-tree is built over
+        return self._h.mg_leaves()["centroid"]
+
+    def align(self, guess=None):
+        self._last = self._h.mg_align(guess)
+        return self._last
+
+    def calculateTransformationProbability(self, T):  # noqa: N802
+        return self._h.mg_calculate_scores(T)[0]
+
+    def calculateNearestVoxelTransformationLikelihood(self, T):  # noqa: N802
+        return self._h.mg_calculate_scores(T)[1]
+
+    def getTargetCells(self):  # noqa: N802
+        return self._h.mg_leaves()
+
+    def computeDerivatives(self, p, T=None, compute_hessian=True):  # noqa: N802
+        return self._h.mg_compute_derivatives(p, T, compute_hessian)
+
+
 class SvnNdtResult:
     """svn_ndt::SvnNdtResult (svn_ndt.h:40-51)."""
 

@@ -64,6 +64,21 @@ int main(int argc, char** argv) {
     std::printf("win %d %d", win.hasConverged() ? 1 : 0, win.getFinalNumIteration());
     for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) std::printf(" %.9g", static_cast<double>(Tw(i, j)));
     std::printf("\n");
+    // multigrid NDT: the target handed over as two tiles (even / odd points), as a dynamic map loader would
+    pclomp::MultiGridNormalDistributionsTransform<PointXYZ, PointXYZ> mg;
+    mg.setResolution(1.0f); mg.setMaximumIterations(50); mg.setTransformationEpsilon(1e-4); mg.setStepSize(0.1);
+    auto whole = load(argv[1]);
+    auto t0 = std::make_shared<Cloud>(), t1 = std::make_shared<Cloud>();
+    for (std::size_t i = 0; i < whole->points.size(); ++i) (whole->points[i].x < 0.f ? t0 : t1)->points.push_back(whole->points[i]);
+    mg.addTarget(t0, "west"); mg.addTarget(t1, "east"); mg.addTarget(t1, "stale"); mg.removeTarget("stale");
+    mg.createVoxelKdtree();
+    mg.setInputSource(load(argv[2]));
+    Cloud aligned3;
+    mg.align(aligned3, guess);
+    const auto Tm = mg.getFinalTransformation();
+    std::printf("mg %d %d", mg.hasConverged() ? 1 : 0, mg.getFinalNumIteration());
+    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) std::printf(" %.9g", static_cast<double>(Tm(i, j)));
+    std::printf(" %zu %zu %.9g\n", mg.getCurrentMapIDs().size(), mg.getVoxelPCD().points.size(), mg.calculateNearestVoxelTransformationLikelihood(Tm));
   }
   return 0;
 }

@@ -74,6 +74,7 @@ def lib():
         L.orc_mg_set_regularization_pose.argtypes = [C.c_void_p, c_f]
         L.orc_mg_compute_derivatives.restype = C.c_double
         L.orc_mg_compute_derivatives.argtypes = [C.c_void_p, c_d, C.c_int, c_d, c_d, c_d]
+        L.orc_mg_calculate_scores.argtypes = [C.c_void_p, c_f, c_d, c_d]
         L.orc_mg_align.argtypes = [C.c_void_p, c_f, c_f, c_d, c_d, c_d, c_i, c_i, c_d, C.c_int, c_i, c_f, C.c_int, c_i]
         L.orc_voxelgrid_filter.restype = C.c_long
         L.orc_svn_create.restype = C.c_void_p
@@ -291,6 +292,11 @@ class OracleMultigrid:
         g = np.zeros(6); H = np.zeros((6, 6)); nv = np.zeros(1)
         s = lib().orc_mg_compute_derivatives(self.h, _d(p), int(compute_hessian), _d(g), _d(H), _d(nv))
         return s, g, H, nv[0]
+
+    def calculate_scores(self, T):
+        t = np.ascontiguousarray(T, np.float32).reshape(16); tp = np.zeros(1); nv = np.zeros(1)
+        lib().orc_mg_calculate_scores(self.h, _f(t), _d(tp), _d(nv))
+        return tp[0], nv[0]
 
     def align(self, guess=None, max_trace=128):
         guess = np.eye(4, dtype=np.float32) if guess is None else np.ascontiguousarray(guess, np.float32)

@@ -56,3 +56,16 @@ def test_facade_matches_python_binding(two_plane, tmp_path):
     assert lines[1].startswith("svn ") and int(lines[1].split()[2]) == 5
     w = lines[2].split()   # device-assembled window of one identity-pose keyframe == the uploaded target
     assert w[0] == "win" and w[1:3] == f[0:2] and w[3:19] == f[2:18]
+    # multigrid facade: two tiles split at x = 0, a third added and removed again
+    m = lines[3].split()
+    assert m[0] == "mg" and int(m[1]) == 1
+    mg = registration.MultiGridNormalDistributionsTransform()
+    mg.setResolution(1.0); mg.setMaximumIterations(50); mg.setTransformationEpsilon(1e-4); mg.setStepSize(0.1)
+    tgt = np.ascontiguousarray(two_plane["target"], np.float32)
+    mg.addTarget(np.ascontiguousarray(tgt[tgt[:, 0] < 0]), "west"); mg.addTarget(np.ascontiguousarray(tgt[tgt[:, 0] >= 0]), "east")
+    mg.createVoxelKdtree(); mg.setInputSource(two_plane["source"])
+    mg.align(guess)
+    assert int(m[2]) == mg.getFinalNumIteration()
+    assert np.abs(np.array([float(v) for v in m[3:19]]).reshape(4, 4) - mg.getFinalTransformation()).max() <= 1e-6
+    assert int(m[19]) == 2 and int(m[20]) == len(mg.getVoxelPCD())
+    assert abs(float(m[21]) - mg.calculateNearestVoxelTransformationLikelihood(mg.getFinalTransformation())) <= 1e-6

@@ -244,3 +244,46 @@ def test_gpu_multigrid_dynamic_map_update(oracle, pair):
     p = np.array([0.2, 0.1, 0.0, 0.0, 0.0, 0.3])
     s, g, H, _ = h.mg_compute_derivatives(p); so, go, Ho, _ = o2.compute_derivatives(p)
     assert abs(s - so) <= TOL * abs(so) and rel_inf(g, go) <= TOL and rel_inf(H, Ho) <= TOL
+
+
+@pytest.mark.gpu
+def test_gpu_multigrid_facade_reads_like_the_reference(oracle, pair):
+    """The call sequence of a dynamic-map localiser on the reference class, on the Python mirror of it."""
+    from slam_sam_b200 import registration
+
+    ndt = registration.MultiGridNormalDistributionsTransform()
+    ndt.setResolution(1.0); ndt.setStepSize(0.1); ndt.setTransformationEpsilon(0.01); ndt.setMaximumIterations(30)
+    ndt.setNumThreads(8)
+    with pytest.raises(ndtb.NdtbError):
+        ndt.setNeighborhoodSearchMethod(registration.DIRECT7)
+    T = tiles(pair["target"], 2, 2)
+    for k, c in T.items():
+        ndt.addTarget(c, k)
+    ndt.createVoxelKdtree()
+    assert ndt.getCurrentMapIDs() == sorted(T)
+    ndt.setInputSource(pair["source"])
+    ndt.align(None)
+    assert ndt.hasConverged() and ndt.getFinalNumIteration() < 30
+    o = O.OracleMultigrid(resolution=1.0, step_size=0.1, trans_epsilon=0.01, max_iterations=30, num_threads=8)
+    for k, c in T.items():
+        o.add_target(c, k)
+    o.create_kdtree(); o.set_source(pair["source"])
+    ro = o.align(None)
+    assert ndt.getFinalNumIteration() == ro["iterations"]
+    assert np.abs(ndt.getFinalTransformation() - ro["T"]).max() <= 1e-6
+    assert abs(ndt.getTransformationProbability() - ro["trans_probability"]) <= TOL * abs(ro["trans_probability"])
+    assert abs(ndt.getNearestVoxelTransformationLikelihood() - ro["nvtl"]) <= TOL * abs(ro["nvtl"])
+    assert rel_inf(ndt.getHessian(), ro["hessian"]) <= TOL
+    assert len(ndt.getFinalTransformationArray()) == len(ro["transformation_array"])
+    tp, nv = o.calculate_scores(ro["T"])
+    assert abs(ndt.calculateTransformationProbability(ro["T"]) - tp) <= TOL * abs(tp)
+    assert abs(ndt.calculateNearestVoxelTransformationLikelihood(ro["T"]) - nv) <= TOL * abs(nv)
+    assert ndt.getVoxelPCD().shape == (len(o.leaves()["n"]), 3)
+    ndt.removeTarget(sorted(T)[0]); ndt.createVoxelKdtree()
+    assert ndt.getCurrentMapIDs() == sorted(T)[1:]
+    # setInputTarget == addTarget("default") + createVoxelKdtree
+    one = registration.MultiGridNormalDistributionsTransform(); one.setResolution(1.0)
+    one.setInputTarget(pair["target"]); one.setInputSource(pair["source"])
+    assert one.getCurrentMapIDs() == ["default"]
+    one.align(None)
+    assert abs(fitness(pair, one.getFinalTransformation()) - 0.213937) < 5e-7
