@@ -62,18 +62,73 @@ struct MgEvalState {
   float r2;       // float(radius * radius), pcl::KdTreeFLANN::radiusSearch
 };
 
-// leaf.centroid_ (multi_voxel_grid_covariance_omp_impl.hpp:404-405, :358): float running sum in input order / float(n)
-__global__ void mg_centroid_kernel(const double* __restrict__ sorted_xyz, const uint32_t* __restrict__ seg_start, uint32_t V, uint32_t n_valid_pts,
-                                   float4* __restrict__ out) {
-  for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < V; v += gridDim.x * blockDim.x) {
-    const uint32_t lo = seg_start[v], hi = (v + 1 < V) ? seg_start[v + 1] : n_valid_pts;
+// leaf.centroid_ (multi_voxel_grid_covariance_omp_impl.hpp:404-405, :358): float running sum in input order / float(n).
+// The three float chains of a leaf are sequential by definition (input order).  Light leaves: one lane each.  Heavy
+// leaves (a dense patch of ground holds thousands of points): the whole warp takes them one at a time -- 32 lanes
+// load 32 points coalesced into shared memory, lanes 0..2 run the x / y / z chains over the tile (8 values in
+// flight), so a heavy leaf costs one dependent FADD per point instead of one dependent global load.
+constexpr int CEN_THREADS = 128;
+constexpr int CEN_HEAVY = 64;
+__global__ void __launch_bounds__(CEN_THREADS) mg_centroid_kernel(const double* __restrict__ sorted_xyz, const uint32_t* __restrict__ seg_start, uint32_t V,
+                                                                  uint32_t n_valid_pts, float4* __restrict__ out) {
+  __shared__ float s_tile[CEN_THREADS / 32][3][32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const uint32_t Vr = (V + 31u) & ~31u;
+  for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < Vr; v += gridDim.x * blockDim.x) {  // warp-uniform trip count
+    const bool has = v < V;
+    const uint32_t lo = has ? seg_start[v] : 0u;
+    const uint32_t hi = has ? ((v + 1 < V) ? seg_start[v + 1] : n_valid_pts) : 0u;
+    const int n = static_cast<int>(hi - lo);
+    const bool heavy = n > CEN_HEAVY;
     float s0 = 0.f, s1 = 0.f, s2 = 0.f;
-    for (uint32_t i = lo; i < hi; ++i) {
-      const double* q = sorted_xyz + 3 * static_cast<size_t>(i);
-      s0 += static_cast<float>(q[0]); s1 += static_cast<float>(q[1]); s2 += static_cast<float>(q[2]);  // exact: widened floats
+    if (has && !heavy) {
+      const double* q = sorted_xyz + 3 * static_cast<size_t>(lo);
+      int i = 0;
+      for (; i + 4 <= n; i += 4) {
+        float t[12];
+#pragma unroll
+        for (int u = 0; u < 12; ++u) t[u] = static_cast<float>(__ldg(q + 3 * i + u));  // exact: widened floats
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { s0 += t[3 * u]; s1 += t[3 * u + 1]; s2 += t[3 * u + 2]; }
+      }
+      for (; i < n; ++i) { s0 += static_cast<float>(__ldg(q + 3 * i)); s1 += static_cast<float>(__ldg(q + 3 * i + 1)); s2 += static_cast<float>(__ldg(q + 3 * i + 2)); }
     }
-    const float fn = static_cast<float>(hi - lo);
-    out[v] = make_float4(s0 / fn, s1 / fn, s2 / fn, 0.f);
+    unsigned int hm = __ballot_sync(0xffffffffu, heavy);
+    while (hm) {
+      const int o = __ffs(hm) - 1;
+      hm &= hm - 1;
+      const uint32_t wlo = __shfl_sync(0xffffffffu, lo, o);
+      const int wn = __shfl_sync(0xffffffffu, n, o);
+      const double* q = sorted_xyz + 3 * static_cast<size_t>(wlo);
+      float acc = 0.f;
+      float x = 0.f, y = 0.f, z = 0.f;
+      if (lane < wn) { x = static_cast<float>(__ldg(q + 3 * lane)); y = static_cast<float>(__ldg(q + 3 * lane + 1)); z = static_cast<float>(__ldg(q + 3 * lane + 2)); }
+      for (int base = 0; base < wn; base += 32) {
+        s_tile[w][0][lane] = x; s_tile[w][1][lane] = y; s_tile[w][2][lane] = z;
+        const int nxt = base + 32 + lane;
+        if (nxt < wn) { x = static_cast<float>(__ldg(q + 3 * nxt)); y = static_cast<float>(__ldg(q + 3 * nxt + 1)); z = static_cast<float>(__ldg(q + 3 * nxt + 2)); }
+        __syncwarp();
+        const int cnt = min(32, wn - base);
+        if (lane < 3) {
+          int k = 0;
+          for (; k + 8 <= cnt; k += 8) {
+            float t8[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) t8[u] = s_tile[w][lane][k + u];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) acc += t8[u];
+          }
+          for (; k < cnt; ++k) acc += s_tile[w][lane][k];
+        }
+        __syncwarp();
+      }
+      const float a0 = __shfl_sync(0xffffffffu, acc, 0), a1 = __shfl_sync(0xffffffffu, acc, 1), a2 = __shfl_sync(0xffffffffu, acc, 2);
+      if (lane == o) { s0 = a0; s1 = a1; s2 = a2; }
+    }
+    if (has) {
+      const float fn = static_cast<float>(n);
+      out[v] = make_float4(s0 / fn, s1 / fn, s2 / fn, 0.f);
+    }
   }
 }
 
@@ -135,122 +190,188 @@ __device__ __forceinline__ double mg_pair(const double (&jc)[3][3], const double
   return score_inc;
 }
 
-constexpr int MG_HITS = 48;  // per-point hit list; a longer neighbourhood is evaluated in several flushes
+constexpr int MG_QCAP = 512;  // pair queue of one warp: < 32 left over + at most 32 x 9 appended per probe batch
 
-// Phase A collects a point's neighbourhood (per overlapping grid 3 layers x 9 hash probes issued together, then the
-// centroid distance test), phase B runs the FP64 pair maths over the collected hits: the lanes of a warp stay in the
-// maths loop together instead of entering it once per probed cell with a handful of lanes active.
+struct __align__(16) MgSlot {  // one source point of the chunk a warp is working on: 208 B
+  float xt[3];
+  int pad;
+  double jc[8];                      // the eight non-trivial entries of the point gradient (eq 6.18/6.19)
+  double hv[15];                     // the non-trivial entries of a..f (eq 6.21)
+  unsigned long long nearest_bits;   // max pair score of the point (scores are >= 0: the bit pattern orders like the value)
+};
+
+struct MgWarpScratch {
+  MgSlot pt[32];
+  int qrow[MG_QCAP];
+  unsigned short qmeta[MG_QCAP];     // slot (5 bits) | grid << 5
+};
+
+template <bool HESS>
+__device__ __forceinline__ void mg_eval_pair(MgWarpScratch& ws, int e, const MgGridDev* __restrict__ grids, const MgEvalState& st, double* __restrict__ acc) {
+  const int meta = ws.qmeta[e & (MG_QCAP - 1)];
+  const size_t row = static_cast<size_t>(ws.qrow[e & (MG_QCAP - 1)]);
+  MgSlot& sl = ws.pt[meta & 31];
+  const MgGridDev& G = grids[meta >> 5];
+  double jc[3][3], hv[6][3];
+  jc[0][0] = 0.0; jc[0][1] = sl.jc[0]; jc[0][2] = sl.jc[1];
+  jc[1][0] = sl.jc[2]; jc[1][1] = sl.jc[3]; jc[1][2] = sl.jc[4];
+  jc[2][0] = sl.jc[5]; jc[2][1] = sl.jc[6]; jc[2][2] = sl.jc[7];
+  if (HESS) {
+    hv[0][0] = 0.0; hv[0][1] = sl.hv[0]; hv[0][2] = sl.hv[1];
+    hv[1][0] = 0.0; hv[1][1] = sl.hv[2]; hv[1][2] = sl.hv[3];
+    hv[2][0] = 0.0; hv[2][1] = sl.hv[4]; hv[2][2] = sl.hv[5];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { hv[3][k] = sl.hv[6 + k]; hv[4][k] = sl.hv[9 + k]; hv[5][k] = sl.hv[12 + k]; }
+  }
+  double xr[3], C[9];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) xr[a] = static_cast<double>(sl.xt[a]) - __ldg(G.c_mean + 3 * row + a);
+#pragma unroll
+  for (int i = 0; i < 9; ++i) C[i] = __ldg(G.c_icov + 9 * row + i);
+  const double s = mg_pair<HESS>(jc, hv, xr, C, st.d1, st.d2, acc);
+  acc[RED_SCORE] += s;
+  if (s > 0.0) atomicMax(&sl.nearest_bits, static_cast<unsigned long long>(__double_as_longlong(s)));
+}
+
+// Every warp works on chunks of 32 consecutive points and alternates two phases through a pair queue of its own:
+//   phase A (one lane per POINT): for every target grid whose bounding box some lane touches, three batches of nine
+//            hash probes (one z layer of the 3x3x3 block; the nine loads are issued together), the centroid distance
+//            test of the radius search, and the surviving (point, grid, leaf) pairs appended to the queue by a warp scan;
+//   phase B (one lane per PAIR): the FP64 pair maths on 32 real pairs at a time -- no lane idles on a probe that missed
+//            and no lane waits for a neighbour with a longer neighbourhood.
+// The queue is drained at the end of a chunk (its slots are reused by the next one).  The point -> warp -> queue
+// position -> lane mapping is static, so every accumulator sees its terms in a fixed order (run-to-run bit stable).
 template <bool HESS>
 __global__ void __launch_bounds__(MG_THREADS) mg_eval_kernel(const float4* __restrict__ src, int n, const MgGridDev* __restrict__ grids, int n_grids,
                                                              const __grid_constant__ MgEvalState st, double* __restrict__ block_out) {
+  __shared__ MgWarpScratch s_warp[MG_WARPS];
   __shared__ double s_red[MG_WARPS][RED_N];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  MgWarpScratch& ws = s_warp[w];
   double acc[RED_N];
 #pragma unroll
   for (int i = 0; i < RED_N; ++i) acc[i] = 0.0;
-  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
-    const float4 p = __ldg(src + idx);
-    float xt[3];
+  const int n_chunks = (n + 31) / 32;
+  const int n_warps = gridDim.x * MG_WARPS;
+  int head = 0, tail = 0;
+  for (int chunk = blockIdx.x * MG_WARPS + w; chunk < n_chunks; chunk += n_warps) {
+    const int idx = chunk * 32 + lane;
+    const bool have = idx < n;
+    float xt[3] = {0.f, 0.f, 0.f};
+    if (have) {
+      const float4 p = __ldg(src + idx);
 #pragma unroll
-    for (int r = 0; r < 3; ++r) xt[r] = st.T[4 * r] * p.x + (st.T[4 * r + 1] * p.y + (st.T[4 * r + 2] * p.z + st.T[4 * r + 3]));
-    // computePointDerivatives, FP64 (multigrid_ndt_omp_impl.hpp:590-636)
-    double jc[3][3], hv[6][3];
-    {
+      for (int r = 0; r < 3; ++r) xt[r] = st.T[4 * r] * p.x + (st.T[4 * r + 1] * p.y + (st.T[4 * r + 2] * p.z + st.T[4 * r + 3]));
+      // computePointDerivatives, FP64 (multigrid_ndt_omp_impl.hpp:590-636)
       const double x0 = static_cast<double>(p.x), x1 = static_cast<double>(p.y), x2 = static_cast<double>(p.z);
-      auto dj = [&](int r) { return dot3s(st.jd[3 * r], st.jd[3 * r + 1], st.jd[3 * r + 2], x0, x1, x2); };
-      auto dh = [&](int r) { return dot3s(st.hd[3 * r], st.hd[3 * r + 1], st.hd[3 * r + 2], x0, x1, x2); };
-      jc[0][0] = 0.0; jc[0][1] = dj(0); jc[0][2] = dj(1);
-      jc[1][0] = dj(2); jc[1][1] = dj(3); jc[1][2] = dj(4);
-      jc[2][0] = dj(5); jc[2][1] = dj(6); jc[2][2] = dj(7);
-      if (HESS) {
-        hv[0][0] = 0.0; hv[0][1] = dh(0); hv[0][2] = dh(1);
-        hv[1][0] = 0.0; hv[1][1] = dh(2); hv[1][2] = dh(3);
-        hv[2][0] = 0.0; hv[2][1] = dh(4); hv[2][2] = dh(5);
+      MgSlot& sl = ws.pt[lane];
+      sl.xt[0] = xt[0]; sl.xt[1] = xt[1]; sl.xt[2] = xt[2];
 #pragma unroll
-        for (int k = 0; k < 3; ++k) { hv[3][k] = dh(6 + k); hv[4][k] = dh(9 + k); hv[5][k] = dh(12 + k); }
+      for (int r = 0; r < 8; ++r) sl.jc[r] = dot3s(st.jd[3 * r], st.jd[3 * r + 1], st.jd[3 * r + 2], x0, x1, x2);
+      if (HESS) {
+#pragma unroll
+        for (int r = 0; r < 15; ++r) sl.hv[r] = dot3s(st.hd[3 * r], st.hd[3 * r + 1], st.hd[3 * r + 2], x0, x1, x2);
       }
     }
-    double sum_score = 0.0, nearest = 0.0;
-    int nn = 0, n_list = 0;
-    int hit_row[MG_HITS];
-    unsigned char hit_grid[MG_HITS];
-    auto flush = [&]() {
-      for (int k = 0; k < n_list; ++k) {
-        const MgGridDev& G = grids[hit_grid[k]];
-        const size_t row = static_cast<size_t>(hit_row[k]);
-        double xr[3], C[9];
-#pragma unroll
-        for (int a = 0; a < 3; ++a) xr[a] = static_cast<double>(xt[a]) - __ldg(G.c_mean + 3 * row + a);
-#pragma unroll
-        for (int i = 0; i < 9; ++i) C[i] = __ldg(G.c_icov + 9 * row + i);
-        const double s = mg_pair<HESS>(jc, hv, xr, C, st.d1, st.d2, acc);
-        sum_score += s;
-        if (s > nearest) nearest = s;
-      }
-      nn += n_list;
-      n_list = 0;
-    };
+    ws.pt[lane].nearest_bits = 0ull;
+    int nn = 0;
+    __syncwarp();
     for (int gi = 0; gi < n_grids; ++gi) {
       const MgGridDev& G = grids[gi];
       const float leaf = G.meta.leaf;
       const int i0 = static_cast<int>(floorf(__fdiv_rn(xt[0], leaf)));
       const int i1 = static_cast<int>(floorf(__fdiv_rn(xt[1], leaf)));
       const int i2 = static_cast<int>(floorf(__fdiv_rn(xt[2], leaf)));
-      if (i0 + 1 < G.meta.min_b[0] || i0 - 1 > G.meta.max_b[0] || i1 + 1 < G.meta.min_b[1] || i1 - 1 > G.meta.max_b[1] ||
-          i2 + 1 < G.meta.min_b[2] || i2 - 1 > G.meta.max_b[2]) continue;
+      const bool touches = have && !(i0 + 1 < G.meta.min_b[0] || i0 - 1 > G.meta.max_b[0] || i1 + 1 < G.meta.min_b[1] || i1 - 1 > G.meta.max_b[1] ||
+                                     i2 + 1 < G.meta.min_b[2] || i2 - 1 > G.meta.max_b[2]);
+      if (!__any_sync(0xffffffffu, touches)) continue;
       const uint32_t mask = G.meta.hash_mask;
       for (int oz = -1; oz <= 1; ++oz) {
         const int c2 = i2 + oz;
-        if (c2 < G.meta.min_b[2] || c2 > G.meta.max_b[2]) continue;
-        uint32_t key[9];
-        uint2 slot[9];
-#pragma unroll
-        for (int q = 0; q < 9; ++q) {
-          const int c0 = i0 + (q % 3) - 1, c1 = i1 + (q / 3) - 1;
-          const bool in = c0 >= G.meta.min_b[0] && c0 <= G.meta.max_b[0] && c1 >= G.meta.min_b[1] && c1 <= G.meta.max_b[1];
-          key[q] = in ? static_cast<uint32_t>((c0 - G.meta.min_b[0]) * G.meta.divb_mul[0] + (c1 - G.meta.min_b[1]) * G.meta.divb_mul[1] +
-                                              (c2 - G.meta.min_b[2]) * G.meta.divb_mul[2])
-                      : HASH_EMPTY;
-        }
-#pragma unroll
-        for (int q = 0; q < 9; ++q)
-          slot[q] = (key[q] != HASH_EMPTY) ? __ldg(reinterpret_cast<const uint2*>(G.table) + (key[q] & mask)) : make_uint2(HASH_EMPTY, 0u);
+        const bool layer = touches && c2 >= G.meta.min_b[2] && c2 <= G.meta.max_b[2];
+        if (!__any_sync(0xffffffffu, layer)) continue;
         int rows[9];
+        int found = 0;
+        if (layer) {
+          uint32_t key[9];
+          uint2 slot[9];
 #pragma unroll
-        for (int q = 0; q < 9; ++q) {
-          uint2 v = slot[q];
-          uint32_t b = key[q] & mask;
-          while (v.x != key[q] && v.x != HASH_EMPTY) {  // displaced key (load <= 0.5): the usual linear probe
-            b = (b + 1) & mask;
-            v = __ldg(reinterpret_cast<const uint2*>(G.table) + b);
+          for (int q = 0; q < 9; ++q) {
+            const int c0 = i0 + (q % 3) - 1, c1 = i1 + (q / 3) - 1;
+            const bool in = c0 >= G.meta.min_b[0] && c0 <= G.meta.max_b[0] && c1 >= G.meta.min_b[1] && c1 <= G.meta.max_b[1];
+            key[q] = in ? static_cast<uint32_t>((c0 - G.meta.min_b[0]) * G.meta.divb_mul[0] + (c1 - G.meta.min_b[1]) * G.meta.divb_mul[1] +
+                                                (c2 - G.meta.min_b[2]) * G.meta.divb_mul[2])
+                        : HASH_EMPTY;
           }
-          rows[q] = (v.x == HASH_EMPTY) ? -1 : static_cast<int>(v.y);
-        }
-        float4 cen[9];
 #pragma unroll
-        for (int q = 0; q < 9; ++q) cen[q] = (rows[q] >= 0) ? __ldg(G.centroid + rows[q]) : make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int q = 0; q < 9; ++q)
+            slot[q] = (key[q] != HASH_EMPTY) ? __ldg(reinterpret_cast<const uint2*>(G.table) + (key[q] & mask)) : make_uint2(HASH_EMPTY, 0u);
 #pragma unroll
-        for (int q = 0; q < 9; ++q) {
-          if (rows[q] < 0) continue;
-          // FLANN L2_Simple<float> against the leaf centroid, strict '<' (RadiusResultSet::addPoint)
-          const float dx = xt[0] - cen[q].x, dy = xt[1] - cen[q].y, dz = xt[2] - cen[q].z;
-          float d = dx * dx; d = d + dy * dy; d = d + dz * dz;
-          if (!(d < st.r2)) continue;
-          if (n_list == MG_HITS) flush();
-          hit_row[n_list] = rows[q];
-          hit_grid[n_list] = static_cast<unsigned char>(gi);
-          ++n_list;
+          for (int q = 0; q < 9; ++q) {
+            uint2 v = slot[q];
+            uint32_t b = key[q] & mask;
+            while (v.x != key[q] && v.x != HASH_EMPTY) {  // displaced key (load <= 0.5): the usual linear probe
+              b = (b + 1) & mask;
+              v = __ldg(reinterpret_cast<const uint2*>(G.table) + b);
+            }
+            rows[q] = (v.x == HASH_EMPTY) ? -1 : static_cast<int>(v.y);
+          }
+          float4 cen[9];
+#pragma unroll
+          for (int q = 0; q < 9; ++q) cen[q] = (rows[q] >= 0) ? __ldg(G.centroid + rows[q]) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int q = 0; q < 9; ++q) {
+            if (rows[q] < 0) continue;
+            // FLANN L2_Simple<float> against the leaf centroid, strict '<' (RadiusResultSet::addPoint)
+            const float dx = xt[0] - cen[q].x, dy = xt[1] - cen[q].y, dz = xt[2] - cen[q].z;
+            float d = dx * dx; d = d + dy * dy; d = d + dz * dz;
+            if (d < st.r2) ++found; else rows[q] = -1;
+          }
+        } else {
+#pragma unroll
+          for (int q = 0; q < 9; ++q) rows[q] = -1;
         }
+        // warp scan of the hit counts -> queue positions
+        int incl = found;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int t = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += t;
+        }
+        const int total = __shfl_sync(0xffffffffu, incl, 31);
+        if (found > 0) {
+          int pos = tail + incl - found;
+#pragma unroll
+          for (int q = 0; q < 9; ++q) {
+            if (rows[q] >= 0) {
+              ws.qrow[pos & (MG_QCAP - 1)] = rows[q];
+              ws.qmeta[pos & (MG_QCAP - 1)] = static_cast<unsigned short>(lane | (gi << 5));
+              ++pos;
+            }
+          }
+        }
+        nn += found;
+        tail += total;
+        __syncwarp();
+        while (tail - head >= 32) {  // phase B on full rounds
+          mg_eval_pair<HESS>(ws, head + lane, grids, st, acc);
+          head += 32;
+        }
+        __syncwarp();
       }
     }
-    flush();
+    if (head < tail) {  // drain: the slots are reused by the next chunk
+      if (head + lane < tail) mg_eval_pair<HESS>(ws, head + lane, grids, st, acc);
+      head = tail;
+    }
+    __syncwarp();
     if (nn > 0) {
-      acc[RED_SCORE] += sum_score;
-      acc[RED_NEAREST] += nearest;
+      acc[RED_NEAREST] += __longlong_as_double(static_cast<long long>(ws.pt[lane].nearest_bits));
       acc[RED_FOUND] += 1.0;
       acc[RED_COUNT] += static_cast<double>(nn);
     }
+    __syncwarp();
   }
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
 #pragma unroll
   for (int i = 0; i < RED_N; ++i) {
     double v = acc[i];
@@ -267,13 +388,16 @@ __global__ void __launch_bounds__(MG_THREADS) mg_eval_kernel(const float4* __res
   }
 }
 
-// Block partials -> RED_N sums, block order (fixed): one thread per component, written to pinned host memory.
-__global__ void mg_reduce_kernel(const double* __restrict__ block_out, int blocks, double* __restrict__ out) {
-  const int c = threadIdx.x;
-  if (c >= RED_N) return;
+// Block partials -> RED_N sums: one warp per component, lane l adds blocks l, l+32, ... in order, then a fixed
+// shuffle tree -> deterministic.  Written to pinned host memory.
+constexpr int RED_WARPS = RED_N / 2;  // two CTAs of 23 warps
+__global__ void __launch_bounds__(32 * RED_WARPS) mg_reduce_kernel(const double* __restrict__ block_out, int blocks, double* __restrict__ out) {
+  const int c = blockIdx.x * RED_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   double v = 0.0;
-  for (int b = 0; b < blocks; ++b) v += block_out[RED_N * static_cast<size_t>(b) + c];
-  out[c] = v;
+  for (int b = lane; b < blocks; b += 32) v += block_out[RED_N * static_cast<size_t>(b) + c];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if (lane == 0) out[c] = v;
 }
 
 static void mg_angle_vectors(const double* p, double* jd, double* hd) {  // computeAngleDerivatives :498-586 (FP64 rows, snap 10e-5)
@@ -321,7 +445,7 @@ int mg_eval(ndtb_handle_s* h, const double* p, const float* T16, bool compute_he
   if (s->dirty) return set_error(h, NDTB_ERR_NOT_READY, "multigrid: targets changed since ndtb_mg_create_kdtree");
   const int n = static_cast<int>(h->n_source);
   if (n == 0) return set_error(h, NDTB_ERR_NOT_READY, "source must be set");
-  const int blocks = std::min((n + MG_THREADS - 1) / MG_THREADS, 148 * 4);
+  const int blocks = std::min((n + MG_THREADS - 1) / MG_THREADS, 148 * 2);  // 250 registers: two resident CTAs per SM, one wave
   if (static_cast<size_t>(blocks) * RED_N > s->partials_alloc) {
     cudaFree(s->d_partials);
     CKH(cudaMalloc(&s->d_partials, sizeof(double) * RED_N * 148 * 4));
@@ -337,7 +461,7 @@ int mg_eval(ndtb_handle_s* h, const double* p, const float* T16, bool compute_he
   st.r2 = static_cast<float>(radius * radius);
   if (compute_hessian) mg_eval_kernel<true><<<blocks, MG_THREADS, 0, h->stream>>>(h->d_source, n, s->d_table, s->n_tree, st, s->d_partials);
   else mg_eval_kernel<false><<<blocks, MG_THREADS, 0, h->stream>>>(h->d_source, n, s->d_table, s->n_tree, st, s->d_partials);
-  mg_reduce_kernel<<<1, 64, 0, h->stream>>>(s->d_partials, blocks, s->h_out);
+  mg_reduce_kernel<<<2, 32 * RED_WARPS, 0, h->stream>>>(s->d_partials, blocks, s->h_out);
   h->launches += 2;
   h->eval_launches += 1;
   CKH(cudaGetLastError());
@@ -378,7 +502,7 @@ int ndtb_mg_add_target(ndtb_handle h, const char* grid_id, const float* xyz, siz
     g->centroid_alloc = V;
   }
   const uint32_t n_valid_pts = static_cast<uint32_t>(n) - static_cast<uint32_t>(g->grid.h_pinned[0]);
-  mg_centroid_kernel<<<std::min<int>((V + 127) / 128, 148 * 8), 128, 0, h->stream>>>(g->grid.sorted_xyz, g->grid.seg_start, V, n_valid_pts, g->d_centroid);
+  mg_centroid_kernel<<<std::min<int>((V + CEN_THREADS - 1) / CEN_THREADS, 148 * 8), CEN_THREADS, 0, h->stream>>>(g->grid.sorted_xyz, g->grid.seg_start, V, n_valid_pts, g->d_centroid);
   g->grid.launches += 1;
   h->launches += g->grid.launches - launches_before;  // ndtb_get_launch_count: the per-tile builds are this handle's kernels too
   CKH(cudaGetLastError());
@@ -418,6 +542,7 @@ int ndtb_mg_create_kdtree(ndtb_handle h) {
     s->tree_ids.push_back(kv.first);
     s->tree_leaves += g->grid.n_valid;
   }
+  if (tab.size() > 2047) return set_error(h, NDTB_ERR_INVALID, "multigrid: at most 2047 targets in one kd-tree");
   if (static_cast<int>(tab.size()) > s->table_alloc) {
     cudaFree(s->d_table);
     const int cap = std::max<int>(16, 2 * static_cast<int>(tab.size()));
