@@ -218,6 +218,65 @@ int ndtb_mg_compute_derivatives(ndtb_handle h, const double p[6], const float* T
 int ndtb_mg_calculate_scores(ndtb_handle h, const float T16[16], double* transform_probability, double* nvtl);
 int ndtb_mg_align(ndtb_handle h, const float guess[16], ndtb_result* res, float* transformation_array, int capacity, float* out_xyz);
 
+/* ---- scan producer: the reference's LidarCallback on the device ------------------------
+ * The step BEFORE setInputSource: Ouster RNG19_RFL8_SIG16_NIR16 lidar packets -> one LidarFrame per revolution
+ * (src/lidarcallback.cpp; include/dataframe.hpp LidarFrame), so that scans are born in HBM and the raw packets
+ * (24 832 bytes per 16 columns x 128 channels) are the only thing that crosses PCIe.
+ *   ndtb_lidar_create        LidarCallback::LidarCallback + Initialize   src/lidarcallback.cpp:17-60, 191-341
+ *                            (channel stride not in {1,2,4,8,16} or > pixels_per_column -> NDTB_ERR_INVALID where the
+ *                            reference throws std::runtime_error, :41-49)
+ *   ndtb_lidar_push_packets  LidarCallback::DecodePacket / DecodePacketRng19   :344-351, 631-878, once per packet in
+ *                            order: wrong size or packet_type != 1 -> packet ignored (:633-646); a packet whose frame id
+ *                            differs from the running one CLOSES the running frame (:658-669) -- its packets, already in
+ *                            HBM, are decoded by one kernel (range / z / vehicle-box / reflectivity filters, channel
+ *                            stride, order-preserving compaction in packet, column, channel order).
+ *   ndtb_lidar_pop_frame     the unique_ptr<LidarFrame> DecodePacket returns: oldest closed frame with >= 1 point
+ *                            (a frame without points is never emitted, :659); the previously popped frame goes back
+ *                            to the pool (ReturnFrameToPool, :903-909).  *available = 0 when there is none.
+ *   ndtb_lidar_read_frame    copies the popped frame's arrays to the host (any pointer may be NULL)
+ *   ndtb_lidar_frame_points  device pointer to the popped frame's packed (x, y, z, 1) float4 points: pass it to
+ *                            ndtb_set_source_device / ndtb_set_target_device (same device); valid until the next pop.
+ * Packets handed to ndtb_lidar_push_packets from PINNED host memory are DMA-ed straight from the caller's buffer:
+ * keep it unchanged until the frame was popped (or ndtb_lidar_sync returned); pageable buffers may be reused at once. */
+typedef struct ndtb_lidar_s* ndtb_lidar;
+typedef struct ndtb_lidar_config {
+  int columns_per_frame;                /* lidar_data_format.columns_per_frame                       */
+  int pixels_per_column;                /* lidar_data_format.pixels_per_column (<= 128 x stride)      */
+  int columns_per_packet;               /* config_params.columns_per_packet (<= 32)                   */
+  int channel_stride;                   /* lidar_parameter.channelStride                              */
+  int reflectivity_threshold;           /* lidar_parameter.reflectionThreshold (stored as uint8_t)    */
+  float lidar_origin_to_beam_origin_mm; /* beam_intrinsics.lidar_origin_to_beam_origin_mm             */
+  float range_min, range_max;           /* lidar_parameter.rangeFilter                                */
+  float z_min, z_max;                   /* lidar_parameter.zAxisFilter                                */
+  float box_center[3];                  /* lidar_parameter.vehicleFilterBox.center                    */
+  float box_dimensions[3];              /* lidar_parameter.vehicleFilterBox.dimensions                */
+  double body_to_lidar_rotation[9];     /* lidar_parameter.Cb2s, row-major                            */
+  double body_to_lidar_translation[3];  /* lidar_parameter.tb2s                                       */
+} ndtb_lidar_config;
+typedef struct ndtb_lidar_frame_info {  /* scalar members of LidarFrame, include/dataframe.hpp */
+  double timestamp;                     /* column time stamp of the first point                       */
+  double timestamp_end;                 /* latest column time stamp seen when the frame closed        */
+  double interframe_timedelta;
+  uint32_t numberpoints;
+  uint16_t frame_id;
+  uint16_t packets;                     /* packets decoded into this frame (not in the reference)      */
+} ndtb_lidar_frame_info;
+int ndtb_lidar_default_config(ndtb_lidar_config* cfg); /* member initialisers of include/lidarcallback.hpp:26-90 */
+int ndtb_lidar_create(int cuda_device, const ndtb_lidar_config* cfg, const float* beam_azimuth_deg, const float* beam_altitude_deg, ndtb_lidar* out);
+int ndtb_lidar_destroy(ndtb_lidar l);
+const char* ndtb_lidar_last_error(ndtb_lidar l);
+int ndtb_lidar_packet_bytes(ndtb_lidar l, size_t* expected_size); /* expected_size_, :207 */
+/* x_1_/y_1_/z_1_ [columns_per_frame x pixels_per_column] and x_2_/y_2_/z_2_ [columns_per_frame] (:283-323) */
+int ndtb_lidar_get_tables(ndtb_lidar l, float* x1, float* y1, float* z1, float* x2, float* y2, float* z2);
+int ndtb_lidar_push_packets(ndtb_lidar l, const uint8_t* packets, size_t n_packets, size_t packet_bytes, size_t pitch_bytes, int* frames_closed);
+int ndtb_lidar_pop_frame(ndtb_lidar l, ndtb_lidar_frame_info* info, int* available);
+int ndtb_lidar_read_frame(ndtb_lidar l, size_t capacity, float* x, float* y, float* z, uint16_t* c_id, uint16_t* m_id, double* timestamp_points,
+                          float* relative_timestamp, uint16_t* reflectivity, uint16_t* signal, uint16_t* nir);
+int ndtb_lidar_frame_points(ndtb_lidar l, const void** d_xyzw, size_t* n_points);
+int ndtb_lidar_sync(ndtb_lidar l);
+/* kernels launched / CUDA-event time (us) of the last decode kernel */
+int ndtb_lidar_get_stats(ndtb_lidar l, uint64_t* launches, float* last_decode_us);
+
 /* ---- batch replay: n independent alignments against the current target ----------------------- */
 int ndtb_align_batch(ndtb_handle h, int n_scans, const float* const* xyz, const size_t* n_points, size_t stride_bytes,
                      const float* guesses16, ndtb_result* results);

@@ -53,10 +53,27 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "nd
            "ndtb_svn_step", "ndtb_svn_align", "ndtb_svn_stage1_local", "ndtb_svn_finish_step", "ndtb_align_batch", "ndtb_get_timings",
            "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_set_profiling", "ndtb_set_option", "ndtb_time_eval_kernel", "ndtb_newton_direction", "ndtb_hessian_to_covariance", "ndtb_keyframe_put", "ndtb_keyframe_drop", "ndtb_keyframe_count",
            "ndtb_set_target_window", "ndtb_get_target_points", "ndtb_voxelgrid_filter", "ndtb_svn_mean_pose", "ndtb_svn_pose_distance",
+           "ndtb_lidar_default_config", "ndtb_lidar_create", "ndtb_lidar_destroy", "ndtb_lidar_last_error", "ndtb_lidar_packet_bytes",
+           "ndtb_lidar_get_tables", "ndtb_lidar_push_packets", "ndtb_lidar_pop_frame", "ndtb_lidar_read_frame", "ndtb_lidar_frame_points",
+           "ndtb_lidar_sync", "ndtb_lidar_get_stats",
            "ndtb_mg_add_target", "ndtb_mg_remove_target", "ndtb_mg_create_kdtree", "ndtb_mg_set_input_target", "ndtb_mg_get_info",
            "ndtb_mg_get_grid_ids", "ndtb_mg_get_leaves", "ndtb_mg_compute_derivatives", "ndtb_mg_align", "ndtb_mg_calculate_scores"]
 
 _LIB = None
+
+
+class LidarConfig(C.Structure):
+    """ndtb_lidar_config (include/ndtb.h)."""
+    _fields_ = [("columns_per_frame", C.c_int), ("pixels_per_column", C.c_int), ("columns_per_packet", C.c_int), ("channel_stride", C.c_int),
+                ("reflectivity_threshold", C.c_int), ("lidar_origin_to_beam_origin_mm", C.c_float), ("range_min", C.c_float),
+                ("range_max", C.c_float), ("z_min", C.c_float), ("z_max", C.c_float), ("box_center", C.c_float * 3),
+                ("box_dimensions", C.c_float * 3), ("body_to_lidar_rotation", C.c_double * 9), ("body_to_lidar_translation", C.c_double * 3)]
+
+
+class LidarFrameInfo(C.Structure):
+    """ndtb_lidar_frame_info (include/ndtb.h)."""
+    _fields_ = [("timestamp", C.c_double), ("timestamp_end", C.c_double), ("interframe_timedelta", C.c_double), ("numberpoints", C.c_uint32),
+                ("frame_id", C.c_uint16), ("packets", C.c_uint16)]
 
 
 class NdtbError(RuntimeError):
@@ -128,6 +145,20 @@ def lib():
         L.ndtb_mg_compute_derivatives.argtypes = [H, c_d, c_f, C.c_int, c_d, c_d, c_d, c_d]
         L.ndtb_mg_align.argtypes = [H, c_f, C.POINTER(Result), c_f, C.c_int, c_f]
         L.ndtb_mg_calculate_scores.argtypes = [H, c_f, c_d, c_d]
+        c_u16 = C.POINTER(C.c_uint16)
+        L.ndtb_lidar_default_config.argtypes = [C.POINTER(LidarConfig)]
+        L.ndtb_lidar_create.argtypes = [C.c_int, C.POINTER(LidarConfig), c_f, c_f, C.POINTER(H)]
+        L.ndtb_lidar_destroy.argtypes = [H]
+        L.ndtb_lidar_last_error.restype = C.c_char_p
+        L.ndtb_lidar_last_error.argtypes = [H]
+        L.ndtb_lidar_packet_bytes.argtypes = [H, C.POINTER(C.c_size_t)]
+        L.ndtb_lidar_get_tables.argtypes = [H, c_f, c_f, c_f, c_f, c_f, c_f]
+        L.ndtb_lidar_push_packets.argtypes = [H, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, c_i]
+        L.ndtb_lidar_pop_frame.argtypes = [H, C.POINTER(LidarFrameInfo), c_i]
+        L.ndtb_lidar_read_frame.argtypes = [H, C.c_size_t, c_f, c_f, c_f, c_u16, c_u16, c_d, c_f, c_u16, c_u16, c_u16]
+        L.ndtb_lidar_frame_points.argtypes = [H, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
+        L.ndtb_lidar_sync.argtypes = [H]
+        L.ndtb_lidar_get_stats.argtypes = [H, C.POINTER(C.c_uint64), c_f]
         _LIB = L
     return _LIB
 

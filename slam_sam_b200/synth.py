@@ -280,3 +280,27 @@ def trajectory_pose(s, lateral=0.0):
     """Body pose (4x4) at arc-length s metres along the street (x axis), gentle yaw wobble."""
     yaw = 0.03 * math.sin(0.05 * s)
     return pose_matrix((-75.0 + s, lateral + 0.5 * math.sin(0.04 * s), 0.0), (0.0, 0.0, yaw))
+
+
+def ouster_range_image(scene, pose, beams=128, cols=1024, seed=0, noise=0.02, max_range=120.0, sensor_height=1.8):
+    """The same revolution as ouster_scan, but as the sensor reports it: a (cols, beams) image of ranges in millimetres
+    (0 = no return) in Ouster's conventions -- measurement azimuth 2*pi*(1 - m/cols), beam 0 on top -- plus the sensor
+    description (beam angles, body->lidar transform) with which the reference's LidarCallback lookup tables
+    (src/lidarcallback.cpp:283-323) turn the image back into body-frame points.
+    Returns (range_mm uint32 (cols, beams), beam_azimuth_deg, beam_altitude_deg, Cb2s (9,), tb2s (3,))."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    alt_deg = np.linspace(22.5, -22.5, beams).astype(np.float32)
+    az_deg = np.zeros(beams, np.float32)
+    m = np.arange(cols)
+    theta = 2.0 * np.pi * (1.0 - m / cols)
+    Z, A = np.meshgrid(theta, np.deg2rad(alt_deg.astype(np.float64)), indexing="ij")  # (cols, beams)
+    d_s = np.stack([np.cos(A) * np.cos(Z), np.cos(A) * np.sin(Z), np.sin(A)], -1).reshape(-1, 3)
+    T_sensor = np.array(pose, np.float64)
+    T_sensor[2, 3] += sensor_height
+    r = scene.cast(T_sensor[:3, 3], d_s @ T_sensor[:3, :3].T, max_range)
+    hit = np.isfinite(r)
+    r = np.where(hit, r + rng.normal(0.0, noise, r.shape), 0.0)
+    range_mm = np.clip(np.rint(r * 1000.0), 0, (1 << 19) - 1).astype(np.uint32).reshape(cols, beams)
+    Cb2s = np.eye(3).reshape(9)
+    tb2s = np.array([0.0, 0.0, -sensor_height])  # lidar = body - (0, 0, h)
+    return range_mm, az_deg, alt_deg, Cb2s, tb2s

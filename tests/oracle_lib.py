@@ -97,6 +97,18 @@ def lib():
                      "orc_pose_logmap", "orc_rot_rpy"):
             getattr(L, name).restype = None
         L.orc_ldlt6_solve.restype = C.c_int
+        c_u16 = C.POINTER(C.c_uint16)
+        L.orc_lidar_create.restype = C.c_void_p
+        L.orc_lidar_create.argtypes = [c_i, c_f, c_d, c_f, c_f]
+        L.orc_lidar_destroy.argtypes = [C.c_void_p]
+        L.orc_lidar_packet_bytes.restype = C.c_size_t
+        L.orc_lidar_packet_bytes.argtypes = [C.c_void_p]
+        L.orc_lidar_tables.argtypes = [C.c_void_p, c_f, c_f, c_f, c_f, c_f, c_f]
+        L.orc_lidar_decode.restype = C.c_long
+        L.orc_lidar_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t]
+        L.orc_lidar_frame_info.argtypes = [C.c_void_p, C.c_long, c_d]
+        L.orc_lidar_frame_get.argtypes = [C.c_void_p, C.c_long, c_f, c_f, c_f, c_u16, c_u16, c_d, c_f, c_u16, c_u16, c_u16]
+        L.orc_lidar_clear_frames.argtypes = [C.c_void_p]
         _LIB = L
     return _LIB
 
@@ -378,3 +390,52 @@ class OracleSvn:
             lib().orc_svn_destroy(self.h)
         except Exception:
             pass
+
+
+class OracleLidar:
+    """oracle/ouster_decode.hpp: LidarCallback::Initialize + DecodePacketRng19 restated (src/lidarcallback.cpp:191-341, 631-878).
+    cfg: any object with the fields of ndtb_lidar_config (the ctypes struct of the product binding is accepted)."""
+
+    def __init__(self, cfg, az_deg, alt_deg):
+        self.L = lib()
+        self.cfg = cfg
+        ci = np.array([cfg.columns_per_frame, cfg.pixels_per_column, cfg.columns_per_packet, cfg.channel_stride, cfg.reflectivity_threshold], np.int32)
+        cf = np.array([cfg.lidar_origin_to_beam_origin_mm, cfg.range_min, cfg.range_max, cfg.z_min, cfg.z_max, *cfg.box_center, *cfg.box_dimensions], np.float32)
+        cd = np.array([*cfg.body_to_lidar_rotation, *cfg.body_to_lidar_translation], np.float64)
+        az = np.ascontiguousarray(az_deg, np.float32); alt = np.ascontiguousarray(alt_deg, np.float32)
+        self.h = self.L.orc_lidar_create(_i(ci), _f(cf), _d(cd), _f(az), _f(alt))
+        if not self.h:
+            raise ValueError("the reference's LidarCallback constructor would throw for this configuration")
+        self.expected_size = self.L.orc_lidar_packet_bytes(self.h)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orc_lidar_destroy(self.h)
+            self.h = None
+
+    def tables(self):
+        W, Hh = self.cfg.columns_per_frame, self.cfg.pixels_per_column
+        t = [np.empty(W * Hh, np.float32) for _ in range(3)] + [np.empty(W, np.float32) for _ in range(3)]
+        self.L.orc_lidar_tables(self.h, *[_f(a) for a in t])
+        return t
+
+    def decode(self, packets):
+        """DecodePacket for every row of `packets` (uint8, (n, size)); returns the frames completed by these packets."""
+        a = np.ascontiguousarray(packets, np.uint8)
+        self.L.orc_lidar_clear_frames(self.h)
+        n = self.L.orc_lidar_decode(self.h, a.ctypes.data, a.shape[0], a.shape[1], a.shape[1])
+        frames = []
+        u16 = C.POINTER(C.c_uint16)
+        for k in range(n):
+            info = np.zeros(5)
+            self.L.orc_lidar_frame_info(self.h, k, _d(info))
+            m = int(info[4])
+            f = {"x": np.empty(m, np.float32), "y": np.empty(m, np.float32), "z": np.empty(m, np.float32), "c_id": np.empty(m, np.uint16),
+                 "m_id": np.empty(m, np.uint16), "timestamp_points": np.empty(m, np.float64), "relative_timestamp": np.empty(m, np.float32),
+                 "reflectivity": np.empty(m, np.uint16), "signal": np.empty(m, np.uint16), "nir": np.empty(m, np.uint16)}
+            self.L.orc_lidar_frame_get(self.h, k, _f(f["x"]), _f(f["y"]), _f(f["z"]), f["c_id"].ctypes.data_as(u16), f["m_id"].ctypes.data_as(u16),
+                                       _d(f["timestamp_points"]), _f(f["relative_timestamp"]), f["reflectivity"].ctypes.data_as(u16),
+                                       f["signal"].ctypes.data_as(u16), f["nir"].ctypes.data_as(u16))
+            f.update(frame_id=int(info[0]), timestamp=info[1], timestamp_end=info[2], interframe_timedelta=info[3], numberpoints=m)
+            frames.append(f)
+        return frames
