@@ -3,7 +3,7 @@
 //   LidarCallback::DecodePacketRng19  src/lidarcallback.cpp:631-878   packets -> LidarFrame (include/dataframe.hpp)
 // The reference decodes packet by packet on one core and push_back()s every surviving return.  Here the packets of
 // the running frame are DMA-ed into HBM as they arrive and, when a packet with a new frame id closes the frame, ONE
-// kernel decodes the whole revolution: one CTA per packet, one warp per column, one lane per (strided) channel.
+// kernel decodes the whole revolution: one CTA per packet (or per four columns of it), one warp per column, one lane per (strided) channel.
 // The reference's output order (packet, column, channel) is kept by an order-preserving compaction: warp ballots
 // inside a column, a 32-entry scan over the columns of a packet, and a decoupled look-back over the packets (every
 // CTA publishes {count, time stamp of its first point} under a per-launch epoch; CTAs take their packet through a
@@ -14,6 +14,7 @@
 // per pixel, 42 B written per surviving point.
 #include "../../include/ndtb.h"
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <limits>
@@ -27,6 +28,7 @@ constexpr int LIDAR_MAX_SLOTS = 64;
 
 struct LidarKParams {
   int cpf, ppc, cpp, stride, subset, rounds;
+  int cpc, upp;  // columns per CTA ("unit"), units per packet
   int block_bytes, pitch;
   float r_min, r_max, z_min, z_max;
   int refl_thr;
@@ -40,7 +42,7 @@ struct FrameArrays {
 
 __device__ __forceinline__ unsigned ld_volatile_u32(const unsigned* p) { return *reinterpret_cast<const volatile unsigned*>(p); }
 
-__global__ void __launch_bounds__(1024) lidar_decode_kernel(const __grid_constant__ LidarKParams P, const unsigned char* __restrict__ packets, int n_packets,
+__global__ void __launch_bounds__(1024) lidar_decode_kernel(const __grid_constant__ LidarKParams P, const unsigned char* __restrict__ packets, int n_units,
                                                             const float* __restrict__ x1, const float* __restrict__ y1, const float* __restrict__ z1,
                                                             const float* __restrict__ x2, const float* __restrict__ y2, const float* __restrict__ z2,
                                                             Ctl* ctl, PacketRec* recs, unsigned epoch, double* chain, const __grid_constant__ FrameArrays out,
@@ -49,11 +51,13 @@ __global__ void __launch_bounds__(1024) lidar_decode_kernel(const __grid_constan
   __shared__ double s_ts[32];
   __shared__ unsigned s_ticket, s_base;
   __shared__ double s_frame_ts;
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;  // w = column of the packet
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;  // w = column inside the unit
   if (threadIdx.x == 0) s_ticket = atomicAdd(&ctl->ticket, 1u);
   __syncthreads();
-  const unsigned t = s_ticket;  // packet index inside the frame
-  const unsigned* blk = reinterpret_cast<const unsigned*>(packets + static_cast<size_t>(t) * P.pitch + 32 + static_cast<size_t>(w) * P.block_bytes);
+  const unsigned t = s_ticket;  // unit index inside the frame: packet t / upp, columns (t % upp) * cpc ...
+  const unsigned pk = t / static_cast<unsigned>(P.upp);
+  const int col = static_cast<int>(t - pk * P.upp) * P.cpc + w;
+  const unsigned* blk = reinterpret_cast<const unsigned*>(packets + static_cast<size_t>(pk) * P.pitch + 32 + static_cast<size_t>(col) * P.block_bytes);
   // column header (:676-700): 64-bit time stamp, measurement id, status
   const unsigned ts_lo = __ldg(blk), ts_hi = __ldg(blk + 1), hdr2 = __ldg(blk + 2);
   const unsigned long long ts_ns = (static_cast<unsigned long long>(ts_hi) << 32) | ts_lo;
@@ -63,20 +67,26 @@ __global__ void __launch_bounds__(1024) lidar_decode_kernel(const __grid_constan
   const float ox = col_ok ? __ldg(x2 + m_id) : 0.f, oy = col_ok ? __ldg(y2 + m_id) : 0.f, oz = col_ok ? __ldg(z2 + m_id) : 0.f;
 
   float px[LIDAR_MAX_ROUNDS], py[LIDAR_MAX_ROUNDS], pz[LIDAR_MAX_ROUNDS];
-  unsigned w1[LIDAR_MAX_ROUNDS], w2[LIDAR_MAX_ROUNDS], ballot[LIDAR_MAX_ROUNDS];
+  unsigned w0[LIDAR_MAX_ROUNDS], w1[LIDAR_MAX_ROUNDS], w2[LIDAR_MAX_ROUNDS], ballot[LIDAR_MAX_ROUNDS];
+  // the pixel words do not depend on the column header: all loads of the column are in flight together
+#pragma unroll
+  for (int r = 0; r < LIDAR_MAX_ROUNDS; ++r) {
+    const int s = r * 32 + lane;
+    w0[r] = w1[r] = w2[r] = 0u;
+    if (r < P.rounds && s < P.subset) {
+      const unsigned* px_w = blk + 3 + 3 * (s * P.stride);
+      w0[r] = __ldg(px_w); w1[r] = __ldg(px_w + 1); w2[r] = __ldg(px_w + 2);
+    }
+  }
   unsigned cnt = 0;
 #pragma unroll
   for (int r = 0; r < LIDAR_MAX_ROUNDS; ++r) {
     bool keep = false;
-    px[r] = py[r] = pz[r] = 0.f; w1[r] = w2[r] = 0u;
+    px[r] = py[r] = pz[r] = 0.f;
     const int s = r * 32 + lane;
     if (r < P.rounds && col_ok && s < P.subset) {
       const int c_id = s * P.stride;
-      const unsigned* px_w = blk + 3 + 3 * c_id;
-      const unsigned w0 = __ldg(px_w);
-      w1[r] = __ldg(px_w + 1);
-      w2[r] = __ldg(px_w + 2);
-      const unsigned range_mm = w0 & 0x0007FFFFu;                  // :807-810 (19 bits of the first three bytes)
+      const unsigned range_mm = w0[r] & 0x0007FFFFu;              // :807-810 (19 bits of the first three bytes)
       const float range_m = static_cast<float>(range_mm) * 0.001f;
       if (!(range_m < P.r_min || range_m > P.r_max || range_m == 0.f)) {  // :813
         const size_t k = static_cast<size_t>(m_id) * P.ppc + c_id;
@@ -96,7 +106,7 @@ __global__ void __launch_bounds__(1024) lidar_decode_kernel(const __grid_constan
 
   if (w == 0) {
     // columns of this packet: exclusive scan of the counts, time stamp of the first point
-    const unsigned c = lane < P.cpp ? s_cnt[lane] : 0u;
+    const unsigned c = lane < P.cpc ? s_cnt[lane] : 0u;
     unsigned incl = c;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -133,15 +143,15 @@ __global__ void __launch_bounds__(1024) lidar_decode_kernel(const __grid_constan
       else if (total > 0u) { frame_ts = own_first_ts; first_idx = t; have_first = true; }
       s_base = base;
       s_frame_ts = frame_ts;
-      if (t == static_cast<unsigned>(n_packets) - 1u) {  // the frame's scalars (:659-663, 856-862) and the hand-over to the next frame
+      if (t == static_cast<unsigned>(n_units) - 1u) {  // the frame's scalars (:659-663, 856-862) and the hand-over to the next frame
         const unsigned n = base + total;
-        const double latest = s_ts[P.cpp - 1];  // latest_timestamp_s: every column updates it, valid or not (:685)
+        const double latest = s_ts[P.cpc - 1];  // latest_timestamp_s: every column updates it, valid or not (:685)
         const double prev = *chain;
         info->numberpoints = n;
         info->timestamp = have_first ? frame_ts : -1.7976931348623157e308;
         info->timestamp_end = latest;
         // interframe_timedelta only sees the previous frame's end when the first point comes from the packet that closed it
-        info->interframe_timedelta = have_first ? ((first_idx == 0u && prev > 0.0) ? fmax(0.0, frame_ts - prev) : 0.0) : -1.7976931348623157e308;
+        info->interframe_timedelta = have_first ? ((first_idx < static_cast<unsigned>(P.upp) && prev > 0.0) ? fmax(0.0, frame_ts - prev) : 0.0) : -1.7976931348623157e308;
         *chain = n > 0u ? latest : 0.0;
       }
     }
@@ -172,7 +182,7 @@ __global__ void __launch_bounds__(1024) lidar_decode_kernel(const __grid_constan
   __syncthreads();
   if (threadIdx.x == 0) {
     const unsigned d = atomicAdd(&ctl->done, 1u);
-    if (d == static_cast<unsigned>(n_packets) - 1u) { ctl->ticket = 0u; ctl->done = 0u; }  // ready for the next frame's launch
+    if (d == static_cast<unsigned>(n_units) - 1u) { ctl->ticket = 0u; ctl->done = 0u; }  // ready for the next frame's launch
   }
 }
 
@@ -277,7 +287,7 @@ int close_active(ndtb_lidar_s* l) {
   ++l->epoch;
   if (l->epoch == 0) ++l->epoch;
   CKL(cudaEventRecord(s->k0, l->stream));
-  lidar_decode_kernel<<<s->n_packets, 32 * l->kp.cpp, 0, l->stream>>>(l->kp, s->d_packets, s->n_packets, l->d_x1, l->d_y1, l->d_z1, l->d_x2, l->d_y2, l->d_z2,
+  lidar_decode_kernel<<<s->n_packets * l->kp.upp, 32 * l->kp.cpc, 0, l->stream>>>(l->kp, s->d_packets, s->n_packets * l->kp.upp, l->d_x1, l->d_y1, l->d_z1, l->d_x2, l->d_y2, l->d_z2,
                                                                      l->d_ctl, l->d_recs, l->epoch, l->d_chain, s->arr, s->h_info);
   CKL(cudaGetLastError());
   CKL(cudaEventRecord(s->k1, l->stream));
@@ -368,6 +378,9 @@ int ndtb_lidar_create(int cuda_device, const ndtb_lidar_config* cfg, const float
   LidarKParams& k = l->kp;
   k.cpf = cfg->columns_per_frame; k.ppc = cfg->pixels_per_column; k.cpp = cfg->columns_per_packet; k.stride = N; k.subset = subset;
   k.rounds = (subset + 31) / 32;
+  // columns per CTA: one CTA per packet measured faster (21.7 us) than four columns per CTA (26.0 us, 256 CTAs: longer look-back)
+  k.cpc = (std::getenv("NDTB_LIDAR_CPC") && k.cpp % 4 == 0) ? 4 : k.cpp;
+  k.upp = k.cpp / k.cpc;
   k.block_bytes = 12 + cfg->pixels_per_column * 12;
   l->expected_size = 32 + static_cast<size_t>(k.cpp) * k.block_bytes + 32;
   k.pitch = static_cast<int>((l->expected_size + 15) / 16 * 16);
@@ -384,7 +397,7 @@ int ndtb_lidar_create(int cuda_device, const ndtb_lidar_config* cfg, const float
   if (cudaStreamCreateWithFlags(&l->stream, cudaStreamNonBlocking) != cudaSuccess) return fail(NDTB_ERR_CUDA);
   const size_t nt = l->x1.size() * 4, nc = l->x2.size() * 4;
   if (cudaMalloc(&l->d_x1, nt) || cudaMalloc(&l->d_y1, nt) || cudaMalloc(&l->d_z1, nt) || cudaMalloc(&l->d_x2, nc) || cudaMalloc(&l->d_y2, nc) ||
-      cudaMalloc(&l->d_z2, nc) || cudaMalloc(&l->d_ctl, sizeof(Ctl)) || cudaMalloc(&l->d_recs, sizeof(PacketRec) * l->cap_packets) ||
+      cudaMalloc(&l->d_z2, nc) || cudaMalloc(&l->d_ctl, sizeof(Ctl)) || cudaMalloc(&l->d_recs, sizeof(PacketRec) * l->cap_packets * l->kp.upp) ||
       cudaMalloc(&l->d_chain, sizeof(double)))
     return fail(NDTB_ERR_CUDA);
   cudaMemcpyAsync(l->d_x1, l->x1.data(), nt, cudaMemcpyHostToDevice, l->stream);
@@ -394,7 +407,7 @@ int ndtb_lidar_create(int cuda_device, const ndtb_lidar_config* cfg, const float
   cudaMemcpyAsync(l->d_y2, l->y2.data(), nc, cudaMemcpyHostToDevice, l->stream);
   cudaMemcpyAsync(l->d_z2, l->z2.data(), nc, cudaMemcpyHostToDevice, l->stream);
   cudaMemsetAsync(l->d_ctl, 0, sizeof(Ctl), l->stream);
-  cudaMemsetAsync(l->d_recs, 0, sizeof(PacketRec) * l->cap_packets, l->stream);
+  cudaMemsetAsync(l->d_recs, 0, sizeof(PacketRec) * l->cap_packets * l->kp.upp, l->stream);
   cudaMemsetAsync(l->d_chain, 0, sizeof(double), l->stream);
   if (cudaStreamSynchronize(l->stream) != cudaSuccess) return fail(NDTB_ERR_CUDA);
   if (take_slot(l, &l->active) != NDTB_OK) return fail(NDTB_ERR_CUDA);

@@ -133,6 +133,9 @@ __global__ void __launch_bounds__(CEN_THREADS) mg_centroid_kernel(const double* 
 }
 
 constexpr int MG_THREADS = 128;
+#ifndef MG_CTAS_PER_SM
+#define MG_CTAS_PER_SM 2
+#endif
 constexpr int MG_WARPS = MG_THREADS / 32;
 
 __device__ __forceinline__ double dot3s(double a0, double a1, double a2, double b0, double b1, double b2) {
@@ -242,7 +245,7 @@ __device__ __forceinline__ void mg_eval_pair(MgWarpScratch& ws, int e, const MgG
 // The queue is drained at the end of a chunk (its slots are reused by the next one).  The point -> warp -> queue
 // position -> lane mapping is static, so every accumulator sees its terms in a fixed order (run-to-run bit stable).
 template <bool HESS>
-__global__ void __launch_bounds__(MG_THREADS) mg_eval_kernel(const float4* __restrict__ src, int n, const MgGridDev* __restrict__ grids, int n_grids,
+__global__ void __launch_bounds__(MG_THREADS, MG_CTAS_PER_SM) mg_eval_kernel(const float4* __restrict__ src, int n, const MgGridDev* __restrict__ grids, int n_grids,
                                                              const __grid_constant__ MgEvalState st, double* __restrict__ block_out) {
   __shared__ MgWarpScratch s_warp[MG_WARPS];
   __shared__ double s_red[MG_WARPS][RED_N];
@@ -445,11 +448,11 @@ int mg_eval(ndtb_handle_s* h, const double* p, const float* T16, bool compute_he
   if (s->dirty) return set_error(h, NDTB_ERR_NOT_READY, "multigrid: targets changed since ndtb_mg_create_kdtree");
   const int n = static_cast<int>(h->n_source);
   if (n == 0) return set_error(h, NDTB_ERR_NOT_READY, "source must be set");
-  const int blocks = std::min((n + MG_THREADS - 1) / MG_THREADS, 148 * 2);  // 250 registers: two resident CTAs per SM, one wave
+  const int blocks = std::min((n + MG_THREADS - 1) / MG_THREADS, 148 * MG_CTAS_PER_SM);  // one wave of resident CTAs
   if (static_cast<size_t>(blocks) * RED_N > s->partials_alloc) {
     cudaFree(s->d_partials);
-    CKH(cudaMalloc(&s->d_partials, sizeof(double) * RED_N * 148 * 4));
-    s->partials_alloc = static_cast<size_t>(RED_N) * 148 * 4;
+    CKH(cudaMalloc(&s->d_partials, sizeof(double) * RED_N * 148 * 8));
+    s->partials_alloc = static_cast<size_t>(RED_N) * 148 * 8;
   }
   if (!s->h_out) CKH(cudaHostAlloc(&s->h_out, sizeof(double) * RED_N, cudaHostAllocDefault));
   MgEvalState st;

@@ -171,21 +171,31 @@ __global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(const uint32_
   }
   __syncthreads();
   const int base = blockIdx.x * RS_TILE + w * (32 * RS_ITEMS);
-  uint32_t key[RS_ITEMS], val[RS_ITEMS], rank[RS_ITEMS];
+  uint32_t key[RS_ITEMS], val[RS_ITEMS], rank[RS_ITEMS], peers[RS_ITEMS];
   const uint32_t lt = (1u << lane) - 1u;
+  // all loads and all eight peer masks first (independent: they pipeline), then the serial shared-memory counter chain
 #pragma unroll
   for (int i = 0; i < RS_ITEMS; ++i) {
     const int idx = base + i * 32 + lane;
     const bool valid = idx < n;
     key[i] = valid ? __ldg(keys_in + idx) : 0u;
     val[i] = valid ? (FIRST ? static_cast<uint32_t>(idx) : __ldg(vals_in + idx)) : 0u;
+  }
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; ++i) {
+    const bool valid = base + i * 32 + lane < n;
     const uint32_t d = valid ? ((key[i] >> shift) & 255u) : 256u;
-    const uint32_t peers = __match_any_sync(0xffffffffu, d);
+    peers[i] = __match_any_sync(0xffffffffu, d);
+  }
+#pragma unroll
+  for (int i = 0; i < RS_ITEMS; ++i) {
+    const bool valid = base + i * 32 + lane < n;
+    const uint32_t d = (key[i] >> shift) & 255u;
     uint32_t prefix = 0;
     if (valid) prefix = cnt[w][d];
     __syncwarp();
-    rank[i] = prefix + __popc(peers & lt);
-    if (valid && (peers & lt) == 0) cnt[w][d] = prefix + __popc(peers);
+    rank[i] = prefix + __popc(peers[i] & lt);
+    if (valid && (peers[i] & lt) == 0) cnt[w][d] = prefix + __popc(peers[i]);
     __syncwarp();
   }
   __syncthreads();
