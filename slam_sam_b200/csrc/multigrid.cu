@@ -17,6 +17,7 @@
 #include "newton_math.cuh"
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -448,7 +449,8 @@ int mg_eval(ndtb_handle_s* h, const double* p, const float* T16, bool compute_he
   if (s->dirty) return set_error(h, NDTB_ERR_NOT_READY, "multigrid: targets changed since ndtb_mg_create_kdtree");
   const int n = static_cast<int>(h->n_source);
   if (n == 0) return set_error(h, NDTB_ERR_NOT_READY, "source must be set");
-  const int blocks = std::min((n + MG_THREADS - 1) / MG_THREADS, 148 * MG_CTAS_PER_SM);  // one wave of resident CTAs
+  static const int blocks_cap = std::getenv("NDTB_MG_BLOCKS") ? std::atoi(std::getenv("NDTB_MG_BLOCKS")) : 148 * MG_CTAS_PER_SM;
+  const int blocks = std::max(1, std::min((n + MG_THREADS - 1) / MG_THREADS, std::min(blocks_cap, 148 * 8)));
   if (static_cast<size_t>(blocks) * RED_N > s->partials_alloc) {
     cudaFree(s->d_partials);
     CKH(cudaMalloc(&s->d_partials, sizeof(double) * RED_N * 148 * 8));
