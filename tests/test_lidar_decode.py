@@ -245,3 +245,80 @@ def test_gpu_decoder_full_size_and_hand_over_to_ndt(oracle):
         res.append(ndt.computeDerivatives(p))
     assert res[0][0] == res[1][0] and np.array_equal(res[0][1], res[1][1]) and np.array_equal(res[0][2], res[1][2])
     assert cb.pop() is None  # nothing else was closed; the popped frame went back to the pool
+
+
+def edge_streams(cfg):
+    """Packet streams around the corners of the frame state machine (src/lidarcallback.cpp:649-671, 856-862)."""
+    out = {}
+    out["frame_id_wraps_65535_to_0"] = make_stream(cfg, 3, seed=21, first_frame_id=65534)
+    out["first_frame_id_is_0"] = make_stream(cfg, 2, seed=22, first_frame_id=0)
+    a = make_stream(cfg, 2, seed=23, first_frame_id=40)
+    n = cfg.columns_per_frame // cfg.columns_per_packet
+    inter = np.concatenate([a[:n // 2], a[n:n + n // 2], a[n // 2:n], a[n + n // 2:]])  # A B A B: every change of id closes a frame
+    out["interleaved_frame_ids"] = inter
+    late = make_stream(cfg, 3, seed=24, first_frame_id=50, bad_columns=False)
+    blk = 12 + 12 * cfg.pixels_per_column
+    for c in range(cfg.columns_per_packet):  # frame 1's first packet has no returns: its first point comes from a later packet -> timedelta 0
+        o = 32 + c * blk + 12
+        late[n, o:o + 12 * cfg.pixels_per_column].reshape(-1, 12)[:, :3] = 0
+    out["first_point_in_a_later_packet"] = late
+    return out
+
+
+def test_oracle_edge_streams(oracle):
+    cfg, az, alt = make_config()
+    s = edge_streams(cfg)
+    f = oracle.OracleLidar(cfg, az, alt).decode(s["frame_id_wraps_65535_to_0"])
+    assert [x["frame_id"] for x in f] == [65534, 65535, 0]
+    f = oracle.OracleLidar(cfg, az, alt).decode(s["first_frame_id_is_0"])
+    assert [x["frame_id"] for x in f] == [0, 1]
+    f = oracle.OracleLidar(cfg, az, alt).decode(s["interleaved_frame_ids"])
+    assert [x["frame_id"] for x in f] == [40, 41, 40, 41]
+    f = oracle.OracleLidar(cfg, az, alt).decode(s["first_point_in_a_later_packet"])
+    assert f[1]["interframe_timedelta"] == 0.0 and f[2]["interframe_timedelta"] > 0.0
+
+
+@pytest.mark.gpu
+def test_gpu_decoder_edge_streams(oracle):
+    cfg, az, alt = make_config(stride=2)
+    for name, pk in edge_streams(cfg).items():
+        want = oracle.OracleLidar(cfg, az, alt).decode(pk)
+        got = frames_as_dicts(LidarCallback(cfg, az, alt).DecodePackets(pk))
+        assert len(want) >= 2, name
+        assert_frames_equal(got, want)
+
+
+@pytest.mark.gpu
+def test_gpu_decoder_buffers_and_limits(oracle):
+    import torch
+
+    cfg, az, alt = make_config(stride=1)
+    pk = make_stream(cfg, 2, seed=31)
+    want = oracle.OracleLidar(cfg, az, alt).decode(pk)
+    # pinned host memory (DMA straight from the caller's buffer) and a strided buffer (pitch > packet size)
+    pinned = torch.from_numpy(pk).pin_memory()
+    cb = LidarCallback(cfg, az, alt)
+    assert cb.push(pinned.data_ptr(), pk.shape[0], pk.shape[1]) == 2
+    got = []
+    for _ in range(2):
+        f = cb.pop(); got += frames_as_dicts([f])
+    assert_frames_equal(got, want)
+    wide = np.zeros((pk.shape[0], pk.shape[1] + 48), np.uint8)
+    wide[:, :pk.shape[1]] = pk
+    cb2 = LidarCallback(cfg, az, alt)
+    assert cb2.push(wide.ctypes.data, pk.shape[0], pk.shape[1], pitch=wide.shape[1]) == 2
+    got2 = []
+    for _ in range(2):
+        f = cb2.pop(); got2 += frames_as_dicts([f])
+    assert_frames_equal(got2, want)
+    # a "frame" longer than two revolutions: the extra packets are refused loudly, the decoder stays usable
+    n = cfg.columns_per_frame // cfg.columns_per_packet
+    same = np.concatenate([pk[:n]] * 3)
+    cb3 = LidarCallback(cfg, az, alt)
+    with pytest.raises(ndtb.NdtbError) as e:
+        cb3.push(same)
+    assert e.value.code == ndtb.NDTB_ERR_OVERFLOW
+    assert cb3.push(pk[n:]) == 2 and cb3.pop().packets == 2 * n + 2 and cb3.pop().packets == n
+    # nothing closed yet -> nothing to pop; empty push is a no-op
+    cb4 = LidarCallback(cfg, az, alt)
+    assert cb4.push(pk[:3]) == 0 and cb4.pop() is None and cb4.push(pk[:0]) == 0
