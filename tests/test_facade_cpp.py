@@ -69,3 +69,47 @@ def test_facade_matches_python_binding(two_plane, tmp_path):
     assert np.abs(np.array([float(v) for v in m[3:19]]).reshape(4, 4) - mg.getFinalTransformation()).max() <= 1e-6
     assert int(m[19]) == 2 and int(m[20]) == len(mg.getVoxelPCD())
     assert abs(float(m[21]) - mg.calculateNearestVoxelTransformationLikelihood(mg.getFinalTransformation())) <= 1e-6
+
+
+LIDAR_EXE = os.path.join(ROOT, "tests", "cpp", "lidar_example")
+
+
+def build_lidar_example():
+    lib_dir = os.path.join(ROOT, "slam_sam_b200")
+    if not os.path.exists(os.path.join(lib_dir, "libndtb.so")):
+        pytest.skip("libndtb.so not built")
+    gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else shutil.which("g++")
+    cmd = [gxx, "-std=c++17", "-O2", "-Wall", "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "cpp", "lidar_example.cpp"),
+           "-L" + lib_dir, "-lndtb", "-Wl,-rpath," + lib_dir, "-o", LIDAR_EXE]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    return LIDAR_EXE
+
+
+def test_lidar_facade_compiles_and_links():
+    """include/ndtb_lidar.hpp (LidarCallback / LidarFrame with the reference's names) builds against libndtb.so."""
+    exe = build_lidar_example()
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 2 and "usage" in r.stderr
+
+
+@pytest.mark.gpu
+def test_lidar_facade_matches_oracle(oracle, tmp_path):
+    from test_lidar_decode import make_config, make_stream
+
+    exe = build_lidar_example()
+    cfg, az, alt = make_config(cols=128, pixels=64, stride=2)
+    pk = make_stream(cfg, 3, seed=77)
+    path = tmp_path / "packets.bin"
+    pk.tofile(path)
+    r = subprocess.run([exe, str(path), "128", "64", "2"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    want = oracle.OracleLidar(cfg, az, alt).decode(pk)
+    lines = r.stdout.strip().splitlines()
+    assert len(lines) == len(want) == 3
+    for line, w in zip(lines, want):
+        f = line.split()
+        assert int(f[0]) == w["frame_id"] and int(f[1]) == w["numberpoints"]
+        assert float(f[2]) == w["timestamp"] and float(f[3]) == w["timestamp_end"] and float(f[4]) == w["interframe_timedelta"]
+        assert float(f[5]) == float(np.sum(w["x"].astype(np.float64))) or abs(float(f[5]) - np.sum(w["x"].astype(np.float64))) < 1e-6
+        assert int(f[6]) == int(w["c_id"].astype(np.int64).sum()) and int(f[7]) == int(w["signal"].astype(np.int64).sum())
