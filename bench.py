@@ -362,6 +362,20 @@ def run_gpu(args, rank, world, local_rank):
         line["cpu_baseline"] = {"value": 1.0 / c["mean_s"], "unit": "scans/s", "cores": threads, "kind": "port",
                                 "sample": f"2 steps (after 1 warm-up) of the same workload: 1M-pt map build ({c['build_s']*1e3:.0f} ms, serial like the "
                                           f"reference) + align ({c['iterations']:.0f} iterations) with {threads} OpenMP threads"}
+        # the scan producer's CPU side: the oracle restatement of DecodePacketRng19 (one thread, like the reference's callback)
+        # decoding the same 65 packets, timed beside the device decode of e2e_packets
+        import oracle_lib as O
+        od = O.OracleLidar(lcfg, az_deg, alt_deg)
+        pk_np = p_packets[0].numpy()
+        pk_np[:n_pk, 2] = 1; pk_np[:n_pk, 3] = 0; pk_np[n_pk, 2] = 2; pk_np[n_pk, 3] = 0
+        od.decode(pk_np)
+        t0 = time.perf_counter()
+        reps = 5
+        for r in range(reps):
+            pk_np[:n_pk, 2] = (3 + 2 * r) & 0xff; pk_np[n_pk, 2] = (4 + 2 * r) & 0xff
+            fr = od.L.orc_lidar_decode(od.h, pk_np.ctypes.data, pk_np.shape[0], pk_np.shape[1], pk_np.shape[1])
+        line["e2e_packets"]["decode_cpu_port_us"] = (time.perf_counter() - t0) / reps * 1e6
+        line["e2e_packets"]["decode_cpu_port_what"] = "oracle/ouster_decode.hpp (restatement of LidarCallback::DecodePacketRng19), 1 thread, same 65 packets"
     if world > 1:
         dist.destroy_process_group()
     return line

@@ -190,10 +190,12 @@ public:
   double getOutlierRatio() const { return p_.outlier_ratio; }
   void setOutlierRatio(double r) { p_.outlier_ratio = r; }
   void setNeighborhoodSearchMethod(NeighborSearchMethod m) {
-    if (m != DIRECT7 && m != DIRECT1) throw std::invalid_argument("ndtb: only DIRECT7 / DIRECT1 neighbour search are provided");
-    p_.search_method = (m == DIRECT7) ? NDTB_DIRECT7 : NDTB_DIRECT1;
+    if (m == KDTREE) throw std::invalid_argument("ndtb: DIRECT7 / DIRECT1 / DIRECT26 are provided; KDTREE only in MultiGridNormalDistributionsTransform");
+    p_.search_method = (m == DIRECT7) ? NDTB_DIRECT7 : (m == DIRECT1 ? NDTB_DIRECT1 : NDTB_DIRECT26);
   }
-  NeighborSearchMethod getNeighborhoodSearchMethod() const { return p_.search_method == NDTB_DIRECT7 ? DIRECT7 : DIRECT1; }
+  NeighborSearchMethod getNeighborhoodSearchMethod() const {
+    return p_.search_method == NDTB_DIRECT7 ? DIRECT7 : (p_.search_method == NDTB_DIRECT1 ? DIRECT1 : DIRECT26);
+  }
   void setTransformationEpsilon(double e) { p_.trans_epsilon = e; }
   double getTransformationEpsilon() { return p_.trans_epsilon; }
   void setMaximumIterations(int n) { p_.max_iterations = n; }

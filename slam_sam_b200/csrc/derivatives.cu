@@ -367,6 +367,13 @@ __device__ __forceinline__ void hash_find_batch(const HashSlot* __restrict__ tab
 }
 
 __device__ __constant__ int c_off[7][3] = {{0, 0, 0}, {1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};
+// DIRECT26 (voxel_grid_covariance_omp_impl.hpp:366-411): pcl::getAllNeighborCellIndices() = the 13 "half" displacements of
+// pcl::getHalfNeighborCellIndices() followed by their negatives; the centre cell is NOT among them.
+__device__ __constant__ int c_off26[26][3] = {
+    {-1, -1, -1}, {-1, 0, -1}, {-1, 1, -1}, {0, -1, -1}, {0, 0, -1}, {0, 1, -1}, {1, -1, -1}, {1, 0, -1}, {1, 1, -1},
+    {-1, -1, 0}, {0, -1, 0}, {1, -1, 0}, {-1, 0, 0},
+    {1, 1, 1}, {1, 0, 1}, {1, -1, 1}, {0, 1, 1}, {0, 0, 1}, {0, -1, 1}, {-1, 1, 1}, {-1, 0, 1}, {-1, -1, 1},
+    {1, 1, 0}, {0, 1, 0}, {-1, 1, 0}, {1, 0, 0}};
 
 // ------------------------------------------------------------------------------ reductions
 constexpr int RED_PAD = 48;  // RED_N padded so the vector can be halved 4 times (48,24,12,6,3)
@@ -436,11 +443,14 @@ struct __align__(16) PtSlot {  // 28 words
   float xh[16];
 };
 
-struct WarpScratch {
+constexpr int Q_CAP26 = 512;                  // >= 31 + 26 * 16: DIRECT26 through the generic kernel, 16 points per chunk (static smem <= 48 KB)
+template <int QC>
+struct WarpScratchT {
   PtSlot pts[SLOT_RING];
-  int qrow[Q_CAP];
-  unsigned char qslot[Q_CAP];
+  int qrow[QC];
+  unsigned char qslot[QC];
 };
+using WarpScratch = WarpScratchT<Q_CAP>;
 
 template <int FLAVOUR, bool HESS, bool GN>
 __device__ __forceinline__ void eval_pair(PtSlot* __restrict__ s_pts, int slot, int row, const EvalState& st, const VoxRec* __restrict__ recs,
@@ -489,7 +499,7 @@ __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefe
 
 // Phase A for one chunk: lane `lane` handles point `idx` (if `have`), fills its slot, appends its pairs
 // to the warp's queue at `tail`; returns the number of pairs the warp appended.
-template <int FLAVOUR, int PROBES, bool HESS, bool GN, bool PAIRED = false>
+template <int FLAVOUR, int PROBES, bool HESS, bool GN, bool PAIRED = false, int QC = Q_CAP>
 __device__ __forceinline__ int phase_a(const float4* __restrict__ src, int idx, bool have, int slot, int lane, int tail, const GridMeta& m,
                                        const VoxRec* __restrict__ recs, const HashSlot* __restrict__ table, const EvalState& st,
                                        PtSlot* __restrict__ s_pts, int* __restrict__ s_qrow, unsigned char* __restrict__ s_qslot,
@@ -512,7 +522,10 @@ __device__ __forceinline__ int phase_a(const float4* __restrict__ src, int idx, 
           const int i1 = static_cast<int>(floorf(__fdiv_rn(xt[1], m.leaf)));
           const int i2 = static_cast<int>(floorf(__fdiv_rn(xt[2], m.leaf)));
 #pragma unroll
-          for (int q = 0; q < PROBES; ++q) key[q] = cell_key_pclomp(m, i0, i1, i2, c_off[q][0], c_off[q][1], c_off[q][2]);
+          for (int q = 0; q < PROBES; ++q) {
+            if (PROBES == 26) key[q] = cell_key_pclomp(m, i0, i1, i2, c_off26[q][0], c_off26[q][1], c_off26[q][2]);
+            else key[q] = cell_key_pclomp(m, i0, i1, i2, c_off[q < 7 ? q : 0][0], c_off[q < 7 ? q : 0][1], c_off[q < 7 ? q : 0][2]);
+          }
         } else {
 #pragma unroll
           for (int q = 0; q < PROBES; ++q) {
@@ -580,8 +593,8 @@ __device__ __forceinline__ int phase_a(const float4* __restrict__ src, int idx, 
 #pragma unroll
       for (int q = 0; q < PROBES; ++q) {
         if (rows[q] >= 0) {
-          s_qrow[pos & (Q_CAP - 1)] = rows[q];
-          s_qslot[pos & (Q_CAP - 1)] = static_cast<unsigned char>(slot);
+          s_qrow[pos & (QC - 1)] = rows[q];
+          s_qslot[pos & (QC - 1)] = static_cast<unsigned char>(slot);
           ++pos;
         }
       }
@@ -597,7 +610,9 @@ __global__ void __launch_bounds__(EVAL_THREADS, EVAL_MIN_BLOCKS) eval_kernel(con
                                                                           double* __restrict__ results, unsigned int* __restrict__ tickets,
                                                                           int particle_offset) {
   __shared__ EvalState st;
-  __shared__ WarpScratch s_warp[EVAL_WARPS];
+  constexpr int QC = (PROBES > 7) ? Q_CAP26 : Q_CAP;
+  constexpr int GPC = (PROBES > 7) ? GROUPS_PER_CHUNK / 2 : GROUPS_PER_CHUNK;  // point groups per chunk
+  __shared__ WarpScratchT<QC> s_warp[EVAL_WARPS];
   __shared__ double s_red[EVAL_WARPS][RED_PAD];
   __shared__ bool s_last;
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -624,17 +639,17 @@ __global__ void __launch_bounds__(EVAL_THREADS, EVAL_MIN_BLOCKS) eval_kernel(con
   const int warp_global = blockIdx.x * EVAL_WARPS + w;
   // this warp's groups: warp_global + k * n_warps, k = 0 .. my_groups-1
   const int my_groups = (n_groups > warp_global) ? (n_groups - warp_global + n_warps - 1) / n_warps : 0;
-  int head = 0, tail = 0;  // queue positions (monotonic; entry = pos & (Q_CAP - 1))
+  int head = 0, tail = 0;  // queue positions (monotonic; entry = pos & (QC - 1))
   int chunk = 0;
-  for (int k0 = 0; k0 < my_groups; k0 += GROUPS_PER_CHUNK, ++chunk) {
+  for (int k0 = 0; k0 < my_groups; k0 += GPC, ++chunk) {
     // ---------------------------------------------------------------- phase A: one lane per point
     const int k = k0 + lane / PT_GROUP;
     const int idx = (warp_global + k * n_warps) * PT_GROUP + (lane % PT_GROUP);
-    const bool have = (k < my_groups) && (idx < n);
+    const bool have = (lane < GPC * PT_GROUP) && (k < my_groups) && (idx < n);
     const int slot = (chunk & 1) * 32 + lane;
     // the slot's previous occupant (two chunks ago) has had all its pairs evaluated: retire its NVTL term
     if (FLAVOUR == FLAVOUR_PCLOMP) acc[RED_NEAREST] += static_cast<double>(__int_as_float(s_pts[slot].nearest_bits));
-    const int total = phase_a<FLAVOUR, PROBES, HESS, GN>(src, idx, have, slot, lane, tail, m, recs, table, st, s_pts, s_qrow, s_qslot,
+    const int total = phase_a<FLAVOUR, PROBES, HESS, GN, false, QC>(src, idx, have, slot, lane, tail, m, recs, table, st, s_pts, s_qrow, s_qslot,
                                                          acc[RED_FOUND], acc[RED_COUNT]);
     const int must = tail;  // everything queued before this chunk must be consumed before its slots are reused
     tail += total;
@@ -642,14 +657,14 @@ __global__ void __launch_bounds__(EVAL_THREADS, EVAL_MIN_BLOCKS) eval_kernel(con
     // ---------------------------------------------------------------- phase B: one lane per pair
     while (tail - head >= 32 || head < must) {
       const int e = head + lane;
-      if (e < tail) eval_pair<FLAVOUR, HESS, GN>(s_pts, s_qslot[e & (Q_CAP - 1)], s_qrow[e & (Q_CAP - 1)], st, recs, c_mean, c_icov, d2f, acc);
+      if (e < tail) eval_pair<FLAVOUR, HESS, GN>(s_pts, s_qslot[e & (QC - 1)], s_qrow[e & (QC - 1)], st, recs, c_mean, c_icov, d2f, acc);
       head = min(head + 32, tail);
     }
     __syncwarp();
   }
   while (head < tail) {  // flush
     const int e = head + lane;
-    if (e < tail) eval_pair<FLAVOUR, HESS, GN>(s_pts, s_qslot[e & (Q_CAP - 1)], s_qrow[e & (Q_CAP - 1)], st, recs, c_mean, c_icov, d2f, acc);
+    if (e < tail) eval_pair<FLAVOUR, HESS, GN>(s_pts, s_qslot[e & (QC - 1)], s_qrow[e & (QC - 1)], st, recs, c_mean, c_icov, d2f, acc);
     head = min(head + 32, tail);
   }
   __syncwarp();
@@ -1084,7 +1099,9 @@ void launch_eval(int flavour, int n_probe, bool compute_hessian, bool gn, const 
                  int n_particles, int particle_offset, cudaStream_t stream) {
 #define ARGS d_src, n, meta, recs, table, c_mean, c_icov, b, n_particles, particle_offset, stream
   if (flavour == FLAVOUR_PCLOMP) {
-    return;  // pclomp evaluations go through launch_eval_pclomp
+    // DIRECT1 / DIRECT7 evaluations go through launch_eval_pclomp; DIRECT26 (off the hot path) uses this generic kernel
+    if (n_probe == 26) { if (compute_hessian) launch_t<FLAVOUR_PCLOMP, 26, true, false>(ARGS); else launch_t<FLAVOUR_PCLOMP, 26, false, false>(ARGS); }
+    return;
   } else {
     if (n_probe == 7) { if (gn) launch_t<FLAVOUR_SVN, 7, true, true>(ARGS); else launch_t<FLAVOUR_SVN, 7, true, false>(ARGS); }
     else { if (gn) launch_t<FLAVOUR_SVN, 1, true, true>(ARGS); else launch_t<FLAVOUR_SVN, 1, true, false>(ARGS); }
