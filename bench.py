@@ -675,8 +675,7 @@ def run_gpu_multigrid(args, rank, world, local_rank):
             "roofline": {"kernel": "mg_eval_kernel<hessian>", "bound": "hbm", "achieved": b_eval / t_eval / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": b_eval / t_eval / 1e9 / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": b_eval,
                          "mean_hits_per_point": hbar, "kernel_us": t_eval * 1e6,
-                         "note": "FP64 pair maths (~700 flops per point-leaf pair): the kernel is FP64-issue bound, not HBM bound; the HBM figure is "
-                                 "reported for comparability with the pclomp kernel"},
+                         "note": "all-FP64 pair maths, 250 registers -> 8 warps per SM: latency-bound (ncu: issue-active 24 %, FP64 pipe 15 %, 3.5 MB of DRAM traffic per launch, profiles/r01_mg_eval_kernel_ncu_full.txt), not HBM bound; the HBM figure is reported for comparability with the pclomp kernel"},
             "clocks": clk}
 
 
