@@ -14,6 +14,12 @@ using namespace ndtb;
 namespace ndtb {
 
 __device__ __constant__ int c_off7[7][3] = {{0, 0, 0}, {1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};
+// DIRECT26: pcl::getAllNeighborCellIndices (13 half displacements, then their negatives; no centre cell), see derivatives.cu
+__device__ __constant__ int c_off26s[26][3] = {
+    {-1, -1, -1}, {-1, 0, -1}, {-1, 1, -1}, {0, -1, -1}, {0, 0, -1}, {0, 1, -1}, {1, -1, -1}, {1, 0, -1}, {1, 1, -1},
+    {-1, -1, 0}, {0, -1, 0}, {1, -1, 0}, {-1, 0, 0},
+    {1, 1, 1}, {1, 0, 1}, {1, -1, 1}, {0, 1, 1}, {0, 0, 1}, {0, -1, 1}, {-1, 1, 1}, {-1, 0, 1}, {-1, -1, 1},
+    {1, 1, 0}, {0, 1, 0}, {-1, 1, 0}, {1, 0, 0}};
 
 // out[0] = sum of scores, out[1] = sum of per-point max score, out[2] = points with neighbours.
 // Block partials are combined in block order by the host (tiny), so the result is deterministic.
@@ -34,7 +40,8 @@ __global__ void __launch_bounds__(128) score_kernel(const float4* __restrict__ s
     double best = 0;
     int nn = 0;
     for (int k = 0; k < probes; ++k) {
-      const int ox = c_off7[k][0], oy = c_off7[k][1], oz = c_off7[k][2];
+      const int* off = (probes == 26) ? c_off26s[k] : c_off7[k];
+      const int ox = off[0], oy = off[1], oz = off[2];
       if (m.min_b[0] - i0 > ox || m.max_b[0] - i0 < ox || m.min_b[1] - i1 > oy || m.max_b[1] - i1 < oy || m.min_b[2] - i2 > oz || m.max_b[2] - i2 < oz) continue;
       const int lin = (i0 + ox - m.min_b[0]) * m.divb_mul[0] + (i1 + oy - m.min_b[1]) * m.divb_mul[1] + (i2 + oz - m.min_b[2]) * m.divb_mul[2];
       const int row = hash_find(table, m.hash_mask, static_cast<uint32_t>(lin));
@@ -84,8 +91,7 @@ int ndtb_calculate_scores(ndtb_handle h, const float T16[16], double* transforma
     const double c2 = h->params.outlier_ratio / pow(static_cast<double>(h->params.resolution), 3);
     d3 = -log(c2); d1 = -log(c1 + c2) - d3; d2 = -2 * log((-log(c1 * exp(-0.5) + c2) - d3) / d1);
   }
-  if (h->params.search_method == NDTB_DIRECT26) return set_error(h, NDTB_ERR_INVALID, "score-only passes are provided for DIRECT1 / DIRECT7");
-  const int probes = (h->params.search_method == NDTB_DIRECT1) ? 1 : 7;
+  const int probes = (h->params.search_method == NDTB_DIRECT1) ? 1 : (h->params.search_method == NDTB_DIRECT26 ? 26 : 7);
   score_kernel<<<blocks, 128, 0, h->stream>>>(h->d_source, n, h->grid.meta, h->grid.table, h->grid.c_mean, h->grid.c_icov, d_T, d1, d2, probes, d_out);
   h->launches += 1;
   std::vector<double> out(3 * static_cast<size_t>(blocks));
