@@ -31,7 +31,7 @@ extern "C" {
 #define NDTB_ERR_NOT_READY (-5) /* target or source not set                                         */
 
 /* pclomp::NeighborSearchMethod values (extern/ndt_omp/include/pclomp/ndt_struct.hpp) */
-#define NDTB_KDTREE 0   /* radius search: provided by the multigrid class only (ndtb_mg_*); NDTB_ERR_INVALID in ndtb_set_params */
+#define NDTB_KDTREE 0   /* pclomp flavour: radius search over the leaf means, derivatives + align without line search (generic kernel) */
 #define NDTB_DIRECT26 1 /* pclomp flavour, derivatives + align without line search (generic kernel, off the hot path)      */
 #define NDTB_DIRECT7 2
 #define NDTB_DIRECT1 3

@@ -190,11 +190,10 @@ public:
   double getOutlierRatio() const { return p_.outlier_ratio; }
   void setOutlierRatio(double r) { p_.outlier_ratio = r; }
   void setNeighborhoodSearchMethod(NeighborSearchMethod m) {
-    if (m == KDTREE) throw std::invalid_argument("ndtb: DIRECT7 / DIRECT1 / DIRECT26 are provided; KDTREE only in MultiGridNormalDistributionsTransform");
-    p_.search_method = (m == DIRECT7) ? NDTB_DIRECT7 : (m == DIRECT1 ? NDTB_DIRECT1 : NDTB_DIRECT26);
+    p_.search_method = (m == DIRECT7) ? NDTB_DIRECT7 : (m == DIRECT1 ? NDTB_DIRECT1 : (m == DIRECT26 ? NDTB_DIRECT26 : NDTB_KDTREE));
   }
   NeighborSearchMethod getNeighborhoodSearchMethod() const {
-    return p_.search_method == NDTB_DIRECT7 ? DIRECT7 : (p_.search_method == NDTB_DIRECT1 ? DIRECT1 : DIRECT26);
+    return p_.search_method == NDTB_DIRECT7 ? DIRECT7 : (p_.search_method == NDTB_DIRECT1 ? DIRECT1 : (p_.search_method == NDTB_DIRECT26 ? DIRECT26 : KDTREE));
   }
   void setTransformationEpsilon(double e) { p_.trans_epsilon = e; }
   double getTransformationEpsilon() { return p_.trans_epsilon; }

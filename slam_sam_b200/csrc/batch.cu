@@ -143,7 +143,7 @@ int ndtb_align_batch(ndtb_handle h, int n_scans, const float* const* xyz, const 
   if (!h || n_scans < 0 || !xyz || !n_points || !guesses16 || !results) return NDTB_ERR_INVALID;
   cudaSetDevice(h->device);
   const bool interleave = h->params.grid_flavour == NDTB_FLAVOUR_PCLOMP && !h->params.use_line_search && !h->kernel_events && h->batch_interleave &&
-                          h->grid.built && n_scans > 1 && h->params.search_method != NDTB_DIRECT26;
+                          h->grid.built && n_scans > 1 && h->params.search_method != NDTB_DIRECT26 && h->params.search_method != NDTB_KDTREE;
   if (!interleave) {  // serial: one ndtb_set_source + ndtb_align per scan
     for (int i = 0; i < n_scans; ++i) {
       int rc = ndtb_set_source(h, xyz[i], n_points[i], stride_bytes);

@@ -367,6 +367,12 @@ __device__ __forceinline__ void hash_find_batch(const HashSlot* __restrict__ tab
 }
 
 __device__ __constant__ int c_off[7][3] = {{0, 0, 0}, {1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};
+// KDTREE (radius search, radius = resolution = leaf size): only the 27 cells around the query can hold a leaf whose mean is closer
+// than one leaf size, so the kd-tree is 27 hash probes + FLANN's float distance test (phase_a).
+__device__ __constant__ int c_off27[27][3] = {
+    {0, 0, 0}, {1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1},
+    {1, 1, 0}, {1, -1, 0}, {-1, 1, 0}, {-1, -1, 0}, {1, 0, 1}, {1, 0, -1}, {-1, 0, 1}, {-1, 0, -1}, {0, 1, 1}, {0, 1, -1}, {0, -1, 1}, {0, -1, -1},
+    {1, 1, 1}, {1, 1, -1}, {1, -1, 1}, {1, -1, -1}, {-1, 1, 1}, {-1, 1, -1}, {-1, -1, 1}, {-1, -1, -1}};
 // DIRECT26 (voxel_grid_covariance_omp_impl.hpp:366-411): pcl::getAllNeighborCellIndices() = the 13 "half" displacements of
 // pcl::getHalfNeighborCellIndices() followed by their negatives; the centre cell is NOT among them.
 __device__ __constant__ int c_off26[26][3] = {
@@ -523,7 +529,8 @@ __device__ __forceinline__ int phase_a(const float4* __restrict__ src, int idx, 
           const int i2 = static_cast<int>(floorf(__fdiv_rn(xt[2], m.leaf)));
 #pragma unroll
           for (int q = 0; q < PROBES; ++q) {
-            if (PROBES == 26) key[q] = cell_key_pclomp(m, i0, i1, i2, c_off26[q][0], c_off26[q][1], c_off26[q][2]);
+            if (PROBES == 27) key[q] = cell_key_pclomp(m, i0, i1, i2, c_off27[q][0], c_off27[q][1], c_off27[q][2]);
+            else if (PROBES == 26) key[q] = cell_key_pclomp(m, i0, i1, i2, c_off26[q][0], c_off26[q][1], c_off26[q][2]);
             else key[q] = cell_key_pclomp(m, i0, i1, i2, c_off[q < 7 ? q : 0][0], c_off[q < 7 ? q : 0][1], c_off[q < 7 ? q : 0][2]);
           }
         } else {
@@ -537,6 +544,21 @@ __device__ __forceinline__ int phase_a(const float4* __restrict__ src, int idx, 
           }
         }
         hash_find_batch<PROBES>(table, m.hash_mask, key, rows);
+        if (FLAVOUR == FLAVOUR_PCLOMP && PROBES == 27) {
+          // pclomp KDTREE: radiusSearch(x_trans, resolution_) over the cloud of float(leaf.mean_) (voxel_grid_covariance_omp.h:458-485,
+          // _omp_impl.hpp:301-303); pcl::KdTreeFLANN hands float(radius * radius) to FLANN, L2_Simple<float> accumulates
+          // dx*dx + dy*dy + dz*dz in float, RadiusResultSet keeps dist < r2 (strict)
+          const float r2 = static_cast<float>(static_cast<double>(m.leaf) * static_cast<double>(m.leaf));
+#pragma unroll
+          for (int q = 0; q < PROBES; ++q) {
+            if (rows[q] >= 0) {
+              const double* mu = recs[rows[q]].mean;
+              const float dx = xt[0] - static_cast<float>(__ldg(mu)), dy = xt[1] - static_cast<float>(__ldg(mu + 1)), dz = xt[2] - static_cast<float>(__ldg(mu + 2));
+              float d = dx * dx; d = d + dy * dy; d = d + dz * dz;
+              if (!(d < r2)) rows[q] = -1;
+            }
+          }
+        }
 #pragma unroll
         for (int q = 0; q < PROBES; ++q) {
           if (rows[q] >= 0) {
@@ -1099,8 +1121,9 @@ void launch_eval(int flavour, int n_probe, bool compute_hessian, bool gn, const 
                  int n_particles, int particle_offset, cudaStream_t stream) {
 #define ARGS d_src, n, meta, recs, table, c_mean, c_icov, b, n_particles, particle_offset, stream
   if (flavour == FLAVOUR_PCLOMP) {
-    // DIRECT1 / DIRECT7 evaluations go through launch_eval_pclomp; DIRECT26 (off the hot path) uses this generic kernel
+    // DIRECT1 / DIRECT7 evaluations go through launch_eval_pclomp; DIRECT26 and KDTREE (27 cells + radius test), off the hot path, use this generic kernel
     if (n_probe == 26) { if (compute_hessian) launch_t<FLAVOUR_PCLOMP, 26, true, false>(ARGS); else launch_t<FLAVOUR_PCLOMP, 26, false, false>(ARGS); }
+    if (n_probe == 27) { if (compute_hessian) launch_t<FLAVOUR_PCLOMP, 27, true, false>(ARGS); else launch_t<FLAVOUR_PCLOMP, 27, false, false>(ARGS); }
     return;
   } else {
     if (n_probe == 7) { if (gn) launch_t<FLAVOUR_SVN, 7, true, true>(ARGS); else launch_t<FLAVOUR_SVN, 7, true, false>(ARGS); }

@@ -91,6 +91,7 @@ int ndtb_calculate_scores(ndtb_handle h, const float T16[16], double* transforma
     const double c2 = h->params.outlier_ratio / pow(static_cast<double>(h->params.resolution), 3);
     d3 = -log(c2); d1 = -log(c1 + c2) - d3; d2 = -2 * log((-log(c1 * exp(-0.5) + c2) - d3) / d1);
   }
+  if (h->params.search_method == NDTB_KDTREE) return set_error(h, NDTB_ERR_INVALID, "score-only passes are provided for DIRECT1 / DIRECT7 / DIRECT26");
   const int probes = (h->params.search_method == NDTB_DIRECT1) ? 1 : (h->params.search_method == NDTB_DIRECT26 ? 26 : 7);
   score_kernel<<<blocks, 128, 0, h->stream>>>(h->d_source, n, h->grid.meta, h->grid.table, h->grid.c_mean, h->grid.c_icov, d_T, d1, d2, probes, d_out);
   h->launches += 1;

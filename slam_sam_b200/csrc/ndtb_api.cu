@@ -146,7 +146,7 @@ static void session_begin(ndtb_handle_s* h) {
   static const bool env_off = getenv("NDTB_NO_SESSION") != nullptr;
   h->session_eval_ns = 0;
   if (!h->use_sessions || h->kernel_events || env_off || h->session_open || h->params.use_line_search) return;
-  if (h->params.search_method == NDTB_DIRECT26) return;  // served by the generic kernel, one launch per evaluation
+  if (h->params.search_method == NDTB_DIRECT26 || h->params.search_method == NDTB_KDTREE) return;  // served by the generic kernel, one launch per evaluation
   const int n = static_cast<int>(h->n_source);
   if (ensure_eval_buffers(h, 1, n) != NDTB_OK) return;
   if (!h->h_mailbox) {
@@ -193,13 +193,13 @@ static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool
     e0 = h->ev_pool[h->ev_used]; e1 = h->ev_pool[h->ev_used + 1];
     h->ev_used += 2;
   }
-  if (h->params.search_method == NDTB_DIRECT26) {
-    // getNeighborhoodAtPoint with the 26 cells of pcl::getAllNeighborCellIndices (voxel_grid_covariance_omp_impl.hpp:366-411): off the
+  if (h->params.search_method == NDTB_DIRECT26 || h->params.search_method == NDTB_KDTREE) {
+    // KDTREE: radius search over the leaf means (27 cells + float distance test).  DIRECT26: getNeighborhoodAtPoint with the 26 cells of pcl::getAllNeighborCellIndices (voxel_grid_covariance_omp_impl.hpp:366-411): off the
     // hot path north_star names, served by the generic two-phase kernel (state from device memory, results by one D2H copy)
     if (h->session_open) session_end(h);
     CKH(cudaMemcpyAsync(h->eval.d_states, h->h_states, sizeof(EvalState), cudaMemcpyHostToDevice, h->stream));
     if (e0) cudaEventRecord(e0, h->stream);
-    launch_eval(FLAVOUR_PCLOMP, 26, compute_hessian, false, h->d_source, n, h->grid.meta, h->grid.recs, h->grid.table, h->grid.c_mean, h->grid.c_icov,
+    launch_eval(FLAVOUR_PCLOMP, h->params.search_method == NDTB_KDTREE ? 27 : 26, compute_hessian, false, h->d_source, n, h->grid.meta, h->grid.recs, h->grid.table, h->grid.c_mean, h->grid.c_icov,
                 h->eval, 1, 0, h->stream);
     CKH(cudaGetLastError());
     if (e1) cudaEventRecord(e1, h->stream);
@@ -383,9 +383,9 @@ int ndtb_get_params(ndtb_handle h, ndtb_params* p) {
 
 int ndtb_set_params(ndtb_handle h, const ndtb_params* p) {
   if (!h || !p) return NDTB_ERR_INVALID;
-  const bool d26_ok = p->search_method == NDTB_DIRECT26 && p->grid_flavour == NDTB_FLAVOUR_PCLOMP && !p->use_line_search;
+  const bool d26_ok = (p->search_method == NDTB_DIRECT26 || p->search_method == NDTB_KDTREE) && p->grid_flavour == NDTB_FLAVOUR_PCLOMP && !p->use_line_search;
   if (p->search_method != NDTB_DIRECT7 && p->search_method != NDTB_DIRECT1 && !d26_ok)
-    return set_error(h, NDTB_ERR_INVALID, "DIRECT7 / DIRECT1 (both flavours) and DIRECT26 (pclomp, without line search) are provided; KDTREE only in the multigrid class");
+    return set_error(h, NDTB_ERR_INVALID, "DIRECT7 / DIRECT1 (both flavours) and DIRECT26 / KDTREE (pclomp flavour, without line search) are provided");
   if (!(p->resolution > 0.0f)) return set_error(h, NDTB_ERR_INVALID, "resolution must be positive");
   if (p->grid_flavour != NDTB_FLAVOUR_PCLOMP && p->grid_flavour != NDTB_FLAVOUR_SVN) return set_error(h, NDTB_ERR_INVALID, "bad grid_flavour");
   cudaSetDevice(h->device);
@@ -726,7 +726,7 @@ int ndtb_time_eval_kernel(ndtb_handle h, const double p[6], const float* T16, in
   int rc = ensure_eval_buffers(h, 1, n);
   if (rc != NDTB_OK) return rc;
   fill_state(h, 0, p, Tloc, 10e-5, false);
-  if (h->params.search_method == NDTB_DIRECT26) return set_error(h, NDTB_ERR_INVALID, "ndtb_time_eval_kernel times the DIRECT1 / DIRECT7 kernel");
+  if (h->params.search_method == NDTB_DIRECT26 || h->params.search_method == NDTB_KDTREE) return set_error(h, NDTB_ERR_INVALID, "ndtb_time_eval_kernel times the DIRECT1 / DIRECT7 kernel");
   const int n_probe = (h->params.search_method == NDTB_DIRECT1) ? 1 : 7;
   for (int warm = 0; warm < 2; ++warm)
     CKH(launch_eval_pclomp(n_probe, true, h->d_source, n, h->grid.meta, h->grid.recs, h->grid.table, h->h_states[0], h->eval, h->h_results, 1ull, h->stream));

@@ -205,21 +205,23 @@ def test_setters_rebuild_only_on_change(street):
     ndt.setResolution(2.0)          # ndt_omp.h:135-142: rebuild with the new leaf size
     v2 = ndt.getTargetCells()
     assert len(v2["idx"]) < len(v1["idx"])
-    with pytest.raises(ndtb.NdtbError):
-        ndt.setNeighborhoodSearchMethod(registration.KDTREE)
+    ndt.setNeighborhoodSearchMethod(registration.KDTREE)   # radius search: generic kernel (off the hot path)
+    ndt.setNeighborhoodSearchMethod(registration.DIRECT7)
     empty = registration.NormalDistributionsTransform()
     with pytest.raises(ndtb.NdtbError):
         empty.align()               # NDTB_ERR_NOT_READY: no target / source
 
 
-def test_direct26_matches_oracle(oracle, street, gold):
-    """DIRECT26 (the 26 cells of pcl::getAllNeighborCellIndices, centre excluded; voxel_grid_covariance_omp_impl.hpp:366-411)
-    runs on the device through the generic two-phase kernel: per-evaluation parity and the whole Newton trajectory."""
+@pytest.mark.parametrize("search", ["DIRECT26", "KDTREE"])
+def test_direct26_and_kdtree_match_oracle(oracle, street, gold, search):
+    """DIRECT26 (the 26 cells of pcl::getAllNeighborCellIndices, centre excluded; voxel_grid_covariance_omp_impl.hpp:366-411) and
+    KDTREE (radius search over float(leaf.mean_), voxel_grid_covariance_omp.h:458-485) run on the device through the generic
+    two-phase kernel: per-evaluation parity and the whole Newton trajectory."""
     for tgt, src, res in ((gold["target"], gold["source"], 2.0), (street["target"], street["source"], 1.0)):
         h = ndtb.Handle(0)
-        h.set_params(resolution=res, search_method=ndtb.DIRECT26, max_iterations=35, trans_epsilon=0.01, step_size=0.1)
+        h.set_params(resolution=res, search_method=getattr(ndtb, search), max_iterations=35, trans_epsilon=0.01, step_size=0.1)
         assert h.set_target(tgt) == 0 and h.set_source(src) == 0
-        o = O.OracleNdt(resolution=res, search="DIRECT26", max_iterations=35, trans_epsilon=0.01, step_size=0.1, num_threads=4)
+        o = O.OracleNdt(resolution=res, search=search, max_iterations=35, trans_epsilon=0.01, step_size=0.1, num_threads=4)
         o.set_target(tgt); o.set_source(src)
         for p in (np.zeros(6), np.array([0.3, -0.1, 0.02, 0.004, -0.003, 0.02])):
             s, g, H, nv = h.compute_derivatives(p)
@@ -228,7 +230,7 @@ def test_direct26_matches_oracle(oracle, street, gold):
             hits26 = h.last_hits()[0]
             h7 = ndtb.Handle(0); h7.set_params(resolution=res, search_method=ndtb.DIRECT7); h7.set_target(tgt); h7.set_source(src)
             h7.compute_derivatives(p)
-            assert hits26 > h7.last_hits()[0]      # 26 cells reach more leaves than the 7 of DIRECT7
+            assert hits26 > h7.last_hits()[0] or search == "KDTREE"   # 26 cells reach more leaves than the 7 of DIRECT7
             s2, g2, H2, _ = h.compute_derivatives(p, compute_hessian=False)
             assert s2 == s and np.array_equal(g2, g) and np.all(H2 == 0)
             s3, g3, H3, _ = h.compute_derivatives(p)
@@ -241,15 +243,14 @@ def test_direct26_matches_oracle(oracle, street, gold):
             assert abs(a[6] - b[6]) <= TOL * abs(b[6]) and np.abs(a[7:49] - b[7:49]).max() <= TOL * np.abs(b[13:49]).max()
         dt, da = pose_delta(rg["T"], ro["T"])
         assert dt <= 1e-4 and da <= 1e-5
-        tp, nv = h.calculate_scores(ro["T"])           # the score-only passes (ndt_omp_impl.hpp:1169-1281) with 26 cells
-        tpo, nvo = o.calculate_scores(ro["T"])
-        assert abs(tp - tpo) <= TOL * abs(tpo) and abs(nv - nvo) <= TOL * abs(nvo)
-    # what stays outside: KDTREE for this class, DIRECT26 with line search or for the svn flavour
+        if search == "DIRECT26":
+            tp, nv = h.calculate_scores(ro["T"])       # the score-only passes (ndt_omp_impl.hpp:1169-1281) with 26 cells
+            tpo, nvo = o.calculate_scores(ro["T"])
+            assert abs(tp - tpo) <= TOL * abs(tpo) and abs(nv - nvo) <= TOL * abs(nvo)
+    # what stays outside: these two with line search or for the svn flavour
     h = ndtb.Handle(0)
     p = ndtb.Params(); h.L.ndtb_get_params(h.h, p)
-    p.search_method = ndtb.KDTREE
-    assert h.L.ndtb_set_params(h.h, p) == ndtb.NDTB_ERR_INVALID
-    p.search_method = ndtb.DIRECT26; p.use_line_search = 1
+    p.search_method = getattr(ndtb, search); p.use_line_search = 1
     assert h.L.ndtb_set_params(h.h, p) == ndtb.NDTB_ERR_INVALID
     p.use_line_search = 0; p.grid_flavour = ndtb.FLAVOUR_SVN
     assert h.L.ndtb_set_params(h.h, p) == ndtb.NDTB_ERR_INVALID

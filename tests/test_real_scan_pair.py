@@ -65,7 +65,7 @@ def test_oracle_tight_epsilon_stays_in_the_readme_band(oracle, pair, search):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("search", ["DIRECT7", "DIRECT1"])
+@pytest.mark.parametrize("search", ["DIRECT7", "DIRECT1", "KDTREE", "DIRECT26"])
 def test_gpu_matches_oracle_on_real_data(oracle, pair, search):
     h = ndtb.Handle(0)
     h.set_params(resolution=1.0, step_size=0.1, trans_epsilon=0.01, max_iterations=35, search_method=getattr(ndtb, search))
@@ -89,7 +89,7 @@ def test_gpu_matches_oracle_on_real_data(oracle, pair, search):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("search", ["DIRECT7", "DIRECT1"])
+@pytest.mark.parametrize("search", ["DIRECT7", "DIRECT1", "KDTREE"])
 def test_gpu_reproduces_the_readme_fitness(pair, search):
     """The CUDA path alone (no oracle in the loop) against the number the reference printed for this pair."""
     h = ndtb.Handle(0)
