@@ -20,6 +20,11 @@ __device__ __constant__ int c_off26s[26][3] = {
     {-1, -1, 0}, {0, -1, 0}, {1, -1, 0}, {-1, 0, 0},
     {1, 1, 1}, {1, 0, 1}, {1, -1, 1}, {0, 1, 1}, {0, 0, 1}, {0, -1, 1}, {-1, 1, 1}, {-1, 0, 1}, {-1, -1, 1},
     {1, 1, 0}, {0, 1, 0}, {-1, 1, 0}, {1, 0, 0}};
+// KDTREE: the 27 cells a radius search with radius = leaf size can reach (+ the float distance test below), see derivatives.cu
+__device__ __constant__ int c_off27s[27][3] = {
+    {0, 0, 0}, {1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1},
+    {1, 1, 0}, {1, -1, 0}, {-1, 1, 0}, {-1, -1, 0}, {1, 0, 1}, {1, 0, -1}, {-1, 0, 1}, {-1, 0, -1}, {0, 1, 1}, {0, 1, -1}, {0, -1, 1}, {0, -1, -1},
+    {1, 1, 1}, {1, 1, -1}, {1, -1, 1}, {1, -1, -1}, {-1, 1, 1}, {-1, 1, -1}, {-1, -1, 1}, {-1, -1, -1}};
 
 // out[0] = sum of scores, out[1] = sum of per-point max score, out[2] = points with neighbours.
 // Block partials are combined in block order by the host (tiny), so the result is deterministic.
@@ -40,12 +45,19 @@ __global__ void __launch_bounds__(128) score_kernel(const float4* __restrict__ s
     double best = 0;
     int nn = 0;
     for (int k = 0; k < probes; ++k) {
-      const int* off = (probes == 26) ? c_off26s[k] : c_off7[k];
+      const int* off = (probes == 27) ? c_off27s[k] : ((probes == 26) ? c_off26s[k] : c_off7[k]);
       const int ox = off[0], oy = off[1], oz = off[2];
       if (m.min_b[0] - i0 > ox || m.max_b[0] - i0 < ox || m.min_b[1] - i1 > oy || m.max_b[1] - i1 < oy || m.min_b[2] - i2 > oz || m.max_b[2] - i2 < oz) continue;
       const int lin = (i0 + ox - m.min_b[0]) * m.divb_mul[0] + (i1 + oy - m.min_b[1]) * m.divb_mul[1] + (i2 + oz - m.min_b[2]) * m.divb_mul[2];
       const int row = hash_find(table, m.hash_mask, static_cast<uint32_t>(lin));
       if (row < 0) continue;
+      if (probes == 27) {  // radiusSearch over float(leaf.mean_): L2_Simple<float>, dist < float(r * r)
+        const float r2 = static_cast<float>(static_cast<double>(m.leaf) * static_cast<double>(m.leaf));
+        const float dx = xt[0] - static_cast<float>(__ldg(c_mean + 3 * row)), dy = xt[1] - static_cast<float>(__ldg(c_mean + 3 * row + 1)),
+                    dz = xt[2] - static_cast<float>(__ldg(c_mean + 3 * row + 2));
+        float d = dx * dx; d = d + dy * dy; d = d + dz * dz;
+        if (!(d < r2)) continue;
+      }
       ++nn;
       double x[3], C[9];
       for (int a = 0; a < 3; ++a) x[a] = static_cast<double>(xt[a]) - __ldg(c_mean + 3 * row + a);
@@ -91,8 +103,7 @@ int ndtb_calculate_scores(ndtb_handle h, const float T16[16], double* transforma
     const double c2 = h->params.outlier_ratio / pow(static_cast<double>(h->params.resolution), 3);
     d3 = -log(c2); d1 = -log(c1 + c2) - d3; d2 = -2 * log((-log(c1 * exp(-0.5) + c2) - d3) / d1);
   }
-  if (h->params.search_method == NDTB_KDTREE) return set_error(h, NDTB_ERR_INVALID, "score-only passes are provided for DIRECT1 / DIRECT7 / DIRECT26");
-  const int probes = (h->params.search_method == NDTB_DIRECT1) ? 1 : (h->params.search_method == NDTB_DIRECT26 ? 26 : 7);
+  const int probes = (h->params.search_method == NDTB_DIRECT1) ? 1 : (h->params.search_method == NDTB_DIRECT26 ? 26 : (h->params.search_method == NDTB_KDTREE ? 27 : 7));
   score_kernel<<<blocks, 128, 0, h->stream>>>(h->d_source, n, h->grid.meta, h->grid.table, h->grid.c_mean, h->grid.c_icov, d_T, d1, d2, probes, d_out);
   h->launches += 1;
   std::vector<double> out(3 * static_cast<size_t>(blocks));

@@ -243,10 +243,9 @@ def test_direct26_and_kdtree_match_oracle(oracle, street, gold, search):
             assert abs(a[6] - b[6]) <= TOL * abs(b[6]) and np.abs(a[7:49] - b[7:49]).max() <= TOL * np.abs(b[13:49]).max()
         dt, da = pose_delta(rg["T"], ro["T"])
         assert dt <= 1e-4 and da <= 1e-5
-        if search == "DIRECT26":
-            tp, nv = h.calculate_scores(ro["T"])       # the score-only passes (ndt_omp_impl.hpp:1169-1281) with 26 cells
-            tpo, nvo = o.calculate_scores(ro["T"])
-            assert abs(tp - tpo) <= TOL * abs(tpo) and abs(nv - nvo) <= TOL * abs(nvo)
+        tp, nv = h.calculate_scores(ro["T"])           # the score-only passes (ndt_omp_impl.hpp:1169-1281) with the same neighbourhood
+        tpo, nvo = o.calculate_scores(ro["T"])
+        assert abs(tp - tpo) <= TOL * abs(tpo) and abs(nv - nvo) <= TOL * abs(nvo)
     # what stays outside: these two with line search or for the svn flavour
     h = ndtb.Handle(0)
     p = ndtb.Params(); h.L.ndtb_get_params(h.h, p)
