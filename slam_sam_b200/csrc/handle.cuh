@@ -70,6 +70,8 @@ struct ndtb_handle_s {
 
   // timing
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev_b[2] = {nullptr, nullptr};  // around the last voxel-map build
+  bool build_time_pending = false, align_time_pending = false;  // elapsed times are resolved by ndtb_get_timings, off the critical path
   float build_ms = 0, align_ms = 0, eval_ms_total = 0; int eval_launches = 0;
   uint64_t launches = 0;  // eval / stein / score kernels launched (builds are counted in grid.launches)
 

@@ -74,13 +74,13 @@ int upload_cloud(ndtb_handle_s* h, const float* xyz, size_t n, size_t stride_byt
 
 int rebuild_grid(ndtb_handle_s* h) {
   if (!h->d_target || h->n_target == 0) return NDTB_ERR_EMPTY;
-  cudaEventRecord(h->ev[0], h->stream);
+  cudaEventRecord(h->ev_b[0], h->stream);
   const int min_pts = (h->params.grid_flavour == NDTB_FLAVOUR_SVN) ? std::max(3, h->params.min_points_per_voxel) : h->params.min_points_per_voxel;
   const int rc = build_voxel_map(h->grid, h->d_target, h->n_target, h->params.resolution, min_pts, h->params.min_covar_eigvalue_mult,
                                  h->params.grid_flavour, h->params.is_dense, h->stream);
-  cudaEventRecord(h->ev[1], h->stream);
-  cudaEventSynchronize(h->ev[1]);
-  cudaEventElapsedTime(&h->build_ms, h->ev[0], h->ev[1]);
+  // the build has already told the host it is done (polled result slots): the event pair is only read by ndtb_get_timings
+  cudaEventRecord(h->ev_b[1], h->stream);
+  h->build_time_pending = true;
   h->built_resolution = h->params.resolution; h->built_min_pts = h->params.min_points_per_voxel;
   h->built_flavour = h->params.grid_flavour; h->built_eig = h->params.min_covar_eigvalue_mult;
   if (rc == NDTB_ERR_CUDA) return set_error(h, rc, "voxel map build failed");
@@ -340,6 +340,7 @@ int ndtb_create(int cuda_device, ndtb_handle* out) {
   ndtb_svn_default_params(&h->svn);
   if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return NDTB_ERR_CUDA; }
   for (int i = 0; i < 4; ++i) cudaEventCreate(&h->ev[i]);
+  for (int i = 0; i < 2; ++i) cudaEventCreate(&h->ev_b[i]);
   *out = h;
   return NDTB_OK;
 }
@@ -368,6 +369,7 @@ int ndtb_destroy(ndtb_handle h) {
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   cudaFree(h->d_svn_in); cudaFree(h->d_svn_out);
   for (int i = 0; i < 4; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+  for (int i = 0; i < 2; ++i) if (h->ev_b[i]) cudaEventDestroy(h->ev_b[i]);
   cudaStreamDestroy(h->stream);
   delete h;
   return NDTB_OK;
@@ -627,8 +629,7 @@ static int align_impl(ndtb_handle h, bool multigrid, const float guess[16], ndtb
   }
   session_end(h);
   cudaEventRecord(h->ev[1], h->stream);
-  cudaEventSynchronize(h->ev[1]);
-  cudaEventElapsedTime(&h->align_ms, h->ev[0], h->ev[1]);
+  h->align_time_pending = true;  // resolved by ndtb_get_timings: the caller does not wait for the resident kernel to leave
   if (h->session_eval_ns > 0) h->eval_ms_total = static_cast<float>(h->session_eval_ns * 1e-6);  // device-side (globaltimer) durations
   return resolve_eval_events(h);
 }
@@ -702,6 +703,14 @@ int ndtb_get_last_hits(ndtb_handle h, double* mean_hits_per_point, double* point
 
 int ndtb_get_timings(ndtb_handle h, float* build_ms, float* align_ms, float* eval_kernel_ms_total, int* eval_kernel_launches) {
   if (!h) return NDTB_ERR_INVALID;
+  if (h->build_time_pending) {
+    h->build_time_pending = false;
+    if (cudaEventSynchronize(h->ev_b[1]) == cudaSuccess) cudaEventElapsedTime(&h->build_ms, h->ev_b[0], h->ev_b[1]);
+  }
+  if (h->align_time_pending) {
+    h->align_time_pending = false;
+    if (cudaEventSynchronize(h->ev[1]) == cudaSuccess) cudaEventElapsedTime(&h->align_ms, h->ev[0], h->ev[1]);
+  }
   if (build_ms) *build_ms = h->build_ms;
   if (align_ms) *align_ms = h->align_ms;
   if (eval_kernel_ms_total) *eval_kernel_ms_total = h->eval_ms_total;

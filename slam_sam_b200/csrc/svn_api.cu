@@ -256,6 +256,7 @@ int ndtb_svn_align(ndtb_handle h, const double prior[16], const double* init_par
   cudaEventRecord(h->ev[1], h->stream);
   cudaEventSynchronize(h->ev[1]);
   cudaEventElapsedTime(&h->align_ms, h->ev[0], h->ev[1]);
+  h->align_time_pending = false;
   return NDTB_OK;
 }
 
