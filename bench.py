@@ -117,13 +117,14 @@ def ncu_traffic():
 
 
 def run_cpu(tgt, scans, guesses, steps, warmup, threads):
-    """The CPU restatement of the reference path, all host threads: build + align per step."""
+    """The CPU restatement of the reference path, all host threads: build + align per step.  The per-step results (pose,
+    iteration count, per-evaluation trace) are kept: bench's `parity` block holds the GPU path against them."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as O
 
     O.build()
     o = O.OracleNdt(resolution=RESOLUTION, max_iterations=35, trans_epsilon=0.01, step_size=0.1, num_threads=threads)
-    times, iters, build_t = [], [], []
+    times, iters, build_t, results = [], [], [], {}
     for i in range(warmup + steps):
         k = i % len(scans)
         t0 = time.perf_counter()
@@ -132,9 +133,40 @@ def run_cpu(tgt, scans, guesses, steps, warmup, threads):
         o.set_source(scans[k])
         r = o.align(guesses[k])
         t2 = time.perf_counter()
+        results[k] = r
         if i >= warmup:
             times.append(t2 - t0); build_t.append(t1 - t0); iters.append(r["iterations"])
-    return dict(total_s=float(np.sum(times)), mean_s=float(np.mean(times)), build_s=float(np.mean(build_t)), iterations=float(np.mean(iters)))
+    return dict(total_s=float(np.sum(times)), mean_s=float(np.mean(times)), build_s=float(np.mean(build_t)), iterations=float(np.mean(iters)),
+                results=results)
+
+
+def pose_delta(Ta, Tb):
+    d = np.linalg.inv(np.asarray(Ta, float)) @ np.asarray(Tb, float)
+    return float(np.linalg.norm(d[:3, 3])), float(np.arccos(np.clip((np.trace(d[:3, :3]) - 1) / 2, -1, 1)))
+
+
+def parity_block(h, tgt, scans, guesses, cpu_results):
+    """The bench line carries its own parity: the scans the CPU leg aligned are aligned again on the GPU (untimed) and every
+    evaluation of every Newton loop is held against the oracle's.  Bars of BASELINE.json north_star; a miss fails the run."""
+    assert h.set_target(tgt) == 0
+    it_equal, dt_max, dr_max, tr_max, n_eval = True, 0.0, 0.0, 0.0, 0
+    for k, ro in sorted(cpu_results.items()):
+        assert h.set_source(scans[k]) == 0
+        rg = h.align(guesses[k])
+        tg, to = h.trace(), ro["trace"]
+        it_equal = it_equal and rg["iterations"] == ro["iterations"] and rg["converged"] == ro["converged"] and tg.shape == to.shape
+        if tg.shape == to.shape:
+            for a, b in zip(tg, to):
+                tr_max = max(tr_max, abs(a[6] - b[6]) / abs(b[6]), float(np.abs(a[7:13] - b[7:13]).max() / np.abs(b[7:13]).max()),
+                             float(np.abs(a[13:49] - b[13:49]).max() / np.abs(b[13:49]).max()))
+                n_eval += 1
+        dt, dr = pose_delta(rg["T"], ro["T"])
+        dt_max, dr_max = max(dt_max, dt), max(dr_max, dr)
+    out = {"against": "oracle (CPU restatement of ndt_omp), same scans as cpu_baseline", "scans": len(cpu_results), "evaluations_compared": n_eval,
+           "iterations_equal": bool(it_equal), "max_dt_m": dt_max, "max_drot_rad": dr_max, "trace_rel_inf": tr_max,
+           "bars": {"trace_rel_inf": 1e-9, "max_dt_m": 1e-4, "max_drot_rad": 1e-5}}
+    out["ok"] = bool(it_equal and tr_max <= 1e-9 and dt_max <= 1e-4 and dr_max <= 1e-5)
+    return out
 
 
 def run_gpu(args, rank, world, local_rank):
@@ -144,9 +176,6 @@ def run_gpu(args, rank, world, local_rank):
     from slam_sam_b200 import distributed as D
     from slam_sam_b200 import ndtb, synth
 
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
     tgt, scans, guesses, truths = make_workload(rank)
     h = ndtb.Handle(local_rank)  # no CPU fallback: raises if the CUDA library / device is missing
     h.set_params(resolution=RESOLUTION, max_iterations=35, trans_epsilon=0.01, step_size=0.1, search_method=ndtb.DIRECT7)
@@ -255,6 +284,7 @@ def run_gpu(args, rank, world, local_rank):
         for i in range(steps):
             with torch.cuda.stream(stream):
                 flush.zero_()          # L2 flush between timed iterations, outside the event pair
+            stream.synchronize()       # the flush has finished before the opening event: no host work of the step hides behind it
             e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
             e0.record(stream)
             r = step(warmup + i, resident)
@@ -303,8 +333,6 @@ def run_gpu(args, rank, world, local_rank):
     if world > 1:
         dist.barrier()
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
         return None
     K = args.steps
     value = world * K / (total_ms * 1e-3)
@@ -356,9 +384,22 @@ def run_gpu(args, rank, world, local_rank):
                      "kernel_us_back_to_back": b2b_us, "frac_back_to_back": b_eval / (b2b_us * 1e-6) / 1e9 / peak},
         "clocks": clk,
     }
+    # the voxel-map build is the other half of the step: its own roofline entry (B_build = 2*16*N_t + 64*V)
+    l0 = h.launch_count()
+    assert h.set_target_device(d_tgt.data_ptr(), N_MAP) == 0
+    build_launches = h.launch_count() - l0
+    n_leaves = int(len(h.voxels()["idx"]))
+    b_build = 2 * 16 * N_MAP + 64 * n_leaves
+    build_s = st["build_ms"] / K * 1e-3
+    line["roofline_build"] = {"kernel": f"voxel-map build ({build_launches} launches)", "bound": "hbm", "achieved": b_build / build_s / 1e9, "peak": peak,
+                              "unit": "GB/s", "frac": b_build / build_s / 1e9 / peak, "algorithmic_bytes": b_build, "leaves": n_leaves,
+                              "build_us": build_s * 1e6, "traffic": None,
+                              "note": "CUDA events on the library's stream around the whole build (all launches + the host read-backs between them)"}
     if not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         c = run_cpu(tgt, scans, guesses, steps=2, warmup=1, threads=threads)
+        line["parity"] = parity_block(h, tgt, scans, guesses, c["results"])
+        assert line["parity"]["ok"], f"parity bars missed: {line['parity']}"
         line["cpu_baseline"] = {"value": 1.0 / c["mean_s"], "unit": "scans/s", "cores": threads, "kind": "port",
                                 "sample": f"2 steps (after 1 warm-up) of the same workload: 1M-pt map build ({c['build_s']*1e3:.0f} ms, serial like the "
                                           f"reference) + align ({c['iterations']:.0f} iterations) with {threads} OpenMP threads"}
@@ -376,50 +417,64 @@ def run_gpu(args, rank, world, local_rank):
             fr = od.L.orc_lidar_decode(od.h, pk_np.ctypes.data, pk_np.shape[0], pk_np.shape[1], pk_np.shape[1])
         line["e2e_packets"]["decode_cpu_port_us"] = (time.perf_counter() - t0) / reps * 1e6
         line["e2e_packets"]["decode_cpu_port_what"] = "oracle/ouster_decode.hpp (restatement of LidarCallback::DecodePacketRng19), 1 thread, same 65 packets"
-    if world > 1:
-        dist.destroy_process_group()
     return line
 
 
-def run_gpu_svn(args, rank, world, local_rank):
-    """configs[2]: SVN-NDT, K = 100 particles, 131072-pt scan pair; particles sharded over the ranks (strong scaling),
-    one all-reduce of K x 43 doubles per iteration.  One step = one full align(source, prior)."""
-    import torch
-    import torch.distributed as dist
+def svn_initial_particles(K):
+    """K particles around the identity prior, seed 7, sigmas of svn_ndt_impl.hpp:710 (translation 0.05 m, rotation 0.01 rad)."""
+    from slam_sam_b200 import synth
 
-    from slam_sam_b200 import distributed as D
-    from slam_sam_b200 import ndtb, synth
+    rng = np.random.Generator(np.random.PCG64(7))
+    return np.stack([synth.pose_matrix(rng.normal(0, 0.05, 3), rng.normal(0, 0.01, 3)) for _ in range(K)])
 
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
-    K = 100
+
+def make_svn_workload(n_scans):
+    """configs[2]: one target scan + `n_scans` source scans of the same place (131 072 points each)."""
+    from slam_sam_b200 import synth
+
     scene = synth.Scene()
     A = synth.trajectory_pose(40.0)
     tgt = synth.ouster_scan(scene, A, seed=1)
     pool = []
-    for i in range(4):
+    for i in range(n_scans):
         B = A @ synth.pose_matrix((0.5 - 0.1 * i, 0.1, 0.02), np.deg2rad((0.5, 0.3, 2.0 - 0.3 * i)))
         pool.append((synth.ouster_scan(scene, B, seed=2 + i), np.linalg.inv(A) @ B))
+    return tgt, pool
+
+
+def run_gpu_svn(args, rank, world, local_rank, sub=False):
+    """configs[2]: SVN-NDT, K = 100 particles, 131072-pt scan pair; particles sharded over the ranks (strong scaling).  One step =
+    one full align(source, prior).  `sub`: a short run whose summary becomes the "svn" object of the default bench line."""
+    import torch
+    import torch.distributed as dist
+
+    from slam_sam_b200 import distributed as D
+    from slam_sam_b200 import ndtb
+
+    K = 100
+    tgt, pool = make_svn_workload(2 if sub else 4)
     h = ndtb.Handle(local_rank)
     h.set_params(grid_flavour=ndtb.FLAVOUR_SVN, resolution=RESOLUTION, min_points_per_voxel=3, search_method=ndtb.DIRECT7)
     h.set_svn_params(particle_count=K, max_iterations=50, kernel_bandwidth=1.0, step_size=1.0, stop_threshold=1e-4, use_gauss_newton=1)
     assert h.set_target(tgt) == 0
     p_scans = [torch.from_numpy(s).pin_memory() for s, _ in pool]
     d_scans = [torch.from_numpy(s).cuda() for s, _ in pool]
-    rng = np.random.Generator(np.random.PCG64(7))
     prior = np.eye(4)
-    P0 = np.stack([prior @ synth.pose_matrix(rng.normal(0, 0.05, 3), rng.normal(0, 0.01, 3)) for _ in range(K)])  # sigmas of svn_ndt_impl.hpp:710
+    P0 = svn_initial_particles(K)
     stream = torch.cuda.ExternalStream(h.stream_ptr(), device=local_rank)
+    comm = D.SvnComm(h, rank, world, local_rank) if world > 1 else None
 
-    def step(i, resident):
-        k = i % len(pool)
+    def align(resident, k):
         if resident:
             assert h.set_source_device(d_scans[k].data_ptr(), N_SCAN) == 0
         else:
             assert h.L.ndtb_set_source(h.h, p_scans[k].data_ptr(), N_SCAN, 16) == 0
-        mean, P, it, conv = D.svn_align(h, prior, P0, rank, world, 50, 1e-4, local_rank)
-        return mean, it, conv, float(np.abs(mean[:3, 3] - pool[k][1][:3, 3]).max())
+        return h.svn_align(prior, P0) if comm is None else comm.align(prior, P0)
+
+    def step(i, resident):
+        k = i % len(pool)
+        r = align(resident, k)
+        return r, float(np.abs(r["final_pose"][:3, 3] - pool[k][1][:3, 3]).max())
 
     def timed(resident, steps, warmup):
         for i in range(warmup):
@@ -427,50 +482,79 @@ def run_gpu_svn(args, rank, world, local_rank):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
-        l0 = h.launch_count(); t0 = h.timings()
+        l0 = h.launch_count()
         e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-        iters = 0; err = 0.0
+        iters = 0; err = 0.0; eval_ms = 0.0; stein_ms = 0.0; xchg_ms = 0.0
         e0.record(stream)
         for i in range(steps):
-            _, it, conv, er = step(warmup + i, resident)
-            iters += it; err = max(err, er)
+            r, er = step(warmup + i, resident)
+            iters += r["iterations"]; err = max(err, er)
+            t = h.svn_timings()
+            eval_ms += t["eval_ms"]; stein_ms += t["stein_ms"]; xchg_ms += t["exchange_wait_ms"]
         e1.record(stream)
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
-        t1 = h.timings()
-        return e0.elapsed_time(e1), dict(iters=iters, err=err, launches=h.launch_count() - l0, eval_ms=t1["eval_ms_total"] - t0["eval_ms_total"],
+        return e0.elapsed_time(e1), dict(iters=iters, err=err, launches=h.launch_count() - l0, eval_ms=eval_ms, stein_ms=stein_ms, xchg_ms=xchg_ms,
                                          hits=h.last_hits()[0])
 
-    clocks = ClockSampler(local_rank)
-    clocks.start()
-    steps = max(1, min(args.steps, 10))
-    total_ms, st = timed(True, steps, min(args.warmup, 3))
+    clocks = None
+    if not sub:
+        clocks = ClockSampler(local_rank); clocks.start()
+    steps = 3 if sub else max(1, min(args.steps, 10))
+    total_ms, st = timed(True, steps, 1 if sub else min(args.warmup, 3))
     e2e_ms, st2 = timed(False, steps, 1)
-    clk = clocks.stop()
+    clk = clocks.stop() if clocks else None
     total_ms = D.max_over_ranks(total_ms, local_rank); e2e_ms = D.max_over_ranks(e2e_ms, local_rank)
     launches = int(D.sum_over_ranks(st["launches"], local_rank))
+    # the sharded result must be the single-GPU result, bit for bit (same records, same Stein update on every rank)
+    equal = None
     if world > 1:
-        dist.barrier(); dist.destroy_process_group()
+        r_sh = align(True, 0)
+        if rank == 0:
+            h1 = ndtb.Handle(local_rank)
+            h1.set_params(grid_flavour=ndtb.FLAVOUR_SVN, resolution=RESOLUTION, min_points_per_voxel=3, search_method=ndtb.DIRECT7)
+            h1.set_svn_params(particle_count=K, max_iterations=50, kernel_bandwidth=1.0, step_size=1.0, stop_threshold=1e-4, use_gauss_newton=1)
+            assert h1.set_target(tgt) == 0 and h1.set_source_device(d_scans[0].data_ptr(), N_SCAN) == 0
+            r_1 = h1.svn_align(prior, P0)
+            equal = bool(r_sh["iterations"] == r_1["iterations"] and np.array_equal(r_sh["final_pose"], r_1["final_pose"])
+                         and np.array_equal(r_sh["particles"], r_1["particles"]) and np.array_equal(r_sh["final_covariance"], r_1["final_covariance"]))
+            h1.close()
+        dist.barrier()
+    if comm is not None:
+        comm.close()
+    h.close()
     if rank != 0:
         return None
+    assert equal is not False, "sharded SVN align differs from the single-GPU align"
     k_local = len(range(0, K, world))
-    b_eval = k_local * N_SCAN * (16 + 8 * 7 + 96 * st["hits"])   # FP64 records (mean 3 + icov 9 doubles) in the svn kernel
+    hb = st["hits"]
+    b64 = k_local * N_SCAN * (16 + 8 * 7 + 64 * hb)   # K * B_eval with the 64-byte record
+    b96 = k_local * N_SCAN * (16 + 8 * 7 + 96 * hb)   # what the svn kernel reads: FP64 mean (24 B) + FP64 inverse covariance (72 B)
     t_eval = st["eval_ms"] / max(st["iters"], 1) * 1e-3
     peak, peak_src = measured_peak()
+    roof = {"kernel": "eval_kernel<svn,DIRECT7,GN>", "bound": "hbm", "achieved": b64 / t_eval / 1e9, "peak": peak, "unit": "GB/s",
+            "frac": b64 / t_eval / 1e9 / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": b64,
+            "frac_with_96_byte_fp64_records": b96 / t_eval / 1e9 / peak, "mean_hits_per_point": hb, "kernel_us": t_eval * 1e6,
+            "note": "frac uses SURVEY 8(d)'s formula (64-byte record per hit); the svn kernel actually gathers 96 bytes of FP64 mean + inverse covariance per hit"}
+    summary = {"value": steps / (total_ms * 1e-3), "unit": "aligns/s", "ms_per_step": total_ms / steps, "steps": steps, "scaling": "strong",
+               "particles": K, "particles_on_rank0": k_local, "iterations": st["iters"] / steps,
+               "eval_us_per_iter": st["eval_ms"] / max(st["iters"], 1) * 1e3, "stein_us_per_iter": st["stein_ms"] / max(st["iters"], 1) * 1e3,
+               "allreduce_us_per_iter": st["xchg_ms"] / max(st["iters"], 1) * 1e3,
+               "exchange": "none (one GPU)" if world == 1 else "records peer-written over NVLink by the eval kernel's last block; allreduce_us_per_iter = time the Stein kernel waited for peer records",
+               "e2e_value": steps / (e2e_ms * 1e-3), "max_abs_translation_error_m": st["err"], "sharded_equals_single_gpu": equal,
+               "roofline_frac": roof["frac"], "gpu_launches": launches}
+    if sub:
+        return summary
     return {"metric": "NDT align scans/sec @131k pts (1/2/4/8 B200) + % gather-BW roofline vs CPU OMP", "value": steps / (total_ms * 1e-3), "unit": "scans/s",
             "n_gpus": world, "steps": steps, "warmup": min(args.warmup, 3), "ms_per_step": total_ms / steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64 Mahalanobis/exp, f32 products, f64 accumulate", "data": "synthetic",
             "config": {"workload": "configs[2]: SVN-NDT align, K=100 particles, 131072-pt OS1-128-shaped scan pair, 1.0 m voxels, Gauss-Newton Hessian, per step",
-                       "particles": K, "parallelism": f"particles sharded x{world}, one all-reduce of K x 43 f64 per iteration", "svn_iterations_per_align": st["iters"] / steps,
+                       "particles": K, "parallelism": f"particles sharded x{world}, per-particle records exchanged once per iteration", "svn_iterations_per_align": st["iters"] / steps,
                        "max_abs_translation_error_m": st["err"], "l2": "inputs of one align (K x 131072 point evaluations per iteration) exceed nothing: L2-resident by design"},
-            "e2e": {"value": steps / (e2e_ms * 1e-3), "unit": "scans/s", "h2d_bytes_per_step": 16 * N_SCAN, "d2h_bytes_per_step": int(43 * 8 * k_local * st2["iters"] / steps),
+            "e2e": {"value": steps / (e2e_ms * 1e-3), "unit": "scans/s", "h2d_bytes_per_step": 16 * N_SCAN + 16 * 8 * K, "d2h_bytes_per_step": 16 * 8 * K + 53 * 8,
                     "ms_per_step": e2e_ms / steps},
-            "gpu_launches": launches,
-            "roofline": {"kernel": "eval_kernel<svn,DIRECT7,GN>", "bound": "hbm", "achieved": b_eval / t_eval / 1e9, "peak": peak, "unit": "GB/s",
-                         "frac": b_eval / t_eval / 1e9 / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": b_eval,
-                         "mean_hits_per_point": st["hits"], "kernel_us": t_eval * 1e6},
-            "clocks": clk}
+            "gpu_launches": launches, "svn": summary, "roofline": roof, "clocks": clk}
 
 
 def run_gpu_replay(args, rank, world, local_rank):

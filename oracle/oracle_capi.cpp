@@ -28,7 +28,7 @@ void orc_euler_angles_012_f(const float* T, float* e) { euler_angles_012_f(T, e)
 // ------------------------------------------------------------------ voxel grid (both flavours)
 void* orc_grid_create(int flavour, float leaf, int min_pts, double eig_mult) {
   VoxelGrid* g = new VoxelGrid();
-  g->flavour = flavour; g->set_leaf_size(leaf); g->min_points_per_voxel = min_pts; g->min_covar_eigvalue_mult = eig_mult;
+  g->flavour = flavour; g->set_leaf_size(leaf); g->min_points_per_voxel = min_pts < 3 ? 3 : min_pts /* setMinPointPerVoxel, voxel_grid_covariance_omp.h:214-224 */; g->min_covar_eigvalue_mult = eig_mult;
   return g;
 }
 void orc_grid_destroy(void* h) { delete static_cast<VoxelGrid*>(h); }
@@ -74,7 +74,7 @@ void orc_ndt_set_params(void* h, float resolution, double step_size, double tran
   n->params.resolution = resolution; n->params.step_size = step_size; n->params.trans_epsilon = trans_epsilon;
   n->params.max_iterations = max_iterations; n->params.search_method = search_method; n->params.num_threads = num_threads;
   n->params.regularization_scale_factor = reg_scale; n->params.use_line_search = use_line_search != 0;
-  n->outlier_ratio = outlier_ratio; n->grid.min_points_per_voxel = min_pts; n->grid.min_covar_eigvalue_mult = eig_mult;
+  n->outlier_ratio = outlier_ratio; n->grid.min_points_per_voxel = min_pts < 3 ? 3 : min_pts /* voxel_grid_covariance_omp.h:214-224 */; n->grid.min_covar_eigvalue_mult = eig_mult;
   n->update_gauss();
 }
 void orc_ndt_gauss(void* h, double* d) { PclompNdt* n = static_cast<PclompNdt*>(h); d[0] = n->gauss_d1; d[1] = n->gauss_d2; d[2] = n->gauss_d3; }

@@ -14,7 +14,7 @@ void orc_mg_set_params(void* h, float resolution, double step_size, double trans
   n->params.resolution = resolution; n->params.step_size = step_size; n->params.trans_epsilon = trans_epsilon;
   n->params.max_iterations = max_iterations; n->params.search_method = KDTREE; n->params.num_threads = num_threads;
   n->params.regularization_scale_factor = reg_scale; n->params.use_line_search = use_line_search != 0;
-  n->outlier_ratio = outlier_ratio; n->min_points_per_voxel = min_pts; n->min_covar_eigvalue_mult = eig_mult;
+  n->outlier_ratio = outlier_ratio; n->min_points_per_voxel = min_pts < 3 ? 3 : min_pts /* multi_voxel_grid_covariance_omp.h setMinPointPerVoxel */; n->min_covar_eigvalue_mult = eig_mult;
   n->update_gauss();
 }
 int orc_mg_add_target(void* h, const float* xyz, size_t n, size_t stride_floats, int is_dense, const char* id) {

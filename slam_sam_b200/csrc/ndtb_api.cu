@@ -34,6 +34,9 @@ int ensure_eval_buffers(ndtb_handle_s* h, int particles, int n_points) {
     cudaFree(b.d_states); cudaFree(b.d_partials); cudaFree(b.d_results); cudaFree(b.d_tickets);
     if (h->h_states) cudaFreeHost(h->h_states);
     if (h->h_results) cudaFreeHost(h->h_results);
+    // nothing dangles if an allocation below fails: the capacity is only restored once all of them succeeded
+    b.d_states = nullptr; b.d_partials = nullptr; b.d_results = nullptr; b.d_tickets = nullptr; h->h_states = nullptr; h->h_results = nullptr;
+    b.max_particles = 0; b.max_blocks = 0;
     CKH(cudaMalloc(&b.d_states, sizeof(EvalState) * np));
     CKH(cudaMalloc(&b.d_partials, sizeof(double) * RED_N * static_cast<size_t>(np) * nb));
     CKH(cudaMalloc(&b.d_results, sizeof(double) * RED_N * np));
@@ -53,6 +56,7 @@ int upload_cloud(ndtb_handle_s* h, const float* xyz, size_t n, size_t stride_byt
   if (n > *alloc) {
     cudaFree(*d_buf);
     *d_buf = nullptr;
+    *alloc = 0;
     const size_t cap = n + n / 8 + 256;
     CKH(cudaMalloc(d_buf, cap * sizeof(float4)));
     *alloc = cap;
@@ -75,7 +79,8 @@ int upload_cloud(ndtb_handle_s* h, const float* xyz, size_t n, size_t stride_byt
 int rebuild_grid(ndtb_handle_s* h) {
   if (!h->d_target || h->n_target == 0) return NDTB_ERR_EMPTY;
   cudaEventRecord(h->ev_b[0], h->stream);
-  const int min_pts = (h->params.grid_flavour == NDTB_FLAVOUR_SVN) ? std::max(3, h->params.min_points_per_voxel) : h->params.min_points_per_voxel;
+  // setMinPointPerVoxel forces values below 3 to 3 in both grids (voxel_grid_covariance_omp.h:214-224, voxel_grid_covariance.h:176-184)
+  const int min_pts = std::max(3, h->params.min_points_per_voxel);
   const int rc = build_voxel_map(h->grid, h->d_target, h->n_target, h->params.resolution, min_pts, h->params.min_covar_eigvalue_mult,
                                  h->params.grid_flavour, h->params.is_dense, h->stream);
   // the build has already told the host it is done (polled result slots): the event pair is only read by ndtb_get_timings
@@ -392,6 +397,10 @@ int ndtb_set_params(ndtb_handle h, const ndtb_params* p) {
   if (p->grid_flavour != NDTB_FLAVOUR_PCLOMP && p->grid_flavour != NDTB_FLAVOUR_SVN) return set_error(h, NDTB_ERR_INVALID, "bad grid_flavour");
   cudaSetDevice(h->device);
   h->params = *p;
+  // setMinPointPerVoxel: values below 3 become 3 in every grid flavour (voxel_grid_covariance_omp.h:214-224,
+  // voxel_grid_covariance.h:176-184, multi_voxel_grid_covariance_omp.h), so getMinPointPerVoxel / ndtb_get_params report 3
+  if (h->params.min_points_per_voxel < 3) h->params.min_points_per_voxel = 3;
+  p = &h->params;
   // setResolution rebuilds only if the value changed and a target is set (ndt_omp.h:135-142)
   const bool changed = h->grid.built && (h->built_resolution != p->resolution || h->built_min_pts != p->min_points_per_voxel ||
                                          h->built_flavour != p->grid_flavour || h->built_eig != p->min_covar_eigvalue_mult);
@@ -617,6 +626,9 @@ static int align_impl(ndtb_handle h, bool multigrid, const float guess[16], ndtb
   res->converged = converged ? 1 : 0;
   res->transformation_array_len = std::min(n_arr, capacity > 0 ? capacity : 0);
   res->evaluations = h->eval_launches;
+  // the resident kernel is told to leave BEFORE anything else is queued on the stream: a copy queued behind it would
+  // only complete once the kernel's idle time-out fires
+  session_end(h);
   if (out_xyz) {
     // `output` of pcl::Registration::align: the source transformed by the final transformation
     // (host loop, N points -- off the timed path; callers that do not need it pass NULL).
@@ -627,7 +639,6 @@ static int align_impl(ndtb_handle h, bool multigrid, const float guess[16], ndtb
       for (int r = 0; r < 3; ++r)
         out_xyz[3 * i + r] = final_T[4 * r] * tmp[i].x + (final_T[4 * r + 1] * tmp[i].y + (final_T[4 * r + 2] * tmp[i].z + final_T[4 * r + 3]));
   }
-  session_end(h);
   cudaEventRecord(h->ev[1], h->stream);
   h->align_time_pending = true;  // resolved by ndtb_get_timings: the caller does not wait for the resident kernel to leave
   if (h->session_eval_ns > 0) h->eval_ms_total = static_cast<float>(h->session_eval_ns * 1e-6);  // device-side (globaltimer) durations

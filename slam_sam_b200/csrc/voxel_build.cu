@@ -24,8 +24,11 @@ static int ensure_capacity(DeviceGrid& g, size_t n, bool voxel_arrays) {
     std::memset(const_cast<unsigned long long*>(g.h_slots), 0, 32 * sizeof(unsigned long long));
   }
   if (n > g.pts_alloc) {
-    for (int i = 0; i < 2; ++i) { cudaFree(g.keys[i]); cudaFree(g.vals[i]); }
+    for (int i = 0; i < 2; ++i) { cudaFree(g.keys[i]); cudaFree(g.vals[i]); g.keys[i] = nullptr; g.vals[i] = nullptr; }
     cudaFree(g.seg_start); cudaFree(g.block_counts); cudaFree(g.hist); cudaFree(g.sorted_xyz); cudaFree(g.c_key);
+    // nothing dangles if an allocation below fails: the capacity is only set once all of them succeeded
+    g.seg_start = nullptr; g.block_counts = nullptr; g.hist = nullptr; g.sorted_xyz = nullptr; g.c_key = nullptr;
+    g.pts_alloc = 0;
     const size_t cap = n + n / 8 + 1024;
     CK(cudaMalloc(&g.sorted_xyz, cap * 3 * sizeof(double)));
     CK(cudaMalloc(&g.c_key, cap * 4));  // leaf keys, written with the segments
@@ -40,6 +43,8 @@ static int ensure_capacity(DeviceGrid& g, size_t n, bool voxel_arrays) {
     const size_t cap = n + n / 8 + 1024;
     cudaFree(g.recs); cudaFree(g.c_n); cudaFree(g.c_mean); cudaFree(g.c_cov); cudaFree(g.c_icov);
     cudaFree(g.c_evecs); cudaFree(g.c_evals); cudaFree(g.vox_sums);
+    g.recs = nullptr; g.c_n = nullptr; g.c_mean = g.c_cov = g.c_icov = g.c_evecs = g.c_evals = nullptr; g.vox_sums = nullptr;
+    g.vox_alloc = 0;
     CK(cudaMalloc(&g.vox_sums, cap * 72));
     CK(cudaMalloc(&g.recs, cap * sizeof(VoxRec)));
     CK(cudaMalloc(&g.c_n, cap * 4));

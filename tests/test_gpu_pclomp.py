@@ -31,6 +31,7 @@ def assert_grid_equal(a, b, exact_stats=True):
         assert np.array_equal(a["mean"][valid], b["mean"][valid])
         assert np.array_equal(a["icov"], b["icov"]) and np.array_equal(a["cov"], b["cov"])
         assert np.array_equal(a["evals"], b["evals"])
+        assert np.array_equal(a["evecs"], b["evecs"])      # Leaf::evecs_ (exported to ndt_ellipsoids.txt, include/pipeline.hpp:163-222): same Jacobi sweeps, same signs
 
 
 def pose_delta(Ta, Tb):
