@@ -557,7 +557,7 @@ def run_gpu_svn(args, rank, world, local_rank, sub=False):
             "gpu_launches": launches, "svn": summary, "roofline": roof, "clocks": clk}
 
 
-def run_gpu_replay(args, rank, world, local_rank):
+def run_gpu_replay(args, rank, world, local_rank, sub=False):
     """configs[3]: replay batch.  Every rank holds the (replicated, built once) 1M-pt map and aligns its own shard of the scans
     through ndtb_align_batch from pinned host buffers; no data-path collective (weak scaling).  One step = one batch of 32 scans."""
     import torch
@@ -566,9 +566,6 @@ def run_gpu_replay(args, rank, world, local_rank):
     from slam_sam_b200 import distributed as D
     from slam_sam_b200 import ndtb
 
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
     tgt, scans, guesses, truths = make_workload(rank)
     B = 32
     h = ndtb.Handle(local_rank)
@@ -605,19 +602,27 @@ def run_gpu_replay(args, rank, world, local_rank):
             dist.barrier()
         return sum(a.elapsed_time(b) for a, b in ev), dict(evals=evals, err=err, launches=h.launch_count() - l0)
 
-    clocks = ClockSampler(local_rank)
-    clocks.start()
-    steps = max(1, min(args.steps, 10))
+    clocks = None
+    if not sub:
+        clocks = ClockSampler(local_rank); clocks.start()
+    steps = 3 if sub else max(1, min(args.steps, 10))
     ms, st = timed(steps, 3, 1)
     ms_serial, st_s = timed(steps, 1, 0)
-    clk = clocks.stop()
+    clk = clocks.stop() if clocks else None
     ms = D.max_over_ranks(ms, local_rank); ms_serial = D.max_over_ranks(ms_serial, local_rank)
     launches = int(D.sum_over_ranks(st["launches"], local_rank))
     if world > 1:
-        dist.barrier(); dist.destroy_process_group()
+        dist.barrier()
+    hbar = h.last_hits()[0]
+    h.close()
     if rank != 0:
         return None
-    hbar = h.last_hits()[0]
+    if sub:
+        return {"value": world * steps * B / (ms * 1e-3), "unit": "scans/s", "ms_per_step": ms / steps, "steps": steps, "scaling": "weak",
+                "scans_per_step_per_rank": B, "evaluations_per_scan": st["evals"] / (steps * B), "serial_scans_per_s": world * steps * B / (ms_serial * 1e-3),
+                "wall_us_per_evaluation": ms * 1e3 / st["evals"], "max_abs_translation_error_m": st["err"], "gpu_launches": launches,
+                "what": "configs[3]: 32 scans per step and rank through ndtb_align_batch from pinned host buffers against the replicated 1M-pt map "
+                        "(built once), scans sharded by rank, no collective"}
     b_eval = N_SCAN * (16 + 8 * 7 + 64 * hbar)
     t_eval = ms * 1e-3 / st["evals"]        # wall time per evaluation with two alignments in flight: the GPU is never idle
     peak, peak_src = measured_peak()
@@ -646,12 +651,12 @@ def run_reference(args, rank):
         return None
     tgt, scans, guesses, truths = make_workload(0)
     threads = os.cpu_count() or 1
-    steps = min(args.steps, 8)   # bounded sample: ~1-2 s of CPU work per step
-    c = run_cpu(tgt, scans, guesses, steps=steps, warmup=min(args.warmup, 1), threads=threads)
+    steps, warmup = max(1, args.steps), max(0, args.warmup)   # ~0.4 s of CPU work per step: 20 + 5 steps end within ~15 s
+    c = run_cpu(tgt, scans, guesses, steps=steps, warmup=warmup, threads=threads)
     v = 1.0 / c["mean_s"]
     sample = f"{steps} steps of the same workload (1M-pt map build + 131072-pt align), {threads} OpenMP threads, oracle port of ndt_omp"
     return {"impl": "reference", "metric": "NDT align scans/sec @131k pts (1/2/4/8 B200) + % gather-BW roofline vs CPU OMP", "value": v, "unit": "scans/s",
-            "n_gpus": args.gpus, "steps": steps, "warmup": min(args.warmup, 1), "ms_per_step": c["mean_s"] * 1e3, "higher_is_better": True,
+            "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": c["mean_s"] * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32 pair maths, f64 accumulate", "data": "synthetic",
             "config": {"workload": "configs[1]: voxel-map build of a 1M-pt synthetic map + DIRECT7 NDT align of one 131072-pt OS1-128-shaped scan, "
                                    "1.0 m voxels, per step", "build_ms": c["build_s"] * 1e3, "newton_iterations": c["iterations"]},
@@ -669,9 +674,6 @@ def run_gpu_multigrid(args, rank, world, local_rank):
     from slam_sam_b200 import distributed as D
     from slam_sam_b200 import ndtb
 
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
     tgt, scans, guesses, truths = make_workload(rank)
     qx = np.quantile(tgt[:, 0], np.linspace(0, 1, 5)); qy = np.quantile(tgt[:, 1], np.linspace(0, 1, 5))
     qx[-1] += 1; qy[-1] += 1
@@ -733,7 +735,7 @@ def run_gpu_multigrid(args, rank, world, local_rank):
     ms = D.max_over_ranks(ms, local_rank)
     launches = int(D.sum_over_ranks(launches, local_rank))
     if world > 1:
-        dist.barrier(); dist.destroy_process_group()
+        dist.barrier()
     if rank != 0:
         return None
     hbar = h.last_hits()[0]
@@ -770,6 +772,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sub-workloads", action="store_true", help="skip the replay / svn sub-objects of the default line")
     ap.add_argument("--workload", default="map_align", choices=["map_align", "svn", "replay", "multigrid"])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -778,14 +781,38 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         line = run_reference(args, rank)
-    elif args.workload == "svn":
+        if line is not None:
+            print(json.dumps(line), flush=True)
+        return
+    import torch
+    import torch.distributed as dist
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
+    if args.workload == "svn":
         line = run_gpu_svn(args, rank, world, local_rank)
     elif args.workload == "replay":
         line = run_gpu_replay(args, rank, world, local_rank)
     elif args.workload == "multigrid":
         line = run_gpu_multigrid(args, rank, world, local_rank)
     else:
+        # the headline line is configs[1] (replicas); the two workloads north_star shards across GPUs ride along as sub-objects,
+        # measured with a bounded step count in the same process group: configs[3] replay (scans sharded, weak scaling) and
+        # configs[2] SVN (particles sharded, strong scaling, records exchanged by the kernels over NVLink)
         line = run_gpu(args, rank, world, local_rank)
+        if not args.no_sub_workloads:
+            torch.cuda.empty_cache()
+            replay = run_gpu_replay(args, rank, world, local_rank, sub=True)
+            torch.cuda.empty_cache()
+            svn = run_gpu_svn(args, rank, world, local_rank, sub=True)
+            if line is not None:
+                line["replay"] = replay
+                line["svn"] = svn
+                line["gpu_launches"] += replay["gpu_launches"] + svn["gpu_launches"]
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
     if line is not None:
         print(json.dumps(line), flush=True)
 

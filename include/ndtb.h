@@ -129,12 +129,28 @@ int ndtb_get_trace(ndtb_handle h, double* trace, int capacity, int* count);
  * (ndt_omp_impl.hpp:1169-1281): FP64 score-only pass over a cloud transformed by T16. */
 int ndtb_calculate_scores(ndtb_handle h, const float T16[16], double* transformation_probability, double* nvtl);
 
+/* calculateScore (ndt_omp_impl.hpp:1083-1167), from cleared maps (cleanScores, ndt_omp.h:236-240): *score = sum / N;
+ * getScoreMap() -> voxel_idx[] / voxel_mean_score[] (ascending key = getLeafIndex(cell mean), value = the voxel's mean score over the
+ * pairs that hit it); getEmptyVoxels() -> empty_ijk[3 * i] = floor(x / resolution) of the points that found no neighbour, in the
+ * set's EigenCmp order (ndt_omp.h:57-65).  *n_voxels / *n_empty report the full counts; at most `capacity` entries are written.
+ * nomap_points_num_ is keyed by an uninitialised variable in the reference (:1124-1127) and is not provided. */
+int ndtb_calculate_score(ndtb_handle h, const float T16[16], double* score, size_t map_capacity, int64_t* voxel_idx, double* voxel_mean_score,
+                         size_t* n_voxels, size_t empty_capacity, int32_t* empty_ijk, size_t* n_empty);
+
 /* ---- voxel map inspection (getTargetCells().getLeaves(), include/pipeline.hpp:163-222) -------- */
 int ndtb_get_voxel_count(ndtb_handle h, size_t* count, int min_b[3], int max_b[3], int div_b[3]);
 /* Arrays sized by count, ascending linear index: idx[V] nr_points[V] mean[3V] cov[9V] icov[9V]
  * evecs[9V] evals[3V]; any pointer may be NULL. */
 int ndtb_get_voxels(ndtb_handle h, int64_t* idx, int32_t* nr_points, double* mean, double* cov, double* icov, double* evecs,
                     double* evals);
+/* extractNdtData + writeNdtDataToFiles (include/pipeline.hpp:163-274), the NDT map export of the reference's pipelines:
+ * `ellipsoid_filename` (ndt_ellipsoids.txt) one line per exported leaf: mean(3) evecs(9, row-major) evals(3) point_count;
+ * `voxel_filename` (ndt_voxels.txt): getLeafCenter(index)(3) resolution; std::fixed, 8 decimals, ascending leaf index.  A leaf is
+ * exported when `getPointCount() >= min_points` in the reference's int-vs-size_t comparison (:194), so leaves flagged -1 are written
+ * too, with the count static_cast<size_t>(-1).  `points_filename` (optional, may be NULL): the caller's map cloud as
+ * "x y z intensity" (intensity = fifth float of a >= 20-byte record, else 0).  Host code over the exported voxel table. */
+int ndtb_write_ndt_files(ndtb_handle h, const char* ellipsoid_filename, const char* voxel_filename, const char* points_filename,
+                         const float* points, size_t n_points, size_t stride_bytes);
 /* Mean hits per source point of the last derivative evaluation (roofline h-bar). */
 int ndtb_get_last_hits(ndtb_handle h, double* mean_hits_per_point, double* points_with_neighbours);
 
@@ -151,11 +167,39 @@ int ndtb_svn_step(ndtb_handle h, int K, double* poses, double* scores, double* g
 /* align(source, prior) (svn_ndt_impl.hpp:675-964).  init_particles: K x 16 doubles or NULL (then
  * drawn from `seed` with the reference's sigmas, :710 -- the reference seeds from the clock).
  * particles_out: optional K x 16. */
+/* The whole loop runs on the device: per iteration a state kernel, the derivative kernel and one Stein kernel (K x K update,
+ * retract, mean pose, stop test) are queued; the host polls one pinned status word per iteration, one iteration behind. */
 int ndtb_svn_align(ndtb_handle h, const double prior[16], const double* init_particles, uint64_t seed, ndtb_svn_result* result,
                    double* particles_out);
-/* Particle sharding for multi-GPU SVN: this handle evaluates particles k with
- * k % world == rank in stage 1; the caller all-gathers the (score,g,H) records (43 doubles per
- * particle) between ndtb_svn_stage1_local and ndtb_svn_finish_step. */
+/* Device time of the last ndtb_svn_align, summed over its iterations: derivative kernels (CUDA events), Stein kernels (events; with
+ * a communicator this includes waiting for the peers' records) and the part of it block 0 of the Stein kernel spent waiting for
+ * records (in-kernel timer). */
+int ndtb_svn_get_timings(ndtb_handle h, float* eval_ms, float* stein_ms, float* exchange_wait_ms, int* iterations);
+
+/* ---- multi-GPU SVN: particles sharded over GPUs, the reference's stage-1 / stage-2 split (svn_ndt_impl.hpp:758-781 independent
+ * per particle, :789-839 sums over all particles) --------------------------------------------------------------------------
+ * Every rank holds the same target map and source cloud and evaluates the particles k with k % world == rank.  There is no
+ * collective library call on the critical path: the LAST BLOCK of a particle's derivative evaluation stores the particle's
+ * 43-double record {score, g, H} into the record window of EVERY rank over NVLink (peer-mapped device memory) and releases a
+ * per-particle flag; each rank's Stein kernel acquires the K flags and updates all K particles redundantly, so poses never
+ * travel and all ranks stay bit-identical.  ~34 KB cross NVLink per iteration at K = 100.
+ *   one process per GPU (torchrun, MPI ...): ndtb_comm_window_handle on every rank -> exchange the opaque handles out of band
+ *       (any all-gather of *handle_bytes bytes) -> ndtb_comm_connect on every rank -> BARRIER -> aligns
+ *   one process, one handle per GPU: ndtb_comm_init(handles, n), then ndtb_svn_align from n threads, one per handle
+ * With a communicator, ndtb_svn_align (= ndtb_svn_align_sharded, which insists on one) is COLLECTIVE: all ranks call it with
+ * the same prior / particles / parameters.  A rank whose peers do not deliver within 4 s returns NDTB_ERR_CUDA instead of
+ * hanging.  ndtb_comm_close returns the handle to single-GPU operation. */
+int ndtb_comm_window_handle(ndtb_handle h, void* ipc_handle, size_t capacity_bytes, size_t* handle_bytes);
+int ndtb_comm_connect(ndtb_handle h, int rank, int world, const void* all_ipc_handles /* world x handle_bytes, rank order */);
+int ndtb_comm_init(ndtb_handle* handles, int n);
+int ndtb_comm_close(ndtb_handle h);
+int ndtb_comm_info(ndtb_handle h, int* rank, int* world);
+int ndtb_svn_align_sharded(ndtb_handle h, const double prior[16], const double* init_particles, uint64_t seed, ndtb_svn_result* result,
+                           double* particles_out);
+
+/* Host-staged halves of one iteration (parity hooks, and the building blocks of a caller that wants to move the records itself):
+ * this handle evaluates particles k with k % world == rank in stage 1; the caller gathers the (score,g,H) records (43 doubles
+ * per particle) between ndtb_svn_stage1_local and ndtb_svn_finish_step. */
 int ndtb_svn_stage1_local(ndtb_handle h, int K, const double* poses, int rank, int world, double* records43);
 int ndtb_svn_finish_step(ndtb_handle h, int K, double* poses, const double* records43, double* updates);
 

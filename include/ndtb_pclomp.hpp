@@ -99,7 +99,16 @@ inline int upload(ndtb_handle h, const Cloud& cloud, bool target) {
 
 }  // namespace ndtb_facade
 
-namespace pclomp {
+// include/ndtb_pcl_adapter.hpp (the pcl::Registration-derived drop-in, for builds WITH PCL) re-homes the classes below into
+// namespace ndtb_core and defines pclomp:: / svn_ndt:: itself; without it they ARE pclomp:: / svn_ndt::.
+#ifndef NDTB_PCLOMP_NS
+#define NDTB_PCLOMP_NS pclomp
+#endif
+#ifndef NDTB_SVN_NS
+#define NDTB_SVN_NS svn_ndt
+#endif
+
+namespace NDTB_PCLOMP_NS {
 
 enum NeighborSearchMethod { KDTREE, DIRECT26, DIRECT7, DIRECT1 };  // ndt_struct.hpp:65
 
@@ -470,9 +479,9 @@ private:
   bool converged_ = false;
 };
 
-}  // namespace pclomp
+}  // namespace NDTB_PCLOMP_NS (pclomp)
 
-namespace svn_ndt {
+namespace NDTB_SVN_NS {
 
 enum class NeighborSearchMethod { KDTREE, DIRECT7, DIRECT1 };  // svn_ndt.h:31-36
 
@@ -551,6 +560,6 @@ private:
   int target_rc_ = NDTB_ERR_NOT_READY;
 };
 
-}  // namespace svn_ndt
+}  // namespace NDTB_SVN_NS (svn_ndt)
 
 #endif  // NDTB_PCLOMP_HPP_

@@ -2,6 +2,10 @@
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
 // load this library.  Not bit-pinned against a reference binary (PCL/Eigen/GTSAM absent); pinned to the README fitness values and
 // against the reference's own test criteria (tests/test_oracle_*.py).
+#include <set>
+#include <array>
+#include <map>
+#include <cstdio>
 #include "ndt_pclomp_align.hpp"
 #include "svn_ndt.hpp"
 
@@ -133,6 +137,81 @@ void orc_ndt_calculate_scores(void* h, const float* T, double* tp, double* nvtl_
   }
   *tp = N ? score / static_cast<double>(N) : 0.0;
   *nvtl_out = found ? nearest / static_cast<double>(found) : 0.0;
+}
+// calculateScore (ndt_omp_impl.hpp:1083-1167) from cleared maps (cleanScores, ndt_omp.h:236-240): returns score / N; getScoreMap()
+// = per-voxel mean score keyed by getLeafIndex(cell mean) (voxel_grid_covariance_omp.h:340-349); getEmptyVoxels() = the voxel ids
+// floor(x / resolution) of the points without neighbours, ordered by EigenCmp (ndt_omp.h:57-65).  nomap_points_num_ is keyed by an
+// uninitialised variable in the reference (:1124-1127) and is not restated.
+double orc_ndt_calculate_score(void* h, const float* T, size_t map_cap, long long* vox_idx, double* vox_mean_score, size_t* n_vox,
+                               size_t empty_cap, int* empty_ijk, size_t* n_empty) {
+  PclompNdt* n = static_cast<PclompNdt*>(h);
+  n->update_gauss();
+  std::vector<float> trans; n->transform_cloud(T, trans);
+  const size_t N = trans.size() / 3;
+  double score = 0;
+  std::map<size_t, double> score_map; std::map<size_t, size_t> num;
+  std::set<std::array<int, 3>> empty;
+  const VoxelGrid& g = n->grid;
+  for (size_t i = 0; i < N; ++i) {
+    const float* xt = &trans[3 * i];
+    const Leaf* nb[PclompNdt::MAX_NB];
+    const int nn = n->find_neighbours(xt, nb);
+    if (nn == 0) {
+      std::array<int, 3> v;
+      for (int a = 0; a < 3; ++a) v[a] = static_cast<int>(std::floor(xt[a] / n->params.resolution));
+      empty.insert(v);
+      continue;
+    }
+    for (int k = 0; k < nn; ++k) {
+      const double x[3] = {static_cast<double>(xt[0]) - nb[k]->mean[0], static_cast<double>(xt[1]) - nb[k]->mean[1], static_cast<double>(xt[2]) - nb[k]->mean[2]};
+      const double* C = nb[k]->icov;
+      double Cx[3];
+      for (int r = 0; r < 3; ++r) Cx[r] = (C[3 * r] * x[0] + C[3 * r + 1] * x[1]) + C[3 * r + 2] * x[2];
+      const double q = (x[0] * Cx[0] + x[1] * Cx[1]) + x[2] * Cx[2];
+      const double s = -n->gauss_d1 * std::exp(-n->gauss_d2 * q / 2);
+      score += s;
+      int ijk[3];
+      for (int a = 0; a < 3; ++a) ijk[a] = static_cast<int>(std::floor(nb[k]->mean[a] * static_cast<double>(g.inverse_leaf_size)) - g.min_b[a]);
+      const size_t vi = static_cast<size_t>(ijk[0] * g.divb_mul[0] + ijk[1] * g.divb_mul[1] + ijk[2] * g.divb_mul[2]);
+      score_map[vi] += s; num[vi] += 1;
+    }
+  }
+  size_t c = 0;
+  for (auto& kv : score_map) { if (c < map_cap) { vox_idx[c] = static_cast<long long>(kv.first); vox_mean_score[c] = kv.second / static_cast<double>(num[kv.first]); } ++c; }
+  if (n_vox) *n_vox = c;
+  c = 0;
+  for (auto& v : empty) { if (c < empty_cap) { empty_ijk[3 * c] = v[0]; empty_ijk[3 * c + 1] = v[1]; empty_ijk[3 * c + 2] = v[2]; } ++c; }
+  if (n_empty) *n_empty = c;
+  return N ? score / static_cast<double>(N) : 0.0;
+}
+// extractNdtData + writeNdtDataToFiles (include/pipeline.hpp:163-274): ndt_ellipsoids.txt = mean, evecs row-major, evals, point count;
+// ndt_voxels.txt = getLeafCenter(index) (voxel_grid_covariance_omp.h:352-367), resolution; std::fixed << std::setprecision(8).
+// The reference compares getPointCount() (int) with a size_t min_points, so leaves flagged nr_points_ = -1 pass the test and are
+// written with the count static_cast<size_t>(-1).
+long orc_ndt_write_files(void* h, const char* ellipsoid_path, const char* voxel_path) {
+  PclompNdt* n = static_cast<PclompNdt*>(h);
+  const VoxelGrid& g = n->grid;
+  FILE* fe = std::fopen(ellipsoid_path, "w"); FILE* fv = std::fopen(voxel_path, "w");
+  if (!fe || !fv) { if (fe) std::fclose(fe); if (fv) std::fclose(fv); return -1; }
+  long written = 0;
+  const size_t min_points = static_cast<size_t>(g.min_points_per_voxel);
+  for (auto& kv : g.leaves_map) {
+    const Leaf& l = kv.second;
+    if (!(static_cast<size_t>(l.nr_points) >= min_points)) continue;
+    std::fprintf(fe, "%.8f %.8f %.8f ", l.mean[0], l.mean[1], l.mean[2]);
+    for (int i = 0; i < 9; ++i) std::fprintf(fe, "%.8f ", l.evecs[i]);
+    std::fprintf(fe, "%.8f %.8f %.8f %zu\n", l.evals[0], l.evals[1], l.evals[2], static_cast<size_t>(l.nr_points));
+    const size_t index = kv.first;
+    const int ijk2 = static_cast<int>(index / g.divb_mul[2]);
+    const int ijk1 = static_cast<int>((index % g.divb_mul[2]) / g.divb_mul[1]);
+    const int ijk0 = static_cast<int>(((index % g.divb_mul[2]) % g.divb_mul[1]) / g.divb_mul[0]);
+    const double inv = static_cast<double>(g.inverse_leaf_size);
+    std::fprintf(fv, "%.8f %.8f %.8f %.8f\n", (static_cast<double>(ijk0 + g.min_b[0]) + 0.5) / inv, (static_cast<double>(ijk1 + g.min_b[1]) + 0.5) / inv,
+                 (static_cast<double>(ijk2 + g.min_b[2]) + 0.5) / inv, static_cast<double>(n->params.resolution));
+    ++written;
+  }
+  std::fclose(fe); std::fclose(fv);
+  return written;
 }
 // trace: 50 doubles per evaluation (p6, score, g6, H36, nvtl); tarray: 16 floats per entry.
 int orc_ndt_align(void* h, const float* guess, float* final_T, double* hessian, double* trans_probability, double* nvtl, int* iterations,

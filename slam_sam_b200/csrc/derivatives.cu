@@ -630,7 +630,8 @@ __global__ void __launch_bounds__(EVAL_THREADS, EVAL_MIN_BLOCKS) eval_kernel(con
                                                                           const double* __restrict__ c_mean, const double* __restrict__ c_icov,
                                                                           const EvalState* __restrict__ states, double* __restrict__ partials,
                                                                           double* __restrict__ results, unsigned int* __restrict__ tickets,
-                                                                          int particle_offset) {
+                                                                          int particle_offset, const SvnExchange xch) {
+  if (FLAVOUR == FLAVOUR_SVN && xch.done && *xch.done) return;  // speculatively queued iteration after the align converged
   __shared__ EvalState st;
   constexpr int QC = (PROBES > 7) ? Q_CAP26 : Q_CAP;
   constexpr int GPC = (PROBES > 7) ? GROUPS_PER_CHUNK / 2 : GROUPS_PER_CHUNK;  // point groups per chunk
@@ -719,6 +720,31 @@ __global__ void __launch_bounds__(EVAL_THREADS, EVAL_MIN_BLOCKS) eval_kernel(con
   __syncthreads();
   block_reduce_store(acc, s_red, results + static_cast<size_t>(particle) * RED_N, 1);
   if (threadIdx.x == 0) tickets[particle] = 0;  // self-reset for the next launch
+  if (FLAVOUR == FLAVOUR_SVN && xch.n_dest > 0) {
+    // ---- fused exchange: this particle's record goes to every rank's window over NVLink (see SvnExchange) ----
+    __shared__ int s_bad[2];
+    if (threadIdx.x == 0) { s_bad[0] = 0; s_bad[1] = 0; }
+    __syncthreads();  // also orders the stores of block_reduce_store before the reads below
+    const int t = threadIdx.x;
+    double v = 0.0;
+    if (t < SVN_REC) {
+      v = __ldcg(results + static_cast<size_t>(particle) * RED_N + t);   // RED_SCORE, RED_G, RED_H are laid out like the record
+      if (t >= 7 && (t - 7) % 7 == 0) v += 1e-6;                         // H += 1e-6 I  (svn_ndt_impl.hpp:650-653)
+      if (t >= 1 && t < 7 && !isfinite(v)) s_bad[0] = 1;
+      if (t >= 7 && !isfinite(v)) s_bad[1] = 1;
+    }
+    __syncthreads();
+    const int k = xch.rank + (blockIdx.y + particle_offset) * xch.world;
+    const size_t row = static_cast<size_t>(xch.parity) * xch.capacity + k;
+    if (t < SVN_REC) {
+      if (t >= 1 && t < 7 && s_bad[0]) v = 0.0;                          // non-finite gradient -> zero (:656-659)
+      if (t >= 7 && s_bad[1]) v = ((t - 7) % 7 == 0) ? 1.0 : 0.0;        // non-finite Hessian -> identity (:660-663)
+      for (int r = 0; r < xch.n_dest; ++r) xch.rec[r][row * SVN_REC + t] = v;
+      __threadfence_system();
+    }
+    __syncthreads();
+    if (t < xch.n_dest) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(xch.flag[t] + row), "l"(xch.stamp) : "memory");
+  }
 }
 
 // ------------------------------------------------------------------------------ the pclomp kernel
@@ -1110,16 +1136,17 @@ cudaError_t launch_eval_pclomp(int n_probe, bool compute_hessian, const float4* 
 
 template <int FLAVOUR, int PROBES, bool HESS, bool GN>
 static void launch_t(const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs, const HashSlot* table, const double* c_mean,
-                     const double* c_icov, const EvalBuffers& b, int n_particles, int particle_offset, cudaStream_t stream) {
+                     const double* c_icov, const EvalBuffers& b, int n_particles, int particle_offset, cudaStream_t stream, const SvnExchange& xch) {
   dim3 grid(eval_blocks_for(n), n_particles);
   eval_kernel<FLAVOUR, PROBES, HESS, GN><<<grid, EVAL_THREADS, 0, stream>>>(d_src, n, meta, recs, table, c_mean, c_icov, b.d_states,
-                                                                           b.d_partials, b.d_results, b.d_tickets, particle_offset);
+                                                                           b.d_partials, b.d_results, b.d_tickets, particle_offset, xch);
 }
 
 void launch_eval(int flavour, int n_probe, bool compute_hessian, bool gn, const float4* d_src, int n, const GridMeta& meta,
                  const VoxRec* recs, const HashSlot* table, const double* c_mean, const double* c_icov, const EvalBuffers& b,
-                 int n_particles, int particle_offset, cudaStream_t stream) {
-#define ARGS d_src, n, meta, recs, table, c_mean, c_icov, b, n_particles, particle_offset, stream
+                 int n_particles, int particle_offset, cudaStream_t stream, const SvnExchange* xch_in) {
+  const SvnExchange xch = xch_in ? *xch_in : SvnExchange();
+#define ARGS d_src, n, meta, recs, table, c_mean, c_icov, b, n_particles, particle_offset, stream, xch
   if (flavour == FLAVOUR_PCLOMP) {
     // DIRECT1 / DIRECT7 evaluations go through launch_eval_pclomp; DIRECT26 and KDTREE (27 cells + radius test), off the hot path, use this generic kernel
     if (n_probe == 26) { if (compute_hessian) launch_t<FLAVOUR_PCLOMP, 26, true, false>(ARGS); else launch_t<FLAVOUR_PCLOMP, 26, false, false>(ARGS); }

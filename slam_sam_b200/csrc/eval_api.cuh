@@ -17,6 +17,24 @@ constexpr int EVAL_THREADS = 128;
 #define EVAL_MIN_BLOCKS 3
 #endif
 
+// SVN record exchange, performed by the LAST block of every particle's evaluation (svn flavour only): the particle's
+// 43-double record {score, g[6], H[36] + 1e-6 I, NaN guards of svn_ndt_impl.hpp:650-663} is stored straight into the record
+// window of EVERY rank (rec[r] are peer-mapped device pointers over NVLink, rec[rank] is the local window), followed by a
+// system-scope release of the particle's flag.  The consumer (stein_kernel) acquires the K flags.  No collective call, no
+// host in the loop.  n_dest == 0 disables the exchange (results only go to EvalBuffers::d_results).
+constexpr int SVN_MAX_RANKS = 8;
+constexpr int SVN_REC = 43;
+struct SvnExchange {
+  int world = 1, rank = 0;          // particle of block row s is  k = rank + s * world
+  int n_dest = 0;                   // windows the record is stored to: rec[0..n_dest-1] (n_dest == world across GPUs, 1 = local only)
+  int capacity = 0;                 // particles per parity half of a window
+  int parity = 0;                   // window half of this iteration (stamp & 1)
+  unsigned long long stamp = 0;     // value the particle's flag is set to
+  const int* done = nullptr;        // device flag: != 0 -> the align has finished, the launch is a no-op
+  double* rec[SVN_MAX_RANKS] = {};              // [2][capacity][43]
+  unsigned long long* flag[SVN_MAX_RANKS] = {}; // [2][capacity]
+};
+
 // One derivative evaluation for `n_particles` poses over `n` source points.
 //   flavour  : FLAVOUR_PCLOMP -> ndt_omp_impl.hpp:217-347 maths (float pair maths, FP64 accumulate)
 //              FLAVOUR_SVN    -> svn_ndt_impl.hpp:518-647 maths (FP64 Mahalanobis/exp, GN or full Hessian)
@@ -24,7 +42,7 @@ constexpr int EVAL_THREADS = 128;
 // Results land in bufs.d_results[particle][RED_N] on `stream`.
 void launch_eval(int flavour, int n_probe, bool compute_hessian, bool svn_gauss_newton, const float4* d_src, int n, const GridMeta& meta,
                  const VoxRec* recs, const HashSlot* table, const double* c_mean, const double* c_icov, const EvalBuffers& bufs,
-                 int n_particles, int particle_offset, cudaStream_t stream);
+                 int n_particles, int particle_offset, cudaStream_t stream, const SvnExchange* xch = nullptr);
 
 int eval_blocks_for(int n);
 

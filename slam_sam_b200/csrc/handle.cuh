@@ -75,10 +75,34 @@ struct ndtb_handle_s {
   float build_ms = 0, align_ms = 0, eval_ms_total = 0; int eval_launches = 0;
   uint64_t launches = 0;  // eval / stein / score kernels launched (builds are counted in grid.launches)
 
-  // svn device scratch
-  double* d_svn_in = nullptr;   // poses(16K) + grads(6K) + hess(36K)
-  double* d_svn_out = nullptr;  // updates(6K) + new poses(16K) + misc
-  int svn_alloc = 0;
+  // ---- SVN-NDT, device-resident loop (svn_stein.cu, svn_api.cu) -------------------------------------------------
+  // Particles, records and updates stay in HBM for the whole align; one iteration = state kernel (poses -> EvalState of the
+  // rank's own particles) + eval kernel (its last blocks store the records into every rank's window) + Stein kernel (acquires
+  // the K flags, updates all K particles, mean pose + stop test in its last block).  The host only polls a pinned status slot.
+  struct SvnDev {
+    static constexpr int CAPACITY = 1024;       // particles per window half
+    // exchange window: flags [2][CAPACITY] u64, then records [2][CAPACITY][43] f64 -- ONE cudaMalloc so that it can be shared by
+    // cudaIpc (one process per GPU) or reached through peer access (one process, several handles)
+    unsigned char* d_window = nullptr;
+    double* d_poses[2] = {nullptr, nullptr};    // [CAPACITY][16], ping-pong (the Stein kernel reads all poses while it writes the new ones)
+    double* d_updates = nullptr;                // [CAPACITY][6]
+    double* d_mean = nullptr;                   // [2][16] mean pose ping-pong + [16] prior
+    int* d_done = nullptr;                      // 0 running, 1 converged, 2 peer time-out
+    unsigned int* d_ticket = nullptr;           // last-block-done ticket of the Stein kernel
+    unsigned long long* d_wait_ns = nullptr;    // time block 0 of the Stein kernel spent waiting for records (summed over iterations)
+    volatile unsigned long long* h_status = nullptr;  // pinned, 64 self-validating slots {word, word ^ key(stamp)}
+    int cur = 0;                                // d_poses[cur] holds the current particles
+    unsigned long long stamp = 0;               // iterations executed so far on this handle (all ranks advance in lock-step)
+    unsigned long long local_seq = 0;           // stamps of the host-staged parity hooks (this handle only)
+    // communicator
+    int rank = 0, world = 1;
+    void* peer_base[8] = {};                    // window base of every rank (peer_base[rank] == d_window)
+    bool peer_is_ipc[8] = {};
+    // per-align timing (CUDA events, resolved after the loop)
+    std::vector<cudaEvent_t> ev;
+    float eval_ms = 0, stein_ms = 0, wait_ms = 0;
+    int iterations = 0;
+  } svnd;
 };
 
 namespace ndtb {
@@ -92,4 +116,5 @@ int compute_hessian_f64(ndtb_handle_s* h, const double* p, const float* T16, dou
 int mg_eval(ndtb_handle_s* h, const double* p, const float* T16, bool compute_hessian, double* score, double* g, double* H, double* nvtl);  // multigrid.cu
 bool mg_ready(ndtb_handle_s* h);
 void mg_free(ndtb_handle_s* h);
+void svn_dev_free(ndtb_handle_s* h);  // svn_stein.cu
 }  // namespace ndtb

@@ -372,7 +372,7 @@ int ndtb_destroy(ndtb_handle h) {
   if (h->batch_copy_stream) cudaStreamDestroy(h->batch_copy_stream);
   if (h->batch_h_results) cudaFreeHost(h->batch_h_results);
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
-  cudaFree(h->d_svn_in); cudaFree(h->d_svn_out);
+  svn_dev_free(h);
   for (int i = 0; i < 4; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   for (int i = 0; i < 2; ++i) if (h->ev_b[i]) cudaEventDestroy(h->ev_b[i]);
   cudaStreamDestroy(h->stream);

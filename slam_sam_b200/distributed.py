@@ -2,11 +2,13 @@
 
 The path shards at two granularities and nowhere else:
   * SVN particles: particle k is evaluated on rank k % world (stage 1, svn_ndt_impl.hpp:758-781);
-    stage 2 couples all particles (:795-808), so the per-particle (score, g, H) records -- 43 doubles
-    each -- are exchanged with ONE all-reduce of a zero-padded K x 43 buffer per iteration.  Every
-    rank contributes exact zeros for rows it does not own, so the sum is exact and every rank ends up
-    with bit-identical records; each rank then runs the K x K Stein update redundantly and all
-    replicas stay in lock-step without exchanging poses.
+    stage 2 couples all particles (:795-808).  Product path (SvnComm -> ndtb_svn_align_sharded): the
+    last block of a particle's derivative kernel stores the particle's 43-double record into every
+    rank's window over NVLink and releases a flag; every rank's Stein kernel acquires the K flags and
+    updates all K particles redundantly, so poses never travel and replicas stay bit-identical.
+    svn_step / svn_align below are the host-staged form of the same split (stage 1 local, ONE
+    all-reduce of a zero-padded K x 43 buffer, Stein update) -- used by the CPU (gloo) tests of the
+    sharding logic and by callers that want to move the records themselves.
   * replay batches: independent alignments against a replicated map, scan i on rank i % world, no
     data-path collective at all.
 A single alignment is NOT split across GPUs (one evaluation is ~10 us of work): replicas only.
@@ -61,6 +63,43 @@ def svn_align(handle, prior, particles, rank, world, max_iterations=50, stop_thr
             converged = True
             break
     return mean_cur, P, it, converged
+
+
+class SvnComm:
+    """Communicator of the device-resident sharded SVN align (include/ndtb.h, ndtb_comm_*): the record windows of all ranks are
+    mapped into every rank (CUDA IPC, peer access over NVLink); torch.distributed only carries the 64-byte window handles once.
+    After that `align` is the library's collective ndtb_svn_align: no NCCL call and no host copy per iteration."""
+
+    def __init__(self, handle, rank, world, device=None):
+        import torch
+        import torch.distributed as dist
+
+        self.h, self.rank, self.world = handle, rank, world
+        mine = torch.from_numpy(handle.comm_window_handle().copy())
+        if dist.get_backend() == "nccl":
+            mine = mine.cuda(device)
+        allh = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allh, mine)
+        handle.comm_connect(rank, world, np.stack([t.cpu().numpy() for t in allh]))
+        dist.barrier()   # every window is zeroed and every rank's stamps restarted before the first collective align
+
+    def align(self, prior, particles):
+        from . import ndtb
+
+        h = self.h
+        prior = np.ascontiguousarray(prior, np.float64).reshape(16)
+        init = np.ascontiguousarray(particles, np.float64)
+        K = init.shape[0]
+        out = np.zeros((K, 4, 4)); r = ndtb.SvnResult()
+        h.check(h.L.ndtb_svn_align_sharded(h.h, ndtb._ptr(prior, ndtb.c_d), ndtb._ptr(init, ndtb.c_d), 0, ndtb.C.byref(r), ndtb._ptr(out, ndtb.c_d)))
+        return dict(final_pose=np.array(r.final_pose).reshape(4, 4), final_covariance=np.array(r.final_covariance).reshape(6, 6),
+                    converged=bool(r.converged), iterations=r.iterations, particles=out)
+
+    def close(self):
+        import torch.distributed as dist
+
+        dist.barrier()
+        self.h.comm_close()
 
 
 def max_over_ranks(value, device=None):

@@ -57,7 +57,9 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "nd
            "ndtb_lidar_get_tables", "ndtb_lidar_push_packets", "ndtb_lidar_pop_frame", "ndtb_lidar_read_frame", "ndtb_lidar_frame_points",
            "ndtb_lidar_sync", "ndtb_lidar_get_stats",
            "ndtb_mg_add_target", "ndtb_mg_remove_target", "ndtb_mg_create_kdtree", "ndtb_mg_set_input_target", "ndtb_mg_get_info",
-           "ndtb_mg_get_grid_ids", "ndtb_mg_get_leaves", "ndtb_mg_compute_derivatives", "ndtb_mg_align", "ndtb_mg_calculate_scores"]
+           "ndtb_mg_get_grid_ids", "ndtb_mg_get_leaves", "ndtb_mg_compute_derivatives", "ndtb_mg_align", "ndtb_mg_calculate_scores",
+           "ndtb_svn_get_timings", "ndtb_comm_window_handle", "ndtb_comm_connect", "ndtb_comm_init", "ndtb_comm_close", "ndtb_comm_info",
+           "ndtb_svn_align_sharded", "ndtb_calculate_score", "ndtb_write_ndt_files"]
 
 _LIB = None
 
@@ -107,6 +109,9 @@ def lib():
         L.ndtb_align.argtypes = [H, c_f, C.POINTER(Result), c_f, C.c_int, c_f]
         L.ndtb_get_trace.argtypes = [H, c_d, C.c_int, c_i]
         L.ndtb_calculate_scores.argtypes = [H, c_f, c_d, c_d]
+        L.ndtb_calculate_score.argtypes = [H, c_f, c_d, C.c_size_t, C.POINTER(C.c_int64), c_d, C.POINTER(C.c_size_t), C.c_size_t,
+                                           C.POINTER(C.c_int32), C.POINTER(C.c_size_t)]
+        L.ndtb_write_ndt_files.argtypes = [H, C.c_char_p, C.c_char_p, C.c_char_p, C.c_void_p, C.c_size_t, C.c_size_t]
         L.ndtb_get_voxel_count.argtypes = [H, C.POINTER(C.c_size_t), c_i, c_i, c_i]
         L.ndtb_get_voxels.argtypes = [H, C.POINTER(C.c_int64), C.POINTER(C.c_int32), c_d, c_d, c_d, c_d, c_d]
         L.ndtb_get_last_hits.argtypes = [H, c_d, c_d]
@@ -116,6 +121,13 @@ def lib():
         L.ndtb_svn_stage2.argtypes = [H, C.c_int, c_d, c_d, c_d, c_d]
         L.ndtb_svn_step.argtypes = [H, C.c_int, c_d, c_d, c_d, c_d, c_d]
         L.ndtb_svn_align.argtypes = [H, c_d, c_d, C.c_uint64, C.POINTER(SvnResult), c_d]
+        L.ndtb_svn_align_sharded.argtypes = [H, c_d, c_d, C.c_uint64, C.POINTER(SvnResult), c_d]
+        L.ndtb_svn_get_timings.argtypes = [H, c_f, c_f, c_f, c_i]
+        L.ndtb_comm_window_handle.argtypes = [H, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.ndtb_comm_connect.argtypes = [H, C.c_int, C.c_int, C.c_void_p]
+        L.ndtb_comm_init.argtypes = [C.POINTER(H), C.c_int]
+        L.ndtb_comm_close.argtypes = [H]
+        L.ndtb_comm_info.argtypes = [H, c_i, c_i]
         L.ndtb_svn_stage1_local.argtypes = [H, C.c_int, c_d, C.c_int, C.c_int, c_d]
         L.ndtb_svn_finish_step.argtypes = [H, C.c_int, c_d, c_d, c_d]
         L.ndtb_align_batch.argtypes = [H, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.c_size_t, c_f, C.POINTER(Result)]
@@ -208,6 +220,14 @@ def newton_direction(H, b, method=1):
     if rc != NDTB_OK:
         raise NdtbError(rc, "ndtb_newton_direction")
     return x, bool(used.value)
+
+
+def comm_init(handles):
+    """ndtb_comm_init: one process, one handle per GPU -- the record windows are reached through peer access."""
+    arr = (C.c_void_p * len(handles))(*[h.h for h in handles])
+    rc = lib().ndtb_comm_init(arr, len(handles))
+    if rc != NDTB_OK:
+        raise NdtbError(rc, lib().ndtb_last_error(handles[0].h).decode())
 
 
 class Handle:
@@ -385,6 +405,23 @@ class Handle:
         self.check(self.L.ndtb_calculate_scores(self.h, _ptr(t, c_f), _ptr(tp, c_d), _ptr(nv, c_d)))
         return tp[0], nv[0]
 
+    def calculate_score(self, T):
+        """calculateScore (ndt_omp_impl.hpp:1083-1167): (score, {voxel index: mean score}, sorted empty voxel ids (m, 3))."""
+        t = np.ascontiguousarray(T, np.float32).reshape(16)
+        sc = np.zeros(1); nv = C.c_size_t(); ne = C.c_size_t()
+        self.check(self.L.ndtb_calculate_score(self.h, _ptr(t, c_f), _ptr(sc, c_d), 0, None, None, C.byref(nv), 0, None, C.byref(ne)))
+        idx = np.zeros(nv.value, np.int64); val = np.zeros(nv.value); emp = np.zeros((ne.value, 3), np.int32)
+        self.check(self.L.ndtb_calculate_score(self.h, _ptr(t, c_f), _ptr(sc, c_d), nv.value, idx.ctypes.data_as(C.POINTER(C.c_int64)), _ptr(val, c_d),
+                                               C.byref(nv), ne.value, emp.ctypes.data_as(C.POINTER(C.c_int32)), C.byref(ne)))
+        return sc[0], dict(zip(idx.tolist(), val.tolist())), emp
+
+    def write_ndt_files(self, ellipsoid_path, voxel_path, points_path=None, points=None):
+        """writeNdtDataToFiles (include/pipeline.hpp:224-274): ndt_ellipsoids.txt / ndt_voxels.txt (/ the map points)."""
+        if points is not None and points_path is not None:
+            a, n, st = host_cloud(points)
+            return self.check(self.L.ndtb_write_ndt_files(self.h, str(ellipsoid_path).encode(), str(voxel_path).encode(), str(points_path).encode(), a.ctypes.data, n, st))
+        return self.check(self.L.ndtb_write_ndt_files(self.h, str(ellipsoid_path).encode(), str(voxel_path).encode(), None, None, 0, 0))
+
     # voxel map
     def voxels(self):
         cnt = C.c_size_t()
@@ -502,6 +539,31 @@ class Handle:
         rec = np.ascontiguousarray(rec, np.float64); u = np.zeros((K, 6))
         self.check(self.L.ndtb_svn_finish_step(self.h, K, _ptr(P, c_d), _ptr(rec, c_d), _ptr(u, c_d)))
         return P, u
+
+    def svn_timings(self):
+        e = np.zeros(1, np.float32); s = np.zeros(1, np.float32); w = np.zeros(1, np.float32); n = np.zeros(1, np.int32)
+        self.L.ndtb_svn_get_timings(self.h, _ptr(e, c_f), _ptr(s, c_f), _ptr(w, c_f), _ptr(n, c_i))
+        return dict(eval_ms=float(e[0]), stein_ms=float(s[0]), exchange_wait_ms=float(w[0]), iterations=int(n[0]))
+
+    # multi-GPU SVN communicator (one process per GPU): window handle -> all-gather -> connect -> barrier
+    def comm_window_handle(self):
+        nb = C.c_size_t()
+        self.check(self.L.ndtb_comm_window_handle(self.h, None, 0, C.byref(nb)))
+        buf = np.zeros(nb.value, np.uint8)
+        self.check(self.L.ndtb_comm_window_handle(self.h, buf.ctypes.data, nb.value, None))
+        return buf
+
+    def comm_connect(self, rank, world, all_handles):
+        a = np.ascontiguousarray(all_handles, np.uint8)
+        self.check(self.L.ndtb_comm_connect(self.h, int(rank), int(world), a.ctypes.data))
+
+    def comm_close(self):
+        self.check(self.L.ndtb_comm_close(self.h))
+
+    def comm_info(self):
+        r = np.zeros(1, np.int32); w = np.zeros(1, np.int32)
+        self.L.ndtb_comm_info(self.h, _ptr(r, c_i), _ptr(w, c_i))
+        return int(r[0]), int(w[0])
 
     def svn_align(self, prior, particles=None, seed=0):
         prior = np.ascontiguousarray(prior, np.float64).reshape(16)

@@ -54,6 +54,10 @@ def lib():
         L.orc_ndt_compute_derivatives_T.restype = C.c_double
         L.orc_ndt_compute_derivatives_T.argtypes = [C.c_void_p, c_f, c_d, C.c_int, c_d, c_d, c_d]
         L.orc_ndt_calculate_scores.argtypes = [C.c_void_p, c_f, c_d, c_d]
+        L.orc_ndt_calculate_score.restype = C.c_double
+        L.orc_ndt_calculate_score.argtypes = [C.c_void_p, c_f, C.c_size_t, c_ll, c_d, C.POINTER(C.c_size_t), C.c_size_t, c_i, C.POINTER(C.c_size_t)]
+        L.orc_ndt_write_files.restype = C.c_long
+        L.orc_ndt_write_files.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p]
         L.orc_ndt_align.argtypes = [C.c_void_p, c_f, c_f, c_d, c_d, c_d, c_i, c_i, c_d, C.c_int, c_i, c_f, C.c_int, c_i]
         L.orc_assemble_window.argtypes = [C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.c_size_t, c_d, c_f]
         L.orc_assemble_window.restype = None
@@ -237,6 +241,17 @@ class OracleNdt:
         t = np.ascontiguousarray(T, np.float32).reshape(16); tp = np.zeros(1); nv = np.zeros(1)
         lib().orc_ndt_calculate_scores(self.h, _f(t), _d(tp), _d(nv))
         return tp[0], nv[0]
+
+    def calculate_score(self, T):
+        t = np.ascontiguousarray(T, np.float32).reshape(16)
+        nv = C.c_size_t(); ne = C.c_size_t()
+        lib().orc_ndt_calculate_score(self.h, _f(t), 0, None, None, C.byref(nv), 0, None, C.byref(ne))
+        idx = np.zeros(nv.value, np.int64); val = np.zeros(nv.value); emp = np.zeros((ne.value, 3), np.int32)
+        s = lib().orc_ndt_calculate_score(self.h, _f(t), nv.value, idx.ctypes.data_as(c_ll), _d(val), C.byref(nv), ne.value, _i(emp), C.byref(ne))
+        return s, dict(zip(idx.tolist(), val.tolist())), emp
+
+    def write_files(self, ellipsoid_path, voxel_path):
+        return lib().orc_ndt_write_files(self.h, str(ellipsoid_path).encode(), str(voxel_path).encode())
 
     def align(self, guess=None, max_trace=128):
         guess = np.eye(4, dtype=np.float32) if guess is None else np.ascontiguousarray(guess, np.float32)

@@ -254,3 +254,41 @@ def test_direct26_and_kdtree_match_oracle(oracle, street, gold, search):
     assert h.L.ndtb_set_params(h.h, p) == ndtb.NDTB_ERR_INVALID
     p.use_line_search = 0; p.grid_flavour = ndtb.FLAVOUR_SVN
     assert h.L.ndtb_set_params(h.h, p) == ndtb.NDTB_ERR_INVALID
+
+
+@pytest.mark.parametrize("search", ["DIRECT7", "DIRECT1", "KDTREE"])
+def test_calculate_score_and_maps(oracle, street, search):
+    """calculateScore (ndt_omp_impl.hpp:1083-1167): score, getScoreMap() and getEmptyVoxels() against the oracle."""
+    h = ndtb.Handle(0)
+    h.set_params(resolution=1.0, search_method=getattr(ndtb, search))
+    assert h.set_target(street["target"]) == 0 and h.set_source(street["source"]) == 0
+    o = O.OracleNdt(resolution=1.0, search=search)
+    o.set_target(street["target"]); o.set_source(street["source"])
+    T = street["rel"].astype(np.float32)
+    sg, mg, eg = h.calculate_score(T)
+    so, mo, eo = o.calculate_score(T)
+    assert abs(sg - so) <= 1e-12 * abs(so)
+    assert sg == pytest.approx(h.calculate_scores(T)[0], rel=1e-12)       # same number as calculateTransformationProbability
+    assert list(mg.keys()) == list(mo.keys()) and len(mg) > 100
+    a, b = np.array(list(mg.values())), np.array(list(mo.values()))
+    assert np.abs(a - b).max() <= 1e-12 * np.abs(b).max()
+    assert np.array_equal(eg, eo) and len(eg) > 0
+
+
+def test_ndt_export_files_byte_for_byte(oracle, street, tmp_path):
+    """extractNdtData + writeNdtDataToFiles (include/pipeline.hpp:163-274): ndt_ellipsoids.txt and ndt_voxels.txt from the device map,
+    written by the library (iostream, std::fixed, 8 decimals like the reference) == the oracle's writer (printf), byte for byte."""
+    h = ndtb.Handle(0)
+    h.set_params(resolution=1.0)
+    assert h.set_target(street["target"]) == 0
+    o = O.OracleNdt(resolution=1.0); o.set_target(street["target"])
+    pts = np.zeros((5, 8), np.float32); pts[:, :3] = street["target"][:5, :3]; pts[:, 4] = np.arange(5) + 0.5
+    h.write_ndt_files(tmp_path / "ge.txt", tmp_path / "gv.txt", tmp_path / "gp.txt", pts)
+    n = o.write_files(tmp_path / "oe.txt", tmp_path / "ov.txt")
+    assert n == int((h.voxels()["n"] >= 6).sum()) and n > 100
+    assert (tmp_path / "ge.txt").read_bytes() == (tmp_path / "oe.txt").read_bytes()
+    assert (tmp_path / "gv.txt").read_bytes() == (tmp_path / "ov.txt").read_bytes()
+    first = (tmp_path / "ge.txt").read_text().splitlines()[0].split()
+    assert len(first) == 16 and int(first[15]) >= 6
+    lines = (tmp_path / "gp.txt").read_text().splitlines()
+    assert len(lines) == 5 and lines[2].split()[3] == "2.50000000"
