@@ -31,7 +31,7 @@ extern "C" {
 #define NDTB_ERR_NOT_READY (-5) /* target or source not set                                         */
 
 /* pclomp::NeighborSearchMethod values (extern/ndt_omp/include/pclomp/ndt_struct.hpp) */
-#define NDTB_KDTREE 0   /* pclomp flavour: radius search over the leaf means, derivatives + align without line search (generic kernel) */
+#define NDTB_KDTREE 0   /* radius search over the leaf means (27 hash probes + FLANN's float distance test); pclomp flavour: derivatives + align without line search; svn flavour: svn_ndt_impl.hpp:576-579 */
 #define NDTB_DIRECT26 1 /* pclomp flavour, derivatives + align without line search (generic kernel, off the hot path)      */
 #define NDTB_DIRECT7 2
 #define NDTB_DIRECT1 3

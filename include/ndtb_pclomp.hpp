@@ -520,8 +520,7 @@ public:
   void setMinPointPerVoxel(int n) { p_.min_points_per_voxel = n; if (target_) target_rc_ = ndtb_set_params(h_.h, &p_); }
   void setOutlierRatio(double r) { p_.outlier_ratio = r; }
   void setNeighborhoodSearchMethod(NeighborSearchMethod m) {
-    if (m == NeighborSearchMethod::KDTREE) throw std::invalid_argument("ndtb: only DIRECT7 / DIRECT1 neighbour search are provided");
-    p_.search_method = (m == NeighborSearchMethod::DIRECT7) ? NDTB_DIRECT7 : NDTB_DIRECT1;
+    p_.search_method = (m == NeighborSearchMethod::DIRECT7) ? NDTB_DIRECT7 : (m == NeighborSearchMethod::KDTREE ? NDTB_KDTREE : NDTB_DIRECT1);
   }
   void setNumThreads(int n) { num_threads_ = n; }
   void setParticleCount(int k) { s_.particle_count = k; }

@@ -10,6 +10,7 @@
 //   * stage 1 computes the angle tables per particle (the reference races on members, :527).
 #pragma once
 #include <vector>
+#include <algorithm>
 #include <random>
 #include "ndt_pclomp.hpp"
 #include "se3.hpp"
@@ -109,6 +110,7 @@ struct SvnNdt {
   int set_target(const float* xyz, size_t n, size_t sf) {
     grid.set_leaf_size(resolution);
     const int rc = grid.build(xyz, n, sf, true);
+    grid.prepare_radius_search();   // filter(search_method_ == KDTREE), svn_ndt_impl.hpp:149-150
     update_constants();
     return rc;
   }
@@ -129,8 +131,16 @@ struct SvnNdt {
     for (size_t idx = 0; idx < N; ++idx) {
       const float* xt = &trans[3 * idx];
       if (!std::isfinite(xt[0]) || !std::isfinite(xt[1]) || !std::isfinite(xt[2])) continue;
-      const Leaf* nb[7];
-      const int nn = grid.neighbours(xt[0], xt[1], xt[2], n_probe, nb);
+      const Leaf* nb[64];
+      int nn = 0;
+      if (search_method == KDTREE) {   // svn_ndt_impl.hpp:576-579: radiusSearch(x_trans, resolution), results sorted by distance
+        std::vector<std::pair<float, const Leaf*>> hits;
+        grid.radius_search(xt, static_cast<double>(grid.leaf_size), false, hits);
+        std::stable_sort(hits.begin(), hits.end(), [](const std::pair<float, const Leaf*>& a, const std::pair<float, const Leaf*>& b) { return a.first < b.first; });
+        for (auto& hh : hits) if (nn < 64) nb[nn++] = hh.second;
+      } else {
+        nn = grid.neighbours(xt[0], xt[1], xt[2], n_probe, nb);
+      }
       if (nn == 0) continue;
       const double x[3] = {source[3 * idx], source[3 * idx + 1], source[3 * idx + 2]};
       PointDeriv pd; init_point_deriv(pd);

@@ -230,8 +230,14 @@ struct VoxelGrid {
   //   mg_centroid = true : the cloud point is leaf.centroid_ (multigrid, multi_..._impl.hpp:221-225)
   void prepare_radius_search() {
     fast_.clear();
-    for (auto& kv : leaves_map)
-      if (kv.second.nr_points >= min_points_per_voxel || kv.second.nr_points == -1) fast_[kv.first] = &kv.second;
+    if (flavour == FLAVOUR_PCLOMP) {
+      for (auto& kv : leaves_map)
+        if (kv.second.nr_points >= min_points_per_voxel || kv.second.nr_points == -1) fast_[kv.first] = &kv.second;
+    } else {
+      // svn: buildCentroidCloudAndIndexMap (voxel_grid_covariance_impl.hpp:383-436) takes every leaf left in the map (invalid ones
+      // were erased), the cloud point is float(leaf.mean_); radiusSearch maps hits back through getLeaf (:505-555)
+      leaves_robin.for_each([&](size_t k, const Leaf& l) { if (l.nr_points >= min_points_per_voxel) fast_[k] = &l; });
+    }
   }
   void radius_search(const float* q, double radius, bool mg_centroid, std::vector<std::pair<float, const Leaf*>>& out) const {
     if (!built) return;

@@ -523,7 +523,7 @@ __device__ __forceinline__ int phase_a(const float4* __restrict__ src, int idx, 
       if (FLAVOUR == FLAVOUR_SVN) point_ok = isfinite(xt[0]) && isfinite(xt[1]) && isfinite(xt[2]);  // svn_ndt_impl.hpp:573
       if (point_ok) {
         uint32_t key[PROBES];
-        if (FLAVOUR == FLAVOUR_PCLOMP) {
+        if (FLAVOUR == FLAVOUR_PCLOMP || PROBES > 7) {  // (svn KDTREE: the 27 cells a radius-`leaf` ball around the query can reach)
           const int i0 = static_cast<int>(floorf(__fdiv_rn(xt[0], m.leaf)));
           const int i1 = static_cast<int>(floorf(__fdiv_rn(xt[1], m.leaf)));
           const int i2 = static_cast<int>(floorf(__fdiv_rn(xt[2], m.leaf)));
@@ -544,8 +544,8 @@ __device__ __forceinline__ int phase_a(const float4* __restrict__ src, int idx, 
           }
         }
         hash_find_batch<PROBES>(table, m.hash_mask, key, rows);
-        if (FLAVOUR == FLAVOUR_PCLOMP && PROBES == 27) {
-          // pclomp KDTREE: radiusSearch(x_trans, resolution_) over the cloud of float(leaf.mean_) (voxel_grid_covariance_omp.h:458-485,
+        if (PROBES == 27) {
+          // KDTREE (pclomp, and svn_ndt_impl.hpp:576-579 / voxel_grid_covariance_impl.hpp:383-436, 505-555): radiusSearch(x_trans, resolution_) over the cloud of float(leaf.mean_) (voxel_grid_covariance_omp.h:458-485,
           // _omp_impl.hpp:301-303); pcl::KdTreeFLANN hands float(radius * radius) to FLANN, L2_Simple<float> accumulates
           // dx*dx + dy*dy + dz*dz in float, RadiusResultSet keeps dist < r2 (strict)
           const float r2 = static_cast<float>(static_cast<double>(m.leaf) * static_cast<double>(m.leaf));
@@ -1154,6 +1154,7 @@ void launch_eval(int flavour, int n_probe, bool compute_hessian, bool gn, const 
     return;
   } else {
     if (n_probe == 7) { if (gn) launch_t<FLAVOUR_SVN, 7, true, true>(ARGS); else launch_t<FLAVOUR_SVN, 7, true, false>(ARGS); }
+    else if (n_probe == 27) { if (gn) launch_t<FLAVOUR_SVN, 27, true, true>(ARGS); else launch_t<FLAVOUR_SVN, 27, true, false>(ARGS); }
     else { if (gn) launch_t<FLAVOUR_SVN, 1, true, true>(ARGS); else launch_t<FLAVOUR_SVN, 1, true, false>(ARGS); }
   }
 #undef ARGS

@@ -391,8 +391,9 @@ int ndtb_get_params(ndtb_handle h, ndtb_params* p) {
 int ndtb_set_params(ndtb_handle h, const ndtb_params* p) {
   if (!h || !p) return NDTB_ERR_INVALID;
   const bool d26_ok = (p->search_method == NDTB_DIRECT26 || p->search_method == NDTB_KDTREE) && p->grid_flavour == NDTB_FLAVOUR_PCLOMP && !p->use_line_search;
-  if (p->search_method != NDTB_DIRECT7 && p->search_method != NDTB_DIRECT1 && !d26_ok)
-    return set_error(h, NDTB_ERR_INVALID, "DIRECT7 / DIRECT1 (both flavours) and DIRECT26 / KDTREE (pclomp flavour, without line search) are provided");
+  const bool svn_kd_ok = p->search_method == NDTB_KDTREE && p->grid_flavour == NDTB_FLAVOUR_SVN;   // svn_ndt::NeighborSearchMethod has no DIRECT26 (svn_ndt.h:31-36)
+  if (p->search_method != NDTB_DIRECT7 && p->search_method != NDTB_DIRECT1 && !d26_ok && !svn_kd_ok)
+    return set_error(h, NDTB_ERR_INVALID, "DIRECT7 / DIRECT1 / KDTREE (both flavours) and DIRECT26 (pclomp flavour; it and pclomp KDTREE without line search) are provided");
   if (!(p->resolution > 0.0f)) return set_error(h, NDTB_ERR_INVALID, "resolution must be positive");
   if (p->grid_flavour != NDTB_FLAVOUR_PCLOMP && p->grid_flavour != NDTB_FLAVOUR_SVN) return set_error(h, NDTB_ERR_INVALID, "bad grid_flavour");
   cudaSetDevice(h->device);

@@ -317,7 +317,7 @@ int svn_dev_stage1(ndtb_handle_s* h, int K, int first, int stride, bool to_peers
     x.n_dest = 1;
     x.rec[0] = svn_window_recs(d.d_window); x.flag[0] = svn_window_flags(d.d_window);
   }
-  const int n_probe = (h->params.search_method == NDTB_DIRECT7) ? 7 : 1;
+  const int n_probe = (h->params.search_method == NDTB_DIRECT7) ? 7 : (h->params.search_method == NDTB_KDTREE ? 27 : 1);
   launch_eval(FLAVOUR_SVN, n_probe, true, h->svn.use_gauss_newton != 0, h->d_source, n, h->grid.meta, h->grid.recs, h->grid.table,
               h->grid.c_mean, h->grid.c_icov, h->eval, m, 0, h->stream, &x);
   CKS(cudaGetLastError());

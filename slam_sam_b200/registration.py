@@ -63,7 +63,7 @@ class NormalDistributionsTransform:
     def setNeighborhoodSearchMethod(self, m):  # noqa: N802
         rc = self._h.set_params(search_method=int(m))
         if rc != ndtb.NDTB_OK:
-            raise ndtb.NdtbError(rc, "DIRECT7 / DIRECT1 / DIRECT26 are provided (KDTREE: MultiGridNormalDistributionsTransform)")
+            raise ndtb.NdtbError(rc, "KDTREE / DIRECT26 / DIRECT7 / DIRECT1 are provided (the first two without line search)")
 
     def setOulierRatio(self, r):  # noqa: N802  (sic: the reference spells it this way, ndt_omp.h:173)
         self._h.set_params(outlier_ratio=float(r))
@@ -227,7 +227,7 @@ class SvnNormalDistributionsTransform:
     def setNeighborhoodSearchMethod(self, m):  # noqa: N802
         rc = self._h.set_params(search_method=int(m))
         if rc != ndtb.NDTB_OK:
-            raise ndtb.NdtbError(rc, "only DIRECT7 / DIRECT1 are provided")
+            raise ndtb.NdtbError(rc, "KDTREE / DIRECT7 / DIRECT1 are provided (svn_ndt.h:31-36)")
 
     def setNumThreads(self, n):  # noqa: N802
         self._num_threads = n

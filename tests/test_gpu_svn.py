@@ -153,3 +153,30 @@ def test_full_size_properties():
     r1 = h.align(guess); r2 = h.align(guess)
     assert r1["converged"] and np.array_equal(r1["T"], r2["T"]) and r1["iterations"] == r2["iterations"]
     assert np.abs(r1["T"][:3, 3] - pose[:3, 3]).max() < 0.05
+
+
+def test_svn_kdtree_matches_oracle(oracle, street, gold):
+    """svn_ndt::NeighborSearchMethod::KDTREE (svn_ndt_impl.hpp:576-579): radiusSearch(x_trans, resolution) over the cloud of
+    float(leaf.mean_) of the valid leaves (voxel_grid_covariance_impl.hpp:383-436, 505-555) = 27 hash probes + FLANN's float
+    distance test on the device.  Per-particle derivatives and a whole K = 6 align against the oracle."""
+    for tgt, src, res in ((gold["target"], gold["source"], 2.0), (street["target"], street["source"], 1.0)):
+        h = ndtb.Handle(0)
+        assert h.set_params(grid_flavour=ndtb.FLAVOUR_SVN, resolution=res, min_points_per_voxel=3, search_method=ndtb.KDTREE) == 0
+        h.set_svn_params(particle_count=6, max_iterations=8, use_gauss_newton=1, kernel_bandwidth=1.0, step_size=1.0)
+        assert h.set_target(tgt) == 0 and h.set_source(src) == 0
+        o = O.OracleSvn(resolution=res, min_pts=3, search="KDTREE", num_threads=8, K=6, max_iter=8, kernel_h=1.0, step_size=1.0)
+        o.set_target(tgt); o.set_source(src)
+        P0 = O.OracleSvn.sample_particles(np.eye(4), 6, seed=11)
+        s, g, H = h.svn_particle_derivatives(P0)
+        hits_kd = h.last_hits()[0]
+        for k in range(6):
+            so, go, Ho = o.particle_derivatives(P0[k])
+            assert abs(s[k] - so) <= TOL * abs(so) and rel_inf(g[k], go) <= TOL and rel_inf(H[k], Ho) <= TOL
+        h7 = ndtb.Handle(0)
+        h7.set_params(grid_flavour=ndtb.FLAVOUR_SVN, resolution=res, min_points_per_voxel=3, search_method=ndtb.DIRECT7)
+        h7.set_target(tgt); h7.set_source(src); h7.svn_particle_derivatives(P0)
+        assert hits_kd != h7.last_hits()[0]                       # a different neighbourhood than DIRECT7
+        rg, ro = h.svn_align(np.eye(4), P0), o.align(np.eye(4), P0)
+        assert rg["iterations"] == ro["iterations"]
+        assert np.abs(rg["particles"] - ro["particles"]).max() <= 1e-8
+        assert np.abs(rg["final_pose"] - ro["final_pose"]).max() <= 1e-8
