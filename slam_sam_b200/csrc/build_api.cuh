@@ -5,12 +5,46 @@
 
 namespace ndtb {
 
+// Everything the build decides ON THE DEVICE (no host round trip inside a build): the grid geometry from the bounding box, the
+// radix-sort plan from the key range, the leaf count, the hash capacity.  Lives in device memory (DeviceGrid::d_meta), read by
+// every build kernel, published to the host once, by the last kernel of the build.
+constexpr int BUILD_NEED_PASSES = 100;  // error = BUILD_NEED_PASSES + k: the host queued fewer than k radix passes (it retries with k)
+constexpr int RADIX_MAX_BITS = 10;      // widest digit: 1024 bins (20 key bits -> 2 passes of 10 bits)
+struct BuildMeta {
+  GridMeta m;
+  int error;                  // 0 | NDTB_ERR_OVERFLOW | BUILD_NEED_PASSES + k
+  int bits, digit_bits, passes;
+  int final_buf;              // pairs[final_buf] holds the sorted (key << 32 | point index) list
+  unsigned int n_skipped;     // non-finite points (never assigned to a leaf)
+  unsigned int V;             // leaves (pclomp keeps under-populated / rejected leaves, flagged)
+  unsigned int n_valid;       // leaves a neighbour search can return
+  unsigned int chunk_counter; // dynamic work hand-out of the statistics kernel
+  unsigned int tile_ticket;   // dynamic tile ids of the segment kernel (decoupled look-back)
+  unsigned int tickets[3];    // last-block-done tickets: bbox, statistics, centroid
+  unsigned int n_flagged;     // pclomp leaves flagged nr_points_ = -1 that stay reachable by radius searches
+};
+static_assert(sizeof(BuildMeta) % 8 == 0, "BuildMeta is published to the host in 8-byte words");
+constexpr int BUILD_META_WORDS = static_cast<int>(sizeof(BuildMeta) / 8);
+
+struct BuildParams {  // what the host knows before the build starts
+  float resolution, inv_leaf;
+  int min_pts, flavour, is_dense;
+  double eig_mult;
+  int n;
+  int passes_queued;
+};
+
 struct DeviceGrid {
-  GridMeta meta{};
+  GridMeta meta{};         // host copy, valid after a successful build
   bool built = false;
-  uint32_t V = 0;          // leaves (pclomp keeps under-populated / rejected leaves, flagged)
+  uint32_t V = 0;          // leaves
   uint32_t n_valid = 0;    // leaves that can be returned by a neighbour search
+  uint32_t n_skipped = 0;  // non-finite points of the last build
+  uint32_t n_flagged = 0;  // leaves flagged -1 (reachable by the radius searches only)
+  int final_buf = 0;       // pairs[final_buf]: sorted (key << 32 | point index) of the last build
+  int pass_hint = 2;       // radix passes queued by the next build (corrected by the device when wrong)
   uint64_t launches = 0;   // kernels launched by builds on this grid
+  int last_build_launches = 0;
   // hot
   VoxRec* recs = nullptr;
   HashSlot* table = nullptr;
@@ -21,28 +55,28 @@ struct DeviceGrid {
   double *c_mean = nullptr, *c_cov = nullptr, *c_icov = nullptr, *c_evecs = nullptr, *c_evals = nullptr;
   size_t vox_alloc = 0;
   // scratch sized by the target cloud
-  uint32_t *keys[2] = {nullptr, nullptr}, *vals[2] = {nullptr, nullptr};
-  uint32_t *hist = nullptr, *seg_start = nullptr, *block_counts = nullptr;
-  size_t pts_alloc = 0, hist_alloc = 0;
+  unsigned long long* pairs[2] = {nullptr, nullptr};   // (voxel key << 32 | point index), ping-pong of the radix sort
+  uint32_t *hist = nullptr, *seg_start = nullptr;
+  double* vox_sums = nullptr;               // [V][9] Sum x, Sum x x^T of the heavy leaves (heavy-sums kernel -> statistics kernel)
+  unsigned long long* seg_state = nullptr;  // look-back state of the segment kernel, one word per tile
+  size_t pts_alloc = 0;
   int* d_bbox = nullptr;            // 6 ordered ints
-  unsigned int* d_counters = nullptr;  // [0] skipped points, [1] V, [2] valid leaves
-  int* h_pinned = nullptr;          // 16 ints of pinned host memory for the small read-backs
-  double* sorted_xyz = nullptr;     // target points in voxel order (input order inside a voxel), widened to FP64, 3 per point
-  double* vox_sums = nullptr;       // [V][9] Sum x, Sum x x^T per voxel (k4a -> k4b)
-  uint32_t* digit_totals = nullptr; // 256 per-digit totals of the current radix pass
-  unsigned int* d_ticket = nullptr; // last-block-done tickets of the bbox / finalize kernels
-  volatile unsigned long long* h_slots = nullptr;  // pinned self-validating slots the kernels publish to (bbox 0..5, counters 8..10)
+  uint32_t* digit_base = nullptr;   // exclusive scan of the digit totals of the current radix pass (256)
+  BuildMeta* d_meta = nullptr;
+  volatile unsigned long long* h_slots = nullptr;  // pinned self-validating slots: BUILD_META_WORDS words of BuildMeta
   unsigned long long slot_seq = 0;
+  unsigned int epoch = 0;           // tags the look-back states of one build
 };
 
-// Returns NDTB_OK / NDTB_ERR_* ; synchronises the stream twice (bbox read-back, final counters).
+// Returns NDTB_OK / NDTB_ERR_*.  The kernels of a build run back to back; the host waits once, for the published BuildMeta.
 int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resolution, int min_pts, double eig_mult, int flavour,
                     int is_dense, cudaStream_t stream);
 void free_device_grid(DeviceGrid& g);
 int voxelgrid_downsample(DeviceGrid& scratch, const float4* d_pts, size_t n, float leaf, int is_dense, float4* d_out, size_t* n_out,
                          cudaStream_t stream);
 
-// voxel_finalize.cu
-void launch_voxel_finalize(const DeviceGrid& g, uint32_t n_points_upper, unsigned long long publish_key, cudaStream_t stream);
+// voxel_finalize.cu: per-leaf statistics (sums in input order, mean / covariance / eigen-inflation / inverse, hot record, hash insert);
+// its last block publishes BuildMeta to the host slots.
+void launch_voxel_stats(const DeviceGrid& g, const float4* d_pts, uint32_t n_points, unsigned long long publish_key, cudaStream_t stream);
 
 }  // namespace ndtb

@@ -551,6 +551,7 @@ __device__ __forceinline__ int phase_a(const float4* __restrict__ src, int idx, 
           const float r2 = static_cast<float>(static_cast<double>(m.leaf) * static_cast<double>(m.leaf));
 #pragma unroll
           for (int q = 0; q < PROBES; ++q) {
+            if (FLAVOUR == FLAVOUR_PCLOMP && rows[q] < -1) rows[q] = -2 - rows[q];  // flagged leaf: still in the reference's kd-tree (voxel_finalize.cu)
             if (rows[q] >= 0) {
               const double* mu = recs[rows[q]].mean;
               const float dx = xt[0] - static_cast<float>(__ldg(mu)), dy = xt[1] - static_cast<float>(__ldg(mu + 1)), dz = xt[2] - static_cast<float>(__ldg(mu + 2));

@@ -55,7 +55,8 @@ __global__ void __launch_bounds__(128) score_kernel(const float4* __restrict__ s
       const int ox = off[0], oy = off[1], oz = off[2];
       if (m.min_b[0] - i0 > ox || m.max_b[0] - i0 < ox || m.min_b[1] - i1 > oy || m.max_b[1] - i1 < oy || m.min_b[2] - i2 > oz || m.max_b[2] - i2 < oz) continue;
       const int lin = (i0 + ox - m.min_b[0]) * m.divb_mul[0] + (i1 + oy - m.min_b[1]) * m.divb_mul[1] + (i2 + oz - m.min_b[2]) * m.divb_mul[2];
-      const int row = hash_find(table, m.hash_mask, static_cast<uint32_t>(lin));
+      int row = hash_find(table, m.hash_mask, static_cast<uint32_t>(lin));
+      if (probes == 27 && row < -1) row = -2 - row;   // flagged leaf: still in the reference's kd-tree (voxel_finalize.cu)
       if (row < 0) continue;
       if (probes == 27) {  // radiusSearch over float(leaf.mean_): L2_Simple<float>, dist < float(r * r)
         const float r2 = static_cast<float>(static_cast<double>(m.leaf) * static_cast<double>(m.leaf));
@@ -113,7 +114,8 @@ __global__ void __launch_bounds__(128) score_map_kernel(const float4* __restrict
       const int ox = off[0], oy = off[1], oz = off[2];
       if (m.min_b[0] - i0 > ox || m.max_b[0] - i0 < ox || m.min_b[1] - i1 > oy || m.max_b[1] - i1 < oy || m.min_b[2] - i2 > oz || m.max_b[2] - i2 < oz) continue;
       const int lin = (i0 + ox - m.min_b[0]) * m.divb_mul[0] + (i1 + oy - m.min_b[1]) * m.divb_mul[1] + (i2 + oz - m.min_b[2]) * m.divb_mul[2];
-      const int row = hash_find(table, m.hash_mask, static_cast<uint32_t>(lin));
+      int row = hash_find(table, m.hash_mask, static_cast<uint32_t>(lin));
+      if (probes == 27 && row < -1) row = -2 - row;   // flagged leaf: still in the reference's kd-tree (voxel_finalize.cu)
       if (row < 0) continue;
       if (probes == 27) {
         const float r2 = static_cast<float>(static_cast<double>(m.leaf) * static_cast<double>(m.leaf));

@@ -70,7 +70,8 @@ struct MgEvalState {
 // flight), so a heavy leaf costs one dependent FADD per point instead of one dependent global load.
 constexpr int CEN_THREADS = 128;
 constexpr int CEN_HEAVY = 64;
-__global__ void __launch_bounds__(CEN_THREADS) mg_centroid_kernel(const double* __restrict__ sorted_xyz, const uint32_t* __restrict__ seg_start, uint32_t V,
+__global__ void __launch_bounds__(CEN_THREADS) mg_centroid_kernel(const float4* __restrict__ pts, const unsigned long long* __restrict__ vals,
+                                                                  const uint32_t* __restrict__ seg_start, uint32_t V,
                                                                   uint32_t n_valid_pts, float4* __restrict__ out) {
   __shared__ float s_tile[CEN_THREADS / 32][3][32];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -83,16 +84,16 @@ __global__ void __launch_bounds__(CEN_THREADS) mg_centroid_kernel(const double* 
     const bool heavy = n > CEN_HEAVY;
     float s0 = 0.f, s1 = 0.f, s2 = 0.f;
     if (has && !heavy) {
-      const double* q = sorted_xyz + 3 * static_cast<size_t>(lo);
+      const unsigned long long* q = vals + lo;   // the leaf's (key << 32 | point index) elements, input order (stable sort)
       int i = 0;
       for (; i + 4 <= n; i += 4) {
-        float t[12];
+        float4 t[4];
 #pragma unroll
-        for (int u = 0; u < 12; ++u) t[u] = static_cast<float>(__ldg(q + 3 * i + u));  // exact: widened floats
+        for (int u = 0; u < 4; ++u) t[u] = __ldg(pts + static_cast<uint32_t>(__ldg(q + i + u)));
 #pragma unroll
-        for (int u = 0; u < 4; ++u) { s0 += t[3 * u]; s1 += t[3 * u + 1]; s2 += t[3 * u + 2]; }
+        for (int u = 0; u < 4; ++u) { s0 += t[u].x; s1 += t[u].y; s2 += t[u].z; }
       }
-      for (; i < n; ++i) { s0 += static_cast<float>(__ldg(q + 3 * i)); s1 += static_cast<float>(__ldg(q + 3 * i + 1)); s2 += static_cast<float>(__ldg(q + 3 * i + 2)); }
+      for (; i < n; ++i) { const float4 t = __ldg(pts + static_cast<uint32_t>(__ldg(q + i))); s0 += t.x; s1 += t.y; s2 += t.z; }
     }
     unsigned int hm = __ballot_sync(0xffffffffu, heavy);
     while (hm) {
@@ -100,14 +101,14 @@ __global__ void __launch_bounds__(CEN_THREADS) mg_centroid_kernel(const double* 
       hm &= hm - 1;
       const uint32_t wlo = __shfl_sync(0xffffffffu, lo, o);
       const int wn = __shfl_sync(0xffffffffu, n, o);
-      const double* q = sorted_xyz + 3 * static_cast<size_t>(wlo);
+      const unsigned long long* q = vals + wlo;
       float acc = 0.f;
       float x = 0.f, y = 0.f, z = 0.f;
-      if (lane < wn) { x = static_cast<float>(__ldg(q + 3 * lane)); y = static_cast<float>(__ldg(q + 3 * lane + 1)); z = static_cast<float>(__ldg(q + 3 * lane + 2)); }
+      if (lane < wn) { const float4 t = __ldg(pts + static_cast<uint32_t>(__ldg(q + lane))); x = t.x; y = t.y; z = t.z; }
       for (int base = 0; base < wn; base += 32) {
         s_tile[w][0][lane] = x; s_tile[w][1][lane] = y; s_tile[w][2][lane] = z;
         const int nxt = base + 32 + lane;
-        if (nxt < wn) { x = static_cast<float>(__ldg(q + 3 * nxt)); y = static_cast<float>(__ldg(q + 3 * nxt + 1)); z = static_cast<float>(__ldg(q + 3 * nxt + 2)); }
+        if (nxt < wn) { const float4 t = __ldg(pts + static_cast<uint32_t>(__ldg(q + nxt))); x = t.x; y = t.y; z = t.z; }
         __syncwarp();
         const int cnt = min(32, wn - base);
         if (lane < 3) {
@@ -319,6 +320,7 @@ __global__ void __launch_bounds__(MG_THREADS, MG_CTAS_PER_SM) mg_eval_kernel(con
               v = __ldg(reinterpret_cast<const uint2*>(G.table) + b);
             }
             rows[q] = (v.x == HASH_EMPTY) ? -1 : static_cast<int>(v.y);
+            if (rows[q] < -1) rows[q] = -2 - rows[q];  // flagged leaf (nr_points_ = -1): computeLeafParams keeps it in the node and the kd-tree (multi_voxel_grid_covariance_omp_impl.hpp:369-389)
           }
           float4 cen[9];
 #pragma unroll
@@ -506,8 +508,8 @@ int ndtb_mg_add_target(ndtb_handle h, const char* grid_id, const float* xyz, siz
     CKH(cudaMalloc(&g->d_centroid, sizeof(float4) * V));
     g->centroid_alloc = V;
   }
-  const uint32_t n_valid_pts = static_cast<uint32_t>(n) - static_cast<uint32_t>(g->grid.h_pinned[0]);
-  mg_centroid_kernel<<<std::min<int>((V + CEN_THREADS - 1) / CEN_THREADS, 148 * 8), CEN_THREADS, 0, h->stream>>>(g->grid.sorted_xyz, g->grid.seg_start, V, n_valid_pts, g->d_centroid);
+  const uint32_t n_valid_pts = static_cast<uint32_t>(n) - g->grid.n_skipped;
+  mg_centroid_kernel<<<std::max(1, std::min<int>((V + CEN_THREADS - 1) / CEN_THREADS, 148 * 8)), CEN_THREADS, 0, h->stream>>>(s->d_in, g->grid.pairs[g->grid.final_buf], g->grid.seg_start, V, n_valid_pts, g->d_centroid);
   g->grid.launches += 1;
   h->launches += g->grid.launches - launches_before;  // ndtb_get_launch_count: the per-tile builds are this handle's kernels too
   CKH(cudaGetLastError());
@@ -545,7 +547,7 @@ int ndtb_mg_create_kdtree(ndtb_handle h) {
     d.meta = g->grid.meta; d.table = g->grid.table; d.c_mean = g->grid.c_mean; d.c_icov = g->grid.c_icov; d.centroid = g->d_centroid;
     tab.push_back(d);
     s->tree_ids.push_back(kv.first);
-    s->tree_leaves += g->grid.n_valid;
+    s->tree_leaves += g->grid.n_valid + g->grid.n_flagged;
   }
   if (tab.size() > 2047) return set_error(h, NDTB_ERR_INVALID, "multigrid: at most 2047 targets in one kd-tree");
   if (static_cast<int>(tab.size()) > s->table_alloc) {
@@ -607,7 +609,7 @@ int ndtb_mg_get_leaves(ndtb_handle h, size_t capacity, int32_t* nr_points, doubl
     CKH(cudaMemcpy(ic.data(), g->grid.c_icov, sizeof(double) * 9 * V, cudaMemcpyDeviceToHost));
     CKH(cudaMemcpy(cen.data(), g->d_centroid, sizeof(float4) * V, cudaMemcpyDeviceToHost));
     for (size_t v = 0; v < V; ++v) {
-      if (n[v] < h->params.min_points_per_voxel) continue;  // dropped by applyFilter :345-347 (and the flagged -1 leaves: unreachable, cov >= I(n-1)/n^2)
+      if (n[v] < h->params.min_points_per_voxel && n[v] != -1) continue;  // dropped by applyFilter :369-372; leaves flagged -1 by computeLeafParams stay in the node
       if (k < capacity) {
         if (nr_points) nr_points[k] = n[v];
         if (mean) std::memcpy(mean + 3 * k, &m[3 * v], 24);

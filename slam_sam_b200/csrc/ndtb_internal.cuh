@@ -92,4 +92,23 @@ __device__ __forceinline__ int hash_find(const HashSlot* __restrict__ table, uin
   }
 }
 
+// Programmatic dependent launch (sm_90+): the kernels of a build are a chain, each consuming what the previous one wrote.  Every
+// kernel first waits for its predecessor to have completed and flushed (griddepcontrol.wait -- a no-op when the launch carries
+// no programmatic dependency), then lets its successor be launched: the successor's CTAs are scheduled while this kernel's
+// last CTAs drain and sit at their own wait, so launch latency and CTA ramp-up leave the critical path.
+__device__ __forceinline__ void pdl_enter() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;");
+}
+template <class... KArgs, class... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 }  // namespace ndtb

@@ -1,50 +1,84 @@
 // Host driver of the target voxel-map build: setInputTarget -> VoxelGridCovariance::filter()
 // (ndt_omp.h:324-330, voxel_grid_covariance_omp_impl.hpp:55-364; svn_ndt_impl.hpp:137-159,
-// voxel_grid_covariance_impl.hpp:77-379).  See voxel_build_kernels.cuh for the kernels.
+// voxel_grid_covariance_impl.hpp:77-379).  See voxel_build_kernels.cuh / voxel_finalize.cu for the kernels.
+//
+// The kernels of one build are queued back to back and never wait for the host: the grid geometry, the radix plan, the leaf
+// count and the hash capacity are derived on the device (BuildMeta).  The host waits ONCE, for the BuildMeta the last kernel
+// publishes into pinned self-validating slots.  The only thing the host has to guess is how many radix passes to queue
+// (DeviceGrid::pass_hint: digits of <= 10 bits, 2 passes up to 1 M cells); a wrong guess is reported by the device and the
+// build is queued again with the right count.
 #include "voxel_build_kernels.cuh"
-#include "../../include/ndtb.h"
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <algorithm>
 
 namespace ndtb {
 
+// Development aid: NDTB_BUILD_TIMING=1 records a CUDA event after every launch of a build and prints the per-kernel times.
+static const bool g_build_timing = getenv("NDTB_BUILD_TIMING") != nullptr;
+static cudaEvent_t g_tev[32];
+static const char* g_tname[32];
+static int g_tn = 0;
+static void tmark(const char* name, cudaStream_t s) {
+  if (!g_build_timing || g_tn >= 32) return;
+  if (!g_tev[g_tn]) cudaEventCreate(&g_tev[g_tn]);
+  cudaEventRecord(g_tev[g_tn], s); g_tname[g_tn] = name; ++g_tn;
+}
+static void tprint() {
+  if (!g_build_timing || g_tn < 2) { g_tn = 0; return; }
+  cudaEventSynchronize(g_tev[g_tn - 1]);
+  float tot = 0; cudaEventElapsedTime(&tot, g_tev[0], g_tev[g_tn - 1]);
+  fprintf(stderr, "[build timing] total %.1f us:", tot * 1e3f);
+  for (int i = 1; i < g_tn; ++i) { float ms = 0; cudaEventElapsedTime(&ms, g_tev[i - 1], g_tev[i]); fprintf(stderr, " %s %.1f", g_tname[i], ms * 1e3f); }
+  fprintf(stderr, "\n"); g_tn = 0;
+}
+
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return NDTB_ERR_CUDA; } while (0)
 
 static int ensure_capacity(DeviceGrid& g, size_t n, bool voxel_arrays) {
   if (!g.d_bbox) {
     CK(cudaMalloc(&g.d_bbox, 6 * sizeof(int)));
-    CK(cudaMalloc(&g.d_counters, 4 * sizeof(unsigned int)));
-    CK(cudaMallocHost(&g.h_pinned, 16 * sizeof(int)));
-    CK(cudaMalloc(&g.digit_totals, 256 * sizeof(uint32_t)));
-    CK(cudaMalloc(&g.d_ticket, 2 * sizeof(unsigned int)));
-    CK(cudaMemset(g.d_ticket, 0, 2 * sizeof(unsigned int)));
-    CK(cudaMallocHost(&g.h_slots, 32 * sizeof(unsigned long long)));
-    std::memset(const_cast<unsigned long long*>(g.h_slots), 0, 32 * sizeof(unsigned long long));
+    int init[6];
+    init[0] = init[1] = init[2] = 0x7f7fffff;                                     // ordered encoding of +FLT_MAX
+    init[3] = init[4] = init[5] = static_cast<int>(0xff7fffffu) ^ 0x7fffffff;     // ordered encoding of -FLT_MAX
+    CK(cudaMemcpy(g.d_bbox, init, sizeof(init), cudaMemcpyHostToDevice));         // the bbox kernel re-arms it after every build
+    CK(cudaMalloc(&g.d_meta, sizeof(BuildMeta)));
+    CK(cudaMemset(g.d_meta, 0, sizeof(BuildMeta)));
+    CK(cudaMalloc(&g.digit_base, RS_MAX_BINS * sizeof(uint32_t)));
+    CK(cudaMallocHost(&g.h_slots, 2 * BUILD_META_WORDS * sizeof(unsigned long long)));
+    std::memset(const_cast<unsigned long long*>(g.h_slots), 0, 2 * BUILD_META_WORDS * sizeof(unsigned long long));
+    static bool configured = false;
+    if (!configured) {
+      CK(cudaFuncSetAttribute(radix_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(RS_SCATTER_SMEM)));
+      configured = true;
+    }
   }
   if (n > g.pts_alloc) {
-    for (int i = 0; i < 2; ++i) { cudaFree(g.keys[i]); cudaFree(g.vals[i]); g.keys[i] = nullptr; g.vals[i] = nullptr; }
-    cudaFree(g.seg_start); cudaFree(g.block_counts); cudaFree(g.hist); cudaFree(g.sorted_xyz); cudaFree(g.c_key);
+    for (int i = 0; i < 2; ++i) { cudaFree(g.pairs[i]); g.pairs[i] = nullptr; }
+    cudaFree(g.seg_start); cudaFree(g.seg_state); cudaFree(g.hist); cudaFree(g.c_key);
     // nothing dangles if an allocation below fails: the capacity is only set once all of them succeeded
-    g.seg_start = nullptr; g.block_counts = nullptr; g.hist = nullptr; g.sorted_xyz = nullptr; g.c_key = nullptr;
+    g.seg_start = nullptr; g.seg_state = nullptr; g.hist = nullptr; g.c_key = nullptr;
     g.pts_alloc = 0;
     const size_t cap = n + n / 8 + 1024;
-    CK(cudaMalloc(&g.sorted_xyz, cap * 3 * sizeof(double)));
     CK(cudaMalloc(&g.c_key, cap * 4));  // leaf keys, written with the segments
-    for (int i = 0; i < 2; ++i) { CK(cudaMalloc(&g.keys[i], cap * 4)); CK(cudaMalloc(&g.vals[i], cap * 4)); }
+    for (int i = 0; i < 2; ++i) CK(cudaMalloc(&g.pairs[i], cap * 8));
     CK(cudaMalloc(&g.seg_start, (cap + 1) * 4));
     const size_t nb = (cap + RS_TILE - 1) / RS_TILE + 1;
-    CK(cudaMalloc(&g.block_counts, nb * 4));
-    CK(cudaMalloc(&g.hist, nb * 256 * 4));
+    const size_t nseg = (cap + SEG_TILE - 1) / SEG_TILE + 1;
+    CK(cudaMalloc(&g.seg_state, nseg * sizeof(unsigned long long)));
+    CK(cudaMemset(g.seg_state, 0, nseg * sizeof(unsigned long long)));
+    CK(cudaMalloc(&g.hist, nb * RS_MAX_BINS * 4));
     g.pts_alloc = cap;
   }
   if (voxel_arrays && n > g.vox_alloc) {  // voxel arrays: V <= n (not needed by the down-sampling scratch)
     const size_t cap = n + n / 8 + 1024;
     cudaFree(g.recs); cudaFree(g.c_n); cudaFree(g.c_mean); cudaFree(g.c_cov); cudaFree(g.c_icov);
-    cudaFree(g.c_evecs); cudaFree(g.c_evals); cudaFree(g.vox_sums);
-    g.recs = nullptr; g.c_n = nullptr; g.c_mean = g.c_cov = g.c_icov = g.c_evecs = g.c_evals = nullptr; g.vox_sums = nullptr;
-    g.vox_alloc = 0;
+    cudaFree(g.c_evecs); cudaFree(g.c_evals); cudaFree(g.table); cudaFree(g.vox_sums);
+    g.vox_sums = nullptr; g.recs = nullptr; g.c_n = nullptr; g.c_mean = g.c_cov = g.c_icov = g.c_evecs = g.c_evals = nullptr; g.table = nullptr;
+    g.vox_alloc = 0; g.table_alloc = 0;
     CK(cudaMalloc(&g.vox_sums, cap * 72));
     CK(cudaMalloc(&g.recs, cap * sizeof(VoxRec)));
     CK(cudaMalloc(&g.c_n, cap * 4));
@@ -53,31 +87,35 @@ static int ensure_capacity(DeviceGrid& g, size_t n, bool voxel_arrays) {
     CK(cudaMalloc(&g.c_icov, cap * 72));
     CK(cudaMalloc(&g.c_evecs, cap * 72));
     CK(cudaMalloc(&g.c_evals, cap * 24));
+    // hash table for the worst case: 2^m >= 2 n slots (the build uses, and clears, 2^m' >= 2 min(n, cells) of them)
+    size_t tcap = 16;
+    while (tcap < 2 * cap) tcap <<= 1;
+    CK(cudaMalloc(&g.table, tcap * sizeof(HashSlot)));
+    g.table_alloc = tcap;
     g.vox_alloc = cap;
   }
   return NDTB_OK;
 }
 
 void free_device_grid(DeviceGrid& g) {
-  for (int i = 0; i < 2; ++i) { cudaFree(g.keys[i]); cudaFree(g.vals[i]); }
-  cudaFree(g.seg_start); cudaFree(g.block_counts); cudaFree(g.hist); cudaFree(g.sorted_xyz); cudaFree(g.vox_sums); cudaFree(g.digit_totals); cudaFree(g.d_ticket);
+  for (int i = 0; i < 2; ++i) cudaFree(g.pairs[i]);
+  cudaFree(g.seg_start); cudaFree(g.seg_state); cudaFree(g.hist); cudaFree(g.digit_base); cudaFree(g.d_meta);
   if (g.h_slots) cudaFreeHost(const_cast<unsigned long long*>(g.h_slots));
-  cudaFree(g.recs); cudaFree(g.table); cudaFree(g.c_key); cudaFree(g.c_n); cudaFree(g.c_mean); cudaFree(g.c_cov);
-  cudaFree(g.c_icov); cudaFree(g.c_evecs); cudaFree(g.c_evals); cudaFree(g.d_bbox); cudaFree(g.d_counters);
-  if (g.h_pinned) cudaFreeHost(g.h_pinned);
+  cudaFree(g.vox_sums); cudaFree(g.recs); cudaFree(g.table); cudaFree(g.c_key); cudaFree(g.c_n); cudaFree(g.c_mean); cudaFree(g.c_cov);
+  cudaFree(g.c_icov); cudaFree(g.c_evecs); cudaFree(g.c_evals); cudaFree(g.d_bbox);
   const uint64_t keep = g.launches;
   g = DeviceGrid();
   g.launches = keep;
 }
 
-// Poll `count` self-validating host slots starting at `first` (see publish_slot); a stream query
-// every 4096 spins catches a failed kernel.
-static int wait_slots(DeviceGrid& g, int first, int count, unsigned long long key, cudaStream_t stream) {
+// Poll the BuildMeta slots (see publish_slot); a stream query every 4096 spins catches a failed kernel.
+static int wait_meta(DeviceGrid& g, unsigned long long key, cudaStream_t stream, BuildMeta* out) {
   unsigned int spins = 0;
-  for (int i = first + count - 1; i >= first; --i) {
+  unsigned long long words[BUILD_META_WORDS];
+  for (int i = BUILD_META_WORDS - 1; i >= 0; --i) {
     for (;;) {
       const unsigned long long w0 = g.h_slots[2 * i], w1 = g.h_slots[2 * i + 1];
-      if ((w0 ^ w1) == key) break;
+      if ((w0 ^ w1) == key) { words[i] = w0; break; }
       if ((++spins & 4095u) == 0) {
         const cudaError_t q = cudaStreamQuery(stream);
         if (q != cudaSuccess && q != cudaErrorNotReady) return NDTB_ERR_CUDA;
@@ -89,81 +127,50 @@ static int wait_slots(DeviceGrid& g, int first, int count, unsigned long long ke
     }
   }
   __sync_synchronize();
+  std::memcpy(out, words, sizeof(BuildMeta));
   return NDTB_OK;
 }
 
-// bbox -> grid geometry -> voxel keys -> stable radix sort -> segments (one per occupied leaf, ascending linear index).
-// Leaves g.meta, g.keys/vals[*cur], g.seg_start, g.c_key and d_counters[0] (skipped points) / [1] (leaf count) ready on the stream.
-static int sort_into_segments(DeviceGrid& g, const float4* d_pts, int ni, float resolution, int min_pts, double eig_mult, int flavour,
-                              int is_dense, cudaStream_t stream, int* cur_out, int* passes_out) {
-  const size_t n = static_cast<size_t>(ni);
-
-  // ---- k0: bounding box (pcl::getMinMax3D); the last block publishes it to pinned host slots -----------
-  {
-    int init[6];
-    init[0] = init[1] = init[2] = 0x7f7fffff;                                     // ordered encoding of +FLT_MAX
-    init[3] = init[4] = init[5] = static_cast<int>(0xff7fffffu) ^ 0x7fffffff;     // ordered encoding of -FLT_MAX
-    std::memcpy(g.h_pinned, init, sizeof(init));
-    CK(cudaMemcpyAsync(g.d_bbox, g.h_pinned, sizeof(init), cudaMemcpyHostToDevice, stream));
-    const int blocks = std::min((ni + BBOX_THREADS - 1) / BBOX_THREADS, 148 * 4);
-    const unsigned long long key = 0x9E3779B97F4A7C15ull * (++g.slot_seq) | 1ull;
-    bbox_kernel<<<blocks, BBOX_THREADS, 0, stream>>>(d_pts, ni, is_dense, g.d_bbox, g.d_ticket, g.h_slots, key);
-    CK(cudaGetLastError());
-    int rc2 = wait_slots(g, 0, 6, key, stream);
-    if (rc2 != NDTB_OK) return rc2;
-    for (int a = 0; a < 6; ++a) g.h_pinned[a] = static_cast<int>(static_cast<unsigned int>(g.h_slots[2 * a]));
-  }
-  float min_p[3], max_p[3];
-  for (int a = 0; a < 3; ++a) { min_p[a] = ordered_to_float_bits(g.h_pinned[a]); max_p[a] = ordered_to_float_bits(g.h_pinned[3 + a]); }
-
-  // ---- grid geometry on the host, float maths as in applyFilter :83-113 ---------------------
-  GridMeta& m = g.meta;
-  m.leaf = resolution;
-  m.inv_leaf = 1.0f / resolution;  // pcl::VoxelGrid::setLeafSize
-  m.min_pts = min_pts; m.flavour = flavour; m.eig_mult = eig_mult;
-  const int64_t dx = static_cast<int64_t>((max_p[0] - min_p[0]) * m.inv_leaf) + 1;
-  const int64_t dy = static_cast<int64_t>((max_p[1] - min_p[1]) * m.inv_leaf) + 1;
-  const int64_t dz = static_cast<int64_t>((max_p[2] - min_p[2]) * m.inv_leaf) + 1;
-  if (flavour == FLAVOUR_SVN && (dx < 0 || dy < 0 || dz < 0)) return NDTB_ERR_OVERFLOW;
-  if ((dx * dy * dz) > static_cast<int64_t>(std::numeric_limits<int32_t>::max())) return NDTB_ERR_OVERFLOW;
-  for (int a = 0; a < 3; ++a) {
-    m.min_b[a] = static_cast<int>(std::floor(min_p[a] * m.inv_leaf));
-    m.max_b[a] = static_cast<int>(std::floor(max_p[a] * m.inv_leaf));
-    m.div_b[a] = m.max_b[a] - m.min_b[a] + 1;
-    m.lo_bound[a] = static_cast<float>(m.min_b[a]) * m.leaf;
-    m.hi_bound[a] = static_cast<float>(m.max_b[a] + 1) * m.leaf;
-  }
-  m.divb_mul[0] = 1; m.divb_mul[1] = m.div_b[0]; m.divb_mul[2] = m.div_b[0] * m.div_b[1];
-  const int64_t cells = static_cast<int64_t>(m.div_b[0]) * m.div_b[1] * m.div_b[2];
-  if (cells > static_cast<int64_t>(std::numeric_limits<int32_t>::max())) return NDTB_ERR_OVERFLOW;
-  m.total_cells = static_cast<uint32_t>(cells);
-
-  (void)n;
-  CK(cudaMemsetAsync(g.d_counters, 0, 4 * sizeof(unsigned int), stream));
-
-  // ---- k1 + k2: keys (fused into the first histogram) and the stable LSD radix sort over the significant key bits
-  int bits = 1;
-  while (bits < 32 && (static_cast<uint64_t>(m.total_cells) >> bits) != 0) ++bits;  // key <= total_cells
-  const int passes = (bits + 7) / 8;
+// Queues bbox -> geometry -> voxel keys -> stable radix sort -> segments (one per occupied leaf, ascending linear index).
+// Leaves BuildMeta, keys/vals[final_buf], seg_start, c_key ready on the stream; nothing is waited for.
+static int queue_sort_into_segments(DeviceGrid& g, const float4* d_pts, int ni, float resolution, int min_pts, double eig_mult, int flavour,
+                                    int is_dense, int passes, cudaStream_t stream, int* launches) {
+  BuildParams prm;
+  prm.resolution = resolution;
+  prm.inv_leaf = 1.0f / resolution;  // pcl::VoxelGrid::setLeafSize
+  prm.min_pts = min_pts; prm.flavour = flavour; prm.is_dense = is_dense; prm.eig_mult = eig_mult;
+  prm.n = ni; prm.passes_queued = passes;
+  const int bb_blocks = std::min((ni + BBOX_THREADS - 1) / BBOX_THREADS, 148 * 4);
+  tmark("start", stream);
+  launch_pdl(bbox_kernel, dim3(bb_blocks), dim3(BBOX_THREADS), 0, stream, d_pts, g.d_bbox, g.d_meta, &g.d_meta->tickets[0], prm);
+  tmark("bbox", stream);
   const int nb = (ni + RS_TILE - 1) / RS_TILE;
-  int cur = 0;
   for (int p = 0; p < passes; ++p) {
-    if (p == 0) radix_hist_kernel<true><<<nb, RS_THREADS, 0, stream>>>(d_pts, m, is_dense, g.keys[0], ni, 0, g.hist, nb, g.d_counters);
-    else radix_hist_kernel<false><<<nb, RS_THREADS, 0, stream>>>(nullptr, m, is_dense, g.keys[cur], ni, 8 * p, g.hist, nb, g.d_counters);
-    radix_scan_kernel<<<256, 256, 0, stream>>>(g.hist, nb, g.digit_totals);
-    if (p == 0) radix_scatter_kernel<true><<<nb, RS_THREADS, 0, stream>>>(g.keys[0], nullptr, g.keys[1], g.vals[1], ni, 0, g.hist, nb, g.digit_totals);
-    else radix_scatter_kernel<false><<<nb, RS_THREADS, 0, stream>>>(g.keys[cur], g.vals[cur], g.keys[cur ^ 1], g.vals[cur ^ 1], ni, 8 * p, g.hist, nb, g.digit_totals);
-    cur ^= 1;
+    if (p == 0) launch_pdl(radix_hist_kernel<true>, dim3(nb), dim3(RS_THREADS), 0, stream, d_pts, g.d_meta, is_dense, g.pairs[0], g.pairs[1], ni, 0, g.hist, nb);
+    else launch_pdl(radix_hist_kernel<false>, dim3(nb), dim3(RS_THREADS), 0, stream, static_cast<const float4*>(nullptr), g.d_meta, is_dense, g.pairs[0], g.pairs[1], ni, p, g.hist, nb);
+    tmark("hist", stream);
+    launch_pdl(radix_scan_kernel, dim3(RS_MAX_BINS / 8), dim3(256), 0, stream, g.d_meta, p, g.hist, nb, g.digit_base);
+    tmark("scan", stream);
+    launch_pdl(radix_scatter_kernel, dim3(nb), dim3(RS_THREADS), RS_SCATTER_SMEM, stream, g.d_meta, p, g.pairs[0], g.pairs[1], ni, g.hist, nb, g.digit_base);
+    tmark("scatter", stream);
   }
-
-  // ---- k3: segments -> voxel numbering in ascending linear index; points gathered into sorted order -----
   const int sb = (ni + SEG_TILE - 1) / SEG_TILE;
-  seg_count_kernel<<<sb, SEG_THREADS, 0, stream>>>(g.keys[cur], ni, m.total_cells, g.block_counts);
-  scan_small_kernel<<<1, 1024, 0, stream>>>(g.block_counts, sb, g.d_counters + 1);
-  seg_write_kernel<<<sb, SEG_THREADS, 0, stream>>>(g.keys[cur], ni, m.total_cells, g.block_counts, g.seg_start, g.c_key);
+  launch_pdl(seg_kernel, dim3(sb), dim3(SEG_THREADS), 0, stream, g.d_meta, g.pairs[0], g.pairs[1], ni, g.seg_state, ++g.epoch, g.seg_start, g.c_key);
+  tmark("seg", stream);
   CK(cudaGetLastError());
-  *cur_out = cur;
-  *passes_out = passes;
+  *launches = 1 + 3 * passes + 1;
+  return NDTB_OK;
+}
+
+// Takes the published BuildMeta over: error -> return code (a wrong pass guess asks for a retry through *retry_passes).
+static int adopt_meta(DeviceGrid& g, const BuildMeta& B, int* retry_passes) {
+  *retry_passes = 0;
+  if (B.error >= BUILD_NEED_PASSES) { *retry_passes = B.error - BUILD_NEED_PASSES; return NDTB_OK; }
+  if (B.error) return B.error;
+  g.meta = B.m;
+  g.V = B.V; g.n_valid = B.n_valid; g.n_skipped = B.n_skipped; g.n_flagged = B.n_flagged; g.final_buf = B.final_buf;
+  g.table_cap = static_cast<size_t>(B.m.hash_mask) + 1;
+  g.pass_hint = B.passes;   // the next build of a map like this one queues exactly the passes it needs
   return NDTB_OK;
 }
 
@@ -175,38 +182,29 @@ int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resoluti
   int rc = ensure_capacity(g, n, true);
   if (rc != NDTB_OK) return rc;
   const int ni = static_cast<int>(n);
-  int cur = 0, passes = 0;
-  rc = sort_into_segments(g, d_pts, ni, resolution, min_pts, eig_mult, flavour, is_dense, stream, &cur, &passes);
-  if (rc != NDTB_OK) return rc;
-  GridMeta& m = g.meta;
-  // ---- hash capacity: 2^m >= 2 * min(N, cells)  (load factor <= 0.5); the table is first touched by the finalize kernel
-  {
-    const uint64_t need = 2ull * std::min<uint64_t>(n, static_cast<uint64_t>(m.total_cells));
-    size_t cap = 16;
-    while (cap < need) cap <<= 1;
-    if (cap > g.table_alloc) {
-      cudaFree(g.table);
-      CK(cudaMalloc(&g.table, cap * sizeof(HashSlot)));
-      g.table_alloc = cap;
-    }
-    g.table_cap = cap;
-    m.hash_mask = static_cast<uint32_t>(cap - 1);
-    CK(cudaMemsetAsync(g.table, 0xFF, cap * sizeof(HashSlot), stream));
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    int launches = 0;
+    rc = queue_sort_into_segments(g, d_pts, ni, resolution, min_pts, eig_mult, flavour, is_dense, g.pass_hint, stream, &launches);
+    if (rc != NDTB_OK) return rc;
+    launch_pdl(hash_clear_kernel, dim3(148 * 2), dim3(256), 0, stream, g.d_meta, g.table);
+    tmark("clear", stream);
+    const unsigned long long key = 0x9E3779B97F4A7C15ull * (++g.slot_seq) | 1ull;
+    launch_voxel_stats(g, d_pts, static_cast<uint32_t>(ni), key, stream);
+    tmark("stats", stream);
+    CK(cudaGetLastError());
+    g.launches += static_cast<uint64_t>(launches) + 3;
+    g.last_build_launches = launches + 3;
+    BuildMeta B;
+    rc = wait_meta(g, key, stream, &B);
+    tprint();
+    if (rc != NDTB_OK) return rc;
+    int retry = 0;
+    rc = adopt_meta(g, B, &retry);
+    if (rc != NDTB_OK) return rc;
+    if (!retry) { g.built = true; return NDTB_OK; }
+    g.pass_hint = retry;
   }
-  gather_points_kernel<<<(ni + 255) / 256, 256, 0, stream>>>(d_pts, g.vals[cur], ni, g.sorted_xyz);
-
-  // ---- k4: per-voxel statistics + hash insert; its last block publishes the counters to the host ---------
-  const unsigned long long key = 0x9E3779B97F4A7C15ull * (++g.slot_seq) | 1ull;
-  launch_voxel_finalize(g, static_cast<uint32_t>(ni), key, stream);
-  g.launches += 1 + 3 * static_cast<uint64_t>(passes) + 4 + 2;  // bbox, radix passes, segments + gather, sums + finalize
-  CK(cudaGetLastError());
-  rc = wait_slots(g, 8, 3, key, stream);
-  if (rc != NDTB_OK) return rc;
-  for (int a = 0; a < 3; ++a) g.h_pinned[a] = static_cast<int>(static_cast<unsigned int>(g.h_slots[2 * (8 + a)]));
-  g.V = static_cast<uint32_t>(g.h_pinned[1]);
-  g.n_valid = static_cast<uint32_t>(g.h_pinned[2]);
-  g.built = true;
-  return NDTB_OK;
+  return NDTB_ERR_CUDA;
 }
 
 // pcl::VoxelGrid::filter on the device: same bbox / index / sort / segment machinery as the map build, then centroids.
@@ -217,18 +215,25 @@ int voxelgrid_downsample(DeviceGrid& g, const float4* d_pts, size_t n, float lea
   int rc = ensure_capacity(g, n, false);
   if (rc != NDTB_OK) return rc;
   const int ni = static_cast<int>(n);
-  int cur = 0, passes = 0;
-  rc = sort_into_segments(g, d_pts, ni, leaf, 0, 0.0, FLAVOUR_PCLOMP, is_dense, stream, &cur, &passes);
-  if (rc != NDTB_OK) return rc;
-  const unsigned long long key = 0x9E3779B97F4A7C15ull * (++g.slot_seq) | 1ull;
-  const int blocks = std::min((ni + 255) / 256, 148 * 8);
-  centroid_kernel<<<blocks, 256, 0, stream>>>(d_pts, g.vals[cur], g.seg_start, g.d_counters, static_cast<uint32_t>(ni), d_out, g.d_ticket + 1, g.h_slots, key);
-  CK(cudaGetLastError());
-  g.launches += 1 + 3 * static_cast<uint64_t>(passes) + 3 + 1;
-  rc = wait_slots(g, 12, 1, key, stream);
-  if (rc != NDTB_OK) return rc;
-  *n_out = static_cast<size_t>(static_cast<unsigned int>(g.h_slots[2 * 12]));
-  return NDTB_OK;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    int launches = 0;
+    rc = queue_sort_into_segments(g, d_pts, ni, leaf, 0, 0.0, FLAVOUR_PCLOMP, is_dense, g.pass_hint, stream, &launches);
+    if (rc != NDTB_OK) return rc;
+    const unsigned long long key = 0x9E3779B97F4A7C15ull * (++g.slot_seq) | 1ull;
+    const int blocks = std::min((ni + 255) / 256, 148 * 8);
+    launch_pdl(centroid_kernel, dim3(blocks), dim3(256), 0, stream, d_pts, g.d_meta, g.pairs[0], g.pairs[1], g.seg_start, static_cast<uint32_t>(ni), d_out, g.h_slots, key);
+    CK(cudaGetLastError());
+    g.launches += static_cast<uint64_t>(launches) + 1;
+    BuildMeta B;
+    rc = wait_meta(g, key, stream, &B);
+    if (rc != NDTB_OK) return rc;
+    int retry = 0;
+    rc = adopt_meta(g, B, &retry);
+    if (rc != NDTB_OK) return rc;
+    if (!retry) { *n_out = static_cast<size_t>(B.V); return NDTB_OK; }
+    g.pass_hint = retry;
+  }
+  return NDTB_ERR_CUDA;
 }
 
 }  // namespace ndtb

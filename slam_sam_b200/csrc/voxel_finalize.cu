@@ -1,5 +1,5 @@
-// k4: per-voxel statistics (SURVEY 8a rows a2 pass 1, a3, a11).
-// One thread per voxel.  The thread walks its segment of the (stably) sorted point list, i.e. its
+// k6: per-voxel statistics (SURVEY 8a rows a2 pass 1, a3, a11), see voxel_stats_kernel.
+// One lane per voxel.  The lane walks its segment of the (stably) sorted point list, i.e. its
 // points IN INPUT ORDER, and accumulates Sum x and Sum x x^T in FP64 exactly like the reference's
 // serial loop (voxel_grid_covariance_omp_impl.hpp:235-239 / voxel_grid_covariance_impl.hpp:237-239),
 // so means and covariances are reproduced bit for bit, not just to rounding.
@@ -133,26 +133,37 @@ __device__ __forceinline__ void hash_insert(HashSlot* table, uint32_t mask, uint
   }
 }
 
-constexpr int FIN_BATCH = 4;   // points per software-pipeline stage (light voxels)
-constexpr int FIN_HEAVY = 48;  // voxels with more points are summed by the whole warp
+constexpr int ST_THREADS = 128;   // 4 warps per CTA, every warp works on its own chunks
+constexpr int ST_CHUNK = 32;      // leaves per chunk: one per lane
+constexpr int ST_PIECE = 256;     // points staged in shared memory at a time (4 KB per warp)
+constexpr int ST_HEAVY = 48;      // leaves with more points are summed by the whole warp (voxel_heavy_sums_kernel)
+#ifndef ST_MIN_BLOCKS
+#define ST_MIN_BLOCKS 5            // 5 x 4 warps per SM: the 2632 chunks of an 84 k-leaf map are one resident wave
+#endif
 
 // Everything per voxel after the sums.  `n`, sums in; writes the cold arrays, the hot record and the hash slot.
 __device__ void finalize_voxel(uint32_t v, int n, double sx, double sy, double sz, double sxx, double sxy, double sxz, double syy, double syz, double szz,
                                const uint32_t* __restrict__ vox_key, const GridMeta& m, VoxRec* __restrict__ recs, HashSlot* __restrict__ table,
                                int32_t* __restrict__ c_n, double* __restrict__ c_mean, double* __restrict__ c_cov, double* __restrict__ c_icov,
-                               double* __restrict__ c_evecs, double* __restrict__ c_evals, unsigned int* __restrict__ n_valid_out);
+                               double* __restrict__ c_evecs, double* __restrict__ c_evals, unsigned int* __restrict__ n_valid_out, unsigned int* __restrict__ n_flagged_out);
 
-// k4a: per-voxel sums (Sum x, Sum x x^T in input order) -> vox_sums[v][0..8], one resident wave.
-__global__ void __launch_bounds__(128) voxel_sum_kernel(const double* __restrict__ sorted_xyz, const uint32_t* __restrict__ seg_start,
-                                                        const unsigned int* __restrict__ counters, uint32_t n_points,
-                                                        double* __restrict__ vox_sums) {
-  __shared__ double s_prod[4][32][9];
+// Sums of the HEAVY leaves (more than ST_HEAVY points), ahead of the statistics kernel.  Heavy leaves come in runs (a wall is a
+// row of equally dense voxels), so they are dealt to the warps through a multiplicative permutation of [0, Vr), Vr = V rounded up
+// to a warp (2654435761 is prime, hence coprime with Vr: t -> t * P mod Vr is a bijection): no warp collects a whole wall.  The
+// whole warp takes one heavy leaf at a time: 32 lanes load 32 points (indices coalesced, points from L2) and form the nine
+// products; lane c < 9 then runs chain c over those 32 points IN INPUT ORDER, so the nine serial FP64 chains advance in the same
+// instruction and a point costs one dependent DADD instead of nine.
+__global__ void __launch_bounds__(ST_THREADS) voxel_heavy_sums_kernel(const float4* __restrict__ pts, const BuildMeta* __restrict__ meta,
+                                                                      const unsigned long long* __restrict__ pairs0,
+                                                                      const unsigned long long* __restrict__ pairs1, const uint32_t* __restrict__ seg_start,
+                                                                      uint32_t n_points, double* __restrict__ vox_sums) {
+  __shared__ double s_prod[ST_THREADS / 32][32][9];
+  pdl_enter();
+  if (meta->error) return;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const uint32_t V = counters[1];
-  const uint32_t n_valid_pts = n_points - counters[0];
-  // Voxels are dealt to threads through a multiplicative permutation of [0, Vr), Vr = V rounded up to a warp:
-  // neighbouring voxels (a wall is a run of equally heavy voxels) land in different warps, so no warp collects
-  // all the long segments.  2654435761 is prime, hence coprime with Vr: t -> t * P mod Vr is a bijection.
+  const uint32_t V = meta->V;
+  const uint32_t n_valid_pts = n_points - meta->n_skipped;
+  const unsigned long long* pairs = meta->final_buf ? pairs1 : pairs0;
   const uint32_t Vr = (V + 31u) & ~31u;
   for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < Vr; t += gridDim.x * blockDim.x) {  // warp-uniform trip count
     const uint32_t v = static_cast<uint32_t>((static_cast<unsigned long long>(t) * 2654435761ull) % Vr);
@@ -160,59 +171,23 @@ __global__ void __launch_bounds__(128) voxel_sum_kernel(const double* __restrict
     const uint32_t lo = has ? seg_start[v] : 0u;
     const uint32_t hi = has ? ((v + 1 < V) ? seg_start[v + 1] : n_valid_pts) : 0u;
     const int n = static_cast<int>(hi - lo);
-    const bool heavy = n > FIN_HEAVY;
-    // sx sy sz sxx sxy sxz syy syz szz.  The reference's Leaf starts cov_ at identity and adds x x^T onto it
-    // (voxel_grid_covariance_omp.h:113 + _impl.hpp:239; svn voxel_grid_covariance.h:109 + _impl.hpp:240), so the
-    // diagonal chains start at 1.0, not 0.
-    double sum[9] = {0, 0, 0, 1.0, 0, 0, 1.0, 0, 1.0};
-    if (has && !heavy) {
-      // Light voxel: this lane adds its points IN INPUT ORDER (stable sort; already widened to FP64 by the
-      // gather kernel), loads software-pipelined one batch ahead of the sequential FP64 chains.
-      const double* q = sorted_xyz + 3 * static_cast<size_t>(lo);
-      double cur[3 * FIN_BATCH], nxt[3 * FIN_BATCH];
-      const int full = n / FIN_BATCH;
-      if (full > 0) {
-#pragma unroll
-        for (int u = 0; u < 3 * FIN_BATCH; ++u) cur[u] = __ldg(q + u);
-      }
-      for (int bt = 0; bt < full; ++bt) {
-        if (bt + 1 < full) {
-#pragma unroll
-          for (int u = 0; u < 3 * FIN_BATCH; ++u) nxt[u] = __ldg(q + 3 * FIN_BATCH * (bt + 1) + u);
-        }
-#pragma unroll
-        for (int u = 0; u < FIN_BATCH; ++u) {
-          const double x = cur[3 * u], y = cur[3 * u + 1], z = cur[3 * u + 2];
-          sum[0] += x; sum[1] += y; sum[2] += z;
-          sum[3] += x * x; sum[4] += x * y; sum[5] += x * z; sum[6] += y * y; sum[7] += y * z; sum[8] += z * z;
-        }
-#pragma unroll
-        for (int u = 0; u < 3 * FIN_BATCH; ++u) cur[u] = nxt[u];
-      }
-      for (int i = full * FIN_BATCH; i < n; ++i) {
-        const double x = __ldg(q + 3 * i), y = __ldg(q + 3 * i + 1), z = __ldg(q + 3 * i + 2);
-        sum[0] += x; sum[1] += y; sum[2] += z;
-        sum[3] += x * x; sum[4] += x * y; sum[5] += x * z; sum[6] += y * y; sum[7] += y * z; sum[8] += z * z;
-      }
-    }
-    // Heavy voxels: the whole warp takes them one at a time.  32 lanes load 32 points (coalesced) and form the
-    // nine products; lane c < 9 then runs chain c over those 32 points in order, so the nine serial FP64 chains
-    // advance in the same instruction and a point costs one dependent DADD instead of nine.
-    unsigned int hm = __ballot_sync(0xffffffffu, heavy);
+    unsigned int hm = __ballot_sync(0xffffffffu, has && n > ST_HEAVY);
     while (hm) {
       const int o = __ffs(hm) - 1;
       hm &= hm - 1;
       const uint32_t wlo = __shfl_sync(0xffffffffu, lo, o);
       const int wn = __shfl_sync(0xffffffffu, n, o);
-      const double* q = sorted_xyz + 3 * static_cast<size_t>(wlo);
-      double acc = (lane == 3 || lane == 6 || lane == 8) ? 1.0 : 0.0;  // identity-initialised second moment (see above)
-      double x = 0, y = 0, z = 0;
-      if (lane < wn) { x = __ldg(q + 3 * lane); y = __ldg(q + 3 * lane + 1); z = __ldg(q + 3 * lane + 2); }
+      const uint32_t wv = __shfl_sync(0xffffffffu, v, o);
+      // the reference's Leaf starts cov_ at identity and adds x x^T onto it: the diagonal chains start at 1.0 (see voxel_stats_kernel)
+      double acc = (lane == 3 || lane == 6 || lane == 8) ? 1.0 : 0.0;
+      float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (lane < wn) p = __ldg(pts + static_cast<uint32_t>(__ldg(pairs + wlo + lane)));
       for (int base = 0; base < wn; base += 32) {
+        const double x = static_cast<double>(p.x), y = static_cast<double>(p.y), z = static_cast<double>(p.z);
         double* pr = s_prod[w][lane];
         pr[0] = x; pr[1] = y; pr[2] = z; pr[3] = x * x; pr[4] = x * y; pr[5] = x * z; pr[6] = y * y; pr[7] = y * z; pr[8] = z * z;
         const int nxt_i = base + 32 + lane;
-        if (nxt_i < wn) { x = __ldg(q + 3 * nxt_i); y = __ldg(q + 3 * nxt_i + 1); z = __ldg(q + 3 * nxt_i + 2); }  // next tile in flight
+        if (nxt_i < wn) p = __ldg(pts + static_cast<uint32_t>(__ldg(pairs + wlo + nxt_i)));  // next tile in flight
         __syncwarp();
         const int cnt = min(32, wn - base);
         if (lane < 9) {
@@ -228,57 +203,115 @@ __global__ void __launch_bounds__(128) voxel_sum_kernel(const double* __restrict
         }
         __syncwarp();
       }
-#pragma unroll
-      for (int c = 0; c < 9; ++c) {
-        const double tv = __shfl_sync(0xffffffffu, acc, c);
-        if (lane == o) sum[c] = tv;
-      }
-    }
-    if (has) {
-      double* o = vox_sums + 9 * static_cast<size_t>(v);
-#pragma unroll
-      for (int c = 0; c < 9; ++c) o[c] = sum[c];
+      if (lane < 9) vox_sums[9 * static_cast<size_t>(wv) + lane] = acc;
     }
   }
 }
 
-// k4b: one thread per voxel: mean / covariance / eigen-inflation / inverse, the hot record and the hash insert.
-__global__ void __launch_bounds__(128, 5) voxel_finalize_kernel(const double* __restrict__ vox_sums, const uint32_t* __restrict__ seg_start,
-                                                                const uint32_t* __restrict__ vox_key, unsigned int* __restrict__ counters,
-                                                                uint32_t n_points, GridMeta m, VoxRec* __restrict__ recs, HashSlot* __restrict__ table,
-                                                                int32_t* __restrict__ c_n, double* __restrict__ c_mean, double* __restrict__ c_cov,
-                                                                double* __restrict__ c_icov, double* __restrict__ c_evecs, double* __restrict__ c_evals,
-                                                                unsigned int* __restrict__ ticket, volatile unsigned long long* host_slots,
-                                                                unsigned long long publish_key) {
+// Per-leaf statistics, ONE kernel: gather + sums + finalize.
+// A warp takes chunks of 32 consecutive leaves (dynamic hand-out); their points are one contiguous run of the sorted
+// (key, point index) list.  The run is staged through shared memory a piece at a time -- the sorted indices are read
+// coalesced, the points themselves (float4, through the index) come from L2 -- and every lane then walks ITS leaf's points in
+// the piece IN INPUT ORDER (the sort is stable), widening to FP64 and accumulating Sum x, Sum x x^T exactly like the
+// reference's serial loop (voxel_grid_covariance_omp_impl.hpp:235-239 / voxel_grid_covariance_impl.hpp:237-239): bit-exact
+// means and covariances.  Leaves with more than ST_HEAVY points arrive summed (voxel_heavy_sums_kernel).
+// The lane then finishes its leaf (mean, covariance, Jacobi eigen-decomposition, inflation, inverse, hot record, hash
+// insert) while other warps are still summing.  The last block publishes BuildMeta to the host.
+__global__ void __launch_bounds__(ST_THREADS, ST_MIN_BLOCKS) voxel_stats_kernel(const float4* __restrict__ pts, BuildMeta* __restrict__ meta,
+                                                                    const unsigned long long* __restrict__ pairs0, const unsigned long long* __restrict__ pairs1,
+                                                                    const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ vox_key,
+                                                                    uint32_t n_points, const double* __restrict__ vox_sums, VoxRec* __restrict__ recs, HashSlot* __restrict__ table,
+                                                                    int32_t* __restrict__ c_n, double* __restrict__ c_mean, double* __restrict__ c_cov,
+                                                                    double* __restrict__ c_icov, double* __restrict__ c_evecs, double* __restrict__ c_evals,
+                                                                    volatile unsigned long long* host_slots, unsigned long long publish_key) {
+  __shared__ float4 s_pts[ST_THREADS / 32][ST_PIECE];
   __shared__ bool s_last;
-  const uint32_t V = counters[1];
-  const uint32_t n_valid_pts = n_points - counters[0];
-  for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < V; v += gridDim.x * blockDim.x) {
-    const uint32_t lo = seg_start[v];
-    const uint32_t hi = (v + 1 < V) ? seg_start[v + 1] : n_valid_pts;
-    const double* q = vox_sums + 9 * static_cast<size_t>(v);
-    finalize_voxel(v, static_cast<int>(hi - lo), q[0], q[1], q[2], q[3], q[4], q[5], q[6], q[7], q[8], vox_key, m, recs, table, c_n, c_mean, c_cov,
-                   c_icov, c_evecs, c_evals, counters + 2);
+  pdl_enter();
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (!meta->error) {
+    const GridMeta m = meta->m;
+    const uint32_t V = meta->V;
+    const uint32_t n_valid_pts = n_points - meta->n_skipped;
+    const unsigned long long* pairs = meta->final_buf ? pairs1 : pairs0;
+    const uint32_t n_chunks = (V + ST_CHUNK - 1) / ST_CHUNK;
+    for (;;) {
+      uint32_t chunk = 0;
+      if (lane == 0) chunk = atomicAdd(&meta->chunk_counter, 1u);
+      chunk = __shfl_sync(0xffffffffu, chunk, 0);
+      if (chunk >= n_chunks) break;
+      const uint32_t v = chunk * ST_CHUNK + lane;
+      const bool has = v < V;
+      const uint32_t lo = has ? seg_start[v] : n_valid_pts;
+      const uint32_t hi = has ? ((v + 1 < V) ? seg_start[v + 1] : n_valid_pts) : n_valid_pts;
+      const int n = static_cast<int>(hi - lo);
+      const bool heavy = n > ST_HEAVY;
+      const uint32_t run_lo = __shfl_sync(0xffffffffu, lo, 0);
+      uint32_t run_hi = hi;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) run_hi = max(run_hi, __shfl_xor_sync(0xffffffffu, run_hi, o));
+      // sx sy sz sxx sxy sxz syy syz szz.  The reference's Leaf starts cov_ at identity and adds x x^T onto it
+      // (voxel_grid_covariance_omp.h:113 + _impl.hpp:239; svn voxel_grid_covariance.h:109 + _impl.hpp:240), so the
+      // diagonal chains start at 1.0, not 0.
+      double sum[9] = {0, 0, 0, 1.0, 0, 0, 1.0, 0, 1.0};
+      // ---- light leaves: the chunk's run, a piece at a time --------------------------------------------------
+      const unsigned int light_any = __ballot_sync(0xffffffffu, has && !heavy);
+      if (light_any) {
+        for (uint32_t base = run_lo; base < run_hi; base += ST_PIECE) {
+          const uint32_t cnt = min(static_cast<uint32_t>(ST_PIECE), run_hi - base);
+          // a piece that only holds points of heavy leaves is not staged
+          if (!__any_sync(0xffffffffu, has && !heavy && lo < base + cnt && hi > base)) continue;
+          uint32_t idx[ST_PIECE / 32];
+#pragma unroll
+          for (int j = 0; j < ST_PIECE / 32; ++j) idx[j] = (j * 32 + lane < cnt) ? static_cast<uint32_t>(__ldg(pairs + base + j * 32 + lane)) : 0xFFFFFFFFu;
+#pragma unroll
+          for (int j = 0; j < ST_PIECE / 32; ++j)
+            if (idx[j] != 0xFFFFFFFFu) s_pts[w][j * 32 + lane] = __ldg(pts + idx[j]);
+          __syncwarp();
+          if (has && !heavy) {
+            const uint32_t a = max(lo, base), b = min(hi, base + cnt);
+            for (uint32_t i = a; i < b; ++i) {
+              const float4 p = s_pts[w][i - base];
+              const double x = static_cast<double>(p.x), y = static_cast<double>(p.y), z = static_cast<double>(p.z);
+              sum[0] += x; sum[1] += y; sum[2] += z;
+              sum[3] += x * x; sum[4] += x * y; sum[5] += x * z; sum[6] += y * y; sum[7] += y * z; sum[8] += z * z;
+            }
+          }
+          __syncwarp();
+        }
+      }
+      // ---- heavy leaves: summed by voxel_heavy_sums_kernel ------------------------------------------------------------
+      if (has && heavy) {
+        const double* q = vox_sums + 9 * static_cast<size_t>(v);
+#pragma unroll
+        for (int c = 0; c < 9; ++c) sum[c] = __ldcg(q + c);
+      }
+      if (has)
+        finalize_voxel(v, n, sum[0], sum[1], sum[2], sum[3], sum[4], sum[5], sum[6], sum[7], sum[8], vox_key, m, recs, table, c_n, c_mean, c_cov,
+                       c_icov, c_evecs, c_evals, &meta->n_valid, &meta->n_flagged);
+      __syncwarp();
+    }
   }
-  // ---- last block done: publish {skipped, V, n_valid} to the host slots 8..10 ----------------------------
+  // ---- last block done: publish BuildMeta (geometry, leaf counts, error) to the host slots ---------------------------
   __syncthreads();
   if (threadIdx.x == 0) {
+    __threadfence();
     unsigned int tk;
-    asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(tk) : "l"(ticket) : "memory");
+    asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(tk) : "l"(&meta->tickets[1]) : "memory");
     s_last = (tk == gridDim.x - 1);
   }
   __syncthreads();
-  if (s_last && threadIdx.x < 3) {
-    const unsigned int c = atomicAdd(counters + threadIdx.x, 0u);
-    publish_slot(host_slots, 8 + threadIdx.x, static_cast<unsigned long long>(c), publish_key);
-    if (threadIdx.x == 0) *ticket = 0;
+  if (s_last) {
+    if (threadIdx.x == 0) { meta->tickets[1] = 0; meta->chunk_counter = 0; __threadfence(); }
+    __syncthreads();
+    const unsigned long long* words = reinterpret_cast<const unsigned long long*>(meta);
+    for (int i = threadIdx.x; i < BUILD_META_WORDS; i += blockDim.x) publish_slot(host_slots, i, __ldcg(words + i), publish_key);
   }
 }
 
 __device__ void finalize_voxel(uint32_t v, int n, double sx, double sy, double sz, double sxx, double sxy, double sxz, double syy, double syz, double szz,
                                const uint32_t* __restrict__ vox_key, const GridMeta& m, VoxRec* __restrict__ recs, HashSlot* __restrict__ table,
                                int32_t* __restrict__ c_n, double* __restrict__ c_mean, double* __restrict__ c_cov, double* __restrict__ c_icov,
-                               double* __restrict__ c_evecs, double* __restrict__ c_evals, unsigned int* __restrict__ n_valid_out) {
+                               double* __restrict__ c_evecs, double* __restrict__ c_evals, unsigned int* __restrict__ n_valid_out, unsigned int* __restrict__ n_flagged_out) {
   const double dn = static_cast<double>(n);
   double mean[3] = {sx, sy, sz};
   double cov[9] = {sxx, sxy, sxz, sxy, syy, syz, sxz, syz, szz};
@@ -370,7 +403,12 @@ __device__ void finalize_voxel(uint32_t v, int n, double sx, double sy, double s
   for (int a = 0; a < 3; ++a) { c_mean[3 * v + a] = mean[a]; c_evals[3 * v + a] = evals[a]; }
 #pragma unroll
   for (int i = 0; i < 9; ++i) { c_cov[9 * v + i] = cov[i]; c_icov[9 * v + i] = icov[i]; c_evecs[9 * v + i] = evecs[i]; }
-  if (valid) {
+  // pclomp: a leaf flagged nr_points_ = -1 (negative eigenvalue / infinite inverse, voxel_grid_covariance_omp_impl.hpp:335-338,
+  // 355-359) had already entered the centroid cloud (:298-323), so the reference's kd-tree still returns it -- with icov_ as the
+  // leaf holds it (zero, or the infinite inverse).  It goes into the table under the row code -2 - v: the DIRECT searches skip it
+  // (they test nr_points_ >= min_points, :390-394), the radius searches decode it.
+  const bool flagged = (m.flavour == FLAVOUR_PCLOMP) && n == -1;
+  if (valid || flagged) {
     VoxRec r;
     r.mean[0] = mean[0]; r.mean[1] = mean[1]; r.mean[2] = mean[2];
 #pragma unroll
@@ -380,18 +418,17 @@ __device__ void finalize_voxel(uint32_t v, int n, double sx, double sy, double s
     const uint4* src = reinterpret_cast<const uint4*>(&r);
     uint4* dst = reinterpret_cast<uint4*>(recs + v);
     dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2]; dst[3] = src[3];
-    hash_insert(table, m.hash_mask, vox_key[v], static_cast<int>(v));
-    atomicAdd(n_valid_out, 1u);
+    hash_insert(table, m.hash_mask, vox_key[v], valid ? static_cast<int>(v) : -2 - static_cast<int>(v));
+    if (valid) atomicAdd(n_valid_out, 1u); else atomicAdd(n_flagged_out, 1u);
   }
 }
 
-void launch_voxel_finalize(const DeviceGrid& g, uint32_t n_points_upper, unsigned long long publish_key, cudaStream_t stream) {
-  const int threads = 128;
-  const int need = static_cast<int>((n_points_upper + threads - 1) / threads);
-  voxel_sum_kernel<<<std::min(need, 148 * 4), threads, 0, stream>>>(g.sorted_xyz, g.seg_start, g.d_counters, n_points_upper, g.vox_sums);
-  voxel_finalize_kernel<<<std::min(need, 148 * 5), threads, 0, stream>>>(g.vox_sums, g.seg_start, g.c_key, g.d_counters, n_points_upper, g.meta, g.recs,
-                                                                      g.table, g.c_n, g.c_mean, g.c_cov, g.c_icov, g.c_evecs, g.c_evals,
-                                                                      g.d_ticket + 1, g.h_slots, publish_key);
+void launch_voxel_stats(const DeviceGrid& g, const float4* d_pts, uint32_t n_points, unsigned long long publish_key, cudaStream_t stream) {
+  const int need = static_cast<int>((n_points + ST_CHUNK * (ST_THREADS / 32) - 1) / (ST_CHUNK * (ST_THREADS / 32)));
+  launch_pdl(voxel_heavy_sums_kernel, dim3(std::max(1, std::min(need, 148 * 8))), dim3(ST_THREADS), 0, stream, d_pts, g.d_meta, g.pairs[0], g.pairs[1], g.seg_start, n_points, g.vox_sums);
+  // one resident wave: 148 SMs x ST_MIN_BLOCKS CTAs of 4 warps; chunks of 32 leaves are handed out dynamically
+  launch_pdl(voxel_stats_kernel, dim3(std::max(1, std::min(need, 148 * ST_MIN_BLOCKS))), dim3(ST_THREADS), 0, stream, d_pts, g.d_meta, g.pairs[0], g.pairs[1],
+             g.seg_start, g.c_key, n_points, g.vox_sums, g.recs, g.table, g.c_n, g.c_mean, g.c_cov, g.c_icov, g.c_evecs, g.c_evals, g.h_slots, publish_key);
 }
 
 }  // namespace ndtb
