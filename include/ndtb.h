@@ -119,6 +119,19 @@ int ndtb_set_regularization_pose(ndtb_handle h, const float* T16);
  * (the initial-guess evaluation :101-135).  Parity hook for SURVEY 8(a) row a8. */
 int ndtb_compute_derivatives(ndtb_handle h, const double p[6], const float* T16, int compute_hessian, double* score,
                              double gradient[6], double hessian[36], double* nvtl);
+/* ndtb_compute_derivatives without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same kernel and same results as ndtb_compute_derivatives (DIRECT1 / DIRECT7, pclomp flavour), but the
+ * kernel's scratch -- per-block partial sums, last-block ticket, result slots, 55 KB -- is a static __device__ array
+ * inside the library (every GPU that loads the library holds it until exit).  The call performs no cudaMalloc /
+ * cudaFree / allocating library call: the target map must already be built (ndtb_set_target*), the source is
+ * `d_source_xyzw` (device memory, n_source packed float4 points, w unused) or, when NULL, the handle's resident source.
+ * n_source > NDTB_STATIC_MAX_POINTS is rejected with NDTB_ERR_INVALID.  Outputs are host pointers as in
+ * ndtb_compute_derivatives.  All calls on one GPU share the scratch: the call clears what must start at zero, returns
+ * after the result is back on the host, and calls that overlap on the same GPU (other threads / handles) race. */
+#define NDTB_STATIC_MAX_POINTS 4194304
+int ndtb_compute_derivatives_static(ndtb_handle h, const void* d_source_xyzw, size_t n_source, const double p[6], const float* T16,
+                                    int compute_hessian, double* score, double gradient[6], double hessian[36], double* nvtl);
 /* align(output, guess): pcl::Registration::align -> computeTransformation (ndt_omp_impl.hpp:85-202).
  * `out_xyz` (optional, n_source*3 floats) receives the transformed source like `output`.
  * `transformation_array` (optional, capacity*16 floats) receives transformation_array_. */

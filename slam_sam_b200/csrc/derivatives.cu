@@ -15,6 +15,10 @@
 // is run-to-run bit stable and differs from the reference's serial in-index-order sum only by FP64
 // summation order.  Bound: HBM/L2 gather, B_eval = N*(16 + 8*P + 64*hbar) bytes.
 #include "eval_api.cuh"
+#include "handle.cuh"       // ndtb_compute_derivatives_static (end of this file)
+#include "newton_math.cuh"
+#include <cstring>
+#include <string>
 
 namespace ndtb {
 
@@ -1162,3 +1166,93 @@ void launch_eval(int flavour, int n_probe, bool compute_hessian, bool gn, const 
 }
 
 }  // namespace ndtb
+
+// ---- allocation-free evaluation (ndtb_compute_derivatives_static, include/ndtb.h) ------------------------------------
+// The one-shot DIRECT1 / DIRECT7 kernel above needs scratch memory: the per-block partial sums, the last-block-done
+// ticket and -- when the result is not written to pinned host memory -- the 46 result slots.  ndtb_compute_derivatives
+// takes them from buffers that ensure_eval_buffers() allocates; callers that may not allocate (code under CUDA graph
+// capture, tight serving loops) get the same kernel over a scratch that is part of the library image: a file-scope
+// __device__ array of STATIC_SCRATCH_BYTES, held by every GPU that loads the library until the process exits.
+// Every call on a device shares the array: calls that overlap on that GPU race, and the array keeps the previous call's
+// contents -- the ticket and the result slots are cleared at the start of every call, the partial sums are all
+// rewritten before they are read.
+
+namespace ndtb {
+
+constexpr int STATIC_MAX_BLOCKS = 148;  // eval_blocks_pclomp() never launches more
+struct StaticEvalScratch {
+  double partials[RED_N * STATIC_MAX_BLOCKS];   // component-major block partials
+  unsigned long long slots[2 * (RED_N + 1)];    // self-validating result slots {bits, bits ^ key}
+  unsigned int ticket[4];
+};
+constexpr size_t STATIC_SCRATCH_BYTES = (sizeof(StaticEvalScratch) + 255) & ~static_cast<size_t>(255);
+static __device__ __align__(256) unsigned char g_static_eval_scratch[STATIC_SCRATCH_BYTES];
+
+// In host code `g_static_eval_scratch` is only a stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+constexpr int STATIC_MAX_DEVICES = 64;
+static StaticEvalScratch* g_static_scratch_ptr[STATIC_MAX_DEVICES] = {};
+
+static cudaError_t static_scratch_for_current_device(int device, StaticEvalScratch** out) {
+  if (device < 0 || device >= STATIC_MAX_DEVICES) return cudaErrorInvalidDevice;
+  if (!g_static_scratch_ptr[device]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_static_eval_scratch);
+    if (e != cudaSuccess) return e;
+    g_static_scratch_ptr[device] = static_cast<StaticEvalScratch*>(p);
+  }
+  *out = g_static_scratch_ptr[device];
+  return cudaSuccess;
+}
+
+}  // namespace ndtb
+
+extern "C" int ndtb_compute_derivatives_static(ndtb_handle h, const void* d_source_xyzw, size_t n_source, const double p[6], const float* T16,
+                                               int compute_hessian, double* score, double gradient[6], double hessian[36], double* nvtl) {
+  using namespace ndtb;
+  if (!h || !p || !score || !gradient || !hessian) return NDTB_ERR_INVALID;
+  if (cudaSetDevice(h->device) != cudaSuccess) return set_error(h, NDTB_ERR_CUDA, "cudaSetDevice failed");
+  if (!h->grid.built) return set_error(h, NDTB_ERR_NOT_READY, "the target must be set before ndtb_compute_derivatives_static");
+  if (h->params.grid_flavour != NDTB_FLAVOUR_PCLOMP) return set_error(h, NDTB_ERR_INVALID, "pclomp entry point on an svn-flavour handle");
+  if (h->params.search_method != NDTB_DIRECT1 && h->params.search_method != NDTB_DIRECT7)
+    return set_error(h, NDTB_ERR_INVALID, "ndtb_compute_derivatives_static serves DIRECT1 and DIRECT7 only");
+  const float4* d_src = static_cast<const float4*>(d_source_xyzw);
+  if (!d_src) { d_src = h->d_source; n_source = h->n_source; }
+  if (!d_src || n_source == 0) return set_error(h, NDTB_ERR_NOT_READY, "no source cloud: pass a device pointer or call ndtb_set_source first");
+  if (n_source > static_cast<size_t>(NDTB_STATIC_MAX_POINTS))
+    return set_error(h, NDTB_ERR_INVALID, "ndtb_compute_derivatives_static: more than NDTB_STATIC_MAX_POINTS (4194304) source points");
+  if (h->session_open) return set_error(h, NDTB_ERR_NOT_READY, "an alignment session is running on this handle");
+  const int n = static_cast<int>(n_source);
+  if (eval_blocks_pclomp(n) > STATIC_MAX_BLOCKS) return set_error(h, NDTB_ERR_INVALID, "ndtb_compute_derivatives_static: grid exceeds the static scratch");
+  StaticEvalScratch* sc = nullptr;
+  cudaError_t e = static_scratch_for_current_device(h->device, &sc);
+  if (e != cudaSuccess) { h->last_error = std::string("cudaGetSymbolAddress(static scratch): ") + cudaGetErrorString(e); return NDTB_ERR_CUDA; }
+  float T[16];
+  if (T16) std::memcpy(T, T16, sizeof(T)); else pose_to_T(p, T);
+  EvalState st;
+  fill_eval_state(h, st, p, T, 10e-5, false);
+  // what must start at zero: the ticket (a call that failed half-way may have left it counted up) and the result slots
+  e = cudaMemsetAsync(sc->slots, 0, sizeof(sc->slots) + sizeof(sc->ticket), h->stream);
+  if (e != cudaSuccess) { h->last_error = std::string("static scratch clear: ") + cudaGetErrorString(e); return NDTB_ERR_CUDA; }
+  EvalBuffers b;  // views into the static scratch, nothing owned
+  b.d_partials = sc->partials;
+  b.d_tickets = sc->ticket;
+  b.max_particles = 1; b.max_blocks = STATIC_MAX_BLOCKS;
+  const unsigned long long key = 0x9E3779B97F4A7C15ull * static_cast<unsigned long long>(++h->flag_seq) | 1ull;
+  const int n_probe = (h->params.search_method == NDTB_DIRECT1) ? 1 : 7;
+  e = launch_eval_pclomp(n_probe, compute_hessian != 0, d_src, n, h->grid.meta, h->grid.recs, h->grid.table, st, b,
+                         reinterpret_cast<double*>(sc->slots), key, h->stream, nullptr);
+  if (e != cudaSuccess) { h->last_error = std::string("static eval kernel launch: ") + cudaGetErrorString(e); return NDTB_ERR_CUDA; }
+  h->launches += 1;
+  unsigned long long words[2 * RED_N];
+  e = cudaMemcpyAsync(words, sc->slots, sizeof(words), cudaMemcpyDeviceToHost, h->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+  if (e != cudaSuccess) { h->last_error = std::string("static eval kernel: ") + cudaGetErrorString(e); return NDTB_ERR_CUDA; }
+  double r[RED_N];
+  for (int c = 0; c < RED_N; ++c) {
+    if ((words[2 * c] ^ words[2 * c + 1]) != key) return set_error(h, NDTB_ERR_CUDA, "static eval kernel finished without publishing its result");
+    std::memcpy(&r[c], &words[2 * c], 8);
+  }
+  finish_eval(h, n, r, p, score, gradient, hessian, nvtl);
+  return NDTB_OK;
+}

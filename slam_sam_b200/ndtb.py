@@ -59,7 +59,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "nd
            "ndtb_mg_add_target", "ndtb_mg_remove_target", "ndtb_mg_create_kdtree", "ndtb_mg_set_input_target", "ndtb_mg_get_info",
            "ndtb_mg_get_grid_ids", "ndtb_mg_get_leaves", "ndtb_mg_compute_derivatives", "ndtb_mg_align", "ndtb_mg_calculate_scores",
            "ndtb_svn_get_timings", "ndtb_comm_window_handle", "ndtb_comm_connect", "ndtb_comm_init", "ndtb_comm_close", "ndtb_comm_info",
-           "ndtb_svn_align_sharded", "ndtb_calculate_score", "ndtb_write_ndt_files"]
+           "ndtb_svn_align_sharded", "ndtb_calculate_score", "ndtb_write_ndt_files", "ndtb_compute_derivatives_static"]
 
 _LIB = None
 
@@ -106,6 +106,7 @@ def lib():
         L.ndtb_set_source_device.argtypes = [H, C.c_void_p, C.c_size_t]
         L.ndtb_set_regularization_pose.argtypes = [H, c_f]
         L.ndtb_compute_derivatives.argtypes = [H, c_d, c_f, C.c_int, c_d, c_d, c_d, c_d]
+        L.ndtb_compute_derivatives_static.argtypes = [H, C.c_void_p, C.c_size_t, c_d, c_f, C.c_int, c_d, c_d, c_d, c_d]
         L.ndtb_align.argtypes = [H, c_f, C.POINTER(Result), c_f, C.c_int, c_f]
         L.ndtb_get_trace.argtypes = [H, c_d, C.c_int, c_i]
         L.ndtb_calculate_scores.argtypes = [H, c_f, c_d, c_d]
@@ -309,6 +310,17 @@ class Handle:
         s = np.zeros(1); g = np.zeros(6); H = np.zeros((6, 6)); nv = np.zeros(1)
         self.check(self.L.ndtb_compute_derivatives(self.h, _ptr(p, c_d), _ptr(t, c_f), int(compute_hessian), _ptr(s, c_d), _ptr(g, c_d),
                                                    _ptr(H, c_d), _ptr(nv, c_d)))
+        return s[0], g, H, nv[0]
+
+    def compute_derivatives_static(self, p, T=None, compute_hessian=True, d_source=None, n_source=0):
+        """ndtb_compute_derivatives_static: the same evaluation over the library's static scratch, no allocation in the call.
+        `d_source` is a device address of n_source packed float4 points; None -> the handle's resident source."""
+        p = np.ascontiguousarray(p, np.float64)
+        t = None if T is None else np.ascontiguousarray(T, np.float32).reshape(16)
+        s = np.zeros(1); g = np.zeros(6); H = np.zeros((6, 6)); nv = np.zeros(1)
+        self.check(self.L.ndtb_compute_derivatives_static(self.h, C.c_void_p(d_source) if d_source else None, int(n_source), _ptr(p, c_d),
+                                                          _ptr(t, c_f), int(compute_hessian), _ptr(s, c_d), _ptr(g, c_d), _ptr(H, c_d),
+                                                          _ptr(nv, c_d)))
         return s[0], g, H, nv[0]
 
     def align(self, guess=None, capacity=64, want_output=False):
