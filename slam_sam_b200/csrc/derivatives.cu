@@ -1079,11 +1079,10 @@ template <int PROBES>
 static cudaError_t launch_session_t(const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs, const HashSlot* table,
                                     const ulonglong2* mailbox, unsigned long long* d_cmd, const EvalBuffers& b, double* results,
                                     unsigned long long seq0, unsigned long long idle_timeout_ns, cudaStream_t stream) {
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[MAX_DEVICES] = {};
+  if (needs_func_setup(configured)) {
     cudaError_t e = cudaFuncSetAttribute(align_session_kernel<PROBES>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(PclSessionShared)));
     if (e != cudaSuccess) return e;
-    configured = true;
   }
   GridMeta m = meta;
   double* partials = b.d_partials;
@@ -1117,11 +1116,10 @@ template <int PROBES, bool HESS>
 static cudaError_t launch_pclomp_t(const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs, const HashSlot* table, const EvalState& st,
                                    const EvalBuffers& b, double* results, unsigned long long result_key,
                                    cudaStream_t stream, unsigned long long* dbg) {
-  static bool configured = false;  // one handle per caller thread, but the attribute is per function: benign if set twice
-  if (!configured) {
+  static bool configured[MAX_DEVICES] = {};  // one handle per caller thread, but the attribute is per function and device: benign if set twice
+  if (needs_func_setup(configured)) {
     cudaError_t e = cudaFuncSetAttribute(eval_kernel_pclomp<PROBES, HESS>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(PclShared)));
     if (e != cudaSuccess) return e;
-    configured = true;
   }
   eval_kernel_pclomp<PROBES, HESS><<<eval_blocks_pclomp(n), PCL_THREADS, sizeof(PclShared), stream>>>(d_src, n, meta, recs, table, st, b.d_partials,
                                                                                                   results, b.d_tickets, result_key, dbg);

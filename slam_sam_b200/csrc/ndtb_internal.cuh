@@ -100,6 +100,16 @@ __device__ __forceinline__ void pdl_enter() {
   asm volatile("griddepcontrol.wait;" ::: "memory");
   asm volatile("griddepcontrol.launch_dependents;");
 }
+// Function attributes (dynamic shared memory opt-in) are per DEVICE: a process that drives several GPUs sets them once on each.
+// `flags` is the call site's static array; returns true when the current device still needs the attribute.
+constexpr int MAX_DEVICES = 64;
+inline bool needs_func_setup(bool (&flags)[MAX_DEVICES]) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) return true;
+  if (flags[dev]) return false;
+  flags[dev] = true;
+  return true;
+}
 template <class... KArgs, class... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
   cudaLaunchConfig_t cfg = {};

@@ -133,39 +133,42 @@ __device__ __forceinline__ void hash_insert(HashSlot* table, uint32_t mask, uint
   }
 }
 
-constexpr int ST_THREADS = 128;   // 4 warps per CTA, every warp works on its own chunks
+constexpr int ST_THREADS = 128;   // 4 warps per CTA
 constexpr int ST_CHUNK = 32;      // leaves per chunk: one per lane
-constexpr int ST_PIECE = 256;     // points staged in shared memory at a time (4 KB per warp)
-constexpr int ST_HEAVY = 48;      // leaves with more points are summed by the whole warp (voxel_heavy_sums_kernel)
-#ifndef ST_MIN_BLOCKS
-#define ST_MIN_BLOCKS 5            // 5 x 4 warps per SM: the 2632 chunks of an 84 k-leaf map are one resident wave
-#endif
+constexpr int ST_HEAVY = 48;      // leaves with more points are summed by a whole warp (voxel_heavy_sums_kernel)
+constexpr int ST_HEAVY_BLOCKS = 148 * 4;   // CTAs of the heavy-sums kernel
+constexpr int FIN_THREADS = 64;            // finalize: 2 warps per CTA, 8 CTAs per SM (128 registers, no spill)
+constexpr int FIN_MIN_BLOCKS = 8;
 
 // Everything per voxel after the sums.  `n`, sums in; writes the cold arrays, the hot record and the hash slot.
-__device__ void finalize_voxel(uint32_t v, int n, double sx, double sy, double sz, double sxx, double sxy, double sxz, double syy, double syz, double szz,
-                               const uint32_t* __restrict__ vox_key, const GridMeta& m, VoxRec* __restrict__ recs, HashSlot* __restrict__ table,
-                               int32_t* __restrict__ c_n, double* __restrict__ c_mean, double* __restrict__ c_cov, double* __restrict__ c_icov,
-                               double* __restrict__ c_evecs, double* __restrict__ c_evals, unsigned int* __restrict__ n_valid_out, unsigned int* __restrict__ n_flagged_out);
+// Returns 1 for a leaf the searches can return, 2 for a pclomp leaf flagged -1 (radius searches only), 0 otherwise.
+__device__ int finalize_voxel(uint32_t v, int n, double sx, double sy, double sz, double sxx, double sxy, double sxz, double syy, double syz, double szz,
+                              const uint32_t* __restrict__ vox_key, const GridMeta& m, VoxRec* __restrict__ recs, HashSlot* __restrict__ table,
+                              int32_t* __restrict__ c_n, double* __restrict__ c_mean, double* __restrict__ c_cov, double* __restrict__ c_icov,
+                              double* __restrict__ c_evecs, double* __restrict__ c_evals);
 
-// Sums of the HEAVY leaves (more than ST_HEAVY points), ahead of the statistics kernel.  Heavy leaves come in runs (a wall is a
-// row of equally dense voxels), so they are dealt to the warps through a multiplicative permutation of [0, Vr), Vr = V rounded up
-// to a warp (2654435761 is prime, hence coprime with Vr: t -> t * P mod Vr is a bijection): no warp collects a whole wall.  The
-// whole warp takes one heavy leaf at a time: 32 lanes load 32 points (indices coalesced, points from L2) and form the nine
-// products; lane c < 9 then runs chain c over those 32 points IN INPUT ORDER, so the nine serial FP64 chains advance in the same
-// instruction and a point costs one dependent DADD instead of nine.
-__global__ void __launch_bounds__(ST_THREADS) voxel_heavy_sums_kernel(const float4* __restrict__ pts, const BuildMeta* __restrict__ meta,
-                                                                      const unsigned long long* __restrict__ pairs0,
-                                                                      const unsigned long long* __restrict__ pairs1, const uint32_t* __restrict__ seg_start,
-                                                                      uint32_t n_points, double* __restrict__ vox_sums) {
-  __shared__ double s_prod[ST_THREADS / 32][32][9];
+// Sums of the HEAVY leaves (more than ST_HEAVY points), ahead of the statistics kernel: Sum x and Sum x x^T IN INPUT ORDER (FP64,
+// one serial chain per component exactly like the reference's loop, voxel_grid_covariance_omp_impl.hpp:235-239 /
+// voxel_grid_covariance_impl.hpp:237-239).  The final radix pass left the points themselves in sorted order (sorted_pts: leaf
+// after leaf, input order inside a leaf -- the sort is stable), so a leaf is a contiguous run of float4 and nothing here chases
+// an index.  One warp per heavy leaf.  Heavy leaves come in runs (a wall is a row of equally dense voxels), so groups of 32
+// leaves are dealt to the warps through a multiplicative permutation of [0, Vr), Vr = V rounded up to a warp (2654435761 is
+// prime, hence coprime with Vr: t -> t * P mod Vr is a bijection).  32 lanes load 32 consecutive points and form the nine
+// products; lane c < 9 then runs chain c over those 32 points, so the nine serial FP64 chains advance in the same instruction
+// and a point costs one dependent DADD instead of nine.  Two tiles are in flight ahead of the chain.
+__global__ void __launch_bounds__(ST_THREADS, 8) voxel_heavy_sums_kernel(const float4* __restrict__ sorted_pts, const BuildMeta* __restrict__ meta,
+                                                                         const uint32_t* __restrict__ seg_start, uint32_t n_points,
+                                                                         double* __restrict__ vox_sums) {
+  __shared__ double s_prod_all[ST_THREADS / 32][32][9];
   pdl_enter();
   if (meta->error) return;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const uint32_t V = meta->V;
   const uint32_t n_valid_pts = n_points - meta->n_skipped;
-  const unsigned long long* pairs = meta->final_buf ? pairs1 : pairs0;
+  double (*s_prod)[9] = s_prod_all[w];
   const uint32_t Vr = (V + 31u) & ~31u;
-  for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < Vr; t += gridDim.x * blockDim.x) {  // warp-uniform trip count
+  const uint32_t stride = gridDim.x * ST_THREADS;
+  for (uint32_t t = blockIdx.x * ST_THREADS + threadIdx.x; t < Vr; t += stride) {  // warp-uniform trip count
     const uint32_t v = static_cast<uint32_t>((static_cast<unsigned long long>(t) * 2654435761ull) % Vr);
     const bool has = v < V;
     const uint32_t lo = has ? seg_start[v] : 0u;
@@ -180,14 +183,13 @@ __global__ void __launch_bounds__(ST_THREADS) voxel_heavy_sums_kernel(const floa
       const uint32_t wv = __shfl_sync(0xffffffffu, v, o);
       // the reference's Leaf starts cov_ at identity and adds x x^T onto it: the diagonal chains start at 1.0 (see voxel_stats_kernel)
       double acc = (lane == 3 || lane == 6 || lane == 8) ? 1.0 : 0.0;
-      float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (lane < wn) p = __ldg(pts + static_cast<uint32_t>(__ldg(pairs + wlo + lane)));
-      for (int base = 0; base < wn; base += 32) {
+      const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4* src = sorted_pts + wlo + lane;
+      // one tile = 32 consecutive points: products to shared memory, then the nine chains over them
+      auto tile = [&](const float4 p, int base) {
         const double x = static_cast<double>(p.x), y = static_cast<double>(p.y), z = static_cast<double>(p.z);
-        double* pr = s_prod[w][lane];
+        double* pr = s_prod[lane];
         pr[0] = x; pr[1] = y; pr[2] = z; pr[3] = x * x; pr[4] = x * y; pr[5] = x * z; pr[6] = y * y; pr[7] = y * z; pr[8] = z * z;
-        const int nxt_i = base + 32 + lane;
-        if (nxt_i < wn) p = __ldg(pts + static_cast<uint32_t>(__ldg(pairs + wlo + nxt_i)));  // next tile in flight
         __syncwarp();
         const int cnt = min(32, wn - base);
         if (lane < 9) {
@@ -195,105 +197,108 @@ __global__ void __launch_bounds__(ST_THREADS) voxel_heavy_sums_kernel(const floa
           for (; k + 8 <= cnt; k += 8) {
             double t8[8];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) t8[u] = s_prod[w][k + u][lane];
+            for (int u = 0; u < 8; ++u) t8[u] = s_prod[k + u][lane];
 #pragma unroll
             for (int u = 0; u < 8; ++u) acc += t8[u];
           }
-          for (; k < cnt; ++k) acc += s_prod[w][k][lane];
+          for (; k < cnt; ++k) acc += s_prod[k][lane];
         }
         __syncwarp();
+      };
+      // two tiles per trip, the next two already in flight: a load is only consumed two chains after it was issued
+      float4 pa = (lane < wn) ? __ldg(src) : zero;
+      float4 pb = (32 + lane < wn) ? __ldg(src + 32) : zero;
+      for (int base = 0; base < wn; base += 64) {
+        const float4 na = (base + 64 + lane < wn) ? __ldg(src + base + 64) : zero;
+        const float4 nb = (base + 96 + lane < wn) ? __ldg(src + base + 96) : zero;
+        tile(pa, base);
+        if (base + 32 < wn) tile(pb, base + 32);
+        pa = na; pb = nb;
       }
       if (lane < 9) vox_sums[9 * static_cast<size_t>(wv) + lane] = acc;
     }
   }
 }
 
-// Per-leaf statistics, ONE kernel: gather + sums + finalize.
-// A warp takes chunks of 32 consecutive leaves (dynamic hand-out); their points are one contiguous run of the sorted
-// (key, point index) list.  The run is staged through shared memory a piece at a time -- the sorted indices are read
-// coalesced, the points themselves (float4, through the index) come from L2 -- and every lane then walks ITS leaf's points in
-// the piece IN INPUT ORDER (the sort is stable), widening to FP64 and accumulating Sum x, Sum x x^T exactly like the
-// reference's serial loop (voxel_grid_covariance_omp_impl.hpp:235-239 / voxel_grid_covariance_impl.hpp:237-239): bit-exact
-// means and covariances.  Leaves with more than ST_HEAVY points arrive summed (voxel_heavy_sums_kernel).
-// The lane then finishes its leaf (mean, covariance, Jacobi eigen-decomposition, inflation, inverse, hot record, hash
-// insert) while other warps are still summing.  The last block publishes BuildMeta to the host.
-__global__ void __launch_bounds__(ST_THREADS, ST_MIN_BLOCKS) voxel_stats_kernel(const float4* __restrict__ pts, BuildMeta* __restrict__ meta,
-                                                                    const unsigned long long* __restrict__ pairs0, const unsigned long long* __restrict__ pairs1,
+// Per-leaf statistics, one thread per leaf, chunks of 32 consecutive leaves per warp (handed out dynamically: the leaf count is
+// only known on the device).  A light leaf (<= ST_HEAVY points) is summed here: the lane walks ITS run of sorted_pts -- its
+// points in input order -- widening to FP64 and accumulating Sum x, Sum x x^T exactly like the reference's serial loop
+// (bit-exact means and covariances); the 32 runs of a chunk are adjacent, every 128-byte line is fetched once and then served
+// from L1.  Heavy leaves arrive summed (voxel_heavy_sums_kernel).  Then mean, covariance, Jacobi eigen-decomposition, inflation,
+// inverse, hot record, hash insert (finalize_voxel).  The last block publishes BuildMeta (geometry, leaf counts, error) to the host.
+__global__ void __launch_bounds__(FIN_THREADS, FIN_MIN_BLOCKS) voxel_stats_kernel(const float4* __restrict__ sorted_pts, BuildMeta* __restrict__ meta,
                                                                     const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ vox_key,
-                                                                    uint32_t n_points, const double* __restrict__ vox_sums, VoxRec* __restrict__ recs, HashSlot* __restrict__ table,
-                                                                    int32_t* __restrict__ c_n, double* __restrict__ c_mean, double* __restrict__ c_cov,
-                                                                    double* __restrict__ c_icov, double* __restrict__ c_evecs, double* __restrict__ c_evals,
-                                                                    volatile unsigned long long* host_slots, unsigned long long publish_key) {
-  __shared__ float4 s_pts[ST_THREADS / 32][ST_PIECE];
+                                                                    uint32_t n_points, const double* __restrict__ vox_sums, VoxRec* __restrict__ recs,
+                                                                    HashSlot* __restrict__ table, int32_t* __restrict__ c_n,
+                                                                    double* __restrict__ c_mean, double* __restrict__ c_cov,
+                                                                    double* __restrict__ c_icov, double* __restrict__ c_evecs,
+                                                                    double* __restrict__ c_evals, volatile unsigned long long* host_slots,
+                                                                    unsigned long long publish_key) {
+  __shared__ unsigned int s_cnt[2];
   __shared__ bool s_last;
   pdl_enter();
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
+  __syncthreads();
   if (!meta->error) {
     const GridMeta m = meta->m;
     const uint32_t V = meta->V;
     const uint32_t n_valid_pts = n_points - meta->n_skipped;
-    const unsigned long long* pairs = meta->final_buf ? pairs1 : pairs0;
     const uint32_t n_chunks = (V + ST_CHUNK - 1) / ST_CHUNK;
+    const int lane = threadIdx.x & 31;
     for (;;) {
       uint32_t chunk = 0;
       if (lane == 0) chunk = atomicAdd(&meta->chunk_counter, 1u);
       chunk = __shfl_sync(0xffffffffu, chunk, 0);
       if (chunk >= n_chunks) break;
       const uint32_t v = chunk * ST_CHUNK + lane;
-      const bool has = v < V;
-      const uint32_t lo = has ? seg_start[v] : n_valid_pts;
-      const uint32_t hi = has ? ((v + 1 < V) ? seg_start[v + 1] : n_valid_pts) : n_valid_pts;
-      const int n = static_cast<int>(hi - lo);
-      const bool heavy = n > ST_HEAVY;
-      const uint32_t run_lo = __shfl_sync(0xffffffffu, lo, 0);
-      uint32_t run_hi = hi;
+      int kind = 0;
+      if (v < V) {
+        const uint32_t lo = seg_start[v], hi = (v + 1 < V) ? seg_start[v + 1] : n_valid_pts;
+        const int n = static_cast<int>(hi - lo);
+        // sx sy sz sxx sxy sxz syy syz szz.  The reference's Leaf starts cov_ at identity and adds x x^T onto it
+        // (voxel_grid_covariance_omp.h:113 + _impl.hpp:239; svn voxel_grid_covariance.h:109 + _impl.hpp:240), so the
+        // diagonal chains start at 1.0, not 0.
+        double sum[9] = {0, 0, 0, 1.0, 0, 0, 1.0, 0, 1.0};
+        if (n > ST_HEAVY) {
+          const double* q = vox_sums + 9 * static_cast<size_t>(v);
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) run_hi = max(run_hi, __shfl_xor_sync(0xffffffffu, run_hi, o));
-      // sx sy sz sxx sxy sxz syy syz szz.  The reference's Leaf starts cov_ at identity and adds x x^T onto it
-      // (voxel_grid_covariance_omp.h:113 + _impl.hpp:239; svn voxel_grid_covariance.h:109 + _impl.hpp:240), so the
-      // diagonal chains start at 1.0, not 0.
-      double sum[9] = {0, 0, 0, 1.0, 0, 0, 1.0, 0, 1.0};
-      // ---- light leaves: the chunk's run, a piece at a time --------------------------------------------------
-      const unsigned int light_any = __ballot_sync(0xffffffffu, has && !heavy);
-      if (light_any) {
-        for (uint32_t base = run_lo; base < run_hi; base += ST_PIECE) {
-          const uint32_t cnt = min(static_cast<uint32_t>(ST_PIECE), run_hi - base);
-          // a piece that only holds points of heavy leaves is not staged
-          if (!__any_sync(0xffffffffu, has && !heavy && lo < base + cnt && hi > base)) continue;
-          uint32_t idx[ST_PIECE / 32];
+          for (int c = 0; c < 9; ++c) sum[c] = __ldcg(q + c);
+        } else {
+          const float4* src = sorted_pts + lo;
+          int k = 0;
+          for (; k + 4 <= n; k += 4) {
+            float4 p[4];
 #pragma unroll
-          for (int j = 0; j < ST_PIECE / 32; ++j) idx[j] = (j * 32 + lane < cnt) ? static_cast<uint32_t>(__ldg(pairs + base + j * 32 + lane)) : 0xFFFFFFFFu;
+            for (int u = 0; u < 4; ++u) p[u] = __ldg(src + k + u);
 #pragma unroll
-          for (int j = 0; j < ST_PIECE / 32; ++j)
-            if (idx[j] != 0xFFFFFFFFu) s_pts[w][j * 32 + lane] = __ldg(pts + idx[j]);
-          __syncwarp();
-          if (has && !heavy) {
-            const uint32_t a = max(lo, base), b = min(hi, base + cnt);
-            for (uint32_t i = a; i < b; ++i) {
-              const float4 p = s_pts[w][i - base];
-              const double x = static_cast<double>(p.x), y = static_cast<double>(p.y), z = static_cast<double>(p.z);
+            for (int u = 0; u < 4; ++u) {
+              const double x = static_cast<double>(p[u].x), y = static_cast<double>(p[u].y), z = static_cast<double>(p[u].z);
               sum[0] += x; sum[1] += y; sum[2] += z;
               sum[3] += x * x; sum[4] += x * y; sum[5] += x * z; sum[6] += y * y; sum[7] += y * z; sum[8] += z * z;
             }
           }
-          __syncwarp();
+          for (; k < n; ++k) {
+            const float4 p = __ldg(src + k);
+            const double x = static_cast<double>(p.x), y = static_cast<double>(p.y), z = static_cast<double>(p.z);
+            sum[0] += x; sum[1] += y; sum[2] += z;
+            sum[3] += x * x; sum[4] += x * y; sum[5] += x * z; sum[6] += y * y; sum[7] += y * z; sum[8] += z * z;
+          }
         }
+        kind = finalize_voxel(v, n, sum[0], sum[1], sum[2], sum[3], sum[4], sum[5], sum[6], sum[7], sum[8], vox_key, m, recs, table, c_n, c_mean,
+                              c_cov, c_icov, c_evecs, c_evals);
       }
-      // ---- heavy leaves: summed by voxel_heavy_sums_kernel ------------------------------------------------------------
-      if (has && heavy) {
-        const double* q = vox_sums + 9 * static_cast<size_t>(v);
-#pragma unroll
-        for (int c = 0; c < 9; ++c) sum[c] = __ldcg(q + c);
+      const unsigned int mv = __ballot_sync(0xffffffffu, kind == 1), mf = __ballot_sync(0xffffffffu, kind == 2);
+      if (lane == 0) {
+        if (mv) atomicAdd(&s_cnt[0], static_cast<unsigned int>(__popc(mv)));
+        if (mf) atomicAdd(&s_cnt[1], static_cast<unsigned int>(__popc(mf)));
       }
-      if (has)
-        finalize_voxel(v, n, sum[0], sum[1], sum[2], sum[3], sum[4], sum[5], sum[6], sum[7], sum[8], vox_key, m, recs, table, c_n, c_mean, c_cov,
-                       c_icov, c_evecs, c_evals, &meta->n_valid, &meta->n_flagged);
-      __syncwarp();
     }
   }
-  // ---- last block done: publish BuildMeta (geometry, leaf counts, error) to the host slots ---------------------------
+  // ---- last block done: publish BuildMeta to the host slots -------------------------------------------------------------
   __syncthreads();
   if (threadIdx.x == 0) {
+    if (s_cnt[0]) atomicAdd(&meta->n_valid, s_cnt[0]);
+    if (s_cnt[1]) atomicAdd(&meta->n_flagged, s_cnt[1]);
     __threadfence();
     unsigned int tk;
     asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(tk) : "l"(&meta->tickets[1]) : "memory");
@@ -308,10 +313,10 @@ __global__ void __launch_bounds__(ST_THREADS, ST_MIN_BLOCKS) voxel_stats_kernel(
   }
 }
 
-__device__ void finalize_voxel(uint32_t v, int n, double sx, double sy, double sz, double sxx, double sxy, double sxz, double syy, double syz, double szz,
-                               const uint32_t* __restrict__ vox_key, const GridMeta& m, VoxRec* __restrict__ recs, HashSlot* __restrict__ table,
-                               int32_t* __restrict__ c_n, double* __restrict__ c_mean, double* __restrict__ c_cov, double* __restrict__ c_icov,
-                               double* __restrict__ c_evecs, double* __restrict__ c_evals, unsigned int* __restrict__ n_valid_out, unsigned int* __restrict__ n_flagged_out) {
+__device__ int finalize_voxel(uint32_t v, int n, double sx, double sy, double sz, double sxx, double sxy, double sxz, double syy, double syz, double szz,
+                              const uint32_t* __restrict__ vox_key, const GridMeta& m, VoxRec* __restrict__ recs, HashSlot* __restrict__ table,
+                              int32_t* __restrict__ c_n, double* __restrict__ c_mean, double* __restrict__ c_cov, double* __restrict__ c_icov,
+                              double* __restrict__ c_evecs, double* __restrict__ c_evals) {
   const double dn = static_cast<double>(n);
   double mean[3] = {sx, sy, sz};
   double cov[9] = {sxx, sxy, sxz, sxy, syy, syz, sxz, syz, szz};
@@ -419,16 +424,21 @@ __device__ void finalize_voxel(uint32_t v, int n, double sx, double sy, double s
     uint4* dst = reinterpret_cast<uint4*>(recs + v);
     dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2]; dst[3] = src[3];
     hash_insert(table, m.hash_mask, vox_key[v], valid ? static_cast<int>(v) : -2 - static_cast<int>(v));
-    if (valid) atomicAdd(n_valid_out, 1u); else atomicAdd(n_flagged_out, 1u);
   }
+  return valid ? 1 : (flagged ? 2 : 0);
 }
 
-void launch_voxel_stats(const DeviceGrid& g, const float4* d_pts, uint32_t n_points, unsigned long long publish_key, cudaStream_t stream) {
-  const int need = static_cast<int>((n_points + ST_CHUNK * (ST_THREADS / 32) - 1) / (ST_CHUNK * (ST_THREADS / 32)));
-  launch_pdl(voxel_heavy_sums_kernel, dim3(std::max(1, std::min(need, 148 * 8))), dim3(ST_THREADS), 0, stream, d_pts, g.d_meta, g.pairs[0], g.pairs[1], g.seg_start, n_points, g.vox_sums);
-  // one resident wave: 148 SMs x ST_MIN_BLOCKS CTAs of 4 warps; chunks of 32 leaves are handed out dynamically
-  launch_pdl(voxel_stats_kernel, dim3(std::max(1, std::min(need, 148 * ST_MIN_BLOCKS))), dim3(ST_THREADS), 0, stream, d_pts, g.d_meta, g.pairs[0], g.pairs[1],
-             g.seg_start, g.c_key, n_points, g.vox_sums, g.recs, g.table, g.c_n, g.c_mean, g.c_cov, g.c_icov, g.c_evecs, g.c_evals, g.h_slots, publish_key);
+void launch_voxel_sums(const DeviceGrid& g, uint32_t n_points, cudaStream_t stream) {
+  launch_pdl(voxel_heavy_sums_kernel, dim3(ST_HEAVY_BLOCKS), dim3(ST_THREADS), 0, stream, static_cast<const float4*>(g.sorted_pts),
+             static_cast<const BuildMeta*>(g.d_meta), static_cast<const uint32_t*>(g.seg_start), n_points, g.vox_sums);
+}
+
+void launch_voxel_finalize(const DeviceGrid& g, uint32_t n_points, unsigned long long publish_key, cudaStream_t stream) {
+  const int fin = static_cast<int>((n_points + FIN_THREADS - 1) / FIN_THREADS);
+  launch_pdl(voxel_stats_kernel, dim3(std::max(1, std::min(fin, 148 * FIN_MIN_BLOCKS))), dim3(FIN_THREADS), 0, stream,
+             static_cast<const float4*>(g.sorted_pts), g.d_meta, static_cast<const uint32_t*>(g.seg_start), static_cast<const uint32_t*>(g.c_key),
+             n_points, static_cast<const double*>(g.vox_sums), g.recs, g.table, g.c_n, g.c_mean, g.c_cov, g.c_icov, g.c_evecs, g.c_evals, g.h_slots,
+             publish_key);
 }
 
 }  // namespace ndtb
