@@ -261,15 +261,29 @@ def run_gpu(args, rank, world, local_rank):
         elif resident == "window":
             rc = h.L.ndtb_set_target_window(h.h, n_kf, kf_ids_ptr, kf_P_ptr)
             rc |= h.L.ndtb_set_source(h.h, p_scans[k].data_ptr(), N_SCAN, 16)
-        elif resident:
+        elif resident is True:
             rc = h.set_target_device(d_tgt.data_ptr(), N_MAP)
             rc |= h.set_source_device(d_scans[k].data_ptr(), N_SCAN)
-        else:
+        elif resident == "serial":
             rc = h.L.ndtb_set_target(h.h, p_tgt.data_ptr(), N_MAP, 16)
             rc |= h.L.ndtb_set_source(h.h, p_scans[k].data_ptr(), N_SCAN, 16)
+        else:
+            # pipelined uploads (ndtb_stage_* / ndtb_commit_*): the copy of step i + 1's map and scan is started first and runs on
+            # the copy stream while step i's map is built and aligned; the step ends once that copy has arrived, so every timed
+            # step contains one full 18 MB host-to-device copy
+            kn = (i + 1) % len(scans)
+            if h.staged_count() == (0, 0):                                   # first step of a region: nothing was staged for it
+                rc = h.L.ndtb_stage_target(h.h, p_tgt.data_ptr(), N_MAP, 16) | h.L.ndtb_stage_source(h.h, p_scans[k].data_ptr(), N_SCAN, 16)
+                assert rc == 0, h.L.ndtb_last_error(h.h)
+            rc = h.L.ndtb_stage_target(h.h, p_tgt.data_ptr(), N_MAP, 16)
+            rc |= h.L.ndtb_stage_source(h.h, p_scans[kn].data_ptr(), N_SCAN, 16)
+            rc |= h.L.ndtb_commit_target(h.h)
+            rc |= h.L.ndtb_commit_source(h.h)
         assert rc == 0, h.L.ndtb_last_error(h.h)
         rc = h.L.ndtb_align(h.h, g16_ptr[k], ctypes.byref(res_struct), None, 0, None)
         assert rc == 0, h.L.ndtb_last_error(h.h)
+        if resident is False:
+            assert h.L.ndtb_stage_sync(h.h) == 0
         return res_struct
 
     def timed(resident, steps, warmup):
@@ -314,6 +328,9 @@ def run_gpu(args, rank, world, local_rank):
     h.set_profiling(False)
     total_ms, st = timed(True, args.steps, args.warmup)
     e2e_ms, st2 = timed(False, args.steps, args.warmup)
+    while h.staged_count() != (0, 0):                                        # drain what the last pipelined step staged
+        h.commit_target(); h.commit_source()
+    ser_ms, st6 = timed("serial", args.steps, args.warmup)
     win_ms, st4 = timed("window", args.steps, args.warmup)
     pkt_ms, st5 = timed("packets", args.steps, args.warmup)
     decode_launches, decode_us = lc.stats()
@@ -327,6 +344,7 @@ def run_gpu(args, rank, world, local_rank):
     clk = clocks.stop()
     total_ms = D.max_over_ranks(total_ms, local_rank)
     e2e_ms = D.max_over_ranks(e2e_ms, local_rank)
+    ser_ms = D.max_over_ranks(ser_ms, local_rank)
     win_ms = D.max_over_ranks(win_ms, local_rank)
     pkt_ms = D.max_over_ranks(pkt_ms, local_rank)
     launches = int(D.sum_over_ranks(st["launches"], local_rank))
@@ -358,7 +376,14 @@ def run_gpu(args, rank, world, local_rank):
                              "and a CUDA event pair around each (an empty launch between two events reads ~7 us on this box); "
                              "roofline.kernel_us_back_to_back is the same kernel as 50 back-to-back launches between one event pair"},
         "e2e": {"value": e2e, "unit": "scans/s", "h2d_bytes_per_step": 16 * (N_MAP + N_SCAN) + 64, "d2h_bytes_per_step": int(368 * st2["eval_launches"] / K + 64),
-                "ms_per_step": e2e_ms / K},
+                "ms_per_step": e2e_ms / K, "max_abs_translation_error_m": st2["err"], "build_ms": st2["build_ms"] / K, "align_ms": st2["align_ms"] / K,
+                "what": "host buffers in, result out, through the C ABI: ndtb_stage_target / ndtb_stage_source start the copy of step i + 1's map "
+                        "and scan (18 MB, pinned host memory, copy stream) before ndtb_commit_target / ndtb_commit_source / ndtb_align of step i; "
+                        "the step ends with ndtb_stage_sync, i.e. once that copy has arrived, so every timed step holds one full H2D copy, "
+                        "one map build, one align and the result read-back"},
+        "e2e_serial": {"value": world * K / (ser_ms * 1e-3), "unit": "scans/s", "h2d_bytes_per_step": 16 * (N_MAP + N_SCAN) + 64,
+                       "d2h_bytes_per_step": int(368 * st6["eval_launches"] / K + 64), "ms_per_step": ser_ms / K,
+                       "what": "the same step without pipelining: ndtb_set_target + ndtb_set_source (copy, then build) + ndtb_align, one after the other"},
         "e2e_window": {"value": world * K / (win_ms * 1e-3), "unit": "scans/s", "h2d_bytes_per_step": 16 * N_SCAN + 64 + 128 * n_kf,
                        "d2h_bytes_per_step": int(368 * st4["eval_launches"] / K + 64), "ms_per_step": win_ms / K,
                        "what": "same step through ndtb_set_target_window: the 1M-pt target is assembled on the device from 5 archived keyframe "

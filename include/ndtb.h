@@ -110,6 +110,18 @@ int ndtb_set_source(ndtb_handle h, const float* xyz, size_t n, size_t stride_byt
 /* Same, but the buffers already live in device memory of the handle's GPU (packed float4). */
 int ndtb_set_target_device(ndtb_handle h, const void* d_xyzw, size_t n);
 int ndtb_set_source_device(ndtb_handle h, const void* d_xyzw, size_t n);
+/* Pipelined form of setInputTarget / setInputSource (ndt_omp.h:126-130; the reference's clouds are host memory, so it has no
+ * copy to hide): ndtb_stage_* starts the host-to-device copy of the NEXT cloud on a copy stream and returns at once (the host
+ * buffer must stay valid, and should be pinned, until the matching commit); ndtb_commit_* makes the oldest staged cloud the
+ * current one -- ndtb_commit_target then builds the voxel map exactly like ndtb_set_target.  Up to two clouds of each kind may
+ * be staged (NDTB_ERR_NOT_READY beyond that, or when committing with nothing staged), so cloud i + 1 can be staged before
+ * cloud i is committed and its copy overlaps the build and align of cloud i. */
+int ndtb_stage_target(ndtb_handle h, const float* xyz, size_t n, size_t stride_bytes);
+int ndtb_stage_source(ndtb_handle h, const float* xyz, size_t n, size_t stride_bytes);
+int ndtb_commit_target(ndtb_handle h);
+int ndtb_commit_source(ndtb_handle h);
+int ndtb_staged_count(ndtb_handle h, int* targets, int* sources);
+int ndtb_stage_sync(ndtb_handle h); /* blocks until every staged copy has arrived (a commit does not need it) */
 /* setRegularizationPose / unsetRegularizationPose: ndt_omp.h:277-283.  T == NULL unsets. */
 int ndtb_set_regularization_pose(ndtb_handle h, const float* T16);
 
@@ -354,7 +366,11 @@ int ndtb_set_profiling(ndtb_handle h, int per_kernel_events);
  *                                For a full-rank H the two agree to ~1e-12 relative.
  *   "sessions" (default 1)       0: one kernel launch per evaluation instead of a resident kernel per ndtb_align.
  *   "session_idle_timeout_ms" (default 50)  the resident kernel leaves by itself after this long without a command;
- *                                the host then falls back to one launch per evaluation. */
+ *                                the host then falls back to one launch per evaluation.
+ *   "session_free_sms" (default 0)  the DIRECT1 / DIRECT7 evaluation kernels -- one CTA per SM, the resident kernel of an
+ *                                align included -- leave this many of the 148 SMs to other streams, so that the lidar decode
+ *                                or the window assembly of the NEXT frame can run while an align is open.  The per-CTA
+ *                                partial sums change with the CTA count: results differ from the default by FP64 rounding. */
 int ndtb_set_option(ndtb_handle h, const char* name, double value);
 /* The Newton-direction solve of ndtb_align on its own (host code, no GPU): x = H^-1 b by the path "direct_solver"
  * selects (method 1; falls back to the SVD when H is not certified well conditioned) or by the Jacobi SVD with

@@ -17,6 +17,7 @@
 #include "eval_api.cuh"
 #include "handle.cuh"       // ndtb_compute_derivatives_static (end of this file)
 #include "newton_math.cuh"
+#include <algorithm>
 #include <cstring>
 #include <string>
 
@@ -644,10 +645,15 @@ __global__ void __launch_bounds__(EVAL_THREADS, EVAL_MIN_BLOCKS) eval_kernel(con
   __shared__ double s_red[EVAL_WARPS][RED_PAD];
   __shared__ bool s_last;
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  const int particle = blockIdx.y + particle_offset;
+  const int particle = blockIdx.y + particle_offset;   // row of partials / tickets / results
+  // svn units (SvnExchange::vshards > 1): the row is a (particle, point shard) pair; states are indexed by particle
+  const int vsh = (FLAVOUR == FLAVOUR_SVN) ? xch.vshards : 1;
+  const int unit = (vsh > 1) ? xch.rank + particle * xch.world : 0;
+  const int shard = (vsh > 1) ? unit % vsh : 0;
+  const int state_idx = (vsh > 1) ? unit / vsh : particle;
   {
     const int words = sizeof(EvalState) / 4;
-    const uint32_t* g = reinterpret_cast<const uint32_t*>(states + particle);
+    const uint32_t* g = reinterpret_cast<const uint32_t*>(states + state_idx);
     uint32_t* s = reinterpret_cast<uint32_t*>(&st);
     for (int i = tid; i < words; i += blockDim.x) s[i] = g[i];
   }
@@ -663,8 +669,8 @@ __global__ void __launch_bounds__(EVAL_THREADS, EVAL_MIN_BLOCKS) eval_kernel(con
   const float d2f = static_cast<float>(st.d2);
 
   const int n_groups = (n + PT_GROUP - 1) / PT_GROUP;
-  const int n_warps = gridDim.x * EVAL_WARPS;
-  const int warp_global = blockIdx.x * EVAL_WARPS + w;
+  const int n_warps = gridDim.x * EVAL_WARPS * vsh;   // the shards of a particle deal the point groups out between them
+  const int warp_global = (shard * gridDim.x + blockIdx.x) * EVAL_WARPS + w;
   // this warp's groups: warp_global + k * n_warps, k = 0 .. my_groups-1
   const int my_groups = (n_groups > warp_global) ? (n_groups - warp_global + n_warps - 1) / n_warps : 0;
   int head = 0, tail = 0;  // queue positions (monotonic; entry = pos & (QC - 1))
@@ -734,12 +740,14 @@ __global__ void __launch_bounds__(EVAL_THREADS, EVAL_MIN_BLOCKS) eval_kernel(con
     double v = 0.0;
     if (t < SVN_REC) {
       v = __ldcg(results + static_cast<size_t>(particle) * RED_N + t);   // RED_SCORE, RED_G, RED_H are laid out like the record
-      if (t >= 7 && (t - 7) % 7 == 0) v += 1e-6;                         // H += 1e-6 I  (svn_ndt_impl.hpp:650-653)
-      if (t >= 1 && t < 7 && !isfinite(v)) s_bad[0] = 1;
-      if (t >= 7 && !isfinite(v)) s_bad[1] = 1;
+      if (vsh == 1) {
+        if (t >= 7 && (t - 7) % 7 == 0) v += 1e-6;                       // H += 1e-6 I  (svn_ndt_impl.hpp:650-653)
+        if (t >= 1 && t < 7 && !isfinite(v)) s_bad[0] = 1;
+        if (t >= 7 && !isfinite(v)) s_bad[1] = 1;
+      }
     }
     __syncthreads();
-    const int k = xch.rank + (blockIdx.y + particle_offset) * xch.world;
+    const int k = xch.rank + (blockIdx.y + particle_offset) * xch.world;   // particle, or unit when the particles are sharded
     const size_t row = static_cast<size_t>(xch.parity) * xch.capacity + k;
     if (t < SVN_REC) {
       if (t >= 1 && t < 7 && s_bad[0]) v = 0.0;                          // non-finite gradient -> zero (:656-659)
@@ -1089,7 +1097,7 @@ static cudaError_t launch_session_t(const float4* d_src, int n, const GridMeta& 
   unsigned int* tickets = b.d_tickets;
   void* args[] = {&d_src, &n, &m, &recs, &table, &mailbox, &d_cmd, &partials, &results, &tickets, &seq0, &idle_timeout_ns};
   // cooperative launch: fails (instead of deadlocking on the inter-CTA spin) if the CTAs cannot all be resident at once
-  return cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(align_session_kernel<PROBES>), dim3(eval_blocks_pclomp(n)), dim3(PCL_THREADS), args,
+  return cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(align_session_kernel<PROBES>), dim3(eval_blocks_pclomp(n, b.free_sms)), dim3(PCL_THREADS), args,
                                      sizeof(PclSessionShared), stream);
 }
 
@@ -1106,10 +1114,11 @@ int eval_blocks_for(int n) {
   return b < 148 * EVAL_MIN_BLOCKS ? b : 148 * EVAL_MIN_BLOCKS;
 }
 
-int eval_blocks_pclomp(int n) {
+int eval_blocks_pclomp(int n, int free_sms) {
   const int per_block = PCL_WARPS * 32;  // at least one full chunk per warp
   const int b = (n + per_block - 1) / per_block;
-  return b < 1 ? 1 : (b < 148 ? b : 148);
+  const int cap = std::max(1, 148 - std::max(0, free_sms));
+  return b < 1 ? 1 : (b < cap ? b : cap);
 }
 
 template <int PROBES, bool HESS>
@@ -1121,7 +1130,7 @@ static cudaError_t launch_pclomp_t(const float4* d_src, int n, const GridMeta& m
     cudaError_t e = cudaFuncSetAttribute(eval_kernel_pclomp<PROBES, HESS>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(PclShared)));
     if (e != cudaSuccess) return e;
   }
-  eval_kernel_pclomp<PROBES, HESS><<<eval_blocks_pclomp(n), PCL_THREADS, sizeof(PclShared), stream>>>(d_src, n, meta, recs, table, st, b.d_partials,
+  eval_kernel_pclomp<PROBES, HESS><<<eval_blocks_pclomp(n, b.free_sms), PCL_THREADS, sizeof(PclShared), stream>>>(d_src, n, meta, recs, table, st, b.d_partials,
                                                                                                   results, b.d_tickets, result_key, dbg);
   return cudaGetLastError();
 }
@@ -1140,7 +1149,8 @@ cudaError_t launch_eval_pclomp(int n_probe, bool compute_hessian, const float4* 
 template <int FLAVOUR, int PROBES, bool HESS, bool GN>
 static void launch_t(const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs, const HashSlot* table, const double* c_mean,
                      const double* c_icov, const EvalBuffers& b, int n_particles, int particle_offset, cudaStream_t stream, const SvnExchange& xch) {
-  dim3 grid(eval_blocks_for(n), n_particles);
+  const int vsh = (FLAVOUR == FLAVOUR_SVN && xch.vshards > 1) ? xch.vshards : 1;
+  dim3 grid(std::max(1, eval_blocks_for(n) / vsh), n_particles);
   eval_kernel<FLAVOUR, PROBES, HESS, GN><<<grid, EVAL_THREADS, 0, stream>>>(d_src, n, meta, recs, table, c_mean, c_icov, b.d_states,
                                                                            b.d_partials, b.d_results, b.d_tickets, particle_offset, xch);
 }

@@ -10,6 +10,7 @@ struct EvalBuffers {
   double* d_results = nullptr;     // [max_particles][RED_N]
   unsigned int* d_tickets = nullptr;  // [max_particles] last-block-done counters (self-resetting)
   int max_particles = 0, max_blocks = 0;
+  int free_sms = 0;   // DIRECT1 / DIRECT7 kernels (one CTA per SM) leave this many SMs to other streams ("session_free_sms")
 };
 
 constexpr int EVAL_THREADS = 128;
@@ -25,7 +26,9 @@ constexpr int EVAL_THREADS = 128;
 constexpr int SVN_MAX_RANKS = 8;
 constexpr int SVN_REC = 43;
 struct SvnExchange {
-  int world = 1, rank = 0;          // particle of block row s is  k = rank + s * world
+  int world = 1, rank = 0;          // block row s evaluates UNIT u = rank + s * world: particle u / vshards, point shard u % vshards
+  int vshards = 1;                  // point shards per particle (1: a unit is a whole particle and the record carries the guards of
+                                    // svn_ndt_impl.hpp:650-663; > 1: raw partial sums, the consumer adds the shards in order first)
   int n_dest = 0;                   // windows the record is stored to: rec[0..n_dest-1] (n_dest == world across GPUs, 1 = local only)
   int capacity = 0;                 // particles per parity half of a window
   int parity = 0;                   // window half of this iteration (stamp & 1)
@@ -53,7 +56,7 @@ int eval_blocks_for(int n);
 cudaError_t launch_eval_pclomp(int n_probe, bool compute_hessian, const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs,
                                const HashSlot* table, const EvalState& st, const EvalBuffers& bufs, double* results,
                                unsigned long long result_key, cudaStream_t stream, unsigned long long* dbg_stamps = nullptr);
-int eval_blocks_pclomp(int n);
+int eval_blocks_pclomp(int n, int free_sms = 0);
 
 // Alignment session (see align_session_kernel): one command per evaluation, written by the host into a pinned
 // mailbox of 64 units {word, word ^ session_key(seq)}; seq increases monotonically over the life of a handle.

@@ -20,6 +20,12 @@ struct ndtb_handle_s {
   float4* d_target = nullptr; size_t n_target = 0, target_alloc = 0; bool target_owned = true;
   float4* d_source = nullptr; size_t n_source = 0, source_alloc = 0; bool source_owned = true;
   void* h_stage = nullptr; size_t stage_alloc = 0;  // pinned staging for strided host clouds
+  // ndtb_stage_target / ndtb_stage_source (stage_api.cu): the NEXT clouds are copied to the device on a copy stream while the
+  // current align runs; a FIFO of two per kind, committed by swapping buffers with d_target / d_source
+  struct StagedCloud { float4* d = nullptr; size_t alloc = 0, n = 0; cudaEvent_t ready = nullptr, reusable = nullptr; };
+  StagedCloud staged[2][2];             // [0] target, [1] source
+  int staged_head[2] = {0, 0}, staged_count[2] = {0, 0};
+  cudaStream_t stage_stream = nullptr;
 
   // keyframe archive (pointsArchive of the reference's pipelines): clouds uploaded once, windows assembled on device
   struct Keyframe { float4* d_points = nullptr; size_t n = 0; };
@@ -117,4 +123,5 @@ int mg_eval(ndtb_handle_s* h, const double* p, const float* T16, bool compute_he
 bool mg_ready(ndtb_handle_s* h);
 void mg_free(ndtb_handle_s* h);
 void svn_dev_free(ndtb_handle_s* h);  // svn_stein.cu
+void stage_free(ndtb_handle_s* h);    // stage_api.cu
 }  // namespace ndtb

@@ -4,6 +4,7 @@
 #include "handle.cuh"
 #include "newton_math.cuh"
 #include <cstring>
+#include <time.h>
 #include <cstdio>
 #include <cmath>
 #include <algorithm>
@@ -180,6 +181,19 @@ static void session_end(ndtb_handle_s* h) {
 
 void finish_eval(ndtb_handle_s* h, int n, const double* r, const double* p, double* score, double* g, double* H, double* nvtl);
 
+// Bounded back-off of the host poll loops: a pipeline hint per probe (the sibling hyper-thread gets the core's issue slots), and
+// once an answer is clearly late (> ~0.1 ms of spinning: a kernel queued behind other work, a debugger, a contended box) the
+// thread yields its time slice instead of burning the core -- at most 50 us per probe, so the latency cost stays bounded.
+static inline void poll_backoff(unsigned int spins) {
+#if defined(__x86_64__) || defined(__i386__)
+  __builtin_ia32_pause();
+#endif
+  if (spins > (1u << 15) && (spins & 255u) == 0) {
+    struct timespec ts = {0, 50000};
+    nanosleep(&ts, nullptr);
+  }
+}
+
 // One pclomp evaluation: upload state, launch, read back the 46-double result, apply the
 // regulariser (ndt_omp_impl.hpp:349-382) and NVTL (:384-389) on the host.
 static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool compute_hessian, double* score, double* g, double* H,
@@ -247,6 +261,7 @@ static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool
       for (;;) {
         const unsigned long long w0 = slots[2 * c], w1 = slots[2 * c + 1];
         if ((w0 ^ w1) == key) { std::memcpy(&rbuf[c], &w0, 8); break; }
+        poll_backoff(spins);
         if ((++spins & 4095u) == 0) {  // a stream query every 4096 spins catches a failed launch
           const cudaError_t q = cudaStreamQuery(h->stream);
           if (q != cudaSuccess && q != cudaErrorNotReady) { h->session_open = false; h->last_error = std::string("eval kernel: ") + cudaGetErrorString(q); return NDTB_ERR_CUDA; }
@@ -269,7 +284,7 @@ static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool
     std::vector<unsigned long long> st(8 * 148);
     cudaStreamSynchronize(h->stream);
     cudaMemcpy(st.data(), d_dbg, st.size() * 8, cudaMemcpyDeviceToHost);
-    const int nb = eval_blocks_pclomp(n);
+    const int nb = eval_blocks_pclomp(n, h->eval.free_sms);
     unsigned long long t0 = ~0ull;
     for (int b = 0; b < nb; ++b) t0 = std::min(t0, st[8 * b]);
     unsigned long long mx[6] = {0, 0, 0, 0, 0, 0}, mn[6] = {~0ull, ~0ull, ~0ull, ~0ull, ~0ull, ~0ull};
@@ -373,6 +388,7 @@ int ndtb_destroy(ndtb_handle h) {
   if (h->batch_h_results) cudaFreeHost(h->batch_h_results);
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   svn_dev_free(h);
+  stage_free(h);
   for (int i = 0; i < 4; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   for (int i = 0; i < 2; ++i) if (h->ev_b[i]) cudaEventDestroy(h->ev_b[i]);
   cudaStreamDestroy(h->stream);
@@ -805,6 +821,11 @@ int ndtb_set_option(ndtb_handle h, const char* name, double value) {
   if (k == "direct_solver") h->direct_solver = value != 0;           // 0: always the Jacobi SVD (Eigen::JacobiSVD restatement)
   else if (k == "sessions") h->use_sessions = value != 0;            // 0: one kernel launch per evaluation
   else if (k == "session_idle_timeout_ms") h->session_idle_ms = value > 0 ? value : 50.0;
+  else if (k == "session_free_sms") {   // the one-CTA-per-SM evaluation kernels (resident session included) leave this many SMs free
+    if (value < 0 || value > 140) return set_error(h, NDTB_ERR_INVALID, "session_free_sms must be in [0, 140]");
+    if (h->session_open) return set_error(h, NDTB_ERR_NOT_READY, "an alignment session is running");
+    h->eval.free_sms = static_cast<int>(value);
+  }
   else if (k == "batch_interleave") h->batch_interleave = value != 0;  // 0: ndtb_align_batch aligns one scan after the other
   else return set_error(h, NDTB_ERR_INVALID, "unknown option");
   return NDTB_OK;

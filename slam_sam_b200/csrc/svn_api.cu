@@ -197,6 +197,14 @@ static int svn_align_device(ndtb_handle h, const double prior[16], const double*
   CKH(cudaMemsetAsync(d.d_wait_ns, 0, sizeof(unsigned long long), h->stream));
   const int max_iter = h->svn.max_iterations;
   while (d.ev.size() < 3 * static_cast<size_t>(std::max(max_iter, 1))) { cudaEvent_t e; CKH(cudaEventCreate(&e)); d.ev.push_back(e); }
+  // Work units of the loop: every particle is cut into `vsh` point shards (the point groups dealt out between them), the K * vsh
+  // units go round-robin to the ranks -- an even load for any particle count, 100 particles over 8 GPUs included -- and the Stein
+  // kernel adds a particle's shard records in shard order.  The shard count depends on K alone, not on the number of ranks, so the
+  // sharded align and the single-GPU align add the same partial sums in the same order: bit-identical results.
+  // vsh = the smallest power of two that makes K * vsh a multiple of 8 (an even split over 1, 2, 4 or 8 ranks): 2 for K = 100.
+  int vsh = 1;
+  while (vsh < 8 && (K * vsh) % 8 != 0) vsh <<= 1;
+  while (vsh > 1 && K * vsh > ndtb_handle_s::SvnDev::CAPACITY) vsh >>= 1;
   const unsigned long long stamp0 = d.stamp;
   int iterations = 0, done = 0, queued = 0;
   auto wait_status = [&](int it) -> int {   // returns the done code of iteration `it` (0 running on, 1 converged, 2 peer time-out), < 0 on a CUDA error
@@ -216,10 +224,10 @@ static int svn_align_device(ndtb_handle h, const double prior[16], const double*
   for (int iter = 0; iter < max_iter; ++iter) {
     unsigned long long stamp = 0;
     cudaEventRecord(d.ev[3 * iter], h->stream);
-    rc = svn_dev_stage1(h, K, d.rank, d.world, true, &stamp);
+    rc = svn_dev_stage1(h, K, d.rank, d.world, true, &stamp, vsh);
     if (rc != NDTB_OK) return rc;
     cudaEventRecord(d.ev[3 * iter + 1], h->stream);
-    rc = svn_dev_stein(h, K, stamp, true, true, true, iter);
+    rc = svn_dev_stein(h, K, stamp, true, true, true, iter, vsh);
     if (rc != NDTB_OK) return rc;
     cudaEventRecord(d.ev[3 * iter + 2], h->stream);
     queued = iter + 1;
@@ -250,7 +258,8 @@ static int svn_align_device(ndtb_handle h, const double prior[16], const double*
   cudaEventRecord(h->ev[1], h->stream);
   CKH(cudaStreamSynchronize(h->stream));
   if (done == 2) return set_error(h, NDTB_ERR_CUDA, "svn align: a peer rank did not deliver its particle records in time");
-  h->last_found = r0[RED_FOUND]; h->last_hits = r0[RED_COUNT] / static_cast<double>(h->n_source);
+  // row 0 is one point shard of a particle (the shards interleave the point groups): scaled to the whole cloud
+  h->last_found = r0[RED_FOUND] * vsh; h->last_hits = r0[RED_COUNT] * vsh / static_cast<double>(h->n_source);
   d.eval_ms = 0; d.stein_ms = 0;
   for (int it = 0; it < iterations; ++it) {
     float a = 0, b = 0;

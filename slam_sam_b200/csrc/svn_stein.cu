@@ -71,107 +71,158 @@ struct SteinMean {               // mean pose + stop test + status slot (all opt
   unsigned long long* wait_ns;   // accumulated record wait of block 0
 };
 
-__global__ void __launch_bounds__(STEIN_THREADS) stein_kernel(int K, const double* __restrict__ poses, const double* rec /* [K][43] window half */,
-                                                              const unsigned long long* flags /* [K] or nullptr */, unsigned long long stamp,
+// Shared memory of one block: the records, kernel values and kernel gradients of a tile of STEIN_THREADS particles l.
+struct SteinTile {
+  double rec[STEIN_THREADS][STEIN_N];   // {g (GTSAM order), H (GTSAM order)} of particle l, guards applied
+  double kg[STEIN_THREADS][6];          // grad_k of the RBF kernel
+  double kv[STEIN_THREADS];             // k(P_l, P_k)
+  unsigned char use[STEIN_THREADS];     // bit 0: pair finite, bit 1: gradient finite, bit 2: Hessian finite
+};
+
+__global__ void __launch_bounds__(STEIN_THREADS) stein_kernel(int K, const double* __restrict__ poses, const double* rec /* [K * vshards][43] window half */,
+                                                              const unsigned long long* flags /* [K * vshards] or nullptr */, unsigned long long stamp,
                                                               double kernel_h, double step_size, double* __restrict__ updates,
-                                                              double* __restrict__ new_poses, const SteinMean mm) {
+                                                              double* __restrict__ new_poses, const SteinMean mm, int vshards) {
   if (mm.done && *mm.done) return;  // speculatively queued iteration after the align converged
-  __shared__ double s_red[STEIN_THREADS / 32][STEIN_N];
-  __shared__ double s_xi[STEIN_THREADS][6];
+  extern __shared__ __align__(16) unsigned char stein_raw[];   // sizeof(SteinTile): above the 48 KB static limit
+  SteinTile& tl = *reinterpret_cast<SteinTile*>(stein_raw);
+  __shared__ double s_acc[STEIN_N];
+  double (*s_xi)[6] = tl.kg;                                    // the tail reuses the kernel-gradient rows
   __shared__ bool s_last;
   __shared__ int s_timeout;
   const int k = blockIdx.x;
-  if (threadIdx.x == 0) s_timeout = 0;
+  const int tid = threadIdx.x;
+  if (tid == 0) s_timeout = 0;
   Pose Pk;
   pose_from16(poses + 16 * k, Pk);
-  double acc[STEIN_N];
-#pragma unroll
-  for (int i = 0; i < STEIN_N; ++i) acc[i] = 0.0;
-  const int perm[6] = {3, 4, 5, 0, 1, 2};  // NDT (t, r) -> GTSAM (r, t)   svn_ndt_impl.hpp:731-735
-  const unsigned long long t_wait0 = (flags && blockIdx.x == 0 && threadIdx.x == 0) ? svn_globaltimer() : 0ull;
+  const unsigned long long t_wait0 = (flags && blockIdx.x == 0 && tid == 0) ? svn_globaltimer() : 0ull;
+  unsigned long long waited = 0;
+  // component t of {phi, H}: its own accumulator, summed over l IN PARTICLE ORDER like the reference's loop (:795-815)
+  double acc = 0.0;
+  const int ci = (tid < 6) ? tid : (tid - 6) / 6, cj = (tid < 6) ? 0 : (tid - 6) % 6;
   __syncthreads();
-  for (int l = threadIdx.x; l < K; l += blockDim.x) {
-    if (flags) {
-      // acquire particle l's record: stored by the derivative kernel of the GPU that owns l (possibly over NVLink)
-      unsigned long long seen;
-      unsigned int spins = 0;
-      unsigned long long t0 = 0;
-      for (;;) {
-        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(flags + l) : "memory");
-        if (seen == stamp) break;
-        if ((++spins & 1023u) == 0) {
-          const unsigned long long now = svn_globaltimer();
-          if (!t0) t0 = now;
-          if (now - t0 > SVN_PEER_TIMEOUT_NS) { s_timeout = 1; break; }
+  for (int base = 0; base < K; base += STEIN_THREADS) {
+    const int l = base + tid;
+    // ---- phase 1, one thread per particle l: its record (shards added in order, guards), kernel value and gradient ---------
+    if (l < K) {
+      double gl[6], Hl[36];
+#pragma unroll
+      for (int i = 0; i < 6; ++i) gl[i] = 0.0;
+#pragma unroll
+      for (int i = 0; i < 36; ++i) Hl[i] = 0.0;
+      for (int sh = 0; sh < vshards; ++sh) {
+        const int row = l * vshards + sh;
+        if (flags) {
+          // acquire the record: stored by the derivative kernel of the GPU that owns the unit (possibly over NVLink)
+          unsigned long long seen;
+          unsigned int spins = 0;
+          unsigned long long t0 = 0;
+          for (;;) {
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(flags + row) : "memory");
+            if (seen == stamp) break;
+            if ((++spins & 1023u) == 0) {
+              const unsigned long long now = svn_globaltimer();
+              if (!t0) t0 = now;
+              if (now - t0 > SVN_PEER_TIMEOUT_NS) { s_timeout = 1; break; }
+            }
+          }
+        }
+        const double* rl = rec + static_cast<size_t>(SVN_REC) * row;
+        if (vshards == 1) {
+#pragma unroll
+          for (int i = 0; i < 6; ++i) gl[i] = __ldcg(rl + 1 + i);
+#pragma unroll
+          for (int i = 0; i < 36; ++i) Hl[i] = __ldcg(rl + 7 + i);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 6; ++i) gl[i] += __ldcg(rl + 1 + i);
+#pragma unroll
+          for (int i = 0; i < 36; ++i) Hl[i] += __ldcg(rl + 7 + i);
+        }
+      }
+      if (t_wait0 && base == 0) waited = svn_globaltimer() - t_wait0;
+      if (vshards > 1) {
+        // particle l's record = the sum, in shard order, of its unit records; the guards of svn_ndt_impl.hpp:650-663 follow the sum
+#pragma unroll
+        for (int i = 0; i < 6; ++i) Hl[7 * i] += 1e-6;                     // H += 1e-6 I  (:650-653)
+        bool gbad = false, hbad = false;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) gbad = gbad || !isfinite(gl[i]);
+#pragma unroll
+        for (int i = 0; i < 36; ++i) hbad = hbad || !isfinite(Hl[i]);
+        if (gbad) {                                                         // non-finite gradient -> zero (:656-659)
+#pragma unroll
+          for (int i = 0; i < 6; ++i) gl[i] = 0.0;
+        }
+        if (hbad) {                                                         // non-finite Hessian -> identity (:660-663)
+#pragma unroll
+          for (int i = 0; i < 36; ++i) Hl[i] = (i % 7 == 0) ? 1.0 : 0.0;
+        }
+      }
+      bool gfin = true, hfin = true;
+#pragma unroll
+      for (int i = 0; i < 6; ++i) gfin = gfin && isfinite(gl[i]);
+#pragma unroll
+      for (int i = 0; i < 36; ++i) hfin = hfin && isfinite(Hl[i]);
+      // NDT (t, r) -> GTSAM (r, t) order  svn_ndt_impl.hpp:731-735: component i of GTSAM is component (i + 3) % 6 of NDT
+#pragma unroll
+      for (int i = 0; i < 6; ++i) tl.rec[tid][i] = gl[(i + 3) % 6];
+#pragma unroll
+      for (int i = 0; i < 6; ++i)
+#pragma unroll
+        for (int j = 0; j < 6; ++j) tl.rec[tid][6 + 6 * i + j] = Hl[6 * ((i + 3) % 6) + (j + 3) % 6];
+      double k_val, k_grad[6];
+      if (kernel_h <= 1e-12) {
+        k_val = (l == k) ? 1.0 : 0.0;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) k_grad[i] = 0.0;
+      } else {
+        Pose Pl;
+        pose_from16(poses + 16 * l, Pl);
+        double xi[6];
+        pose_logmap(pose_between(Pl, Pk), xi);                              // xi_lk = Logmap(P_l^-1 P_k)   :214-244
+        double sq = 0.0;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) sq += xi[i] * xi[i];
+        k_val = exp(-sq / kernel_h);
+        const double f = k_val * (-2.0 / kernel_h);
+#pragma unroll
+        for (int i = 0; i < 6; ++i) k_grad[i] = f * xi[i];
+      }
+      bool fin = isfinite(k_val);
+#pragma unroll
+      for (int i = 0; i < 6; ++i) fin = fin && isfinite(k_grad[i]);
+      tl.kv[tid] = k_val;
+#pragma unroll
+      for (int i = 0; i < 6; ++i) tl.kg[tid][i] = k_grad[i];
+      tl.use[tid] = static_cast<unsigned char>((fin ? 1 : 0) | (gfin ? 2 : 0) | (hfin ? 4 : 0));
+    }
+    __syncthreads();
+    // ---- phase 2, one thread per component: the sum over the tile's particles, in particle order ---------------------------
+    if (tid < STEIN_N) {
+      const int cnt = min(STEIN_THREADS, K - base);
+      for (int q = 0; q < cnt; ++q) {
+        const unsigned char u = tl.use[q];
+        if (!(u & 1)) continue;
+        const double kv = tl.kv[q];
+        if (tid < 6) {
+          if (u & 2) acc += kv * tl.rec[q][tid];
+          acc += tl.kg[q][tid];
+        } else {
+          if (u & 4) acc += (kv * kv) * tl.rec[q][tid];
+          acc += tl.kg[q][ci] * tl.kg[q][cj];
         }
       }
     }
-    const double* rl = rec + static_cast<size_t>(SVN_REC) * l;
-    double gl[6], Hl[36];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) gl[i] = __ldcg(rl + 1 + i);
-#pragma unroll
-    for (int i = 0; i < 36; ++i) Hl[i] = __ldcg(rl + 7 + i);
-    double k_val, k_grad[6];
-    if (kernel_h <= 1e-12) {
-      k_val = (l == k) ? 1.0 : 0.0;
-#pragma unroll
-      for (int i = 0; i < 6; ++i) k_grad[i] = 0.0;
-    } else {
-      Pose Pl;
-      pose_from16(poses + 16 * l, Pl);
-      double xi[6];
-      pose_logmap(pose_between(Pl, Pk), xi);
-      double sq = 0.0;
-#pragma unroll
-      for (int i = 0; i < 6; ++i) sq += xi[i] * xi[i];
-      k_val = exp(-sq / kernel_h);
-      const double f = k_val * (-2.0 / kernel_h);
-#pragma unroll
-      for (int i = 0; i < 6; ++i) k_grad[i] = f * xi[i];
-    }
-    bool fin = isfinite(k_val);
-#pragma unroll
-    for (int i = 0; i < 6; ++i) fin = fin && isfinite(k_grad[i]);
-    if (!fin) continue;
-    bool gfin = true, hfin = true;
-#pragma unroll
-    for (int i = 0; i < 6; ++i) gfin = gfin && isfinite(gl[i]);
-#pragma unroll
-    for (int i = 0; i < 36; ++i) hfin = hfin && isfinite(Hl[i]);
-#pragma unroll
-    for (int i = 0; i < 6; ++i) {
-      if (gfin) acc[i] += k_val * gl[perm[i]];
-      acc[i] += k_grad[i];
-    }
-    const double kk = k_val * k_val;
-#pragma unroll
-    for (int i = 0; i < 6; ++i)
-#pragma unroll
-      for (int j = 0; j < 6; ++j) {
-        if (hfin) acc[6 + 6 * i + j] += kk * Hl[6 * perm[i] + perm[j]];
-        acc[6 + 6 * i + j] += k_grad[i] * k_grad[j];
-      }
+    __syncthreads();
   }
-#pragma unroll
-  for (int i = 0; i < STEIN_N; ++i) {
-    double v = acc[i];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    acc[i] = v;
-  }
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  if (lane == 0) {
-#pragma unroll
-    for (int i = 0; i < STEIN_N; ++i) s_red[w][i] = acc[i];
-  }
+  if (tid < STEIN_N) s_acc[tid] = acc;
   __syncthreads();
-  if (threadIdx.x == 0) {
-    if (t_wait0 && mm.wait_ns) *mm.wait_ns += svn_globaltimer() - t_wait0;  // (upper bound: includes this block's own sums)
+  if (tid == 0) {
+    if (t_wait0 && mm.wait_ns) *mm.wait_ns += waited;
     double phi[6], Ht[36];
     for (int i = 0; i < STEIN_N; ++i) {
-      double v = s_red[0][i];
-      for (int ww = 1; ww < STEIN_THREADS / 32; ++ww) v += s_red[ww][i];
+      const double v = s_acc[i];
       if (i < 6) phi[i] = v / static_cast<double>(K); else Ht[i - 6] = v / static_cast<double>(K);
     }
     for (int i = 0; i < 6; ++i) Ht[7 * i] += 1e-6;
@@ -207,6 +258,7 @@ __global__ void __launch_bounds__(STEIN_THREADS) stein_kernel(int K, const doubl
   Pose prior_p;
   pose_from16(mm.prior, prior_p);
   double mean_xi[6] = {0, 0, 0, 0, 0, 0};
+  double mean_one = 0.0;
   for (int base = 0; base < K; base += STEIN_THREADS) {
     const int kk = base + threadIdx.x;
     if (kk < K) {
@@ -221,15 +273,16 @@ __global__ void __launch_bounds__(STEIN_THREADS) stein_kernel(int K, const doubl
       for (int i = 0; i < 6; ++i) s_xi[threadIdx.x][i] = xi[i];
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (threadIdx.x < 6) {                // one thread per component, k order like the reference's loop (:865-870)
       const int cnt = min(STEIN_THREADS, K - base);
-      for (int t = 0; t < cnt; ++t)       // k order, like the reference's loop (:865-870)
-        for (int i = 0; i < 6; ++i) mean_xi[i] += s_xi[t][i];
+      for (int t = 0; t < cnt; ++t) mean_one += s_xi[t][threadIdx.x];
     }
     __syncthreads();
   }
+  if (threadIdx.x < 6) s_xi[0][threadIdx.x] = mean_one;
+  __syncthreads();
   if (threadIdx.x == 0) {
-    for (int i = 0; i < 6; ++i) mean_xi[i] /= static_cast<double>(K);
+    for (int i = 0; i < 6; ++i) mean_xi[i] = s_xi[0][i] / static_cast<double>(K);
     const Pose mean_cur = pose_retract(prior_p, mean_xi);
     Pose mean_last;
     pose_from16(mm.mean_prev, mean_last);
@@ -293,11 +346,12 @@ int svn_dev_upload_poses(ndtb_handle_s* h, int K, const double* poses) {
   return NDTB_OK;
 }
 
-int svn_dev_stage1(ndtb_handle_s* h, int K, int first, int stride, bool to_peers, unsigned long long* stamp_out) {
+int svn_dev_stage1(ndtb_handle_s* h, int K, int first, int stride, bool to_peers, unsigned long long* stamp_out, int vshards) {
   ndtb_handle_s::SvnDev& d = h->svnd;
   const int n = static_cast<int>(h->n_source);
-  const int m = (K > first) ? (K - first + stride - 1) / stride : 0;  // own particles
-  int rc = ensure_eval_buffers(h, std::max(m, 1), n);
+  const int units = K * vshards;                                                  // vshards == 1: a unit is a particle
+  const int m = (units > first) ? (units - first + stride - 1) / stride : 0;      // own units
+  int rc = ensure_eval_buffers(h, std::max(vshards > 1 ? std::max(m, K) : m, 1), n);
   if (rc != NDTB_OK) return rc;
   // collective iterations count in d.stamp (all ranks in lock-step); local parity hooks take stamps from their own sequence with
   // the top bit set, so they can never satisfy -- or be mistaken for -- a flag a peer is waited on for
@@ -306,8 +360,10 @@ int svn_dev_stage1(ndtb_handle_s* h, int K, int first, int stride, bool to_peers
   if (m == 0) return NDTB_OK;
   double d1, d2, d3;
   gauss_svn(h->params.outlier_ratio, h->params.resolution, &d1, &d2, &d3);
-  svn_state_kernel<<<(m + 127) / 128, 128, 0, h->stream>>>(K, first, stride, d.d_poses[d.cur], h->eval.d_states, d1, d2, d3, d.d_done);
+  if (vshards > 1) svn_state_kernel<<<(K + 127) / 128, 128, 0, h->stream>>>(K, 0, 1, d.d_poses[d.cur], h->eval.d_states, d1, d2, d3, d.d_done);  // every particle: units index the states by particle
+  else svn_state_kernel<<<(m + 127) / 128, 128, 0, h->stream>>>(K, first, stride, d.d_poses[d.cur], h->eval.d_states, d1, d2, d3, d.d_done);
   SvnExchange x;
+  x.vshards = vshards;
   x.world = stride; x.rank = first; x.capacity = ndtb_handle_s::SvnDev::CAPACITY;
   x.parity = static_cast<int>(stamp & 1ull); x.stamp = stamp; x.done = d.d_done;
   if (to_peers && d.world > 1) {
@@ -325,7 +381,7 @@ int svn_dev_stage1(ndtb_handle_s* h, int K, int first, int stride, bool to_peers
   return NDTB_OK;
 }
 
-int svn_dev_stein(ndtb_handle_s* h, int K, unsigned long long stamp, bool wait_flags, bool write_poses, bool with_mean, int iter) {
+int svn_dev_stein(ndtb_handle_s* h, int K, unsigned long long stamp, bool wait_flags, bool write_poses, bool with_mean, int iter, int vshards) {
   ndtb_handle_s::SvnDev& d = h->svnd;
   constexpr int C = ndtb_handle_s::SvnDev::CAPACITY;
   const int parity = static_cast<int>(stamp & 1ull);
@@ -341,8 +397,10 @@ int svn_dev_stein(ndtb_handle_s* h, int K, unsigned long long stamp, bool wait_f
     mm.status_key = 0x9E3779B97F4A7C15ull * stamp | 1ull;
     mm.iter = iter; mm.wait_ns = d.d_wait_ns;
   }
-  stein_kernel<<<K, STEIN_THREADS, 0, h->stream>>>(K, d.d_poses[d.cur], rec, flags, stamp, h->svn.kernel_bandwidth, h->svn.step_size, d.d_updates,
-                                                   write_poses ? d.d_poses[d.cur ^ 1] : nullptr, mm);
+  static bool configured[MAX_DEVICES] = {};
+  if (needs_func_setup(configured)) CKS(cudaFuncSetAttribute(stein_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(SteinTile))));
+  stein_kernel<<<K, STEIN_THREADS, sizeof(SteinTile), h->stream>>>(K, d.d_poses[d.cur], rec, flags, stamp, h->svn.kernel_bandwidth, h->svn.step_size, d.d_updates,
+                                                   write_poses ? d.d_poses[d.cur ^ 1] : nullptr, mm, vshards);
   CKS(cudaGetLastError());
   if (write_poses) d.cur ^= 1;
   h->launches += 1;

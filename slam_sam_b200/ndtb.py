@@ -59,7 +59,8 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "nd
            "ndtb_mg_add_target", "ndtb_mg_remove_target", "ndtb_mg_create_kdtree", "ndtb_mg_set_input_target", "ndtb_mg_get_info",
            "ndtb_mg_get_grid_ids", "ndtb_mg_get_leaves", "ndtb_mg_compute_derivatives", "ndtb_mg_align", "ndtb_mg_calculate_scores",
            "ndtb_svn_get_timings", "ndtb_comm_window_handle", "ndtb_comm_connect", "ndtb_comm_init", "ndtb_comm_close", "ndtb_comm_info",
-           "ndtb_svn_align_sharded", "ndtb_calculate_score", "ndtb_write_ndt_files", "ndtb_compute_derivatives_static"]
+           "ndtb_svn_align_sharded", "ndtb_calculate_score", "ndtb_write_ndt_files", "ndtb_compute_derivatives_static", "ndtb_stage_target", "ndtb_stage_source",
+           "ndtb_commit_target", "ndtb_commit_source", "ndtb_staged_count", "ndtb_stage_sync"]
 
 _LIB = None
 
@@ -104,6 +105,12 @@ def lib():
         L.ndtb_set_source.argtypes = [H, C.c_void_p, C.c_size_t, C.c_size_t]
         L.ndtb_set_target_device.argtypes = [H, C.c_void_p, C.c_size_t]
         L.ndtb_set_source_device.argtypes = [H, C.c_void_p, C.c_size_t]
+        L.ndtb_stage_target.argtypes = [H, C.c_void_p, C.c_size_t, C.c_size_t]
+        L.ndtb_stage_source.argtypes = [H, C.c_void_p, C.c_size_t, C.c_size_t]
+        L.ndtb_commit_target.argtypes = [H]
+        L.ndtb_commit_source.argtypes = [H]
+        L.ndtb_stage_sync.argtypes = [H]
+        L.ndtb_staged_count.argtypes = [H, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.ndtb_set_regularization_pose.argtypes = [H, c_f]
         L.ndtb_compute_derivatives.argtypes = [H, c_d, c_f, C.c_int, c_d, c_d, c_d, c_d]
         L.ndtb_compute_derivatives_static.argtypes = [H, C.c_void_p, C.c_size_t, c_d, c_f, C.c_int, c_d, c_d, c_d, c_d]
@@ -292,6 +299,30 @@ class Handle:
     def set_source(self, cloud):
         a, n, s = host_cloud(cloud)
         return self.L.ndtb_set_source(self.h, a.ctypes.data, n, s)
+
+    def stage_target(self, cloud):
+        """Starts the upload of the NEXT target (keep `cloud` alive until commit_target); see ndtb_stage_target."""
+        a, n, s = host_cloud(cloud)
+        self._staged = getattr(self, "_staged", []) + [a]
+        return self.L.ndtb_stage_target(self.h, a.ctypes.data, n, s)
+
+    def stage_source(self, cloud):
+        a, n, s = host_cloud(cloud)
+        self._staged = getattr(self, "_staged", []) + [a]
+        return self.L.ndtb_stage_source(self.h, a.ctypes.data, n, s)
+
+    def commit_target(self):
+        return self.L.ndtb_commit_target(self.h)
+
+    def commit_source(self):
+        return self.L.ndtb_commit_source(self.h)
+
+    def staged_count(self):
+        t, s = C.c_int(0), C.c_int(0)
+        self.check(self.L.ndtb_staged_count(self.h, C.byref(t), C.byref(s)))
+        if t.value == 0 and s.value == 0:
+            self._staged = []
+        return t.value, s.value
 
     def set_target_device(self, ptr, n):
         return self.L.ndtb_set_target_device(self.h, C.c_void_p(ptr), n)
@@ -513,7 +544,7 @@ class Handle:
         return float(us[0])
 
     def set_option(self, name, value):
-        """ndtb_set_option: "direct_solver", "sessions", "session_idle_timeout_ms"."""
+        """ndtb_set_option: "direct_solver", "sessions", "session_idle_timeout_ms", "session_free_sms", "batch_interleave"."""
         self.check(self.L.ndtb_set_option(self.h, name.encode(), float(value)))
 
     def stream_ptr(self):

@@ -292,3 +292,41 @@ def test_ndt_export_files_byte_for_byte(oracle, street, tmp_path):
     assert len(first) == 16 and int(first[15]) >= 6
     lines = (tmp_path / "gp.txt").read_text().splitlines()
     assert len(lines) == 5 and lines[2].split()[3] == "2.50000000"
+
+
+def test_staged_uploads_equal_the_direct_ones(street):
+    """ndtb_stage_* / ndtb_commit_*: the pipelined setInputTarget / setInputSource give the same map and the same align, in
+    FIFO order, and refuse a third staged cloud / a commit with nothing staged."""
+    tgt, src = street["target"], street["source"]
+    tgt2 = np.ascontiguousarray(tgt[: tgt.shape[0] // 2])
+    direct = ndtb.Handle(0); direct.set_params(resolution=1.0)
+    assert direct.set_target(tgt) == 0 and direct.set_source(src) == 0
+    want_map, want = direct.voxels(), direct.align()
+    h = ndtb.Handle(0); h.set_params(resolution=1.0)
+    assert h.commit_target() == ndtb.NDTB_ERR_NOT_READY and h.commit_source() == ndtb.NDTB_ERR_NOT_READY
+    assert h.stage_target(tgt2) == 0 and h.stage_target(tgt) == 0        # two in flight
+    assert h.stage_target(tgt) == ndtb.NDTB_ERR_NOT_READY                # a third is refused
+    assert h.stage_source(src[:, :3]) == 0                               # 12-byte stride
+    assert h.staged_count() == (2, 1)
+    assert h.commit_target() == 0                                        # oldest first: the half cloud
+    direct2 = ndtb.Handle(0); direct2.set_params(resolution=1.0)
+    assert direct2.set_target(tgt2) == 0
+    assert_grid_equal(h.voxels(), direct2.voxels())
+    assert h.commit_target() == 0 and h.commit_source() == 0
+    assert h.staged_count() == (0, 0)
+    assert_grid_equal(h.voxels(), want_map)
+    got = h.align()
+    assert got["iterations"] == want["iterations"] and np.array_equal(got["T"], want["T"])
+    # keep going: the buffers rotate (the former target buffer is the next staging slot)
+    for k in range(4):
+        assert h.stage_target(tgt if k % 2 else tgt2) == 0 and h.stage_source(src) == 0
+        assert h.commit_target() == 0 and h.commit_source() == 0
+        assert_grid_equal(h.voxels(), want_map if k % 2 else direct2.voxels())
+    assert np.array_equal(h.align()["T"], want["T"])
+    # after a caller-owned device buffer the commit must not recycle that buffer
+    import torch
+    d = torch.from_numpy(np.ascontiguousarray(tgt)).cuda(); torch.cuda.synchronize()
+    assert h.set_target_device(d.data_ptr(), tgt.shape[0]) == 0
+    assert h.stage_target(tgt2) == 0 and h.commit_target() == 0 and h.stage_target(tgt) == 0 and h.commit_target() == 0
+    assert_grid_equal(h.voxels(), want_map)
+    assert np.array_equal(d.cpu().numpy(), tgt)

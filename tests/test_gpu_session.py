@@ -83,3 +83,28 @@ def test_direct_solver_stays_inside_the_parity_bar(gold):
         assert np.abs(a[:6] - b[:6]).max() <= 1e-11
         assert abs(a[6] - b[6]) <= 1e-9 * abs(b[6]) and rel_inf(a[7:13], b[7:13]) <= 1e-9 and rel_inf(a[13:49], b[13:49]) <= 1e-9
     assert np.abs(r0["T"] - r1["T"]).max() <= 1e-6
+
+
+def test_session_can_leave_sms_free_for_other_streams(street):
+    """ "session_free_sms": the one-CTA-per-SM evaluation kernels run on fewer SMs, so another stream's kernel (here a second
+    handle's map build) makes progress while an align is open; results stay inside the parity bar (other partial sums)."""
+    import torch
+
+    assert torch.cuda.get_device_properties(0).multi_processor_count == 148
+    def handle(free):
+        h = ndtb.Handle(0)
+        h.set_params(resolution=1.0, search_method=ndtb.DIRECT7, max_iterations=35, trans_epsilon=0.01, step_size=0.1)
+        h.set_option("session_free_sms", free)
+        assert h.set_target(street["target"]) == 0 and h.set_source(street["source"]) == 0
+        return h
+    full, part = handle(0), handle(16)
+    ra, rb = full.align(), part.align()
+    ta, tb = full.trace(), part.trace()
+    assert ra["iterations"] == rb["iterations"] and ta.shape == tb.shape
+    assert rel_inf(tb[:, 6:49], ta[:, 6:49]) <= 1e-9 and np.abs(ra["T"] - rb["T"]).max() <= 1e-6
+    # session and one launch per evaluation still agree bit for bit on the reduced grid
+    part.set_option("sessions", 0)
+    rc = part.align()
+    assert np.array_equal(part.trace(), tb) and np.array_equal(rc["T"], rb["T"])
+    with pytest.raises(ndtb.NdtbError):
+        part.set_option("session_free_sms", 500)
