@@ -106,6 +106,22 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def build_traffic():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "profiles", "build_kernels_traffic.json")))["dram_bytes_per_build"])
+    except Exception:
+        return None
+
+
+def ncu_inst_executed():
+    """Warp instructions one eval-kernel launch executes (ncu smsp__inst_executed.sum, profiles/eval_kernel_traffic.json)."""
+    path = os.path.join(ROOT, "profiles", "eval_kernel_traffic.json")
+    try:
+        return float(json.load(open(path))["inst_executed_per_launch"])
+    except Exception:
+        return None
+
+
 def ncu_traffic():
     path = os.path.join(ROOT, "profiles", "eval_kernel_traffic.json")
     if os.path.exists(path):
@@ -409,6 +425,15 @@ def run_gpu(args, rank, world, local_rank):
                      "kernel_us_back_to_back": b2b_us, "frac_back_to_back": b_eval / (b2b_us * 1e-6) / 1e9 / peak},
         "clocks": clk,
     }
+    # the kernel is L2-resident and issue/latency-bound: its instruction-issue floor beside the HBM roofline
+    inst = ncu_inst_executed()
+    if inst and clk and clk.get("sm_mhz"):
+        floor_us = inst / (148 * 4) / (clk["sm_mhz"] * 1e6) * 1e6
+        sess_us = line["roofline"]["session_eval_us"]
+        line["roofline"]["issue"] = {"bound": "warp-instruction issue (4 schedulers x 148 SMs, 1 instruction per cycle each)",
+                                     "inst_executed_per_launch": inst, "floor_us": floor_us, "frac_of_kernel_us": floor_us / (t_eval * 1e6),
+                                     "frac_of_session_eval_us": floor_us / sess_us if sess_us else None,
+                                     "source": "ncu smsp__inst_executed.sum (profiles/eval_kernel_traffic.json) / live SM clock"}
     # the voxel-map build is the other half of the step: its own roofline entry (B_build = 2*16*N_t + 64*V)
     l0 = h.launch_count()
     assert h.set_target_device(d_tgt.data_ptr(), N_MAP) == 0
@@ -418,8 +443,10 @@ def run_gpu(args, rank, world, local_rank):
     build_s = st["build_ms"] / K * 1e-3
     line["roofline_build"] = {"kernel": f"voxel-map build ({build_launches} launches)", "bound": "hbm", "achieved": b_build / build_s / 1e9, "peak": peak,
                               "unit": "GB/s", "frac": b_build / build_s / 1e9 / peak, "algorithmic_bytes": b_build, "leaves": n_leaves,
-                              "build_us": build_s * 1e6, "traffic": None,
-                              "note": "CUDA events on the library's stream around the whole build (all launches + the host read-backs between them)"}
+                              "build_us": build_s * 1e6, "traffic": build_traffic(),
+                              "note": "CUDA events on the library's stream around the whole build (sort_segments_kernel + voxel_stats_kernel, one host "
+                                      "wait at the end); latency-bound, not bandwidth-bound: DESIGN 4.3; traffic = ncu dram bytes of the two kernels "
+                                      "(profiles/build_kernels_traffic.json)"}
     if not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         c = run_cpu(tgt, scans, guesses, steps=2, warmup=1, threads=threads)

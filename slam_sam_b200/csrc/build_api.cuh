@@ -8,6 +8,7 @@ namespace ndtb {
 // Everything the build decides ON THE DEVICE (no host round trip inside a build): the grid geometry from the bounding box, the
 // radix-sort plan from the key range, the leaf count, the hash capacity.  Lives in device memory (DeviceGrid::d_meta), read by
 // every build kernel, published to the host once, by the last kernel of the build.
+constexpr int HEAVY_LEAF_POINTS = 48;  // leaves with more points are summed by a whole warp, the others by one lane (voxel_stats_kernel)
 constexpr int RADIX_MAX_BITS = 10;      // widest digit: 1024 bins (20 key bits -> 2 passes of 10 bits)
 struct BuildMeta {
   GridMeta m;
@@ -18,7 +19,7 @@ struct BuildMeta {
   unsigned int V;             // leaves (pclomp keeps under-populated / rejected leaves, flagged)
   unsigned int n_valid;       // leaves a neighbour search can return
   unsigned int chunk_counter; // dynamic work hand-out of the statistics kernel
-  unsigned int reserved;
+  unsigned int n_heavy;       // leaves with more than HEAVY_LEAF_POINTS points (summed warp-wide at the end of the sort kernel)
   unsigned int tickets[3];    // last-block-done tickets: -, statistics, centroid
   unsigned int n_flagged;     // pclomp leaves flagged nr_points_ = -1 that stay reachable by radius searches
 };
@@ -73,9 +74,8 @@ void free_device_grid(DeviceGrid& g);
 int voxelgrid_downsample(DeviceGrid& scratch, const float4* d_pts, size_t n, float leaf, int is_dense, float4* d_out, size_t* n_out,
                          cudaStream_t stream);
 
-// voxel_finalize.cu: per-leaf statistics, two launches: sums in input order over DeviceGrid::sorted_pts, then mean / covariance /
-// eigen-inflation / inverse / hot record / hash insert; the last block of the second publishes BuildMeta to the host slots.
-void launch_voxel_sums(const DeviceGrid& g, uint32_t n_points, cudaStream_t stream);
+// voxel_finalize.cu: per-leaf statistics: sums in input order over DeviceGrid::sorted_pts (heavy leaves arrive summed by the sort
+// kernel), mean / covariance / eigen-inflation / inverse / hot record / hash insert; the last block publishes BuildMeta to the host slots.
 void launch_voxel_finalize(const DeviceGrid& g, uint32_t n_points, unsigned long long publish_key, cudaStream_t stream);
 
 }  // namespace ndtb

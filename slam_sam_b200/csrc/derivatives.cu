@@ -1150,7 +1150,7 @@ template <int FLAVOUR, int PROBES, bool HESS, bool GN>
 static void launch_t(const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs, const HashSlot* table, const double* c_mean,
                      const double* c_icov, const EvalBuffers& b, int n_particles, int particle_offset, cudaStream_t stream, const SvnExchange& xch) {
   const int vsh = (FLAVOUR == FLAVOUR_SVN && xch.vshards > 1) ? xch.vshards : 1;
-  dim3 grid(std::max(1, eval_blocks_for(n) / vsh), n_particles);
+  dim3 grid((vsh > 1 && xch.blocks_per_unit > 0) ? xch.blocks_per_unit : std::max(1, eval_blocks_for(n) / vsh), n_particles);
   eval_kernel<FLAVOUR, PROBES, HESS, GN><<<grid, EVAL_THREADS, 0, stream>>>(d_src, n, meta, recs, table, c_mean, c_icov, b.d_states,
                                                                            b.d_partials, b.d_results, b.d_tickets, particle_offset, xch);
 }

@@ -29,6 +29,7 @@ struct SvnExchange {
   int world = 1, rank = 0;          // block row s evaluates UNIT u = rank + s * world: particle u / vshards, point shard u % vshards
   int vshards = 1;                  // point shards per particle (1: a unit is a whole particle and the record carries the guards of
                                     // svn_ndt_impl.hpp:650-663; > 1: raw partial sums, the consumer adds the shards in order first)
+  int blocks_per_unit = 0;          // vshards > 1: CTAs per unit (0 = eval_blocks_for(n) / vshards)
   int n_dest = 0;                   // windows the record is stored to: rec[0..n_dest-1] (n_dest == world across GPUs, 1 = local only)
   int capacity = 0;                 // particles per parity half of a window
   int parity = 0;                   // window half of this iteration (stamp & 1)

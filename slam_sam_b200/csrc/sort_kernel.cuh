@@ -5,7 +5,7 @@
 // the barriers).  Per radix pass: rank the tile by digit and publish its digit counts | barrier | one warp per digit scans the
 // counts over the tiles | barrier | reorder the tile by digit in shared memory and store it coalesced (the final pass of a map
 // build also stores the POINTS in sorted order) | barrier.  Nothing returns to the host in between; the number of passes is
-// whatever the key range asks for.
+// whatever the key range asks for.  A map build ends with the sums of the heavy leaves (two more barriers).
 //   pcl::getMinMax3D + applyFilter geometry: voxel_grid_covariance_omp_impl.hpp:83-113 / voxel_grid_covariance_impl.hpp:103-140
 //   leaf index of a point:                   voxel_grid_covariance_omp_impl.hpp:219-227 / voxel_grid_covariance_impl.hpp:222-225
 //   leaves in ascending index (std::map):    voxel_grid_covariance_omp.h leaves_
@@ -30,6 +30,7 @@ struct SortArgs {
   uint32_t* seg_start;
   uint32_t* vox_key;
   HashSlot* table;                 // cleared over the capacity the build uses; nullptr: no table (down-sampling)
+  double* vox_sums;                // map build: [V][9] sums of the heavy leaves; nullptr: not wanted
   int nb;                          // tiles
   unsigned long long* dbg;         // development aid (NDTB_SORT_DEBUG): globaltimer stamps of CTA 0 at the phase boundaries
 };
@@ -413,6 +414,67 @@ __global__ void __launch_bounds__(RS_THREADS, 1) sort_segments_kernel(const Sort
 #pragma unroll
       for (int i = 0; i < RS_ITEMS; ++i)
         if (heads & (1u << i)) { a.seg_start[v] = static_cast<uint32_t>(base + i); a.vox_key[v] = k[i]; ++v; }
+    }
+  }
+  // ---------------------------------------------------------------------------------------------- heavy leaves
+  // Sum x and Sum x x^T of the leaves with more than HEAVY_LEAF_POINTS points, IN INPUT ORDER (FP64, one serial chain per component
+  // exactly like the reference's loop, voxel_grid_covariance_omp_impl.hpp:235-239 / voxel_grid_covariance_impl.hpp:237-239): a
+  // lane of the statistics kernel would walk such a leaf for microseconds while its 31 neighbours wait.  The leaves are listed
+  // first (any order: it only decides which warp takes which leaf), then one warp per leaf: 32 lanes load 32 consecutive points
+  // of sorted_pts and form the nine products; lane c < 9 runs chain c over them, so the nine chains advance in the same
+  // instruction.  Two 32-point tiles are in flight ahead of the chain.
+  if (a.vox_sums != nullptr) {
+    stamp();
+    sort_grid_barrier(a.sync, target, &s_dead);   // seg_start and the leaf count are complete
+    stamp();
+    const uint32_t V = __ldcg(&a.meta->V);
+    const uint32_t n_valid_pts = static_cast<uint32_t>(n) - __ldcg(&a.meta->n_skipped);
+    uint32_t* heavy_list = a.hist;                  // free since the last radix pass; V_heavy <= n / 49 < its n / 8 words
+    for (uint32_t v = blockIdx.x * RS_THREADS + tid; v < V; v += static_cast<uint32_t>(G) * RS_THREADS) {
+      const uint32_t lo = __ldcg(a.seg_start + v), hi = (v + 1 < V) ? __ldcg(a.seg_start + v + 1) : n_valid_pts;
+      if (hi - lo > static_cast<uint32_t>(HEAVY_LEAF_POINTS)) heavy_list[atomicAdd(&a.meta->n_heavy, 1u)] = v;
+    }
+    sort_grid_barrier(a.sync, target, &s_dead);
+    stamp();
+    const uint32_t n_heavy = __ldcg(&a.meta->n_heavy);
+    double (*s_prod)[9] = reinterpret_cast<double (*)[9]>(rs_raw + static_cast<size_t>(w) * 32 * 9 * sizeof(double));
+    for (uint32_t hi_i = blockIdx.x * RS_WARPS + w; hi_i < n_heavy; hi_i += static_cast<uint32_t>(G) * RS_WARPS) {
+      const uint32_t v = __ldcg(heavy_list + hi_i);
+      const uint32_t wlo = __ldcg(a.seg_start + v);
+      const int wn = static_cast<int>(((v + 1 < V) ? __ldcg(a.seg_start + v + 1) : n_valid_pts) - wlo);
+      // the reference's Leaf starts cov_ at identity and adds x x^T onto it: the diagonal chains start at 1.0
+      double acc = (lane == 3 || lane == 6 || lane == 8) ? 1.0 : 0.0;
+      const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4* src = a.sorted_pts + wlo + lane;
+      auto tile = [&](const float4 pt, int base) {
+        const double x = static_cast<double>(pt.x), y = static_cast<double>(pt.y), z = static_cast<double>(pt.z);
+        double* pr = s_prod[lane];
+        pr[0] = x; pr[1] = y; pr[2] = z; pr[3] = x * x; pr[4] = x * y; pr[5] = x * z; pr[6] = y * y; pr[7] = y * z; pr[8] = z * z;
+        __syncwarp();
+        const int cnt = min(32, wn - base);
+        if (lane < 9) {
+          int kk = 0;
+          for (; kk + 8 <= cnt; kk += 8) {
+            double t8[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) t8[u] = s_prod[kk + u][lane];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) acc += t8[u];
+          }
+          for (; kk < cnt; ++kk) acc += s_prod[kk][lane];
+        }
+        __syncwarp();
+      };
+      float4 pa = (lane < wn) ? __ldcg(src) : zero;
+      float4 pb = (32 + lane < wn) ? __ldcg(src + 32) : zero;
+      for (int base = 0; base < wn; base += 64) {
+        const float4 na = (base + 64 + lane < wn) ? __ldcg(src + base + 64) : zero;
+        const float4 nb2 = (base + 96 + lane < wn) ? __ldcg(src + base + 96) : zero;
+        tile(pa, base);
+        if (base + 32 < wn) tile(pb, base + 32);
+        pa = na; pb = nb2;
+      }
+      if (lane < 9) a.vox_sums[9 * static_cast<size_t>(v) + lane] = acc;
     }
   }
   // ---------------------------------------------------------------------------------------------- empty hash table

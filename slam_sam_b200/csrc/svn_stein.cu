@@ -364,6 +364,16 @@ int svn_dev_stage1(ndtb_handle_s* h, int K, int first, int stride, bool to_peers
   else svn_state_kernel<<<(m + 127) / 128, 128, 0, h->stream>>>(K, first, stride, d.d_poses[d.cur], h->eval.d_states, d1, d2, d3, d.d_done);
   SvnExchange x;
   x.vshards = vshards;
+  if (vshards > 1) {
+    // CTAs per unit: the units of one rank AT 8 RANKS should fill whole waves of 148 SMs x EVAL_MIN_BLOCKS CTAs (a last wave that
+    // is half empty costs 4 % at 25 units x 222 CTAs).  Derived from K and the cloud size only -- never from the actual number of
+    // ranks -- so every world size cuts the cloud into the same blocks and adds the same partial sums (bit-identical results).
+    const int wave = 148 * EVAL_MIN_BLOCKS;
+    const int b0 = std::max(1, eval_blocks_for(n) / vshards);
+    const int u8 = (units + 7) / 8;
+    const int waves = (u8 * b0) / wave;
+    x.blocks_per_unit = waves > 0 ? std::min(b0, std::max(1, (waves * wave) / u8)) : b0;
+  }
   x.world = stride; x.rank = first; x.capacity = ndtb_handle_s::SvnDev::CAPACITY;
   x.parity = static_cast<int>(stamp & 1ull); x.stamp = stamp; x.done = d.d_done;
   if (to_peers && d.world > 1) {

@@ -2,8 +2,8 @@
 // (ndt_omp.h:324-330, voxel_grid_covariance_omp_impl.hpp:55-364; svn_ndt_impl.hpp:137-159,
 // voxel_grid_covariance_impl.hpp:77-379).  See voxel_build_kernels.cuh / voxel_finalize.cu for the kernels.
 //
-// A build is three launches queued back to back that never wait for the host: the cooperative sort kernel (bbox -> geometry ->
-// keys -> radix sort -> segments, sort_kernel.cuh), the heavy-leaf sums and the statistics kernel (voxel_finalize.cu).  The grid
+// A build is two launches queued back to back that never wait for the host: the cooperative sort kernel (bbox -> geometry ->
+// keys -> radix sort -> segments -> sums of the heavy leaves, sort_kernel.cuh) and the statistics kernel (voxel_finalize.cu).  The grid
 // geometry, the radix plan, the leaf count and the hash capacity are derived on the device (BuildMeta).  The host waits ONCE,
 // for the BuildMeta the last kernel publishes into pinned self-validating slots.
 #include "voxel_build_kernels.cuh"
@@ -162,6 +162,7 @@ static int queue_sort_into_segments(DeviceGrid& g, const float4* d_pts, int ni, 
   a.seg_start = g.seg_start;
   a.vox_key = g.c_key;
   a.table = map_build ? g.table : nullptr;
+  a.vox_sums = map_build ? g.vox_sums : nullptr;
   a.nb = (ni + RS_TILE - 1) / RS_TILE;
   static const bool dbg_on = getenv("NDTB_SORT_DEBUG") != nullptr;
   static unsigned long long* d_dbg = nullptr;
@@ -215,13 +216,11 @@ int build_voxel_map(DeviceGrid& g, const float4* d_pts, size_t n, float resoluti
   rc = queue_sort_into_segments(g, d_pts, ni, resolution, min_pts, eig_mult, flavour, is_dense, true, stream, &launches);
   if (rc != NDTB_OK) return rc;
   const unsigned long long key = 0x9E3779B97F4A7C15ull * (++g.slot_seq) | 1ull;
-  launch_voxel_sums(g, static_cast<uint32_t>(ni), stream);
-  tmark("heavy", stream);
   launch_voxel_finalize(g, static_cast<uint32_t>(ni), key, stream);
   tmark("stats", stream);
   CK(cudaGetLastError());
-  g.launches += static_cast<uint64_t>(launches) + 2;
-  g.last_build_launches = launches + 2;
+  g.launches += static_cast<uint64_t>(launches) + 1;
+  g.last_build_launches = launches + 1;
   BuildMeta B;
   rc = wait_meta(g, key, stream, &B);
   tprint();

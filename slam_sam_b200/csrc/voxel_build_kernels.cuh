@@ -24,7 +24,7 @@ __device__ inline void make_build_meta(BuildMeta& B, const int* ordered_bbox, co
   m.min_pts = prm.min_pts; m.flavour = prm.flavour; m.eig_mult = prm.eig_mult;
   m.hash_mask = 0; m.total_cells = 0;
   B.error = 0; B.bits = 0; B.digit_bits = 0; B.passes = 0; B.final_buf = 0;
-  B.n_skipped = 0; B.V = 0; B.n_valid = 0; B.chunk_counter = 0; B.reserved = 0;
+  B.n_skipped = 0; B.V = 0; B.n_valid = 0; B.chunk_counter = 0; B.n_heavy = 0;
   B.tickets[0] = 0; B.tickets[1] = 0; B.tickets[2] = 0; B.n_flagged = 0;
   const long long dx = static_cast<long long>((max_p[0] - min_p[0]) * m.inv_leaf) + 1;
   const long long dy = static_cast<long long>((max_p[1] - min_p[1]) * m.inv_leaf) + 1;

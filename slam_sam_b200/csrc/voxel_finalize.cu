@@ -135,8 +135,7 @@ __device__ __forceinline__ void hash_insert(HashSlot* table, uint32_t mask, uint
 
 constexpr int ST_THREADS = 128;   // 4 warps per CTA
 constexpr int ST_CHUNK = 32;      // leaves per chunk: one per lane
-constexpr int ST_HEAVY = 48;      // leaves with more points are summed by a whole warp (voxel_heavy_sums_kernel)
-constexpr int ST_HEAVY_BLOCKS = 148 * 4;   // CTAs of the heavy-sums kernel
+constexpr int ST_HEAVY = HEAVY_LEAF_POINTS;   // leaves with more points arrive summed (end of sort_segments_kernel)
 constexpr int FIN_THREADS = 64;            // finalize: 2 warps per CTA, 8 CTAs per SM (128 registers, no spill)
 constexpr int FIN_MIN_BLOCKS = 8;
 
@@ -147,84 +146,11 @@ __device__ int finalize_voxel(uint32_t v, int n, double sx, double sy, double sz
                               int32_t* __restrict__ c_n, double* __restrict__ c_mean, double* __restrict__ c_cov, double* __restrict__ c_icov,
                               double* __restrict__ c_evecs, double* __restrict__ c_evals);
 
-// Sums of the HEAVY leaves (more than ST_HEAVY points), ahead of the statistics kernel: Sum x and Sum x x^T IN INPUT ORDER (FP64,
-// one serial chain per component exactly like the reference's loop, voxel_grid_covariance_omp_impl.hpp:235-239 /
-// voxel_grid_covariance_impl.hpp:237-239).  The final radix pass left the points themselves in sorted order (sorted_pts: leaf
-// after leaf, input order inside a leaf -- the sort is stable), so a leaf is a contiguous run of float4 and nothing here chases
-// an index.  One warp per heavy leaf.  Heavy leaves come in runs (a wall is a row of equally dense voxels), so groups of 32
-// leaves are dealt to the warps through a multiplicative permutation of [0, Vr), Vr = V rounded up to a warp (2654435761 is
-// prime, hence coprime with Vr: t -> t * P mod Vr is a bijection).  32 lanes load 32 consecutive points and form the nine
-// products; lane c < 9 then runs chain c over those 32 points, so the nine serial FP64 chains advance in the same instruction
-// and a point costs one dependent DADD instead of nine.  Two tiles are in flight ahead of the chain.
-__global__ void __launch_bounds__(ST_THREADS, 8) voxel_heavy_sums_kernel(const float4* __restrict__ sorted_pts, const BuildMeta* __restrict__ meta,
-                                                                         const uint32_t* __restrict__ seg_start, uint32_t n_points,
-                                                                         double* __restrict__ vox_sums) {
-  __shared__ double s_prod_all[ST_THREADS / 32][32][9];
-  pdl_enter();
-  if (meta->error) return;
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const uint32_t V = meta->V;
-  const uint32_t n_valid_pts = n_points - meta->n_skipped;
-  double (*s_prod)[9] = s_prod_all[w];
-  const uint32_t Vr = (V + 31u) & ~31u;
-  const uint32_t stride = gridDim.x * ST_THREADS;
-  for (uint32_t t = blockIdx.x * ST_THREADS + threadIdx.x; t < Vr; t += stride) {  // warp-uniform trip count
-    const uint32_t v = static_cast<uint32_t>((static_cast<unsigned long long>(t) * 2654435761ull) % Vr);
-    const bool has = v < V;
-    const uint32_t lo = has ? seg_start[v] : 0u;
-    const uint32_t hi = has ? ((v + 1 < V) ? seg_start[v + 1] : n_valid_pts) : 0u;
-    const int n = static_cast<int>(hi - lo);
-    unsigned int hm = __ballot_sync(0xffffffffu, has && n > ST_HEAVY);
-    while (hm) {
-      const int o = __ffs(hm) - 1;
-      hm &= hm - 1;
-      const uint32_t wlo = __shfl_sync(0xffffffffu, lo, o);
-      const int wn = __shfl_sync(0xffffffffu, n, o);
-      const uint32_t wv = __shfl_sync(0xffffffffu, v, o);
-      // the reference's Leaf starts cov_ at identity and adds x x^T onto it: the diagonal chains start at 1.0 (see voxel_stats_kernel)
-      double acc = (lane == 3 || lane == 6 || lane == 8) ? 1.0 : 0.0;
-      const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
-      const float4* src = sorted_pts + wlo + lane;
-      // one tile = 32 consecutive points: products to shared memory, then the nine chains over them
-      auto tile = [&](const float4 p, int base) {
-        const double x = static_cast<double>(p.x), y = static_cast<double>(p.y), z = static_cast<double>(p.z);
-        double* pr = s_prod[lane];
-        pr[0] = x; pr[1] = y; pr[2] = z; pr[3] = x * x; pr[4] = x * y; pr[5] = x * z; pr[6] = y * y; pr[7] = y * z; pr[8] = z * z;
-        __syncwarp();
-        const int cnt = min(32, wn - base);
-        if (lane < 9) {
-          int k = 0;
-          for (; k + 8 <= cnt; k += 8) {
-            double t8[8];
-#pragma unroll
-            for (int u = 0; u < 8; ++u) t8[u] = s_prod[k + u][lane];
-#pragma unroll
-            for (int u = 0; u < 8; ++u) acc += t8[u];
-          }
-          for (; k < cnt; ++k) acc += s_prod[k][lane];
-        }
-        __syncwarp();
-      };
-      // two tiles per trip, the next two already in flight: a load is only consumed two chains after it was issued
-      float4 pa = (lane < wn) ? __ldg(src) : zero;
-      float4 pb = (32 + lane < wn) ? __ldg(src + 32) : zero;
-      for (int base = 0; base < wn; base += 64) {
-        const float4 na = (base + 64 + lane < wn) ? __ldg(src + base + 64) : zero;
-        const float4 nb = (base + 96 + lane < wn) ? __ldg(src + base + 96) : zero;
-        tile(pa, base);
-        if (base + 32 < wn) tile(pb, base + 32);
-        pa = na; pb = nb;
-      }
-      if (lane < 9) vox_sums[9 * static_cast<size_t>(wv) + lane] = acc;
-    }
-  }
-}
-
 // Per-leaf statistics, one thread per leaf, chunks of 32 consecutive leaves per warp (handed out dynamically: the leaf count is
 // only known on the device).  A light leaf (<= ST_HEAVY points) is summed here: the lane walks ITS run of sorted_pts -- its
 // points in input order -- widening to FP64 and accumulating Sum x, Sum x x^T exactly like the reference's serial loop
 // (bit-exact means and covariances); the 32 runs of a chunk are adjacent, every 128-byte line is fetched once and then served
-// from L1.  Heavy leaves arrive summed (voxel_heavy_sums_kernel).  Then mean, covariance, Jacobi eigen-decomposition, inflation,
+// from L1.  Heavy leaves arrive summed (heavy_leaf_sums at the end of sort_segments_kernel).  Then mean, covariance, Jacobi eigen-decomposition, inflation,
 // inverse, hot record, hash insert (finalize_voxel).  The last block publishes BuildMeta (geometry, leaf counts, error) to the host.
 __global__ void __launch_bounds__(FIN_THREADS, FIN_MIN_BLOCKS) voxel_stats_kernel(const float4* __restrict__ sorted_pts, BuildMeta* __restrict__ meta,
                                                                     const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ vox_key,
@@ -426,11 +352,6 @@ __device__ int finalize_voxel(uint32_t v, int n, double sx, double sy, double sz
     hash_insert(table, m.hash_mask, vox_key[v], valid ? static_cast<int>(v) : -2 - static_cast<int>(v));
   }
   return valid ? 1 : (flagged ? 2 : 0);
-}
-
-void launch_voxel_sums(const DeviceGrid& g, uint32_t n_points, cudaStream_t stream) {
-  launch_pdl(voxel_heavy_sums_kernel, dim3(ST_HEAVY_BLOCKS), dim3(ST_THREADS), 0, stream, static_cast<const float4*>(g.sorted_pts),
-             static_cast<const BuildMeta*>(g.d_meta), static_cast<const uint32_t*>(g.seg_start), n_points, g.vox_sums);
 }
 
 void launch_voxel_finalize(const DeviceGrid& g, uint32_t n_points, unsigned long long publish_key, cudaStream_t stream) {

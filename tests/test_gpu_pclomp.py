@@ -330,3 +330,39 @@ def test_staged_uploads_equal_the_direct_ones(street):
     assert h.stage_target(tgt2) == 0 and h.commit_target() == 0 and h.stage_target(tgt) == 0 and h.commit_target() == 0
     assert_grid_equal(h.voxels(), want_map)
     assert np.array_equal(d.cpu().numpy(), tgt)
+
+
+@pytest.mark.parametrize("scale", [1e8, 1e12, 1e20])
+def test_flagged_leaves_stay_reachable_by_the_radius_search(oracle, scale):
+    """Leaves the reference flags nr_points_ = -1 AFTER they entered its centroid cloud (negative eigenvalue / infinite inverse,
+    voxel_grid_covariance_omp_impl.hpp:335-338, 355-359) are still returned by its kd-tree, with the icov_ the leaf holds.
+    Clusters of points one float ulp apart along x, at coordinates where x^2 swamps the FP64 second moment, produce such leaves:
+    the map must flag the same leaves, KDTREE must see them (row code -2 - v in the table), DIRECT7 must not."""
+    rng = np.random.default_rng(3)
+    leaf = scale / 8
+    centers = (rng.uniform(-4, 4, (60, 3)) * leaf).astype(np.float32)
+    pts = []
+    for c in centers:
+        k = rng.integers(6, 12)
+        p = np.tile(c, (k, 1))
+        p[:, 0] = c[0] + rng.integers(0, 3, k).astype(np.float32) * np.spacing(np.abs(c[0]))
+        pts.append(p)
+    cloud = np.zeros((sum(len(p) for p in pts), 4), np.float32)
+    cloud[:, :3] = np.concatenate(pts)
+    src = cloud[::3].copy()
+    g = O.OracleGrid(0, float(leaf), 6); g.build(cloud); e = g.export()
+    assert (e["n"] == -1).sum() >= 5 and (e["n"] >= 6).sum() >= 5
+    scores = {}
+    for search in ("KDTREE", "DIRECT7"):
+        h = ndtb.Handle(0)
+        h.set_params(resolution=float(leaf), search_method=getattr(ndtb, search))
+        assert h.set_target(cloud) == 0 and h.set_source(src) == 0
+        assert_grid_equal(h.voxels(), e)
+        o = O.OracleNdt(resolution=float(leaf), search=search, num_threads=2)
+        assert o.set_target(cloud) == 0
+        o.set_source(src)
+        s, gr, H, nv = h.compute_derivatives(np.zeros(6))
+        so, go, Ho, nvo = o.compute_derivatives(np.zeros(6))
+        assert abs(s - so) <= TOL * abs(so) and rel_inf(gr, go) <= TOL and rel_inf(H, Ho) <= TOL and abs(nv - nvo) <= TOL * abs(nvo)
+        scores[search] = s
+    assert scores["KDTREE"] > scores["DIRECT7"] * 1.1                     # the flagged leaves contribute to the radius search only
