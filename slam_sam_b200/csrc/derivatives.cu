@@ -637,6 +637,9 @@ __global__ void __launch_bounds__(EVAL_THREADS, EVAL_MIN_BLOCKS) eval_kernel(con
                                                                           const EvalState* __restrict__ states, double* __restrict__ partials,
                                                                           double* __restrict__ results, unsigned int* __restrict__ tickets,
                                                                           int particle_offset, const SvnExchange xch) {
+  // programmatic dependent launch: wait for the predecessor (the state kernel), then let the successor be scheduled while this grid
+  // drains -- the Stein kernel of the device-resident SVN loop does not wait for this kernel to END, it acquires the record flags
+  pdl_enter();
   if (FLAVOUR == FLAVOUR_SVN && xch.done && *xch.done) return;  // speculatively queued iteration after the align converged
   __shared__ EvalState st;
   constexpr int QC = (PROBES > 7) ? Q_CAP26 : Q_CAP;
@@ -1151,8 +1154,8 @@ static void launch_t(const float4* d_src, int n, const GridMeta& meta, const Vox
                      const double* c_icov, const EvalBuffers& b, int n_particles, int particle_offset, cudaStream_t stream, const SvnExchange& xch) {
   const int vsh = (FLAVOUR == FLAVOUR_SVN && xch.vshards > 1) ? xch.vshards : 1;
   dim3 grid((vsh > 1 && xch.blocks_per_unit > 0) ? xch.blocks_per_unit : std::max(1, eval_blocks_for(n) / vsh), n_particles);
-  eval_kernel<FLAVOUR, PROBES, HESS, GN><<<grid, EVAL_THREADS, 0, stream>>>(d_src, n, meta, recs, table, c_mean, c_icov, b.d_states,
-                                                                           b.d_partials, b.d_results, b.d_tickets, particle_offset, xch);
+  launch_pdl(eval_kernel<FLAVOUR, PROBES, HESS, GN>, grid, dim3(EVAL_THREADS), 0, stream, d_src, n, meta, recs, table, c_mean, c_icov,
+             static_cast<const EvalState*>(b.d_states), b.d_partials, b.d_results, b.d_tickets, particle_offset, xch);
 }
 
 void launch_eval(int flavour, int n_probe, bool compute_hessian, bool gn, const float4* d_src, int n, const GridMeta& meta,

@@ -295,7 +295,7 @@ __global__ void __launch_bounds__(STEIN_THREADS) stein_kernel(int K, const doubl
     int d = atomicAdd(mm.done, 0);
     if (converged && d == 0) { *mm.done = 1; d = 1; }
     *mm.ticket = 0;
-    __threadfence_system();
+    __threadfence();   // device data (mean, done flag) is read after the kernel boundary; the host only reads the self-validating slot
     const unsigned long long word = static_cast<unsigned long long>(mm.iter + 1) | (static_cast<unsigned long long>(d) << 32);
     publish_slot(mm.h_status, mm.iter & 63, word, mm.status_key);
   }
@@ -409,8 +409,16 @@ int svn_dev_stein(ndtb_handle_s* h, int K, unsigned long long stamp, bool wait_f
   }
   static bool configured[MAX_DEVICES] = {};
   if (needs_func_setup(configured)) CKS(cudaFuncSetAttribute(stein_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(SteinTile))));
-  stein_kernel<<<K, STEIN_THREADS, sizeof(SteinTile), h->stream>>>(K, d.d_poses[d.cur], rec, flags, stamp, h->svn.kernel_bandwidth, h->svn.step_size, d.d_updates,
-                                                   write_poses ? d.d_poses[d.cur ^ 1] : nullptr, mm, vshards);
+  double* new_poses = write_poses ? d.d_poses[d.cur ^ 1] : nullptr;
+  if (wait_flags) {
+    // the kernel acquires every record through its flag, so it need not wait for the derivative kernel to END: launched as a
+    // programmatic dependent (and without a griddepcontrol.wait of its own) its blocks are scheduled while that grid drains
+    CKS(launch_pdl(stein_kernel, dim3(K), dim3(STEIN_THREADS), sizeof(SteinTile), h->stream, K, static_cast<const double*>(d.d_poses[d.cur]), rec, flags, stamp,
+                   h->svn.kernel_bandwidth, h->svn.step_size, d.d_updates, new_poses, mm, vshards));
+  } else {
+    stein_kernel<<<K, STEIN_THREADS, sizeof(SteinTile), h->stream>>>(K, d.d_poses[d.cur], rec, flags, stamp, h->svn.kernel_bandwidth, h->svn.step_size,
+                                                                     d.d_updates, new_poses, mm, vshards);
+  }
   CKS(cudaGetLastError());
   if (write_poses) d.cur ^= 1;
   h->launches += 1;
