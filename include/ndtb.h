@@ -299,6 +299,13 @@ int ndtb_mg_align(ndtb_handle h, const float guess[16], ndtb_result* res, float*
  *                            differs from the running one CLOSES the running frame (:658-669) -- its packets, already in
  *                            HBM, are decoded by one kernel (range / z / vehicle-box / reflectivity filters, channel
  *                            stride, order-preserving compaction in packet, column, channel order).
+ *                            LEGACY profile (udp_profile_legacy = 1): DecodePacketLegacy :376-629 -- no packet header, the
+ *                            frame id travels in every column header, so a frame is cut at the COLUMN whose id differs (the
+ *                            host reads the 12 header bytes of every column; a packet that straddles two frames is copied
+ *                            into both), columns need block status 0xFFFFFFFF, range = 20 bits.  When one packet completes
+ *                            two frames the reference's `completed_frame` keeps only the later one: so does the pop.  Not
+ *                            reproduced: `interframe_timedelta` when one packet holds more than one frame switch, and the
+ *                            `frame_id_` reset of :416-418 (it needs a column time stamp of exactly 0.0 s).
  *   ndtb_lidar_pop_frame     the unique_ptr<LidarFrame> DecodePacket returns: oldest closed frame with >= 1 point
  *                            (a frame without points is never emitted, :659); the previously popped frame goes back
  *                            to the pool (ReturnFrameToPool, :903-909).  *available = 0 when there is none.
@@ -321,6 +328,7 @@ typedef struct ndtb_lidar_config {
   float box_dimensions[3];              /* lidar_parameter.vehicleFilterBox.dimensions                */
   double body_to_lidar_rotation[9];     /* lidar_parameter.Cb2s, row-major                            */
   double body_to_lidar_translation[3];  /* lidar_parameter.tb2s                                       */
+  int udp_profile_legacy;               /* config_params.udp_profile_lidar: 0 = "RNG19_RFL8_SIG16_NIR16", 1 = "LEGACY" */
 } ndtb_lidar_config;
 typedef struct ndtb_lidar_frame_info {  /* scalar members of LidarFrame, include/dataframe.hpp */
   double timestamp;                     /* column time stamp of the first point                       */

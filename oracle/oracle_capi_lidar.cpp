@@ -13,13 +13,13 @@ struct LidarOracle {
 
 extern "C" {
 
-// cfg_i: columns_per_frame, pixels_per_column, columns_per_packet, channel_stride, reflectivity_threshold
+// cfg_i: columns_per_frame, pixels_per_column, columns_per_packet, channel_stride, reflectivity_threshold, legacy profile (0 / 1)
 // cfg_f: lidar_origin_to_beam_origin_mm, range_min, range_max, z_min, z_max, box_center[3], box_dimensions[3]
 // cfg_d: Cb2s[9] row-major, tb2s[3]
 void* orc_lidar_create(const int* cfg_i, const float* cfg_f, const double* cfg_d, const float* az_deg, const float* alt_deg) {
   LidarConfig c;
   c.columns_per_frame = cfg_i[0]; c.pixels_per_column = cfg_i[1]; c.columns_per_packet = cfg_i[2]; c.channel_stride = cfg_i[3];
-  c.reflectivity_threshold = cfg_i[4];
+  c.reflectivity_threshold = cfg_i[4]; c.legacy = cfg_i[5] != 0;
   c.lidar_origin_to_beam_origin_mm = cfg_f[0]; c.range_min = cfg_f[1]; c.range_max = cfg_f[2]; c.z_min = cfg_f[3]; c.z_max = cfg_f[4];
   for (int a = 0; a < 3; ++a) { c.box_center[a] = cfg_f[5 + a]; c.box_dimensions[a] = cfg_f[8 + a]; c.tb2s[a] = cfg_d[9 + a]; }
   for (int i = 0; i < 9; ++i) c.Cb2s[i] = cfg_d[i];

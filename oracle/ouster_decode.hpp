@@ -2,6 +2,7 @@
 // CPU restatement of the reference's scan producer, the step before setInputSource:
 //   LidarCallback::Initialize        src/lidarcallback.cpp:191-341   (lookup tables, subset channels, vehicle box)
 //   LidarCallback::DecodePacketRng19 src/lidarcallback.cpp:631-878   (RNG19_RFL8_SIG16_NIR16 packets -> LidarFrame)
+//   LidarCallback::DecodePacketLegacy src/lidarcallback.cpp:376-629  (LEGACY packets: per-column frame ids, block status word)
 //   LidarFrame                       include/dataframe.hpp           (the per-point arrays that are filled)
 // The reference's AVX2 branch is compiled out (CMakeLists.txt:85-89 keeps -mavx2 -mfma commented), so the scalar
 // branch (:799-869) is what runs: pt = range_m * x_1 + x_2 with two roundings (no FMA; this file is built with
@@ -23,6 +24,7 @@ struct LidarConfig {
   float range_min = 1.0f, range_max = 200.0f;  // rfiltermin_/rfiltermax_ defaults, lidarcallback.hpp:76-77
   float z_min = -300.0f, z_max = 0.0f;         // zfiltermin_/zfiltermax_, lidarcallback.hpp:74-75
   int reflectivity_threshold = 0;
+  bool legacy = false;                         // udp_profile_lidar == "LEGACY" (lidarcallback.cpp:198-203)
   float box_center[3] = {0, 0, 0}, box_dimensions[3] = {0, 0, 0};
   double Cb2s[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};  // body_to_lidar_rotation_ (row-major), Zero() by default like the reference
   double tb2s[3] = {0, 0, 0};
@@ -86,8 +88,13 @@ struct LidarDecoder {
     if (N > cfg.pixels_per_column) return false;
     if (static_cast<int>(cfg.beam_azimuth_deg.size()) != cfg.pixels_per_column || static_cast<int>(cfg.beam_altitude_deg.size()) != cfg.pixels_per_column)
       return false;
-    block_size = 12 + static_cast<size_t>(cfg.pixels_per_column) * 12;                 // :193-197, :206
-    expected_size = 32 + static_cast<size_t>(cfg.columns_per_packet) * block_size + 32;  // :207
+    if (cfg.legacy) {  // :198-203: no packet header / footer, 16-byte column header, 4-byte block status
+      block_size = 16 + static_cast<size_t>(cfg.pixels_per_column) * 12 + 4;
+      expected_size = static_cast<size_t>(cfg.columns_per_packet) * block_size;
+    } else {
+      block_size = 12 + static_cast<size_t>(cfg.pixels_per_column) * 12;                 // :193-197, :206
+      expected_size = 32 + static_cast<size_t>(cfg.columns_per_packet) * block_size + 32;  // :207
+    }
     subset_channels = (cfg.pixels_per_column + N - 1) / N;
     const int W = cfg.columns_per_frame, Hh = cfg.pixels_per_column;
     x1.assign(static_cast<size_t>(W) * Hh, 0.f); y1 = x1; z1 = x1;
@@ -135,8 +142,78 @@ struct LidarDecoder {
   static uint16_t rd16(const uint8_t* p) { return static_cast<uint16_t>(p[0] | (p[1] << 8)); }
   static uint64_t rd64(const uint8_t* p) { uint64_t v = 0; for (int i = 7; i >= 0; --i) v = (v << 8) | p[i]; return v; }
 
-  // DecodePacketRng19 (:631-878).  Returns the completed frame or nullptr.
+  static uint32_t rd32(const uint8_t* p) { return static_cast<uint32_t>(p[0]) | (static_cast<uint32_t>(p[1]) << 8) | (static_cast<uint32_t>(p[2]) << 16) | (static_cast<uint32_t>(p[3]) << 24); }
+
+  // DecodePacketLegacy (:376-629), scalar branch (:567-624; the AVX2 branch is compiled out).  The frame id travels in every
+  // COLUMN header, so a frame can end in the middle of a packet -- and a second frame completed by the same packet overwrites
+  // `completed_frame` (the first one is lost, like in the reference).
+  std::unique_ptr<LidarFrameO> decode_packet_legacy(const uint8_t* packet, size_t size) {
+    if (size != expected_size) return nullptr;  // :378-381
+    std::unique_ptr<LidarFrameO> completed;
+    double prev_frame_completed_latest_ts = 0.0;
+    if (latest_timestamp_s > 0.0) prev_frame_completed_latest_ts = latest_timestamp_s;  // :385-388
+    const int Hh = cfg.pixels_per_column;
+    for (int col = 0; col < cfg.columns_per_packet; ++col) {
+      const size_t block = static_cast<size_t>(col) * block_size;
+      const uint64_t ts_ns = rd64(packet + block);
+      const double col_ts = std::fmod(static_cast<double>(ts_ns) * 1e-9, 86400.0);  // :396
+      if (col_ts < 0) continue;
+      const uint16_t m_id = rd16(packet + block + 8);
+      if (m_id >= static_cast<uint16_t>(cfg.columns_per_frame)) continue;  // :407-410
+      const uint16_t fid = rd16(packet + block + 10);
+      if (number_points_ == 0 && active->timestamp == 0.0) frame_id_ = fid;  // :416-418
+      if (fid != frame_id_) {  // :420-431
+        if (number_points_ > 0) {
+          active->numberpoints = number_points_;
+          active->timestamp_end = latest_timestamp_s;
+          completed = std::move(active);
+          active.reset(new LidarFrameO());
+          prev_frame_completed_latest_ts = latest_timestamp_s;
+        }
+        number_points_ = 0;
+        frame_id_ = fid;
+      }
+      latest_timestamp_s = col_ts;  // :433
+      if (rd32(packet + block + 16 + static_cast<size_t>(Hh) * 12) != 0xFFFFFFFFu) continue;  // :435-441
+      bool first_point = (number_points_ == 0);  // :443
+      const size_t first_pixel = block + 16;
+      for (uint16_t c_id = 0; c_id < static_cast<uint16_t>(Hh); c_id += cfg.channel_stride) {  // :568
+        const size_t o = first_pixel + static_cast<size_t>(c_id) * 12;
+        if (o + 11 >= size) continue;
+        const uint32_t range_mm = rd32(packet + o) & 0x000FFFFFu;  // :576
+        const float range_m = static_cast<float>(range_mm) * 0.001f;
+        if (range_m < cfg.range_min || range_m > cfg.range_max || range_m == 0) continue;  // :579
+        const uint8_t refl = packet[o + 4];
+        const uint16_t sig = rd16(packet + o + 6), nir = rd16(packet + o + 8);
+        const size_t k = static_cast<size_t>(m_id) * Hh + c_id;
+        const float px = range_m * x1[k] + x2[m_id];  // :591-594
+        const float py = range_m * y1[k] + y2[m_id];
+        const float pz = range_m * z1[k] + z2[m_id];
+        const bool in_box = px >= box_min[0] && px <= box_max[0] && py >= box_min[1] && py <= box_max[1] && pz >= box_min[2] && pz <= box_max[2];
+        if (!in_box && ((pz >= cfg.z_min && pz <= cfg.z_max) || (refl >= refl_thr))) {  // :601
+          const double rel = (active->numberpoints > 0 || number_points_ > 0) && active->timestamp > 0 ? std::max(0.0, col_ts - active->timestamp) : 0.0;
+          active->x.push_back(px); active->y.push_back(py); active->z.push_back(pz);
+          active->c_id.push_back(c_id); active->m_id.push_back(m_id);
+          active->timestamp_points.push_back(col_ts);
+          active->relative_timestamp.push_back(static_cast<float>(rel));
+          active->reflectivity.push_back(refl); active->signal.push_back(sig); active->nir.push_back(nir);
+          ++number_points_;
+          if (first_point) {  // :618-624
+            active->timestamp = col_ts;
+            active->frame_id = frame_id_;
+            active->interframe_timedelta = prev_frame_completed_latest_ts > 0.0 ? std::max(0.0, col_ts - prev_frame_completed_latest_ts) : 0.0;
+            first_point = false;
+          }
+        }
+      }
+    }
+    if (active) active->numberpoints = number_points_;  // :628-630
+    return completed;
+  }
+
+  // DecodePacket (:344-351) dispatch + DecodePacketRng19 (:631-878).  Returns the completed frame or nullptr.
   std::unique_ptr<LidarFrameO> decode_packet(const uint8_t* packet, size_t size) {
+    if (cfg.legacy) return decode_packet_legacy(packet, size);
     if (size != expected_size) return nullptr;  // :633-636
     std::unique_ptr<LidarFrameO> completed;
     if (rd16(packet) != 0x0001) return nullptr;  // :640-646

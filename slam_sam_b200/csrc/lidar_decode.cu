@@ -30,9 +30,19 @@ struct LidarKParams {
   int cpf, ppc, cpp, stride, subset, rounds;
   int cpc, upp;  // columns per CTA ("unit"), units per packet
   int block_bytes, pitch;
+  int legacy;    // LEGACY profile (DecodePacketLegacy): no packet header, 16-byte column header with the frame id, block status word
   float r_min, r_max, z_min, z_max;
   int refl_thr;
   float bmin[3], bmax[3];
+};
+// LEGACY frames are cut at COLUMN granularity (the frame id travels in every column header): unit t of a frame is a packet with
+// the column range [cb, ce) that belongs to the frame, and the host-tracked latest_timestamp_s at the start of that packet.
+constexpr int LEGACY_MAX_UNITS = 288;
+struct LegacyUnits {
+  unsigned char cb[LEGACY_MAX_UNITS], ce[LEGACY_MAX_UNITS];
+  double latest_at_start[LEGACY_MAX_UNITS];
+  double prev_completion_ts;   // latest_timestamp_s when the previous frame was completed by this frame's first packet, < 0: none
+  double end_ts;               // latest_timestamp_s when this frame was completed (timestamp_end)
 };
 struct PacketRec { double first_ts; unsigned count; unsigned flag; };
 struct Ctl { unsigned ticket, done; };
@@ -46,7 +56,7 @@ __global__ void __launch_bounds__(1024) lidar_decode_kernel(const __grid_constan
                                                             const float* __restrict__ x1, const float* __restrict__ y1, const float* __restrict__ z1,
                                                             const float* __restrict__ x2, const float* __restrict__ y2, const float* __restrict__ z2,
                                                             Ctl* ctl, PacketRec* recs, unsigned epoch, double* chain, const __grid_constant__ FrameArrays out,
-                                                            ndtb_lidar_frame_info* info) {
+                                                            ndtb_lidar_frame_info* info, const __grid_constant__ LegacyUnits U) {
   __shared__ unsigned s_cnt[32], s_off[32];
   __shared__ double s_ts[32];
   __shared__ unsigned s_ticket, s_base;
@@ -57,13 +67,18 @@ __global__ void __launch_bounds__(1024) lidar_decode_kernel(const __grid_constan
   const unsigned t = s_ticket;  // unit index inside the frame: packet t / upp, columns (t % upp) * cpc ...
   const unsigned pk = t / static_cast<unsigned>(P.upp);
   const int col = static_cast<int>(t - pk * P.upp) * P.cpc + w;
-  const unsigned* blk = reinterpret_cast<const unsigned*>(packets + static_cast<size_t>(pk) * P.pitch + 32 + static_cast<size_t>(col) * P.block_bytes);
-  // column header (:676-700): 64-bit time stamp, measurement id, status
+  const unsigned* blk = reinterpret_cast<const unsigned*>(packets + static_cast<size_t>(pk) * P.pitch + (P.legacy ? 0 : 32) + static_cast<size_t>(col) * P.block_bytes);
+  // column header (:676-700): 64-bit time stamp, measurement id, status; LEGACY (:391-441): time stamp, measurement id, frame id,
+  // encoder count, and the block status word behind the pixels
   const unsigned ts_lo = __ldg(blk), ts_hi = __ldg(blk + 1), hdr2 = __ldg(blk + 2);
   const unsigned long long ts_ns = (static_cast<unsigned long long>(ts_hi) << 32) | ts_lo;
   const double col_ts = fmod(static_cast<double>(ts_ns) * 1e-9, 86400.0);
   const unsigned m_id = hdr2 & 0xffffu;
-  const bool col_ok = m_id < static_cast<unsigned>(P.cpf) && ((hdr2 >> 16) & 1u);
+  bool col_ok = m_id < static_cast<unsigned>(P.cpf);
+  if (P.legacy) col_ok = col_ok && col >= static_cast<int>(U.cb[t]) && col < static_cast<int>(U.ce[t]) && __ldg(blk + 4 + 3 * P.ppc) == 0xFFFFFFFFu;
+  else col_ok = col_ok && ((hdr2 >> 16) & 1u);
+  const int px0 = P.legacy ? 4 : 3;                                    // first pixel word behind the column header
+  const unsigned range_mask = P.legacy ? 0x000FFFFFu : 0x0007FFFFu;    // :480 (20 bits) / :807-810 (19 bits)
   const float ox = col_ok ? __ldg(x2 + m_id) : 0.f, oy = col_ok ? __ldg(y2 + m_id) : 0.f, oz = col_ok ? __ldg(z2 + m_id) : 0.f;
 
   float px[LIDAR_MAX_ROUNDS], py[LIDAR_MAX_ROUNDS], pz[LIDAR_MAX_ROUNDS];
@@ -74,7 +89,7 @@ __global__ void __launch_bounds__(1024) lidar_decode_kernel(const __grid_constan
     const int s = r * 32 + lane;
     w0[r] = w1[r] = w2[r] = 0u;
     if (r < P.rounds && s < P.subset) {
-      const unsigned* px_w = blk + 3 + 3 * (s * P.stride);
+      const unsigned* px_w = blk + px0 + 3 * (s * P.stride);
       w0[r] = __ldg(px_w); w1[r] = __ldg(px_w + 1); w2[r] = __ldg(px_w + 2);
     }
   }
@@ -86,7 +101,7 @@ __global__ void __launch_bounds__(1024) lidar_decode_kernel(const __grid_constan
     const int s = r * 32 + lane;
     if (r < P.rounds && col_ok && s < P.subset) {
       const int c_id = s * P.stride;
-      const unsigned range_mm = w0[r] & 0x0007FFFFu;              // :807-810 (19 bits of the first three bytes)
+      const unsigned range_mm = w0[r] & range_mask;
       const float range_m = static_cast<float>(range_mm) * 0.001f;
       if (!(range_m < P.r_min || range_m > P.r_max || range_m == 0.f)) {  // :813
         const size_t k = static_cast<size_t>(m_id) * P.ppc + c_id;
@@ -145,14 +160,24 @@ __global__ void __launch_bounds__(1024) lidar_decode_kernel(const __grid_constan
       s_frame_ts = frame_ts;
       if (t == static_cast<unsigned>(n_units) - 1u) {  // the frame's scalars (:659-663, 856-862) and the hand-over to the next frame
         const unsigned n = base + total;
-        const double latest = s_ts[P.cpc - 1];  // latest_timestamp_s: every column updates it, valid or not (:685)
         const double prev = *chain;
         info->numberpoints = n;
         info->timestamp = have_first ? frame_ts : -1.7976931348623157e308;
-        info->timestamp_end = latest;
-        // interframe_timedelta only sees the previous frame's end when the first point comes from the packet that closed it
-        info->interframe_timedelta = have_first ? ((first_idx < static_cast<unsigned>(P.upp) && prev > 0.0) ? fmax(0.0, frame_ts - prev) : 0.0) : -1.7976931348623157e308;
-        *chain = n > 0u ? latest : 0.0;
+        if (P.legacy) {
+          // prev_frame_completed_latest_ts (:385-388, :428): latest_timestamp_s at the start of the packet that holds the first
+          // point -- unless that packet also completed the previous frame (with points), then the value at that completion
+          double pv = U.latest_at_start[first_idx < static_cast<unsigned>(LEGACY_MAX_UNITS) ? first_idx : 0];
+          if (first_idx == 0u && prev > 0.0 && U.prev_completion_ts >= 0.0) pv = U.prev_completion_ts;
+          info->timestamp_end = U.end_ts;
+          info->interframe_timedelta = have_first ? (pv > 0.0 ? fmax(0.0, frame_ts - pv) : 0.0) : -1.7976931348623157e308;
+          *chain = n > 0u ? 1.0 : 0.0;   // "the frame before had points"
+        } else {
+          const double latest = s_ts[P.cpc - 1];  // latest_timestamp_s: every column updates it, valid or not (:685)
+          info->timestamp_end = latest;
+          // interframe_timedelta only sees the previous frame's end when the first point comes from the packet that closed it
+          info->interframe_timedelta = have_first ? ((first_idx < static_cast<unsigned>(P.upp) && prev > 0.0) ? fmax(0.0, frame_ts - prev) : 0.0) : -1.7976931348623157e308;
+          *chain = n > 0u ? latest : 0.0;
+        }
       }
     }
   }
@@ -218,6 +243,8 @@ struct Slot {
   cudaEvent_t done = nullptr, k0 = nullptr, k1 = nullptr;
   int n_packets = 0;
   unsigned short frame_id = 0;
+  LegacyUnits lu{};                 // LEGACY: column ranges of the units, time stamps the host tracked
+  unsigned long long closing_seq = 0;  // LEGACY: number of the packet whose column closed the frame
 };
 
 }  // namespace
@@ -241,6 +268,8 @@ struct ndtb_lidar_s {
   Slot* active = nullptr;
   Slot* current = nullptr;  // the popped frame
   unsigned short frame_id_ = 0;  // LidarCallback::frame_id_
+  double latest_ts = 0.0;        // LEGACY: LidarCallback::latest_timestamp_s, tracked on the host from the column headers
+  unsigned long long packet_seq = 0;
   uint64_t launches = 0;
   float last_decode_us = 0.f;
   std::string last_error;
@@ -273,10 +302,11 @@ int new_slot(ndtb_lidar_s* l, Slot** out) {
 }
 
 int take_slot(ndtb_lidar_s* l, Slot** out) {
-  if (!l->free_slots.empty()) { *out = l->free_slots.front(); l->free_slots.pop_front(); (*out)->n_packets = 0; return NDTB_OK; }
-  const int rc = new_slot(l, out);
-  if (rc == NDTB_OK) (*out)->n_packets = 0;
-  return rc;
+  if (!l->free_slots.empty()) { *out = l->free_slots.front(); l->free_slots.pop_front(); }
+  else { const int rc = new_slot(l, out); if (rc != NDTB_OK) return rc; }
+  (*out)->n_packets = 0;
+  (*out)->lu.prev_completion_ts = -1.0; (*out)->lu.end_ts = 0.0; (*out)->closing_seq = 0;
+  return NDTB_OK;
 }
 
 // The running frame is complete (:658-669): decode its packets with one kernel.
@@ -288,7 +318,7 @@ int close_active(ndtb_lidar_s* l) {
   if (l->epoch == 0) ++l->epoch;
   CKL(cudaEventRecord(s->k0, l->stream));
   lidar_decode_kernel<<<s->n_packets * l->kp.upp, 32 * l->kp.cpc, 0, l->stream>>>(l->kp, s->d_packets, s->n_packets * l->kp.upp, l->d_x1, l->d_y1, l->d_z1, l->d_x2, l->d_y2, l->d_z2,
-                                                                     l->d_ctl, l->d_recs, l->epoch, l->d_chain, s->arr, s->h_info);
+                                                                     l->d_ctl, l->d_recs, l->epoch, l->d_chain, s->arr, s->h_info, s->lu);
   CKL(cudaGetLastError());
   CKL(cudaEventRecord(s->k1, l->stream));
   CKL(cudaEventRecord(s->done, l->stream));
@@ -381,8 +411,15 @@ int ndtb_lidar_create(int cuda_device, const ndtb_lidar_config* cfg, const float
   // columns per CTA: one CTA per packet measured faster (21.7 us) than four columns per CTA (26.0 us, 256 CTAs: longer look-back)
   k.cpc = (std::getenv("NDTB_LIDAR_CPC") && k.cpp % 4 == 0) ? 4 : k.cpp;
   k.upp = k.cpp / k.cpc;
-  k.block_bytes = 12 + cfg->pixels_per_column * 12;
-  l->expected_size = 32 + static_cast<size_t>(k.cpp) * k.block_bytes + 32;
+  k.legacy = cfg->udp_profile_legacy ? 1 : 0;
+  if (k.legacy) {  // :198-203: no packet header / footer, 16-byte column header, 4-byte block status; a unit is a whole packet
+    k.cpc = k.cpp; k.upp = 1;
+    k.block_bytes = 16 + cfg->pixels_per_column * 12 + 4;
+    l->expected_size = static_cast<size_t>(k.cpp) * k.block_bytes;
+  } else {
+    k.block_bytes = 12 + cfg->pixels_per_column * 12;
+    l->expected_size = 32 + static_cast<size_t>(k.cpp) * k.block_bytes + 32;
+  }
   k.pitch = static_cast<int>((l->expected_size + 15) / 16 * 16);
   k.r_min = cfg->range_min; k.r_max = cfg->range_max; k.z_min = cfg->z_min; k.z_max = cfg->z_max;
   k.refl_thr = static_cast<int>(static_cast<unsigned char>(static_cast<float>(cfg->reflectivity_threshold)));
@@ -392,6 +429,7 @@ int ndtb_lidar_create(int cuda_device, const ndtb_lidar_config* cfg, const float
     k.bmax[a] = cfg->box_center[a] + half;
   }
   l->cap_packets = 2 * ((k.cpf + k.cpp - 1) / k.cpp) + 2;
+  if (k.legacy && l->cap_packets > LEGACY_MAX_UNITS) { delete l; return NDTB_ERR_INVALID; }  // unit table travels as a kernel parameter
   l->cap_points = static_cast<unsigned>(l->cap_packets) * k.cpp * subset;
   auto fail = [&](int code) { ndtb_lidar_destroy(l); return code; };
   if (cudaStreamCreateWithFlags(&l->stream, cudaStreamNonBlocking) != cudaSuccess) return fail(NDTB_ERR_CUDA);
@@ -477,6 +515,56 @@ int ndtb_lidar_push_packets(ndtb_lidar l, const uint8_t* packets, size_t n_packe
     run_len = 0;
     return over;
   };
+  if (l->kp.legacy) {
+    // DecodePacketLegacy (:376-629): the frame id travels in every column header.  The host reads the 12 header bytes of every
+    // column, cuts the stream at the column whose id differs, and hands every frame its packets with the column range that
+    // belongs to it (a packet that straddles two frames is copied into both).
+    const int cpp = l->kp.cpp, cpf = l->kp.cpf, bb = l->kp.block_bytes;
+    auto add_unit = [&](const uint8_t* p, int cb, int ce, double las) -> int {
+      Slot* s = l->active;
+      if (s->n_packets >= l->cap_packets || s->n_packets >= LEGACY_MAX_UNITS)
+        return lidar_fail(l, NDTB_ERR_OVERFLOW, "more packets in one frame than two revolutions hold: packets dropped");
+      CKL(cudaMemcpyAsync(s->d_packets + static_cast<size_t>(s->n_packets) * l->kp.pitch, p, packet_bytes, cudaMemcpyHostToDevice, l->stream));
+      s->lu.cb[s->n_packets] = static_cast<unsigned char>(cb);
+      s->lu.ce[s->n_packets] = static_cast<unsigned char>(ce);
+      s->lu.latest_at_start[s->n_packets] = las;
+      s->n_packets += 1;
+      return NDTB_OK;
+    };
+    for (size_t i = 0; i < n_packets; ++i) {
+      const uint8_t* p = packets + i * pitch_bytes;
+      const double las = l->latest_ts > 0.0 ? l->latest_ts : 0.0;   // :385-388
+      int seg_begin = 0;
+      for (int col = 0; col < cpp; ++col) {
+        const uint8_t* hp = p + static_cast<size_t>(col) * bb;
+        unsigned long long ts_ns = 0;
+        for (int b = 7; b >= 0; --b) ts_ns = (ts_ns << 8) | hp[b];
+        const unsigned m_id = hp[8] | (hp[9] << 8);
+        if (m_id >= static_cast<unsigned>(cpf)) continue;            // :407-410: the column leaves no trace
+        const unsigned short fid = static_cast<unsigned short>(hp[10] | (hp[11] << 8));
+        if (fid != l->frame_id_) {                                    // :420-431
+          if (col > seg_begin) { const int r = add_unit(p, seg_begin, col, las); if (r != NDTB_OK) rc = r; }
+          double completed_at = -1.0;
+          if (l->active->n_packets > 0) {
+            l->active->lu.end_ts = l->latest_ts;
+            l->active->closing_seq = l->packet_seq;
+            completed_at = l->latest_ts;
+            const int c = close_active(l);
+            if (c != NDTB_OK) return c;
+            ++closed;
+          }
+          l->active->lu.prev_completion_ts = completed_at;
+          l->frame_id_ = fid;
+          seg_begin = col;
+        }
+        l->latest_ts = fmod(static_cast<double>(ts_ns) * 1e-9, 86400.0);   // :396, :433
+      }
+      if (cpp > seg_begin) { const int r = add_unit(p, seg_begin, cpp, las); if (r != NDTB_OK) rc = r; }
+      ++l->packet_seq;
+    }
+    if (frames_closed) *frames_closed = closed;
+    return rc;
+  }
   for (size_t i = 0; i < n_packets; ++i) {
     const uint8_t* p = packets + i * pitch_bytes;
     const unsigned packet_type = p[0] | (p[1] << 8);
@@ -517,6 +605,17 @@ int ndtb_lidar_pop_frame(ndtb_lidar l, ndtb_lidar_frame_info* info, int* availab
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, s->k0, s->k1) == cudaSuccess) l->last_decode_us = ms * 1000.f;
     if (s->h_info->numberpoints == 0) { l->free_slots.push_back(s); continue; }  // never emitted by the reference (:659)
+    if (l->kp.legacy) {
+      // one DecodePacketLegacy call returns ONE frame: when the same packet completed a later frame with points as well, that
+      // one overwrote `completed_frame` (:426) and this one was never seen by the caller
+      bool overwritten = false;
+      for (Slot* later : l->closed) {
+        if (later->closing_seq != s->closing_seq) break;
+        CKL(cudaEventSynchronize(later->done));
+        if (later->h_info->numberpoints > 0) { overwritten = true; break; }
+      }
+      if (overwritten) { l->free_slots.push_back(s); continue; }
+    }
     s->h_info->frame_id = s->frame_id;
     s->h_info->packets = static_cast<uint16_t>(s->n_packets);
     l->current = s;

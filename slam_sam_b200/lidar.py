@@ -24,8 +24,9 @@ def config_from_json(meta, param):
     cfg = LidarConfig()
     ndtb.lib().ndtb_lidar_default_config(C.byref(cfg))
     fmt, par, beam = meta["lidar_data_format"], meta["config_params"], meta["beam_intrinsics"]
-    if par["udp_profile_lidar"] != "RNG19_RFL8_SIG16_NIR16":
-        raise ValueError("Unsupported udp_profile_lidar: " + par["udp_profile_lidar"])  # LEGACY is not built
+    if par["udp_profile_lidar"] not in ("RNG19_RFL8_SIG16_NIR16", "LEGACY"):
+        raise ValueError("Unsupported udp_profile_lidar: " + par["udp_profile_lidar"])  # :205
+    cfg.udp_profile_legacy = 1 if par["udp_profile_lidar"] == "LEGACY" else 0
     cfg.columns_per_frame = int(fmt["columns_per_frame"])
     cfg.pixels_per_column = int(fmt["pixels_per_column"])
     cfg.columns_per_packet = int(par["columns_per_packet"])
@@ -211,3 +212,38 @@ def encode_rng19_packets(range_mm, reflectivity, signal, nir, timestamps_ns, fra
     cols[:, 12:] = px.reshape(ncol, 12 * H)
     out[:, 32:32 + columns_per_packet * block] = cols.reshape(n_pk, columns_per_packet * block)
     return out
+
+
+def encode_legacy_packets(range_mm, reflectivity, signal, nir, timestamps_ns, frame_ids, columns_per_packet=16, m_ids=None, status=None, rng=None):
+    """Synthetic LEGACY packets (the layout DecodePacketLegacy parses, src/lidarcallback.cpp:391-497): no packet header; per
+    column 16 header bytes {time stamp u64, measurement id u16, frame id u16, encoder u32}, 12 bytes per pixel {range u32 (20
+    bits used), reflectivity u8, -, signal u16, nir u16, -} and a 4-byte block status (0xFFFFFFFF = valid).  The frame id is
+    PER COLUMN: a frame may end in the middle of a packet.  `status`: per column, truthy = valid.
+    Returns a uint8 array (n_packets, cpp * (16 + 12 * pixels + 4))."""
+    range_mm = np.asarray(range_mm, np.uint32)
+    ncol, H = range_mm.shape
+    assert ncol % columns_per_packet == 0
+    n_pk = ncol // columns_per_packet
+    block = 16 + 12 * H + 4
+    noise = (lambda shape: np.zeros(shape, np.uint8)) if rng is None else (lambda shape: rng.integers(0, 256, shape, dtype=np.uint8))
+    m_ids = np.arange(ncol) if m_ids is None else np.asarray(m_ids)
+    status = np.ones(ncol, np.uint8) if status is None else np.asarray(status, np.uint8)
+    px = noise((ncol, H, 12))
+    r = range_mm & 0xFFFFF
+    px[:, :, 0] = r & 0xff
+    px[:, :, 1] = (r >> 8) & 0xff
+    px[:, :, 2] = (px[:, :, 2] & 0xF0) | ((r >> 16) & 0x0F)   # the upper twelve bits of the range word are not range (mask 0x000FFFFF)
+    px[:, :, 4] = np.asarray(reflectivity, np.uint8)
+    px[:, :, 6:8] = np.ascontiguousarray(signal, np.uint16).astype("<u2").view(np.uint8).reshape(ncol, H, 2)
+    px[:, :, 8:10] = np.ascontiguousarray(nir, np.uint16).astype("<u2").view(np.uint8).reshape(ncol, H, 2)
+    cols = noise((ncol, block))
+    cols[:, 0:8] = np.ascontiguousarray(timestamps_ns, np.uint64).astype("<u8").view(np.uint8).reshape(ncol, 8)
+    cols[:, 8:10] = np.ascontiguousarray(m_ids).astype("<u2").view(np.uint8).reshape(ncol, 2)
+    cols[:, 10:12] = np.ascontiguousarray(frame_ids, np.uint16).astype("<u2").view(np.uint8).reshape(ncol, 2)
+    cols[:, 16:16 + 12 * H] = px.reshape(ncol, 12 * H)
+    good = status.astype(bool)
+    cols[good, 16 + 12 * H:] = 0xFF
+    bad = cols[~good, 16 + 12 * H:]
+    bad[:, 0] &= 0xFE                                           # anything but 0xFFFFFFFF
+    cols[~good, 16 + 12 * H:] = bad
+    return cols.reshape(n_pk, columns_per_packet * block)

@@ -70,7 +70,8 @@ class LidarConfig(C.Structure):
     _fields_ = [("columns_per_frame", C.c_int), ("pixels_per_column", C.c_int), ("columns_per_packet", C.c_int), ("channel_stride", C.c_int),
                 ("reflectivity_threshold", C.c_int), ("lidar_origin_to_beam_origin_mm", C.c_float), ("range_min", C.c_float),
                 ("range_max", C.c_float), ("z_min", C.c_float), ("z_max", C.c_float), ("box_center", C.c_float * 3),
-                ("box_dimensions", C.c_float * 3), ("body_to_lidar_rotation", C.c_double * 9), ("body_to_lidar_translation", C.c_double * 3)]
+                ("box_dimensions", C.c_float * 3), ("body_to_lidar_rotation", C.c_double * 9), ("body_to_lidar_translation", C.c_double * 3),
+                ("udp_profile_legacy", C.c_int)]
 
 
 class LidarFrameInfo(C.Structure):

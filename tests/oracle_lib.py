@@ -414,7 +414,8 @@ class OracleLidar:
     def __init__(self, cfg, az_deg, alt_deg):
         self.L = lib()
         self.cfg = cfg
-        ci = np.array([cfg.columns_per_frame, cfg.pixels_per_column, cfg.columns_per_packet, cfg.channel_stride, cfg.reflectivity_threshold], np.int32)
+        ci = np.array([cfg.columns_per_frame, cfg.pixels_per_column, cfg.columns_per_packet, cfg.channel_stride, cfg.reflectivity_threshold,
+                       int(getattr(cfg, "udp_profile_legacy", 0))], np.int32)
         cf = np.array([cfg.lidar_origin_to_beam_origin_mm, cfg.range_min, cfg.range_max, cfg.z_min, cfg.z_max, *cfg.box_center, *cfg.box_dimensions], np.float32)
         cd = np.array([*cfg.body_to_lidar_rotation, *cfg.body_to_lidar_translation], np.float64)
         az = np.ascontiguousarray(az_deg, np.float32); alt = np.ascontiguousarray(alt_deg, np.float32)

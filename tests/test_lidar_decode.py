@@ -168,7 +168,7 @@ def test_lidar_create_needs_a_gpu_and_validates():
     if not torch.cuda.is_available():
         with pytest.raises(ndtb.NdtbError):
             LidarCallback(*make_config())  # no CPU fallback
-    assert C.sizeof(ndtb.LidarConfig) == 160 and C.sizeof(ndtb.LidarFrameInfo) == 32
+    assert C.sizeof(ndtb.LidarConfig) == 168 and C.sizeof(ndtb.LidarFrameInfo) == 32
 
 
 # ------------------------------------------------------------------------------------------------- GPU: device decoder
@@ -322,3 +322,77 @@ def test_gpu_decoder_buffers_and_limits(oracle):
     # nothing closed yet -> nothing to pop; empty push is a no-op
     cb4 = LidarCallback(cfg, az, alt)
     assert cb4.push(pk[:3]) == 0 and cb4.pop() is None and cb4.push(pk[:0]) == 0
+
+
+# ------------------------------------------------------------------------------------------------------ LEGACY profile
+def make_legacy_stream(cfg, frame_cols, seed, first_frame_id=11, t0_ns=1_762_300_000_000_000_000, empty_frames=(), bad_columns=True):
+    """LEGACY packets (DecodePacketLegacy, src/lidarcallback.cpp:376-629) of frames with `frame_cols[f]` columns each -- the frame id
+    travels in every column header, so frames whose length is not a multiple of the packet end in the middle of a packet --
+    followed by the columns that close the last frame and pad the final packet."""
+    from slam_sam_b200.lidar import encode_legacy_packets
+
+    rng = np.random.default_rng(seed)
+    W, Hh, cpp = cfg.columns_per_frame, cfg.pixels_per_column, cfg.columns_per_packet
+    total = sum(frame_cols)
+    pad = (-total) % cpp or cpp
+    fid = np.concatenate([np.full(n, (first_frame_id + f) & 0xffff) for f, n in enumerate(list(frame_cols) + [pad])])
+    ncol = total + pad
+    rng_mm = rng.integers(0, 1 << 20, (ncol, Hh)).astype(np.uint32)
+    close = rng.random((ncol, Hh))
+    rng_mm[close < 0.3] = rng.integers(0, 9000, int((close < 0.3).sum()))
+    rng_mm[close > 0.9] = 0
+    start = 0
+    for f, n in enumerate(frame_cols):
+        if f in empty_frames:
+            rng_mm[start:start + n] = 0
+        start += n
+    refl = rng.integers(0, 256, (ncol, Hh)); sig = rng.integers(0, 65536, (ncol, Hh)); nir = rng.integers(0, 65536, (ncol, Hh))
+    ts = t0_ns + np.arange(ncol, dtype=np.uint64) * np.uint64(48_828)
+    m_ids = np.arange(ncol) % W
+    status = np.ones(ncol, np.uint8)
+    if bad_columns:
+        status[rng.integers(0, total, 5)] = 0                     # block status != 0xFFFFFFFF -> column skipped (:435-441)
+        m_ids = m_ids.copy(); m_ids[rng.integers(0, total, 4)] = W + 9   # invalid measurement id -> the column leaves no trace (:407-410)
+    return encode_legacy_packets(rng_mm, refl, sig, nir, ts, fid, cpp, m_ids=m_ids, status=status, rng=rng)
+
+
+def test_oracle_legacy_state_machine(oracle):
+    """The LEGACY restatement: packet size, frames cut at the column whose id differs, time stamps of the frame scalars."""
+    cfg, az, alt = make_config(udp_profile_legacy=1)
+    o = oracle.OracleLidar(cfg, az, alt)
+    assert o.expected_size == 16 * (16 + 12 * 32 + 4)
+    pk = make_legacy_stream(cfg, [64, 40, 64], seed=5, bad_columns=False)   # the second frame ends in the middle of a packet
+    frames = o.decode(pk)
+    assert [f["frame_id"] for f in frames] == [11, 12, 13]
+    col_ts = np.fmod((1_762_300_000_000_000_000 + np.arange(64 + 40 + 64 + 8, dtype=np.uint64) * np.uint64(48_828)).astype(np.float64) * 1e-9, 86400.0)
+    assert frames[0]["timestamp_end"] == col_ts[63] and frames[1]["timestamp_end"] == col_ts[103] and frames[2]["timestamp_end"] == col_ts[167]
+    assert set(np.unique(frames[1]["timestamp_points"])) <= set(col_ts[64:104])
+    assert frames[0]["interframe_timedelta"] == 0.0                         # nothing before the first packet
+    # frame 1 starts at a packet boundary: prev = latest_timestamp_s at the start of its first packet
+    assert frames[1]["interframe_timedelta"] == max(0.0, frames[1]["timestamp"] - col_ts[63])
+    # frame 2 starts in the middle of a packet that completed frame 1: prev = latest_timestamp_s at that completion
+    assert frames[2]["interframe_timedelta"] == max(0.0, frames[2]["timestamp"] - col_ts[103])
+    assert o.decode(pk[:, :-1]) == []                                       # wrong size: every packet ignored
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("stride,frame_cols", [(1, [64, 64, 64]), (2, [64, 40, 64, 24, 64]), (4, [50, 70, 64])])
+def test_gpu_legacy_decoder_matches_oracle(oracle, stride, frame_cols):
+    """LEGACY packets through the device decoder: frames that end at packet boundaries and in the middle of a packet, invalid
+    measurement ids, bad block status, an empty frame; one call and packet by packet."""
+    cfg, az, alt = make_config(stride=stride, udp_profile_legacy=1)
+    o = oracle.OracleLidar(cfg, az, alt)
+    pk = make_legacy_stream(cfg, frame_cols, seed=17 + stride, empty_frames=(1,) if len(frame_cols) > 3 else ())
+    want = o.decode(pk)
+    assert len(want) >= len(frame_cols) - 1 and all(f["numberpoints"] > 50 for f in want)
+    cb = LidarCallback(cfg, az, alt)
+    assert cb.expected_size == o.expected_size
+    got = frames_as_dicts(cb.DecodePackets(pk))
+    assert_frames_equal(got, want)
+    cb2 = LidarCallback(cfg, az, alt)
+    got2 = []
+    for i in range(pk.shape[0]):
+        f = cb2.DecodePacket(pk[i])
+        if f is not None:
+            got2 += frames_as_dicts([f])
+    assert_frames_equal(got2, want)
