@@ -393,6 +393,14 @@ int ndtb_newton_direction(const double H[36], const double b[6], int method, dou
  * measured as `reps` back-to-back launches between a single pair of CUDA events on the handle's stream: the event
  * overhead (~7 us per pair on a B200 box) is amortised over the launches instead of being added to each. */
 int ndtb_time_eval_kernel(ndtb_handle h, const double p[6], const float* T16, int reps, float* mean_us);
+/* Test hook: ONE Newton step between two evaluations of ndtb_align (direction by pivoted elimination, normalisation, descent flip,
+ * step clamp, pose -> float 4x4, angle tables; ndt_omp_impl.hpp:128-190, 396-538, 915-990), computed by the warp-cooperative device
+ * code (which = 0, device_newton.cuh) or by the host code the align loop runs (which = 1), for bit-for-bit comparison.
+ * params = {step_max, step_min, trans_epsilon, -}; status: 0 continue (out_state81 = T[12], j_ang[24], h_ang[45]; out_p6 = the next
+ * pose), 1 converged, 2 the host decides (ill-conditioned H -> SVD, zero / NaN step, zero slope). */
+int ndtb_test_newton_step(int which, int cuda_device, const double g[6], const double H[36], const double p[6], const double params[4],
+                          int max_iterations, int first, int nr_iterations, double a_t_prev, int* status, int* nr_out, double* a_t_out,
+                          float* out_state81, double* out_p6);
 /* Number of CUDA kernels this handle has launched since creation (bench.py's gpu_launches). */
 int ndtb_get_launch_count(ndtb_handle h, uint64_t* launches);
 

@@ -60,7 +60,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "nd
            "ndtb_mg_get_grid_ids", "ndtb_mg_get_leaves", "ndtb_mg_compute_derivatives", "ndtb_mg_align", "ndtb_mg_calculate_scores",
            "ndtb_svn_get_timings", "ndtb_comm_window_handle", "ndtb_comm_connect", "ndtb_comm_init", "ndtb_comm_close", "ndtb_comm_info",
            "ndtb_svn_align_sharded", "ndtb_calculate_score", "ndtb_write_ndt_files", "ndtb_compute_derivatives_static", "ndtb_stage_target", "ndtb_stage_source",
-           "ndtb_commit_target", "ndtb_commit_source", "ndtb_staged_count", "ndtb_stage_sync"]
+           "ndtb_commit_target", "ndtb_commit_source", "ndtb_staged_count", "ndtb_stage_sync", "ndtb_test_newton_step"]
 
 _LIB = None
 
@@ -111,6 +111,8 @@ def lib():
         L.ndtb_commit_target.argtypes = [H]
         L.ndtb_commit_source.argtypes = [H]
         L.ndtb_stage_sync.argtypes = [H]
+        L.ndtb_test_newton_step.argtypes = [C.c_int, C.c_int, c_d, c_d, c_d, c_d, C.c_int, C.c_int, C.c_int, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                            c_d, c_f, c_d]
         L.ndtb_staged_count.argtypes = [H, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.ndtb_set_regularization_pose.argtypes = [H, c_f]
         L.ndtb_compute_derivatives.argtypes = [H, c_d, c_f, C.c_int, c_d, c_d, c_d, c_d]
@@ -194,6 +196,22 @@ def host_cloud(cloud):
     if a.ndim != 2 or a.shape[1] < 3:
         raise ValueError("cloud must be (N, >=3) float32")
     return a, a.shape[0], a.shape[1] * 4
+
+
+def test_newton_step(which, g, H, p, step_max, step_min, eps, max_iterations, first, nr_iterations, a_t_prev, device=0):
+    """ndtb_test_newton_step: (status, nr_iterations, a_t, state81 float32, next pose)."""
+    g = np.ascontiguousarray(g, np.float64); H = np.ascontiguousarray(H, np.float64).reshape(36); p = np.ascontiguousarray(p, np.float64)
+    prm = np.array([step_max, step_min, eps, 0.0])
+    st, nr = C.c_int(0), C.c_int(0)
+    a_t = np.zeros(1); state = np.zeros(81, np.float32); pn = np.zeros(6)
+    rc = lib().ndtb_test_newton_step(which, device, _ptr(g, c_d), _ptr(H, c_d), _ptr(p, c_d), _ptr(prm, c_d), max_iterations, int(first), nr_iterations,
+                                     float(a_t_prev), C.byref(st), C.byref(nr), _ptr(a_t, c_d), _ptr(state, c_f), _ptr(pn, c_d))
+    if rc != NDTB_OK:
+        raise NdtbError(rc, "ndtb_test_newton_step")
+    return st.value, nr.value, a_t[0], state, pn
+
+
+test_newton_step.__test__ = False   # not a pytest test
 
 
 def svn_mean_pose(poses, prior):

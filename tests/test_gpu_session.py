@@ -108,3 +108,46 @@ def test_session_can_leave_sms_free_for_other_streams(street):
     assert np.array_equal(part.trace(), tb) and np.array_equal(rc["T"], rb["T"])
     with pytest.raises(ndtb.NdtbError):
         part.set_option("session_free_sms", 500)
+
+
+def test_device_newton_step_against_the_host_step():
+    """device_newton.cuh, the experiment behind DESIGN 4.4: a warp-cooperative Newton step on the device reproduces the host step
+    of ndtb_align BIT FOR BIT in everything that is IEEE arithmetic -- direction (pivoted elimination + refinement), step length,
+    next pose, the decision to continue / stop / hand over to the host -- but not in the float transform and the angle tables:
+    those go through sin / cos, and CUDA's routines do not round like glibc's sinf / sin (1 ulp apart in a few per cent of the
+    entries).  That is why the step stays on the host: a 1-ulp transform moves every evaluation by ~1e-7 relative, outside the
+    1e-9 per-evaluation bar against the oracle."""
+    rng = np.random.default_rng(11)
+    n_cont = 0
+    n_entries = n_off = 0
+    for case in range(300):
+        A = rng.normal(size=(6, 6)) * np.array([1, 1, 1, 8, 8, 8])
+        H = -(A @ A.T) * rng.uniform(10, 1e4)                             # NDT Hessians near an optimum are negative definite
+        if case % 7 == 0:
+            H = H + rng.normal(size=(6, 6)) * 1e-3                        # not exactly symmetric
+        g = rng.normal(size=6) * rng.uniform(1e-3, 1e3)
+        if case % 11 == 3:
+            g = -g
+        p = np.concatenate([rng.uniform(-50, 50, 3), rng.uniform(-3.1, 3.1, 3)])
+        if case % 13 == 5:
+            p[3:] = rng.uniform(-2e-4, 2e-4, 3)                           # around the 1e-4 snap of the angle tables
+        first = case % 5 == 0
+        nr = int(rng.integers(0, 40)); a_prev = float(rng.choice([0.1, 0.02, 0.004, 0.0009]))
+        args = (g, H, p, 0.1, 0.005, 0.01, 35, first, nr, a_prev)
+        d, h = ndtb.test_newton_step(0, *args), ndtb.test_newton_step(1, *args)
+        assert d[0] == h[0] and d[1] == h[1], case
+        if h[0] == 0:
+            n_cont += 1
+            assert d[2] == h[2] and np.array_equal(d[4], h[4]), case     # step length and next pose: exact
+            du, hu = d[3].view(np.int32), h[3].view(np.int32)
+            assert np.abs(d[3].astype(np.float64) - h[3].astype(np.float64)).max() <= 4e-7, case   # entries of rotations and tables (|.| <= 1): a few float ulps
+            assert np.array_equal(d[3][[3, 7, 11]], h[3][[3, 7, 11]])                           # the translation column is float(p): exact
+            n_entries += du.size; n_off += int((du != hu).sum())
+    assert n_cont > 150
+    assert 0 < n_off < 0.1 * n_entries                                    # libm differences exist, and they are rare
+    # the cases the host has to decide: singular H, zero gradient, NaN
+    Hs = -np.outer(np.arange(1, 7.0), np.arange(1, 7.0))
+    for g, H in ((np.ones(6), Hs), (np.zeros(6), -np.eye(6)), (np.full(6, np.nan), -np.eye(6))):
+        d = ndtb.test_newton_step(0, g, H, np.zeros(6), 0.1, 0.005, 0.01, 35, True, 0, 0.0)
+        h = ndtb.test_newton_step(1, g, H, np.zeros(6), 0.1, 0.005, 0.01, 35, True, 0, 0.0)
+        assert d[0] == h[0] == 2
