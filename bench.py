@@ -106,31 +106,6 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-ALL_CPUS = os.sched_getaffinity(0)
-
-
-def pin_to_gpu_numa_node(local_rank):
-    """Keeps this rank's threads (the polling Newton loop, the copy issuers) on the CPU cores next to its GPU: with several ranks on
-    one box the host side is what limits weak scaling.  NVML's ideal CPU affinity of the device; silently skipped when unavailable
-    (or with NDTB_BENCH_NO_AFFINITY=1)."""
-    if os.environ.get("NDTB_BENCH_NO_AFFINITY"):
-        return None
-    try:
-        import pynvml
-
-        pynvml.nvmlInit()
-        h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
-        words = (os.cpu_count() + 63) // 64
-        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
-        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
-        cpus &= os.sched_getaffinity(0)
-        if cpus:
-            os.sched_setaffinity(0, cpus)
-        return sorted(cpus)
-    except Exception:
-        return None
-
-
 def build_traffic():
     try:
         return float(json.load(open(os.path.join(ROOT, "profiles", "build_kernels_traffic.json")))["dram_bytes_per_build"])
@@ -474,9 +449,7 @@ def run_gpu(args, rank, world, local_rank):
                                       "(profiles/build_kernels_traffic.json)"}
     if not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
-        os.sched_setaffinity(0, ALL_CPUS)      # the CPU baseline gets every host core, not only the ones next to the GPU
         c = run_cpu(tgt, scans, guesses, steps=2, warmup=1, threads=threads)
-        pin_to_gpu_numa_node(local_rank)
         line["parity"] = parity_block(h, tgt, scans, guesses, c["results"])
         assert line["parity"]["ok"], f"parity bars missed: {line['parity']}"
         line["cpu_baseline"] = {"value": 1.0 / c["mean_s"], "unit": "scans/s", "cores": threads, "kind": "port",
@@ -867,7 +840,6 @@ def main():
     import torch.distributed as dist
 
     torch.cuda.set_device(local_rank)
-    pin_to_gpu_numa_node(local_rank)
     if world > 1:
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
     if args.workload == "svn":
