@@ -393,6 +393,7 @@ def run_gpu(args, rank, world, local_rank):
                              "roofline.kernel_us_back_to_back is the same kernel as 50 back-to-back launches between one event pair"},
         "e2e": {"value": e2e, "unit": "scans/s", "h2d_bytes_per_step": 16 * (N_MAP + N_SCAN) + 64, "d2h_bytes_per_step": int(368 * st2["eval_launches"] / K + 64),
                 "ms_per_step": e2e_ms / K, "max_abs_translation_error_m": st2["err"], "build_ms": st2["build_ms"] / K, "align_ms": st2["align_ms"] / K,
+                "session_eval_us": st2["eval_ms"] / max(st2["eval_launches"], 1) * 1e3,
                 "what": "host buffers in, result out, through the C ABI: ndtb_stage_target / ndtb_stage_source start the copy of step i + 1's map "
                         "and scan (18 MB, pinned host memory, copy stream) before ndtb_commit_target / ndtb_commit_source / ndtb_align of step i; "
                         "the step ends with ndtb_stage_sync, i.e. once that copy has arrived, so every timed step holds one full H2D copy, "

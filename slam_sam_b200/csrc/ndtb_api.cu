@@ -63,17 +63,43 @@ int upload_cloud(ndtb_handle_s* h, const float* xyz, size_t n, size_t stride_byt
     *alloc = cap;
   }
   if (n == 0) return NDTB_OK;
-  if (stride_bytes == sizeof(float4)) {
-    CKH(cudaMemcpyAsync(*d_buf, xyz, n * sizeof(float4), cudaMemcpyHostToDevice, h->stream));
-  } else if (stride_bytes >= sizeof(float4)) {
-    // e.g. pcl::PointXYZI (32-byte stride): copy the first 16 bytes of every point
-    CKH(cudaMemcpy2DAsync(*d_buf, sizeof(float4), xyz, stride_bytes, sizeof(float4), n, cudaMemcpyHostToDevice, h->stream));
-  } else if (stride_bytes == 12) {
-    CKH(cudaMemsetAsync(*d_buf, 0, n * sizeof(float4), h->stream));
-    CKH(cudaMemcpy2DAsync(*d_buf, sizeof(float4), xyz, 12, 12, n, cudaMemcpyHostToDevice, h->stream));
-  } else {
-    return set_error(h, NDTB_ERR_INVALID, "stride_bytes must be 12 or >= 16");
+  return copy_cloud_to_device(h, xyz, n, stride_bytes, *d_buf, h->stream, &h->d_raw, &h->raw_alloc);
+}
+
+// Point i of a strided host cloud (already on the device, byte for byte) -> packed float4: x, y, z and, for strides >= 16, the
+// fourth float of the point (what the 16-byte rows of the former 2-D copy carried); 0 for packed xyz.
+__global__ void __launch_bounds__(256) repack_cloud_kernel(const unsigned char* __restrict__ raw, size_t stride, size_t n, float4* __restrict__ out) {
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n; i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const float* p = reinterpret_cast<const float*>(raw + i * stride);
+    float4 v;
+    v.x = p[0]; v.y = p[1]; v.z = p[2];
+    v.w = (stride >= sizeof(float4)) ? p[3] : 0.0f;
+    out[i] = v;
   }
+}
+
+int copy_cloud_to_device(ndtb_handle_s* h, const float* xyz, size_t n, size_t stride_bytes, float4* d_dst, cudaStream_t stream, unsigned char** d_raw,
+                         size_t* raw_alloc) {
+  if (stride_bytes == sizeof(float4)) {
+    CKH(cudaMemcpyAsync(d_dst, xyz, n * sizeof(float4), cudaMemcpyHostToDevice, stream));
+    return NDTB_OK;
+  }
+  if (!(stride_bytes == 12 || stride_bytes >= sizeof(float4)) || (stride_bytes & 3u)) return set_error(h, NDTB_ERR_INVALID, "stride_bytes must be 12 or >= 16, and a multiple of 4");
+  const size_t tail = stride_bytes >= sizeof(float4) ? sizeof(float4) : 12;   // bytes of the last point that are read
+  const size_t bytes = (n - 1) * stride_bytes + tail;
+  if (bytes > *raw_alloc) {
+    CKH(cudaStreamSynchronize(stream));
+    cudaFree(*d_raw);
+    *d_raw = nullptr; *raw_alloc = 0;
+    const size_t cap = bytes + bytes / 8 + 4096;
+    CKH(cudaMalloc(d_raw, cap));
+    *raw_alloc = cap;
+  }
+  CKH(cudaMemcpyAsync(*d_raw, xyz, bytes, cudaMemcpyHostToDevice, stream));
+  const int blocks = static_cast<int>(std::min<size_t>((n + 255) / 256, 148 * 8));
+  repack_cloud_kernel<<<blocks, 256, 0, stream>>>(*d_raw, stride_bytes, n, d_dst);
+  CKH(cudaGetLastError());
+  h->launches += 1;
   return NDTB_OK;
 }
 
@@ -372,6 +398,7 @@ int ndtb_destroy(ndtb_handle h) {
   if (h->target_owned) cudaFree(h->d_target);
   if (h->source_owned) cudaFree(h->d_source);
   if (h->h_stage) cudaFreeHost(h->h_stage);
+  cudaFree(h->d_raw);
   free_device_grid(h->grid);
   cudaFree(h->eval.d_states); cudaFree(h->eval.d_partials); cudaFree(h->eval.d_results); cudaFree(h->eval.d_tickets);
   if (h->h_states) cudaFreeHost(h->h_states);

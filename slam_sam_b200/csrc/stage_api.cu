@@ -13,7 +13,7 @@ void stage_free(ndtb_handle_s* h) {
   for (int k = 0; k < 2; ++k)
     for (int i = 0; i < 2; ++i) {
       ndtb_handle_s::StagedCloud& s = h->staged[k][i];
-      cudaFree(s.d);
+      cudaFree(s.d); cudaFree(s.d_raw);
       if (s.ready) cudaEventDestroy(s.ready);
       if (s.reusable) cudaEventDestroy(s.reusable);
       s = ndtb_handle_s::StagedCloud();
@@ -28,7 +28,7 @@ static int stage_cloud(ndtb_handle_s* h, int kind, const float* xyz, size_t n, s
   if (!h) return NDTB_ERR_INVALID;
   CKS(cudaSetDevice(h->device));
   if (!xyz || n == 0) return set_error(h, NDTB_ERR_EMPTY, kind == 0 ? "empty target cloud" : "empty source cloud");
-  if (stride_bytes != 12 && stride_bytes < sizeof(float4)) return set_error(h, NDTB_ERR_INVALID, "stride_bytes must be 12 or >= 16");
+  if ((stride_bytes != 12 && stride_bytes < sizeof(float4)) || (stride_bytes & 3u)) return set_error(h, NDTB_ERR_INVALID, "stride_bytes must be 12 or >= 16, and a multiple of 4");
   if (h->staged_count[kind] == 2) return set_error(h, NDTB_ERR_NOT_READY, "two clouds are already staged: commit one first");
   if (!h->stage_stream) CKS(cudaStreamCreateWithFlags(&h->stage_stream, cudaStreamNonBlocking));
   ndtb_handle_s::StagedCloud& s = h->staged[kind][(h->staged_head[kind] + h->staged_count[kind]) & 1];
@@ -47,13 +47,9 @@ static int stage_cloud(ndtb_handle_s* h, int kind, const float* xyz, size_t n, s
   }
   // the buffer may be a former d_target / d_source: whatever the handle's stream still had to read from it comes first
   CKS(cudaStreamWaitEvent(h->stage_stream, s.reusable, 0));
-  if (stride_bytes == sizeof(float4)) {
-    CKS(cudaMemcpyAsync(s.d, xyz, n * sizeof(float4), cudaMemcpyHostToDevice, h->stage_stream));
-  } else if (stride_bytes > sizeof(float4)) {
-    CKS(cudaMemcpy2DAsync(s.d, sizeof(float4), xyz, stride_bytes, sizeof(float4), n, cudaMemcpyHostToDevice, h->stage_stream));
-  } else {
-    CKS(cudaMemsetAsync(s.d, 0, n * sizeof(float4), h->stage_stream));
-    CKS(cudaMemcpy2DAsync(s.d, sizeof(float4), xyz, 12, 12, n, cudaMemcpyHostToDevice, h->stage_stream));
+  {
+    const int rc = copy_cloud_to_device(h, xyz, n, stride_bytes, s.d, h->stage_stream, &s.d_raw, &s.raw_alloc);
+    if (rc != NDTB_OK) return rc;
   }
   CKS(cudaEventRecord(s.ready, h->stage_stream));
   s.n = n;
