@@ -78,6 +78,17 @@ __global__ void __launch_bounds__(256) repack_cloud_kernel(const unsigned char* 
   }
 }
 
+// out = T * p for every source point, rows r of the float 4x4: T[4r] x + (T[4r+1] y + (T[4r+2] z + T[4r+3]))  (the evaluation
+// order of the host loop this kernel replaced; -fmad=false keeps the two roundings per term).
+struct TransformT { float m[12]; };
+__global__ void __launch_bounds__(256) transform_cloud_kernel(const float4* __restrict__ src, size_t n, const TransformT T, float* __restrict__ out_xyz) {
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n; i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const float4 p = __ldg(src + i);
+#pragma unroll
+    for (int r = 0; r < 3; ++r) out_xyz[3 * i + r] = T.m[4 * r] * p.x + (T.m[4 * r + 1] * p.y + (T.m[4 * r + 2] * p.z + T.m[4 * r + 3]));
+  }
+}
+
 int copy_cloud_to_device(ndtb_handle_s* h, const float* xyz, size_t n, size_t stride_bytes, float4* d_dst, cudaStream_t stream, unsigned char** d_raw,
                          size_t* raw_alloc) {
   if (stride_bytes == sizeof(float4)) {
@@ -674,14 +685,22 @@ static int align_impl(ndtb_handle h, bool multigrid, const float guess[16], ndtb
   // only complete once the kernel's idle time-out fires
   session_end(h);
   if (out_xyz) {
-    // `output` of pcl::Registration::align: the source transformed by the final transformation
-    // (host loop, N points -- off the timed path; callers that do not need it pass NULL).
-    std::vector<float4> tmp(N);
-    CKH(cudaMemcpyAsync(tmp.data(), h->d_source, N * sizeof(float4), cudaMemcpyDeviceToHost, h->stream));
+    // `output` of pcl::Registration::align: the source transformed by the final transformation.  Transformed on the device
+    // (same float operations in the same order as the host loop it replaces), packed xyz, one D2H copy of 12 N bytes.
+    const size_t bytes = N * 3 * sizeof(float);
+    if (bytes > h->raw_alloc) {
+      cudaFree(h->d_raw);
+      h->d_raw = nullptr; h->raw_alloc = 0;
+      CKH(cudaMalloc(&h->d_raw, bytes + bytes / 8 + 4096));
+      h->raw_alloc = bytes + bytes / 8 + 4096;
+    }
+    TransformT Tk;
+    std::memcpy(Tk.m, final_T, 12 * sizeof(float));
+    transform_cloud_kernel<<<static_cast<int>(std::min<size_t>((N + 255) / 256, 148 * 8)), 256, 0, h->stream>>>(h->d_source, N, Tk, reinterpret_cast<float*>(h->d_raw));
+    CKH(cudaGetLastError());
+    h->launches += 1;
+    CKH(cudaMemcpyAsync(out_xyz, h->d_raw, bytes, cudaMemcpyDeviceToHost, h->stream));
     CKH(cudaStreamSynchronize(h->stream));
-    for (size_t i = 0; i < N; ++i)
-      for (int r = 0; r < 3; ++r)
-        out_xyz[3 * i + r] = final_T[4 * r] * tmp[i].x + (final_T[4 * r + 1] * tmp[i].y + (final_T[4 * r + 2] * tmp[i].z + final_T[4 * r + 3]));
   }
   cudaEventRecord(h->ev[1], h->stream);
   h->align_time_pending = true;  // resolved by ndtb_get_timings: the caller does not wait for the resident kernel to leave

@@ -139,6 +139,12 @@ def test_pcl_adapter_through_the_base_pointer(two_plane, tmp_path):
         assert rc == 0
     assert dt < 0.025, f"align with out_xyz took {dt * 1e3:.1f} ms: queued behind the resident kernel?"
     assert np.abs(out[0] - p0).max() <= 1e-4
+    # every point, bit for bit: T[4r] x + (T[4r+1] y + (T[4r+2] z + T[4r+3])) in float, two roundings per term (the device kernel
+    # restates the host loop it replaced)
+    Tf = np.array(res.pose, np.float32).reshape(4, 4)
+    s3 = np.ascontiguousarray(two_plane["source"][:, :3], np.float32)
+    want = np.stack([Tf[r, 0] * s3[:, 0] + (Tf[r, 1] * s3[:, 1] + (Tf[r, 2] * s3[:, 2] + Tf[r, 3])) for r in range(3)], axis=1).astype(np.float32)
+    assert np.array_equal(out, want)
 
 
 LIDAR_EXE = os.path.join(ROOT, "tests", "cpp", "lidar_example")
