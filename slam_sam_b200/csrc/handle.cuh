@@ -32,11 +32,11 @@ struct ndtb_handle_s {
   struct Keyframe { float4* d_points = nullptr; size_t n = 0; };
   std::map<int64_t, Keyframe> keyframes;
 
-  // ndtb_align_batch scratch, kept between calls (allocation costs milliseconds): three scan slots + a copy stream
+  // ndtb_align_batch scratch, kept between calls (allocation costs milliseconds): four scan slots + a copy stream
   struct BatchSlot { float4* d_src = nullptr; size_t alloc = 0; cudaEvent_t uploaded = nullptr; };
-  BatchSlot batch_slot[3];
+  BatchSlot batch_slot[4];
   cudaStream_t batch_copy_stream = nullptr;
-  double* batch_h_results = nullptr;    // pinned, 3 x 2 x (RED_N + 2) words
+  double* batch_h_results = nullptr;    // pinned, 4 x 2 x (RED_N + 2) words
 
   // pcl::VoxelGrid down-sampling scratch (ndtb_voxelgrid_filter): its own sort buffers, so the current map is untouched
   ndtb::DeviceGrid ds_grid;
@@ -64,7 +64,7 @@ struct ndtb_handle_s {
   bool session_open = false;
   bool use_sessions = true;             // off with per-kernel events (ndtb_set_profiling) or NDTB_NO_SESSION=1
   double session_idle_ms = 50.0;        // the resident kernel leaves after this long without a command
-  bool batch_interleave = true;         // ndtb_align_batch keeps two alignments in flight (ndtb_set_option "batch_interleave")
+  bool batch_interleave = true;         // ndtb_align_batch keeps three alignments in flight (ndtb_set_option "batch_interleave")
   bool direct_solver = true;            // Newton direction by pivoted elimination when well conditioned (ndtb_set_option)
   unsigned long long pending_time_key = 0;  // result key of the last session evaluation whose duration slot is unread
   double session_eval_ns = 0;           // device-side duration of the session evaluations of the last align
