@@ -677,7 +677,7 @@ def run_gpu_replay(args, rank, world, local_rank, sub=False):
                 "what": "configs[3]: 32 scans per step and rank through ndtb_align_batch from pinned host buffers against the replicated 1M-pt map "
                         "(built once), scans sharded by rank, no collective"}
     b_eval = N_SCAN * (16 + 8 * 7 + 64 * hbar)
-    t_eval = ms * 1e-3 / st["evals"]        # wall time per evaluation with two alignments in flight: the GPU is never idle
+    t_eval = ms * 1e-3 / st["evals"]        # wall time per evaluation with three alignments in flight: the GPU is never idle
     peak, peak_src = measured_peak()
     v = world * steps * B / (ms * 1e-3)
     return {"metric": "NDT align scans/sec @131k pts (1/2/4/8 B200) + % gather-BW roofline vs CPU OMP", "value": v, "unit": "scans/s",
@@ -688,7 +688,7 @@ def run_gpu_replay(args, rank, world, local_rank, sub=False):
                        "scans_per_step_per_rank": B, "parallelism": f"scan shards x{world} (no collective)", "l2": "256 MB flush between timed steps",
                        "evaluations_per_scan": st["evals"] / (steps * B), "max_abs_translation_error_m": st["err"],
                        "serial_scans_per_s": world * steps * B / (ms_serial * 1e-3),
-                       "note": "value == e2e: the batch entry point takes host buffers; two alignments are kept in flight on one stream "
+                       "note": "value == e2e: the batch entry point takes host buffers; three alignments are kept in flight on one stream "
                                "(serial_scans_per_s is the same batch with batch_interleave = 0)"},
             "e2e": {"value": v, "unit": "scans/s", "h2d_bytes_per_step": 16 * N_SCAN * B, "d2h_bytes_per_step": int(736 * st["evals"] / steps), "ms_per_step": ms / steps},
             "gpu_launches": launches,
