@@ -151,3 +151,29 @@ def test_device_newton_step_against_the_host_step():
         d = ndtb.test_newton_step(0, g, H, np.zeros(6), 0.1, 0.005, 0.01, 35, True, 0, 0.0)
         h = ndtb.test_newton_step(1, g, H, np.zeros(6), 0.1, 0.005, 0.01, 35, True, 0, 0.0)
         assert d[0] == h[0] == 2
+
+
+def test_two_handles_from_two_threads(street):
+    """Two registrars driven from two host threads at once (slam-sam runs the odometry and the loop-closure registration in separate
+    threads): the cooperative sort kernel and the resident session kernel of one handle must not dead-lock the other's -- each
+    needs the whole GPU, the launches serialise -- and every result equals the single-threaded one."""
+    import threading
+
+    def work(out, reps):
+        h = ndtb.Handle(0)
+        h.set_params(resolution=1.0, search_method=ndtb.DIRECT7, max_iterations=35, trans_epsilon=0.01, step_size=0.1)
+        for _ in range(reps):
+            assert h.set_target(street["target"]) == 0 and h.set_source(street["source"]) == 0
+            out.append(h.align()["T"])
+
+    ref = []
+    work(ref, 1)
+    outs = [[], []]
+    ts = [threading.Thread(target=work, args=(outs[i], 12)) for i in range(2)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(timeout=120)
+        assert not t.is_alive(), "dead-lock between two handles"
+    for o in outs:
+        assert len(o) == 12 and all(np.array_equal(T, ref[0]) for T in o)
