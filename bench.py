@@ -254,6 +254,10 @@ def run_gpu(args, rank, world, local_rank):
     kf_P = np.ascontiguousarray(kf_poses, np.float64).reshape(n_kf, 16)
     kf_P_ptr = kf_P.ctypes.data_as(ndtb.c_d)
 
+    pipe_state = {"primed": False}
+    tgt_ptr = p_tgt.data_ptr()
+    scan_ptr = [t.data_ptr() for t in p_scans]
+
     def unpack(r):
         return dict(T=np.array(r.pose, np.float32).reshape(4, 4), iterations=r.iteration_num, converged=bool(r.converged), evaluations=r.evaluations)
 
@@ -288,11 +292,12 @@ def run_gpu(args, rank, world, local_rank):
             # the copy stream while step i's map is built and aligned; the step ends once that copy has arrived, so every timed
             # step contains one full 18 MB host-to-device copy
             kn = (i + 1) % len(scans)
-            if h.staged_count() == (0, 0):                                   # first step of a region: nothing was staged for it
-                rc = h.L.ndtb_stage_target(h.h, p_tgt.data_ptr(), N_MAP, 16) | h.L.ndtb_stage_source(h.h, p_scans[k].data_ptr(), N_SCAN, 16)
+            if not pipe_state["primed"]:                                     # first step of a region: nothing was staged for it
+                rc = h.L.ndtb_stage_target(h.h, tgt_ptr, N_MAP, 16) | h.L.ndtb_stage_source(h.h, scan_ptr[k], N_SCAN, 16)
                 assert rc == 0, h.L.ndtb_last_error(h.h)
-            rc = h.L.ndtb_stage_target(h.h, p_tgt.data_ptr(), N_MAP, 16)
-            rc |= h.L.ndtb_stage_source(h.h, p_scans[kn].data_ptr(), N_SCAN, 16)
+                pipe_state["primed"] = True
+            rc = h.L.ndtb_stage_target(h.h, tgt_ptr, N_MAP, 16)
+            rc |= h.L.ndtb_stage_source(h.h, scan_ptr[kn], N_SCAN, 16)
             rc |= h.L.ndtb_commit_target(h.h)
             rc |= h.L.ndtb_commit_source(h.h)
         assert rc == 0, h.L.ndtb_last_error(h.h)
@@ -346,6 +351,7 @@ def run_gpu(args, rank, world, local_rank):
     e2e_ms, st2 = timed(False, args.steps, args.warmup)
     while h.staged_count() != (0, 0):                                        # drain what the last pipelined step staged
         h.commit_target(); h.commit_source()
+    pipe_state["primed"] = False
     ser_ms, st6 = timed("serial", args.steps, args.warmup)
     win_ms, st4 = timed("window", args.steps, args.warmup)
     pkt_ms, st5 = timed("packets", args.steps, args.warmup)
