@@ -195,6 +195,8 @@ def run_gpu(args, rank, world, local_rank):
     tgt, scans, guesses, truths = make_workload(rank)
     h = ndtb.Handle(local_rank)  # no CPU fallback: raises if the CUDA library / device is missing
     h.set_params(resolution=RESOLUTION, max_iterations=35, trans_epsilon=0.01, step_size=0.1, search_method=ndtb.DIRECT7)
+    if os.environ.get("NDTB_BENCH_DEVICE_NEWTON") == "1":   # A/B aid: the resident kernel takes the Newton steps (opt-in)
+        h.set_option("device_newton", 1)
     stream = torch.cuda.ExternalStream(h.stream_ptr(), device=local_rank)
     # device-resident copies (value) and pinned host copies (e2e)
     d_tgt = torch.from_numpy(tgt).cuda()
@@ -425,6 +427,9 @@ def run_gpu(args, rank, world, local_rank):
                         "decode_algorithmic_bytes": int(n_pk * pk_bytes + 12 * 1024 * 128 + 42 * pk_state["points"]),
                         "decode_gbs": (n_pk * pk_bytes + 12 * 1024 * 128 + 42 * pk_state["points"]) / max(decode_us, 1e-3) / 1e3},
         "gpu_launches": launches,
+        "device_newton": dict(h.session_stats(), what="opt-in (NDTB_BENCH_DEVICE_NEWTON=1; off by default because the host step is faster, "
+                              "DESIGN 4.4): Newton steps the resident kernel took itself and the host confirmed word for word (accepted) / "
+                              "handed to the host (declined) / that the host had to repair (mismatches)"),
         "roofline": {"kernel": "eval_kernel_pclomp<7,hessian>", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": ncu_traffic(), "peak_source": peak_src, "algorithmic_bytes_per_launch": b_eval,
                      "mean_hits_per_point": hbar, "kernel_us": t_eval * 1e6,

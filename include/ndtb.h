@@ -378,8 +378,25 @@ int ndtb_set_profiling(ndtb_handle h, int per_kernel_events);
  *   "session_free_sms" (default 0)  the DIRECT1 / DIRECT7 evaluation kernels -- one CTA per SM, the resident kernel of an
  *                                align included -- leave this many of the 148 SMs to other streams, so that the lidar decode
  *                                or the window assembly of the NEXT frame can run while an align is open.  The per-CTA
- *                                partial sums change with the CTA count: results differ from the default by FP64 rounding. */
+ *                                partial sums change with the CTA count: results differ from the default by FP64 rounding.
+ *   "device_newton" (default 0)  1: the resident kernel of an align takes the Newton step between two evaluations itself (direction
+ *                                by pivoted elimination, step clamp, pose -> T, angle tables: ndt_omp_impl.hpp:128-190, 396-538) and
+ *                                starts the next evaluation without the PCIe round trip through the host.  The host still
+ *                                receives every result, repeats the step with the code the reference path uses (glibc sin / cos)
+ *                                and compares the device's next state with its own, word for word; on a difference it lets the
+ *                                kernel run out and evaluates its own state with one launch per evaluation, so results do not
+ *                                depend on this switch.  Steps that need the host (ill-conditioned H -> SVD, zero slope, the end
+ *                                of the loop, a regularisation pose, the line search) are taken by the host as with 0.
+ *                                Off by default: measured on a B200 the step costs ~14 us on the device (serial FP64 chains:
+ *                                18 dependent divisions) against the ~7 us round trip it replaces -- align 0.257 ms against 0.216.
+ *   "device_newton_fault_at" (default 0)  test hook: n > 0 makes the n-th comparison of every align fail. */
 int ndtb_set_option(ndtb_handle h, const char* name, double value);
+/* Life-time counters of the device Newton step: stats[0] steps taken on the device and confirmed by the host, stats[1] steps
+ * the device handed to the host, stats[2] comparisons that failed (each closes the resident kernel of that align), stats[3] 1 when
+ * the library's restatement of the host libm's sincosf (glibc >= 2.28, x86-64 FMA build) reproduces the running libm bit for bit
+ * on a sample of 24 000 arguments -- with 0 the device step is never used, whatever "device_newton" says.  h may be NULL (the
+ * counters then read 0; stats[3] needs no GPU). */
+int ndtb_get_session_stats(ndtb_handle h, unsigned long long stats[4]);
 /* The Newton-direction solve of ndtb_align on its own (host code, no GPU): x = H^-1 b by the path "direct_solver"
  * selects (method 1; falls back to the SVD when H is not certified well conditioned) or by the Jacobi SVD with
  * Eigen's rank threshold (method 0).  *used_direct reports which one produced x.  Parity hook for the tests. */

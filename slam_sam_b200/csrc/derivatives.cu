@@ -17,6 +17,7 @@
 #include "eval_api.cuh"
 #include "handle.cuh"       // ndtb_compute_derivatives_static (end of this file)
 #include "newton_math.cuh"
+#include "device_newton.cuh"
 #include <algorithm>
 #include <cstring>
 #include <string>
@@ -867,7 +868,8 @@ __device__ __forceinline__ void pclomp_eval_body(PclShared& sh, const float4* __
                                                  const VoxRec* __restrict__ recs, const HashSlot* __restrict__ table, const EvalState& st,
                                                  double* __restrict__ partials, double* __restrict__ results, unsigned int* __restrict__ tickets,
                                                  unsigned long long result_key, unsigned long long* __restrict__ dbg /* optional: 8 stamps per block */,
-                                                 unsigned long long t_seen /* session: globaltimer when the command was seen, else 0 */) {
+                                                 unsigned long long t_seen /* session: globaltimer when the command was seen, else 0 */,
+                                                 double* __restrict__ s_final = nullptr /* session: shared-memory copy of the RED_N sums (last CTA) */) {
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   auto stamp = [&](int k) {
     if (dbg && tid == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); dbg[8 * blockIdx.x + k] = t; }
@@ -990,6 +992,7 @@ __device__ __forceinline__ void pclomp_eval_body(PclShared& sh, const float4* __
         volatile unsigned long long* slot = reinterpret_cast<volatile unsigned long long*>(results) + 2 * c;
         slot[0] = bits;
         slot[1] = bits ^ result_key;
+        if (s_final) s_final[c] = sum;
       }
     }
     stamp(4);
@@ -1027,88 +1030,192 @@ struct PclSessionShared {
   SessionCmd cmd;
   unsigned long long t_seen;
 };
+// 196 KB is a shared-memory carve-out step of the SM: one byte more (with the 1 KB the system reserves per CTA) and the L1 that
+// caches the voxel-record gathers shrinks from 60 KB to 28 KB -- measured as +4 % on every evaluation.
+static_assert(sizeof(PclSessionShared) + 1024 <= 196 * 1024, "the session kernel must stay inside the 196 KB carve-out");
+// Device Newton step (SESSION_SPECULATE): scratch of warp 0 of the last CTA of an evaluation.  It lives in the transposition tile
+// of warp 1, which is idle then: every warp of the CTA has left its main loop before the final reduction writes final_sums, and
+// none re-enters it before warp 0 is back at the loop's barrier; the tile is rewritten before it is read in every round.
+struct NewtonArea {
+  double final_sums[RED_N];
+  SessionCmd next;
+  NewtonScratch newton;
+};
+static_assert(sizeof(NewtonArea) <= sizeof(WarpScratchP::tr) && offsetof(WarpScratchP, tr) % 16 == 0 && sizeof(WarpScratchP) % 16 == 0, "NewtonArea aliases warp 1's tile");
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
+__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
 
-template <int PROBES>
+// Speculation (SESSION_SPECULATE in a command): warp 0 of the LAST CTA of the evaluation takes the Newton step on the device
+// (newton_step_warp: direction, normalisation, step clamp, pose -> T and angle tables), writes the next command into d_cmd and
+// releases the next sequence number itself -- the other CTAs start the next evaluation ~3 us after the previous one ended
+// instead of after a PCIe round trip through the host (~7 us).  The host still receives every result, repeats the step with
+// its own code (glibc sin / cos) and compares the command the device built, word for word, with its own: equal -> nothing to
+// do, the evaluation is already running; different (an ulp of sin / cos that survives the rounding to float: ~1e-8 of the
+// steps) -> the host lets the kernel run out and repeats the evaluation with its own state, so results never depend on the
+// device's libm.  When the step needs the host (ill-conditioned H -> SVD, zero slope, convergence) the warp declines and CTA 0
+// polls the mailbox as usual.
+template <int PROBES, bool SPEC>
 __global__ void __launch_bounds__(PCL_THREADS, 1) align_session_kernel(const float4* __restrict__ src, int n, GridMeta m,
                                                                        const VoxRec* __restrict__ recs, const HashSlot* __restrict__ table,
                                                                        const ulonglong2* mailbox, unsigned long long* d_cmd,
                                                                        double* __restrict__ partials, double* __restrict__ results,
-                                                                       unsigned int* __restrict__ tickets, unsigned long long seq0,
-                                                                       unsigned long long idle_timeout_ns) {
+                                                                       ulonglong2* spec_record, unsigned int* __restrict__ tickets,
+                                                                       unsigned long long seq0, unsigned long long idle_timeout_ns) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   PclSessionShared& ss = *reinterpret_cast<PclSessionShared*>(smem_raw);
+  NewtonArea& na = *reinterpret_cast<NewtonArea*>(ss.sh.warp[1].tr);
   const int tid = threadIdx.x, lane = tid & 31;
   unsigned long long seq = seq0;
+  bool spec_prev = false;  // the evaluation that has just finished speculates: its last CTA releases `seq` or declines it
   for (;;) {
     ++seq;
     if (blockIdx.x == 0 && tid < 32) {
-      const unsigned long long key = session_key(seq);
-      const volatile ulonglong2* mb = mailbox;
-      const unsigned long long t_wait = globaltimer_ns();
-      unsigned long long w0 = 0, w1 = 0;
-      bool quit = false;
-      for (;;) {
-        const unsigned long long a0 = mb[lane].x, a1 = mb[lane].y, b0 = mb[32 + lane].x, b1 = mb[32 + lane].y;
-        w0 = a0; w1 = b0;
-        if (__all_sync(0xffffffffu, ((a0 ^ a1) == key) && ((b0 ^ b1) == key))) break;
-        const bool late = globaltimer_ns() - t_wait > idle_timeout_ns;
-        if (__shfl_sync(0xffffffffu, late ? 1 : 0, 0)) { quit = true; break; }
+      int released = 0;
+      if (SPEC && spec_prev) {
+        if (lane == 0) {  // no time-out: the last CTA does one or the other after a bounded amount of work of its own
+          for (;;) {
+            if (ld_acquire_u64(d_cmd + SESSION_SEQ_WORD) == seq) { released = 1; break; }
+            if (ld_acquire_u64(d_cmd + SESSION_DECLINE_WORD) == seq) break;
+          }
+        }
+        released = __shfl_sync(0xffffffffu, released, 0);
       }
-      d_cmd[lane] = w0;
-      d_cmd[32 + lane] = w1;
-      __syncwarp();
-      if (lane == 0) {
-        if (quit) d_cmd[SESSION_FLAGS_WORD] = SESSION_QUIT;
-        d_cmd[SESSION_TSEEN_WORD] = globaltimer_ns();
-        __threadfence();
-        asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(d_cmd + SESSION_SEQ_WORD), "l"(seq) : "memory");
+      if (!released) {
+        const unsigned long long key = session_key(seq);
+        const volatile ulonglong2* mb = mailbox;
+        const unsigned long long t_wait = globaltimer_ns();
+        unsigned long long w0 = 0, w1 = 0;
+        bool quit = false;
+        for (;;) {
+          const unsigned long long a0 = mb[lane].x, a1 = mb[lane].y, b0 = mb[32 + lane].x, b1 = mb[32 + lane].y;
+          w0 = a0; w1 = b0;
+          if (__all_sync(0xffffffffu, ((a0 ^ a1) == key) && ((b0 ^ b1) == key))) break;
+          const bool late = globaltimer_ns() - t_wait > idle_timeout_ns;
+          if (__shfl_sync(0xffffffffu, late ? 1 : 0, 0)) { quit = true; break; }
+        }
+        d_cmd[lane] = w0;
+        d_cmd[32 + lane] = w1;
+        __syncwarp();
+        if (lane == 0) {
+          if (quit) d_cmd[SESSION_FLAGS_WORD] = SESSION_QUIT;
+          d_cmd[SESSION_TSEEN_WORD] = globaltimer_ns();
+          __threadfence();
+          st_release_u64(d_cmd + SESSION_SEQ_WORD, seq);
+        }
       }
     }
     if (tid == 0) {
-      unsigned long long seen;
-      do {
-        asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(seen) : "l"(d_cmd + SESSION_SEQ_WORD) : "memory");
-      } while (seen != seq);
+      while (ld_acquire_u64(d_cmd + SESSION_SEQ_WORD) != seq) {}
     }
     __syncthreads();
     if (tid < SESSION_CMD_WORDS) reinterpret_cast<unsigned long long*>(&ss.cmd)[tid] = __ldcg(d_cmd + tid);
     if (tid == 64) ss.t_seen = __ldcg(d_cmd + SESSION_TSEEN_WORD);
     __syncthreads();
     if (ss.cmd.flags & SESSION_QUIT) return;
-    pclomp_eval_body<PROBES, true>(ss.sh, src, n, m, recs, table, ss.cmd.st, partials, results, tickets, ss.cmd.result_key, nullptr, ss.t_seen);
+    const bool spec = SPEC && (ss.cmd.flags & SESSION_SPECULATE) != 0;   // SPEC = false: the kernel without the step's code (the default)
+    // with the step, results and records are double-buffered by the parity of key_seq (eval_api.cuh): the host may be reading
+    // the previous evaluation's while this one is published
+    double* const res = SPEC ? reinterpret_cast<double*>(spec_record + SESSION_SPEC_RESULT_UNIT0 + (ss.cmd.key_seq & 1ull) * SESSION_SPEC_RESULT_UNITS) : results;
+    pclomp_eval_body<PROBES, true>(ss.sh, src, n, m, recs, table, ss.cmd.st, partials, res, tickets, ss.cmd.result_key, nullptr, ss.t_seen,
+                                   spec ? na.final_sums : nullptr);
+    __syncthreads();
+#ifdef NDTB_NEWTON_TIMING
+    const unsigned long long t_reduced = globaltimer_ns();
+#endif
+    if constexpr (SPEC) if (spec && ss.sh.last && tid < 32) {
+      // flow control: the next evaluation's results land where those of evaluation key_seq - 1 are -- the host must have read
+      // them.  The acknowledgement is fetched over PCIe now and looked at after the step (~1.5 us, hidden behind it).
+      const volatile unsigned long long* ack = reinterpret_cast<const volatile unsigned long long*>(spec_record + SESSION_SPEC_ACK_UNIT);
+      const unsigned long long ack0 = ack[0];   // one aligned 8-byte word: no tearing, and an old value only errs on the safe side
+      NewtonParams prm;
+      prm.step_max = ss.cmd.step_max; prm.step_min = ss.cmd.step_min; prm.trans_eps = ss.cmd.trans_eps; prm.max_iterations = ss.cmd.max_iterations; prm.pad = 0;
+      NewtonCarry carry;
+      carry.a_t = ss.cmd.a_t; carry.nr_iterations = static_cast<int>(ss.cmd.nr_iterations); carry.first = ss.cmd.first;
+      int status = newton_step_warp(na.final_sums + RED_G, na.final_sums + RED_H, ss.cmd.st, carry, prm, &na.next.st, na.newton);
+      if (status == NEWTON_CONTINUE && !(ack0 + 1 >= ss.cmd.key_seq)) status = NEWTON_FLOW;
+      const unsigned long long next_key = result_key_of(ss.cmd.key_seq + 1);
+      const unsigned long long* nw = reinterpret_cast<const unsigned long long*>(&na.next);
+      if (status == NEWTON_CONTINUE) {
+        if (lane == 0) {
+          na.next.result_key = next_key; na.next.flags = SESSION_SPECULATE;
+          na.next.step_max = prm.step_max; na.next.step_min = prm.step_min; na.next.trans_eps = prm.trans_eps; na.next.max_iterations = prm.max_iterations;
+          na.next.first = 0; na.next.a_t = carry.a_t; na.next.nr_iterations = static_cast<unsigned long long>(carry.nr_iterations);
+          na.next.key_seq = ss.cmd.key_seq + 1;
+        }
+        __syncwarp();
+        for (int i = lane; i < SESSION_CMD_WORDS; i += 32) d_cmd[i] = nw[i];
+        __syncwarp();
+        if (lane == 0) {
+          d_cmd[SESSION_TSEEN_WORD] = globaltimer_ns();
+          __threadfence();
+          st_release_u64(d_cmd + SESSION_SEQ_WORD, seq + 1);
+        }
+      } else if (lane == 0) {
+        st_release_u64(d_cmd + SESSION_DECLINE_WORD, seq + 1);
+      }
+#ifdef NDTB_NEWTON_TIMING
+      if (lane == 0 && status == NEWTON_CONTINUE) {   // d_cmd[67..]: summed phase durations + count, printed by session_end
+        const unsigned long long t_end = globaltimer_ns();
+        for (int k = 0; k < 6; ++k) d_cmd[67 + k] += na.newton.stamp[k + 1] - na.newton.stamp[k];
+        d_cmd[73] += t_end - na.newton.stamp[6];
+        d_cmd[74] += na.newton.stamp[0] - t_reduced;
+        d_cmd[75] += 1;
+      }
+#endif
+      // the record the host compares with its own step (self-validating units, off the critical path)
+      volatile ulonglong2* rec = spec_record + ((ss.cmd.key_seq + 1) & 1ull) * SESSION_UNITS;
+      if (status == NEWTON_CONTINUE)
+        for (int i = lane; i < SESSION_CMD_WORDS; i += 32) { rec[i].x = nw[i]; rec[i].y = nw[i] ^ next_key; }
+      if (lane == 0) {
+        const unsigned long long sw = ((seq + 1) << 8) | static_cast<unsigned long long>(status);
+        rec[SESSION_SPEC_STATUS_UNIT].x = sw;
+        rec[SESSION_SPEC_STATUS_UNIT].y = sw ^ next_key;
+      }
+    }
+    spec_prev = spec;
     __syncthreads();
   }
 }
 
-template <int PROBES>
+template <int PROBES, bool SPEC>
 static cudaError_t launch_session_t(const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs, const HashSlot* table,
                                     const ulonglong2* mailbox, unsigned long long* d_cmd, const EvalBuffers& b, double* results,
-                                    unsigned long long seq0, unsigned long long idle_timeout_ns, cudaStream_t stream) {
+                                    ulonglong2* spec_record, unsigned long long seq0, unsigned long long idle_timeout_ns, cudaStream_t stream) {
   static bool configured[MAX_DEVICES] = {};
   if (needs_func_setup(configured)) {
-    cudaError_t e = cudaFuncSetAttribute(align_session_kernel<PROBES>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(PclSessionShared)));
+    cudaError_t e = cudaFuncSetAttribute(align_session_kernel<PROBES, SPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(sizeof(PclSessionShared)));
     if (e != cudaSuccess) return e;
   }
   GridMeta m = meta;
   double* partials = b.d_partials;
   unsigned int* tickets = b.d_tickets;
-  void* args[] = {&d_src, &n, &m, &recs, &table, &mailbox, &d_cmd, &partials, &results, &tickets, &seq0, &idle_timeout_ns};
+  void* args[] = {&d_src, &n, &m, &recs, &table, &mailbox, &d_cmd, &partials, &results, &spec_record, &tickets, &seq0, &idle_timeout_ns};
   // cooperative launch: fails (instead of deadlocking on the inter-CTA spin) if the CTAs cannot all be resident at once
-  return cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(align_session_kernel<PROBES>), dim3(eval_blocks_pclomp(n, b.free_sms)), dim3(PCL_THREADS), args,
+  return cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(align_session_kernel<PROBES, SPEC>), dim3(eval_blocks_pclomp(n, b.free_sms)), dim3(PCL_THREADS), args,
                                      sizeof(PclSessionShared), stream);
 }
 
 cudaError_t launch_align_session(int n_probe, const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs, const HashSlot* table,
                                  const ulonglong2* mailbox, unsigned long long* d_cmd, const EvalBuffers& b, double* results,
-                                 unsigned long long seq0, unsigned long long idle_timeout_ns, cudaStream_t stream) {
-  return n_probe == 7 ? launch_session_t<7>(d_src, n, meta, recs, table, mailbox, d_cmd, b, results, seq0, idle_timeout_ns, stream)
-                      : launch_session_t<1>(d_src, n, meta, recs, table, mailbox, d_cmd, b, results, seq0, idle_timeout_ns, stream);
+                                 ulonglong2* spec_record, unsigned long long seq0, unsigned long long idle_timeout_ns, cudaStream_t stream) {
+  // spec_record == nullptr: the kernel without the device Newton step (it ignores SESSION_SPECULATE)
+  if (spec_record)
+    return n_probe == 7 ? launch_session_t<7, true>(d_src, n, meta, recs, table, mailbox, d_cmd, b, results, spec_record, seq0, idle_timeout_ns, stream)
+                        : launch_session_t<1, true>(d_src, n, meta, recs, table, mailbox, d_cmd, b, results, spec_record, seq0, idle_timeout_ns, stream);
+  return n_probe == 7 ? launch_session_t<7, false>(d_src, n, meta, recs, table, mailbox, d_cmd, b, results, spec_record, seq0, idle_timeout_ns, stream)
+                      : launch_session_t<1, false>(d_src, n, meta, recs, table, mailbox, d_cmd, b, results, spec_record, seq0, idle_timeout_ns, stream);
 }
 
 // Generic (svn) kernel: one resident wave of 148 SMs x EVAL_MIN_BLOCKS CTAs (register-limited); the cloud is dealt to the warps round-robin.

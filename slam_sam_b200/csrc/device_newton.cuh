@@ -3,9 +3,10 @@
 // order, spread over the lanes), normalisation, descent-direction flip, step clamp (computeStepLengthMT's first trial, :915-990),
 // pose -> float 4x4 and the angle tables of the next evaluation.  One thread would need ~10 us for this chain (as long as the PCIe
 // round trip to the host it replaces); a warp needs ~3 us.  Every arithmetic result is bit-identical to the host code: each
-// matrix entry sees the same operations, sums keep their order, only independent entries are computed side by side.  The one
-// exception is libm: sin / cos come from CUDA's FP64 routines, which differ from glibc's by an ulp for some arguments -- after
-// the rounding to float of the tables and of T that shows in ~1e-8 of the values (newton_math.cuh, nm_sinf).
+// matrix entry sees the same operations, sums keep their order, only independent entries are computed side by side.  libm: the
+// float sin / cos of T restate glibc's sincosf operation by operation (nm_sincosf_glibc, newton_math.cuh: bit-identical); the
+// FP64 sin / cos of the angle tables come from CUDA's routines, an ulp from glibc's for some arguments, which survives the
+// rounding to float of a table entry in ~1e-8 of the cases -- the host compares every step (eval_pclomp) and takes over then.
 #pragma once
 #include "ndtb_internal.cuh"
 #include "newton_math.cuh"
@@ -24,7 +25,14 @@ struct NewtonCarry {       // travels from one evaluation of an align to the nex
 };
 constexpr int NEWTON_CONTINUE = 0;   // st_out holds the state of the next evaluation
 constexpr int NEWTON_CONVERGED = 1;  // the loop's convergence test fired: no further evaluation
+constexpr int NEWTON_FLOW = 3;       // (session kernel) the host has not yet read the results two evaluations back: wait for it
 constexpr int NEWTON_HOST = 2;       // the host decides: ill-conditioned H (SVD), zero or NaN step, zero slope
+
+#ifdef NDTB_NEWTON_TIMING   // development aid: globaltimer stamps of the phases of one step (lane 0), read by the session kernel
+#define NEWTON_STAMP(k) do { if (lane == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); s.stamp[k] = t_; } } while (0)
+#else
+#define NEWTON_STAMP(k) do { } while (0)
+#endif
 
 struct NewtonScratch {     // shared memory of the warp
   double M[36];
@@ -32,12 +40,16 @@ struct NewtonScratch {     // shared memory of the warp
   double sc[12];           // sin / cos of the three angles: double argument (tables) and float argument (T)
   int rowperm[6], colperm[6];
   int status;
+#ifdef NDTB_NEWTON_TIMING
+  unsigned long long stamp[8];
+#endif
 };
 
 // All 32 lanes of one warp call this with the same arguments.  g / H: gradient and Hessian of the evaluation at st_in.p.
 __device__ inline int newton_step_warp(const double* __restrict__ g, const double* __restrict__ H, const EvalState& st_in, NewtonCarry& carry,
                                        const NewtonParams& prm, EvalState* __restrict__ st_out, NewtonScratch& s) {
   const int lane = threadIdx.x & 31;
+  NEWTON_STAMP(0);
   // ---- finish the iteration whose evaluation this was (ndt_omp_impl.hpp:176-186)
   if (!carry.first) {
     if (carry.nr_iterations > prm.max_iterations || (carry.nr_iterations && (fabs(carry.a_t) < prm.trans_eps))) return NEWTON_CONVERGED;
@@ -100,6 +112,7 @@ __device__ inline int newton_step_warp(const double* __restrict__ g, const doubl
     }
     __syncwarp();
   }
+  NEWTON_STAMP(1);
   // the two triangular solves + one refinement step: short dependent chains, lane 0; the residual on six lanes
   for (int pass = 0; pass < 2; ++pass) {
     if (lane == 0) {
@@ -128,6 +141,7 @@ __device__ inline int newton_step_warp(const double* __restrict__ g, const doubl
       __syncwarp();
     }
   }
+  NEWTON_STAMP(2);
   // ---- the step (lane 0: a handful of dependent operations)
   if (lane == 0) {
     int status = NEWTON_CONTINUE;
@@ -160,15 +174,24 @@ __device__ inline int newton_step_warp(const double* __restrict__ g, const doubl
   const int status = s.status;
   carry.a_t = __shfl_sync(0xffffffffu, carry.a_t, 0);
   if (status != NEWTON_CONTINUE) return status;
-  // ---- state of the next evaluation: six sin / cos pairs side by side, then the tables and T
-  if (lane < 12) {
+  NEWTON_STAMP(3);
+  // ---- state of the next evaluation: sin / cos side by side -- lanes 0..5 the double arguments (angle tables), lanes 6..8 the
+  // float arguments (T) through the restatement of the host's sincosf (newton_math.cuh); an angle it does not cover -> host
+  bool covered = true;
+  if (lane < 6) {
     const int a = lane % 3;
-    const bool for_T = lane >= 6;                       // lanes 0..5: double argument (angle tables), 6..11: float argument (T)
-    const bool want_cos = (lane % 6) >= 3;
-    const double x = for_T ? static_cast<double>(static_cast<float>(s.x_t[3 + a])) : s.x_t[3 + a];
-    s.sc[lane] = want_cos ? cos(x) : sin(x);
+    const double x = s.x_t[3 + a];
+    s.sc[lane] = (lane >= 3) ? cos(x) : sin(x);
+  } else if (lane < 9) {
+    const int a = lane - 6;
+    float sv = 0.0f, cv = 1.0f;
+    covered = nm_sincosf_glibc(static_cast<float>(s.x_t[3 + a]), &sv, &cv);
+    s.sc[6 + a] = static_cast<double>(sv);
+    s.sc[9 + a] = static_cast<double>(cv);
   }
+  if (!__all_sync(0xffffffffu, covered)) return NEWTON_HOST;
   __syncwarp();
+  NEWTON_STAMP(4);
   if (lane == 0) {
     // angle_tables(x_t, 10e-5): the snap of ndt_omp_impl.hpp:401-437
     const double snap = 10e-5;
@@ -212,6 +235,7 @@ __device__ inline int newton_step_warp(const double* __restrict__ g, const doubl
       if (e < 24) st_out->jang[e] = static_cast<float>(v); else st_out->hang[e - 24] = static_cast<float>(v);
     }
   }
+  NEWTON_STAMP(5);
   if (lane == 0) {
     // pose_to_T(x_t): Translation * Rx * Ry * Rz in float (Eigen::AngleAxis<float>::toRotationMatrix for a unit axis)
     float Rm[3][9];
@@ -242,6 +266,7 @@ __device__ inline int newton_step_warp(const double* __restrict__ g, const doubl
     for (int i = 0; i < 6; ++i) st_out->p[i] = s.x_t[i];
   }
   __syncwarp();
+  NEWTON_STAMP(6);
   return NEWTON_CONTINUE;
 }
 

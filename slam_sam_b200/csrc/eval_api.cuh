@@ -64,20 +64,40 @@ int eval_blocks_pclomp(int n, int free_sms = 0);
 struct SessionCmd {
   EvalState st;
   unsigned long long result_key;  // key of the result slots of this evaluation
-  unsigned long long flags;       // SESSION_QUIT
+  unsigned long long flags;       // SESSION_QUIT, SESSION_SPECULATE
+  // SESSION_SPECULATE: what the last CTA of this evaluation needs to take the Newton step itself and start the next evaluation
+  // without waiting for the host (device_newton.cuh); the host repeats the step and compares, see eval_pclomp()
+  double step_max, step_min, trans_eps;
+  int max_iterations;
+  int first;                      // 1: this is the evaluation at the initial guess
+  double a_t;                     // step length that led to this evaluation
+  unsigned long long nr_iterations;
+  unsigned long long key_seq;     // result_key == result_key_of(key_seq); the next evaluation's is result_key_of(key_seq + 1)
 };
 constexpr int SESSION_CMD_WORDS = static_cast<int>(sizeof(SessionCmd) / 8);
-constexpr int SESSION_FLAGS_WORD = SESSION_CMD_WORDS - 1;
+constexpr int SESSION_FLAGS_WORD = static_cast<int>((sizeof(EvalState) + 8) / 8);
 constexpr int SESSION_UNITS = 64;           // mailbox units (16 bytes each)
-constexpr int SESSION_SEQ_WORD = 64;        // d_cmd[64]: sequence number released by CTA 0
+constexpr int SESSION_SEQ_WORD = 64;        // d_cmd[64]: sequence number released by CTA 0 (or by the last CTA of a speculating evaluation)
 constexpr int SESSION_TSEEN_WORD = 65;      // d_cmd[65]: globaltimer when CTA 0 saw the command
+constexpr int SESSION_DECLINE_WORD = 66;    // d_cmd[66]: sequence number the last CTA will NOT release itself (CTA 0 polls the mailbox for it)
 constexpr int SESSION_DCMD_WORDS = 80;
+constexpr int SESSION_SPEC_STATUS_UNIT = 62;  // unit of a speculation record that holds the Newton status
+// Speculation area (pinned host memory, 16-byte units), everything double-buffered by the parity of the evaluation's key_seq so
+// that the device may run at most two evaluations ahead of the host:
+//   units [0, 128)    two records: the command the device built for evaluation key_seq + its status
+//   units [128, 224)  two result-slot sets (RED_N + 1 self-validating slots each) of the session's evaluations
+//   unit  224         the host's acknowledgement (one 8-byte word s): it has read the results of every evaluation up to key_seq s
+constexpr int SESSION_SPEC_RESULT_UNIT0 = 128, SESSION_SPEC_RESULT_UNITS = 48, SESSION_SPEC_ACK_UNIT = 224, SESSION_SPEC_AREA_UNITS = 256;
+static_assert(SESSION_SPEC_RESULT_UNITS >= RED_N + 1, "a result-slot set holds RED_N values and the duration");
 constexpr unsigned long long SESSION_QUIT = 1ull;
-static_assert(sizeof(SessionCmd) % 8 == 0 && SESSION_CMD_WORDS <= SESSION_UNITS, "command must fit the mailbox");
+constexpr unsigned long long SESSION_SPECULATE = 2ull;
+static_assert(sizeof(SessionCmd) % 8 == 0 && SESSION_CMD_WORDS <= SESSION_SPEC_STATUS_UNIT, "command must fit the mailbox");
+static_assert(sizeof(EvalState) % 8 == 0, "the flags word is addressed by index");
+__host__ __device__ inline unsigned long long result_key_of(unsigned long long key_seq) { return (0x9E3779B97F4A7C15ull * key_seq) | 1ull; }
 __host__ __device__ inline unsigned long long session_key(unsigned long long seq) { return (0xD1B54A32D192ED03ull * seq) | 1ull; }
 
 cudaError_t launch_align_session(int n_probe, const float4* d_src, int n, const GridMeta& meta, const VoxRec* recs, const HashSlot* table,
                                  const ulonglong2* mailbox, unsigned long long* d_cmd, const EvalBuffers& bufs, double* results,
-                                 unsigned long long seq0, unsigned long long idle_timeout_ns, cudaStream_t stream);
+                                 ulonglong2* spec_record, unsigned long long seq0, unsigned long long idle_timeout_ns, cudaStream_t stream);
 
 }  // namespace ndtb

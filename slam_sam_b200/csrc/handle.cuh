@@ -66,6 +66,16 @@ struct ndtb_handle_s {
   double session_idle_ms = 50.0;        // the resident kernel leaves after this long without a command
   bool batch_interleave = true;         // ndtb_align_batch keeps three alignments in flight (ndtb_set_option "batch_interleave")
   bool direct_solver = true;            // Newton direction by pivoted elimination when well conditioned (ndtb_set_option)
+  // device Newton step inside the session kernel (SESSION_SPECULATE, derivatives.cu): the host repeats every step and compares
+  ulonglong2* h_spec = nullptr;         // pinned, SESSION_SPEC_AREA_UNITS x 16 bytes: records, result-slot sets and the host's acknowledgement (eval_api.cuh)
+  bool device_newton = false;           // ndtb_set_option "device_newton": opt-in, the host step is faster
+  bool session_spec = false;            // the resident kernel that is open was built with the step (align_session_kernel<., true>)
+  bool spec_armed = false;              // the command of the evaluation in flight allows the device to go on by itself
+  struct SpecCarry { double a_t = 0; int nr_iterations = 0; int first = 0; bool valid = false; } spec_carry;  // set by align_impl before each evaluation
+  unsigned long long spec_accepted = 0, spec_declined = 0, spec_mismatches = 0;  // life-time counters (ndtb_get_session_stats)
+  int spec_fault_at = 0, spec_checks = 0;   // test hook: the spec_fault_at-th comparison of an align is treated as a mismatch
+  unsigned long long seq_init[3] = {0, 0, 0};
+  volatile unsigned long long* pending_time_slots = nullptr;  // the result-slot set that evaluation was published to
   unsigned long long pending_time_key = 0;  // result key of the last session evaluation whose duration slot is unread
   double session_eval_ns = 0;           // device-side duration of the session evaluations of the last align
 

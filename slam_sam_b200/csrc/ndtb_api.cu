@@ -160,12 +160,20 @@ static int resolve_eval_events(ndtb_handle_s* h) {
 }
 
 // ---- alignment session (host side) ---------------------------------------------------------------------------
-static void session_send(ndtb_handle_s* h, const EvalState* st, unsigned long long result_key, unsigned long long flags) {
-  SessionCmd cmd;
+static void fill_session_cmd(ndtb_handle_s* h, SessionCmd& cmd, const EvalState* st, unsigned long long result_key, unsigned long long flags) {
   std::memset(&cmd, 0, sizeof(cmd));
   if (st) cmd.st = *st;
   cmd.result_key = result_key;
   cmd.flags = flags;
+  cmd.key_seq = h->flag_seq;        // result_key == result_key_of(key_seq); picks the result-slot set of a speculating session
+  if (flags & SESSION_SPECULATE) {  // what newton_step_warp needs: the constants of the loop and where the loop stands
+    cmd.step_max = h->params.step_size; cmd.step_min = h->params.trans_epsilon / 2; cmd.trans_eps = h->params.trans_epsilon;
+    cmd.max_iterations = h->params.max_iterations;
+    cmd.first = h->spec_carry.first; cmd.a_t = h->spec_carry.a_t; cmd.nr_iterations = static_cast<unsigned long long>(h->spec_carry.nr_iterations);
+  }
+}
+
+static void session_send(ndtb_handle_s* h, const SessionCmd& cmd) {
   unsigned long long words[SESSION_UNITS] = {0};
   std::memcpy(words, &cmd, sizeof(cmd));
   const unsigned long long key = session_key(++h->mail_seq);
@@ -174,10 +182,88 @@ static void session_send(ndtb_handle_s* h, const EvalState* st, unsigned long lo
   __sync_synchronize();
 }
 
+static inline void poll_backoff(unsigned int spins);
+
+// The device Newton step restates the sincosf of the host's libm (nm_sincosf_glibc).  Checked once per process against the libm
+// that is actually running -- through nm_sinf / nm_cosf, i.e. the very calls pose_to_T makes -- on 24 k arguments of every range;
+// another libm build (no FMA, another version) fails this check on ~1 % of them and the step then stays on the host.
+bool sincosf_port_matches_libm() {
+  static const bool ok = [] {
+    unsigned int state = 2463534242u;
+    auto next = [&state] { state = state * 1664525u + 1013904223u; return state; };
+    for (int i = 0; i < 24000; ++i) {
+      const unsigned int r = next();
+      const double u = static_cast<double>(next() >> 8) * (2.0 / 16777216.0) - 1.0;   // [-1, 1)
+      volatile float x = (i % 3 == 0) ? static_cast<float>(u * 119.0) : (i % 3 == 1) ? static_cast<float>(ldexp(u, -static_cast<int>(r % 30u))) : static_cast<float>(u * 3.3);
+      const float xa = x;
+      const float s = nm_sinf(xa), c = nm_cosf(xa);
+      float s2 = 0, c2 = 0;
+      if (!nm_sincosf_glibc(xa, &s2, &c2)) return false;
+      if (std::memcmp(&s, &s2, 4) != 0 || std::memcmp(&c, &c2, 4) != 0) return false;
+    }
+    return true;
+  }();
+  return ok;
+}
+
+// One self-validating unit {word, word ^ key} of the speculation record; false when the kernel has left the stream instead.
+static bool spec_wait_unit(ndtb_handle_s* h, unsigned long long key_seq, int unit, unsigned long long key, unsigned long long* word) {
+  volatile unsigned long long* rec = reinterpret_cast<volatile unsigned long long*>(h->h_spec + (key_seq & 1ull) * SESSION_UNITS);
+  unsigned int spins = 0;
+  for (;;) {
+    const unsigned long long w0 = rec[2 * unit], w1 = rec[2 * unit + 1];
+    if ((w0 ^ w1) == key) { *word = w0; return true; }
+    poll_backoff(spins);
+    if ((++spins & 4095u) == 0 && cudaStreamQuery(h->stream) != cudaErrorNotReady) {
+      const unsigned long long x0 = rec[2 * unit], x1 = rec[2 * unit + 1];
+      if ((x0 ^ x1) == key) { *word = x0; return true; }
+      return false;
+    }
+  }
+}
+
+// The resident kernel runs on by itself (a chain of speculated evaluations nobody will read) or has been lost: wait until it has
+// left -- at the latest one idle time-out after its chain ends -- and go on with one launch per evaluation.
+static void session_drain(ndtb_handle_s* h) {
+  cudaStreamSynchronize(h->stream);
+  cudaGetLastError();
+  h->session_open = false;
+  h->spec_armed = false;
+  h->pending_time_key = 0;
+}
+
+// Flow control of the device Newton step: the results of every evaluation up to key_seq have been read (the device lets the
+// evaluation after next overwrite them only then, align_session_kernel).
+static void spec_acknowledge(ndtb_handle_s* h, unsigned long long key_seq) {
+  volatile unsigned long long* ack = reinterpret_cast<volatile unsigned long long*>(h->h_spec + SESSION_SPEC_ACK_UNIT);
+  ack[0] = key_seq;   // one aligned 8-byte store
+  __sync_synchronize();
+}
+
+enum { SPEC_RUNNING = 0, SPEC_WAITING = 1, SPEC_DRAINED = 2 };
+// After an evaluation whose command carried SESSION_SPECULATE.  `key_seq` numbers the NEXT evaluation, `mine` is the command
+// the host would send for it.  SPEC_RUNNING: the device has started exactly that evaluation.  SPEC_WAITING: it declined (the step
+// needs the host) and polls the mailbox.  SPEC_DRAINED: it started something else, or its record never came -- session closed.
+static int spec_check(ndtb_handle_s* h, unsigned long long key_seq, const SessionCmd* mine) {
+  const unsigned long long key = result_key_of(key_seq);
+  unsigned long long sw = 0;
+  if (!spec_wait_unit(h, key_seq, SESSION_SPEC_STATUS_UNIT, key, &sw)) { h->spec_mismatches += 1; session_drain(h); return SPEC_DRAINED; }
+  if ((sw & 0xffull) != 0) { h->spec_declined += 1; return SPEC_WAITING; }   // NEWTON_CONVERGED / NEWTON_HOST / NEWTON_FLOW
+  bool match = mine != nullptr;
+  unsigned long long theirs[SESSION_CMD_WORDS];
+  for (int i = 0; i < SESSION_CMD_WORDS && match; ++i) match = spec_wait_unit(h, key_seq, i, key, &theirs[i]);
+  if (match) match = std::memcmp(theirs, mine, sizeof(SessionCmd)) == 0;
+  if (match && h->spec_fault_at && ++h->spec_checks == h->spec_fault_at) match = false;
+  if (!match) { h->spec_mismatches += 1; session_drain(h); return SPEC_DRAINED; }
+  h->mail_seq += 1;   // the device consumed a sequence number for the evaluation it started
+  h->spec_accepted += 1;
+  return SPEC_RUNNING;
+}
+
 // The duration slot of the previous session evaluation is published a little after its results: collect it late.
 static void session_collect_time(ndtb_handle_s* h) {
   if (!h->pending_time_key) return;
-  volatile unsigned long long* slots = reinterpret_cast<volatile unsigned long long*>(h->h_results);
+  volatile unsigned long long* slots = h->pending_time_slots;
   for (int spin = 0; spin < 200000; ++spin) {
     const unsigned long long w0 = slots[2 * RED_N], w1 = slots[2 * RED_N + 1];
     if ((w0 ^ w1) == h->pending_time_key) { h->session_eval_ns += static_cast<double>(w0); break; }
@@ -194,16 +280,26 @@ static void session_begin(ndtb_handle_s* h) {
   if (ensure_eval_buffers(h, 1, n) != NDTB_OK) return;
   if (!h->h_mailbox) {
     if (cudaMallocHost(&h->h_mailbox, SESSION_UNITS * sizeof(ulonglong2)) != cudaSuccess ||
+        cudaMallocHost(&h->h_spec, SESSION_SPEC_AREA_UNITS * sizeof(ulonglong2)) != cudaSuccess ||
         cudaMalloc(&h->d_cmd, SESSION_DCMD_WORDS * sizeof(unsigned long long)) != cudaSuccess) { cudaGetLastError(); h->use_sessions = false; return; }
     std::memset(h->h_mailbox, 0, SESSION_UNITS * sizeof(ulonglong2));
+    std::memset(h->h_spec, 0, SESSION_SPEC_AREA_UNITS * sizeof(ulonglong2));
   }
-  // the device copy of the sequence number starts at the value the kernel starts from
-  if (cudaMemcpyAsync(h->d_cmd + SESSION_SEQ_WORD, &h->mail_seq, sizeof(unsigned long long), cudaMemcpyHostToDevice, h->stream) != cudaSuccess) {
+  // the device copy of the sequence number starts at the value the kernel starts from; time stamp and decline word at zero
+  static_assert(SESSION_TSEEN_WORD == SESSION_SEQ_WORD + 1 && SESSION_DECLINE_WORD == SESSION_SEQ_WORD + 2, "one copy initialises the three words");
+  h->seq_init[0] = h->mail_seq; h->seq_init[1] = 0; h->seq_init[2] = 0;
+#ifdef NDTB_NEWTON_TIMING
+  { static bool cleared = false; if (!cleared) { cudaMemset(h->d_cmd + 67, 0, 9 * sizeof(unsigned long long)); cleared = true; } }
+#endif
+  h->spec_armed = false;
+  h->session_spec = h->device_newton && h->direct_solver && !h->has_reg_pose && sincosf_port_matches_libm();
+  if (h->session_spec) spec_acknowledge(h, h->flag_seq);   // nothing older than this session is waiting to be read
+  if (cudaMemcpyAsync(h->d_cmd + SESSION_SEQ_WORD, h->seq_init, sizeof(h->seq_init), cudaMemcpyHostToDevice, h->stream) != cudaSuccess) {
     cudaGetLastError(); h->use_sessions = false; return;
   }
   const int n_probe = (h->params.search_method == NDTB_DIRECT1) ? 1 : 7;
   const cudaError_t e = launch_align_session(n_probe, h->d_source, n, h->grid.meta, h->grid.recs, h->grid.table, h->h_mailbox, h->d_cmd, h->eval,
-                                             h->h_results, h->mail_seq, static_cast<unsigned long long>(h->session_idle_ms * 1e6), h->stream);
+                                             h->h_results, h->session_spec ? h->h_spec : nullptr, h->mail_seq, static_cast<unsigned long long>(h->session_idle_ms * 1e6), h->stream);
   if (e != cudaSuccess) { cudaGetLastError(); h->use_sessions = false; return; }  // e.g. the CTAs cannot be co-resident: one-shot launches
   h->session_open = true;
   h->launches += 1;
@@ -212,8 +308,29 @@ static void session_begin(ndtb_handle_s* h) {
 static void session_end(ndtb_handle_s* h) {
   if (!h->session_open) return;
   session_collect_time(h);
-  session_send(h, nullptr, 0, SESSION_QUIT);
+  if (h->spec_armed) {
+    // the last command allowed the device to go on: it must have declined (the loop is over), else nobody reads what it computes
+    h->spec_armed = false;
+    if (spec_check(h, static_cast<unsigned long long>(h->flag_seq) + 1, nullptr) != SPEC_WAITING) return;
+  }
+  SessionCmd quit;
+  fill_session_cmd(h, quit, nullptr, 0, SESSION_QUIT);
+  session_send(h, quit);
   h->session_open = false;
+#ifdef NDTB_NEWTON_TIMING
+  {
+    static unsigned long long acc[9] = {0}, sessions = 0;
+    unsigned long long w[9];
+    cudaStreamSynchronize(h->stream);
+    cudaMemcpy(w, h->d_cmd + 67, sizeof(w), cudaMemcpyDeviceToHost);
+    cudaMemset(h->d_cmd + 67, 0, sizeof(w));
+    for (int i = 0; i < 9; ++i) acc[i] += w[i];
+    if ((++sessions % 100) == 0 && acc[8])
+      fprintf(stderr, "[newton timing, %llu steps] ns/step: load+eliminate %.0f | tri-solves %.0f | step %.0f | sincos %.0f | tables %.0f | T %.0f | compose+release %.0f | barrier->start %.0f\n",
+              acc[8], acc[0] / (double)acc[8], acc[1] / (double)acc[8], acc[2] / (double)acc[8], acc[3] / (double)acc[8], acc[4] / (double)acc[8],
+              acc[5] / (double)acc[8], acc[6] / (double)acc[8], acc[7] / (double)acc[8]);
+  }
+#endif
 }
 
 void finish_eval(ndtb_handle_s* h, int n, const double* r, const double* p, double* score, double* g, double* H, double* nvtl);
@@ -229,6 +346,13 @@ static inline void poll_backoff(unsigned int spins) {
     struct timespec ts = {0, 50000};
     nanosleep(&ts, nullptr);
   }
+}
+
+// Result slots of the session evaluation numbered h->flag_seq: the handle's own set, or -- with the device Newton step -- one of
+// the two sets of the speculation area.
+static volatile unsigned long long* session_slots(ndtb_handle_s* h) {
+  if (!h->session_spec) return reinterpret_cast<volatile unsigned long long*>(h->h_results);
+  return reinterpret_cast<volatile unsigned long long*>(h->h_spec + SESSION_SPEC_RESULT_UNIT0 + (h->flag_seq & 1u) * SESSION_SPEC_RESULT_UNITS);
 }
 
 // One pclomp evaluation: upload state, launch, read back the 46-double result, apply the
@@ -272,13 +396,28 @@ static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool
   static const bool dbg_on = getenv("NDTB_DEBUG_TIMING") != nullptr;
   double rbuf[RED_N];
   for (int attempt = 0;; ++attempt) {
-    const unsigned long long key = 0x9E3779B97F4A7C15ull * static_cast<unsigned long long>(++h->flag_seq) | 1ull;
+    const unsigned long long key = result_key_of(static_cast<unsigned long long>(++h->flag_seq));
     const bool via_session = h->session_open && compute_hessian && !dbg_on;
     if (via_session) {
-      // one command into the resident kernel's mailbox; it answers through the same result slots
+      // one command into the resident kernel's mailbox; it answers through the same result slots.  With the device Newton step
+      // the kernel may already have started this very evaluation (see align_session_kernel): then there is nothing to send.
       session_collect_time(h);
-      session_send(h, &h->h_states[0], key, 0);
+      const bool speculate = h->session_spec && h->spec_carry.valid && h->direct_solver && !h->has_reg_pose;
+      SessionCmd cmd;
+      fill_session_cmd(h, cmd, &h->h_states[0], key, speculate ? SESSION_SPECULATE : 0);
+      int state = SPEC_WAITING;
+      if (h->spec_armed) {
+        h->spec_armed = false;
+        state = spec_check(h, h->flag_seq, speculate ? &cmd : nullptr);
+        if (state == SPEC_DRAINED) continue;   // the session is closed: this evaluation again, as a one-shot launch
+      }
+      if (state == SPEC_WAITING) session_send(h, cmd);
+      // after this evaluation the device's step starts with the loop's convergence test: when that will fire, it declines
+      const ndtb_handle_s::SpecCarry& c = h->spec_carry;
+      const bool loop_ends = !c.first && (c.nr_iterations > h->params.max_iterations || (c.nr_iterations && std::fabs(c.a_t) < h->params.trans_epsilon));
+      h->spec_armed = speculate && !loop_ends;
       h->pending_time_key = key;
+      h->pending_time_slots = session_slots(h);
     } else {
       if (h->session_open) session_end(h);  // an evaluation the session kernel does not serve: it leaves, the launch queues behind it
       if (e0) cudaEventRecord(e0, h->stream);
@@ -292,7 +431,7 @@ static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool
       h->launches += 1;
     }
     bool lost = false;
-    volatile unsigned long long* slots = reinterpret_cast<volatile unsigned long long*>(h->h_results);
+    volatile unsigned long long* slots = via_session ? session_slots(h) : reinterpret_cast<volatile unsigned long long*>(h->h_results);
     unsigned int spins = 0;
     for (int c = RED_N - 1; c >= 0 && !lost; --c) {
       for (;;) {
@@ -312,7 +451,10 @@ static int eval_pclomp(ndtb_handle_s* h, const double* p, const float* T16, bool
         }
       }
     }
-    if (!lost) break;
+    if (!lost) {
+      if (via_session && h->session_spec) spec_acknowledge(h, h->flag_seq);
+      break;
+    }
     h->session_open = false;
     h->pending_time_key = 0;
   }
@@ -416,6 +558,7 @@ int ndtb_destroy(ndtb_handle h) {
   if (h->h_results) cudaFreeHost(h->h_results);
   if (h->h_flag) cudaFreeHost(const_cast<unsigned int*>(h->h_flag));
   if (h->h_mailbox) cudaFreeHost(h->h_mailbox);
+  if (h->h_spec) cudaFreeHost(h->h_spec);
   cudaFree(h->d_cmd);
   for (auto& kv : h->keyframes) cudaFree(kv.second.d_points);
   free_device_grid(h->ds_grid);
@@ -570,6 +713,13 @@ static int align_impl(ndtb_handle h, bool multigrid, const float guess[16], ndtb
     ~SessionGuard() { session_end(h); }
   } session_guard{h};
   if (!multigrid) session_begin(h);
+  // where the loop stands, for the device Newton step of the resident kernel (eval_pclomp reads it; invalid outside this loop)
+  struct CarryGuard {
+    ndtb_handle_s* h;
+    ~CarryGuard() { h->spec_carry.valid = false; }
+  } carry_guard{h};
+  h->spec_checks = 0;
+  h->spec_carry.a_t = 0; h->spec_carry.nr_iterations = 0; h->spec_carry.first = 1; h->spec_carry.valid = !multigrid;
   int rc = evaluate(p, final_T, true, &score, g, H, &nvtl);
   if (rc != NDTB_OK) return rc;
   push_trace(p);
@@ -612,10 +762,12 @@ static int align_impl(ndtb_handle h, bool multigrid, const float guess[16], ndtb
         double x_t[6];
         for (int i = 0; i < 6; ++i) x_t[i] = p[i] + delta_p[i] * a_t;
         pose_to_T(x_t, final_T);
+        h->spec_carry.a_t = a_t; h->spec_carry.nr_iterations = nr_iterations; h->spec_carry.first = 0;
         rc = evaluate(x_t, final_T, true, &score, g, H, &nvtl);
         if (rc != NDTB_OK) return rc;
         push_trace(x_t);
         if (P.use_line_search) {
+          h->spec_carry.valid = false;
           double phi_t = -score, d_phi_t = 0;
           for (int i = 0; i < 6; ++i) d_phi_t += g[i] * delta_p[i];
           d_phi_t = -d_phi_t;
@@ -872,8 +1024,17 @@ int ndtb_set_option(ndtb_handle h, const char* name, double value) {
     if (h->session_open) return set_error(h, NDTB_ERR_NOT_READY, "an alignment session is running");
     h->eval.free_sms = static_cast<int>(value);
   }
+  else if (k == "device_newton") h->device_newton = value != 0;       // 0: every Newton step of a session on the host (one PCIe round trip per evaluation)
+  else if (k == "device_newton_fault_at") h->spec_fault_at = static_cast<int>(value);  // test hook: that comparison of every align "fails"
   else if (k == "batch_interleave") h->batch_interleave = value != 0;  // 0: ndtb_align_batch aligns one scan after the other
   else return set_error(h, NDTB_ERR_INVALID, "unknown option");
+  return NDTB_OK;
+}
+
+int ndtb_get_session_stats(ndtb_handle h, unsigned long long stats[4]) {
+  if (!stats) return NDTB_ERR_INVALID;
+  stats[0] = h ? h->spec_accepted : 0; stats[1] = h ? h->spec_declined : 0; stats[2] = h ? h->spec_mismatches : 0;   // h may be NULL: stats[3] only
+  stats[3] = sincosf_port_matches_libm() ? 1ull : 0ull;
   return NDTB_OK;
 }
 

@@ -10,6 +10,7 @@
 #pragma once
 #include <math.h>
 #include <float.h>
+#include <string.h>
 #include <cuda_runtime.h>
 
 #define NM_HD __host__ __device__ inline
@@ -27,6 +28,61 @@ NM_HD float nm_sinf(float x) { return sinf(x); }
 NM_HD float nm_cosf(float x) { return cosf(x); }
 NM_HD float nm_atan2f(float y, float x) { return atan2f(y, x); }
 #endif
+
+// ---- sincosf as the host's libm computes it ---------------------------------------------------------------------
+// pose_to_T (below) is Eigen's AngleAxis<float>: std::sin / std::cos of a float, which gcc turns into ONE sincosf call.  glibc's
+// sincosf (sysdeps/ieee754/flt-32/s_sincosf.c, 2.28 and later; the x86-64 build selected on CPUs with FMA + AVX2) is a pair of
+// double-precision polynomials -- within 0.56 ulp, i.e. NOT the correctly rounded value for ~1 % of the arguments -- so a device
+// step that must land on the host's bits restates it operation by operation: the same products, the same fused multiply-adds
+// (IEEE operations, identical on both machines), the same two coefficient tables, the same quadrant logic.  Arguments of
+// magnitude >= 120 take glibc's large-argument reduction, which is not restated: the function then returns false.
+// nm_sincosf_port_matches_libm() checks the restatement against the running libm; the device Newton step is only used when
+// it holds (another libm build, e.g. the non-FMA one, would simply switch it off).
+NM_HD double nm_fma(double a, double b, double c) {
+#ifdef __CUDA_ARCH__
+  return __fma_rn(a, b, c);
+#else
+  return fma(a, b, c);
+#endif
+}
+NM_HD bool nm_sincosf_glibc(float xf, float* sp, float* cp) {
+  // c0, c1, c2, c3, c4, s1, s2, s3 of the two quadrant tables (the second one holds -cos)
+  const double C[2][5] = {{0x1p0, -0x1.ffffffd0c621cp-2, 0x1.55553e1068f19p-5, -0x1.6c087e89a359dp-10, 0x1.99343027bf8c3p-16},
+                          {-0x1p0, 0x1.ffffffd0c621cp-2, -0x1.55553e1068f19p-5, 0x1.6c087e89a359dp-10, -0x1.99343027bf8c3p-16}};
+  const double S1 = -0x1.555545995a603p-3, S2 = 0x1.1107605230bc4p-7, S3 = -0x1.994eb3774cf24p-13;
+  const double HPI_INV = 0x1.45f306dc9c883p+23 /* 2/pi * 2^24 */, HPI = 0x1.921fb54442d18p+0;
+  unsigned int bits;
+#ifdef __CUDA_ARCH__
+  bits = __float_as_uint(xf);
+#else
+  memcpy(&bits, &xf, 4);
+#endif
+  const unsigned int top = (bits >> 20) & 0x7ffu;
+  const double x = static_cast<double>(xf);
+  double xs, x2;
+  int n = 0;
+  if (top <= 0x3f3u) {            // |x| < 0.75
+    if (top <= 0x397u) { *sp = xf; *cp = 1.0f; return true; }   // |x| < 2^-12
+    xs = x; x2 = x * x;
+  } else if (top <= 0x42eu) {     // |x| < 120
+    const double r = x * HPI_INV;
+    n = (static_cast<int>(r) + 0x800000) >> 24;
+    const double xr = nm_fma(-static_cast<double>(n), HPI, x);
+    const double sign = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0;
+    xs = xr * sign; x2 = xr * xr;
+  } else {
+    return false;
+  }
+  const double* c = C[(n >> 1) & 1];
+  const double x3 = x2 * xs, x4 = x2 * x2;
+  const double sa = nm_fma(x2, S3, S2), ca = nm_fma(x2, c[4], c[3]);
+  const double x5 = x2 * x3, x6 = x2 * x4;
+  const double c01 = nm_fma(x2, c[1], c[0]);
+  const double sb = nm_fma(x3, S1, xs), cb = nm_fma(x4, c[2], c01);
+  const float sv = static_cast<float>(nm_fma(sa, x5, sb)), cv = static_cast<float>(nm_fma(ca, x6, cb));
+  if (n & 1) { *sp = cv; *cp = sv; } else { *sp = sv; *cp = cv; }
+  return true;
+}
 
 // ---- gauss constants ------------------------------------------------------------------------
 NM_HD void gauss_pclomp(double outlier_ratio, float resolution, double* d1, double* d2, double* d3) {

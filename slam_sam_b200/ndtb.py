@@ -51,7 +51,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_version", "nd
            "ndtb_compute_derivatives", "ndtb_align", "ndtb_get_trace", "ndtb_calculate_scores", "ndtb_get_voxel_count", "ndtb_get_voxels",
            "ndtb_get_last_hits", "ndtb_svn_default_params", "ndtb_svn_set_params", "ndtb_svn_particle_derivatives", "ndtb_svn_stage2",
            "ndtb_svn_step", "ndtb_svn_align", "ndtb_svn_stage1_local", "ndtb_svn_finish_step", "ndtb_align_batch", "ndtb_get_timings",
-           "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_set_profiling", "ndtb_set_option", "ndtb_time_eval_kernel", "ndtb_newton_direction", "ndtb_hessian_to_covariance", "ndtb_keyframe_put", "ndtb_keyframe_drop", "ndtb_keyframe_count",
+           "ndtb_get_stream", "ndtb_get_launch_count", "ndtb_get_session_stats", "ndtb_set_profiling", "ndtb_set_option", "ndtb_time_eval_kernel", "ndtb_newton_direction", "ndtb_hessian_to_covariance", "ndtb_keyframe_put", "ndtb_keyframe_drop", "ndtb_keyframe_count",
            "ndtb_set_target_window", "ndtb_get_target_points", "ndtb_voxelgrid_filter", "ndtb_svn_mean_pose", "ndtb_svn_pose_distance",
            "ndtb_lidar_default_config", "ndtb_lidar_create", "ndtb_lidar_destroy", "ndtb_lidar_last_error", "ndtb_lidar_packet_bytes",
            "ndtb_lidar_get_tables", "ndtb_lidar_push_packets", "ndtb_lidar_pop_frame", "ndtb_lidar_read_frame", "ndtb_lidar_frame_points",
@@ -145,6 +145,7 @@ def lib():
         L.ndtb_get_timings.argtypes = [H, c_f, c_f, c_f, c_i]
         L.ndtb_get_stream.argtypes = [H, C.POINTER(C.c_void_p)]
         L.ndtb_get_launch_count.argtypes = [H, C.POINTER(C.c_uint64)]
+        L.ndtb_get_session_stats.argtypes = [H, C.POINTER(C.c_ulonglong)]
         L.ndtb_set_profiling.argtypes = [H, C.c_int]
         L.ndtb_set_option.argtypes = [H, C.c_char_p, C.c_double]
         L.ndtb_time_eval_kernel.argtypes = [H, C.POINTER(C.c_double), C.POINTER(C.c_float), C.c_int, C.POINTER(C.c_float)]
@@ -512,6 +513,12 @@ class Handle:
         self.L.ndtb_get_launch_count(self.h, C.byref(n))
         return n.value
 
+    def session_stats(self):
+        """ndtb_get_session_stats: device Newton steps confirmed by the host / handed to the host / comparisons that failed."""
+        st = (C.c_ulonglong * 4)()
+        self.check(self.L.ndtb_get_session_stats(self.h, st))
+        return dict(accepted=int(st[0]), declined=int(st[1]), mismatches=int(st[2]), libm_port_ok=bool(st[3]))
+
     def set_profiling(self, on):
         self.check(self.L.ndtb_set_profiling(self.h, int(bool(on))))
 
@@ -563,7 +570,7 @@ class Handle:
         return float(us[0])
 
     def set_option(self, name, value):
-        """ndtb_set_option: "direct_solver", "sessions", "session_idle_timeout_ms", "session_free_sms", "batch_interleave"."""
+        """ndtb_set_option: "direct_solver", "sessions", "session_idle_timeout_ms", "session_free_sms", "device_newton", "batch_interleave"."""
         self.check(self.L.ndtb_set_option(self.h, name.encode(), float(value)))
 
     def stream_ptr(self):

@@ -69,3 +69,15 @@ def test_no_cpu_fallback_without_gpu():
     for f in os.listdir(os.path.join(ROOT, "slam_sam_b200", "csrc")):
         if f.endswith((".cu", ".cuh")):
             assert "oracle/" not in open(os.path.join(ROOT, "slam_sam_b200", "csrc", f)).read(), f
+
+
+def test_sincosf_restatement_matches_the_running_libm():
+    """The device Newton step of the resident align kernel restates glibc's sincosf (newton_math.cuh, nm_sincosf_glibc); the
+    library checks the restatement against the libm it runs with (24 000 arguments) and only then lets the device take steps.
+    Host code, no GPU: on this image (glibc 2.39, FMA build selected) it must hold."""
+    import ctypes as C
+
+    from slam_sam_b200 import ndtb
+    st = (C.c_ulonglong * 4)()
+    assert ndtb.lib().ndtb_get_session_stats(None, st) == 0
+    assert list(st) == [0, 0, 0, 1]
