@@ -986,15 +986,29 @@ __device__ __forceinline__ void pclomp_eval_body(PclShared& sh, const float4* __
 #pragma unroll
       for (int o = 1; o < 8; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
       if (l == 0 && valid) {
-        // Self-validating result slot {value, value ^ key}: two 8-byte stores, no system fence and no separate flag.
-        // The host accepts slot c once w0 ^ w1 == key (a stale half cannot satisfy it), see eval_pclomp().
+#ifdef NDTB_RESULTS_PER_LANE   // A/B aid: the 46 owners store their slot themselves (92 scattered 8-byte writes over PCIe)
         const unsigned long long bits = static_cast<unsigned long long>(__double_as_longlong(sum));
         volatile unsigned long long* slot = reinterpret_cast<volatile unsigned long long*>(results) + 2 * c;
         slot[0] = bits;
         slot[1] = bits ^ result_key;
+#else
+        sh.red[0][c] = sum;   // the block partials of sh.red were consumed two barriers ago
+#endif
         if (s_final) s_final[c] = sum;
       }
     }
+#ifndef NDTB_RESULTS_PER_LANE
+    // Self-validating result slots {value, value ^ key}: no system fence and no separate flag -- the host accepts slot c once
+    // w0 ^ w1 == key (a stale half cannot satisfy it), see eval_pclomp().  ONE warp publishes them as two coalesced runs of
+    // 16-byte stores (a handful of PCIe write packets instead of 92).
+    __syncthreads();
+    if (tid < 32) {
+      for (int c = tid; c < RED_N; c += 32) {
+        const unsigned long long bits = static_cast<unsigned long long>(__double_as_longlong(sh.red[0][c]));
+        asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(reinterpret_cast<unsigned long long*>(results) + 2 * c), "l"(bits), "l"(bits ^ result_key) : "memory");
+      }
+    }
+#endif
     stamp(4);
     if (t_seen && tid == 0) {  // session: device-side duration of this evaluation (command seen -> results stored), slot RED_N
       unsigned long long t;
@@ -1094,12 +1108,18 @@ __global__ void __launch_bounds__(PCL_THREADS, 1) align_session_kernel(const flo
       }
       if (!released) {
         const unsigned long long key = session_key(seq);
-        const volatile ulonglong2* mb = mailbox;
         const unsigned long long t_wait = globaltimer_ns();
         unsigned long long w0 = 0, w1 = 0;
         bool quit = false;
         for (;;) {
+#ifdef NDTB_RESULTS_PER_LANE
+          const volatile ulonglong2* mb = mailbox;
           const unsigned long long a0 = mb[lane].x, a1 = mb[lane].y, b0 = mb[32 + lane].x, b1 = mb[32 + lane].y;
+#else
+          unsigned long long a0, a1, b0, b1;   // two 16-byte loads per lane: half the PCIe read requests of four 8-byte ones
+          asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a0), "=l"(a1) : "l"(mailbox + lane) : "memory");
+          asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(b0), "=l"(b1) : "l"(mailbox + 32 + lane) : "memory");
+#endif
           w0 = a0; w1 = b0;
           if (__all_sync(0xffffffffu, ((a0 ^ a1) == key) && ((b0 ^ b1) == key))) break;
           const bool late = globaltimer_ns() - t_wait > idle_timeout_ns;
