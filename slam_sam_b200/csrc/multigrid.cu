@@ -52,7 +52,7 @@ struct MgState {
   float tree_resolution = 0.f;
   float4* d_in = nullptr; size_t in_alloc = 0; bool in_owned = true;  // upload scratch of add_target
   double* d_partials = nullptr; size_t partials_alloc = 0;
-  double* h_out = nullptr;               // pinned, RED_N doubles
+  double* h_out = nullptr;               // pinned, RED_N self-validating slots {bits, bits ^ key} (2 RED_N words)
 };
 
 struct MgEvalState {
@@ -395,15 +395,21 @@ __global__ void __launch_bounds__(MG_THREADS, MG_CTAS_PER_SM) mg_eval_kernel(con
 }
 
 // Block partials -> RED_N sums: one warp per component, lane l adds blocks l, l+32, ... in order, then a fixed
-// shuffle tree -> deterministic.  Written to pinned host memory.
+// shuffle tree -> deterministic.  Published to pinned host memory as self-validating slots {bits, bits ^ key} (publish_slot:
+// one coalesced run of 16-byte stores per CTA), which the host polls instead of synchronising the stream.
 constexpr int RED_WARPS = RED_N / 2;  // two CTAs of 23 warps
-__global__ void __launch_bounds__(32 * RED_WARPS) mg_reduce_kernel(const double* __restrict__ block_out, int blocks, double* __restrict__ out) {
+__global__ void __launch_bounds__(32 * RED_WARPS) mg_reduce_kernel(const double* __restrict__ block_out, int blocks, volatile unsigned long long* out_slots,
+                                                                   unsigned long long key) {
+  __shared__ double s_v[RED_WARPS];
   const int c = blockIdx.x * RED_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   double v = 0.0;
   for (int b = lane; b < blocks; b += 32) v += block_out[RED_N * static_cast<size_t>(b) + c];
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  if (lane == 0) out[c] = v;
+  if (lane == 0) s_v[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x < RED_WARPS)
+    publish_slot(out_slots, blockIdx.x * RED_WARPS + threadIdx.x, static_cast<unsigned long long>(__double_as_longlong(s_v[threadIdx.x])), key);
 }
 
 static void mg_angle_vectors(const double* p, double* jd, double* hd) {  // computeAngleDerivatives :498-586 (FP64 rows, snap 10e-5)
@@ -458,7 +464,11 @@ int mg_eval(ndtb_handle_s* h, const double* p, const float* T16, bool compute_he
     CKH(cudaMalloc(&s->d_partials, sizeof(double) * RED_N * 148 * 8));
     s->partials_alloc = static_cast<size_t>(RED_N) * 148 * 8;
   }
-  if (!s->h_out) CKH(cudaHostAlloc(&s->h_out, sizeof(double) * RED_N, cudaHostAllocDefault));
+  if (!s->h_out) {
+    CKH(cudaHostAlloc(&s->h_out, sizeof(double) * 2 * RED_N, cudaHostAllocDefault));
+    std::memset(s->h_out, 0, sizeof(double) * 2 * RED_N);
+  }
+  const unsigned long long key = (0x9E3779B97F4A7C15ull * static_cast<unsigned long long>(++h->flag_seq)) | 1ull;
   MgEvalState st;
   std::memcpy(st.T, T16, 12 * sizeof(float));
   mg_angle_vectors(p, st.jd, st.hd);
@@ -468,13 +478,34 @@ int mg_eval(ndtb_handle_s* h, const double* p, const float* T16, bool compute_he
   st.r2 = static_cast<float>(radius * radius);
   if (compute_hessian) mg_eval_kernel<true><<<blocks, MG_THREADS, 0, h->stream>>>(h->d_source, n, s->d_table, s->n_tree, st, s->d_partials);
   else mg_eval_kernel<false><<<blocks, MG_THREADS, 0, h->stream>>>(h->d_source, n, s->d_table, s->n_tree, st, s->d_partials);
-  mg_reduce_kernel<<<2, 32 * RED_WARPS, 0, h->stream>>>(s->d_partials, blocks, s->h_out);
+  volatile unsigned long long* slots = reinterpret_cast<volatile unsigned long long*>(s->h_out);
+  mg_reduce_kernel<<<2, 32 * RED_WARPS, 0, h->stream>>>(s->d_partials, blocks, slots, key);
   h->launches += 2;
   h->eval_launches += 1;
   CKH(cudaGetLastError());
-  CKH(cudaStreamSynchronize(h->stream));
+  // poll the slots (as eval_pclomp does) instead of synchronising the stream; a stream query every 4096 probes catches a failed launch
   double r[RED_N];
-  std::memcpy(r, s->h_out, sizeof(r));
+  unsigned int spins = 0;
+  for (int c = RED_N - 1; c >= 0; --c) {
+    for (;;) {
+      const unsigned long long w0 = slots[2 * c], w1 = slots[2 * c + 1];
+      if ((w0 ^ w1) == key) { std::memcpy(&r[c], &w0, 8); break; }
+#if defined(__x86_64__) || defined(__i386__)
+      __builtin_ia32_pause();
+#endif
+      if ((++spins & 4095u) == 0) {
+        const cudaError_t q = cudaStreamQuery(h->stream);
+        if (q != cudaSuccess && q != cudaErrorNotReady) { h->last_error = std::string("multigrid eval kernel: ") + cudaGetErrorString(q); return NDTB_ERR_CUDA; }
+        if (q == cudaSuccess) {
+          const unsigned long long x0 = slots[2 * c], x1 = slots[2 * c + 1];
+          if ((x0 ^ x1) == key) continue;
+          h->last_error = "multigrid eval kernel finished without publishing its result";
+          return NDTB_ERR_CUDA;
+        }
+      }
+    }
+  }
+  __sync_synchronize();
   finish_eval(h, n, r, p, score, g, H, nvtl);  // regulariser (:446-480) and NVTL (:482-488): same host epilogue as pclomp
   return NDTB_OK;
 }
